@@ -1,0 +1,190 @@
+/*
+ * svb200.h -- C ABI of libsvb200.so: the B200 (sm_100a) implementation of the per-frame hot path of
+ * thien/stereo.vision (disparity -> 3-D cloud -> RANSAC plane -> road points -> road mask).
+ *
+ * The reference has no native layer: its "operator interface" for this path is the set of Python
+ * helpers in functions.py that stereovision.py:58-140 calls.  Each entry point below states the
+ * helper(s) it replaces (file:line in the reference).  The Python drop-in module
+ * (stereo.vision_b200/functions.py) binds these with ctypes; INTEGRATION.md shows the stub.
+ *
+ * Conventions
+ *   - every data pointer is a CALLER-OWNED DEVICE pointer (e.g. torch.Tensor.data_ptr()) unless the
+ *     parameter name starts with h_ (host memory, read during the call only);
+ *   - images are C-contiguous uint8, [F,H,W] or [F,H,W,3] (BGR); F = frames in the batch;
+ *   - `stream` is a cudaStream_t passed as void* (torch.cuda.current_stream().cuda_stream);
+ *     all work is enqueued on it and the call returns without synchronising;
+ *   - return value: 0 = ok, < 0 = argument error (SVB_E_*), > 0 = a cudaError_t from the launch;
+ *   - nothing is allocated or retained: scratch comes from the caller, sizes from svb_*_bytes().
+ *
+ * Records
+ *   cloud  : uint64 per point,  bits  0-10 x | 11-21 y | 22-29 d | 30-31 hue&3   (low word)
+ *                               bits 32-39 R | 40-47 G | 48-55 B | 56-63 hue>>2  (high word)
+ *   mcloud : uint32 per point,  bits  0-10 x | 11-21 y | 22-29 d                 (masked cloud)
+ *   (x,y) = pixel site, d = uint8 disparity, hue = rint(1000*colorsys_hue) in [0,1000].
+ *   X,Y,Z are never stored: they are exact float64 functions of (x,y,d) (functions.py:191-193)
+ *   and are recomputed where needed, which is what makes the reprojection bit-exact.
+ *   Point order inside a frame is the reference's append order (row-major over the lattice).
+ *   Frame f of a batch owns the slab [f*cap, f*cap + n_f) of the record arrays, cap = lattice size.
+ */
+#ifndef SVB200_H
+#define SVB200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SVB_OK            0
+#define SVB_E_NULL       -1   /* required pointer is NULL */
+#define SVB_E_SHAPE      -2   /* H,W outside [2,2048], F < 1, step < 1, ... */
+#define SVB_E_ARG        -3   /* other invalid argument */
+#define SVB_E_SCRATCH    -4   /* scratch buffer too small */
+
+#define SVB_HUE_BINS     1001 /* keys '0.0' .. '1.0' of functions.py:76-78 */
+#define SVB_HIST_STRIDE  1024 /* uint32 per frame in histogram arrays */
+#define SVB_PLANE_STRIDE 8    /* doubles per frame in plane arrays, see svb_ransac_finalize */
+
+/* camera constants, functions.py:15-22 */
+typedef struct svb_camera {
+    double focal_px;     /* camera_focal_length_px  */
+    double baseline_m;   /* stereo_camera_baseline_m */
+    double centre_h;     /* image_centre_h */
+    double centre_w;     /* image_centre_w */
+} svb_camera;
+
+/* ABI version (bumped on any signature change) and a static description of an error code. */
+int         svb_version(void);
+const char *svb_error_string(int code);
+
+/* lattice visited by range(0,H-1,step) x range(0,W-1,step), functions.py:185-186 */
+int svb_lattice_rows(int H, int step);
+int svb_lattice_cols(int W, int step);
+
+/* ---- a1  fillDisparity / disparityCleaning('previous')            functions.py:130-147
+ * filled[t] = sat_add_u8(raw[t], (raw[t] <= 2) ? filled[t-1] : 0), filled[-1] = prev0.
+ * prev0 == NULL: frame 0 is copied unchanged (prev_disp is None, functions.py:134).
+ * The recurrence over t runs inside one launch (one thread owns 16 pixels for all F frames). */
+int svb_fill_sequence(const uint8_t *raw, const uint8_t *prev0, uint8_t *filled,
+                      int F, int H, int W, void *stream);
+
+/* ---- a2  maskDisparity                                             functions.py:169-172
+ * out = d where carmask != 0 else 0.  (a3 capDisparity is the identity, functions.py:164-167.) */
+int svb_mask_disparity(const uint8_t *d, const uint8_t *carmask, uint8_t *out,
+                       int F, int H, int W, void *stream);
+
+/* ---- a4  projectDisparityTo3d (both calls of stereovision.py:84-85)  functions.py:178-198
+ * For each frame: cloud  = lattice sites with d > 0, with RGB = bgr[y,x,2..0] and the hue bin;
+ *                 mcloud = lattice sites with d > 0 and carmask != 0 (no colour).
+ * Any of cloud / mcloud may be NULL (that output is skipped); bgr NULL -> colour bits are 0;
+ * carmask NULL -> every site counts as inside the mask.
+ * counts[f*4+0] = N_f (cloud), counts[f*4+1] = M_f (mcloud); entries 2,3 are left untouched.
+ * scratch: svb_project_scratch_bytes(F,H,W,step) bytes. */
+int64_t svb_project_scratch_bytes(int F, int H, int W, int step);
+int svb_project_compact(const uint8_t *disp, const uint8_t *carmask, const uint8_t *bgr,
+                        int F, int H, int W, int step, const svb_camera *cam,
+                        uint64_t *cloud, uint32_t *mcloud, int32_t *counts,
+                        void *scratch, int64_t scratch_bytes, void *stream);
+
+/* Materialise what the reference's list holds: xyz float64 [n,3] (functions.py:191-193, bit-exact),
+ * rgb uint8 [n,3] (functions.py:195), sites int32 [n,2] as (y,x), disparity uint8 [n].
+ * Any output may be NULL.  `rec_stride_words` = 2 for a cloud, 1 for an mcloud (32-bit words). */
+int svb_cloud_export(const uint32_t *records, int rec_stride_words, int n, const svb_camera *cam,
+                     double *xyz, float *xyz_f32, uint8_t *rgb, int32_t *sites, uint8_t *d,
+                     uint16_t *hue, void *stream);
+
+/* ---- a5-a7  RANSAC / planarFitting / randomNonCollinearPoints       functions.py:240-298
+ * One warp scores one hypothesis: plane through the triple (abc = inv([P1;P2;P3]).1, fp64),
+ * error = mean |P.abc - 1| / |abc| over the trial's S sample points (functions.py:275,289).
+ * errors[f*T + t] = +inf for a singular triple or a frame with M_f < S (functions.py:286,294).
+ *
+ * Index source
+ *   sample_idx != NULL : explicit draws, sample_idx int32 [F,T,S], triple_idx int32 [F,T,3]
+ *                        (the replay of Python's `random` stream) -- parity mode;
+ *   sample_idx == NULL : counter-based on-device draws keyed by (rng_seed, frame0+f, t):
+ *                        S distinct indices (keyed bijection + cycle walking) and triples redrawn
+ *                        while exactly collinear (functions.py:251-259) -- throughput mode.
+ *                        svb_ransac_dump_indices writes the same draws out for the oracle. */
+int svb_ransac_score(const uint32_t *mcloud, int rec_stride_words, int64_t slab_stride_records,
+                     const int32_t *counts, int counts_stride, int counts_col,
+                     int F, int T, int S, const svb_camera *cam,
+                     const int32_t *sample_idx, const int32_t *triple_idx,
+                     uint64_t rng_seed, int frame0,
+                     double *errors, void *stream);
+int svb_ransac_dump_indices(const uint32_t *mcloud, int rec_stride_words, int64_t slab_stride_records,
+                            const int32_t *counts, int counts_stride, int counts_col,
+                            int F, int T, int S, const svb_camera *cam,
+                            uint64_t rng_seed, int frame0,
+                            int32_t *sample_idx, int32_t *triple_idx, void *stream);
+/* First strict minimum over the T errors of each frame (functions.py:291) and the winning plane.
+ * planes[f*8 + ..] = { a, b, c, |abc|, cutoff, best_error, best_trial, valid }
+ *   cutoff = the smallest double v with fl(v/|abc|) >= point_threshold, so that
+ *            "|P.abc-1| < cutoff"  <=>  "fl(|P.abc-1| / |abc|) < point_threshold" exactly;
+ *   valid  = 1.0 when a plane was found, else 0.0 (RANSAC returned (None, None)), best_trial = -1.
+ * triple_idx / rng_seed as in svb_ransac_score. */
+int svb_ransac_finalize(const uint32_t *mcloud, int rec_stride_words, int64_t slab_stride_records,
+                        const int32_t *counts, int counts_stride, int counts_col,
+                        int F, int T, int S, const svb_camera *cam,
+                        const int32_t *triple_idx, uint64_t rng_seed, int frame0,
+                        const double *errors, double point_threshold,
+                        double *planes, void *stream);
+/* planes row from host coefficients (drop-in helpers that are handed `abc` by the caller). */
+int svb_plane_from_abc(const double *h_abc, double point_threshold, double *h_plane_row);
+
+/* ---- a8  calculatePointErrors                                        functions.py:300-312
+ * dist[i] = | (X*a + Y*b + Z*c - 1) / |abc| |, float64, for one cloud of n records. */
+int svb_point_errors(const uint32_t *records, int rec_stride_words, int n, const svb_camera *cam,
+                     const double *h_abc, double *dist, void *stream);
+
+/* ---- a9 / a12  computePlanarThreshold, filterPointsByHistogram       functions.py:314-323, 228-230
+ * Stable compaction of one cloud: keep record i when
+ *   mode 0: dist[i] < threshold                       (dist float64 [n])
+ *   mode 1: hist[hue(record i)] > (uint32) threshold   (hist uint32 [>=1001])
+ * out_count[0] = kept.  scratch: svb_compact_scratch_bytes(n). */
+int64_t svb_compact_scratch_bytes(int n);
+int svb_compact_cloud(const uint64_t *cloud, int n, int mode, const double *dist,
+                      const uint32_t *hist, double threshold,
+                      uint64_t *out_cloud, int32_t *out_count,
+                      void *scratch, int64_t scratch_bytes, void *stream);
+
+/* ---- a10-a11  BGRtoHSVHue + calculateColourHistogram                 functions.py:73-78, 215-226
+ * hist[bin] += 1 for every record (bin = rint(1000*hue), functions.py:76).  hist is zeroed first. */
+int svb_hue_histogram(const uint64_t *cloud, int n, uint32_t *hist, void *stream);
+/* hue bin of raw colours (exhaustive known-answer test of a10): bins[i] from rgb[i*3..]. */
+int svb_hue_bins(const uint8_t *rgb, int64_t n, uint16_t *bins, void *stream);
+
+/* ---- a13  project3DPointsTo2DImagePoints (+ the caller's int32 cast)  functions.py:201-209
+ * xy_f64 [n,2] = (((X*f)/Z)+cw, ((Y*f)/Z)+ch); xy_i32 [n,2] = trunc toward zero
+ * (stereovision.py:112).  Either output may be NULL. */
+int svb_reproject(const uint32_t *records, int rec_stride_words, int n, const svb_camera *cam,
+                  double *xy_f64, int32_t *xy_i32, void *stream);
+/* reprojection of every (coordinate, d) pair: out[c*256 + d] for c in [0,n_coord), d in [1,255]
+ * with axis 0 = x (centre_w), 1 = y (centre_h) -- the exhaustive known-answer table of SURVEY 7.1-1. */
+int svb_reproject_table(int axis, int n_coord, const svb_camera *cam, int32_t *out, void *stream);
+
+/* ---- a14  generatePointsAsImage / the overlay loop      functions.py:339-344, stereovision.py:131-133
+ * img[y,x,:] = value[:] for each (x,y) in pts int32 [n,2]; channels = 1 (mask) or 3 (overlay).
+ * The image is NOT cleared (the caller copies blackImg / imgL first, as the reference does).
+ * Points outside the image are reported through *oob (device int32, incremented) and skipped
+ * -- the reference would raise IndexError (or wrap for small negatives). */
+int svb_scatter_points(const int32_t *pts, int n, uint8_t *img, int H, int W, int channels,
+                       const uint8_t *h_value, int32_t *oob, void *stream);
+
+/* ---- a8-a14 fused, batched: the road points of F frames               stereovision.py:97-140
+ * pass 1: near = |P.abc-1| < cutoff ; per-frame hue histogram of the near points (shared memory,
+ *         merged with global atomics); near bits kept;
+ * pass 2: keep = near && hist[hue] > colour_threshold ; reproject (exact fp64) ; road_mask[y',x'] = 255.
+ * counts[f*4+2] = K_f (near), counts[f*4+3] = R_f (kept).  hist uint32 [F,1024]; road_mask uint8
+ * [F,H,W] is cleared here.  overlay (optional, uint8 [F,H,W,3], pre-filled by the caller with imgL)
+ * receives BGR (0,255,0) at the same sites.  scratch: svb_road_scratch_bytes(F,H,W,step). */
+int64_t svb_road_scratch_bytes(int F, int H, int W, int step);
+int svb_road_points(const uint64_t *cloud, const int32_t *counts, const double *planes,
+                    int F, int H, int W, int step, const svb_camera *cam,
+                    uint32_t colour_threshold,
+                    uint32_t *hist, uint8_t *road_mask, uint8_t *overlay, int32_t *counts_out,
+                    void *scratch, int64_t scratch_bytes, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SVB200_H */

@@ -1,0 +1,250 @@
+"""TEST INFRASTRUCTURE -- CPU restatement (numpy, float64) of the reference's per-frame hot path.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference leg may import
+this file, and only as the checker or the timed CPU arm.  The product (stereo.vision_b200) never
+does.  Parity pinning: every function below is checked against outputs of the *unmodified*
+reference (functions.py executed in the build container by oracle/ref_harness.py) stored under
+tests/golden/ -- see tests/test_oracle_golden.py.  The reference ships no tests of its own
+(SURVEY 4), so those fixtures are the only pin there is.
+
+Each function cites the reference lines it restates.  Arrays replace the reference's Python lists:
+a cloud is (sites [N,2] int32 as (y,x), d [N] uint8, xyz [N,3] float64, rgb [N,3] uint8) in the
+reference's append order (row-major over the lattice).
+"""
+import random
+
+import numpy as np
+
+F_PX = 399.9745178222656        # functions.py:15
+BASE_M = 0.2090607502           # functions.py:19
+CENTRE_H = 262.0                # functions.py:21
+CENTRE_W = 474.5                # functions.py:22
+HUE_BINS = 1001                 # str(round(h,3)) has 1001 possible values '0.0' .. '1.0'
+
+
+class Cam:
+    def __init__(self, f=F_PX, B=BASE_M, ch=CENTRE_H, cw=CENTRE_W):
+        self.f, self.B, self.ch, self.cw = float(f), float(B), float(ch), float(cw)
+
+
+def cam_of(camera=None):
+    if camera is None:
+        return Cam()
+    if isinstance(camera, Cam):
+        return camera
+    return Cam(camera.focal_px, camera.baseline_m, camera.centre_h, camera.centre_w)
+
+
+# ---------------------------------------------------------------- a1-a3: disparity clean / mask
+def fill_disparity(d, prev):
+    """functions.py:140-147: where d <= 2 add the previous frame's value, saturating at 255."""
+    if prev is None:
+        return d
+    hole = d <= 2                                   # NOT(threshold(d, 2) -> 255 where d > 2)
+    s = d.astype(np.uint16) + np.where(hole, prev, 0).astype(np.uint16)
+    return np.minimum(s, 255).astype(np.uint8)      # cv2.add saturates
+
+
+def mask_disparity(d, carmask):
+    """functions.py:169-172: keep d where carmask != 0, else 0 (new array)."""
+    return np.where(carmask != 0, d, 0).astype(np.uint8)
+
+
+def cap_disparity(d):
+    """functions.py:164-167: the bitwise_and result is discarded -- identity, same object."""
+    return d
+
+
+# ---------------------------------------------------------------- a4: projection
+def lattice_shape(H, W, step=2):
+    """Sites visited by range(0,H-1,step) x range(0,W-1,step) (functions.py:185-186)."""
+    return len(range(0, H - 1, step)), len(range(0, W - 1, step))
+
+
+def project(d, camera=None, step=2, bgr=None):
+    """functions.py:178-198.  Returns dict(sites, d, xyz, rgb) in row-major lattice order.
+
+    Z = (f*B)/d ; X = ((x-cw)*Z)/f ; Y = ((y-ch)*Z)/f, all float64, product/quotient order kept.
+    rgb = bgr[y,x,2], bgr[y,x,1], bgr[y,x,0] (functions.py:195).
+    """
+    c = cam_of(camera)
+    H, W = d.shape[:2]
+    ys = np.arange(0, H - 1, step)
+    xs = np.arange(0, W - 1, step)
+    sub = d[np.ix_(ys, xs)]
+    iy, ix = np.nonzero(sub > 0)                   # C order == the reference's append order
+    y = ys[iy]
+    x = xs[ix]
+    dv = sub[iy, ix]
+    fB = c.f * c.B
+    Z = fB / dv.astype(np.float64)
+    X = ((x.astype(np.float64) - c.cw) * Z) / c.f
+    Y = ((y.astype(np.float64) - c.ch) * Z) / c.f
+    out = {
+        "sites": np.stack([y, x], axis=1).astype(np.int32),
+        "d": dv.astype(np.uint8),
+        "xyz": np.stack([X, Y, Z], axis=1),
+        "rgb": None,
+    }
+    if bgr is not None and len(bgr) > 0:
+        out["rgb"] = np.ascontiguousarray(bgr[y, x][:, ::-1]).astype(np.uint8)
+    return out
+
+
+# ---------------------------------------------------------------- a13: reprojection
+def reproject(xyz, camera=None):
+    """functions.py:201-209 then the caller's np.int32 truncation (stereovision.py:112).
+
+    x = ((X*f)/Z) + cw ; y = ((Y*f)/Z) + ch in float64.  Returns (float [R,2], int32 [R,2]) as (x,y).
+    """
+    c = cam_of(camera)
+    if len(xyz) == 0:
+        z = np.zeros((0, 2))
+        return z, z.astype(np.int32)
+    X, Y, Z = xyz[:, 0], xyz[:, 1], xyz[:, 2]
+    x = ((X * c.f) / Z) + c.cw
+    y = ((Y * c.f) / Z) + c.ch
+    fl = np.stack([x, y], axis=1)
+    return fl, fl.astype(np.int32)                  # astype truncates toward zero, as np.array(.., int32)
+
+
+# ---------------------------------------------------------------- a10: hue key
+def hue_bin(r, g, b):
+    """functions.py:73-78 with colorsys.rgb_to_hsv fed np.uint8 channels.
+
+    colorsys: maxc/minc; grey -> h = 0.0; rc,gc,bc = (maxc-ch)/(maxc-minc) (uint8/uint8 -> float64);
+    h = bc-gc | 2+rc-bc | 4+gc-rc; h = (h/6) % 1 (np.remainder).  round(np.float64, 3) is
+    rint(h*1000)/1000, so the dictionary key is identified by the integer rint(h*1000) in [0,1000].
+    """
+    r = np.asarray(r, dtype=np.uint8)
+    g = np.asarray(g, dtype=np.uint8)
+    b = np.asarray(b, dtype=np.uint8)
+    maxc = np.maximum(np.maximum(r, g), b)
+    minc = np.minimum(np.minimum(r, g), b)
+    rng_ = (maxc - minc).astype(np.float64)
+    grey = maxc == minc
+    den = np.where(grey, 1.0, rng_)
+    rc = (maxc - r).astype(np.float64) / den
+    gc = (maxc - g).astype(np.float64) / den
+    bc = (maxc - b).astype(np.float64) / den
+    h = np.where(r == maxc, bc - gc, np.where(g == maxc, (2.0 + rc) - bc, (4.0 + gc) - rc))
+    h = np.remainder(h / 6.0, 1.0)
+    k = np.rint(h * 1000.0).astype(np.int32)
+    return np.where(grey, 0, k).astype(np.int32)
+
+
+def hue_key(bin_id: int) -> str:
+    """The reference's dictionary key for a bin (functions.py:76-78)."""
+    return str(round(np.float64(bin_id) / 1000.0, 3)) if bin_id else "0.0"
+
+
+# ---------------------------------------------------------------- a5-a7: RANSAC
+def replay_indices(mask_xyz, trials, n_samples, seed=None, rng=None):
+    """The reference's draw order on index ranges (functions.py:286, 252-254).
+
+    One random.sample(range(M), S) then rounds of three random.sample(range(M), 1) until the cross
+    product of (P1-P2, P2-P3) is not exactly zero (functions.py:251-259).  M < S: every trial raises
+    before drawing (functions.py:286,294) -> all indices -1.
+    """
+    if rng is None:
+        rng = random.Random()
+        rng.seed(seed)
+    m = len(mask_xyz)
+    samp = -np.ones((trials, n_samples), dtype=np.int32)
+    trip = -np.ones((trials, 3), dtype=np.int32)
+    if m < n_samples:
+        return samp, trip
+    pop = range(m)
+    for t in range(trials):
+        samp[t] = rng.sample(pop, n_samples)
+        while True:
+            i = [rng.sample(pop, 1)[0] for _ in range(3)]
+            u = mask_xyz[i[0]] - mask_xyz[i[1]]
+            v = mask_xyz[i[1]] - mask_xyz[i[2]]
+            cp = (u[1] * v[2] - u[2] * v[1], u[2] * v[0] - u[0] * v[2], u[0] * v[1] - u[1] * v[0])
+            if not (cp[0] == 0 and cp[1] == 0 and cp[2] == 0):
+                break
+        trip[t] = i
+    return samp, trip
+
+
+def plane_of_triple(P):
+    """functions.py:267: abc = inv([P1;P2;P3]) . ones.  Exactly singular -> None (trial skipped, :294)."""
+    try:
+        with np.errstate(all="ignore"):
+            return np.dot(np.linalg.inv(P), np.ones(3))
+    except np.linalg.LinAlgError:
+        return None
+
+
+def plane_distance(xyz, abc):
+    """functions.py:269,275 / 307,310: |P.abc - 1| / sqrt(a^2+b^2+c^2), products summed left to right."""
+    nrm = np.sqrt(abc[0] * abc[0] + abc[1] * abc[1] + abc[2] * abc[2])
+    s = (xyz[:, 0] * abc[0] + xyz[:, 1] * abc[1]) + xyz[:, 2] * abc[2]
+    return np.abs((s - 1.0) / nrm)
+
+
+def ransac_from_indices(mask_xyz, sample_idx, triple_idx):
+    """functions.py:278-298 with the draws given.  Returns (best_trial, abc or None, errors [T]).
+
+    error = mean distance of the trial's S sample points to the trial's plane (:289); the first
+    strict minimum wins (:291); a singular triple or a NaN error never wins.
+    """
+    T = len(sample_idx)
+    errs = np.full(T, np.inf)
+    planes = np.full((T, 3), np.nan)
+    for t in range(T):
+        if triple_idx[t, 0] < 0:
+            continue
+        abc = plane_of_triple(mask_xyz[triple_idx[t]])
+        if abc is None:
+            continue
+        planes[t] = abc
+        with np.errstate(all="ignore"):
+            e = np.mean(plane_distance(mask_xyz[sample_idx[t]], abc))
+        errs[t] = e if not np.isnan(e) else np.inf
+    best, best_err = -1, np.inf
+    for t in range(T):
+        if errs[t] < best_err:
+            best, best_err = t, errs[t]
+    return best, (planes[best].copy() if best >= 0 else None), errs
+
+
+# ---------------------------------------------------------------- a8-a14: road points
+def road_points(cloud, abc, threshold=0.05, colour_threshold=10, shape=(544, 1024), camera=None):
+    """stereovision.py:97-140: distances (functions.py:300-312), dist < threshold (:314-323), hue
+    histogram (:215-226), count > colour_threshold (:228-230), reprojection (:201-209) truncated to
+    int32 (stereovision.py:112), scatter of 255 into a black image (functions.py:339-344).
+    """
+    H, W = shape
+    mask = np.zeros((H, W), dtype=np.uint8)
+    out = {"near": None, "hist": np.zeros(HUE_BINS, dtype=np.int64), "keep": None,
+           "near_n": 0, "road_n": 0, "pts": np.zeros((0, 2), dtype=np.int32), "mask": mask}
+    if abc is None:
+        return out
+    dist = plane_distance(cloud["xyz"], abc)
+    near = dist < threshold
+    rgb = cloud["rgb"]
+    bins = hue_bin(rgb[:, 0], rgb[:, 1], rgb[:, 2])
+    hist = np.bincount(bins[near], minlength=HUE_BINS)
+    keep = near & (hist[bins] > colour_threshold)
+    _, pts = reproject(cloud["xyz"][keep], camera)
+    mask[pts[:, 1], pts[:, 0]] = 255
+    out.update(dist=dist, near=near, bins=bins, hist=hist, keep=keep, near_n=int(near.sum()),
+               road_n=int(keep.sum()), pts=pts, mask=mask)
+    return out
+
+
+# ---------------------------------------------------------------- the frame, end to end
+def run_frame(disparity, bgr, prev, carmask, seed=None, trials=600, n_samples=600, step=2,
+              threshold=0.05, colour_threshold=10, camera=None, indices=None):
+    """stereovision.py:58-140 on one frame.  `indices` = (sample_idx, triple_idx) overrides the replay."""
+    filled = fill_disparity(disparity, prev)
+    cloud = project(filled, camera, step, bgr)
+    mcloud = project(mask_disparity(filled, carmask), camera, step)
+    if indices is None:
+        indices = replay_indices(mcloud["xyz"], trials, n_samples, seed)
+    best, abc, errs = ransac_from_indices(mcloud["xyz"], indices[0], indices[1])
+    rp = road_points(cloud, abc, threshold, colour_threshold, disparity.shape[:2], camera)
+    return {"filled": filled, "cloud": cloud, "mcloud": mcloud, "indices": indices, "best": best,
+            "abc": abc, "errors": errs, "road": rp}

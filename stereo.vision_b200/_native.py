@@ -1,0 +1,132 @@
+"""ctypes binding of libsvb200.so (include/svb200.h).
+
+There is no CPU fallback: if the library is missing it is built with nvcc (csrc/build.py); if that
+fails, or a call returns non-zero, an exception is raised.  Tensors are handed over as raw device
+pointers; nothing here synchronises.
+"""
+import ctypes as C
+import os
+
+import torch
+
+from .camera import Camera
+
+_PKG = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_PKG, "libsvb200.so")
+
+HUE_BINS = 1001
+HIST_STRIDE = 1024
+PLANE_STRIDE = 8
+ABI_VERSION = 1
+
+
+class SvbError(RuntimeError):
+    pass
+
+
+class _CCamera(C.Structure):
+    _fields_ = [("focal_px", C.c_double), ("baseline_m", C.c_double),
+                ("centre_h", C.c_double), ("centre_w", C.c_double)]
+
+
+def ccam(cam: Camera) -> _CCamera:
+    return _CCamera(cam.focal_px, cam.baseline_m, cam.centre_h, cam.centre_w)
+
+
+P = C.c_void_p
+I = C.c_int
+L = C.c_int64
+U64 = C.c_uint64
+U32 = C.c_uint32
+D = C.c_double
+CAMP = C.POINTER(_CCamera)
+
+# name -> (restype, argtypes); every symbol include/svb200.h declares
+SIGNATURES = {
+    "svb_version": (I, []),
+    "svb_error_string": (C.c_char_p, [I]),
+    "svb_lattice_rows": (I, [I, I]),
+    "svb_lattice_cols": (I, [I, I]),
+    "svb_fill_sequence": (I, [P, P, P, I, I, I, P]),
+    "svb_mask_disparity": (I, [P, P, P, I, I, I, P]),
+    "svb_project_scratch_bytes": (L, [I, I, I, I]),
+    "svb_project_compact": (I, [P, P, P, I, I, I, I, CAMP, P, P, P, P, L, P]),
+    "svb_cloud_export": (I, [P, I, I, CAMP, P, P, P, P, P, P, P]),
+    "svb_ransac_score": (I, [P, I, L, P, I, I, I, I, I, CAMP, P, P, U64, I, P, P]),
+    "svb_ransac_dump_indices": (I, [P, I, L, P, I, I, I, I, I, CAMP, U64, I, P, P, P]),
+    "svb_ransac_finalize": (I, [P, I, L, P, I, I, I, I, I, CAMP, P, U64, I, P, D, P, P]),
+    "svb_plane_from_abc": (I, [P, D, P]),
+    "svb_point_errors": (I, [P, I, I, CAMP, P, P, P]),
+    "svb_compact_scratch_bytes": (L, [I]),
+    "svb_compact_cloud": (I, [P, I, I, P, P, D, P, P, P, L, P]),
+    "svb_hue_histogram": (I, [P, I, P, P]),
+    "svb_hue_bins": (I, [P, L, P, P]),
+    "svb_reproject": (I, [P, I, I, CAMP, P, P, P]),
+    "svb_reproject_table": (I, [I, I, CAMP, P, P]),
+    "svb_scatter_points": (I, [P, I, P, I, I, I, P, P, P]),
+    "svb_road_scratch_bytes": (L, [I, I, I, I]),
+    "svb_road_points": (I, [P, P, P, I, I, I, I, CAMP, U32, P, P, P, P, P, L, P]),
+}
+
+_lib = None
+
+
+def load(build_if_missing: bool = True):
+    """Load (building first if needed) the native library.  Raises if it cannot be had."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if build_if_missing:
+        from .csrc import build as _b
+        try:
+            _b.build()
+        except Exception:
+            if not os.path.isfile(LIB_PATH):
+                raise
+    if not os.path.isfile(LIB_PATH):
+        raise SvbError("libsvb200.so is missing: run `python __graft_entry__.py build`")
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)           # AttributeError if the .so lacks a declared symbol
+        fn.restype = res
+        fn.argtypes = args
+    if lib.svb_version() != ABI_VERSION:
+        raise SvbError("libsvb200.so ABI %d != binding %d: rebuild" % (lib.svb_version(), ABI_VERSION))
+    _lib = lib
+    return lib
+
+
+def check(code: int, what: str):
+    if code != 0:
+        msg = load().svb_error_string(code)
+        raise SvbError("%s failed: %s (%d)" % (what, msg.decode() if msg else "?", code))
+
+
+def require_cuda():
+    if not torch.cuda.is_available():
+        raise SvbError("stereo.vision_b200 needs a CUDA device (sm_100a); there is no CPU path")
+
+
+def ptr(t):
+    """Device pointer of a tensor (None -> NULL)."""
+    if t is None:
+        return None
+    if not t.is_cuda:
+        raise SvbError("expected a CUDA tensor")
+    if not t.is_contiguous():
+        raise SvbError("expected a contiguous tensor")
+    return C.c_void_p(t.data_ptr())
+
+
+def stream_ptr():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+# launch counter: every kernel launch the library performs on our behalf is accounted here
+# (bench.py reports it as gpu_launches)
+launches = 0
+
+
+def count(n: int):
+    global launches
+    launches += n

@@ -1,0 +1,484 @@
+// a1-a4: temporal disparity fill, mask, disparity -> 3-D cloud with stable stream compaction.
+//
+// Layout.  A frame's lattice is LH x LW sites (every `step`-th pixel of every `step`-th row,
+// functions.py:185-186).  One thread owns one 16-pixel chunk of one lattice row: it reads the 16
+// disparity bytes (one 128-bit load), the 16 mask bytes and, for rows that carry colour, the 48
+// BGR bytes (three 128-bit loads), and turns them into a 16-bit "valid" and a 16-bit "masked
+// valid" bitmap.  Threads of a block are laid out row-major over a group of lattice rows, so an
+// exclusive block scan of the popcounts gives every site its rank in the reference's append order.
+// Records are compacted into shared memory first and leave the SM as fully coalesced 8-byte (cloud)
+// and 4-byte (mcloud) stores; the hue bin is computed in that copy-out loop, where consecutive
+// lanes hold consecutive *valid* points and no lane idles on a hole.
+#include "svb_common.cuh"
+
+#define PROJ_THREADS 256
+#define CHUNK 16
+
+// ------------------------------------------------------------------ a1 fill
+// d' = sat_add(d, (d <= 2) ? prev : 0) on 4 bytes at once           functions.py:142-146
+__device__ __forceinline__ uint32_t fill4(uint32_t d, uint32_t prev) {
+    uint32_t hole = __vcmpleu4(d, 0x02020202u);        // 0xff where d <= 2
+    return __vaddus4(d, prev & hole);                  // cv2.add saturates
+}
+__device__ __forceinline__ uint4 fill16(uint4 d, uint4 p) {
+    return make_uint4(fill4(d.x, p.x), fill4(d.y, p.y), fill4(d.z, p.z), fill4(d.w, p.w));
+}
+
+// One thread = 16 pixels for all F frames; the loads of up to UNROLL future frames are in flight
+// while the recurrence advances (they do not depend on it).
+template <int UNROLL>
+__global__ void __launch_bounds__(256)
+fill_seq_v16(const uint4 *__restrict__ raw, const uint4 *__restrict__ prev0, uint4 *__restrict__ filled,
+             int F, int64_t chunks) {
+    int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= chunks) return;
+    bool have = prev0 != nullptr;
+    uint4 prev = have ? __ldg(prev0 + p) : make_uint4(0, 0, 0, 0);
+    int t = 0;
+    for (; t + UNROLL <= F; t += UNROLL) {
+        uint4 d[UNROLL];
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) d[u] = __ldcs(raw + (int64_t)(t + u) * chunks + p);
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) {
+            uint4 v = have ? fill16(d[u], prev) : d[u];
+            __stcs(filled + (int64_t)(t + u) * chunks + p, v);
+            prev = v;
+            have = true;
+        }
+    }
+    for (; t < F; ++t) {
+        uint4 d = __ldcs(raw + (int64_t)t * chunks + p);
+        uint4 v = have ? fill16(d, prev) : d;
+        __stcs(filled + (int64_t)t * chunks + p, v);
+        prev = v;
+        have = true;
+    }
+}
+
+// any-size fallback, one pixel per thread
+__global__ void fill_seq_scalar(const uint8_t *__restrict__ raw, const uint8_t *__restrict__ prev0,
+                                uint8_t *__restrict__ filled, int F, int64_t pixels) {
+    int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= pixels) return;
+    bool have = prev0 != nullptr;
+    int prev = have ? prev0[p] : 0;
+    for (int t = 0; t < F; ++t) {
+        int d = raw[(int64_t)t * pixels + p];
+        if (have && d <= 2) d = min(d + prev, 255);
+        filled[(int64_t)t * pixels + p] = (uint8_t)d;
+        prev = d;
+        have = true;
+    }
+}
+
+extern "C" int svb_fill_sequence(const uint8_t *raw, const uint8_t *prev0, uint8_t *filled,
+                                 int F, int H, int W, void *stream) {
+    if (!raw || !filled) return SVB_E_NULL;
+    if (F < 1 || H < 1 || W < 1) return SVB_E_SHAPE;
+    cudaStream_t st = (cudaStream_t)stream;
+    int64_t pixels = (int64_t)H * W;
+    bool aligned = (pixels % 16 == 0) && (((uintptr_t)raw | (uintptr_t)filled | (uintptr_t)prev0) % 16 == 0);
+    if (aligned) {
+        int64_t chunks = pixels / 16;
+        int threads = 128;
+        int64_t blocks = (chunks + threads - 1) / threads;
+        fill_seq_v16<8><<<(unsigned)blocks, threads, 0, st>>>((const uint4 *)raw, (const uint4 *)prev0,
+                                                             (uint4 *)filled, F, chunks);
+    } else {
+        int threads = 256;
+        int64_t blocks = (pixels + threads - 1) / threads;
+        fill_seq_scalar<<<(unsigned)blocks, threads, 0, st>>>(raw, prev0, filled, F, pixels);
+    }
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
+}
+
+// ------------------------------------------------------------------ a2 mask
+__global__ void mask_disp_kernel(const uint8_t *__restrict__ d, const uint8_t *__restrict__ cm,
+                                 uint8_t *__restrict__ out, int64_t pixels, int64_t total) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= total) return;
+    out[i] = cm[i % pixels] != 0 ? d[i] : (uint8_t)0;
+}
+__global__ void mask_disp_v16(const uint4 *__restrict__ d, const uint4 *__restrict__ cm,
+                              uint4 *__restrict__ out, int64_t chunks, int64_t total) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= total) return;
+    uint4 v = __ldcs(d + i);
+    uint4 m = __ldg(cm + i % chunks);
+    // 0xff where mask byte != 0
+    v.x &= ~__vcmpeq4(m.x, 0u);
+    v.y &= ~__vcmpeq4(m.y, 0u);
+    v.z &= ~__vcmpeq4(m.z, 0u);
+    v.w &= ~__vcmpeq4(m.w, 0u);
+    __stcs(out + i, v);
+}
+
+extern "C" int svb_mask_disparity(const uint8_t *d, const uint8_t *carmask, uint8_t *out,
+                                  int F, int H, int W, void *stream) {
+    if (!d || !carmask || !out) return SVB_E_NULL;
+    if (F < 1 || H < 1 || W < 1) return SVB_E_SHAPE;
+    cudaStream_t st = (cudaStream_t)stream;
+    int64_t pixels = (int64_t)H * W;
+    bool aligned = (pixels % 16 == 0) && (((uintptr_t)d | (uintptr_t)carmask | (uintptr_t)out) % 16 == 0);
+    if (aligned) {
+        int64_t chunks = pixels / 16, total = chunks * F;
+        mask_disp_v16<<<(unsigned)((total + 255) / 256), 256, 0, st>>>((const uint4 *)d, (const uint4 *)carmask,
+                                                                      (uint4 *)out, chunks, total);
+    } else {
+        int64_t total = pixels * F;
+        mask_disp_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(d, carmask, out, pixels, total);
+    }
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
+}
+
+// ------------------------------------------------------------------ a4 projection + compaction
+struct ProjGeom {
+    int H, W, step, LH, LW;
+    int cpr;            // 16-pixel chunks per row
+    int rpb;            // lattice rows per block
+    int groups;         // row groups (blocks) per frame
+    int vec_ok;         // W % 16 == 0 and all bases 16-byte aligned
+};
+
+static inline int lattice_len(int n, int step) { return n <= 1 ? 0 : (n - 1 + step - 1) / step; }
+
+static ProjGeom make_geom(int H, int W, int step, bool aligned) {
+    ProjGeom g;
+    g.H = H; g.W = W; g.step = step;
+    g.LH = lattice_len(H, step);
+    g.LW = lattice_len(W, step);
+    g.cpr = (W + CHUNK - 1) / CHUNK;
+    g.rpb = PROJ_THREADS / g.cpr;
+    if (g.rpb < 1) g.rpb = 1;
+    g.groups = (g.LH + g.rpb - 1) / g.rpb;
+    g.vec_ok = (W % CHUNK == 0) && aligned;
+    return g;
+}
+
+// The 16 disparity / mask bytes of one chunk and the two site bitmaps.
+struct ChunkBits {
+    uint32_t d[4];
+    uint32_t vm, mm;     // valid sites, valid sites inside carmask (bit j = pixel x0 + j)
+};
+
+__device__ __forceinline__ uint32_t byte_of(const uint32_t *w, int j) { return (w[j >> 2] >> ((j & 3) * 8)) & 0xFFu; }
+
+// nonzero-byte bitmap of 4 packed bytes -> 4 bits
+__device__ __forceinline__ uint32_t nz4(uint32_t w) {
+    uint32_t m = __vcmpne4(w, 0u) & 0x01010101u;       // 1 per nonzero byte
+    return (m | (m >> 7) | (m >> 14) | (m >> 21)) & 0xFu;
+}
+
+template <bool HAS_MASK>
+__device__ __forceinline__ ChunkBits load_chunk(const uint8_t *__restrict__ drow, const uint8_t *__restrict__ mrow,
+                                                int x0, int W, int step, bool vec_ok) {
+    ChunkBits c;
+    uint32_t m[4];
+    if (vec_ok) {
+        uint4 v = __ldg((const uint4 *)(drow + x0));
+        c.d[0] = v.x; c.d[1] = v.y; c.d[2] = v.z; c.d[3] = v.w;
+        if (HAS_MASK) {
+            uint4 q = __ldg((const uint4 *)(mrow + x0));
+            m[0] = q.x; m[1] = q.y; m[2] = q.z; m[3] = q.w;
+        }
+    } else {
+#pragma unroll
+        for (int w = 0; w < 4; ++w) {
+            uint32_t dv = 0, mv = 0;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                int x = x0 + w * 4 + k;
+                if (x < W) {
+                    dv |= (uint32_t)drow[x] << (k * 8);
+                    if (HAS_MASK) mv |= (uint32_t)mrow[x] << (k * 8);
+                }
+            }
+            c.d[w] = dv;
+            m[w] = mv;
+        }
+    }
+    uint32_t nzd = nz4(c.d[0]) | (nz4(c.d[1]) << 4) | (nz4(c.d[2]) << 8) | (nz4(c.d[3]) << 12);
+    // lattice sites of this chunk: x % step == 0 and x < W-1
+    uint32_t site;
+    if (step == 1) site = 0xFFFFu;
+    else if (step == 2) site = 0x5555u;                 // x0 is a multiple of 16, hence even
+    else {
+        site = 0;
+#pragma unroll
+        for (int j = 0; j < CHUNK; ++j) if ((x0 + j) % step == 0) site |= 1u << j;
+    }
+    int lim = W - 1 - x0;                               // pixels of this chunk with x < W-1
+    if (lim < CHUNK) site &= (lim <= 0) ? 0u : ((1u << lim) - 1u);
+    c.vm = nzd & site;
+    if (HAS_MASK) {
+        uint32_t nzm = nz4(m[0]) | (nz4(m[1]) << 4) | (nz4(m[2]) << 8) | (nz4(m[3]) << 12);
+        c.mm = c.vm & nzm;
+    } else {
+        c.mm = c.vm;
+    }
+    return c;
+}
+
+// exclusive scan of one packed (cloud | mcloud << 16) count per thread over the 256-thread block
+__device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t *warp_tot, uint32_t *total) {
+    int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    uint32_t inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        uint32_t n = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += n;
+    }
+    if (lane == 31) warp_tot[wid] = inc;
+    __syncthreads();
+    uint32_t base = 0, tot = 0;
+#pragma unroll
+    for (int w = 0; w < PROJ_THREADS / 32; ++w) {
+        uint32_t t = warp_tot[w];
+        if (w < wid) base += t;
+        tot += t;
+    }
+    *total = tot;
+    return base + inc - v;
+}
+
+// pass 1: per (frame, row group) site counts
+template <bool HAS_MASK>
+__global__ void __launch_bounds__(PROJ_THREADS)
+proj_count_kernel(const uint8_t *__restrict__ disp, const uint8_t *__restrict__ carmask, ProjGeom g,
+                  uint32_t *__restrict__ group_counts) {
+    __shared__ uint32_t warp_tot[PROJ_THREADS / 32];
+    int f = blockIdx.y, grp = blockIdx.x;
+    int r = threadIdx.x / g.cpr, ch = threadIdx.x % g.cpr;
+    int ly = grp * g.rpb + r;
+    uint32_t cnt = 0;
+    if (r < g.rpb && ly < g.LH) {
+        int y = ly * g.step;
+        const uint8_t *drow = disp + ((int64_t)f * g.H + y) * g.W;
+        const uint8_t *mrow = HAS_MASK ? carmask + (int64_t)y * g.W : nullptr;
+        ChunkBits c = load_chunk<HAS_MASK>(drow, mrow, ch * CHUNK, g.W, g.step, g.vec_ok);
+        cnt = (uint32_t)__popc(c.vm) | ((uint32_t)__popc(c.mm) << 16);
+    }
+    // block reduce
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+    if ((threadIdx.x & 31) == 0) warp_tot[threadIdx.x >> 5] = cnt;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t t = 0;
+#pragma unroll
+        for (int w = 0; w < PROJ_THREADS / 32; ++w) t += warp_tot[w];
+        group_counts[(int64_t)f * g.groups + grp] = t;
+    }
+}
+
+// pass 2: exclusive scan of the group counts of each frame (one block per frame)
+__global__ void proj_scan_kernel(uint32_t *__restrict__ group_counts, int groups, int32_t *__restrict__ counts) {
+    __shared__ uint32_t sv[32], sm[32];
+    int f = blockIdx.x;
+    uint32_t *gc = group_counts + (int64_t)f * groups;
+    int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    uint32_t carry_v = 0, carry_m = 0;
+    for (int base = 0; base < groups; base += blockDim.x) {
+        int i = base + threadIdx.x;
+        uint32_t p = i < groups ? gc[i] : 0u;
+        int v = (int)(p & 0xFFFFu), m = (int)(p >> 16);
+        int iv = warp_incl_scan(v, lane), im = warp_incl_scan(m, lane);
+        if (lane == 31) { sv[wid] = iv; sm[wid] = im; }
+        __syncthreads();
+        uint32_t bv = 0, bm = 0, tv = 0, tm = 0;
+        for (int w = 0; w < nw; ++w) {
+            if (w < wid) { bv += sv[w]; bm += sm[w]; }
+            tv += sv[w]; tm += sm[w];
+        }
+        // the offsets need more than 16 bits: the cloud offset replaces the packed count in plane 0
+        // of the scratch array, the mcloud offset goes to plane 1 ([F][groups] each)
+        if (i < groups) {
+            uint32_t *gm = group_counts + (int64_t)gridDim.x * groups + (int64_t)f * groups;
+            gc[i] = carry_v + bv + iv - v;
+            gm[i] = carry_m + bm + im - m;
+        }
+        carry_v += tv; carry_m += tm;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        counts[f * 4 + 0] = (int32_t)carry_v;
+        counts[f * 4 + 1] = (int32_t)carry_m;
+    }
+}
+
+// pass 3: write the records
+template <bool HAS_MASK, bool HAS_RGB>
+__global__ void __launch_bounds__(PROJ_THREADS)
+proj_write_kernel(const uint8_t *__restrict__ disp, const uint8_t *__restrict__ carmask,
+                  const uint8_t *__restrict__ bgr, ProjGeom g, const uint32_t *__restrict__ group_offsets,
+                  int64_t plane_stride, uint64_t *__restrict__ cloud, uint32_t *__restrict__ mcloud) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ uint32_t warp_tot[PROJ_THREADS / 32];
+    const int cap = g.rpb * g.cpr * CHUNK;                       // sites a block can hold
+    uint64_t *s_cloud = (uint64_t *)smem_raw;                    // [cap]
+    uint32_t *s_m = (uint32_t *)(smem_raw + (size_t)cap * 8);    // [cap]
+
+    int f = blockIdx.y, grp = blockIdx.x;
+    int r = threadIdx.x / g.cpr, ch = threadIdx.x % g.cpr;
+    int ly = grp * g.rpb + r;
+    ChunkBits c;
+    c.vm = c.mm = 0;
+    int y = 0, x0 = ch * CHUNK;
+    bool active = (r < g.rpb && ly < g.LH);
+    if (active) {
+        y = ly * g.step;
+        const uint8_t *drow = disp + ((int64_t)f * g.H + y) * g.W;
+        const uint8_t *mrow = HAS_MASK ? carmask + (int64_t)y * g.W : nullptr;
+        c = load_chunk<HAS_MASK>(drow, mrow, x0, g.W, g.step, g.vec_ok);
+    }
+    uint32_t cnt = (uint32_t)__popc(c.vm) | ((uint32_t)__popc(c.mm) << 16);
+    uint32_t total;
+    uint32_t off = block_excl_scan(cnt, warp_tot, &total);
+    int ov = (int)(off & 0xFFFFu), om = (int)(off >> 16);
+    int tv = (int)(total & 0xFFFFu), tm = (int)(total >> 16);
+
+    if (c.vm) {
+        uint32_t px[12];                                         // 48 BGR bytes of the chunk
+        if (HAS_RGB) {
+            const uint8_t *crow = bgr + (((int64_t)f * g.H + y) * g.W + x0) * 3;
+            if (g.vec_ok) {
+                const uint4 *q = (const uint4 *)crow;
+                uint4 a = __ldg(q), b = __ldg(q + 1), d = __ldg(q + 2);
+                px[0] = a.x; px[1] = a.y; px[2] = a.z; px[3] = a.w;
+                px[4] = b.x; px[5] = b.y; px[6] = b.z; px[7] = b.w;
+                px[8] = d.x; px[9] = d.y; px[10] = d.z; px[11] = d.w;
+            } else {
+#pragma unroll
+                for (int w = 0; w < 12; ++w) {
+                    uint32_t v = 0;
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        int bi = w * 4 + k;
+                        if (x0 + bi / 3 < g.W) v |= (uint32_t)crow[bi] << (k * 8);
+                    }
+                    px[w] = v;
+                }
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < CHUNK; ++j) {
+            if (c.vm & (1u << j)) {
+                int d = (int)byte_of(c.d, j);
+                uint32_t lo = pack_xyd(x0 + j, y, d);
+                uint32_t hi = 0;
+                if (HAS_RGB) {
+                    uint32_t bb = byte_of(px, 3 * j), gg = byte_of(px, 3 * j + 1), rr = byte_of(px, 3 * j + 2);
+                    hi = rr | (gg << 8) | (bb << 16);            // R,G,B = bgr[..,2],[..,1],[..,0]
+                }
+                s_cloud[ov++] = (uint64_t)lo | ((uint64_t)hi << 32);
+                if (c.mm & (1u << j)) s_m[om++] = lo;
+            }
+        }
+    }
+    __syncthreads();
+
+    const uint32_t *offs_v = group_offsets + (int64_t)f * g.groups;
+    const uint32_t *offs_m = group_offsets + plane_stride + (int64_t)f * g.groups;
+    int64_t slab = (int64_t)f * g.LH * g.LW;
+    if (cloud) {
+        uint64_t *dst = cloud + slab + offs_v[grp];
+        for (int i = threadIdx.x; i < tv; i += PROJ_THREADS) {
+            uint64_t rec = s_cloud[i];
+            if (HAS_RGB) {
+                uint32_t hi = (uint32_t)(rec >> 32);
+                int hue = exact_hue_bin((int)(hi & 0xFF), (int)((hi >> 8) & 0xFF), (int)((hi >> 16) & 0xFF));
+                rec |= ((uint64_t)(hue & 3) << 30) | ((uint64_t)(hue >> 2) << 56);
+            }
+            dst[i] = rec;
+        }
+    }
+    if (mcloud) {
+        uint32_t *dst = mcloud + slab + offs_m[grp];
+        for (int i = threadIdx.x; i < tm; i += PROJ_THREADS) dst[i] = s_m[i];
+    }
+}
+
+extern "C" int svb_lattice_rows(int H, int step) { return step < 1 ? 0 : lattice_len(H, step); }
+extern "C" int svb_lattice_cols(int W, int step) { return step < 1 ? 0 : lattice_len(W, step); }
+
+extern "C" int64_t svb_project_scratch_bytes(int F, int H, int W, int step) {
+    if (F < 1 || H < 2 || W < 2 || step < 1) return 0;
+    ProjGeom g = make_geom(H, W, step, true);
+    return (int64_t)2 * F * g.groups * (int64_t)sizeof(uint32_t);
+}
+
+extern "C" int svb_project_compact(const uint8_t *disp, const uint8_t *carmask, const uint8_t *bgr,
+                                   int F, int H, int W, int step, const svb_camera *cam,
+                                   uint64_t *cloud, uint32_t *mcloud, int32_t *counts,
+                                   void *scratch, int64_t scratch_bytes, void *stream) {
+    (void)cam;
+    if (!disp || !counts || !scratch) return SVB_E_NULL;
+    if (F < 1 || H < 2 || W < 2 || H > SVB_MAX_DIM || W > SVB_MAX_DIM || step < 1) return SVB_E_SHAPE;
+    if (scratch_bytes < svb_project_scratch_bytes(F, H, W, step)) return SVB_E_SCRATCH;
+    cudaStream_t st = (cudaStream_t)stream;
+    bool aligned = (((uintptr_t)disp | (uintptr_t)carmask | (uintptr_t)bgr) % 16 == 0);
+    ProjGeom g = make_geom(H, W, step, aligned);
+    if (g.cpr > PROJ_THREADS) return SVB_E_SHAPE;
+    uint32_t *gc = (uint32_t *)scratch;
+    dim3 grid(g.groups, F);
+    if (carmask) proj_count_kernel<true><<<grid, PROJ_THREADS, 0, st>>>(disp, carmask, g, gc);
+    else         proj_count_kernel<false><<<grid, PROJ_THREADS, 0, st>>>(disp, carmask, g, gc);
+    SVB_LAUNCH_CHECK();
+    proj_scan_kernel<<<F, 256, 0, st>>>(gc, g.groups, counts);
+    SVB_LAUNCH_CHECK();
+    if (!cloud && !mcloud) return SVB_OK;
+    size_t smem = (size_t)g.rpb * g.cpr * CHUNK * 12;
+    int64_t plane = (int64_t)F * g.groups;
+#define LAUNCH_W(M, R)                                                                              \
+    do {                                                                                            \
+        if (smem > 48 * 1024)                                                                       \
+            cudaFuncSetAttribute(proj_write_kernel<M, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+        proj_write_kernel<M, R><<<grid, PROJ_THREADS, smem, st>>>(disp, carmask, bgr, g, gc, plane, cloud, mcloud); \
+    } while (0)
+    if (carmask) { if (bgr) LAUNCH_W(true, true); else LAUNCH_W(true, false); }
+    else         { if (bgr) LAUNCH_W(false, true); else LAUNCH_W(false, false); }
+#undef LAUNCH_W
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
+}
+
+// ------------------------------------------------------------------ export of what the reference's list holds
+__global__ void cloud_export_kernel(const uint32_t *__restrict__ rec, int stride, int n, CamD cam,
+                                    double *__restrict__ xyz, float *__restrict__ xyz32, uint8_t *__restrict__ rgb,
+                                    int32_t *__restrict__ sites, uint8_t *__restrict__ dout, uint16_t *__restrict__ hue) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint32_t lo = rec[(int64_t)i * stride];
+    uint32_t hi = stride > 1 ? rec[(int64_t)i * stride + 1] : 0u;
+    int x = rec_x(lo), y = rec_y(lo), d = rec_d(lo);
+    if (xyz || xyz32) {
+        double Z = exact_Z(cam, d);
+        double X = exact_XY(cam.cw, cam.f, x, Z);
+        double Y = exact_XY(cam.ch, cam.f, y, Z);
+        if (xyz) { xyz[3 * (int64_t)i] = X; xyz[3 * (int64_t)i + 1] = Y; xyz[3 * (int64_t)i + 2] = Z; }
+        if (xyz32) { xyz32[3 * (int64_t)i] = (float)X; xyz32[3 * (int64_t)i + 1] = (float)Y; xyz32[3 * (int64_t)i + 2] = (float)Z; }
+    }
+    if (rgb) {
+        rgb[3 * (int64_t)i] = (uint8_t)(hi & 0xFF);
+        rgb[3 * (int64_t)i + 1] = (uint8_t)((hi >> 8) & 0xFF);
+        rgb[3 * (int64_t)i + 2] = (uint8_t)((hi >> 16) & 0xFF);
+    }
+    if (sites) { sites[2 * (int64_t)i] = y; sites[2 * (int64_t)i + 1] = x; }
+    if (dout) dout[i] = (uint8_t)d;
+    if (hue) hue[i] = (uint16_t)rec_hue(lo, hi);
+}
+
+extern "C" int svb_cloud_export(const uint32_t *records, int rec_stride_words, int n, const svb_camera *cam,
+                                double *xyz, float *xyz_f32, uint8_t *rgb, int32_t *sites, uint8_t *d,
+                                uint16_t *hue, void *stream) {
+    if (n == 0) return SVB_OK;
+    if (!records || !cam) return SVB_E_NULL;
+    if (n < 0 || (rec_stride_words != 1 && rec_stride_words != 2)) return SVB_E_ARG;
+    cloud_export_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(records, rec_stride_words, n, make_camd(cam),
+                                                                            xyz, xyz_f32, rgb, sites, d, hue);
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
+}

@@ -1,0 +1,377 @@
+// a5-a7: RANSAC plane fit.  One warp scores one hypothesis; a block holds 8 hypotheses of one frame
+// and shares the 255-entry table Z(d) = (f*B)/d in shared memory.  The masked cloud of a frame is
+// at most 4 bytes x lattice sites (128 KB at the reference size), i.e. L2-resident: the S gathers
+// of a hypothesis are 4-byte L2 reads, the sample-index stream (explicit mode) is read coalesced.
+//
+// Arithmetic.  The three points of a hypothesis are expanded with the path's exact float64
+// expressions (svb_common.cuh) because the "exactly collinear -> draw again" rule of
+// functions.py:251-259 is an exact-zero test, and the plane is abc = inv([P1;P2;P3]).1 evaluated
+// with the adjugate (fp64).  The S point-plane distances of the score use the factored form
+// |Z(d)*(a/f*(x-cw) + b/f*(y-ch) + c) - 1| (5 flops, no division); it differs from the reference
+// expression by ~1e-16 relative, far below the gap between two hypotheses' mean errors, and only
+// the arg-min (not the error value) is an observable.
+#include "svb_common.cuh"
+#include <math.h>
+
+#define RANSAC_WARPS 8
+#define RANSAC_THREADS (RANSAC_WARPS * 32)
+#define MAX_TRIPLE_ROUNDS 64
+
+// ------------------------------------------------------------------ counter-based draws (throughput mode)
+__host__ __device__ __forceinline__ uint32_t mix32(uint32_t x) {
+    x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16;
+    return x;
+}
+__host__ __device__ __forceinline__ uint32_t trial_key(uint64_t seed, int frame, int trial) {
+    uint32_t k = mix32((uint32_t)seed ^ 0x9E3779B9u);
+    k = mix32(k ^ (uint32_t)(seed >> 32));
+    k = mix32(k ^ (uint32_t)frame);
+    k = mix32(k ^ (uint32_t)trial ^ 0x85EBCA6Bu);
+    return k;
+}
+// keyed bijection of [0, 2^bits): 4 alternating Feistel half-rounds; cycle-walk into [0, m)
+__host__ __device__ __forceinline__ uint32_t perm_draw(uint32_t key, uint32_t i, int bits, uint32_t m) {
+    const int lo_bits = bits >> 1, hi_bits = bits - lo_bits;
+    const uint32_t lo_mask = (1u << lo_bits) - 1u, hi_mask = (1u << hi_bits) - 1u;
+    uint32_t v = i;
+    do {
+        uint32_t lo = v & lo_mask, hi = v >> lo_bits;
+        hi ^= mix32(lo ^ key) & hi_mask;
+        lo ^= mix32(hi ^ (key + 0x9E3779B9u)) & lo_mask;
+        hi ^= mix32(lo ^ (key + 0x3C6EF372u)) & hi_mask;
+        lo ^= mix32(hi ^ (key + 0xDAA66D2Bu)) & lo_mask;
+        v = (hi << lo_bits) | lo;
+    } while (v >= m);
+    return v;
+}
+__host__ __device__ __forceinline__ int bits_for(uint32_t m) {       // smallest b >= 2 with 2^b >= m
+    int b = 2;
+    while ((1u << b) < m) ++b;
+    return b;
+}
+__device__ __forceinline__ uint32_t uniform_draw(uint32_t key, uint32_t ctr, uint32_t m) {
+    return __umulhi(mix32(key ^ mix32(ctr + 0x632BE5ABu)), m);
+}
+
+// ------------------------------------------------------------------ geometry
+struct P3 { double x, y, z; };
+
+__device__ __forceinline__ P3 expand_point(const CamD &cam, uint32_t lo) {
+    P3 p;
+    p.z = exact_Z(cam, rec_d(lo));
+    p.x = exact_XY(cam.cw, cam.f, rec_x(lo), p.z);
+    p.y = exact_XY(cam.ch, cam.f, rec_y(lo), p.z);
+    return p;
+}
+// np.cross(P1-P2, P2-P3) == (0,0,0) exactly                     functions.py:256-259
+__device__ __forceinline__ bool exactly_collinear(const P3 &a, const P3 &b, const P3 &c) {
+    double ux = __dsub_rn(a.x, b.x), uy = __dsub_rn(a.y, b.y), uz = __dsub_rn(a.z, b.z);
+    double vx = __dsub_rn(b.x, c.x), vy = __dsub_rn(b.y, c.y), vz = __dsub_rn(b.z, c.z);
+    double cx = __dsub_rn(__dmul_rn(uy, vz), __dmul_rn(uz, vy));
+    double cy = __dsub_rn(__dmul_rn(uz, vx), __dmul_rn(ux, vz));
+    double cz = __dsub_rn(__dmul_rn(ux, vy), __dmul_rn(uy, vx));
+    return cx == 0.0 && cy == 0.0 && cz == 0.0;
+}
+// abc = inv([P1;P2;P3]) . (1,1,1)^T = (P2xP3 + P3xP1 + P1xP2) / det      functions.py:267
+__device__ __forceinline__ bool plane_of(const P3 &p1, const P3 &p2, const P3 &p3, double &a, double &b, double &c) {
+    double c23x = p2.y * p3.z - p2.z * p3.y, c23y = p2.z * p3.x - p2.x * p3.z, c23z = p2.x * p3.y - p2.y * p3.x;
+    double c31x = p3.y * p1.z - p3.z * p1.y, c31y = p3.z * p1.x - p3.x * p1.z, c31z = p3.x * p1.y - p3.y * p1.x;
+    double c12x = p1.y * p2.z - p1.z * p2.y, c12y = p1.z * p2.x - p1.x * p2.z, c12z = p1.x * p2.y - p1.y * p2.x;
+    double det = p1.x * c23x + p1.y * c23y + p1.z * c23z;
+    if (det == 0.0 || !isfinite(det)) return false;             // LinAlgError -> trial skipped, :294
+    a = (c23x + c31x + c12x) / det;
+    b = (c23y + c31y + c12y) / det;
+    c = (c23z + c31z + c12z) / det;
+    return isfinite(a) && isfinite(b) && isfinite(c);
+}
+
+// The triple of trial t: explicit indices, or counter-based draws repeated while exactly collinear.
+// Returns false when the trial has no plane (M < S, missing indices, retry budget exhausted).
+__device__ __forceinline__ bool trial_triple(const uint32_t *__restrict__ rec, int stride, uint32_t M,
+                                             const CamD &cam, const int32_t *__restrict__ triple,
+                                             uint32_t key, P3 &p1, P3 &p2, P3 &p3, int idx_out[3]) {
+    if (triple) {
+        int i1 = triple[0], i2 = triple[1], i3 = triple[2];
+        if (i1 < 0 || i2 < 0 || i3 < 0 || (uint32_t)i1 >= M || (uint32_t)i2 >= M || (uint32_t)i3 >= M) return false;
+        p1 = expand_point(cam, __ldg(rec + (int64_t)i1 * stride));
+        p2 = expand_point(cam, __ldg(rec + (int64_t)i2 * stride));
+        p3 = expand_point(cam, __ldg(rec + (int64_t)i3 * stride));
+        idx_out[0] = i1; idx_out[1] = i2; idx_out[2] = i3;
+        return true;
+    }
+    for (int round = 0; round < MAX_TRIPLE_ROUNDS; ++round) {
+        uint32_t i1 = uniform_draw(key, 3u * round + 0u, M);
+        uint32_t i2 = uniform_draw(key, 3u * round + 1u, M);
+        uint32_t i3 = uniform_draw(key, 3u * round + 2u, M);
+        p1 = expand_point(cam, __ldg(rec + (int64_t)i1 * stride));
+        p2 = expand_point(cam, __ldg(rec + (int64_t)i2 * stride));
+        p3 = expand_point(cam, __ldg(rec + (int64_t)i3 * stride));
+        if (!exactly_collinear(p1, p2, p3)) {
+            idx_out[0] = (int)i1; idx_out[1] = (int)i2; idx_out[2] = (int)i3;
+            return true;
+        }
+    }
+    return false;
+}
+
+// ------------------------------------------------------------------ score: one warp per hypothesis
+template <bool EXPLICIT>
+__global__ void __launch_bounds__(RANSAC_THREADS)
+ransac_score_kernel(const uint32_t *__restrict__ mcloud, int stride, int64_t slab_records,
+                    const int32_t *__restrict__ counts, int cstride, int ccol,
+                    int T, int S, CamD cam,
+                    const int32_t *__restrict__ sample_idx, const int32_t *__restrict__ triple_idx,
+                    uint64_t seed, int frame0, double *__restrict__ errors) {
+    __shared__ double s_Z[256];
+    s_Z[threadIdx.x] = threadIdx.x ? exact_Z(cam, threadIdx.x) : 0.0;
+    __syncthreads();
+
+    const int f = blockIdx.y;
+    const int lane = threadIdx.x & 31;
+    const int t = blockIdx.x * RANSAC_WARPS + (threadIdx.x >> 5);
+    if (t >= T) return;
+    const int Mi = counts[(int64_t)f * cstride + ccol];
+    double *err_out = errors + (int64_t)f * T + t;
+    if (Mi < S || Mi < 1 || S < 1) {                              // random.sample raises, :286,294
+        if (lane == 0) *err_out = INFINITY;
+        return;
+    }
+    const uint32_t M = (uint32_t)Mi;
+    const uint32_t *rec = mcloud + (int64_t)f * slab_records * stride;
+    const uint32_t key = trial_key(seed, frame0 + f, t);
+    const int32_t *trip = EXPLICIT ? triple_idx + ((int64_t)f * T + t) * 3 : nullptr;
+
+    P3 p1, p2, p3;
+    int tri[3];
+    double a, b, c;
+    bool ok = trial_triple(rec, stride, M, cam, trip, key, p1, p2, p3, tri);
+    ok = ok && plane_of(p1, p2, p3, a, b, c);
+    if (!ok) {
+        if (lane == 0) *err_out = INFINITY;
+        return;
+    }
+    const double af = a / cam.f, bf = b / cam.f;
+    const double nrm = sqrt(a * a + b * b + c * c);
+    const int32_t *samp = EXPLICIT ? sample_idx + ((int64_t)f * T + t) * S : nullptr;
+    const int bits = bits_for(M);
+
+    double acc = 0.0;
+    bool bad = false;
+    for (int j0 = 0; j0 < S; j0 += 128) {
+        uint32_t r[4];
+        bool have[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            int j = j0 + u * 32 + lane;
+            have[u] = j < S;
+            r[u] = 0;
+            if (have[u]) {
+                uint32_t idx;
+                if (EXPLICIT) {
+                    int i = __ldg(samp + j);
+                    if (i < 0 || (uint32_t)i >= M) { bad = true; have[u] = false; idx = 0; }
+                    else idx = (uint32_t)i;
+                } else {
+                    idx = perm_draw(key ^ 0x51ED270Bu, (uint32_t)j, bits, M);
+                }
+                if (have[u]) r[u] = __ldg(rec + (int64_t)idx * stride);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            if (have[u]) {
+                double zd = s_Z[rec_d(r[u])];
+                double s = zd * fma(af, (double)rec_x(r[u]) - cam.cw, fma(bf, (double)rec_y(r[u]) - cam.ch, c));
+                acc += fabs(s - 1.0);
+            }
+        }
+    }
+    acc = warp_sum(acc);
+    bad = __any_sync(0xffffffffu, bad);
+    if (lane == 0) {
+        double e = acc / ((double)S * nrm);
+        *err_out = (bad || isnan(e)) ? INFINITY : e;              // NaN never beats bestError, :291
+    }
+}
+
+extern "C" int svb_ransac_score(const uint32_t *mcloud, int rec_stride_words, int64_t slab_stride_records,
+                                const int32_t *counts, int counts_stride, int counts_col,
+                                int F, int T, int S, const svb_camera *cam,
+                                const int32_t *sample_idx, const int32_t *triple_idx,
+                                uint64_t rng_seed, int frame0, double *errors, void *stream) {
+    if (!mcloud || !counts || !cam || !errors) return SVB_E_NULL;
+    if ((sample_idx == nullptr) != (triple_idx == nullptr)) return SVB_E_NULL;
+    if (F < 1 || T < 1 || S < 1) return SVB_E_SHAPE;
+    if ((rec_stride_words != 1 && rec_stride_words != 2) || counts_stride < 1 || counts_col < 0 ||
+        counts_col >= counts_stride) return SVB_E_ARG;
+    dim3 grid((T + RANSAC_WARPS - 1) / RANSAC_WARPS, F);
+    cudaStream_t st = (cudaStream_t)stream;
+    CamD c = make_camd(cam);
+    if (sample_idx)
+        ransac_score_kernel<true><<<grid, RANSAC_THREADS, 0, st>>>(mcloud, rec_stride_words, slab_stride_records, counts,
+                                                                   counts_stride, counts_col, T, S, c, sample_idx,
+                                                                   triple_idx, rng_seed, frame0, errors);
+    else
+        ransac_score_kernel<false><<<grid, RANSAC_THREADS, 0, st>>>(mcloud, rec_stride_words, slab_stride_records, counts,
+                                                                    counts_stride, counts_col, T, S, c, nullptr,
+                                                                    nullptr, rng_seed, frame0, errors);
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
+}
+
+// ------------------------------------------------------------------ dump of the counter-based draws
+__global__ void ransac_dump_kernel(const uint32_t *__restrict__ mcloud, int stride, int64_t slab_records,
+                                   const int32_t *__restrict__ counts, int cstride, int ccol,
+                                   int T, int S, CamD cam, uint64_t seed, int frame0,
+                                   int32_t *__restrict__ sample_idx, int32_t *__restrict__ triple_idx) {
+    const int f = blockIdx.y;
+    const int lane = threadIdx.x & 31;
+    const int t = blockIdx.x * RANSAC_WARPS + (threadIdx.x >> 5);
+    if (t >= T) return;
+    const int Mi = counts[(int64_t)f * cstride + ccol];
+    int32_t *samp = sample_idx + ((int64_t)f * T + t) * S;
+    int32_t *trip = triple_idx + ((int64_t)f * T + t) * 3;
+    if (Mi < S || Mi < 1) {
+        for (int j = lane; j < S; j += 32) samp[j] = -1;
+        if (lane < 3) trip[lane] = -1;
+        return;
+    }
+    const uint32_t M = (uint32_t)Mi;
+    const uint32_t *rec = mcloud + (int64_t)f * slab_records * stride;
+    const uint32_t key = trial_key(seed, frame0 + f, t);
+    const int bits = bits_for(M);
+    for (int j = lane; j < S; j += 32) samp[j] = (int32_t)perm_draw(key ^ 0x51ED270Bu, (uint32_t)j, bits, M);
+    P3 p1, p2, p3;
+    int tri[3] = {-1, -1, -1};
+    bool ok = trial_triple(rec, stride, M, cam, nullptr, key, p1, p2, p3, tri);
+    if (lane < 3) trip[lane] = ok ? tri[lane] : -1;
+}
+
+extern "C" int svb_ransac_dump_indices(const uint32_t *mcloud, int rec_stride_words, int64_t slab_stride_records,
+                                       const int32_t *counts, int counts_stride, int counts_col,
+                                       int F, int T, int S, const svb_camera *cam,
+                                       uint64_t rng_seed, int frame0,
+                                       int32_t *sample_idx, int32_t *triple_idx, void *stream) {
+    if (!mcloud || !counts || !cam || !sample_idx || !triple_idx) return SVB_E_NULL;
+    if (F < 1 || T < 1 || S < 1) return SVB_E_SHAPE;
+    if ((rec_stride_words != 1 && rec_stride_words != 2) || counts_stride < 1 || counts_col < 0 ||
+        counts_col >= counts_stride) return SVB_E_ARG;
+    dim3 grid((T + RANSAC_WARPS - 1) / RANSAC_WARPS, F);
+    ransac_dump_kernel<<<grid, RANSAC_THREADS, 0, (cudaStream_t)stream>>>(mcloud, rec_stride_words, slab_stride_records,
+                                                                          counts, counts_stride, counts_col, T, S,
+                                                                          make_camd(cam), rng_seed, frame0,
+                                                                          sample_idx, triple_idx);
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
+}
+
+// ------------------------------------------------------------------ arg-min + the winning plane
+// smallest v with fl(v / nrm) >= thr  (so that  |s-1| < v  <=>  fl(|s-1|/nrm) < thr)
+__host__ __device__ inline double plane_cutoff(double nrm, double thr) {
+    if (!(thr > 0.0)) return 0.0;
+    if (thr > 1.7e308) return thr;                              // +inf: everything finite is near
+    double v = thr * nrm;
+    if (!(v > 0.0) || v > 1.7e308) return v > 0.0 ? v : 0.0;
+    union DU { double d; uint64_t u; };
+    DU q;
+    q.d = v;
+    for (int i = 0; i < 64 && (q.d / nrm) < thr; ++i) q.u += 1;      // next double up
+    for (int i = 0; i < 64; ++i) {
+        DU w;
+        w.u = q.u - 1;
+        if (w.u != 0 && (w.d / nrm) >= thr) q.u = w.u; else break;
+    }
+    return q.d;
+}
+
+__host__ __device__ inline void fill_plane_row(double a, double b, double c, double thr, double best_err,
+                                               double best_trial, double *row) {
+#ifdef __CUDA_ARCH__
+    double nrm = __dsqrt_rn(__dadd_rn(__dadd_rn(__dmul_rn(a, a), __dmul_rn(b, b)), __dmul_rn(c, c)));
+#else
+    volatile double aa = a * a, bb = b * b, cc = c * c;          // math.sqrt(a*a+b*b+c*c), :269/:307
+    volatile double s1 = aa + bb;
+    volatile double s2 = s1 + cc;
+    double nrm = sqrt(s2);
+#endif
+    row[0] = a; row[1] = b; row[2] = c; row[3] = nrm;
+    row[4] = plane_cutoff(nrm, thr);
+    row[5] = best_err; row[6] = best_trial;
+    row[7] = (nrm > 0.0 && nrm < 1.7e308) ? 1.0 : 0.0;
+}
+
+__global__ void ransac_finalize_kernel(const uint32_t *__restrict__ mcloud, int stride, int64_t slab_records,
+                                       const int32_t *__restrict__ counts, int cstride, int ccol,
+                                       int T, int S, CamD cam, const int32_t *__restrict__ triple_idx,
+                                       uint64_t seed, int frame0, const double *__restrict__ errors,
+                                       double thr, double *__restrict__ planes) {
+    __shared__ double s_e[128];
+    __shared__ int s_t[128];
+    const int f = blockIdx.x;
+    const double *e = errors + (int64_t)f * T;
+    double be = INFINITY;
+    int bt = -1;
+    for (int t = threadIdx.x; t < T; t += blockDim.x) {
+        double v = e[t];
+        if (v < be) { be = v; bt = t; }                          // strict <, increasing t: first minimum
+    }
+    s_e[threadIdx.x] = be;
+    s_t[threadIdx.x] = bt;
+    __syncthreads();
+    for (int o = blockDim.x >> 1; o > 0; o >>= 1) {
+        if (threadIdx.x < o) {
+            double v = s_e[threadIdx.x + o];
+            int tt = s_t[threadIdx.x + o];
+            bool take = tt >= 0 && (s_t[threadIdx.x] < 0 || v < s_e[threadIdx.x] ||
+                                    (v == s_e[threadIdx.x] && tt < s_t[threadIdx.x]));
+            if (take) { s_e[threadIdx.x] = v; s_t[threadIdx.x] = tt; }
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x != 0) return;
+    double *row = planes + (int64_t)f * SVB_PLANE_STRIDE;
+    bt = s_t[0];
+    be = s_e[0];
+    bool ok = bt >= 0;
+    double a = 0, b = 0, c = 0;
+    if (ok) {
+        const int Mi = counts[(int64_t)f * cstride + ccol];
+        const uint32_t *rec = mcloud + (int64_t)f * slab_records * stride;
+        const int32_t *trip = triple_idx ? triple_idx + ((int64_t)f * T + bt) * 3 : nullptr;
+        P3 p1, p2, p3;
+        int tri[3];
+        ok = Mi >= S && trial_triple(rec, stride, (uint32_t)Mi, cam, trip, trial_key(seed, frame0 + f, bt), p1, p2, p3, tri) &&
+             plane_of(p1, p2, p3, a, b, c);
+    }
+    if (ok) {
+        fill_plane_row(a, b, c, thr, be, (double)bt, row);
+    } else {
+        for (int k = 0; k < SVB_PLANE_STRIDE; ++k) row[k] = 0.0;
+        row[0] = row[1] = row[2] = nan("");
+        row[5] = INFINITY;
+        row[6] = -1.0;
+    }
+}
+
+extern "C" int svb_ransac_finalize(const uint32_t *mcloud, int rec_stride_words, int64_t slab_stride_records,
+                                   const int32_t *counts, int counts_stride, int counts_col,
+                                   int F, int T, int S, const svb_camera *cam,
+                                   const int32_t *triple_idx, uint64_t rng_seed, int frame0,
+                                   const double *errors, double point_threshold,
+                                   double *planes, void *stream) {
+    if (!mcloud || !counts || !cam || !errors || !planes) return SVB_E_NULL;
+    if (F < 1 || T < 1 || S < 1) return SVB_E_SHAPE;
+    if ((rec_stride_words != 1 && rec_stride_words != 2) || counts_stride < 1 || counts_col < 0 ||
+        counts_col >= counts_stride) return SVB_E_ARG;
+    ransac_finalize_kernel<<<F, 128, 0, (cudaStream_t)stream>>>(mcloud, rec_stride_words, slab_stride_records, counts,
+                                                               counts_stride, counts_col, T, S, make_camd(cam),
+                                                               triple_idx, rng_seed, frame0, errors, point_threshold, planes);
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
+}
+
+extern "C" int svb_plane_from_abc(const double *h_abc, double point_threshold, double *h_plane_row) {
+    if (!h_abc || !h_plane_row) return SVB_E_NULL;
+    fill_plane_row(h_abc[0], h_abc[1], h_abc[2], point_threshold, 0.0, -1.0, h_plane_row);
+    return SVB_OK;
+}

@@ -1,0 +1,436 @@
+// a8-a14: point-plane distances, threshold, hue histogram + dominant-colour filter, 3-D -> 2-D
+// reprojection and the road-mask scatter -- as stand-alone helpers (one per reference function)
+// and as the fused, frame-batched pair of passes the throughput path runs.
+//
+// Two passes are inherent: the colour filter needs the complete histogram of the near-plane points
+// before any point can be kept (functions.py:215-230).  Pass 1 streams the 8-byte records once,
+// tests |P.abc - 1| < cutoff (the exact-equivalent of dist < threshold, see svb_ransac_finalize),
+// keeps the answer as one bit per point and builds the frame's 1001-bin histogram in shared memory
+// (merged into global memory with one atomic per non-empty bin per block).  Pass 2 streams the
+// records again, looks the bit and the bin count up, reprojects the survivors with the reference's
+// float64 expression and stores 255 into the mask (idempotent byte stores, no atomics).
+#include "svb_common.cuh"
+#include <math.h>
+
+#define ROAD_THREADS 256
+#define ROAD_CHUNK 8192          // records per block in the fused passes
+
+// ------------------------------------------------------------------ a8 calculatePointErrors
+__global__ void point_errors_kernel(const uint32_t *__restrict__ rec, int stride, int n, CamD cam,
+                                    double a, double b, double c, double nrm, double *__restrict__ dist) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint32_t lo = __ldg(rec + (int64_t)i * stride);
+    double Z = exact_Z(cam, rec_d(lo));
+    double X = exact_XY(cam.cw, cam.f, rec_x(lo), Z);
+    double Y = exact_XY(cam.ch, cam.f, rec_y(lo), Z);
+    double s = exact_dot(X, Y, Z, a, b, c);
+    dist[i] = fabs(__ddiv_rn(__dsub_rn(s, 1.0), nrm));           // abs((dot - 1)/d), functions.py:310
+}
+
+extern "C" int svb_point_errors(const uint32_t *records, int rec_stride_words, int n, const svb_camera *cam,
+                                const double *h_abc, double *dist, void *stream) {
+    if (n == 0) return SVB_OK;
+    if (!records || !cam || !h_abc || !dist) return SVB_E_NULL;
+    if (n < 0 || (rec_stride_words != 1 && rec_stride_words != 2)) return SVB_E_ARG;
+    double row[SVB_PLANE_STRIDE];
+    svb_plane_from_abc(h_abc, 0.0, row);
+    point_errors_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(records, rec_stride_words, n, make_camd(cam),
+                                                                            row[0], row[1], row[2], row[3], dist);
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
+}
+
+// ------------------------------------------------------------------ a9 / a12 stable compaction
+#define COMPACT_PER_BLOCK 2048
+
+__device__ __forceinline__ bool keep_flag(int mode, const uint64_t *__restrict__ cloud, const double *__restrict__ dist,
+                                          const uint32_t *__restrict__ hist, double thr, uint32_t uthr, int i) {
+    if (mode == 0) return dist[i] < thr;                         // differences[i] < threshold, :321
+    uint64_t r = cloud[i];
+    return hist[rec_hue((uint32_t)r, (uint32_t)(r >> 32))] > uthr;   // histogram[key] > threshold, :230
+}
+
+__global__ void compact_count_kernel(const uint64_t *__restrict__ cloud, int n, int mode, const double *__restrict__ dist,
+                                     const uint32_t *__restrict__ hist, double thr, uint32_t uthr,
+                                     uint32_t *__restrict__ block_counts) {
+    __shared__ int s_cnt;
+    if (threadIdx.x == 0) s_cnt = 0;
+    __syncthreads();
+    int base = blockIdx.x * COMPACT_PER_BLOCK;
+    int c = 0;
+    for (int k = threadIdx.x; k < COMPACT_PER_BLOCK; k += blockDim.x) {
+        int i = base + k;
+        if (i < n && keep_flag(mode, cloud, dist, hist, thr, uthr, i)) ++c;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+    if ((threadIdx.x & 31) == 0) atomicAdd(&s_cnt, c);
+    __syncthreads();
+    if (threadIdx.x == 0) block_counts[blockIdx.x] = (uint32_t)s_cnt;
+}
+
+__global__ void compact_scan_kernel(uint32_t *__restrict__ block_counts, int nblocks, int32_t *__restrict__ out_count) {
+    __shared__ uint32_t sw[32];
+    int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    uint32_t carry = 0;
+    for (int base = 0; base < nblocks; base += blockDim.x) {
+        int i = base + threadIdx.x;
+        int v = i < nblocks ? (int)block_counts[i] : 0;
+        int inc = warp_incl_scan(v, lane);
+        if (lane == 31) sw[wid] = inc;
+        __syncthreads();
+        uint32_t b = 0, tot = 0;
+        for (int w = 0; w < nw; ++w) { if (w < wid) b += sw[w]; tot += sw[w]; }
+        if (i < nblocks) block_counts[i] = carry + b + inc - v;
+        carry += tot;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) out_count[0] = (int32_t)carry;
+}
+
+__global__ void __launch_bounds__(256)
+compact_write_kernel(const uint64_t *__restrict__ cloud, int n, int mode, const double *__restrict__ dist,
+                     const uint32_t *__restrict__ hist, double thr, uint32_t uthr,
+                     const uint32_t *__restrict__ block_offsets, uint64_t *__restrict__ out) {
+    __shared__ uint32_t s_w[8];
+    __shared__ uint32_t s_run;
+    if (threadIdx.x == 0) s_run = block_offsets[blockIdx.x];
+    __syncthreads();
+    int base = blockIdx.x * COMPACT_PER_BLOCK;
+    int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    for (int k0 = 0; k0 < COMPACT_PER_BLOCK; k0 += 256) {
+        int i = base + k0 + threadIdx.x;
+        bool keep = i < n && keep_flag(mode, cloud, dist, hist, thr, uthr, i);
+        uint32_t bal = __ballot_sync(0xffffffffu, keep);
+        if (lane == 0) s_w[wid] = __popc(bal);
+        __syncthreads();
+        uint32_t off = s_run, tot = 0;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) { if (w < wid) off += s_w[w]; tot += s_w[w]; }
+        if (keep) out[off + __popc(bal & ((1u << lane) - 1u))] = cloud[i];
+        __syncthreads();
+        if (threadIdx.x == 0) s_run += tot;
+        __syncthreads();
+    }
+}
+
+extern "C" int64_t svb_compact_scratch_bytes(int n) {
+    int nb = (n + COMPACT_PER_BLOCK - 1) / COMPACT_PER_BLOCK;
+    return (int64_t)(nb + 1) * (int64_t)sizeof(uint32_t);
+}
+
+extern "C" int svb_compact_cloud(const uint64_t *cloud, int n, int mode, const double *dist,
+                                 const uint32_t *hist, double threshold,
+                                 uint64_t *out_cloud, int32_t *out_count,
+                                 void *scratch, int64_t scratch_bytes, void *stream) {
+    if (!out_count) return SVB_E_NULL;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n == 0) {
+        cudaError_t e = cudaMemsetAsync(out_count, 0, sizeof(int32_t), st);
+        return e == cudaSuccess ? SVB_OK : (int)e;
+    }
+    if (!cloud || !out_cloud || !scratch) return SVB_E_NULL;
+    if (n < 0 || (mode != 0 && mode != 1)) return SVB_E_ARG;
+    if ((mode == 0 && !dist) || (mode == 1 && !hist)) return SVB_E_NULL;
+    if (scratch_bytes < svb_compact_scratch_bytes(n)) return SVB_E_SCRATCH;
+    int nb = (n + COMPACT_PER_BLOCK - 1) / COMPACT_PER_BLOCK;
+    uint32_t *bc = (uint32_t *)scratch;
+    // histogram[key] > threshold compares integer counts with the caller's number
+    double t = threshold;
+    uint32_t uthr = t < 0 ? 0u : (t >= 4294967295.0 ? 0xFFFFFFFFu : (uint32_t)floor(t));
+    if (mode == 1 && t < 0) uthr = 0;                            // count > negative: always true (count >= 1 ... or 0 > t)
+    compact_count_kernel<<<nb, 256, 0, st>>>(cloud, n, mode, dist, hist, threshold, uthr, bc);
+    SVB_LAUNCH_CHECK();
+    compact_scan_kernel<<<1, 256, 0, st>>>(bc, nb, out_count);
+    SVB_LAUNCH_CHECK();
+    compact_write_kernel<<<nb, 256, 0, st>>>(cloud, n, mode, dist, hist, threshold, uthr, bc, out_cloud);
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
+}
+
+// ------------------------------------------------------------------ a10-a11 hue histogram
+__global__ void __launch_bounds__(256)
+hue_hist_kernel(const uint64_t *__restrict__ cloud, int n, uint32_t *__restrict__ hist) {
+    __shared__ uint32_t s_h[SVB_HIST_STRIDE];
+    for (int k = threadIdx.x; k < SVB_HIST_STRIDE; k += blockDim.x) s_h[k] = 0;
+    __syncthreads();
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        uint64_t r = cloud[i];
+        atomicAdd(&s_h[rec_hue((uint32_t)r, (uint32_t)(r >> 32))], 1u);
+    }
+    __syncthreads();
+    for (int k = threadIdx.x; k < SVB_HUE_BINS; k += blockDim.x)
+        if (s_h[k]) atomicAdd(&hist[k], s_h[k]);
+}
+
+extern "C" int svb_hue_histogram(const uint64_t *cloud, int n, uint32_t *hist, void *stream) {
+    if (!hist) return SVB_E_NULL;
+    cudaStream_t st = (cudaStream_t)stream;
+    cudaError_t e = cudaMemsetAsync(hist, 0, SVB_HIST_STRIDE * sizeof(uint32_t), st);
+    if (e != cudaSuccess) return (int)e;
+    if (n == 0) return SVB_OK;
+    if (!cloud) return SVB_E_NULL;
+    if (n < 0) return SVB_E_ARG;
+    int blocks = (n + 256 * 16 - 1) / (256 * 16);
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    hue_hist_kernel<<<blocks, 256, 0, st>>>(cloud, n, hist);
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
+}
+
+__global__ void hue_bins_kernel(const uint8_t *__restrict__ rgb, int64_t n, uint16_t *__restrict__ bins) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    bins[i] = (uint16_t)exact_hue_bin(rgb[3 * i], rgb[3 * i + 1], rgb[3 * i + 2]);
+}
+
+extern "C" int svb_hue_bins(const uint8_t *rgb, int64_t n, uint16_t *bins, void *stream) {
+    if (n == 0) return SVB_OK;
+    if (!rgb || !bins) return SVB_E_NULL;
+    if (n < 0) return SVB_E_ARG;
+    hue_bins_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(rgb, n, bins);
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
+}
+
+// ------------------------------------------------------------------ a13 reprojection
+__global__ void reproject_kernel(const uint32_t *__restrict__ rec, int stride, int n, CamD cam,
+                                 double *__restrict__ xy, int32_t *__restrict__ xyi) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint32_t lo = __ldg(rec + (int64_t)i * stride);
+    double Z = exact_Z(cam, rec_d(lo));
+    double X = exact_XY(cam.cw, cam.f, rec_x(lo), Z);
+    double Y = exact_XY(cam.ch, cam.f, rec_y(lo), Z);
+    double px = exact_reproject(cam.cw, cam.f, X, Z);
+    double py = exact_reproject(cam.ch, cam.f, Y, Z);
+    if (xy) { xy[2 * (int64_t)i] = px; xy[2 * (int64_t)i + 1] = py; }
+    if (xyi) { xyi[2 * (int64_t)i] = (int32_t)px; xyi[2 * (int64_t)i + 1] = (int32_t)py; }   // trunc toward zero
+}
+
+extern "C" int svb_reproject(const uint32_t *records, int rec_stride_words, int n, const svb_camera *cam,
+                             double *xy_f64, int32_t *xy_i32, void *stream) {
+    if (n == 0) return SVB_OK;
+    if (!records || !cam) return SVB_E_NULL;
+    if (n < 0 || (rec_stride_words != 1 && rec_stride_words != 2)) return SVB_E_ARG;
+    reproject_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(records, rec_stride_words, n, make_camd(cam),
+                                                                         xy_f64, xy_i32);
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
+}
+
+__global__ void reproject_table_kernel(int axis, int n_coord, CamD cam, int32_t *__restrict__ out) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_coord * 256) return;
+    int coord = i >> 8, d = i & 255;
+    if (d == 0) { out[i] = -1; return; }
+    double centre = axis == 0 ? cam.cw : cam.ch;
+    double Z = exact_Z(cam, d);
+    double V = exact_XY(centre, cam.f, coord, Z);
+    out[i] = (int32_t)exact_reproject(centre, cam.f, V, Z);
+}
+
+extern "C" int svb_reproject_table(int axis, int n_coord, const svb_camera *cam, int32_t *out, void *stream) {
+    if (!cam || !out) return SVB_E_NULL;
+    if (n_coord < 1 || (axis != 0 && axis != 1)) return SVB_E_ARG;
+    int total = n_coord * 256;
+    reproject_table_kernel<<<(total + 255) / 256, 256, 0, (cudaStream_t)stream>>>(axis, n_coord, make_camd(cam), out);
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
+}
+
+// ------------------------------------------------------------------ a14 scatter
+__global__ void scatter_points_kernel(const int32_t *__restrict__ pts, int n, uint8_t *__restrict__ img,
+                                      int H, int W, int channels, uint32_t value, int32_t *__restrict__ oob) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    int x = pts[2 * (int64_t)i], y = pts[2 * (int64_t)i + 1];
+    if (x < 0 || y < 0 || x >= W || y >= H) {
+        if (oob) atomicAdd(oob, 1);
+        return;
+    }
+    uint8_t *p = img + ((int64_t)y * W + x) * channels;
+    for (int k = 0; k < channels; ++k) p[k] = (uint8_t)(value >> (8 * k));
+}
+
+extern "C" int svb_scatter_points(const int32_t *pts, int n, uint8_t *img, int H, int W, int channels,
+                                  const uint8_t *h_value, int32_t *oob, void *stream) {
+    if (n == 0) return SVB_OK;
+    if (!pts || !img || !h_value) return SVB_E_NULL;
+    if (n < 0 || H < 1 || W < 1 || channels < 1 || channels > 4) return SVB_E_ARG;
+    uint32_t v = 0;
+    for (int k = 0; k < channels; ++k) v |= (uint32_t)h_value[k] << (8 * k);
+    scatter_points_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(pts, n, img, H, W, channels, v, oob);
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
+}
+
+// ------------------------------------------------------------------ fused, frame-batched road points
+struct RoadGeom {
+    int H, W;
+    int64_t slab;        // records per frame slab (= lattice size)
+    int words;           // near-bit words per frame
+    int parts;           // blocks per frame
+};
+
+static RoadGeom make_road_geom(int H, int W, int step) {
+    RoadGeom g;
+    g.H = H; g.W = W;
+    int LH = svb_lattice_rows(H, step), LW = svb_lattice_cols(W, step);
+    g.slab = (int64_t)LH * LW;
+    g.words = (int)((g.slab + 31) / 32);
+    g.parts = (int)((g.slab + ROAD_CHUNK - 1) / ROAD_CHUNK);
+    if (g.parts < 1) g.parts = 1;
+    return g;
+}
+
+// pass 1: near bits + histogram of the near points
+__global__ void __launch_bounds__(ROAD_THREADS)
+road_pass1_kernel(const uint64_t *__restrict__ cloud, const int32_t *__restrict__ counts,
+                  const double *__restrict__ planes, RoadGeom g, CamD cam,
+                  uint32_t *__restrict__ nearbits, uint32_t *__restrict__ hist, int32_t *__restrict__ counts_out) {
+    __shared__ uint32_t s_h[SVB_HIST_STRIDE];
+    __shared__ double s_Z[256];
+    __shared__ int s_k;
+    const int f = blockIdx.y;
+    const int n = counts[f * 4 + 0];
+    const int begin = blockIdx.x * ROAD_CHUNK;
+    if (begin >= n) return;
+    const double *pl = planes + (int64_t)f * SVB_PLANE_STRIDE;
+    const bool valid = pl[7] != 0.0;
+    const int end = min(n, begin + ROAD_CHUNK);
+    uint32_t *bits = nearbits + (int64_t)f * g.words;
+    if (!valid) {                                                 // no plane: nothing is near (stereovision.py:117)
+        for (int w = begin / 32 + threadIdx.x; w < (end + 31) / 32; w += ROAD_THREADS) bits[w] = 0u;
+        return;
+    }
+    for (int k = threadIdx.x; k < SVB_HIST_STRIDE; k += ROAD_THREADS) s_h[k] = 0;
+    s_Z[threadIdx.x] = threadIdx.x ? exact_Z(cam, threadIdx.x) : 0.0;
+    if (threadIdx.x == 0) s_k = 0;
+    __syncthreads();
+    const double a = pl[0], b = pl[1], c = pl[2], cutoff = pl[4];
+    const uint64_t *rec = cloud + (int64_t)f * g.slab;
+    int kcount = 0;
+    for (int i0 = begin + (threadIdx.x & ~31); i0 < end; i0 += ROAD_THREADS) {
+        int i = i0 + (threadIdx.x & 31);
+        bool near = false;
+        if (i < end) {
+            uint64_t r = __ldcs((const unsigned long long *)(rec + i));
+            uint32_t lo = (uint32_t)r, hi = (uint32_t)(r >> 32);
+            double Z = s_Z[rec_d(lo)];
+            double X = exact_XY(cam.cw, cam.f, rec_x(lo), Z);
+            double Y = exact_XY(cam.ch, cam.f, rec_y(lo), Z);
+            double s = exact_dot(X, Y, Z, a, b, c);
+            near = fabs(__dsub_rn(s, 1.0)) < cutoff;
+            if (near) atomicAdd(&s_h[rec_hue(lo, hi)], 1u);
+        }
+        uint32_t bal = __ballot_sync(0xffffffffu, near);
+        if ((threadIdx.x & 31) == 0) {
+            bits[i0 >> 5] = bal;
+            kcount += __popc(bal);
+        }
+    }
+    if ((threadIdx.x & 31) == 0 && kcount) atomicAdd(&s_k, kcount);
+    __syncthreads();
+    uint32_t *gh = hist + (int64_t)f * SVB_HIST_STRIDE;
+    for (int k = threadIdx.x; k < SVB_HUE_BINS; k += ROAD_THREADS)
+        if (s_h[k]) atomicAdd(&gh[k], s_h[k]);
+    if (threadIdx.x == 0 && s_k) atomicAdd(&counts_out[f * 4 + 2], s_k);
+}
+
+// pass 2: colour filter, reprojection, scatter
+template <bool OVERLAY>
+__global__ void __launch_bounds__(ROAD_THREADS)
+road_pass2_kernel(const uint64_t *__restrict__ cloud, const int32_t *__restrict__ counts,
+                  const double *__restrict__ planes, RoadGeom g, CamD cam, uint32_t colour_threshold,
+                  const uint32_t *__restrict__ nearbits, const uint32_t *__restrict__ hist,
+                  uint8_t *__restrict__ road_mask, uint8_t *__restrict__ overlay, int32_t *__restrict__ counts_out) {
+    __shared__ uint32_t s_h[SVB_HIST_STRIDE];
+    __shared__ double s_Z[256];
+    __shared__ int s_r;
+    const int f = blockIdx.y;
+    const int n = counts[f * 4 + 0];
+    const int begin = blockIdx.x * ROAD_CHUNK;
+    if (begin >= n) return;
+    const double *pl = planes + (int64_t)f * SVB_PLANE_STRIDE;
+    if (pl[7] == 0.0) return;
+    const int end = min(n, begin + ROAD_CHUNK);
+    const uint32_t *gh = hist + (int64_t)f * SVB_HIST_STRIDE;
+    for (int k = threadIdx.x; k < SVB_HIST_STRIDE; k += ROAD_THREADS) s_h[k] = gh[k];
+    s_Z[threadIdx.x] = threadIdx.x ? exact_Z(cam, threadIdx.x) : 0.0;
+    if (threadIdx.x == 0) s_r = 0;
+    __syncthreads();
+    const uint64_t *rec = cloud + (int64_t)f * g.slab;
+    const uint32_t *bits = nearbits + (int64_t)f * g.words;
+    uint8_t *mask = road_mask + (int64_t)f * g.H * g.W;
+    uint8_t *ovl = OVERLAY ? overlay + (int64_t)f * g.H * g.W * 3 : nullptr;
+    int rcount = 0;
+    for (int i0 = begin + (threadIdx.x & ~31); i0 < end; i0 += ROAD_THREADS) {
+        uint32_t word = __ldg(bits + (i0 >> 5));
+        int lane = threadIdx.x & 31;
+        bool keep = false;
+        if ((word >> lane) & 1u) {
+            uint64_t r = __ldcs((const unsigned long long *)(rec + i0 + lane));
+            uint32_t lo = (uint32_t)r, hi = (uint32_t)(r >> 32);
+            if (s_h[rec_hue(lo, hi)] > colour_threshold) {
+                keep = true;
+                double Z = s_Z[rec_d(lo)];
+                double X = exact_XY(cam.cw, cam.f, rec_x(lo), Z);
+                double Y = exact_XY(cam.ch, cam.f, rec_y(lo), Z);
+                int px = (int)exact_reproject(cam.cw, cam.f, X, Z);
+                int py = (int)exact_reproject(cam.ch, cam.f, Y, Z);
+                if (px >= 0 && py >= 0 && px < g.W && py < g.H) {
+                    mask[(int64_t)py * g.W + px] = 255;
+                    if (OVERLAY) {
+                        uint8_t *q = ovl + ((int64_t)py * g.W + px) * 3;
+                        q[0] = 0; q[1] = 255; q[2] = 0;           // [0,255,0], stereovision.py:133
+                    }
+                }
+            }
+        }
+        uint32_t bal = __ballot_sync(0xffffffffu, keep);
+        if (lane == 0) rcount += __popc(bal);
+    }
+    if ((threadIdx.x & 31) == 0 && rcount) atomicAdd(&s_r, rcount);
+    __syncthreads();
+    if (threadIdx.x == 0 && s_r) atomicAdd(&counts_out[f * 4 + 3], s_r);
+}
+
+extern "C" int64_t svb_road_scratch_bytes(int F, int H, int W, int step) {
+    if (F < 1 || H < 2 || W < 2 || step < 1) return 0;
+    RoadGeom g = make_road_geom(H, W, step);
+    return (int64_t)F * g.words * (int64_t)sizeof(uint32_t);
+}
+
+extern "C" int svb_road_points(const uint64_t *cloud, const int32_t *counts, const double *planes,
+                               int F, int H, int W, int step, const svb_camera *cam,
+                               uint32_t colour_threshold,
+                               uint32_t *hist, uint8_t *road_mask, uint8_t *overlay, int32_t *counts_out,
+                               void *scratch, int64_t scratch_bytes, void *stream) {
+    if (!cloud || !counts || !planes || !cam || !hist || !road_mask || !counts_out || !scratch) return SVB_E_NULL;
+    if (F < 1 || H < 2 || W < 2 || H > SVB_MAX_DIM || W > SVB_MAX_DIM || step < 1) return SVB_E_SHAPE;
+    if (scratch_bytes < svb_road_scratch_bytes(F, H, W, step)) return SVB_E_SCRATCH;
+    cudaStream_t st = (cudaStream_t)stream;
+    RoadGeom g = make_road_geom(H, W, step);
+    CamD c = make_camd(cam);
+    cudaError_t e;
+    e = cudaMemsetAsync(hist, 0, (size_t)F * SVB_HIST_STRIDE * sizeof(uint32_t), st);
+    if (e != cudaSuccess) return (int)e;
+    e = cudaMemsetAsync(road_mask, 0, (size_t)F * H * W, st);
+    if (e != cudaSuccess) return (int)e;
+    e = cudaMemset2DAsync(counts_out + 2, 4 * sizeof(int32_t), 0, 2 * sizeof(int32_t), F, st);
+    if (e != cudaSuccess) return (int)e;
+    dim3 grid(g.parts, F);
+    uint32_t *nearbits = (uint32_t *)scratch;
+    road_pass1_kernel<<<grid, ROAD_THREADS, 0, st>>>(cloud, counts, planes, g, c, nearbits, hist, counts_out);
+    SVB_LAUNCH_CHECK();
+    if (overlay)
+        road_pass2_kernel<true><<<grid, ROAD_THREADS, 0, st>>>(cloud, counts, planes, g, c, colour_threshold, nearbits,
+                                                               hist, road_mask, overlay, counts_out);
+    else
+        road_pass2_kernel<false><<<grid, ROAD_THREADS, 0, st>>>(cloud, counts, planes, g, c, colour_threshold, nearbits,
+                                                                hist, road_mask, nullptr, counts_out);
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
+}

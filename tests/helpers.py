@@ -1,0 +1,73 @@
+"""Shared test helpers: record decoding and the oracle run over a sequence."""
+import numpy as np
+
+import np_oracle as no
+import stereo.vision_b200.synth as synth
+
+
+def decode_cloud(rec_i64: np.ndarray):
+    """uint64 records (as int64) -> dict(x, y, d, rgb [n,3], hue)."""
+    r = rec_i64.astype(np.uint64)
+    lo = (r & np.uint64(0xFFFFFFFF)).astype(np.uint32)
+    hi = (r >> np.uint64(32)).astype(np.uint32)
+    return {
+        "x": (lo & 0x7FF).astype(np.int32), "y": ((lo >> 11) & 0x7FF).astype(np.int32),
+        "d": ((lo >> 22) & 0xFF).astype(np.uint8),
+        "rgb": np.stack([hi & 0xFF, (hi >> 8) & 0xFF, (hi >> 16) & 0xFF], axis=1).astype(np.uint8),
+        "hue": ((lo >> 30) | ((hi >> 24) << 2)).astype(np.int32),
+    }
+
+
+def decode_mcloud(rec_i32: np.ndarray):
+    lo = rec_i32.astype(np.uint32)
+    return {"x": (lo & 0x7FF).astype(np.int32), "y": ((lo >> 11) & 0x7FF).astype(np.int32),
+            "d": ((lo >> 22) & 0xFF).astype(np.uint8)}
+
+
+def oracle_sequence(disp, bgr, carmask, seeds=None, indices=None, prev=None, **kw):
+    """Run the numpy oracle frame by frame, chaining the filled disparity.  Returns list of dicts."""
+    out = []
+    for t in range(len(disp)):
+        ind = None if indices is None else (indices[0][t], indices[1][t])
+        o = no.run_frame(disp[t], bgr[t], prev, carmask, seed=None if seeds is None else seeds[t],
+                         indices=ind, **kw)
+        prev = o["filled"]
+        out.append(o)
+    return out
+
+
+def check_frame(res, t, o, abc_rtol=1e-9):
+    """Compare frame t of a BatchResult (already on host as dict of numpy arrays) with oracle dict o."""
+    N, M, K, R = [int(v) for v in res["counts"][t]]
+    assert np.array_equal(res["filled"][t], o["filled"]), "filled disparity"
+    c, mc = o["cloud"], o["mcloud"]
+    assert N == len(c["d"]) and M == len(mc["d"]), ("counts", N, len(c["d"]), M, len(mc["d"]))
+    g = decode_cloud(res["cloud"][t][:N])
+    assert np.array_equal(g["y"], c["sites"][:, 0]) and np.array_equal(g["x"], c["sites"][:, 1]), "cloud order"
+    assert np.array_equal(g["d"], c["d"]), "cloud d"
+    assert np.array_equal(g["rgb"], c["rgb"]), "cloud rgb"
+    assert np.array_equal(g["hue"], no.hue_bin(c["rgb"][:, 0], c["rgb"][:, 1], c["rgb"][:, 2])), "hue bins"
+    gm = decode_mcloud(res["mcloud"][t][:M])
+    assert np.array_equal(gm["y"], mc["sites"][:, 0]) and np.array_equal(gm["x"], mc["sites"][:, 1]), "mcloud order"
+    assert np.array_equal(gm["d"], mc["d"]), "mcloud d"
+    pl = res["planes"][t]
+    if o["abc"] is None:
+        assert pl[7] == 0.0 and int(pl[6]) == -1 and K == 0 and R == 0
+        assert not res["road_mask"][t].any()
+        return
+    assert pl[7] == 1.0
+    assert int(pl[6]) == o["best"], ("best trial", int(pl[6]), o["best"])
+    np.testing.assert_allclose(pl[:3], o["abc"], rtol=abc_rtol)
+    fin = np.isfinite(o["errors"])
+    assert np.array_equal(np.isfinite(res["errors"][t]), fin)
+    np.testing.assert_allclose(res["errors"][t][fin], o["errors"][fin], rtol=1e-9)
+    rd = o["road"]
+    assert K == rd["near_n"], ("near", K, rd["near_n"])
+    assert np.array_equal(res["hist"][t][:no.HUE_BINS].astype(np.int64), rd["hist"]), "hue histogram"
+    assert R == rd["road_n"], ("road", R, rd["road_n"])
+    assert np.array_equal(res["road_mask"][t], rd["mask"]), "road mask"
+
+
+def to_host(res):
+    return {k: getattr(res, k).cpu().numpy() for k in
+            ("filled", "counts", "planes", "errors", "hist", "road_mask", "cloud", "mcloud")}

@@ -1,0 +1,87 @@
+"""GPU parity of the fused path (RoadPath.process) against the numpy oracle."""
+import numpy as np
+import pytest
+
+import np_oracle as no
+import stereo.vision_b200.synth as synth
+from helpers import check_frame, oracle_sequence, to_host
+
+pytestmark = pytest.mark.gpu
+
+
+def _carmask(shape):
+    from stereo.vision_b200.masks import default_carmask
+    return default_carmask(shape, prefer_cwd=False)
+
+
+def test_sequence_python_replay_indices(cuda):
+    """3 chained frames, full size, draws = replay of Python's random under the frame seeds."""
+    from stereo.vision_b200.pipeline import RoadPath
+    F, T, S = 3, 600, 600
+    disp, bgr = synth.make_sequence(0, F)
+    cm = _carmask(disp.shape[1:])
+    seeds = [synth.ransac_seed(0, t) for t in range(F)]
+    orc = oracle_sequence(disp, bgr, cm, seeds=seeds, trials=T, n_samples=S)
+    si = np.stack([o["indices"][0] for o in orc])
+    ti = np.stack([o["indices"][1] for o in orc])
+    eng = RoadPath(trials=T, samples=S, carmask=cm, max_frames=F)
+    res = to_host(eng.process(disp, bgr, indices=(si, ti)))
+    for t in range(F):
+        check_frame(res, t, orc[t])
+
+
+@pytest.mark.parametrize("S", [400, 600])
+def test_sequence_device_draws(cuda, S):
+    """Counter-based on-device draws: dump them, feed the oracle the same indices, compare."""
+    from stereo.vision_b200.pipeline import RoadPath
+    F, T = 4, 600
+    disp, bgr = synth.make_sequence(1, F)
+    cm = _carmask(disp.shape[1:])
+    eng = RoadPath(trials=T, samples=S, carmask=cm, max_frames=F)
+    r = eng.process(disp, bgr, seed=1234, frame0=7)
+    si, ti = eng.dump_indices(F, seed=1234, frame0=7)
+    si, ti = si.cpu().numpy(), ti.cpu().numpy()
+    res = to_host(r)
+    M = res["counts"][:, 1]
+    for t in range(F):
+        assert si[t].min() >= 0 and si[t].max() < M[t]
+        srt = np.sort(si[t], axis=1)
+        assert (np.diff(srt, axis=1) > 0).all(), "samples of a trial must be distinct"
+    orc = oracle_sequence(disp, bgr, cm, indices=(si, ti), trials=T, n_samples=S)
+    for t in range(F):
+        check_frame(res, t, orc[t])
+
+
+@pytest.mark.parametrize("shape,step", [((37, 53), 1), ((37, 53), 2), ((64, 96), 3), ((48, 80), 2), ((33, 64), 1)])
+def test_small_ragged_shapes(cuda, shape, step):
+    """Unaligned widths (scalar loads), odd steps, tiny clouds; draws from the device."""
+    from stereo.vision_b200.pipeline import RoadPath
+    rng = np.random.default_rng(5)
+    F, T, S = 3, 64, 40
+    H, W = shape
+    disp = rng.integers(0, 60, size=(F, H, W), dtype=np.uint8)
+    disp[rng.random((F, H, W)) < 0.3] = 0
+    bgr = rng.integers(0, 256, size=(F, H, W, 3), dtype=np.uint8)
+    cm = (rng.random((H, W)) < 0.7).astype(np.uint8) * 200
+    eng = RoadPath(shape=shape, step=step, trials=T, samples=S, carmask=cm, max_frames=F, point_threshold=0.5,
+                   colour_threshold=0)
+    r = eng.process(disp, bgr, seed=9)
+    si, ti = eng.dump_indices(F, seed=9)
+    res = to_host(r)
+    orc = oracle_sequence(disp, bgr, cm, indices=(si.cpu().numpy(), ti.cpu().numpy()), trials=T, n_samples=S,
+                          step=step, threshold=0.5, colour_threshold=0)
+    for t in range(F):
+        check_frame(res, t, orc[t])
+
+
+def test_no_plane_when_masked_cloud_too_small(cuda):
+    """M < S: every trial raises in the reference -> RANSAC returns (None, None) -> black mask."""
+    from stereo.vision_b200.pipeline import RoadPath
+    disp, bgr = synth.make_sequence(2, 1)
+    cm = np.zeros(disp.shape[1:], np.uint8)
+    cm[200:210, 100:160] = 255                       # 5 x 30 lattice sites at most
+    eng = RoadPath(carmask=cm, max_frames=1)
+    res = to_host(eng.process(disp, bgr, seed=3))
+    orc = oracle_sequence(disp, bgr, cm, seeds=[0])
+    assert orc[0]["abc"] is None
+    check_frame(res, 0, orc[0])
