@@ -184,17 +184,30 @@ def plane_distance(xyz, abc):
     return np.abs((s - 1.0) / nrm)
 
 
-def ransac_from_indices(mask_xyz, sample_idx, triple_idx):
+def image_collinear(sites3):
+    """Three pixel sites on one image line: their plane contains the camera centre, [P1;P2;P3] has
+    rank 2 in exact arithmetic and np.linalg.inv returns rounding noise (LinAlgError for about half
+    of such triples here, |abc| ~ 1e14 otherwise -- machine dependent).  Both this oracle and the
+    product treat the triple as singular (trial skipped, functions.py:294-296); measured on the
+    golden frames such a hypothesis never comes near winning ("degenerate triples")."""
+    (y1, x1), (y2, x2), (y3, x3) = [(int(a), int(b)) for a, b in sites3]
+    return (x2 - x1) * (y3 - y1) - (x3 - x1) * (y2 - y1) == 0
+
+
+def ransac_from_indices(mask_xyz, sample_idx, triple_idx, sites=None):
     """functions.py:278-298 with the draws given.  Returns (best_trial, abc or None, errors [T]).
 
     error = mean distance of the trial's S sample points to the trial's plane (:289); the first
-    strict minimum wins (:291); a singular triple or a NaN error never wins.
+    strict minimum wins (:291); a singular triple or a NaN error never wins.  `sites` [M,2] enables
+    the image-collinear rule above.
     """
     T = len(sample_idx)
     errs = np.full(T, np.inf)
     planes = np.full((T, 3), np.nan)
     for t in range(T):
         if triple_idx[t, 0] < 0:
+            continue
+        if sites is not None and image_collinear(sites[triple_idx[t]]):
             continue
         abc = plane_of_triple(mask_xyz[triple_idx[t]])
         if abc is None:
@@ -244,7 +257,7 @@ def run_frame(disparity, bgr, prev, carmask, seed=None, trials=600, n_samples=60
     mcloud = project(mask_disparity(filled, carmask), camera, step)
     if indices is None:
         indices = replay_indices(mcloud["xyz"], trials, n_samples, seed)
-    best, abc, errs = ransac_from_indices(mcloud["xyz"], indices[0], indices[1])
+    best, abc, errs = ransac_from_indices(mcloud["xyz"], indices[0], indices[1], mcloud["sites"])
     rp = road_points(cloud, abc, threshold, colour_threshold, disparity.shape[:2], camera)
     return {"filled": filled, "cloud": cloud, "mcloud": mcloud, "indices": indices, "best": best,
             "abc": abc, "errors": errs, "road": rp}

@@ -140,6 +140,7 @@ struct ProjGeom {
     int cpr;            // 16-pixel chunks per row
     int rpb;            // lattice rows per block
     int groups;         // row groups (blocks) per frame
+    int cap;            // most sites one block can emit
     int vec_ok;         // W % 16 == 0 and all bases 16-byte aligned
 };
 
@@ -154,6 +155,7 @@ static ProjGeom make_geom(int H, int W, int step, bool aligned) {
     g.rpb = PROJ_THREADS / g.cpr;
     if (g.rpb < 1) g.rpb = 1;
     g.groups = (g.LH + g.rpb - 1) / g.rpb;
+    g.cap = g.rpb * g.cpr * ((CHUNK + step - 1) / step);
     g.vec_ok = (W % CHUNK == 0) && aligned;
     return g;
 }
@@ -317,7 +319,7 @@ proj_write_kernel(const uint8_t *__restrict__ disp, const uint8_t *__restrict__ 
                   int64_t plane_stride, uint64_t *__restrict__ cloud, uint32_t *__restrict__ mcloud) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ uint32_t warp_tot[PROJ_THREADS / 32];
-    const int cap = g.rpb * g.cpr * CHUNK;                       // sites a block can hold
+    const int cap = g.cap;                                       // sites a block can hold
     uint64_t *s_cloud = (uint64_t *)smem_raw;                    // [cap]
     uint32_t *s_m = (uint32_t *)(smem_raw + (size_t)cap * 8);    // [cap]
 
@@ -430,11 +432,11 @@ extern "C" int svb_project_compact(const uint8_t *disp, const uint8_t *carmask, 
     proj_scan_kernel<<<F, 256, 0, st>>>(gc, g.groups, counts);
     SVB_LAUNCH_CHECK();
     if (!cloud && !mcloud) return SVB_OK;
-    size_t smem = (size_t)g.rpb * g.cpr * CHUNK * 12;
+    size_t smem = (size_t)g.cap * 12;
     int64_t plane = (int64_t)F * g.groups;
 #define LAUNCH_W(M, R)                                                                              \
     do {                                                                                            \
-        if (smem > 48 * 1024)                                                                       \
+        if (smem + 256 > 48 * 1024)                                                                 \
             cudaFuncSetAttribute(proj_write_kernel<M, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
         proj_write_kernel<M, R><<<grid, PROJ_THREADS, smem, st>>>(disp, carmask, bgr, g, gc, plane, cloud, mcloud); \
     } while (0)

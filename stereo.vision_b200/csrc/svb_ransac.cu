@@ -72,6 +72,14 @@ __device__ __forceinline__ bool exactly_collinear(const P3 &a, const P3 &b, cons
     double cz = __dsub_rn(__dmul_rn(ux, vy), __dmul_rn(uy, vx));
     return cx == 0.0 && cy == 0.0 && cz == 0.0;
 }
+// Pixels collinear in the image <=> the plane through the three points contains the camera centre
+// <=> [P1;P2;P3] is rank 2 in exact arithmetic.  The reference then gets LAPACK rounding noise
+// (LinAlgError for about half of such triples, |abc| ~ 1e14 for the rest, machine dependent); the
+// product treats every such triple as the singular case (trial skipped, functions.py:294-296).
+__device__ __forceinline__ bool image_collinear(uint32_t r1, uint32_t r2, uint32_t r3) {
+    int x1 = rec_x(r1), y1 = rec_y(r1);
+    return (rec_x(r2) - x1) * (rec_y(r3) - y1) - (rec_x(r3) - x1) * (rec_y(r2) - y1) == 0;
+}
 // abc = inv([P1;P2;P3]) . (1,1,1)^T = (P2xP3 + P3xP1 + P1xP2) / det      functions.py:267
 __device__ __forceinline__ bool plane_of(const P3 &p1, const P3 &p2, const P3 &p3, double &a, double &b, double &c) {
     double c23x = p2.y * p3.z - p2.z * p3.y, c23y = p2.z * p3.x - p2.x * p3.z, c23z = p2.x * p3.y - p2.y * p3.x;
@@ -93,22 +101,26 @@ __device__ __forceinline__ bool trial_triple(const uint32_t *__restrict__ rec, i
     if (triple) {
         int i1 = triple[0], i2 = triple[1], i3 = triple[2];
         if (i1 < 0 || i2 < 0 || i3 < 0 || (uint32_t)i1 >= M || (uint32_t)i2 >= M || (uint32_t)i3 >= M) return false;
-        p1 = expand_point(cam, __ldg(rec + (int64_t)i1 * stride));
-        p2 = expand_point(cam, __ldg(rec + (int64_t)i2 * stride));
-        p3 = expand_point(cam, __ldg(rec + (int64_t)i3 * stride));
+        uint32_t r1 = __ldg(rec + (int64_t)i1 * stride), r2 = __ldg(rec + (int64_t)i2 * stride),
+                 r3 = __ldg(rec + (int64_t)i3 * stride);
+        p1 = expand_point(cam, r1);
+        p2 = expand_point(cam, r2);
+        p3 = expand_point(cam, r3);
         idx_out[0] = i1; idx_out[1] = i2; idx_out[2] = i3;
-        return true;
+        return !image_collinear(r1, r2, r3);
     }
     for (int round = 0; round < MAX_TRIPLE_ROUNDS; ++round) {
         uint32_t i1 = uniform_draw(key, 3u * round + 0u, M);
         uint32_t i2 = uniform_draw(key, 3u * round + 1u, M);
         uint32_t i3 = uniform_draw(key, 3u * round + 2u, M);
-        p1 = expand_point(cam, __ldg(rec + (int64_t)i1 * stride));
-        p2 = expand_point(cam, __ldg(rec + (int64_t)i2 * stride));
-        p3 = expand_point(cam, __ldg(rec + (int64_t)i3 * stride));
+        uint32_t r1 = __ldg(rec + (int64_t)i1 * stride), r2 = __ldg(rec + (int64_t)i2 * stride),
+                 r3 = __ldg(rec + (int64_t)i3 * stride);
+        p1 = expand_point(cam, r1);
+        p2 = expand_point(cam, r2);
+        p3 = expand_point(cam, r3);
         if (!exactly_collinear(p1, p2, p3)) {
             idx_out[0] = (int)i1; idx_out[1] = (int)i2; idx_out[2] = (int)i3;
-            return true;
+            return !image_collinear(r1, r2, r3);
         }
     }
     return false;
@@ -244,7 +256,8 @@ __global__ void ransac_dump_kernel(const uint32_t *__restrict__ mcloud, int stri
     P3 p1, p2, p3;
     int tri[3] = {-1, -1, -1};
     bool ok = trial_triple(rec, stride, M, cam, nullptr, key, p1, p2, p3, tri);
-    if (lane < 3) trip[lane] = ok ? tri[lane] : -1;
+    (void)ok;                                                    // image-collinear triples are dumped too
+    if (lane < 3) trip[lane] = tri[lane];
 }
 
 extern "C" int svb_ransac_dump_indices(const uint32_t *mcloud, int rec_stride_words, int64_t slab_stride_records,
