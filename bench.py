@@ -1,0 +1,391 @@
+#!/usr/bin/env python
+"""Benchmark of the hot path (project + RANSAC + road points) on synthetic 1024x544 sequences.
+
+    python bench.py --gpus N --steps K --warmup W            # this repo's arm (B200 kernels)
+    python bench.py --impl reference --gpus N --steps K ...  # CPU arm: the oracle port on host cores
+
+A "step" is one pass of the path over one resident sequence of --frames frames (BASELINE config 2:
+300 chained frames, previous-disparity fill, step 2, 600 trials x 400 samples).  `value` is frames/s
+with the inputs already in HBM (they are 668 MB per sequence, larger than the 126 MB L2, so every
+step streams them from DRAM again); `e2e` is the same metric through RoadPath.process with pinned
+HOST buffers, host->device copies of the frames and device->host reads of masks/planes/counts inside
+the timed region.  One rank per GPU, one independent sequence per rank, no hot-path collective.
+Prints ONE JSON line on rank 0.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+H, W = 544, 1024
+METRIC = "frames/sec @1024x544 (project+RANSAC+road pts)"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--frames", type=int, default=300)
+    ap.add_argument("--trials", type=int, default=600)
+    ap.add_argument("--samples", type=int, default=400)
+    ap.add_argument("--step", type=int, default=2)
+    ap.add_argument("--chunk", type=int, default=60, help="frames per host->device chunk in the e2e leg")
+    ap.add_argument("--cpu-frames", type=int, default=0, help="frames of the CPU baseline sample (0 = auto)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------ synthetic input
+def _gen_one(args):
+    import stereo.vision_b200.synth as synth
+    seq, t = args
+    return synth.make_frame(seq, t, (H, W))
+
+
+def make_sequence_parallel(seq, n_frames, workers):
+    """disp [F,H,W], bgr [F,H,W,3] of sequence `seq`, generated on `workers` processes."""
+    import multiprocessing as mp
+    disp = np.empty((n_frames, H, W), np.uint8)
+    bgr = np.empty((n_frames, H, W, 3), np.uint8)
+    if workers <= 1:
+        for t in range(n_frames):
+            disp[t], bgr[t] = _gen_one((seq, t))
+        return disp, bgr
+    with mp.get_context("fork").Pool(workers) as pool:
+        for t, (d, c) in enumerate(pool.imap(_gen_one, [(seq, t) for t in range(n_frames)], chunksize=4)):
+            disp[t], bgr[t] = d, c
+    return disp, bgr
+
+
+# ------------------------------------------------------------------ CPU arm: the oracle port
+def _oracle_chain(job):
+    """Run `n` chained frames of sequence `seq` through the numpy oracle; returns seconds spent."""
+    seq, n, trials, samples, step = job
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import np_oracle as no
+    import stereo.vision_b200.synth as synth
+    from stereo.vision_b200.masks import default_carmask
+    cm = default_carmask((H, W), prefer_cwd=False)
+    frames = [synth.make_frame(seq, t, (H, W)) for t in range(n)]
+    prev = None
+    t0 = time.perf_counter()
+    for t, (d, c) in enumerate(frames):
+        o = no.run_frame(d, c, prev, cm, seed=synth.ransac_seed(seq, t), trials=trials, n_samples=samples, step=step)
+        prev = o["filled"]
+    return time.perf_counter() - t0
+
+
+def cpu_oracle_throughput(frames_per_proc, procs, trials, samples, step):
+    """frames/s of the oracle port with one independent sequence per process."""
+    import multiprocessing as mp
+    jobs = [(1000 + p, frames_per_proc, trials, samples, step) for p in range(procs)]
+    if procs == 1:
+        times = [_oracle_chain(jobs[0])]
+    else:
+        with mp.get_context("fork").Pool(procs) as pool:
+            times = pool.map(_oracle_chain, jobs)
+    # every worker times only its oracle calls (frame synthesis excluded); the job ends with the slowest
+    wall = max(times)
+    return frames_per_proc * procs / wall, wall
+
+
+# ------------------------------------------------------------------ clocks during the timed region
+class ClockSampler:
+    def __init__(self, index):
+        self.index, self.samples, self.reasons, self._stop, self._thr = index, [], set(), threading.Event(), None
+        self.max_mhz = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _run(self):
+        nv = self.nv
+        names = {"hw_slowdown": 0x8, "sw_power_cap": 0x4, "hw_thermal_slowdown": 0x40,
+                 "sw_thermal_slowdown": 0x20, "hw_power_brake_slowdown": 0x80}
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h) if hasattr(nv, "nvmlDeviceGetCurrentClocksEventReasons") \
+                    else nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for k, bit in names.items():
+                    if r & bit:
+                        self.reasons.add(k)
+            except Exception:
+                pass
+            self._stop.wait(0.02)
+
+    def __enter__(self):
+        if self.nv:
+            self._thr = threading.Thread(target=self._run, daemon=True)
+            self._thr.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        if self._thr:
+            self._thr.join()
+
+    def summary(self):
+        return {"sm_mhz": float(np.median(self.samples)) if self.samples else None,
+                "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+# ------------------------------------------------------------------ this repo's arm
+def algorithmic_bytes(kernel, L, N, M, K, R, T, S):
+    """Algorithmic bytes per FRAME of each kernel (DESIGN.md "Kernels"; SURVEY 8d restated for the
+    8-byte cloud / 4-byte mcloud records).  N, M, K, R are per-frame means."""
+    table = {
+        "fill_seq": 2.0 * H * W,                              # raw in + filled out (prev lives in registers)
+        "proj_count": 2.0 * L,                                # d + carmask at lattice sites
+        "proj_write": 2.0 * L + 3.0 * N + 8.0 * N + 4.0 * M,  # d, carmask, rgb in; cloud + mcloud out
+        "ransac_score": 4.0 * T * (S + 3) + 8.0 * T,          # gathered records (L2) + errors out
+        "road_pass1": 8.0 * N + N / 8.0,                      # records in, near bits out
+        "road_pass2": N / 8.0 + 8.0 * K + 1.0 * R,            # near bits, near records in, mask bytes out
+        "road_clear": 1.0 * H * W,                            # mask clear (memset node)
+    }
+    return table.get(kernel)
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    import stereo.vision_b200._native as N
+    from stereo.vision_b200.pipeline import RoadPath, KERNELS_PER_BATCH
+    from stereo.vision_b200.masks import default_carmask
+
+    F, T, S = args.frames, args.trials, args.samples
+    ncpu = os.cpu_count() or 1
+    disp_h, bgr_h = make_sequence_parallel(rank, F, max(1, min(16, ncpu // max(1, world))))
+    disp_p = torch.from_numpy(disp_h).pin_memory()
+    bgr_p = torch.from_numpy(bgr_h).pin_memory()
+    cm = default_carmask((H, W), prefer_cwd=False)
+    eng = RoadPath((H, W), step=args.step, trials=T, samples=S, carmask=cm, max_frames=F, device=dev)
+    disp_d, bgr_d = disp_p.to(dev), bgr_p.to(dev)
+    seed = 20260000 + rank
+
+    def step():
+        return eng.process(disp_d, bgr_d, prev=None, seed=seed, frame0=0)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    barrier()
+    N.launches = 0
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local) as clk:
+        barrier()
+        e0.record()
+        for _ in range(args.steps):
+            res = step()
+        e1.record()
+        barrier()
+    ms = e0.elapsed_time(e1)
+    launches = N.launches
+    counts = res.counts.cpu().numpy().astype(np.float64)
+    ref_counts = counts.copy()
+    planes_valid = float(res.planes[:, 7].sum().item())
+
+    # ---- per-kernel device times (3 extra steps with event tracing on) -> roofline of the dominant kernel
+    N.profile_enable(True)
+    for _ in range(3):
+        step()
+    torch.cuda.synchronize()
+    prof = N.profile_read()
+    N.profile_enable(False)
+    Nm, Mm, Km, Rm = counts.mean(axis=0)
+    kern = {k: {"ms_per_launch": v[0] / v[1], "launches": v[1]} for k, v in prof.items()}
+    tot = sum(v["ms_per_launch"] for v in kern.values())
+    for k, v in kern.items():
+        v["share"] = v["ms_per_launch"] / tot
+        ab = algorithmic_bytes(k, eng.L, Nm, Mm, Km, Rm, T, S)
+        if ab is not None:
+            v["alg_bytes"] = ab * F
+            v["gbs"] = ab * F / (v["ms_per_launch"] * 1e-3) / 1e9
+
+    # ---- end to end: pinned host frames in, masks / planes / counts out, chunked + double buffered
+    e2e = None
+    if not args.no_e2e:
+        e2e = run_e2e(args, torch, dev, eng.camera, cm, disp_p, bgr_p, seed, ref_counts)
+
+    # ---- max over ranks
+    t = torch.tensor([ms, e2e["ms"] if e2e else 0.0], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_max, e2e_ms_max = t.tolist()
+    out = None
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        peak, peak_src = (peaks["hbm_gbs"], "measured (MEASURED_PEAKS.json hbm_gbs)") if "hbm_gbs" in peaks \
+            else (6650.0, "fallback (B200_PROFILING.md)")
+        hbm_kernels = {k: v for k, v in kern.items() if "gbs" in v and k not in ("ransac_score", "road_clear")}
+        dom = max(hbm_kernels, key=lambda k: hbm_kernels[k]["ms_per_launch"])
+        top = max(kern, key=lambda k: kern[k]["ms_per_launch"])
+        d = kern[dom]
+        out = {
+            "metric": METRIC, "value": F * args.steps * world / (ms_max * 1e-3), "unit": "frames/s",
+            "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u8 in / f64 plane + reprojection arithmetic", "data": "synthetic",
+            "config": {"workload": "config 2: %d-frame sequence per GPU, 1024x544, previous-disparity fill, step %d, "
+                                   "%d RANSAC trials x %d samples, counter-based on-device draws" % (F, args.step, T, S),
+                       "frames_per_step_per_gpu": F, "l2": "inputs (%.0f MB/sequence) exceed the 126 MB L2; no flush needed"
+                                                          % ((disp_h.nbytes + bgr_h.nbytes) / 1e6),
+                       "parallelism": "one independent sequence per GPU, no hot-path collective",
+                       "mean_points": {"N": Nm, "M": Mm, "K": Km, "R": Rm}, "frames_with_plane": planes_valid},
+            "gpu_launches": launches,
+            "clocks": clk.summary(),
+            "roofline": {"kernel": dom, "bound": "hbm", "achieved": d["gbs"], "peak": peak, "unit": "GB/s",
+                         "frac": d["gbs"] / peak, "traffic": None, "peak_source": peak_src,
+                         "alg_bytes_per_launch": d["alg_bytes"], "ms_per_launch": d["ms_per_launch"],
+                         "share_of_step": d["share"], "longest_kernel": top},
+            "kernels": {k: {kk: (round(vv, 6) if isinstance(vv, float) else vv) for kk, vv in v.items()} for k, v in kern.items()},
+        }
+        if e2e:
+            out["e2e"] = {"value": F * world / (e2e_ms_max * 1e-3), "unit": "frames/s",
+                          "h2d_bytes_per_step": e2e["h2d"], "d2h_bytes_per_step": e2e["d2h"],
+                          "ms_per_step": e2e_ms_max, "chunk_frames": args.chunk, "matches_resident_run": e2e["match"]}
+        if world == 1 and not args.no_cpu_baseline:
+            procs = ncpu
+            fpp = args.cpu_frames or 4
+            v, wall = cpu_oracle_throughput(fpp, procs, T, S, args.step)
+            out["cpu_baseline"] = {"value": v, "unit": "frames/s", "cores": procs, "kind": "port",
+                                   "sample": "%d independent sequences x %d chained frames through oracle/np_oracle.py "
+                                             "(numpy float64 restatement), one process per core, %.1f s wall" % (procs, fpp, wall)}
+        print(json.dumps(out))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return out
+
+
+def run_e2e(args, torch, dev, camera, cm, disp_p, bgr_p, seed, ref_counts):
+    """One sequence through RoadPath.process from pinned HOST buffers: per chunk, H2D copy of the
+    frames (copy stream), the path (compute stream), D2H of road masks + planes + counts (output
+    stream) into pinned host memory; two engines/buffers alternate so copies overlap compute."""
+    from stereo.vision_b200.pipeline import RoadPath
+    F, C = args.frames, min(args.chunk, args.frames)
+    engs = [RoadPath((H, W), step=args.step, trials=args.trials, samples=args.samples, carmask=cm, max_frames=C,
+                     device=dev, camera=camera) for _ in range(2)]
+    din = [torch.empty((C, H, W), dtype=torch.uint8, device=dev) for _ in range(2)]
+    cin = [torch.empty((C, H, W, 3), dtype=torch.uint8, device=dev) for _ in range(2)]
+    mask_o = torch.empty((F, H, W), dtype=torch.uint8).pin_memory()
+    plane_o = torch.empty((F, 8), dtype=torch.float64).pin_memory()
+    count_o = torch.empty((F, 4), dtype=torch.int32).pin_memory()
+    s_in, s_cmp, s_out = torch.cuda.Stream(dev), torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+    chunks = [(a, min(F, a + C)) for a in range(0, F, C)]
+
+    def one_pass():
+        ev_in, ev_cmp, ev_out = {}, {}, {}
+        for i, (a, b) in enumerate(chunks):
+            k, n = i % 2, b - a
+            with torch.cuda.stream(s_in):
+                if i >= 2:
+                    s_in.wait_event(ev_cmp[i - 2])            # buffer k is free once chunk i-2 was computed
+                din[k][:n].copy_(disp_p[a:b], non_blocking=True)
+                cin[k][:n].copy_(bgr_p[a:b], non_blocking=True)
+                ev_in[i] = torch.cuda.Event()
+                ev_in[i].record(s_in)
+            with torch.cuda.stream(s_cmp):
+                s_cmp.wait_event(ev_in[i])
+                if i >= 2:
+                    s_cmp.wait_event(ev_out[i - 2])           # engine k's outputs were read back
+                prev = engs[1 - k].filled[chunks[i - 1][1] - chunks[i - 1][0] - 1] if i else None
+                r = engs[k].process(din[k][:n], cin[k][:n], prev=prev, seed=seed, frame0=a)
+                ev_cmp[i] = torch.cuda.Event()
+                ev_cmp[i].record(s_cmp)
+            with torch.cuda.stream(s_out):
+                s_out.wait_event(ev_cmp[i])
+                mask_o[a:b].copy_(r.road_mask, non_blocking=True)
+                plane_o[a:b].copy_(r.planes, non_blocking=True)
+                count_o[a:b].copy_(r.counts, non_blocking=True)
+                ev_out[i] = torch.cuda.Event()
+                ev_out[i].record(s_out)
+
+    for _ in range(2):
+        one_pass()
+    torch.cuda.synchronize()
+    steps = max(3, min(args.steps, 10))
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(s_in)
+    for _ in range(steps):
+        one_pass()
+    s_out.wait_stream(s_cmp)
+    e1.record(s_out)
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    match = bool(np.array_equal(count_o.numpy().astype(np.float64), ref_counts))
+    h2d = int(disp_p.nbytes + bgr_p.nbytes)
+    d2h = int(mask_o.nbytes + plane_o.nbytes + count_o.nbytes)
+    return {"ms": ms, "h2d": h2d, "d2h": d2h, "match": match}
+
+
+# ------------------------------------------------------------------ reference arm (CPU)
+def run_reference(args):
+    """The reference's CPU path for the same workload.  /root/reference (pure Python, no build) does
+    not exist on the GPU box, so this arm times the oracle port (oracle/np_oracle.py), one
+    independent sequence per host core; each step is a bounded sample of the 300-frame workload."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    procs = os.cpu_count() or 1
+    fpp = args.cpu_frames or 2
+    T, S = args.trials, args.samples
+    for _ in range(min(args.warmup, 1)):
+        cpu_oracle_throughput(1, procs, T, S, args.step)
+    vals, walls = [], []
+    for _ in range(args.steps):
+        v, wall = cpu_oracle_throughput(fpp, procs, T, S, args.step)
+        vals.append(v)
+        walls.append(wall)
+    v = float(np.mean(vals))
+    sample = ("each step = %d independent sequences x %d chained frames (of the %d-frame workload) through "
+              "oracle/np_oracle.py, one process per core" % (procs, fpp, args.frames))
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
+        "warmup": min(args.warmup, 1), "ms_per_step": 1e3 * float(np.mean(walls)), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f64 (numpy)", "data": "synthetic",
+        "config": {"workload": "config 2: %d-frame sequence, 1024x544, previous-disparity fill, step %d, %d RANSAC "
+                               "trials x %d samples (bounded sample per step)" % (args.frames, args.step, T, S)},
+        "cpu_baseline": {"value": v, "unit": "frames/s", "cores": procs, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+if __name__ == "__main__":
+    a = parse_args()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_b200(a)

@@ -184,6 +184,15 @@ int svb_road_points(const uint64_t *cloud, const int32_t *counts, const double *
                     uint32_t *hist, uint8_t *road_mask, uint8_t *overlay, int32_t *counts_out,
                     void *scratch, int64_t scratch_bytes, void *stream);
 
+/* ---- tracing: per-kernel CUDA-event timing, off by default.
+ * svb_profile_enable(1) clears the records and brackets every later kernel launch of this library
+ * with two events on its stream; after the caller has synchronised, svb_profile_get(id, ..) returns
+ * the kernel's name, the summed device time in ms and the number of launches, id in
+ * [0, svb_profile_kernels()).  Process-global; not for concurrent use from several threads. */
+int svb_profile_enable(int on);
+int svb_profile_kernels(void);
+int svb_profile_get(int id, char *name, int name_cap, double *ms_total, int *launches);
+
 #ifdef __cplusplus
 }
 #endif

@@ -66,6 +66,9 @@ SIGNATURES = {
     "svb_scatter_points": (I, [P, I, P, I, I, I, P, P, P]),
     "svb_road_scratch_bytes": (L, [I, I, I, I]),
     "svb_road_points": (I, [P, P, P, I, I, I, I, CAMP, U32, P, P, P, P, P, L, P]),
+    "svb_profile_enable": (I, [I]),
+    "svb_profile_kernels": (I, []),
+    "svb_profile_get": (I, [I, C.c_char_p, I, C.POINTER(D), C.POINTER(I)]),
 }
 
 _lib = None
@@ -130,3 +133,20 @@ launches = 0
 def count(n: int):
     global launches
     launches += n
+
+
+def profile_enable(on: bool):
+    check(load().svb_profile_enable(1 if on else 0), "svb_profile_enable")
+
+
+def profile_read():
+    """{kernel name: (total ms, launches)} since profile_enable(True); caller must have synchronised."""
+    lib = load()
+    out = {}
+    for i in range(lib.svb_profile_kernels()):
+        name = C.create_string_buffer(64)
+        ms, n = D(0.0), I(0)
+        check(lib.svb_profile_get(i, name, 64, C.byref(ms), C.byref(n)), "svb_profile_get")
+        if n.value:
+            out[name.value.decode()] = (ms.value, n.value)
+    return out

@@ -16,7 +16,7 @@ def needs_build() -> bool:
     if not os.path.isfile(OUT):
         return True
     t = os.path.getmtime(OUT)
-    deps = [os.path.join(HERE, s) for s in SOURCES] + [os.path.join(HERE, "svb_common.cuh"),
+    deps = [os.path.join(HERE, s) for s in SOURCES] + [os.path.join(HERE, "svb_common.cuh"), os.path.join(HERE, "svb_prof.cuh"),
             os.path.join(os.path.dirname(PKG), "include", "svb200.h")]
     return any(os.path.getmtime(d) > t for d in deps)
 

@@ -15,3 +15,55 @@ extern "C" const char *svb_error_string(int code) {
     if (code > 0) return cudaGetErrorString((cudaError_t)code);
     return "unknown error";
 }
+
+// ------------------------------------------------------------------ per-kernel event tracing
+#include "svb_prof.cuh"
+#include <vector>
+#include <string.h>
+
+bool g_svb_prof_on = false;
+static const char *k_names[K_COUNT_] = {
+    "fill_seq", "mask_disp", "proj_count", "proj_scan", "proj_write", "cloud_export", "ransac_score",
+    "ransac_dump", "ransac_finalize", "point_errors", "compact_cloud", "hue_hist", "hue_bins", "reproject",
+    "scatter_points", "road_pass1", "road_pass2", "road_clear"};
+struct EvPair { int id; cudaEvent_t a, b; };
+static std::vector<EvPair> g_events;
+static cudaEvent_t g_pending[K_COUNT_];
+
+void svb_prof_begin(int id, cudaStream_t st) {
+    cudaEvent_t e;
+    if (cudaEventCreate(&e) != cudaSuccess) return;
+    cudaEventRecord(e, st);
+    g_pending[id] = e;
+}
+void svb_prof_end(int id, cudaStream_t st) {
+    cudaEvent_t e;
+    if (!g_pending[id] || cudaEventCreate(&e) != cudaSuccess) return;
+    cudaEventRecord(e, st);
+    g_events.push_back({id, g_pending[id], e});
+    g_pending[id] = nullptr;
+}
+
+extern "C" int svb_profile_enable(int on) {
+    for (auto &p : g_events) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
+    g_events.clear();
+    memset(g_pending, 0, sizeof(g_pending));
+    g_svb_prof_on = on != 0;
+    return SVB_OK;
+}
+extern "C" int svb_profile_kernels(void) { return K_COUNT_; }
+extern "C" int svb_profile_get(int id, char *name, int name_cap, double *ms_total, int *launches) {
+    if (id < 0 || id >= K_COUNT_ || !name || !ms_total || !launches) return SVB_E_ARG;
+    strncpy(name, k_names[id], name_cap > 0 ? name_cap - 1 : 0);
+    if (name_cap > 0) name[name_cap - 1] = 0;
+    double tot = 0; int n = 0;
+    for (auto &p : g_events) {
+        if (p.id != id) continue;
+        float ms = 0;
+        cudaError_t e = cudaEventElapsedTime(&ms, p.a, p.b);
+        if (e != cudaSuccess) return (int)e;
+        tot += ms; ++n;
+    }
+    *ms_total = tot; *launches = n;
+    return SVB_OK;
+}

@@ -1,0 +1,21 @@
+// Per-kernel CUDA-event tracing (off by default).  When enabled through svb_profile_enable(1) every
+// kernel launch of the library is bracketed by two events on the launching stream; svb_profile_get
+// sums the elapsed times per kernel name.  bench.py uses it for the live roofline numbers.
+#pragma once
+#include <cuda_runtime.h>
+
+enum SvbKernelId {
+    K_FILL = 0, K_MASK, K_PROJ_COUNT, K_PROJ_SCAN, K_PROJ_WRITE, K_EXPORT, K_RANSAC_SCORE, K_RANSAC_DUMP,
+    K_RANSAC_FINAL, K_POINT_ERR, K_COMPACT, K_HUE_HIST, K_HUE_BINS, K_REPROJECT, K_SCATTER, K_ROAD_PASS1,
+    K_ROAD_PASS2, K_ROAD_CLEAR, K_COUNT_
+};
+
+void svb_prof_begin(int id, cudaStream_t st);
+void svb_prof_end(int id, cudaStream_t st);
+extern bool g_svb_prof_on;
+
+struct ProfScope {
+    int id; cudaStream_t st; bool on;
+    ProfScope(int id_, cudaStream_t st_) : id(id_), st(st_), on(g_svb_prof_on) { if (on) svb_prof_begin(id, st); }
+    ~ProfScope() { if (on) svb_prof_end(id, st); }
+};

@@ -10,6 +10,7 @@
 // and 4-byte (mcloud) stores; the hue bin is computed in that copy-out loop, where consecutive
 // lanes hold consecutive *valid* points and no lane idles on a hole.
 #include "svb_common.cuh"
+#include "svb_prof.cuh"
 
 #define PROJ_THREADS 256
 #define CHUNK 16
@@ -79,6 +80,7 @@ extern "C" int svb_fill_sequence(const uint8_t *raw, const uint8_t *prev0, uint8
     cudaStream_t st = (cudaStream_t)stream;
     int64_t pixels = (int64_t)H * W;
     bool aligned = (pixels % 16 == 0) && (((uintptr_t)raw | (uintptr_t)filled | (uintptr_t)prev0) % 16 == 0);
+    ProfScope ps(K_FILL, st);
     if (aligned) {
         int64_t chunks = pixels / 16;
         int threads = 128;
@@ -122,6 +124,7 @@ extern "C" int svb_mask_disparity(const uint8_t *d, const uint8_t *carmask, uint
     cudaStream_t st = (cudaStream_t)stream;
     int64_t pixels = (int64_t)H * W;
     bool aligned = (pixels % 16 == 0) && (((uintptr_t)d | (uintptr_t)carmask | (uintptr_t)out) % 16 == 0);
+    ProfScope ps(K_MASK, st);
     if (aligned) {
         int64_t chunks = pixels / 16, total = chunks * F;
         mask_disp_v16<<<(unsigned)((total + 255) / 256), 256, 0, st>>>((const uint4 *)d, (const uint4 *)carmask,
@@ -426,10 +429,16 @@ extern "C" int svb_project_compact(const uint8_t *disp, const uint8_t *carmask, 
     if (g.cpr > PROJ_THREADS) return SVB_E_SHAPE;
     uint32_t *gc = (uint32_t *)scratch;
     dim3 grid(g.groups, F);
-    if (carmask) proj_count_kernel<true><<<grid, PROJ_THREADS, 0, st>>>(disp, carmask, g, gc);
-    else         proj_count_kernel<false><<<grid, PROJ_THREADS, 0, st>>>(disp, carmask, g, gc);
+    {
+        ProfScope ps(K_PROJ_COUNT, st);
+        if (carmask) proj_count_kernel<true><<<grid, PROJ_THREADS, 0, st>>>(disp, carmask, g, gc);
+        else         proj_count_kernel<false><<<grid, PROJ_THREADS, 0, st>>>(disp, carmask, g, gc);
+    }
     SVB_LAUNCH_CHECK();
-    proj_scan_kernel<<<F, 256, 0, st>>>(gc, g.groups, counts);
+    {
+        ProfScope ps(K_PROJ_SCAN, st);
+        proj_scan_kernel<<<F, 256, 0, st>>>(gc, g.groups, counts);
+    }
     SVB_LAUNCH_CHECK();
     if (!cloud && !mcloud) return SVB_OK;
     size_t smem = (size_t)g.cap * 12;
@@ -440,8 +449,11 @@ extern "C" int svb_project_compact(const uint8_t *disp, const uint8_t *carmask, 
             cudaFuncSetAttribute(proj_write_kernel<M, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
         proj_write_kernel<M, R><<<grid, PROJ_THREADS, smem, st>>>(disp, carmask, bgr, g, gc, plane, cloud, mcloud); \
     } while (0)
-    if (carmask) { if (bgr) LAUNCH_W(true, true); else LAUNCH_W(true, false); }
-    else         { if (bgr) LAUNCH_W(false, true); else LAUNCH_W(false, false); }
+    {
+        ProfScope ps(K_PROJ_WRITE, st);
+        if (carmask) { if (bgr) LAUNCH_W(true, true); else LAUNCH_W(true, false); }
+        else         { if (bgr) LAUNCH_W(false, true); else LAUNCH_W(false, false); }
+    }
 #undef LAUNCH_W
     SVB_LAUNCH_CHECK();
     return SVB_OK;
@@ -479,6 +491,7 @@ extern "C" int svb_cloud_export(const uint32_t *records, int rec_stride_words, i
     if (n == 0) return SVB_OK;
     if (!records || !cam) return SVB_E_NULL;
     if (n < 0 || (rec_stride_words != 1 && rec_stride_words != 2)) return SVB_E_ARG;
+    ProfScope ps(K_EXPORT, (cudaStream_t)stream);
     cloud_export_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(records, rec_stride_words, n, make_camd(cam),
                                                                             xyz, xyz_f32, rgb, sites, d, hue);
     SVB_LAUNCH_CHECK();

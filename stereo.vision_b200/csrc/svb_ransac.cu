@@ -11,6 +11,7 @@
 // expression by ~1e-16 relative, far below the gap between two hypotheses' mean errors, and only
 // the arg-min (not the error value) is an observable.
 #include "svb_common.cuh"
+#include "svb_prof.cuh"
 #include <math.h>
 
 #define RANSAC_WARPS 8
@@ -219,6 +220,7 @@ extern "C" int svb_ransac_score(const uint32_t *mcloud, int rec_stride_words, in
     dim3 grid((T + RANSAC_WARPS - 1) / RANSAC_WARPS, F);
     cudaStream_t st = (cudaStream_t)stream;
     CamD c = make_camd(cam);
+    ProfScope ps(K_RANSAC_SCORE, st);
     if (sample_idx)
         ransac_score_kernel<true><<<grid, RANSAC_THREADS, 0, st>>>(mcloud, rec_stride_words, slab_stride_records, counts,
                                                                    counts_stride, counts_col, T, S, c, sample_idx,
@@ -270,6 +272,7 @@ extern "C" int svb_ransac_dump_indices(const uint32_t *mcloud, int rec_stride_wo
     if ((rec_stride_words != 1 && rec_stride_words != 2) || counts_stride < 1 || counts_col < 0 ||
         counts_col >= counts_stride) return SVB_E_ARG;
     dim3 grid((T + RANSAC_WARPS - 1) / RANSAC_WARPS, F);
+    ProfScope ps(K_RANSAC_DUMP, (cudaStream_t)stream);
     ransac_dump_kernel<<<grid, RANSAC_THREADS, 0, (cudaStream_t)stream>>>(mcloud, rec_stride_words, slab_stride_records,
                                                                           counts, counts_stride, counts_col, T, S,
                                                                           make_camd(cam), rng_seed, frame0,
@@ -376,6 +379,7 @@ extern "C" int svb_ransac_finalize(const uint32_t *mcloud, int rec_stride_words,
     if (F < 1 || T < 1 || S < 1) return SVB_E_SHAPE;
     if ((rec_stride_words != 1 && rec_stride_words != 2) || counts_stride < 1 || counts_col < 0 ||
         counts_col >= counts_stride) return SVB_E_ARG;
+    ProfScope ps(K_RANSAC_FINAL, (cudaStream_t)stream);
     ransac_finalize_kernel<<<F, 128, 0, (cudaStream_t)stream>>>(mcloud, rec_stride_words, slab_stride_records, counts,
                                                                counts_stride, counts_col, T, S, make_camd(cam),
                                                                triple_idx, rng_seed, frame0, errors, point_threshold, planes);

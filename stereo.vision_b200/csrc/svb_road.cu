@@ -10,6 +10,7 @@
 // records again, looks the bit and the bin count up, reprojects the survivors with the reference's
 // float64 expression and stores 255 into the mask (idempotent byte stores, no atomics).
 #include "svb_common.cuh"
+#include "svb_prof.cuh"
 #include <math.h>
 
 #define ROAD_THREADS 256
@@ -35,6 +36,7 @@ extern "C" int svb_point_errors(const uint32_t *records, int rec_stride_words, i
     if (n < 0 || (rec_stride_words != 1 && rec_stride_words != 2)) return SVB_E_ARG;
     double row[SVB_PLANE_STRIDE];
     svb_plane_from_abc(h_abc, 0.0, row);
+    ProfScope ps(K_POINT_ERR, (cudaStream_t)stream);
     point_errors_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(records, rec_stride_words, n, make_camd(cam),
                                                                             row[0], row[1], row[2], row[3], dist);
     SVB_LAUNCH_CHECK();
@@ -140,6 +142,7 @@ extern "C" int svb_compact_cloud(const uint64_t *cloud, int n, int mode, const d
     double t = threshold;
     uint32_t uthr = t < 0 ? 0u : (t >= 4294967295.0 ? 0xFFFFFFFFu : (uint32_t)floor(t));
     if (mode == 1 && t < 0) uthr = 0;                            // count > negative: always true (count >= 1 ... or 0 > t)
+    ProfScope ps(K_COMPACT, st);
     compact_count_kernel<<<nb, 256, 0, st>>>(cloud, n, mode, dist, hist, threshold, uthr, bc);
     SVB_LAUNCH_CHECK();
     compact_scan_kernel<<<1, 256, 0, st>>>(bc, nb, out_count);
@@ -174,6 +177,7 @@ extern "C" int svb_hue_histogram(const uint64_t *cloud, int n, uint32_t *hist, v
     if (n < 0) return SVB_E_ARG;
     int blocks = (n + 256 * 16 - 1) / (256 * 16);
     if (blocks > 148 * 8) blocks = 148 * 8;
+    ProfScope ps(K_HUE_HIST, st);
     hue_hist_kernel<<<blocks, 256, 0, st>>>(cloud, n, hist);
     SVB_LAUNCH_CHECK();
     return SVB_OK;
@@ -189,6 +193,7 @@ extern "C" int svb_hue_bins(const uint8_t *rgb, int64_t n, uint16_t *bins, void 
     if (n == 0) return SVB_OK;
     if (!rgb || !bins) return SVB_E_NULL;
     if (n < 0) return SVB_E_ARG;
+    ProfScope ps(K_HUE_BINS, (cudaStream_t)stream);
     hue_bins_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(rgb, n, bins);
     SVB_LAUNCH_CHECK();
     return SVB_OK;
@@ -214,6 +219,7 @@ extern "C" int svb_reproject(const uint32_t *records, int rec_stride_words, int 
     if (n == 0) return SVB_OK;
     if (!records || !cam) return SVB_E_NULL;
     if (n < 0 || (rec_stride_words != 1 && rec_stride_words != 2)) return SVB_E_ARG;
+    ProfScope ps(K_REPROJECT, (cudaStream_t)stream);
     reproject_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(records, rec_stride_words, n, make_camd(cam),
                                                                          xy_f64, xy_i32);
     SVB_LAUNCH_CHECK();
@@ -235,6 +241,7 @@ extern "C" int svb_reproject_table(int axis, int n_coord, const svb_camera *cam,
     if (!cam || !out) return SVB_E_NULL;
     if (n_coord < 1 || (axis != 0 && axis != 1)) return SVB_E_ARG;
     int total = n_coord * 256;
+    ProfScope ps(K_REPROJECT, (cudaStream_t)stream);
     reproject_table_kernel<<<(total + 255) / 256, 256, 0, (cudaStream_t)stream>>>(axis, n_coord, make_camd(cam), out);
     SVB_LAUNCH_CHECK();
     return SVB_OK;
@@ -261,6 +268,7 @@ extern "C" int svb_scatter_points(const int32_t *pts, int n, uint8_t *img, int H
     if (n < 0 || H < 1 || W < 1 || channels < 1 || channels > 4) return SVB_E_ARG;
     uint32_t v = 0;
     for (int k = 0; k < channels; ++k) v |= (uint32_t)h_value[k] << (8 * k);
+    ProfScope ps(K_SCATTER, (cudaStream_t)stream);
     scatter_points_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(pts, n, img, H, W, channels, v, oob);
     SVB_LAUNCH_CHECK();
     return SVB_OK;
@@ -414,17 +422,24 @@ extern "C" int svb_road_points(const uint64_t *cloud, const int32_t *counts, con
     cudaStream_t st = (cudaStream_t)stream;
     RoadGeom g = make_road_geom(H, W, step);
     CamD c = make_camd(cam);
-    cudaError_t e;
-    e = cudaMemsetAsync(hist, 0, (size_t)F * SVB_HIST_STRIDE * sizeof(uint32_t), st);
-    if (e != cudaSuccess) return (int)e;
-    e = cudaMemsetAsync(road_mask, 0, (size_t)F * H * W, st);
-    if (e != cudaSuccess) return (int)e;
-    e = cudaMemset2DAsync(counts_out + 2, 4 * sizeof(int32_t), 0, 2 * sizeof(int32_t), F, st);
-    if (e != cudaSuccess) return (int)e;
+    {
+        ProfScope pc(K_ROAD_CLEAR, st);
+        cudaError_t e;
+        e = cudaMemsetAsync(hist, 0, (size_t)F * SVB_HIST_STRIDE * sizeof(uint32_t), st);
+        if (e != cudaSuccess) return (int)e;
+        e = cudaMemsetAsync(road_mask, 0, (size_t)F * H * W, st);
+        if (e != cudaSuccess) return (int)e;
+        e = cudaMemset2DAsync(counts_out + 2, 4 * sizeof(int32_t), 0, 2 * sizeof(int32_t), F, st);
+        if (e != cudaSuccess) return (int)e;
+    }
     dim3 grid(g.parts, F);
     uint32_t *nearbits = (uint32_t *)scratch;
-    road_pass1_kernel<<<grid, ROAD_THREADS, 0, st>>>(cloud, counts, planes, g, c, nearbits, hist, counts_out);
+    {
+        ProfScope ps(K_ROAD_PASS1, st);
+        road_pass1_kernel<<<grid, ROAD_THREADS, 0, st>>>(cloud, counts, planes, g, c, nearbits, hist, counts_out);
+    }
     SVB_LAUNCH_CHECK();
+    ProfScope ps2(K_ROAD_PASS2, st);
     if (overlay)
         road_pass2_kernel<true><<<grid, ROAD_THREADS, 0, st>>>(cloud, counts, planes, g, c, colour_threshold, nearbits,
                                                                hist, road_mask, overlay, counts_out);
