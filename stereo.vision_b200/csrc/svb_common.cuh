@@ -64,8 +64,9 @@ __device__ __forceinline__ double exact_dot(double X, double Y, double Z, double
 }
 
 // hue bin = rint(1000 * colorsys.rgb_to_hsv(r,g,b)[0]) with np.uint8 channels
-// (functions.py:73-78).  Grey -> 0.
-__device__ __forceinline__ int exact_hue_bin(int r, int g, int b) {
+// (functions.py:73-78).  Grey -> 0.  This is the reference's float64 operation
+// sequence, one rounding per operation; it is the definition, and the slow path of hue_bin().
+static __device__ __noinline__ int exact_hue_bin(int r, int g, int b) {
     int maxc = max(r, max(g, b));
     int minc = min(r, min(g, b));
     if (maxc == minc) return 0;
@@ -87,6 +88,32 @@ __device__ __forceinline__ int exact_hue_bin(int r, int g, int b) {
     h = __ddiv_rn(h, 6.0);
     if (h < 0.0) h = __dadd_rn(h, 1.0);          // np.remainder(h, 1.0) for h in (-1, 0)
     return __double2int_rn(__dmul_rn(h, 1000.0)); // rint, ties to even
+}
+
+// Fast path.  In real arithmetic 1000*h = 1000*hn / (6*range) with the integer
+//   hn = (g-b) | 2*range + (b-r) | 4*range + (r-g)   (+ 6*range when negative),
+// a rational with denominator <= 1530.  The float64 sequence above carries a relative error of a
+// few 1e-16, so its rint() can differ from the exactly rounded rational only when the rational is an
+// exact tie k + 1/2 (any other value is at least 1/3060 away from a tie).  Integer quotient and
+// remainder give the bin; the rare exact ties (0.06 % of colours) take the float64 path, which
+// decides them the way the reference's roundings do.  tests: exhaustive over all 2^24 colours.
+__device__ __forceinline__ int hue_bin(int r, int g, int b) {
+    int maxc = max(r, max(g, b));
+    int minc = min(r, min(g, b));
+    int range = maxc - minc;
+    if (range == 0) return 0;
+    int hn = (r == maxc) ? (g - b) : (g == maxc) ? 2 * range + (b - r) : 4 * range + (r - g);
+    uint32_t den = 6u * (uint32_t)range;
+    if (hn < 0) hn += (int)den;
+    uint32_t num = 1000u * (uint32_t)hn;                       // < 6000*255
+    // num / den (num < 2^21, den <= 1530): float estimate, off by at most one, fixed with the remainder
+    uint32_t q = __float2uint_rz(__fmul_rn((float)num, __frcp_rn((float)den)));
+    int rem = (int)num - (int)(q * den);
+    if (rem < 0) { --q; rem += (int)den; }
+    else if (rem >= (int)den) { ++q; rem -= (int)den; }
+    uint32_t twice = 2u * (uint32_t)rem;
+    if (twice == den) return exact_hue_bin(r, g, b);           // exact tie: let the float64 roundings decide
+    return (int)(q + (twice > den ? 1u : 0u));
 }
 
 // ------------------------------------------------------------------ warp helpers

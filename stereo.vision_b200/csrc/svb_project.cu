@@ -394,7 +394,7 @@ proj_write_kernel(const uint8_t *__restrict__ disp, const uint8_t *__restrict__ 
             uint64_t rec = s_cloud[i];
             if (HAS_RGB) {
                 uint32_t hi = (uint32_t)(rec >> 32);
-                int hue = exact_hue_bin((int)(hi & 0xFF), (int)((hi >> 8) & 0xFF), (int)((hi >> 16) & 0xFF));
+                int hue = hue_bin((int)(hi & 0xFF), (int)((hi >> 8) & 0xFF), (int)((hi >> 16) & 0xFF));
                 rec |= ((uint64_t)(hue & 3) << 30) | ((uint64_t)(hue >> 2) << 56);
             }
             dst[i] = rec;

@@ -186,7 +186,7 @@ extern "C" int svb_hue_histogram(const uint64_t *cloud, int n, uint32_t *hist, v
 __global__ void hue_bins_kernel(const uint8_t *__restrict__ rgb, int64_t n, uint16_t *__restrict__ bins) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    bins[i] = (uint16_t)exact_hue_bin(rgb[3 * i], rgb[3 * i + 1], rgb[3 * i + 2]);
+    bins[i] = (uint16_t)hue_bin(rgb[3 * i], rgb[3 * i + 1], rgb[3 * i + 2]);
 }
 
 extern "C" int svb_hue_bins(const uint8_t *rgb, int64_t n, uint16_t *bins, void *stream) {

@@ -1,0 +1,271 @@
+"""Drop-in for the hot-path helpers of the reference's functions.py (same names, positional
+signatures and error behaviour), executed by the sm_100a kernels behind libsvb200.so.
+
+    import stereo.vision_b200.functions as f        # instead of `import functions as f`
+
+Covered: the calls of stereovision.py:58-140 -- disparityCleaning / fillDisparity, maskDisparity,
+capDisparity, projectDisparityTo3d, RANSAC, calculatePointErrors, computePlanarThreshold,
+calculateColourHistogram, filterPointsByHistogram, project3DPointsTo2DImagePoints,
+generatePointsAsImage -- plus the module constants they read.  Clouds are returned as device handles
+(handles.py) that behave like the reference's lists for everything the orchestrator does with them.
+There is no CPU fallback: without a CUDA device every helper raises.
+
+Two literals of the reference are module settings here: `lattice_step` (functions.py:185-186,
+2) and `ransac_samples` (functions.py:286, 600).
+"""
+import ctypes as C
+import random
+
+import numpy as np
+import torch
+
+from . import _native as N
+from .camera import DEFAULT_CAMERA, Camera
+from .handles import DeviceColumn, HueHistogram, ImagePoints, PointCloud, bins_from_dict
+from .masks import default_carmask
+
+# ---- constants, functions.py:15-24
+camera_focal_length_px = DEFAULT_CAMERA.focal_px
+camera_focal_length_m = 4.8 / 1000
+stereo_camera_baseline_m = DEFAULT_CAMERA.baseline_m
+image_centre_h = DEFAULT_CAMERA.centre_h
+image_centre_w = DEFAULT_CAMERA.centre_w
+max_disparity = 128
+# ---- masks, functions.py:29-35 (masks/*.png of the CWD when present, else the packaged arrays)
+carmask = default_carmask((544, 1024))
+blackImg = np.zeros((544, 1024), dtype=np.uint8)
+# ---- literals of the reference exposed as settings
+lattice_step = 2
+ransac_samples = 600
+
+_state = {}
+
+
+def _camera() -> Camera:
+    return Camera(camera_focal_length_px, stereo_camera_baseline_m, image_centre_h, image_centre_w)
+
+
+def _dev():
+    N.require_cuda()
+    return torch.device("cuda", torch.cuda.current_device())
+
+
+def _to_dev_u8(a):
+    if torch.is_tensor(a):
+        return a.to(_dev()).contiguous(), True
+    return torch.from_numpy(np.ascontiguousarray(a, dtype=np.uint8)).to(_dev()), False
+
+
+def _carmask_dev():
+    key = (id(carmask), carmask.shape)
+    if _state.get("cm_key") != key:
+        _state["cm"] = torch.from_numpy(np.ascontiguousarray(carmask)).to(_dev())
+        _state["cm_key"] = key
+    return _state["cm"]
+
+
+def _back(t, was_tensor):
+    return t if was_tensor else t.cpu().numpy()
+
+
+# ---------------------------------------------------------------- a1-a3
+def disparityCleaning(disparity, option, prev_disp=None):
+    """functions.py:130-138."""
+    if option == 'previous':
+        if prev_disp is not None:
+            disparity = fillDisparity(disparity, prev_disp)
+    elif option == 'mean':
+        raise NotImplementedError("threshold_option 'mean' (fillAltDisparity) is outside the hot path")
+    return disparity
+
+
+def fillDisparity(disparity, previousDisparity):
+    """functions.py:140-147."""
+    if previousDisparity is None:
+        return disparity
+    d, was = _to_dev_u8(disparity)
+    p, _ = _to_dev_u8(previousDisparity)
+    H, W = d.shape
+    out = torch.empty_like(d)
+    N.check(N.load().svb_fill_sequence(N.ptr(d), N.ptr(p), N.ptr(out), 1, H, W, N.stream_ptr()), "svb_fill_sequence")
+    N.count(1)
+    return _back(out, was)
+
+
+def capDisparity(disparity):
+    """functions.py:164-167: the masked copy is discarded; the argument is returned unchanged."""
+    return disparity
+
+
+def maskDisparity(disparity):
+    """functions.py:169-172."""
+    d, was = _to_dev_u8(disparity)
+    H, W = d.shape
+    out = torch.empty_like(d)
+    N.check(N.load().svb_mask_disparity(N.ptr(d), N.ptr(_carmask_dev()), N.ptr(out), 1, H, W, N.stream_ptr()),
+            "svb_mask_disparity")
+    N.count(1)
+    return _back(out, was)
+
+
+# ---------------------------------------------------------------- a4
+def projectDisparityTo3d(disparity, max_disparity, rgb=[]):
+    """functions.py:178-198.  Returns a PointCloud (len / iteration / indexing / np.array like the list)."""
+    lib = N.load()
+    d, _ = _to_dev_u8(disparity)
+    H, W = d.shape[:2]
+    has_rgb = len(rgb) > 0
+    c = _to_dev_u8(rgb)[0] if has_rgb else None
+    step = int(lattice_step)
+    L = lib.svb_lattice_rows(H, step) * lib.svb_lattice_cols(W, step)
+    dev = d.device
+    cloud = torch.empty((max(L, 1),), dtype=torch.int64, device=dev)
+    counts = torch.zeros((1, 4), dtype=torch.int32, device=dev)
+    scratch = torch.empty((max(16, lib.svb_project_scratch_bytes(1, H, W, step)),), dtype=torch.uint8, device=dev)
+    cam = _camera()
+    cc = N.ccam(cam)
+    N.check(lib.svb_project_compact(N.ptr(d), None, N.ptr(c), 1, H, W, step, C.byref(cc), N.ptr(cloud), None,
+                                    N.ptr(counts), N.ptr(scratch), scratch.numel(), N.stream_ptr()), "svb_project_compact")
+    N.count(3)
+    n = int(counts[0, 0].item())
+    return PointCloud(cloud, n, cam, has_rgb)
+
+
+def project3DPointsTo2DImagePoints(points):
+    """functions.py:201-209."""
+    _need_cloud(points)
+    xy = torch.empty((len(points), 2), dtype=torch.float64, device=points.records.device)
+    cc = N.ccam(points.camera)
+    N.check(N.load().svb_reproject(N.ptr(points.records), 2, len(points), C.byref(cc), N.ptr(xy), None, N.stream_ptr()),
+            "svb_reproject")
+    N.count(1 if len(points) else 0)
+    return ImagePoints(xy)
+
+
+def _need_cloud(points):
+    if not isinstance(points, PointCloud):
+        raise TypeError("expected the PointCloud returned by projectDisparityTo3d, got %s" % type(points).__name__)
+
+
+# ---------------------------------------------------------------- a10-a12
+def calculateColourHistogram(points):
+    """functions.py:215-226."""
+    _need_cloud(points)
+    hist = torch.zeros((N.HIST_STRIDE,), dtype=torch.int32, device=points.records.device)
+    N.check(N.load().svb_hue_histogram(N.ptr(points.records), len(points), N.ptr(hist), N.stream_ptr()), "svb_hue_histogram")
+    N.count(1 if len(points) else 0)
+    return HueHistogram(hist)
+
+
+def _compact(points, mode, dist, hist, threshold):
+    lib, n = N.load(), len(points)
+    dev = points.records.device
+    out = torch.empty((max(n, 1),), dtype=torch.int64, device=dev)
+    cnt = torch.zeros((1,), dtype=torch.int32, device=dev)
+    scratch = torch.empty((max(16, lib.svb_compact_scratch_bytes(n)),), dtype=torch.uint8, device=dev)
+    N.check(lib.svb_compact_cloud(N.ptr(points.records), n, mode, N.ptr(dist), N.ptr(hist), float(threshold), N.ptr(out),
+                                  N.ptr(cnt), N.ptr(scratch), scratch.numel(), N.stream_ptr()), "svb_compact_cloud")
+    N.count(3 if n else 0)
+    return PointCloud(out, int(cnt.item()), points.camera, points.has_rgb)
+
+
+def filterPointsByHistogram(points, histogram, threshold=100):
+    """functions.py:228-230: keep points whose hue key count is > threshold, order kept."""
+    _need_cloud(points)
+    return _compact(points, 1, None, bins_from_dict(histogram, points.records.device), threshold)
+
+
+# ---------------------------------------------------------------- a8-a9
+def calculatePointErrors(abc, points):
+    """functions.py:300-312.  abc None raises TypeError like `abc[0]` does in the reference (:307)."""
+    _need_cloud(points)
+    if abc is None:
+        raise TypeError("'NoneType' object is not subscriptable")
+    h = np.ascontiguousarray(np.asarray(abc, dtype=np.float64).reshape(-1)[:3])
+    dist = torch.empty((len(points),), dtype=torch.float64, device=points.records.device)
+    cc = N.ccam(points.camera)
+    N.check(N.load().svb_point_errors(N.ptr(points.records), 2, len(points), C.byref(cc),
+                                      h.ctypes.data_as(C.c_void_p), N.ptr(dist), N.stream_ptr()), "svb_point_errors")
+    N.count(1 if len(points) else 0)
+    return DeviceColumn(dist)
+
+
+def computePlanarThreshold(points, differences, threshold=0.01):
+    """functions.py:314-323: keep points[i] where differences[i] < threshold, order kept."""
+    _need_cloud(points)
+    if isinstance(differences, DeviceColumn):
+        dist = differences.t
+    else:
+        dist = torch.from_numpy(np.ascontiguousarray(np.asarray(differences, dtype=np.float64).reshape(-1))).to(points.records.device)
+    if dist.numel() < len(points):
+        raise IndexError("index %d is out of bounds for axis 0 with size %d" % (dist.numel(), dist.numel()))
+    return _compact(points, 0, dist, None, threshold)
+
+
+# ---------------------------------------------------------------- a5-a7
+def _replay_draws(xyz, trials, S):
+    """Consume Python's global `random` stream exactly as functions.py:286 and :252-254 do."""
+    m = len(xyz)
+    samp = np.empty((trials, S), dtype=np.int32)
+    trip = np.empty((trials, 3), dtype=np.int32)
+    pop = range(m)
+    for t in range(trials):
+        samp[t] = random.sample(pop, S)
+        while True:
+            i1, i2, i3 = random.sample(pop, 1)[0], random.sample(pop, 1)[0], random.sample(pop, 1)[0]
+            u, v = xyz[i1] - xyz[i2], xyz[i2] - xyz[i3]
+            if not (u[1] * v[2] - u[2] * v[1] == 0 and u[2] * v[0] - u[0] * v[2] == 0 and u[0] * v[1] - u[1] * v[0] == 0):
+                break
+        trip[t] = (i1, i2, i3)
+    return samp, trip
+
+
+def RANSAC(points, trials):
+    """functions.py:278-298.  Returns (normal, coefficients): the same (3,1) float64 array twice, or
+    (None, None) when no trial produced a plane (e.g. fewer than `ransac_samples` points)."""
+    _need_cloud(points)
+    lib, S, T, M = N.load(), int(ransac_samples), int(trials), len(points)
+    if M < S or T < 1:
+        return (None, None)                   # random.sample raises in every trial, swallowed at :294
+    samp, trip = _replay_draws(points.xyz, T, S)
+    dev = points.records.device
+    si, ti = torch.from_numpy(samp).to(dev), torch.from_numpy(trip).to(dev)
+    counts = torch.tensor([[M]], dtype=torch.int32, device=dev)
+    errors = torch.empty((1, T), dtype=torch.float64, device=dev)
+    planes = torch.zeros((1, N.PLANE_STRIDE), dtype=torch.float64, device=dev)
+    cc, st = N.ccam(points.camera), N.stream_ptr()
+    N.check(lib.svb_ransac_score(N.ptr(points.records), 2, 0, N.ptr(counts), 1, 0, 1, T, S, C.byref(cc), N.ptr(si),
+                                 N.ptr(ti), 0, 0, N.ptr(errors), st), "svb_ransac_score")
+    N.check(lib.svb_ransac_finalize(N.ptr(points.records), 2, 0, N.ptr(counts), 1, 0, 1, T, S, C.byref(cc), N.ptr(ti),
+                                    0, 0, N.ptr(errors), 0.0, N.ptr(planes), st), "svb_ransac_finalize")
+    N.count(2)
+    row = planes[0].cpu().numpy()
+    if row[7] == 0.0:
+        return (None, None)
+    abc = row[:3].reshape(3, 1).copy()
+    RANSAC.last = {"best_trial": int(row[6]), "best_error": float(row[5]), "errors": errors}
+    return (abc, abc)
+
+
+# ---------------------------------------------------------------- a14
+def generatePointsAsImage(points):
+    """functions.py:339-344: 255 at img[y][x] for each (x,y) of an int32 (R,1,2) array."""
+    pts = np.ascontiguousarray(np.asarray(points, dtype=np.int32).reshape(-1, 2))
+    H, W = blackImg.shape
+    dev = _dev()
+    img = torch.from_numpy(np.ascontiguousarray(blackImg)).to(dev)
+    if len(pts):
+        p = torch.from_numpy(pts).to(dev)
+        oob = torch.zeros((1,), dtype=torch.int32, device=dev)
+        val = (C.c_uint8 * 4)(255, 0, 0, 0)
+        N.check(N.load().svb_scatter_points(N.ptr(p), len(pts), N.ptr(img), H, W, 1, val, N.ptr(oob), N.stream_ptr()),
+                "svb_scatter_points")
+        N.count(1)
+        if int(oob.item()):
+            raise IndexError("road point outside the %dx%d image" % (H, W))
+    return img.cpu().numpy()
+
+
+def getBlackImage():
+    """functions.py:448-450."""
+    return blackImg

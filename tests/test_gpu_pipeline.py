@@ -85,3 +85,22 @@ def test_no_plane_when_masked_cloud_too_small(cuda):
     orc = oracle_sequence(disp, bgr, cm, seeds=[0])
     assert orc[0]["abc"] is None
     check_frame(res, 0, orc[0])
+
+
+def test_hue_bins_exhaustive(cuda):
+    """a10 known-answer test over ALL 2^24 colours: kernel hue bin == oracle hue bin."""
+    import ctypes as C
+    import torch
+    import stereo.vision_b200._native as N
+    lib = N.load()
+    for r0 in range(0, 256, 32):                                  # 32 red values (2M colours) per launch
+        r, g, b = np.meshgrid(np.arange(r0, r0 + 32, dtype=np.uint8), np.arange(256, dtype=np.uint8),
+                              np.arange(256, dtype=np.uint8), indexing="ij")
+        rgb = np.stack([r.ravel(), g.ravel(), b.ravel()], axis=1)
+        t = torch.from_numpy(rgb).to(cuda)
+        out = torch.empty((len(rgb),), dtype=torch.int16, device=cuda)
+        N.check(lib.svb_hue_bins(N.ptr(t), len(rgb), N.ptr(out), N.stream_ptr()), "svb_hue_bins")
+        got = out.cpu().numpy().astype(np.int32)
+        want = no.hue_bin(rgb[:, 0], rgb[:, 1], rgb[:, 2])
+        bad = np.nonzero(got != want)[0]
+        assert len(bad) == 0, (len(bad), rgb[bad[:5]], got[bad[:5]], want[bad[:5]])
