@@ -162,6 +162,15 @@ int svb_reproject(const uint32_t *records, int rec_stride_words, int n, const sv
  * with axis 0 = x (centre_w), 1 = y (centre_h) -- the exhaustive known-answer table of SURVEY 7.1-1. */
 int svb_reproject_table(int axis, int n_coord, const svb_camera *cam, int32_t *out, void *stream);
 
+/* Displacement bits of the reprojection: x' = x - bit_x(x,d), y' = y - bit_y(y,d) (the float64
+ * expression of functions.py:206-207 lands on the site itself or one pixel before it, depending only on
+ * the coordinate and d).  bits: uint32 [svb_reproject_bits_words(H,W)], word [c*8 + (d>>5)] bit (d&31),
+ * x rows [0,W) then y rows [W,W+H).  *ok (device int32) = 1 if every pair moves by 0 or -1, else 0 and
+ * the table must not be used.  Passing the table to svb_road_points replaces four float64 divisions
+ * per kept point by two L1-resident bit lookups; NULL keeps the per-point arithmetic. */
+int64_t svb_reproject_bits_words(int H, int W);
+int svb_reproject_bits(int H, int W, const svb_camera *cam, uint32_t *bits, int32_t *ok, void *stream);
+
 /* ---- a14  generatePointsAsImage / the overlay loop      functions.py:339-344, stereovision.py:131-133
  * img[y,x,:] = value[:] for each (x,y) in pts int32 [n,2]; channels = 1 (mask) or 3 (overlay).
  * The image is NOT cleared (the caller copies blackImg / imgL first, as the reference does).
@@ -171,6 +180,7 @@ int svb_scatter_points(const int32_t *pts, int n, uint8_t *img, int H, int W, in
                        const uint8_t *h_value, int32_t *oob, void *stream);
 
 /* ---- a8-a14 fused, batched: the road points of F frames               stereovision.py:97-140
+ * reproj_bits: table of svb_reproject_bits or NULL.
  * pass 1: near = |P.abc-1| < cutoff ; per-frame hue histogram of the near points (shared memory,
  *         merged with global atomics); near bits kept;
  * pass 2: keep = near && hist[hue] > colour_threshold ; reproject (exact fp64) ; road_mask[y',x'] = 255.
@@ -180,7 +190,7 @@ int svb_scatter_points(const int32_t *pts, int n, uint8_t *img, int H, int W, in
 int64_t svb_road_scratch_bytes(int F, int H, int W, int step);
 int svb_road_points(const uint64_t *cloud, const int32_t *counts, const double *planes,
                     int F, int H, int W, int step, const svb_camera *cam,
-                    uint32_t colour_threshold,
+                    uint32_t colour_threshold, const uint32_t *reproj_bits,
                     uint32_t *hist, uint8_t *road_mask, uint8_t *overlay, int32_t *counts_out,
                     void *scratch, int64_t scratch_bytes, void *stream);
 

@@ -17,7 +17,7 @@ LIB_PATH = os.path.join(_PKG, "libsvb200.so")
 HUE_BINS = 1001
 HIST_STRIDE = 1024
 PLANE_STRIDE = 8
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 
 class SvbError(RuntimeError):
@@ -65,7 +65,9 @@ SIGNATURES = {
     "svb_reproject_table": (I, [I, I, CAMP, P, P]),
     "svb_scatter_points": (I, [P, I, P, I, I, I, P, P, P]),
     "svb_road_scratch_bytes": (L, [I, I, I, I]),
-    "svb_road_points": (I, [P, P, P, I, I, I, I, CAMP, U32, P, P, P, P, P, L, P]),
+    "svb_road_points": (I, [P, P, P, I, I, I, I, CAMP, U32, P, P, P, P, P, P, L, P]),
+    "svb_reproject_bits_words": (L, [I, I]),
+    "svb_reproject_bits": (I, [I, I, CAMP, P, P, P]),
     "svb_profile_enable": (I, [I]),
     "svb_profile_kernels": (I, []),
     "svb_profile_get": (I, [I, C.c_char_p, I, C.POINTER(D), C.POINTER(I)]),

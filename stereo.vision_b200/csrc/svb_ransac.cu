@@ -30,18 +30,26 @@ __host__ __device__ __forceinline__ uint32_t trial_key(uint64_t seed, int frame,
     k = mix32(k ^ (uint32_t)trial ^ 0x85EBCA6Bu);
     return k;
 }
-// keyed bijection of [0, 2^bits): 4 alternating Feistel half-rounds; cycle-walk into [0, m)
-__host__ __device__ __forceinline__ uint32_t perm_draw(uint32_t key, uint32_t i, int bits, uint32_t m) {
-    const int lo_bits = bits >> 1, hi_bits = bits - lo_bits;
-    const uint32_t lo_mask = (1u << lo_bits) - 1u, hi_mask = (1u << hi_bits) - 1u;
+// keyed bijection of [0, 2^bits): (odd multiply + add) and xor-shift by >= bits/2 are both invertible
+// modulo 2^bits; two rounds of each, then cycle-walk into [0, m).  The three multipliers/offset are
+// derived once per hypothesis from its key, so a draw costs ~10 integer instructions.
+struct PermKey { uint32_t A, B, C, mask; int sh; };
+__host__ __device__ __forceinline__ PermKey make_perm(uint32_t key, int bits) {
+    PermKey k;
+    k.A = mix32(key ^ 0x51ED270Bu) | 1u;
+    k.B = mix32(key + 0x9E3779B9u);
+    k.C = mix32(key + 0x3C6EF372u) | 1u;
+    k.mask = (bits >= 32) ? 0xFFFFFFFFu : ((1u << bits) - 1u);
+    k.sh = (bits + 1) >> 1;
+    return k;
+}
+__host__ __device__ __forceinline__ uint32_t perm_draw(const PermKey &k, uint32_t i, uint32_t m) {
     uint32_t v = i;
     do {
-        uint32_t lo = v & lo_mask, hi = v >> lo_bits;
-        hi ^= mix32(lo ^ key) & hi_mask;
-        lo ^= mix32(hi ^ (key + 0x9E3779B9u)) & lo_mask;
-        hi ^= mix32(lo ^ (key + 0x3C6EF372u)) & hi_mask;
-        lo ^= mix32(hi ^ (key + 0xDAA66D2Bu)) & lo_mask;
-        v = (hi << lo_bits) | lo;
+        v = (v * k.A + k.B) & k.mask;
+        v ^= v >> k.sh;
+        v = (v * k.C) & k.mask;
+        v ^= v >> k.sh;
     } while (v >= m);
     return v;
 }
@@ -163,41 +171,28 @@ ransac_score_kernel(const uint32_t *__restrict__ mcloud, int stride, int64_t sla
         if (lane == 0) *err_out = INFINITY;
         return;
     }
+    // |Z(d) * (a/f*(x-cw) + b/f*(y-ch) + c) - 1| with the constant terms folded into c2
     const double af = a / cam.f, bf = b / cam.f;
+    const double c2 = c - af * cam.cw - bf * cam.ch;
     const double nrm = sqrt(a * a + b * b + c * c);
     const int32_t *samp = EXPLICIT ? sample_idx + ((int64_t)f * T + t) * S : nullptr;
-    const int bits = bits_for(M);
+    const PermKey pk = make_perm(key, bits_for(M));
 
     double acc = 0.0;
     bool bad = false;
-    for (int j0 = 0; j0 < S; j0 += 128) {
-        uint32_t r[4];
-        bool have[4];
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            int j = j0 + u * 32 + lane;
-            have[u] = j < S;
-            r[u] = 0;
-            if (have[u]) {
-                uint32_t idx;
-                if (EXPLICIT) {
-                    int i = __ldg(samp + j);
-                    if (i < 0 || (uint32_t)i >= M) { bad = true; have[u] = false; idx = 0; }
-                    else idx = (uint32_t)i;
-                } else {
-                    idx = perm_draw(key ^ 0x51ED270Bu, (uint32_t)j, bits, M);
-                }
-                if (have[u]) r[u] = __ldg(rec + (int64_t)idx * stride);
-            }
+#pragma unroll 4
+    for (int j = lane; j < S; j += 32) {
+        uint32_t idx;
+        if (EXPLICIT) {
+            int i = __ldg(samp + j);
+            bad |= (i < 0 || (uint32_t)i >= M);
+            idx = bad ? 0u : (uint32_t)i;
+        } else {
+            idx = perm_draw(pk, (uint32_t)j, M);
         }
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            if (have[u]) {
-                double zd = s_Z[rec_d(r[u])];
-                double s = zd * fma(af, (double)rec_x(r[u]) - cam.cw, fma(bf, (double)rec_y(r[u]) - cam.ch, c));
-                acc += fabs(s - 1.0);
-            }
-        }
+        uint32_t r = __ldg(rec + (int64_t)idx * stride);
+        double s = s_Z[rec_d(r)] * fma(af, (double)rec_x(r), fma(bf, (double)rec_y(r), c2));
+        acc += fabs(s - 1.0);
     }
     acc = warp_sum(acc);
     bad = __any_sync(0xffffffffu, bad);
@@ -254,7 +249,8 @@ __global__ void ransac_dump_kernel(const uint32_t *__restrict__ mcloud, int stri
     const uint32_t *rec = mcloud + (int64_t)f * slab_records * stride;
     const uint32_t key = trial_key(seed, frame0 + f, t);
     const int bits = bits_for(M);
-    for (int j = lane; j < S; j += 32) samp[j] = (int32_t)perm_draw(key ^ 0x51ED270Bu, (uint32_t)j, bits, M);
+    const PermKey pk = make_perm(key, bits);
+    for (int j = lane; j < S; j += 32) samp[j] = (int32_t)perm_draw(pk, (uint32_t)j, M);
     P3 p1, p2, p3;
     int tri[3] = {-1, -1, -1};
     bool ok = trial_triple(rec, stride, M, cam, nullptr, key, p1, p2, p3, tri);

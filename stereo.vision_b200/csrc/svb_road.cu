@@ -247,6 +247,49 @@ extern "C" int svb_reproject_table(int axis, int n_coord, const svb_camera *cam,
     return SVB_OK;
 }
 
+// Reprojection displacement bits.  x' = trunc(((X*f)/Z)+cw) with X = ((x-cw)*Z)/f is x or x-1
+// depending only on (x, d), likewise y' on (y, d).  The table holds that one bit for
+// every coordinate and every d, computed with the exact float64 sequence; 50 KB at 1024x544, so the
+// lookups of pass 2 stay in L1.  Layout: word [c*8 + (d>>5)] bit (d&31), x rows first ([0,W)), then
+// y rows ([W, W+H)).  *ok is cleared if some pair moves by anything other than 0 or -1 (then the
+// caller must not pass the table and pass 2 evaluates the expression per point).
+__global__ void reproject_bits_kernel(int H, int W, CamD cam, uint32_t *__restrict__ bits, int32_t *__restrict__ ok) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;             // one thread per (coordinate, 32 d-values)
+    if (i >= (W + H) * 8) return;
+    int row = i >> 3, dw = i & 7;
+    bool is_x = row < W;
+    int coord = is_x ? row : row - W;
+    double centre = is_x ? cam.cw : cam.ch;
+    uint32_t word = 0;
+    for (int k = 0; k < 32; ++k) {
+        int d = dw * 32 + k;
+        if (d == 0) continue;
+        double Z = exact_Z(cam, d);
+        double V = exact_XY(centre, cam.f, coord, Z);
+        int p = (int)exact_reproject(centre, cam.f, V, Z);
+        int delta = coord - p;
+        if (delta == 1) word |= 1u << k;
+        else if (delta != 0) atomicExch(ok, 0);
+    }
+    bits[i] = word;
+}
+
+extern "C" int64_t svb_reproject_bits_words(int H, int W) { return (int64_t)(H + W) * 8; }
+
+extern "C" int svb_reproject_bits(int H, int W, const svb_camera *cam, uint32_t *bits, int32_t *ok, void *stream) {
+    if (!cam || !bits || !ok) return SVB_E_NULL;
+    if (H < 1 || W < 1 || H > SVB_MAX_DIM || W > SVB_MAX_DIM) return SVB_E_SHAPE;
+    cudaStream_t st = (cudaStream_t)stream;
+    int32_t one = 1;
+    cudaError_t e = cudaMemcpyAsync(ok, &one, sizeof(one), cudaMemcpyHostToDevice, st);
+    if (e != cudaSuccess) return (int)e;
+    int total = (W + H) * 8;
+    ProfScope ps(K_REPROJECT, st);
+    reproject_bits_kernel<<<(total + 127) / 128, 128, 0, st>>>(H, W, make_camd(cam), bits, ok);
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
+}
+
 // ------------------------------------------------------------------ a14 scatter
 __global__ void scatter_points_kernel(const int32_t *__restrict__ pts, int n, uint8_t *__restrict__ img,
                                       int H, int W, int channels, uint32_t value, int32_t *__restrict__ oob) {
@@ -293,6 +336,13 @@ static RoadGeom make_road_geom(int H, int W, int step) {
     return g;
 }
 
+// the reference's operation sequence for  |P.abc - 1| < cutoff  (slow path of the filtered test)
+static __device__ __noinline__ bool exact_near(CamD cam, uint32_t lo, double Z, double a, double b, double c, double cutoff) {
+    double X = exact_XY(cam.cw, cam.f, rec_x(lo), Z);
+    double Y = exact_XY(cam.ch, cam.f, rec_y(lo), Z);
+    return fabs(__dsub_rn(exact_dot(X, Y, Z, a, b, c), 1.0)) < cutoff;
+}
+
 // pass 1: near bits + histogram of the near points
 __global__ void __launch_bounds__(ROAD_THREADS)
 road_pass1_kernel(const uint64_t *__restrict__ cloud, const int32_t *__restrict__ counts,
@@ -318,6 +368,7 @@ road_pass1_kernel(const uint64_t *__restrict__ cloud, const int32_t *__restrict_
     if (threadIdx.x == 0) s_k = 0;
     __syncthreads();
     const double a = pl[0], b = pl[1], c = pl[2], cutoff = pl[4];
+    const double af = a / cam.f, bf = b / cam.f;
     const uint64_t *rec = cloud + (int64_t)f * g.slab;
     int kcount = 0;
     for (int i0 = begin + (threadIdx.x & ~31); i0 < end; i0 += ROAD_THREADS) {
@@ -327,10 +378,13 @@ road_pass1_kernel(const uint64_t *__restrict__ cloud, const int32_t *__restrict_
             uint64_t r = __ldcs((const unsigned long long *)(rec + i));
             uint32_t lo = (uint32_t)r, hi = (uint32_t)(r >> 32);
             double Z = s_Z[rec_d(lo)];
-            double X = exact_XY(cam.cw, cam.f, rec_x(lo), Z);
-            double Y = exact_XY(cam.ch, cam.f, rec_y(lo), Z);
-            double s = exact_dot(X, Y, Z, a, b, c);
-            near = fabs(__dsub_rn(s, 1.0)) < cutoff;
+            // filtered predicate: a 5-flop estimate of P.abc decides unless it lands within a guard band
+            // (~1e4 x the worst-case rounding difference) of the cutoff; then the exact sequence decides
+            double p = af * ((double)rec_x(lo) - cam.cw), q = bf * ((double)rec_y(lo) - cam.ch);
+            double est = fabs(fma(Z, p + q + c, -1.0));
+            double band = 1e-11 * fma(Z, fabs(p) + fabs(q) + fabs(c), 1.0);
+            if (fabs(est - cutoff) > band) near = est < cutoff;
+            else near = exact_near(cam, lo, Z, a, b, c, cutoff);
             if (near) atomicAdd(&s_h[rec_hue(lo, hi)], 1u);
         }
         uint32_t bal = __ballot_sync(0xffffffffu, near);
@@ -348,12 +402,12 @@ road_pass1_kernel(const uint64_t *__restrict__ cloud, const int32_t *__restrict_
 }
 
 // pass 2: colour filter, reprojection, scatter
-template <bool OVERLAY>
+template <bool OVERLAY, bool TABLE>
 __global__ void __launch_bounds__(ROAD_THREADS)
 road_pass2_kernel(const uint64_t *__restrict__ cloud, const int32_t *__restrict__ counts,
                   const double *__restrict__ planes, RoadGeom g, CamD cam, uint32_t colour_threshold,
                   const uint32_t *__restrict__ nearbits, const uint32_t *__restrict__ hist,
-                  uint8_t *__restrict__ road_mask, uint8_t *__restrict__ overlay, int32_t *__restrict__ counts_out) {
+                  const uint32_t *__restrict__ rbits, uint8_t *__restrict__ road_mask, uint8_t *__restrict__ overlay, int32_t *__restrict__ counts_out) {
     __shared__ uint32_t s_h[SVB_HIST_STRIDE];
     __shared__ double s_Z[256];
     __shared__ int s_r;
@@ -383,11 +437,17 @@ road_pass2_kernel(const uint64_t *__restrict__ cloud, const int32_t *__restrict_
             uint32_t lo = (uint32_t)r, hi = (uint32_t)(r >> 32);
             if (s_h[rec_hue(lo, hi)] > colour_threshold) {
                 keep = true;
-                double Z = s_Z[rec_d(lo)];
-                double X = exact_XY(cam.cw, cam.f, rec_x(lo), Z);
-                double Y = exact_XY(cam.ch, cam.f, rec_y(lo), Z);
-                int px = (int)exact_reproject(cam.cw, cam.f, X, Z);
-                int py = (int)exact_reproject(cam.ch, cam.f, Y, Z);
+                int x = rec_x(lo), y = rec_y(lo), d = rec_d(lo), px, py;
+                if (TABLE) {
+                    px = x - (int)((__ldg(rbits + x * 8 + (d >> 5)) >> (d & 31)) & 1u);
+                    py = y - (int)((__ldg(rbits + (g.W + y) * 8 + (d >> 5)) >> (d & 31)) & 1u);
+                } else {
+                    double Z = s_Z[d];
+                    double X = exact_XY(cam.cw, cam.f, x, Z);
+                    double Y = exact_XY(cam.ch, cam.f, y, Z);
+                    px = (int)exact_reproject(cam.cw, cam.f, X, Z);
+                    py = (int)exact_reproject(cam.ch, cam.f, Y, Z);
+                }
                 if (px >= 0 && py >= 0 && px < g.W && py < g.H) {
                     mask[(int64_t)py * g.W + px] = 255;
                     if (OVERLAY) {
@@ -413,7 +473,7 @@ extern "C" int64_t svb_road_scratch_bytes(int F, int H, int W, int step) {
 
 extern "C" int svb_road_points(const uint64_t *cloud, const int32_t *counts, const double *planes,
                                int F, int H, int W, int step, const svb_camera *cam,
-                               uint32_t colour_threshold,
+                               uint32_t colour_threshold, const uint32_t *reproj_bits,
                                uint32_t *hist, uint8_t *road_mask, uint8_t *overlay, int32_t *counts_out,
                                void *scratch, int64_t scratch_bytes, void *stream) {
     if (!cloud || !counts || !planes || !cam || !hist || !road_mask || !counts_out || !scratch) return SVB_E_NULL;
@@ -440,12 +500,12 @@ extern "C" int svb_road_points(const uint64_t *cloud, const int32_t *counts, con
     }
     SVB_LAUNCH_CHECK();
     ProfScope ps2(K_ROAD_PASS2, st);
-    if (overlay)
-        road_pass2_kernel<true><<<grid, ROAD_THREADS, 0, st>>>(cloud, counts, planes, g, c, colour_threshold, nearbits,
-                                                               hist, road_mask, overlay, counts_out);
-    else
-        road_pass2_kernel<false><<<grid, ROAD_THREADS, 0, st>>>(cloud, counts, planes, g, c, colour_threshold, nearbits,
-                                                                hist, road_mask, nullptr, counts_out);
+#define LAUNCH_P2(O, T)                                                                                        \
+    road_pass2_kernel<O, T><<<grid, ROAD_THREADS, 0, st>>>(cloud, counts, planes, g, c, colour_threshold, nearbits, \
+                                                           hist, reproj_bits, road_mask, overlay, counts_out)
+    if (overlay) { if (reproj_bits) LAUNCH_P2(true, true); else LAUNCH_P2(true, false); }
+    else         { if (reproj_bits) LAUNCH_P2(false, true); else LAUNCH_P2(false, false); }
+#undef LAUNCH_P2
     SVB_LAUNCH_CHECK();
     return SVB_OK;
 }

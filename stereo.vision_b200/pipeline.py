@@ -59,7 +59,7 @@ class BatchResult:
 class RoadPath:
     def __init__(self, shape=(544, 1024), step=2, trials=600, samples=600, point_threshold=0.05,
                  colour_threshold=10, carmask=None, camera: Camera = DEFAULT_CAMERA, max_frames=1,
-                 device="cuda:0"):
+                 device="cuda:0", use_reproj_table=True):
         N.require_cuda()
         self.lib = N.load()
         self.device = torch.device(device)
@@ -91,6 +91,13 @@ class RoadPath:
         nb = max(self.lib.svb_project_scratch_bytes(F, H, W, self.step),
                  self.lib.svb_road_scratch_bytes(F, H, W, self.step))
         self.scratch = torch.empty(((nb + 15) // 16 * 16,), dtype=torch.uint8, device=dev)
+        # reprojection displacement bits (built once; used only if every (coordinate, d) moves by 0 or -1)
+        self.reproj_bits = torch.empty((self.lib.svb_reproject_bits_words(H, W),), dtype=torch.int32, device=dev)
+        ok = torch.zeros((1,), dtype=torch.int32, device=dev)
+        N.check(self.lib.svb_reproject_bits(H, W, C.byref(self._cam), N.ptr(self.reproj_bits), N.ptr(ok), N.stream_ptr()),
+                "svb_reproject_bits")
+        if int(ok.item()) != 1 or not use_reproj_table:
+            self.reproj_bits = None
 
     # ------------------------------------------------------------------
     def process(self, disp, bgr, prev=None, seed=0, frame0=0, indices=None, overlay=None,
@@ -141,7 +148,7 @@ class RoadPath:
             ov = _as_cuda_u8(overlay, dev)
             res.overlay = ov
         N.check(lib.svb_road_points(N.ptr(self.cloud), N.ptr(self.counts), N.ptr(self.planes), F, H, W, self.step,
-                                    C.byref(self._cam), self.colour_threshold, N.ptr(self.hist), N.ptr(self.road_mask),
+                                    C.byref(self._cam), self.colour_threshold, N.ptr(self.reproj_bits), N.ptr(self.hist), N.ptr(self.road_mask),
                                     N.ptr(ov), N.ptr(self.counts), N.ptr(self.scratch), self.scratch.numel(), st),
                 "svb_road_points")
         N.count(KERNELS_PER_BATCH)

@@ -104,3 +104,49 @@ def test_hue_bins_exhaustive(cuda):
         want = no.hue_bin(rgb[:, 0], rgb[:, 1], rgb[:, 2])
         bad = np.nonzero(got != want)[0]
         assert len(bad) == 0, (len(bad), rgb[bad[:5]], got[bad[:5]], want[bad[:5]])
+
+
+def test_reprojection_exhaustive(cuda):
+    """a13 known-answer test over every (x,d) and (y,d) pair: the kernel's float64
+    sequence and the displacement-bit table both equal the oracle's reprojection."""
+    import ctypes as C
+    import torch
+    import stereo.vision_b200._native as N
+    from stereo.vision_b200.camera import DEFAULT_CAMERA
+    lib, cam = N.load(), N.ccam(DEFAULT_CAMERA)
+    H, W = 544, 1024
+    bits = torch.empty((lib.svb_reproject_bits_words(H, W),), dtype=torch.int32, device=cuda)
+    ok = torch.zeros((1,), dtype=torch.int32, device=cuda)
+    N.check(lib.svb_reproject_bits(H, W, C.byref(cam), N.ptr(bits), N.ptr(ok), N.stream_ptr()), "bits")
+    assert int(ok.item()) == 1
+    bits = bits.cpu().numpy().astype(np.uint32)
+    c = no.cam_of(None)
+    for axis, n, centre, row0 in ((0, W, c.cw, 0), (1, H, c.ch, W)):
+        out = torch.empty((n, 256), dtype=torch.int32, device=cuda)
+        N.check(lib.svb_reproject_table(axis, n, C.byref(cam), N.ptr(out), N.stream_ptr()), "table")
+        got = out.cpu().numpy()[:, 1:]
+        coord = np.arange(n, dtype=np.float64)[:, None]
+        d = np.arange(1, 256, dtype=np.float64)[None, :]
+        Z = (c.f * c.B) / d
+        V = ((coord - centre) * Z) / c.f
+        want = (((V * c.f) / Z) + centre).astype(np.int32)
+        assert np.array_equal(got, want)
+        delta = np.arange(n)[:, None] - want
+        assert set(np.unique(delta)) <= {0, 1} and (delta == 1).sum() > 0
+        di = np.arange(1, 256)
+        tb = (bits[(row0 + np.arange(n))[:, None] * 8 + (di >> 5)[None, :]] >> (di & 31)[None, :].astype(np.uint32)) & 1
+        assert np.array_equal(tb.astype(np.int64), delta)
+
+
+def test_road_points_without_reprojection_table(cuda):
+    """The per-point float64 reprojection path (no table) gives the same masks."""
+    from stereo.vision_b200.pipeline import RoadPath
+    F = 2
+    disp, bgr = synth.make_sequence(4, F)
+    cm = _carmask(disp.shape[1:])
+    a = RoadPath(carmask=cm, max_frames=F, samples=400)
+    b = RoadPath(carmask=cm, max_frames=F, samples=400, use_reproj_table=False)
+    assert a.reproj_bits is not None and b.reproj_bits is None
+    ra, rb = to_host(a.process(disp, bgr, seed=5)), to_host(b.process(disp, bgr, seed=5))
+    assert np.array_equal(ra["road_mask"], rb["road_mask"]) and np.array_equal(ra["counts"], rb["counts"])
+    assert ra["road_mask"].any()
