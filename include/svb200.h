@@ -200,6 +200,8 @@ int svb_road_points(const uint64_t *cloud, const int32_t *counts, const double *
  * the kernel's name, the summed device time in ms and the number of launches, id in
  * [0, svb_profile_kernels()).  Process-global; not for concurrent use from several threads. */
 int svb_profile_enable(int on);
+/* test hook: force svb_road_points onto its two-kernel path even when the fused cluster kernel applies */
+int svb_debug_force_two_pass(int on);
 int svb_profile_kernels(void);
 int svb_profile_get(int id, char *name, int name_cap, double *ms_total, int *launches);
 

@@ -69,6 +69,7 @@ SIGNATURES = {
     "svb_reproject_bits_words": (L, [I, I]),
     "svb_reproject_bits": (I, [I, I, CAMP, P, P, P]),
     "svb_profile_enable": (I, [I]),
+    "svb_debug_force_two_pass": (I, [I]),
     "svb_profile_kernels": (I, []),
     "svb_profile_get": (I, [I, C.c_char_p, I, C.POINTER(D), C.POINTER(I)]),
 }

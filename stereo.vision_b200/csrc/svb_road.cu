@@ -12,6 +12,11 @@
 #include "svb_common.cuh"
 #include "svb_prof.cuh"
 #include <math.h>
+#include <cooperative_groups.h>
+namespace cg = cooperative_groups;
+
+bool g_svb_force_two_pass = false;     // test hook: svb_debug_force_two_pass()
+extern "C" int svb_debug_force_two_pass(int on) { g_svb_force_two_pass = on != 0; return SVB_OK; }
 
 #define ROAD_THREADS 256
 #define ROAD_CHUNK 8192          // records per block in the fused passes
@@ -465,6 +470,161 @@ road_pass2_kernel(const uint64_t *__restrict__ cloud, const int32_t *__restrict_
     if (threadIdx.x == 0 && s_r) atomicAdd(&counts_out[f * 4 + 3], s_r);
 }
 
+// ------------------------------------------------------------------ the fused road kernel (clusters + DSMEM)
+// One thread-block CLUSTER of 8 CTAs owns one frame; CTA r owns the r-th eighth of the frame's records.
+//   A  clear this CTA's eighth of the road mask (replaces a memset launch)
+//   B  stream the records once (128-bit loads, 8 records in flight per thread): filtered near-plane
+//      test; a near point is reprojected through the displacement-bit table and appended to a list
+//      in SHARED memory as one word  px | py<<11 | hue<<22 ; its hue bin is counted in a shared histogram
+//      -- cluster barrier --
+//   C  every CTA sums the 8 partial histograms straight out of its peers' shared memory (DSMEM)
+//      -- cluster barrier --   (peers may not exit while their shared memory is being read)
+//   D  colour filter over the CTA's own near list, 255 into the mask.
+// The records are read from HBM exactly once and the near list never leaves the SM.
+#define RC_THREADS 512
+#define RC_PARTS 8
+#define RC_U 2                    // 128-bit loads in flight per thread (2 records each)
+
+template <bool OVERLAY>
+__global__ void __launch_bounds__(RC_THREADS, 2)
+road_cluster_kernel(const uint64_t *__restrict__ cloud, const int32_t *__restrict__ counts,
+                    const double *__restrict__ planes, RoadGeom g, CamD cam, uint32_t colour_threshold,
+                    const uint32_t *__restrict__ rbits, uint32_t *__restrict__ hist,
+                    uint8_t *__restrict__ road_mask, uint8_t *__restrict__ overlay, int32_t *__restrict__ counts_out) {
+    extern __shared__ __align__(16) uint32_t s_list[];
+    __shared__ uint32_t s_h[SVB_HIST_STRIDE];
+    __shared__ uint32_t s_tot[SVB_HIST_STRIDE];
+    __shared__ double s_Z[256];
+    __shared__ uint32_t s_n;
+    __shared__ int s_r;
+    cg::cluster_group cluster = cg::this_cluster();
+    const int rank = (int)cluster.block_rank();
+    const int f = blockIdx.x / RC_PARTS;
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int n = counts[f * 4 + 0];
+    const double *pl = planes + (int64_t)f * SVB_PLANE_STRIDE;
+    const bool valid = pl[7] != 0.0 && n > 0;
+
+    // A: clear my eighth of the mask (and zero the frame's histogram when there is nothing to do)
+    {
+        const int64_t bytes = (int64_t)g.H * g.W;
+        uint8_t *mask = road_mask + (int64_t)f * bytes;
+        int64_t per = (bytes / RC_PARTS) & ~(int64_t)15;
+        int64_t b0 = per * rank, b1 = rank == RC_PARTS - 1 ? bytes : b0 + per;
+        if ((((uintptr_t)mask) & 15) == 0) {
+            uint4 z = make_uint4(0, 0, 0, 0);
+            int64_t v1 = b0 + ((b1 - b0) & ~(int64_t)15);
+            for (int64_t o = b0 + (int64_t)tid * 16; o < v1; o += RC_THREADS * 16) *(uint4 *)(mask + o) = z;
+            for (int64_t o = v1 + tid; o < b1; o += RC_THREADS) mask[o] = 0;
+        } else {
+            for (int64_t o = b0 + tid; o < b1; o += RC_THREADS) mask[o] = 0;
+        }
+    }
+    if (!valid) {                                                // uniform over the cluster: nobody syncs
+        if (rank == 0) for (int k = tid; k < SVB_HIST_STRIDE; k += RC_THREADS) hist[(int64_t)f * SVB_HIST_STRIDE + k] = 0;
+        return;
+    }
+    for (int k = tid; k < SVB_HIST_STRIDE; k += RC_THREADS) s_h[k] = 0;
+    if (tid < 256) s_Z[tid] = tid ? exact_Z(cam, tid) : 0.0;
+    if (tid == 0) { s_n = 0; s_r = 0; }
+    __syncthreads();
+
+    // B: my part of the records
+    const double a = pl[0], b = pl[1], c = pl[2], cutoff = pl[4];
+    const double af = a / cam.f, bf = b / cam.f;
+    const uint64_t *rec = cloud + (int64_t)f * g.slab;
+    const int part = (((n + RC_PARTS - 1) / RC_PARTS) + 1) & ~1;  // even, so 128-bit loads stay aligned
+    const int begin = min(n, rank * part), end = min(n, begin + part);
+    const bool vec = ((((uintptr_t)rec) & 15) == 0);
+    for (int i0 = begin + (tid & ~31) * (2 * RC_U); i0 < end; i0 += RC_THREADS * 2 * RC_U) {
+        // this warp covers records [i0, i0 + 64*RC_U): RC_U rounds of 64, lane takes 2 adjacent records per round
+        uint64_t r[2 * RC_U];
+#pragma unroll
+        for (int u = 0; u < RC_U; ++u) {
+            int i = i0 + u * 64 + lane * 2;
+            r[2 * u] = r[2 * u + 1] = 0;
+            if (vec && i + 1 < end) {
+                uint4 v = __ldcs((const uint4 *)(rec + i));
+                r[2 * u] = (uint64_t)v.x | ((uint64_t)v.y << 32);
+                r[2 * u + 1] = (uint64_t)v.z | ((uint64_t)v.w << 32);
+            } else {
+                if (i < end) r[2 * u] = __ldcs((const unsigned long long *)(rec + i));
+                if (i + 1 < end) r[2 * u + 1] = __ldcs((const unsigned long long *)(rec + i + 1));
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < 2 * RC_U; ++k) {
+            int i = i0 + (k >> 1) * 64 + lane * 2 + (k & 1);
+            bool near = false;
+            uint32_t word = 0;
+            if (i < end) {
+                uint32_t lo = (uint32_t)r[k], hi = (uint32_t)(r[k] >> 32);
+                int x = rec_x(lo), y = rec_y(lo), d = rec_d(lo);
+                double Z = s_Z[d];
+                double p = af * ((double)x - cam.cw), q = bf * ((double)y - cam.ch);
+                double est = fabs(fma(Z, p + q + c, -1.0));
+                double band = 1e-11 * fma(Z, fabs(p) + fabs(q) + fabs(c), 1.0);
+                if (fabs(est - cutoff) > band) near = est < cutoff;
+                else near = exact_near(cam, lo, Z, a, b, c, cutoff);
+                if (near) {
+                    int hue = rec_hue(lo, hi);
+                    atomicAdd(&s_h[hue], 1u);
+                    int px = x - (int)((__ldg(rbits + x * 8 + (d >> 5)) >> (d & 31)) & 1u);
+                    int py = y - (int)((__ldg(rbits + (g.W + y) * 8 + (d >> 5)) >> (d & 31)) & 1u);
+                    word = (uint32_t)px | ((uint32_t)py << 11) | ((uint32_t)hue << 22);
+                }
+            }
+            uint32_t bal = __ballot_sync(0xffffffffu, near);
+            if (bal) {
+                uint32_t base = 0;
+                if (lane == 0) base = atomicAdd(&s_n, (uint32_t)__popc(bal));
+                base = __shfl_sync(0xffffffffu, base, 0);
+                if (near) s_list[base + __popc(bal & ((1u << lane) - 1u))] = word;
+            }
+        }
+    }
+    __syncthreads();
+    cluster.sync();
+
+    // C: full histogram = sum of the 8 partial ones, read through distributed shared memory
+    for (int k = tid; k < SVB_HIST_STRIDE; k += RC_THREADS) {
+        uint32_t t = 0;
+#pragma unroll
+        for (int rr = 0; rr < RC_PARTS; ++rr) t += cluster.map_shared_rank(s_h, rr)[k];
+        s_tot[k] = t;
+        if (rank == 0) hist[(int64_t)f * SVB_HIST_STRIDE + k] = t;
+    }
+    cluster.sync();
+
+    // D: colour filter + scatter of my near list
+    uint8_t *mask = road_mask + (int64_t)f * g.H * g.W;
+    uint8_t *ovl = OVERLAY ? overlay + (int64_t)f * g.H * g.W * 3 : nullptr;
+    const uint32_t nn = s_n;
+    int rcount = 0;
+    for (uint32_t k = tid; k < nn; k += RC_THREADS) {
+        uint32_t w = s_list[k];
+        if (s_tot[w >> 22] > colour_threshold) {
+            ++rcount;
+            int px = (int)(w & 0x7FFu), py = (int)((w >> 11) & 0x7FFu);
+            if (px < g.W && py < g.H) {
+                mask[(int64_t)py * g.W + px] = 255;
+                if (OVERLAY) {
+                    uint8_t *q = ovl + ((int64_t)py * g.W + px) * 3;
+                    q[0] = 0; q[1] = 255; q[2] = 0;               // [0,255,0], stereovision.py:133
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) rcount += __shfl_xor_sync(0xffffffffu, rcount, o);
+    if (lane == 0 && rcount) atomicAdd(&s_r, rcount);
+    __syncthreads();
+    if (tid == 0) {
+        if (nn) atomicAdd(&counts_out[f * 4 + 2], (int)nn);
+        if (s_r) atomicAdd(&counts_out[f * 4 + 3], s_r);
+    }
+}
+
 extern "C" int64_t svb_road_scratch_bytes(int F, int H, int W, int step) {
     if (F < 1 || H < 2 || W < 2 || step < 1) return 0;
     RoadGeom g = make_road_geom(H, W, step);
@@ -482,6 +642,38 @@ extern "C" int svb_road_points(const uint64_t *cloud, const int32_t *counts, con
     cudaStream_t st = (cudaStream_t)stream;
     RoadGeom g = make_road_geom(H, W, step);
     CamD c = make_camd(cam);
+    // fused cluster kernel when the displacement table is given and a CTA's near list fits in shared memory
+    const int64_t list_cap = ((g.slab + RC_PARTS - 1) / RC_PARTS + 2 + 255) & ~(int64_t)255;
+    const size_t list_bytes = (size_t)list_cap * sizeof(uint32_t);
+    const bool mask_no_wrap = (H <= 2048 && W <= 2048);
+    if (reproj_bits && mask_no_wrap && list_bytes <= 160 * 1024 && !g_svb_force_two_pass) {
+        cudaError_t e = cudaMemset2DAsync(counts_out + 2, 4 * sizeof(int32_t), 0, 2 * sizeof(int32_t), F, st);
+        if (e != cudaSuccess) return (int)e;
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(RC_PARTS * F);
+        cfg.blockDim = dim3(RC_THREADS);
+        cfg.dynamicSmemBytes = list_bytes;
+        cfg.stream = st;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = RC_PARTS; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+        cfg.attrs = at; cfg.numAttrs = 1;
+        ProfScope ps(K_ROAD_CLUSTER, st);
+        if (overlay) {
+            e = cudaFuncSetAttribute(road_cluster_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)list_bytes);
+            if (e == cudaSuccess)
+                e = cudaLaunchKernelEx(&cfg, road_cluster_kernel<true>, cloud, counts, planes, g, c, colour_threshold,
+                                       reproj_bits, hist, road_mask, overlay, counts_out);
+        } else {
+            e = cudaFuncSetAttribute(road_cluster_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)list_bytes);
+            if (e == cudaSuccess)
+                e = cudaLaunchKernelEx(&cfg, road_cluster_kernel<false>, cloud, counts, planes, g, c, colour_threshold,
+                                       reproj_bits, hist, road_mask, (uint8_t *)nullptr, counts_out);
+        }
+        if (e != cudaSuccess) return (int)e;
+        SVB_LAUNCH_CHECK();
+        return SVB_OK;
+    }
     {
         ProfScope pc(K_ROAD_CLEAR, st);
         cudaError_t e;

@@ -20,7 +20,7 @@ import torch
 from . import _native as N
 from .camera import DEFAULT_CAMERA, Camera
 
-KERNELS_PER_BATCH = 8      # fill, count, scan, write, score, finalize, road pass 1, road pass 2
+KERNELS_PER_BATCH = 7      # fill, count, scan, write, score, finalize, fused road kernel (8 on the two-pass road path)
 
 
 def _as_cuda_u8(x, device):
@@ -98,6 +98,8 @@ class RoadPath:
                 "svb_reproject_bits")
         if int(ok.item()) != 1 or not use_reproj_table:
             self.reproj_bits = None
+        # svb_road_points takes its fused cluster path when a CTA's near list fits in shared memory
+        self.fused_road = self.reproj_bits is not None and (((self.L + 7) // 8 + 2 + 255) // 256 * 256) * 4 <= 160 * 1024
 
     # ------------------------------------------------------------------
     def process(self, disp, bgr, prev=None, seed=0, frame0=0, indices=None, overlay=None,
@@ -151,7 +153,7 @@ class RoadPath:
                                     C.byref(self._cam), self.colour_threshold, N.ptr(self.reproj_bits), N.ptr(self.hist), N.ptr(self.road_mask),
                                     N.ptr(ov), N.ptr(self.counts), N.ptr(self.scratch), self.scratch.numel(), st),
                 "svb_road_points")
-        N.count(KERNELS_PER_BATCH)
+        N.count(KERNELS_PER_BATCH if self.fused_road else KERNELS_PER_BATCH + 1)
         return res
 
     def dump_indices(self, F, seed=0, frame0=0):

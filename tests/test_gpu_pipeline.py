@@ -150,3 +150,23 @@ def test_road_points_without_reprojection_table(cuda):
     ra, rb = to_host(a.process(disp, bgr, seed=5)), to_host(b.process(disp, bgr, seed=5))
     assert np.array_equal(ra["road_mask"], rb["road_mask"]) and np.array_equal(ra["counts"], rb["counts"])
     assert ra["road_mask"].any()
+
+
+def test_two_pass_road_path_matches_fused(cuda):
+    """svb_road_points' two-kernel path (large lattices / no table) equals the fused cluster kernel."""
+    import stereo.vision_b200._native as N
+    from stereo.vision_b200.pipeline import RoadPath
+    F = 3
+    disp, bgr = synth.make_sequence(5, F)
+    cm = _carmask(disp.shape[1:])
+    eng = RoadPath(carmask=cm, max_frames=F, samples=400)
+    assert eng.fused_road
+    ra = to_host(eng.process(disp, bgr, seed=5))
+    N.load().svb_debug_force_two_pass(1)
+    try:
+        rb = to_host(eng.process(disp, bgr, seed=5))
+    finally:
+        N.load().svb_debug_force_two_pass(0)
+    for k in ("road_mask", "counts", "hist"):
+        assert np.array_equal(ra[k], rb[k]), k
+    assert ra["road_mask"].any()

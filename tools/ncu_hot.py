@@ -11,6 +11,7 @@ import sys
 
 rep, pat = sys.argv[1], sys.argv[2]
 top = int(sys.argv[3]) if len(sys.argv) > 3 else 25
+by = 1 if (len(sys.argv) > 4 and sys.argv[4] == "stall") else 0
 out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "cuda,sass",
                       "--kernel-name", "regex:" + pat], capture_output=True, text=True).stdout
 rows = list(csv.reader(out.splitlines()))
@@ -39,5 +40,5 @@ for r in rows[hdr_i + 1:]:
 tot_i = sum(v[0] for v in agg.values()) or 1
 tot_s = sum(v[1] for v in agg.values()) or 1
 print("total warp instructions %.3g, samples %.0f" % (tot_i, tot_s))
-for (addr, src), (ins, smp) in sorted(agg.items(), key=lambda kv: -kv[1][0])[:top]:
+for (addr, src), (ins, smp) in sorted(agg.items(), key=lambda kv: -kv[1][by])[:top]:
     print("%5.1f%% inst %5.1f%% stall  %-28s %s" % (100 * ins / tot_i, 100 * smp / tot_s, addr[-28:], src[:110]))
