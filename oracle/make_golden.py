@@ -1,0 +1,186 @@
+"""TEST INFRASTRUCTURE -- generates tests/golden/*.npz by running the UNMODIFIED reference
+(/root/reference/functions.py, imported by oracle/ref_harness.py) on seeded synthetic inputs.
+
+Run in the build container only (the reference tree does not exist on the GPU box):
+
+    python oracle/make_golden.py            # all fixtures, ~4 min on 8 cores
+
+The fixtures are the only pin the oracle has (the reference ships no tests).  Inputs are
+not stored: they are regenerated from (sequence id, frame id) by stereo.vision_b200/synth.py, whose
+output is itself pinned here by a hash.  Large outputs are stored as sha256 digests plus compact
+forms (bit-packed road mask, histogram bins, counts, plane).
+"""
+import hashlib
+import multiprocessing as mp
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "oracle"))
+
+import ref_harness as rh  # noqa: E402
+import stereo.vision_b200.synth as synth  # noqa: E402
+
+OUT = os.path.join(ROOT, "tests", "golden")
+
+
+def sha(a) -> str:
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+def frame_record(o, d, bgr):
+    """Compact, comparable form of one ref_harness.run_frame result."""
+    rec = {
+        "in_disp_sha": sha(d), "in_bgr_sha": sha(bgr),
+        "filled_sha": sha(o["filled"]), "masked_disp_sha": sha(o["masked_disp"]),
+        "N": len(o["points_xyz"]), "M": len(o["mask_xyz"]),
+        "xyz_sha": sha(o["points_xyz"]), "rgb_sha": sha(o["points_rgb"]), "mask_xyz_sha": sha(o["mask_xyz"]),
+        "xyz_head": o["points_xyz"][:64].copy(), "xyz_tail": o["points_xyz"][-64:].copy(),
+        "has_plane": o["abc"] is not None,
+        "abc": o["abc"] if o["abc"] is not None else np.full(3, np.nan),
+        "best_error": o["best_error"], "trials_logged": o["trial_log_n"],
+        "near_n": o["near_n"], "road_n": o["road_n"],
+        "hist_bins": rh.hist_to_bins(o["hist"]),
+        "pts_sha": sha(o["plane_pts_int"]), "pts_head": o["plane_pts_int"][:64].copy(),
+        "road_mask_bits": np.packbits(o["road_mask"] != 0), "road_mask_sha": sha(o["road_mask"]),
+        "road_mask_values": np.unique(o["road_mask"]),
+    }
+    if "diffs" in o:
+        rec["diffs_head"] = o["diffs"][:256].copy()
+        rec["diffs_sum"] = float(np.sum(o["diffs"]))
+    return rec
+
+
+def save(name, frames, **meta):
+    flat = dict(meta)
+    flat["n_frames"] = len(frames)
+    for i, r in enumerate(frames):
+        for k, v in r.items():
+            flat["f%d_%s" % (i, k)] = v
+    path = os.path.join(OUT, name)
+    np.savez_compressed(path, **flat)
+    print("wrote %s (%.1f KB)" % (name, os.path.getsize(path) / 1024))
+
+
+def sequence_fixture(name, seq, n_frames, step=2, n_samples=600, trials=600):
+    f = rh.load_reference(step=step, n_samples=n_samples)
+    frames, prev = [], None
+    for t in range(n_frames):
+        d, bgr = synth.make_frame(seq, t)
+        t0 = time.perf_counter()
+        o = rh.run_frame(f, d, bgr, prev, synth.ransac_seed(seq, t), trials=trials)
+        prev = o["filled"]
+        r = frame_record(o, d, bgr)
+        r["ref_seconds"] = time.perf_counter() - t0
+        frames.append(r)
+        print("  %s frame %d: N=%d M=%d near=%d road=%d  %.1fs" % (name, t, r["N"], r["M"], r["near_n"], r["road_n"], r["ref_seconds"]))
+    save(name, frames, seq=seq, step=step, n_samples=n_samples, trials=trials, shape=np.array([544, 1024]))
+
+
+def small_fixture():
+    """A 64x96 frame with its own masks (module globals swapped, functions.py:32,35) and full arrays."""
+    f = rh.load_reference()
+    rng = np.random.default_rng(77)
+    H, W = 64, 96
+    d = rng.integers(0, 40, size=(H, W), dtype=np.uint8)
+    d[rng.random((H, W)) < 0.25] = 0
+    prev = rng.integers(0, 40, size=(H, W), dtype=np.uint8)
+    bgr = rng.integers(0, 256, size=(H, W, 3), dtype=np.uint8)
+    bgr[:, :, 1] = bgr[:, :, 0] // 2 + 60                      # a few populated hue bins
+    cm = (rng.random((H, W)) < 0.8).astype(np.uint8) * 255
+    rh.install_masks(f, carmask=cm, black=np.zeros((H, W), np.uint8))
+    # the sample size is the literal 600 (functions.py:286); a 32x48 lattice has at most 1536 sites
+    o = rh.run_frame(f, d, bgr, prev, seed=5, trials=50, point_threshold=0.5, road_color_thresh=2)
+    r = frame_record(o, d, bgr)
+    r.update(in_disp=d, in_prev=prev, in_bgr=bgr, in_carmask=cm, filled=o["filled"], xyz=o["points_xyz"],
+             rgb=o["points_rgb"], mask_xyz=o["mask_xyz"], pts=o["plane_pts_int"], road_mask=o["road_mask"],
+             diffs=o.get("diffs", np.zeros(0)))
+    save("small_64x96.npz", [r], seed=5, trials=50, n_samples=600, point_threshold=0.5, colour_threshold=2)
+
+
+def noplane_fixture():
+    """Fewer masked points than the sample size: RANSAC -> (None, None), black mask."""
+    f = rh.load_reference()
+    d, bgr = synth.make_frame(2, 0)
+    cm = np.zeros((544, 1024), np.uint8)
+    cm[200:210, 100:160] = 255
+    rh.install_masks(f, carmask=cm)
+    o = rh.run_frame(f, d, bgr, None, seed=1)
+    r = frame_record(o, d, bgr)
+    save("noplane.npz", [r], seq=2)
+
+
+def _hue_chunk(r):
+    f = rh.load_reference()
+    out = np.empty((256, 256), dtype=np.uint16)
+    rr = np.uint8(r)
+    for g in range(256):
+        gg = np.uint8(g)
+        for b in range(256):
+            out[g, b] = int(round(float(f.BGRtoHSVHue((rr, gg, np.uint8(b)))) * 1000.0))
+    return r, out
+
+
+def hue_fixture():
+    """Reference hue key of ALL 2^24 colours (functions.py:73-78 with np.uint8 channels), as bins."""
+    table = np.empty((256, 256, 256), dtype=np.uint16)
+    with mp.get_context("fork").Pool(os.cpu_count()) as pool:
+        for r, t in pool.imap_unordered(_hue_chunk, range(256)):
+            table[r] = t
+    # keep the hash of the full table and, verbatim, every 17th red plane (1 MB raw, compresses well)
+    np.savez_compressed(os.path.join(OUT, "hue_bins.npz"), sha=sha(table), planes=np.arange(0, 256, 17),
+                        table_planes=table[::17].copy(), populated=len(np.unique(table)))
+    print("wrote hue_bins.npz, %d distinct bins, sha %s" % (len(np.unique(table)), sha(table)[:16]))
+
+
+def reproject_fixture():
+    """x' for every (x, d) and y' for every (y, d) through the reference's own projection and
+    reprojection helpers (functions.py:178-209) and the caller's int32 cast (stereovision.py:112);
+    the step-1 variant of the loader gives odd coordinates too, the unmodified one is cross-checked."""
+    out = {}
+    for step in (1, 2):
+        f = rh.load_reference(step=step)
+        xt = np.full((1024, 256), -1, dtype=np.int32)
+        yt = np.full((544, 256), -1, dtype=np.int32)
+        for d in range(1, 256):
+            row = np.full((2, 1025), d, dtype=np.uint8)           # y = 0 only, x = 0..1023
+            pts = f.projectDisparityTo3d(row, 128)
+            pp = np.array(f.project3DPointsTo2DImagePoints(pts), np.int32)
+            xt[0:1024:step, d] = pp[:, 0]
+            col = np.full((545, 2), d, dtype=np.uint8)            # x = 0 only, y = 0..543
+            pts = f.projectDisparityTo3d(col, 128)
+            pp = np.array(f.project3DPointsTo2DImagePoints(pts), np.int32)
+            yt[0:544:step, d] = pp[:, 1]
+        out[step] = (xt, yt)
+    x1, y1 = out[1]
+    x2, y2 = out[2]
+    assert np.array_equal(x1[::2], x2[::2]) and np.array_equal(y1[::2], y2[::2])
+    dx = (np.arange(1024)[:, None] - x1)[:, 1:]
+    dy = (np.arange(544)[:, None] - y1)[:, 1:]
+    assert set(np.unique(dx)) <= {0, 1} and set(np.unique(dy)) <= {0, 1}
+    np.savez_compressed(os.path.join(OUT, "reproject_table.npz"), dx_bits=np.packbits(dx.astype(np.uint8)),
+                        dy_bits=np.packbits(dy.astype(np.uint8)), moved_x=int(dx.sum()), moved_y=int(dy.sum()))
+    print("wrote reproject_table.npz: %d (x,d) and %d (y,d) pairs land one pixel before" % (dx.sum(), dy.sum()))
+
+
+if __name__ == "__main__":
+    os.makedirs(OUT, exist_ok=True)
+    which = sys.argv[1:] or ["seq", "s400", "step1", "small", "noplane", "reproject", "hue"]
+    if "seq" in which:
+        sequence_fixture("seq0_step2_s600.npz", 0, 3)
+    if "s400" in which:
+        sequence_fixture("seq6_step2_s400.npz", 6, 2, n_samples=400)
+    if "step1" in which:
+        sequence_fixture("seq7_step1_s600.npz", 7, 1, step=1)
+    if "small" in which:
+        small_fixture()
+    if "noplane" in which:
+        noplane_fixture()
+    if "reproject" in which:
+        reproject_fixture()
+    if "hue" in which:
+        hue_fixture()

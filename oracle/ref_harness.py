@@ -57,6 +57,9 @@ def install_masks(f, carmask=None, black=None):
         f.carmask = np.ascontiguousarray(carmask)
     if black is not None:
         f.blackImg = np.ascontiguousarray(black)
+        # capDisparity (functions.py:166) masks with disparity_range; its result is discarded but the
+        # shapes must agree for the call to succeed
+        f.disparity_range = np.full(black.shape, 255, dtype=np.uint8)
 
 
 def install_camera(f, cam):

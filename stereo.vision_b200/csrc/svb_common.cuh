@@ -58,7 +58,7 @@ __device__ __forceinline__ double exact_XY(double centre, double f, int coord, d
 __device__ __forceinline__ double exact_reproject(double centre, double f, double XY, double Z) {
     return __dadd_rn(__ddiv_rn(__dmul_rn(XY, f), Z), centre);
 }
-// P . abc with the products summed left to right, no FMA (oracle/np_oracle.py: plane_distance)
+// P . abc with the products summed left to right, no FMA (functions.py:275,310 evaluate it with np.dot)
 __device__ __forceinline__ double exact_dot(double X, double Y, double Z, double a, double b, double c) {
     return __dadd_rn(__dadd_rn(__dmul_rn(X, a), __dmul_rn(Y, b)), __dmul_rn(Z, c));
 }

@@ -1,0 +1,115 @@
+"""Pins the oracle (oracle/np_oracle.py) to outputs of the UNMODIFIED reference stored in tests/golden
+(made by oracle/make_golden.py from /root/reference/functions.py).  CPU only."""
+import hashlib
+import os
+
+import numpy as np
+import pytest
+
+import np_oracle as no
+import stereo.vision_b200.synth as synth
+from stereo.vision_b200.masks import default_carmask
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def sha(a):
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+def load(name):
+    with np.load(os.path.join(GOLD, name), allow_pickle=False) as z:
+        return {k: z[k] for k in z.files}
+
+
+def frame(g, i):
+    p = "f%d_" % i
+    return {k[len(p):]: v for k, v in g.items() if k.startswith(p)}
+
+
+def compare(o, r):
+    """oracle frame dict o vs golden record r: bit-exact sets/orders/masks, planes to 1e-9."""
+    assert sha(o["filled"]) == str(r["filled_sha"])
+    c, m, rd = o["cloud"], o["mcloud"], o["road"]
+    assert len(c["d"]) == int(r["N"]) and len(m["d"]) == int(r["M"])
+    assert sha(c["xyz"]) == str(r["xyz_sha"]), "XYZ float64 must be bit-identical to the reference's"
+    assert sha(c["rgb"]) == str(r["rgb_sha"])
+    assert sha(m["xyz"]) == str(r["mask_xyz_sha"])
+    if not bool(r["has_plane"]):
+        assert o["abc"] is None and rd["road_n"] == 0 and not rd["mask"].any()
+        return
+    np.testing.assert_allclose(o["abc"], r["abc"], rtol=1e-9)
+    np.testing.assert_allclose(o["errors"][o["best"]], float(r["best_error"]), rtol=1e-9)
+    assert rd["near_n"] == int(r["near_n"]) and rd["road_n"] == int(r["road_n"])
+    assert np.array_equal(rd["hist"], r["hist_bins"])
+    assert sha(rd["pts"]) == str(r["pts_sha"]), "reprojected integer points, in order"
+    assert sha(rd["mask"]) == str(r["road_mask_sha"])
+    assert np.array_equal(np.packbits(rd["mask"] != 0), r["road_mask_bits"])
+    np.testing.assert_allclose(rd["dist"][:256], r["diffs_head"], rtol=1e-10, atol=1e-13)
+
+
+@pytest.mark.parametrize("name", ["seq0_step2_s600.npz", "seq6_step2_s400.npz", "seq7_step1_s600.npz"])
+def test_sequences(name):
+    g = load(name)
+    seq, step, S, T = int(g["seq"]), int(g["step"]), int(g["n_samples"]), int(g["trials"])
+    cm = default_carmask((544, 1024), prefer_cwd=False)
+    prev = None
+    for t in range(int(g["n_frames"])):
+        r = frame(g, t)
+        d, bgr = synth.make_frame(seq, t)
+        assert sha(d) == str(r["in_disp_sha"]) and sha(bgr) == str(r["in_bgr_sha"]), "synthetic input drifted"
+        o = no.run_frame(d, bgr, prev, cm, seed=synth.ransac_seed(seq, t), trials=T, n_samples=S, step=step)
+        prev = o["filled"]
+        compare(o, r)
+
+
+def test_small_frame_with_own_masks():
+    g = load("small_64x96.npz")
+    r = frame(g, 0)
+    o = no.run_frame(r["in_disp"], r["in_bgr"], r["in_prev"], r["in_carmask"], seed=int(g["seed"]),
+                     trials=int(g["trials"]), n_samples=int(g["n_samples"]),
+                     threshold=float(g["point_threshold"]), colour_threshold=int(g["colour_threshold"]))
+    compare(o, r)
+    assert np.array_equal(o["filled"], r["filled"]) and np.array_equal(o["cloud"]["xyz"], r["xyz"])
+    assert np.array_equal(o["road"]["pts"], r["pts"]) and np.array_equal(o["road"]["mask"], r["road_mask"])
+
+
+def test_no_plane():
+    g = load("noplane.npz")
+    r = frame(g, 0)
+    d, bgr = synth.make_frame(int(g["seq"]), 0)
+    cm = np.zeros((544, 1024), np.uint8)
+    cm[200:210, 100:160] = 255
+    o = no.run_frame(d, bgr, None, cm, seed=1)
+    assert not bool(r["has_plane"])
+    compare(o, r)
+
+
+def test_hue_bins_all_colours():
+    """a10 exhaustively: oracle hue bin of all 2^24 colours == the reference's key (hash + sampled planes)."""
+    g = load("hue_bins.npz")
+    h = hashlib.sha256()
+    gg, bb = np.meshgrid(np.arange(256, dtype=np.uint8), np.arange(256, dtype=np.uint8), indexing="ij")
+    planes = {int(p): i for i, p in enumerate(g["planes"])}
+    for r in range(256):
+        t = no.hue_bin(np.full_like(gg, r), gg, bb).astype(np.uint16)
+        h.update(np.ascontiguousarray(t).tobytes())
+        if r in planes:
+            assert np.array_equal(t, g["table_planes"][planes[r]])
+    assert h.hexdigest() == str(g["sha"])
+
+
+def test_reprojection_table():
+    """a13 exhaustively: every (x,d), (y,d) pair lands on the site or one pixel before, as in the reference."""
+    g = load("reproject_table.npz")
+    c = no.cam_of(None)
+    for n, centre, key, moved in ((1024, c.cw, "dx_bits", "moved_x"), (544, c.ch, "dy_bits", "moved_y")):
+        coord = np.arange(n, dtype=np.float64)[:, None]
+        d = np.arange(1, 256, dtype=np.float64)[None, :]
+        Z = (c.f * c.B) / d
+        V = ((coord - centre) * Z) / c.f
+        xyz = np.stack([V.ravel(), V.ravel(), np.broadcast_to(Z, V.shape).ravel()], axis=1)
+        cam = no.Cam(c.f, c.B, centre, centre)
+        _, pi = no.reproject(xyz, cam)
+        delta = (np.arange(n)[:, None] - pi[:, 0].reshape(n, 255)).astype(np.uint8)
+        assert np.array_equal(np.packbits(delta), g[key]) and int(delta.sum()) == int(g[moved])
