@@ -163,21 +163,18 @@ def algorithmic_bytes(kernel, L, N, M, K, R, T, S):
 
 def run_b200(args):
     import torch
-    import torch.distributed as dist
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
+    import stereo.vision_b200.shard as shard
+    rank, world, local = shard.rank_world()
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
+    shard.init("nccl", dev)
     import stereo.vision_b200._native as N
     from stereo.vision_b200.pipeline import RoadPath, KERNELS_PER_BATCH
     from stereo.vision_b200.masks import default_carmask
 
     F, T, S = args.frames, args.trials, args.samples
     ncpu = os.cpu_count() or 1
-    disp_h, bgr_h = make_sequence_parallel(rank, F, max(1, min(16, ncpu // max(1, world))))
+    disp_h, bgr_h = make_sequence_parallel(shard.sequence_of_rank(rank), F, max(1, min(16, ncpu // max(1, world))))
     disp_p = torch.from_numpy(disp_h).pin_memory()
     bgr_p = torch.from_numpy(bgr_h).pin_memory()
     cm = default_carmask((H, W), prefer_cwd=False)
@@ -189,8 +186,7 @@ def run_b200(args):
         return eng.process(disp_d, bgr_d, prev=None, seed=seed, frame0=0)
 
     def barrier():
-        if world > 1:
-            dist.barrier()
+        shard.barrier()
         torch.cuda.synchronize()
 
     for _ in range(max(args.warmup, 3)):
@@ -234,10 +230,7 @@ def run_b200(args):
         e2e = run_e2e(args, torch, dev, eng.camera, cm, disp_p, bgr_p, seed, ref_counts)
 
     # ---- max over ranks
-    t = torch.tensor([ms, e2e["ms"] if e2e else 0.0], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_max, e2e_ms_max = t.tolist()
+    ms_max, e2e_ms_max = shard.max_over_ranks([ms, e2e["ms"] if e2e else 0.0], dev)
     out = None
     if rank == 0:
         peaks = {}
@@ -282,9 +275,7 @@ def run_b200(args):
                                    "sample": "%d independent sequences x %d chained frames through oracle/np_oracle.py "
                                              "(numpy float64 restatement), one process per core, %.1f s wall" % (procs, fpp, wall)}
         print(json.dumps(out))
-    if world > 1:
-        dist.barrier()
-        dist.destroy_process_group()
+    shard.finish()
     return out
 
 
