@@ -104,10 +104,14 @@ int svb_cloud_export(const uint32_t *records, int rec_stride_words, int n, const
  *   sample_idx == NULL : counter-based on-device draws keyed by (rng_seed, frame0+f, t):
  *                        S distinct indices (keyed bijection + cycle walking) and triples redrawn
  *                        while exactly collinear (functions.py:251-259) -- throughput mode.
- *                        svb_ransac_dump_indices writes the same draws out for the oracle. */
+ *                        svb_ransac_dump_indices writes the same draws out for the oracle.
+ * max_m: an upper bound of every frame's cloud size known to the host (e.g. the number of lattice sites
+ *        inside carmask), or 0.  When 4*max_m bytes fit in shared memory each block stages its frame's
+ *        cloud there once and the S gathers of a hypothesis become shared-memory reads; frames that
+ *        turn out larger than max_m, and max_m = 0, gather from global memory (L2). */
 int svb_ransac_score(const uint32_t *mcloud, int rec_stride_words, int64_t slab_stride_records,
                      const int32_t *counts, int counts_stride, int counts_col,
-                     int F, int T, int S, const svb_camera *cam,
+                     int F, int T, int S, int max_m, const svb_camera *cam,
                      const int32_t *sample_idx, const int32_t *triple_idx,
                      uint64_t rng_seed, int frame0,
                      double *errors, void *stream);

@@ -17,7 +17,7 @@ LIB_PATH = os.path.join(_PKG, "libsvb200.so")
 HUE_BINS = 1001
 HIST_STRIDE = 1024
 PLANE_STRIDE = 8
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 
 class SvbError(RuntimeError):
@@ -52,7 +52,7 @@ SIGNATURES = {
     "svb_project_scratch_bytes": (L, [I, I, I, I]),
     "svb_project_compact": (I, [P, P, P, I, I, I, I, CAMP, P, P, P, P, L, P]),
     "svb_cloud_export": (I, [P, I, I, CAMP, P, P, P, P, P, P, P]),
-    "svb_ransac_score": (I, [P, I, L, P, I, I, I, I, I, CAMP, P, P, U64, I, P, P]),
+    "svb_ransac_score": (I, [P, I, L, P, I, I, I, I, I, I, CAMP, P, P, U64, I, P, P]),
     "svb_ransac_dump_indices": (I, [P, I, L, P, I, I, I, I, I, CAMP, U64, I, P, P, P]),
     "svb_ransac_finalize": (I, [P, I, L, P, I, I, I, I, I, CAMP, P, U64, I, P, D, P, P]),
     "svb_plane_from_abc": (I, [P, D, P]),

@@ -136,48 +136,77 @@ __device__ __forceinline__ bool trial_triple(const uint32_t *__restrict__ rec, i
 }
 
 // ------------------------------------------------------------------ score: one warp per hypothesis
-template <bool EXPLICIT>
-__global__ void __launch_bounds__(RANSAC_THREADS)
-ransac_score_kernel(const uint32_t *__restrict__ mcloud, int stride, int64_t slab_records,
-                    const int32_t *__restrict__ counts, int cstride, int ccol,
-                    int T, int S, CamD cam,
-                    const int32_t *__restrict__ sample_idx, const int32_t *__restrict__ triple_idx,
-                    uint64_t seed, int frame0, double *__restrict__ errors) {
-    __shared__ double s_Z[256];
-    s_Z[threadIdx.x] = threadIdx.x ? exact_Z(cam, threadIdx.x) : 0.0;
-    __syncthreads();
+// int -> double without the (quarter-rate) conversion instruction: 2^52 + x has x in its low mantissa bits
+__device__ __forceinline__ double u2d(uint32_t x) { return __hiloint2double(0x43300000, (int)x) - 4503599627370496.0; }
 
-    const int f = blockIdx.y;
-    const int lane = threadIdx.x & 31;
-    const int t = blockIdx.x * RANSAC_WARPS + (threadIdx.x >> 5);
-    if (t >= T) return;
-    const int Mi = counts[(int64_t)f * cstride + ccol];
-    double *err_out = errors + (int64_t)f * T + t;
-    if (Mi < S || Mi < 1 || S < 1) {                              // random.sample raises, :286,294
-        if (lane == 0) *err_out = INFINITY;
-        return;
+__device__ __forceinline__ double bcast(double v, int src) {
+    return __hiloint2double(__shfl_sync(0xffffffffu, __double2hiint(v), src), __shfl_sync(0xffffffffu, __double2loint(v), src));
+}
+
+// Warp-cooperative version of trial_triple: lanes 0..2 each fetch and expand one point (one division
+// sequence per coordinate for the whole warp instead of three), then the nine values are broadcast.
+__device__ __forceinline__ bool warp_triple(const uint32_t *__restrict__ rec, int stride, uint32_t M, const CamD &cam,
+                                            const int32_t *__restrict__ triple, uint32_t key, int lane,
+                                            P3 &p1, P3 &p2, P3 &p3) {
+    const int rounds = triple ? 1 : MAX_TRIPLE_ROUNDS;
+    for (int round = 0; round < rounds; ++round) {
+        uint32_t idx;
+        bool valid = true;
+        if (triple) {
+            int i = lane < 3 ? triple[lane] : 0;
+            valid = i >= 0 && (uint32_t)i < M;
+            idx = valid ? (uint32_t)i : 0u;
+            if (__any_sync(0xffffffffu, !valid)) return false;
+        } else {
+            idx = uniform_draw(key, 3u * round + (lane < 3 ? lane : 0), M);
+        }
+        uint32_t r = __ldg(rec + (int64_t)idx * stride);
+        P3 p = expand_point(cam, r | (lane < 3 ? 0u : (1u << 22)));     // idle lanes: d >= 1, no division by zero
+        p1.x = bcast(p.x, 0); p1.y = bcast(p.y, 0); p1.z = bcast(p.z, 0);
+        p2.x = bcast(p.x, 1); p2.y = bcast(p.y, 1); p2.z = bcast(p.z, 1);
+        p3.x = bcast(p.x, 2); p3.y = bcast(p.y, 2); p3.z = bcast(p.z, 2);
+        if (triple || !exactly_collinear(p1, p2, p3)) {
+            uint32_t r1 = __shfl_sync(0xffffffffu, r, 0), r2 = __shfl_sync(0xffffffffu, r, 1), r3 = __shfl_sync(0xffffffffu, r, 2);
+            return !image_collinear(r1, r2, r3);
+        }
     }
-    const uint32_t M = (uint32_t)Mi;
-    const uint32_t *rec = mcloud + (int64_t)f * slab_records * stride;
-    const uint32_t key = trial_key(seed, frame0 + f, t);
-    const int32_t *trip = EXPLICIT ? triple_idx + ((int64_t)f * T + t) * 3 : nullptr;
+    return false;
+}
 
+// plane as in plane_of, with one reciprocal of the determinant instead of three divisions (the result
+// moves by ~1 ulp; only the arg-min of the scores and abc to 1e-5 are observables)
+__device__ __forceinline__ bool plane_fast(const P3 &p1, const P3 &p2, const P3 &p3, double &a, double &b, double &c) {
+    double c23x = p2.y * p3.z - p2.z * p3.y, c23y = p2.z * p3.x - p2.x * p3.z, c23z = p2.x * p3.y - p2.y * p3.x;
+    double c31x = p3.y * p1.z - p3.z * p1.y, c31y = p3.z * p1.x - p3.x * p1.z, c31z = p3.x * p1.y - p3.y * p1.x;
+    double c12x = p1.y * p2.z - p1.z * p2.y, c12y = p1.z * p2.x - p1.x * p2.z, c12z = p1.x * p2.y - p1.y * p2.x;
+    double det = p1.x * c23x + p1.y * c23y + p1.z * c23z;
+    if (det == 0.0 || !isfinite(det)) return false;
+    double inv = 1.0 / det;
+    a = (c23x + c31x + c12x) * inv;
+    b = (c23y + c31y + c12y) * inv;
+    c = (c23z + c31z + c12z) * inv;
+    return isfinite(a) && isfinite(b) && isfinite(c);
+}
+
+// One warp scores trial t of one frame.  `src` = where the S sample gathers read the 4-byte records:
+// global memory (stride words apart) or the frame's cloud staged in shared memory (stride 1).
+template <bool EXPLICIT>
+__device__ __forceinline__ void score_trial(const uint32_t *__restrict__ rec, int stride, const uint32_t *src, int src_stride,
+                                            uint32_t M, int bits, int S, const CamD &cam, double inv_f, const double *s_Z,
+                                            const int32_t *__restrict__ samp, const int32_t *__restrict__ trip,
+                                            uint32_t key, int lane, double *err_out) {
     P3 p1, p2, p3;
-    int tri[3];
     double a, b, c;
-    bool ok = trial_triple(rec, stride, M, cam, trip, key, p1, p2, p3, tri);
-    ok = ok && plane_of(p1, p2, p3, a, b, c);
+    bool ok = warp_triple(rec, stride, M, cam, trip, key, lane, p1, p2, p3);
+    ok = ok && plane_fast(p1, p2, p3, a, b, c);
     if (!ok) {
         if (lane == 0) *err_out = INFINITY;
         return;
     }
     // |Z(d) * (a/f*(x-cw) + b/f*(y-ch) + c) - 1| with the constant terms folded into c2
-    const double af = a / cam.f, bf = b / cam.f;
+    const double af = a * inv_f, bf = b * inv_f;
     const double c2 = c - af * cam.cw - bf * cam.ch;
-    const double nrm = sqrt(a * a + b * b + c * c);
-    const int32_t *samp = EXPLICIT ? sample_idx + ((int64_t)f * T + t) * S : nullptr;
-    const PermKey pk = make_perm(key, bits_for(M));
-
+    const PermKey pk = make_perm(key, bits);
     double acc = 0.0;
     bool bad = false;
 #pragma unroll 4
@@ -190,32 +219,134 @@ ransac_score_kernel(const uint32_t *__restrict__ mcloud, int stride, int64_t sla
         } else {
             idx = perm_draw(pk, (uint32_t)j, M);
         }
-        uint32_t r = __ldg(rec + (int64_t)idx * stride);
-        double s = s_Z[rec_d(r)] * fma(af, (double)rec_x(r), fma(bf, (double)rec_y(r), c2));
+        uint32_t r = src[(int64_t)idx * src_stride];
+        double s = s_Z[r >> 22 & 0xFFu] * fma(af, u2d(r & 0x7FFu), fma(bf, u2d(r >> 11 & 0x7FFu), c2));
         acc += fabs(s - 1.0);
     }
     acc = warp_sum(acc);
     bad = __any_sync(0xffffffffu, bad);
     if (lane == 0) {
-        double e = acc / ((double)S * nrm);
+        double e = acc / ((double)S * sqrt(a * a + b * b + c * c));
         *err_out = (bad || isnan(e)) ? INFINITY : e;              // NaN never beats bestError, :291
+    }
+}
+
+// variant 1: gathers from global memory (L2); 8 hypotheses per block
+template <bool EXPLICIT>
+__global__ void __launch_bounds__(RANSAC_THREADS)
+ransac_score_kernel(const uint32_t *__restrict__ mcloud, int stride, int64_t slab_records,
+                    const int32_t *__restrict__ counts, int cstride, int ccol,
+                    int T, int S, CamD cam,
+                    const int32_t *__restrict__ sample_idx, const int32_t *__restrict__ triple_idx,
+                    uint64_t seed, int frame0, double *__restrict__ errors) {
+    __shared__ double s_Z[256];
+    s_Z[threadIdx.x] = threadIdx.x ? exact_Z(cam, threadIdx.x) : 0.0;
+    __syncthreads();
+    const int f = blockIdx.y;
+    const int lane = threadIdx.x & 31;
+    const int t = blockIdx.x * RANSAC_WARPS + (threadIdx.x >> 5);
+    if (t >= T) return;
+    const int Mi = counts[(int64_t)f * cstride + ccol];
+    double *err_out = errors + (int64_t)f * T + t;
+    if (Mi < S || Mi < 1 || S < 1) {                              // random.sample raises, :286,294
+        if (lane == 0) *err_out = INFINITY;
+        return;
+    }
+    const uint32_t *rec = mcloud + (int64_t)f * slab_records * stride;
+    score_trial<EXPLICIT>(rec, stride, rec, stride, (uint32_t)Mi, bits_for((uint32_t)Mi), S, cam, 1.0 / cam.f, s_Z,
+                          EXPLICIT ? sample_idx + ((int64_t)f * T + t) * S : nullptr,
+                          EXPLICIT ? triple_idx + ((int64_t)f * T + t) * 3 : nullptr,
+                          trial_key(seed, frame0 + f, t), lane, err_out);
+}
+
+// variant 2: the frame's masked cloud (<= 4 bytes x max_m) is staged once per block in shared memory
+// and the block's warps share it for T/gridDim.x hypotheses each; the S gathers of a hypothesis are
+// shared-memory reads (no 32-byte-sector over-fetch from L2).
+#define RANSAC_SMEM_THREADS 1024
+template <bool EXPLICIT>
+__global__ void __launch_bounds__(RANSAC_SMEM_THREADS, 1)
+ransac_score_smem_kernel(const uint32_t *__restrict__ mcloud, int stride, int64_t slab_records,
+                         const int32_t *__restrict__ counts, int cstride, int ccol,
+                         int T, int S, int cap, CamD cam,
+                         const int32_t *__restrict__ sample_idx, const int32_t *__restrict__ triple_idx,
+                         uint64_t seed, int frame0, double *__restrict__ errors) {
+    extern __shared__ __align__(16) uint32_t s_rec[];
+    __shared__ double s_Z[256];
+    const int f = blockIdx.y;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = RANSAC_SMEM_THREADS / 32;
+    const int Mi = counts[(int64_t)f * cstride + ccol];
+    const uint32_t *rec = mcloud + (int64_t)f * slab_records * stride;
+    const bool none = (Mi < S || Mi < 1 || S < 1);
+    const bool staged = !none && Mi <= cap;
+    const int bits = bits_for((uint32_t)max(Mi, 1));
+    const double inv_f = 1.0 / cam.f;
+    if (threadIdx.x < 256) s_Z[threadIdx.x] = threadIdx.x ? exact_Z(cam, threadIdx.x) : 0.0;
+    if (staged) {
+        if (stride == 1 && ((((uintptr_t)rec) & 15) == 0)) {
+            const uint4 *src = (const uint4 *)rec;
+            int n4 = Mi >> 2;
+            for (int i = threadIdx.x; i < n4; i += RANSAC_SMEM_THREADS) ((uint4 *)s_rec)[i] = __ldg(src + i);
+            for (int i = (n4 << 2) + threadIdx.x; i < Mi; i += RANSAC_SMEM_THREADS) s_rec[i] = __ldg(rec + i);
+        } else {
+            for (int i = threadIdx.x; i < Mi; i += RANSAC_SMEM_THREADS) s_rec[i] = __ldg(rec + (int64_t)i * stride);
+        }
+    }
+    __syncthreads();
+    // trials of this block: t = blockIdx.x + k * gridDim.x, dealt to the warps round-robin
+    for (int t = blockIdx.x + warp * gridDim.x; t < T; t += nwarps * gridDim.x) {
+        double *err_out = errors + (int64_t)f * T + t;
+        if (none) {
+            if (lane == 0) *err_out = INFINITY;
+            continue;
+        }
+        score_trial<EXPLICIT>(rec, stride, staged ? s_rec : rec, staged ? 1 : stride, (uint32_t)Mi, bits, S, cam, inv_f, s_Z,
+                              EXPLICIT ? sample_idx + ((int64_t)f * T + t) * S : nullptr,
+                              EXPLICIT ? triple_idx + ((int64_t)f * T + t) * 3 : nullptr,
+                              trial_key(seed, frame0 + f, t), lane, err_out);
     }
 }
 
 extern "C" int svb_ransac_score(const uint32_t *mcloud, int rec_stride_words, int64_t slab_stride_records,
                                 const int32_t *counts, int counts_stride, int counts_col,
-                                int F, int T, int S, const svb_camera *cam,
+                                int F, int T, int S, int max_m, const svb_camera *cam,
                                 const int32_t *sample_idx, const int32_t *triple_idx,
                                 uint64_t rng_seed, int frame0, double *errors, void *stream) {
     if (!mcloud || !counts || !cam || !errors) return SVB_E_NULL;
     if ((sample_idx == nullptr) != (triple_idx == nullptr)) return SVB_E_NULL;
     if (F < 1 || T < 1 || S < 1) return SVB_E_SHAPE;
     if ((rec_stride_words != 1 && rec_stride_words != 2) || counts_stride < 1 || counts_col < 0 ||
-        counts_col >= counts_stride) return SVB_E_ARG;
-    dim3 grid((T + RANSAC_WARPS - 1) / RANSAC_WARPS, F);
+        counts_col >= counts_stride || max_m < 0) return SVB_E_ARG;
     cudaStream_t st = (cudaStream_t)stream;
     CamD c = make_camd(cam);
     ProfScope ps(K_RANSAC_SCORE, st);
+    const size_t smem = (((size_t)max_m + 3) & ~(size_t)3) * sizeof(uint32_t);
+    if (max_m > 0 && smem <= 200 * 1024 && T >= 64) {
+        // blocks per frame: enough blocks for ~8 rounds over the SMs (1 block per SM), at least 32 trials each
+        int dev = 0, sms = 148;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        int per_frame = (8 * sms + F - 1) / F;
+        if (per_frame > T / 32) per_frame = T / 32;
+        if (per_frame < 1) per_frame = 1;
+        dim3 grid(per_frame, F);
+        cudaError_t e;
+        if (sample_idx) {
+            e = cudaFuncSetAttribute(ransac_score_smem_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            if (e != cudaSuccess) return (int)e;
+            ransac_score_smem_kernel<true><<<grid, RANSAC_SMEM_THREADS, smem, st>>>(
+                mcloud, rec_stride_words, slab_stride_records, counts, counts_stride, counts_col, T, S, max_m, c,
+                sample_idx, triple_idx, rng_seed, frame0, errors);
+        } else {
+            e = cudaFuncSetAttribute(ransac_score_smem_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            if (e != cudaSuccess) return (int)e;
+            ransac_score_smem_kernel<false><<<grid, RANSAC_SMEM_THREADS, smem, st>>>(
+                mcloud, rec_stride_words, slab_stride_records, counts, counts_stride, counts_col, T, S, max_m, c,
+                nullptr, nullptr, rng_seed, frame0, errors);
+        }
+        SVB_LAUNCH_CHECK();
+        return SVB_OK;
+    }
+    dim3 grid((T + RANSAC_WARPS - 1) / RANSAC_WARPS, F);
     if (sample_idx)
         ransac_score_kernel<true><<<grid, RANSAC_THREADS, 0, st>>>(mcloud, rec_stride_words, slab_stride_records, counts,
                                                                    counts_stride, counts_col, T, S, c, sample_idx,

@@ -80,6 +80,9 @@ class RoadPath:
         self.carmask = _as_cuda_u8(carmask, dev)
         if tuple(self.carmask.shape) != (H, W):
             raise ValueError("carmask shape %s != %s" % (tuple(self.carmask.shape), (H, W)))
+        # most masked-cloud points a frame can have: lattice sites inside carmask (bounds the RANSAC staging)
+        cm_host = self.carmask.cpu().numpy()
+        self.max_m = int((cm_host[0:H - 1:self.step, 0:W - 1:self.step] != 0).sum())
         self.filled = torch.empty((F, H, W), dtype=torch.uint8, device=dev)
         self.cloud = torch.empty((F, self.L), dtype=torch.int64, device=dev)
         self.mcloud = torch.empty((F, self.L), dtype=torch.int32, device=dev)
@@ -140,7 +143,7 @@ class RoadPath:
             si = si.to(dev).contiguous().view(F, self.T, self.S)
             ti = ti.to(dev).contiguous().view(F, self.T, 3)
         N.check(lib.svb_ransac_score(N.ptr(self.mcloud), 1, self.L, N.ptr(self.counts), 4, 1, F, self.T, self.S,
-                                     C.byref(self._cam), N.ptr(si), N.ptr(ti), seed, frame0, N.ptr(self.errors), st),
+                                     self.max_m, C.byref(self._cam), N.ptr(si), N.ptr(ti), seed, frame0, N.ptr(self.errors), st),
                 "svb_ransac_score")
         N.check(lib.svb_ransac_finalize(N.ptr(self.mcloud), 1, self.L, N.ptr(self.counts), 4, 1, F, self.T, self.S,
                                         C.byref(self._cam), N.ptr(ti), seed, frame0, N.ptr(self.errors),
