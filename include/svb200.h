@@ -17,10 +17,11 @@
  *   - nothing is allocated or retained: scratch comes from the caller, sizes from svb_*_bytes().
  *
  * Records
- *   cloud  : uint64 per point,  bits  0-10 x | 11-21 y | 22-29 d | 30-31 hue&3   (low word)
- *                               bits 32-39 R | 40-47 G | 48-55 B | 56-63 hue>>2  (high word)
+ *   cloud  : uint64 per point,  bits  0-10 x | 11-21 y | 22-29 d | 30-31 zero    (low word)
+ *                               bits 32-39 R | 40-47 G | 48-55 B | 56-63 zero    (high word)
  *   mcloud : uint32 per point,  bits  0-10 x | 11-21 y | 22-29 d                 (masked cloud)
- *   (x,y) = pixel site, d = uint8 disparity, hue = rint(1000*colorsys_hue) in [0,1000].
+ *   (x,y) = pixel site, d = uint8 disparity.  The hue bin rint(1000*colorsys_hue) in [0,1000] is a
+ *   function of (R,G,B) and is computed where it is consumed (only near-plane points need it).
  *   X,Y,Z are never stored: they are exact float64 functions of (x,y,d) (functions.py:191-193)
  *   and are recomputed where needed, which is what makes the reprojection bit-exact.
  *   Point order inside a frame is the reference's append order (row-major over the lattice).

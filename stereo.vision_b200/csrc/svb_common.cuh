@@ -38,12 +38,9 @@ __host__ __device__ __forceinline__ uint32_t pack_xyd(int x, int y, int d) {
 __host__ __device__ __forceinline__ int rec_x(uint32_t lo) { return (int)(lo & 0x7FFu); }
 __host__ __device__ __forceinline__ int rec_y(uint32_t lo) { return (int)((lo >> 11) & 0x7FFu); }
 __host__ __device__ __forceinline__ int rec_d(uint32_t lo) { return (int)((lo >> 22) & 0xFFu); }
-__host__ __device__ __forceinline__ int rec_hue(uint32_t lo, uint32_t hi) {
-    return (int)((lo >> 30) | ((hi >> 24) << 2));
-}
-__host__ __device__ __forceinline__ uint64_t pack_cloud(int x, int y, int d, int r, int g, int b, int hue) {
-    uint32_t lo = pack_xyd(x, y, d) | ((uint32_t)(hue & 3) << 30);
-    uint32_t hi = (uint32_t)r | ((uint32_t)g << 8) | ((uint32_t)b << 16) | ((uint32_t)(hue >> 2) << 24);
+__host__ __device__ __forceinline__ uint64_t pack_cloud(int x, int y, int d, int r, int g, int b) {
+    uint32_t lo = pack_xyd(x, y, d);
+    uint32_t hi = (uint32_t)r | ((uint32_t)g << 8) | ((uint32_t)b << 16);
     return (uint64_t)lo | ((uint64_t)hi << 32);
 }
 
@@ -94,9 +91,30 @@ static __device__ __noinline__ int exact_hue_bin(int r, int g, int b) {
 //   hn = (g-b) | 2*range + (b-r) | 4*range + (r-g)   (+ 6*range when negative),
 // a rational with denominator <= 1530.  The float64 sequence above carries a relative error of a
 // few 1e-16, so its rint() can differ from the exactly rounded rational only when the rational is an
-// exact tie k + 1/2 (any other value is at least 1/3060 away from a tie).  Integer quotient and
-// remainder give the bin; the rare exact ties (0.06 % of colours) take the float64 path, which
-// decides them the way the reference's roundings do.  tests: exhaustive over all 2^24 colours.
+// exact tie k + 1/2 (any other value is at least 1/3060 away from a tie).  Quotient and remainder come
+// from one multiply-high with a per-range reciprocal (exact: num * (m*den - 2^32) < 2^32 for every
+// num < 1000*1530).  Exact ties (0.375 % of all colours) land on 200 of the bins, and which way the
+// reference's float64 roundings push a tie depends on the bin alone -- correctly rounded division
+// gives (maxc-ch)/range the same double for every colour with the same ratio -- so one bit per bin,
+// taken from exact_hue_bin() / the reference over all 2^24 colours, decides them.
+// tests: exhaustive over all 2^24 colours against the oracle (test_hue_bins_exhaustive).
+struct HueMagic { uint32_t m[256]; };
+constexpr HueMagic make_hue_magic() {
+    HueMagic t{};
+    for (int r = 1; r < 256; ++r) {
+        unsigned long long den = 6ull * (unsigned long long)r;
+        t.m[r] = (uint32_t)(((1ull << 32) + den - 1ull) / den);       // ceil(2^32 / (6*range))
+    }
+    return t;
+}
+__device__ const HueMagic d_hue_magic = make_hue_magic();
+// bit q set: a tie at q + 1/2 goes to q + 1 under the reference's roundings, clear: stays at q
+__constant__ uint32_t c_hue_tie_up[32] = {
+    0x08400084u, 0x00008020u, 0x00802108u, 0x80200800u, 0x20080000u, 0x08421000u, 0x02008020u, 0x00040008u,
+    0x80200802u, 0x20000200u, 0x08000000u, 0x02008021u, 0x10800008u, 0x84200842u, 0x20080200u, 0x00020080u,
+    0x02108021u, 0x00802108u, 0x00200802u, 0x20080200u, 0x08020084u, 0x02008000u, 0x00800008u, 0x84200800u,
+    0x20084200u, 0x08020084u, 0x02008020u, 0x00802000u, 0x80200802u, 0x20080200u, 0x08020080u, 0x00000020u};
+
 __device__ __forceinline__ int hue_bin(int r, int g, int b) {
     int maxc = max(r, max(g, b));
     int minc = min(r, min(g, b));
@@ -106,14 +124,14 @@ __device__ __forceinline__ int hue_bin(int r, int g, int b) {
     uint32_t den = 6u * (uint32_t)range;
     if (hn < 0) hn += (int)den;
     uint32_t num = 1000u * (uint32_t)hn;                       // < 6000*255
-    // num / den (num < 2^21, den <= 1530): float estimate, off by at most one, fixed with the remainder
-    uint32_t q = __float2uint_rz(__fmul_rn((float)num, __frcp_rn((float)den)));
-    int rem = (int)num - (int)(q * den);
-    if (rem < 0) { --q; rem += (int)den; }
-    else if (rem >= (int)den) { ++q; rem -= (int)den; }
-    uint32_t twice = 2u * (uint32_t)rem;
-    if (twice == den) return exact_hue_bin(r, g, b);           // exact tie: let the float64 roundings decide
+    uint32_t q = __umulhi(num, __ldg(&d_hue_magic.m[range]));  // floor(num / den)
+    uint32_t twice = 2u * (num - q * den);
+    if (twice == den) return (int)(q + ((c_hue_tie_up[q >> 5] >> (q & 31)) & 1u));
     return (int)(q + (twice > den ? 1u : 0u));
+}
+// hue bin of a cloud record's colour word  R | G << 8 | B << 16
+__device__ __forceinline__ int hue_of_hi(uint32_t hi) {
+    return hue_bin((int)(hi & 0xFFu), (int)((hi >> 8) & 0xFFu), (int)((hi >> 16) & 0xFFu));
 }
 
 // ------------------------------------------------------------------ warp helpers

@@ -6,9 +6,9 @@
 // BGR bytes (three 128-bit loads), and turns them into a 16-bit "valid" and a 16-bit "masked
 // valid" bitmap.  Threads of a block are laid out row-major over a group of lattice rows, so an
 // exclusive block scan of the popcounts gives every site its rank in the reference's append order.
-// Records are compacted into shared memory first and leave the SM as fully coalesced 8-byte (cloud)
-// and 4-byte (mcloud) stores; the hue bin is computed in that copy-out loop, where consecutive
-// lanes hold consecutive *valid* points and no lane idles on a hole.
+// Records are compacted into (swizzled) shared memory first and leave the SM as fully coalesced 8-byte
+// (cloud) and 4-byte (mcloud) stores.  The hue bin is not stored: only the near-plane points need it
+// (functions.py:215-230), so the road kernels compute it from the record's colour word.
 #include "svb_common.cuh"
 #include "svb_prof.cuh"
 
@@ -158,7 +158,7 @@ static ProjGeom make_geom(int H, int W, int step, bool aligned) {
     g.rpb = PROJ_THREADS / g.cpr;
     if (g.rpb < 1) g.rpb = 1;
     g.groups = (g.LH + g.rpb - 1) / g.rpb;
-    g.cap = g.rpb * g.cpr * ((CHUNK + step - 1) / step);
+    g.cap = (g.rpb * g.cpr * ((CHUNK + step - 1) / step) + 31) & ~31;      // multiple of 32: the staging swizzles
     g.vec_ok = (W % CHUNK == 0) && aligned;
     return g;
 }
@@ -315,14 +315,47 @@ __global__ void proj_scan_kernel(uint32_t *__restrict__ group_counts, int groups
 }
 
 // pass 3: write the records
-template <bool HAS_MASK, bool HAS_RGB>
+// Shared-memory staging is swizzled: a thread appends a run of up to CHUNK/step records, so without
+// it the lanes of a warp would hit the same two (8-byte list) or four (4-byte list) bank groups.
+__device__ __forceinline__ int swz8(int p) { return p ^ ((p >> 4) & 15); }      // 8-byte slots, 16 per bank row
+__device__ __forceinline__ int swz4(int p) { return p ^ ((p >> 5) & 31); }      // 4-byte slots, 32 per bank row
+
+// colour word R | G << 8 | B << 16 of pixel J of a chunk whose 48 BGR bytes sit in px[12]
+template <int J>
+__device__ __forceinline__ uint32_t colour_of(const uint32_t *px) {
+    constexpr int b0 = 3 * J, w = b0 >> 2, o = b0 & 3;            // B at byte b0, G at b0+1, R at b0+2
+    constexpr int w1 = w + 1 < 12 ? w + 1 : 11;
+    if constexpr (o == 0) return __byte_perm(px[w], 0u, 0x4012);                       // (0, B, G, R) <- bytes 2,1,0
+    else if constexpr (o == 1) return __byte_perm(px[w], 0u, 0x4123);
+    else if constexpr (o == 2) return __byte_perm(px[w], px[w1], 0x0234) & 0x00FFFFFFu;   // R = byte 0 of the next word
+    else return __byte_perm(px[w], px[w1], 0x0345) & 0x00FFFFFFu;                      // G, R = bytes 0, 1 of the next word
+}
+
+template <int STEP, bool HAS_MASK, bool HAS_RGB, int J>
+__device__ __forceinline__ void emit_site(const ChunkBits &c, const uint32_t *px, uint32_t base_lo,
+                                          uint64_t *s_cloud, uint32_t *s_m, int &ov, int &om) {
+    if (c.vm & (1u << J)) {
+        uint32_t d = (c.d[J >> 2] >> ((J & 3) * 8)) & 0xFFu;
+        uint32_t lo = base_lo + (uint32_t)J + (d << 22);         // x0 + J never carries into y (x0 + 15 < 2048)
+        uint32_t hi = HAS_RGB ? colour_of<J>(px) : 0u;
+        s_cloud[swz8(ov)] = (uint64_t)lo | ((uint64_t)hi << 32);
+        ++ov;
+        if (HAS_MASK) {
+            if (c.mm & (1u << J)) { s_m[swz4(om)] = lo; ++om; }
+        } else {
+            s_m[swz4(om)] = lo; ++om;
+        }
+    }
+}
+
+template <int STEP, bool HAS_MASK, bool HAS_RGB>
 __global__ void __launch_bounds__(PROJ_THREADS)
 proj_write_kernel(const uint8_t *__restrict__ disp, const uint8_t *__restrict__ carmask,
                   const uint8_t *__restrict__ bgr, ProjGeom g, const uint32_t *__restrict__ group_offsets,
                   int64_t plane_stride, uint64_t *__restrict__ cloud, uint32_t *__restrict__ mcloud) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ uint32_t warp_tot[PROJ_THREADS / 32];
-    const int cap = g.cap;                                       // sites a block can hold
+    const int cap = g.cap;                                       // sites a block can hold (multiple of 32)
     uint64_t *s_cloud = (uint64_t *)smem_raw;                    // [cap]
     uint32_t *s_m = (uint32_t *)(smem_raw + (size_t)cap * 8);    // [cap]
 
@@ -333,11 +366,32 @@ proj_write_kernel(const uint8_t *__restrict__ disp, const uint8_t *__restrict__ 
     c.vm = c.mm = 0;
     int y = 0, x0 = ch * CHUNK;
     bool active = (r < g.rpb && ly < g.LH);
+    uint32_t px[12];                                             // 48 BGR bytes of the chunk
     if (active) {
         y = ly * g.step;
         const uint8_t *drow = disp + ((int64_t)f * g.H + y) * g.W;
         const uint8_t *mrow = HAS_MASK ? carmask + (int64_t)y * g.W : nullptr;
+        if (HAS_RGB && g.vec_ok) {                               // issue the colour loads together with d / mask
+            const uint4 *q = (const uint4 *)(bgr + (((int64_t)f * g.H + y) * g.W + x0) * 3);
+            uint4 a = __ldcs(q), b = __ldcs(q + 1), d = __ldcs(q + 2);
+            px[0] = a.x; px[1] = a.y; px[2] = a.z; px[3] = a.w;
+            px[4] = b.x; px[5] = b.y; px[6] = b.z; px[7] = b.w;
+            px[8] = d.x; px[9] = d.y; px[10] = d.z; px[11] = d.w;
+        }
         c = load_chunk<HAS_MASK>(drow, mrow, x0, g.W, g.step, g.vec_ok);
+        if (HAS_RGB && !g.vec_ok) {
+            const uint8_t *crow = bgr + (((int64_t)f * g.H + y) * g.W + x0) * 3;
+#pragma unroll
+            for (int w = 0; w < 12; ++w) {
+                uint32_t v = 0;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    int bi = w * 4 + k;
+                    if (x0 + bi / 3 < g.W) v |= (uint32_t)crow[bi] << (k * 8);
+                }
+                px[w] = v;
+            }
+        }
     }
     uint32_t cnt = (uint32_t)__popc(c.vm) | ((uint32_t)__popc(c.mm) << 16);
     uint32_t total;
@@ -346,42 +400,15 @@ proj_write_kernel(const uint8_t *__restrict__ disp, const uint8_t *__restrict__ 
     int tv = (int)(total & 0xFFFFu), tm = (int)(total >> 16);
 
     if (c.vm) {
-        uint32_t px[12];                                         // 48 BGR bytes of the chunk
-        if (HAS_RGB) {
-            const uint8_t *crow = bgr + (((int64_t)f * g.H + y) * g.W + x0) * 3;
-            if (g.vec_ok) {
-                const uint4 *q = (const uint4 *)crow;
-                uint4 a = __ldg(q), b = __ldg(q + 1), d = __ldg(q + 2);
-                px[0] = a.x; px[1] = a.y; px[2] = a.z; px[3] = a.w;
-                px[4] = b.x; px[5] = b.y; px[6] = b.z; px[7] = b.w;
-                px[8] = d.x; px[9] = d.y; px[10] = d.z; px[11] = d.w;
-            } else {
-#pragma unroll
-                for (int w = 0; w < 12; ++w) {
-                    uint32_t v = 0;
-#pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        int bi = w * 4 + k;
-                        if (x0 + bi / 3 < g.W) v |= (uint32_t)crow[bi] << (k * 8);
-                    }
-                    px[w] = v;
-                }
-            }
+        const uint32_t base_lo = pack_xyd(x0, y, 0);
+#define SITE(J) emit_site<STEP, HAS_MASK, HAS_RGB, J>(c, px, base_lo, s_cloud, s_m, ov, om)
+        if (STEP == 2) {                                         // only even pixels are lattice sites
+            SITE(0); SITE(2); SITE(4); SITE(6); SITE(8); SITE(10); SITE(12); SITE(14);
+        } else {
+            SITE(0); SITE(1); SITE(2); SITE(3); SITE(4); SITE(5); SITE(6); SITE(7);
+            SITE(8); SITE(9); SITE(10); SITE(11); SITE(12); SITE(13); SITE(14); SITE(15);
         }
-#pragma unroll
-        for (int j = 0; j < CHUNK; ++j) {
-            if (c.vm & (1u << j)) {
-                int d = (int)byte_of(c.d, j);
-                uint32_t lo = pack_xyd(x0 + j, y, d);
-                uint32_t hi = 0;
-                if (HAS_RGB) {
-                    uint32_t bb = byte_of(px, 3 * j), gg = byte_of(px, 3 * j + 1), rr = byte_of(px, 3 * j + 2);
-                    hi = rr | (gg << 8) | (bb << 16);            // R,G,B = bgr[..,2],[..,1],[..,0]
-                }
-                s_cloud[ov++] = (uint64_t)lo | ((uint64_t)hi << 32);
-                if (c.mm & (1u << j)) s_m[om++] = lo;
-            }
-        }
+#undef SITE
     }
     __syncthreads();
 
@@ -390,19 +417,11 @@ proj_write_kernel(const uint8_t *__restrict__ disp, const uint8_t *__restrict__ 
     int64_t slab = (int64_t)f * g.LH * g.LW;
     if (cloud) {
         uint64_t *dst = cloud + slab + offs_v[grp];
-        for (int i = threadIdx.x; i < tv; i += PROJ_THREADS) {
-            uint64_t rec = s_cloud[i];
-            if (HAS_RGB) {
-                uint32_t hi = (uint32_t)(rec >> 32);
-                int hue = hue_bin((int)(hi & 0xFF), (int)((hi >> 8) & 0xFF), (int)((hi >> 16) & 0xFF));
-                rec |= ((uint64_t)(hue & 3) << 30) | ((uint64_t)(hue >> 2) << 56);
-            }
-            dst[i] = rec;
-        }
+        for (int i = threadIdx.x; i < tv; i += PROJ_THREADS) __stcs((unsigned long long *)dst + i, (unsigned long long)s_cloud[swz8(i)]);
     }
     if (mcloud) {
         uint32_t *dst = mcloud + slab + offs_m[grp];
-        for (int i = threadIdx.x; i < tm; i += PROJ_THREADS) dst[i] = s_m[i];
+        for (int i = threadIdx.x; i < tm; i += PROJ_THREADS) dst[i] = s_m[swz4(i)];
     }
 }
 
@@ -443,17 +462,22 @@ extern "C" int svb_project_compact(const uint8_t *disp, const uint8_t *carmask, 
     if (!cloud && !mcloud) return SVB_OK;
     size_t smem = (size_t)g.cap * 12;
     int64_t plane = (int64_t)F * g.groups;
-#define LAUNCH_W(M, R)                                                                              \
+#define LAUNCH_W(S, M, R)                                                                           \
     do {                                                                                            \
         if (smem + 256 > 48 * 1024)                                                                 \
-            cudaFuncSetAttribute(proj_write_kernel<M, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
-        proj_write_kernel<M, R><<<grid, PROJ_THREADS, smem, st>>>(disp, carmask, bgr, g, gc, plane, cloud, mcloud); \
+            cudaFuncSetAttribute(proj_write_kernel<S, M, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+        proj_write_kernel<S, M, R><<<grid, PROJ_THREADS, smem, st>>>(disp, carmask, bgr, g, gc, plane, cloud, mcloud); \
+    } while (0)
+#define LAUNCH_WS(S)                                                                                \
+    do {                                                                                            \
+        if (carmask) { if (bgr) LAUNCH_W(S, true, true); else LAUNCH_W(S, true, false); }           \
+        else         { if (bgr) LAUNCH_W(S, false, true); else LAUNCH_W(S, false, false); }         \
     } while (0)
     {
         ProfScope ps(K_PROJ_WRITE, st);
-        if (carmask) { if (bgr) LAUNCH_W(true, true); else LAUNCH_W(true, false); }
-        else         { if (bgr) LAUNCH_W(false, true); else LAUNCH_W(false, false); }
+        if (step == 2) LAUNCH_WS(2); else LAUNCH_WS(0);
     }
+#undef LAUNCH_WS
 #undef LAUNCH_W
     SVB_LAUNCH_CHECK();
     return SVB_OK;
@@ -482,7 +506,7 @@ __global__ void cloud_export_kernel(const uint32_t *__restrict__ rec, int stride
     }
     if (sites) { sites[2 * (int64_t)i] = y; sites[2 * (int64_t)i + 1] = x; }
     if (dout) dout[i] = (uint8_t)d;
-    if (hue) hue[i] = (uint16_t)rec_hue(lo, hi);
+    if (hue) hue[i] = (uint16_t)hue_of_hi(hi);
 }
 
 extern "C" int svb_cloud_export(const uint32_t *records, int rec_stride_words, int n, const svb_camera *cam,

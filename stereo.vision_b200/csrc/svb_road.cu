@@ -55,7 +55,7 @@ __device__ __forceinline__ bool keep_flag(int mode, const uint64_t *__restrict__
                                           const uint32_t *__restrict__ hist, double thr, uint32_t uthr, int i) {
     if (mode == 0) return dist[i] < thr;                         // differences[i] < threshold, :321
     uint64_t r = cloud[i];
-    return hist[rec_hue((uint32_t)r, (uint32_t)(r >> 32))] > uthr;   // histogram[key] > threshold, :230
+    return hist[hue_of_hi((uint32_t)(r >> 32))] > uthr;   // histogram[key] > threshold, :230
 }
 
 __global__ void compact_count_kernel(const uint64_t *__restrict__ cloud, int n, int mode, const double *__restrict__ dist,
@@ -165,7 +165,7 @@ hue_hist_kernel(const uint64_t *__restrict__ cloud, int n, uint32_t *__restrict_
     __syncthreads();
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         uint64_t r = cloud[i];
-        atomicAdd(&s_h[rec_hue((uint32_t)r, (uint32_t)(r >> 32))], 1u);
+        atomicAdd(&s_h[hue_of_hi((uint32_t)(r >> 32))], 1u);
     }
     __syncthreads();
     for (int k = threadIdx.x; k < SVB_HUE_BINS; k += blockDim.x)
@@ -390,7 +390,7 @@ road_pass1_kernel(const uint64_t *__restrict__ cloud, const int32_t *__restrict_
             double band = 1e-11 * fma(Z, fabs(p) + fabs(q) + fabs(c), 1.0);
             if (fabs(est - cutoff) > band) near = est < cutoff;
             else near = exact_near(cam, lo, Z, a, b, c, cutoff);
-            if (near) atomicAdd(&s_h[rec_hue(lo, hi)], 1u);
+            if (near) atomicAdd(&s_h[hue_of_hi(hi)], 1u);
         }
         uint32_t bal = __ballot_sync(0xffffffffu, near);
         if ((threadIdx.x & 31) == 0) {
@@ -440,7 +440,7 @@ road_pass2_kernel(const uint64_t *__restrict__ cloud, const int32_t *__restrict_
         if ((word >> lane) & 1u) {
             uint64_t r = __ldcs((const unsigned long long *)(rec + i0 + lane));
             uint32_t lo = (uint32_t)r, hi = (uint32_t)(r >> 32);
-            if (s_h[rec_hue(lo, hi)] > colour_threshold) {
+            if (s_h[hue_of_hi(hi)] > colour_threshold) {
                 keep = true;
                 int x = rec_x(lo), y = rec_y(lo), d = rec_d(lo), px, py;
                 if (TABLE) {
@@ -473,17 +473,26 @@ road_pass2_kernel(const uint64_t *__restrict__ cloud, const int32_t *__restrict_
 // ------------------------------------------------------------------ the fused road kernel (clusters + DSMEM)
 // One thread-block CLUSTER of 8 CTAs owns one frame; CTA r owns the r-th eighth of the frame's records.
 //   A  clear this CTA's eighth of the road mask (replaces a memset launch)
-//   B  stream the records once (128-bit loads, 8 records in flight per thread): filtered near-plane
-//      test; a near point is reprojected through the displacement-bit table and appended to a list
-//      in SHARED memory as one word  px | py<<11 | hue<<22 ; its hue bin is counted in a shared histogram
+//   B  stream the records once (128-bit loads, the next round's loads in flight while this round is
+//      tested): filtered near-plane test; a near point gets its hue bin (counted in a shared-memory
+//      histogram), is reprojected through the displacement-bit table and kept as one word
+//      px | py<<11 | hue<<22 in a list in SHARED memory.  The list is private per thread (slot-major,
+//      conflict-free, no ballots or atomics): the order of the near points is not an observable.
 //      -- cluster barrier --
 //   C  every CTA sums the 8 partial histograms straight out of its peers' shared memory (DSMEM)
-//      -- cluster barrier --   (peers may not exit while their shared memory is being read)
-//   D  colour filter over the CTA's own near list, 255 into the mask.
+//      -- cluster barrier arrive (peers may not exit while their shared memory is being read) --
+//   D  colour filter over the thread's own near list, 255 into the mask
+//      -- cluster barrier wait --
 // The records are read from HBM exactly once and the near list never leaves the SM.
 #define RC_THREADS 512
 #define RC_PARTS 8
-#define RC_U 2                    // 128-bit loads in flight per thread (2 records each)
+#define RC_PER_ROUND 4            // records per thread per round: two 128-bit loads of 2 records each
+#define RC_ROUND (RC_THREADS * RC_PER_ROUND)
+
+__device__ __forceinline__ void cluster_arrive() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
+__device__ __forceinline__ void cluster_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
+// int -> double without the conversion instruction: 2^52 + x has x in its low mantissa bits
+__device__ __forceinline__ double road_u2d(uint32_t x) { return __hiloint2double(0x43300000, (int)x) - 4503599627370496.0; }
 
 template <bool OVERLAY>
 __global__ void __launch_bounds__(RC_THREADS, 2)
@@ -491,12 +500,11 @@ road_cluster_kernel(const uint64_t *__restrict__ cloud, const int32_t *__restric
                     const double *__restrict__ planes, RoadGeom g, CamD cam, uint32_t colour_threshold,
                     const uint32_t *__restrict__ rbits, uint32_t *__restrict__ hist,
                     uint8_t *__restrict__ road_mask, uint8_t *__restrict__ overlay, int32_t *__restrict__ counts_out) {
-    extern __shared__ __align__(16) uint32_t s_list[];
+    extern __shared__ __align__(16) uint32_t s_list[];           // [slots][RC_THREADS]
     __shared__ uint32_t s_h[SVB_HIST_STRIDE];
     __shared__ uint32_t s_tot[SVB_HIST_STRIDE];
     __shared__ double s_Z[256];
-    __shared__ uint32_t s_n;
-    __shared__ int s_r;
+    __shared__ int s_k, s_r;
     cg::cluster_group cluster = cg::this_cluster();
     const int rank = (int)cluster.block_rank();
     const int f = blockIdx.x / RC_PARTS;
@@ -504,6 +512,30 @@ road_cluster_kernel(const uint64_t *__restrict__ cloud, const int32_t *__restric
     const int n = counts[f * 4 + 0];
     const double *pl = planes + (int64_t)f * SVB_PLANE_STRIDE;
     const bool valid = pl[7] != 0.0 && n > 0;
+
+    // records of this CTA, and the first round's loads (issued before anything else)
+    const uint64_t *rec = cloud + (int64_t)f * g.slab;
+    const int part = (((n + RC_PARTS - 1) / RC_PARTS) + 1) & ~1;  // even, so 128-bit loads stay aligned
+    const int begin = min(n, rank * part), end = min(n, begin + part);
+    const bool vec = ((((uintptr_t)rec) & 15) == 0);
+    const int toff = (tid >> 5) * 128 + lane * 2;                 // warp w covers [128 w, 128 w + 128) of a round
+    uint64_t nx[RC_PER_ROUND];
+    auto load_round = [&](int i0) {
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+            int i = i0 + toff + u * 64;
+            nx[2 * u] = nx[2 * u + 1] = 0;
+            if (vec && i + 1 < end) {
+                uint4 v = __ldcs((const uint4 *)(rec + i));
+                nx[2 * u] = (uint64_t)v.x | ((uint64_t)v.y << 32);
+                nx[2 * u + 1] = (uint64_t)v.z | ((uint64_t)v.w << 32);
+            } else {
+                if (i < end) nx[2 * u] = __ldcs((const unsigned long long *)(rec + i));
+                if (i + 1 < end) nx[2 * u + 1] = __ldcs((const unsigned long long *)(rec + i + 1));
+            }
+        }
+    };
+    if (valid) load_round(begin);
 
     // A: clear my eighth of the mask (and zero the frame's histogram when there is nothing to do)
     {
@@ -526,65 +558,50 @@ road_cluster_kernel(const uint64_t *__restrict__ cloud, const int32_t *__restric
     }
     for (int k = tid; k < SVB_HIST_STRIDE; k += RC_THREADS) s_h[k] = 0;
     if (tid < 256) s_Z[tid] = tid ? exact_Z(cam, tid) : 0.0;
-    if (tid == 0) { s_n = 0; s_r = 0; }
+    if (tid == 0) { s_k = 0; s_r = 0; }
     __syncthreads();
 
-    // B: my part of the records
-    const double a = pl[0], b = pl[1], c = pl[2], cutoff = pl[4];
-    const double af = a / cam.f, bf = b / cam.f;
-    const uint64_t *rec = cloud + (int64_t)f * g.slab;
-    const int part = (((n + RC_PARTS - 1) / RC_PARTS) + 1) & ~1;  // even, so 128-bit loads stay aligned
-    const int begin = min(n, rank * part), end = min(n, begin + part);
-    const bool vec = ((((uintptr_t)rec) & 15) == 0);
-    for (int i0 = begin + (tid & ~31) * (2 * RC_U); i0 < end; i0 += RC_THREADS * 2 * RC_U) {
-        // this warp covers records [i0, i0 + 64*RC_U): RC_U rounds of 64, lane takes 2 adjacent records per round
-        uint64_t r[2 * RC_U];
+    // B: my part of the records.  Estimate e = |Z (af x + bf y + c2) - 1| (4 flops); it decides unless it
+    // lands within `band` (~1e5 x the worst-case rounding difference to the reference's operation
+    // sequence, bounded once per frame) of the cutoff; then the exact sequence decides.
+    double af, bf, c2, cut_lo, cut_hi;
+    {
+        const double a = pl[0], b = pl[1], c = pl[2], cutoff = pl[4];
+        af = a / cam.f; bf = b / cam.f;
+        c2 = c - af * cam.cw - bf * cam.ch;
+        const double band = 1e-11 * fma(s_Z[1], fabs(af) * (double)(g.W + cam.cw) + fabs(bf) * (double)(g.H + cam.ch) + fabs(c) + fabs(c2), 1.0);
+        cut_lo = cutoff - band; cut_hi = cutoff + band;
+    }
+    int cnt = 0;
+    for (int i0 = begin; i0 < end; i0 += RC_ROUND) {
+        uint64_t r[RC_PER_ROUND];
 #pragma unroll
-        for (int u = 0; u < RC_U; ++u) {
-            int i = i0 + u * 64 + lane * 2;
-            r[2 * u] = r[2 * u + 1] = 0;
-            if (vec && i + 1 < end) {
-                uint4 v = __ldcs((const uint4 *)(rec + i));
-                r[2 * u] = (uint64_t)v.x | ((uint64_t)v.y << 32);
-                r[2 * u + 1] = (uint64_t)v.z | ((uint64_t)v.w << 32);
-            } else {
-                if (i < end) r[2 * u] = __ldcs((const unsigned long long *)(rec + i));
-                if (i + 1 < end) r[2 * u + 1] = __ldcs((const unsigned long long *)(rec + i + 1));
-            }
-        }
+        for (int k = 0; k < RC_PER_ROUND; ++k) r[k] = nx[k];
+        if (i0 + RC_ROUND < end) load_round(i0 + RC_ROUND);
 #pragma unroll
-        for (int k = 0; k < 2 * RC_U; ++k) {
-            int i = i0 + (k >> 1) * 64 + lane * 2 + (k & 1);
-            bool near = false;
-            uint32_t word = 0;
+        for (int k = 0; k < RC_PER_ROUND; ++k) {
+            const int i = i0 + toff + (k >> 1) * 64 + (k & 1);
             if (i < end) {
-                uint32_t lo = (uint32_t)r[k], hi = (uint32_t)(r[k] >> 32);
-                int x = rec_x(lo), y = rec_y(lo), d = rec_d(lo);
-                double Z = s_Z[d];
-                double p = af * ((double)x - cam.cw), q = bf * ((double)y - cam.ch);
-                double est = fabs(fma(Z, p + q + c, -1.0));
-                double band = 1e-11 * fma(Z, fabs(p) + fabs(q) + fabs(c), 1.0);
-                if (fabs(est - cutoff) > band) near = est < cutoff;
-                else near = exact_near(cam, lo, Z, a, b, c, cutoff);
+                const uint32_t lo = (uint32_t)r[k], hi = (uint32_t)(r[k] >> 32);
+                const uint32_t x = lo & 0x7FFu, y = (lo >> 11) & 0x7FFu, d = (lo >> 22) & 0xFFu;
+                const double Z = s_Z[d];
+                const double e = fabs(fma(Z, fma(af, road_u2d(x), fma(bf, road_u2d(y), c2)), -1.0));
+                bool near = e < cut_lo;
+                if (!near && e < cut_hi) near = exact_near(cam, lo, Z, pl[0], pl[1], pl[2], pl[4]);   // rare
                 if (near) {
-                    int hue = rec_hue(lo, hi);
+                    const uint32_t hue = (uint32_t)hue_of_hi(hi);
                     atomicAdd(&s_h[hue], 1u);
-                    int px = x - (int)((__ldg(rbits + x * 8 + (d >> 5)) >> (d & 31)) & 1u);
-                    int py = y - (int)((__ldg(rbits + (g.W + y) * 8 + (d >> 5)) >> (d & 31)) & 1u);
-                    word = (uint32_t)px | ((uint32_t)py << 11) | ((uint32_t)hue << 22);
+                    const uint32_t px = x - ((__ldg(rbits + x * 8 + (d >> 5)) >> (d & 31)) & 1u);
+                    const uint32_t py = y - ((__ldg(rbits + (g.W + y) * 8 + (d >> 5)) >> (d & 31)) & 1u);
+                    s_list[cnt * RC_THREADS + tid] = (px & 0x7FFu) | ((py & 0x7FFu) << 11) | (hue << 22);
+                    ++cnt;
                 }
-            }
-            uint32_t bal = __ballot_sync(0xffffffffu, near);
-            if (bal) {
-                uint32_t base = 0;
-                if (lane == 0) base = atomicAdd(&s_n, (uint32_t)__popc(bal));
-                base = __shfl_sync(0xffffffffu, base, 0);
-                if (near) s_list[base + __popc(bal & ((1u << lane) - 1u))] = word;
             }
         }
     }
     __syncthreads();
-    cluster.sync();
+    cluster_arrive();
+    cluster_wait();
 
     // C: full histogram = sum of the 8 partial ones, read through distributed shared memory
     for (int k = tid; k < SVB_HIST_STRIDE; k += RC_THREADS) {
@@ -594,15 +611,15 @@ road_cluster_kernel(const uint64_t *__restrict__ cloud, const int32_t *__restric
         s_tot[k] = t;
         if (rank == 0) hist[(int64_t)f * SVB_HIST_STRIDE + k] = t;
     }
-    cluster.sync();
+    __syncthreads();
+    cluster_arrive();
 
     // D: colour filter + scatter of my near list
     uint8_t *mask = road_mask + (int64_t)f * g.H * g.W;
     uint8_t *ovl = OVERLAY ? overlay + (int64_t)f * g.H * g.W * 3 : nullptr;
-    const uint32_t nn = s_n;
     int rcount = 0;
-    for (uint32_t k = tid; k < nn; k += RC_THREADS) {
-        uint32_t w = s_list[k];
+    for (int k = 0; k < cnt; ++k) {
+        uint32_t w = s_list[k * RC_THREADS + tid];
         if (s_tot[w >> 22] > colour_threshold) {
             ++rcount;
             int px = (int)(w & 0x7FFu), py = (int)((w >> 11) & 0x7FFu);
@@ -615,14 +632,22 @@ road_cluster_kernel(const uint64_t *__restrict__ cloud, const int32_t *__restric
             }
         }
     }
+    int kcount = cnt;
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) rcount += __shfl_xor_sync(0xffffffffu, rcount, o);
-    if (lane == 0 && rcount) atomicAdd(&s_r, rcount);
+    for (int o = 16; o > 0; o >>= 1) {
+        rcount += __shfl_xor_sync(0xffffffffu, rcount, o);
+        kcount += __shfl_xor_sync(0xffffffffu, kcount, o);
+    }
+    if (lane == 0) {
+        if (kcount) atomicAdd(&s_k, kcount);
+        if (rcount) atomicAdd(&s_r, rcount);
+    }
     __syncthreads();
     if (tid == 0) {
-        if (nn) atomicAdd(&counts_out[f * 4 + 2], (int)nn);
+        if (s_k) atomicAdd(&counts_out[f * 4 + 2], s_k);
         if (s_r) atomicAdd(&counts_out[f * 4 + 3], s_r);
     }
+    cluster_wait();
 }
 
 extern "C" int64_t svb_road_scratch_bytes(int F, int H, int W, int step) {
@@ -643,7 +668,8 @@ extern "C" int svb_road_points(const uint64_t *cloud, const int32_t *counts, con
     RoadGeom g = make_road_geom(H, W, step);
     CamD c = make_camd(cam);
     // fused cluster kernel when the displacement table is given and a CTA's near list fits in shared memory
-    const int64_t list_cap = ((g.slab + RC_PARTS - 1) / RC_PARTS + 2 + 255) & ~(int64_t)255;
+    const int64_t part_max = (g.slab + RC_PARTS - 1) / RC_PARTS + 2;             // records of one CTA, at most
+    const int64_t list_cap = (part_max + RC_ROUND - 1) / RC_ROUND * RC_ROUND;   // RC_PER_ROUND slots per round per thread
     const size_t list_bytes = (size_t)list_cap * sizeof(uint32_t);
     const bool mask_no_wrap = (H <= 2048 && W <= 2048);
     if (reproj_bits && mask_no_wrap && list_bytes <= 160 * 1024 && !g_svb_force_two_pass) {

@@ -6,7 +6,7 @@ import stereo.vision_b200.synth as synth
 
 
 def decode_cloud(rec_i64: np.ndarray):
-    """uint64 records (as int64) -> dict(x, y, d, rgb [n,3], hue)."""
+    """uint64 records (as int64) -> dict(x, y, d, rgb [n,3])."""
     r = rec_i64.astype(np.uint64)
     lo = (r & np.uint64(0xFFFFFFFF)).astype(np.uint32)
     hi = (r >> np.uint64(32)).astype(np.uint32)
@@ -14,7 +14,7 @@ def decode_cloud(rec_i64: np.ndarray):
         "x": (lo & 0x7FF).astype(np.int32), "y": ((lo >> 11) & 0x7FF).astype(np.int32),
         "d": ((lo >> 22) & 0xFF).astype(np.uint8),
         "rgb": np.stack([hi & 0xFF, (hi >> 8) & 0xFF, (hi >> 16) & 0xFF], axis=1).astype(np.uint8),
-        "hue": ((lo >> 30) | ((hi >> 24) << 2)).astype(np.int32),
+        "spare": ((lo >> 30) | ((hi >> 24) << 2)).astype(np.int32),      # unused record bits, must be 0
     }
 
 
@@ -46,7 +46,7 @@ def check_frame(res, t, o, abc_rtol=1e-9):
     assert np.array_equal(g["y"], c["sites"][:, 0]) and np.array_equal(g["x"], c["sites"][:, 1]), "cloud order"
     assert np.array_equal(g["d"], c["d"]), "cloud d"
     assert np.array_equal(g["rgb"], c["rgb"]), "cloud rgb"
-    assert np.array_equal(g["hue"], no.hue_bin(c["rgb"][:, 0], c["rgb"][:, 1], c["rgb"][:, 2])), "hue bins"
+    assert not g["spare"].any(), "spare record bits"
     gm = decode_mcloud(res["mcloud"][t][:M])
     assert np.array_equal(gm["y"], mc["sites"][:, 0]) and np.array_equal(gm["x"], mc["sites"][:, 1]), "mcloud order"
     assert np.array_equal(gm["d"], mc["d"]), "mcloud d"
