@@ -488,6 +488,7 @@ road_pass2_kernel(const uint64_t *__restrict__ cloud, const int32_t *__restrict_
 #define RC_PARTS 8
 #define RC_PER_ROUND 4            // records per thread per round: two 128-bit loads of 2 records each
 #define RC_ROUND (RC_THREADS * RC_PER_ROUND)
+#define RC_WARPS (RC_THREADS / 32)
 
 __device__ __forceinline__ void cluster_arrive() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
 __device__ __forceinline__ void cluster_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
@@ -499,8 +500,10 @@ __global__ void __launch_bounds__(RC_THREADS, 2)
 road_cluster_kernel(const uint64_t *__restrict__ cloud, const int32_t *__restrict__ counts,
                     const double *__restrict__ planes, RoadGeom g, CamD cam, uint32_t colour_threshold,
                     const uint32_t *__restrict__ rbits, uint32_t *__restrict__ hist,
-                    uint8_t *__restrict__ road_mask, uint8_t *__restrict__ overlay, int32_t *__restrict__ counts_out) {
-    extern __shared__ __align__(16) uint32_t s_list[];           // [slots][RC_THREADS]
+                    uint8_t *__restrict__ road_mask, uint8_t *__restrict__ overlay, int32_t *__restrict__ counts_out,
+                    int warp_cap) {
+    extern __shared__ __align__(16) uint32_t s_list[];           // [RC_WARPS][warp_cap]: near lists, one per warp
+    __shared__ uint64_t s_stage[RC_WARPS][64];                   // per-warp ring of near records awaiting the dense step
     __shared__ uint32_t s_h[SVB_HIST_STRIDE];
     __shared__ uint32_t s_tot[SVB_HIST_STRIDE];
     __shared__ double s_Z[256];
@@ -508,17 +511,18 @@ road_cluster_kernel(const uint64_t *__restrict__ cloud, const int32_t *__restric
     cg::cluster_group cluster = cg::this_cluster();
     const int rank = (int)cluster.block_rank();
     const int f = blockIdx.x / RC_PARTS;
-    const int tid = threadIdx.x, lane = tid & 31;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int n = counts[f * 4 + 0];
     const double *pl = planes + (int64_t)f * SVB_PLANE_STRIDE;
     const bool valid = pl[7] != 0.0 && n > 0;
 
-    // records of this CTA, and the first round's loads (issued before anything else)
+    // records of this CTA, and the first round's loads (issued before anything else).
+    // CTA r takes rounds r, r + 8, ... of RC_ROUND records each: the near points (the expensive ones) sit in
+    // the lower image rows, and a contiguous split would leave the CTAs of a cluster waiting for the last one
     const uint64_t *rec = cloud + (int64_t)f * g.slab;
-    const int part = (((n + RC_PARTS - 1) / RC_PARTS) + 1) & ~1;  // even, so 128-bit loads stay aligned
-    const int begin = min(n, rank * part), end = min(n, begin + part);
+    const int begin = rank * RC_ROUND, end = n;
     const bool vec = ((((uintptr_t)rec) & 15) == 0);
-    const int toff = (tid >> 5) * 128 + lane * 2;                 // warp w covers [128 w, 128 w + 128) of a round
+    const int toff = warp * 128 + lane * 2;                       // warp w covers [128 w, 128 w + 128) of a round
     uint64_t nx[RC_PER_ROUND];
     auto load_round = [&](int i0) {
 #pragma unroll
@@ -572,33 +576,55 @@ road_cluster_kernel(const uint64_t *__restrict__ cloud, const int32_t *__restric
         const double band = 1e-11 * fma(s_Z[1], fabs(af) * (double)(g.W + cam.cw) + fabs(bf) * (double)(g.H + cam.ch) + fabs(c) + fabs(c2), 1.0);
         cut_lo = cutoff - band; cut_hi = cutoff + band;
     }
-    int cnt = 0;
-    for (int i0 = begin; i0 < end; i0 += RC_ROUND) {
+    // The near points are scattered over the lanes (about a third of the records), so their expensive part
+    // -- hue bin, histogram, reprojection -- runs DENSE: near records are first compacted into the warp's
+    // ring (ballot + popc), and whenever 32 are waiting every lane takes one.
+    uint64_t *stage = s_stage[warp];
+    uint32_t *wlist = s_list + (size_t)warp * warp_cap;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    uint32_t fill = 0, head = 0;                                 // warp-uniform: records waiting, ring position
+    int wcnt = 0;                                                // warp-uniform: near points in the warp's list
+    auto dense = [&](uint64_t rc, bool on) {
+        if (on) {
+            const uint32_t lo = (uint32_t)rc, hi = (uint32_t)(rc >> 32);
+            const uint32_t x = lo & 0x7FFu, y = (lo >> 11) & 0x7FFu, d = (lo >> 22) & 0xFFu;
+            const uint32_t hue = (uint32_t)hue_of_hi(hi);
+            atomicAdd(&s_h[hue], 1u);
+            const uint32_t px = x - ((__ldg(rbits + x * 8 + (d >> 5)) >> (d & 31)) & 1u);
+            const uint32_t py = y - ((__ldg(rbits + (g.W + y) * 8 + (d >> 5)) >> (d & 31)) & 1u);
+            wlist[wcnt + lane] = (px & 0x7FFu) | ((py & 0x7FFu) << 11) | (hue << 22);
+        }
+    };
+    for (int i0 = begin; i0 < end; i0 += RC_PARTS * RC_ROUND) {
         uint64_t r[RC_PER_ROUND];
 #pragma unroll
         for (int k = 0; k < RC_PER_ROUND; ++k) r[k] = nx[k];
-        if (i0 + RC_ROUND < end) load_round(i0 + RC_ROUND);
+        if (i0 + RC_PARTS * RC_ROUND < end) load_round(i0 + RC_PARTS * RC_ROUND);
 #pragma unroll
         for (int k = 0; k < RC_PER_ROUND; ++k) {
             const int i = i0 + toff + (k >> 1) * 64 + (k & 1);
+            bool near = false;
             if (i < end) {
-                const uint32_t lo = (uint32_t)r[k], hi = (uint32_t)(r[k] >> 32);
-                const uint32_t x = lo & 0x7FFu, y = (lo >> 11) & 0x7FFu, d = (lo >> 22) & 0xFFu;
-                const double Z = s_Z[d];
-                const double e = fabs(fma(Z, fma(af, road_u2d(x), fma(bf, road_u2d(y), c2)), -1.0));
-                bool near = e < cut_lo;
+                const uint32_t lo = (uint32_t)r[k];
+                const double Z = s_Z[(lo >> 22) & 0xFFu];
+                const double e = fabs(fma(Z, fma(af, road_u2d(lo & 0x7FFu), fma(bf, road_u2d((lo >> 11) & 0x7FFu), c2)), -1.0));
+                near = e < cut_lo;
                 if (!near && e < cut_hi) near = exact_near(cam, lo, Z, pl[0], pl[1], pl[2], pl[4]);   // rare
-                if (near) {
-                    const uint32_t hue = (uint32_t)hue_of_hi(hi);
-                    atomicAdd(&s_h[hue], 1u);
-                    const uint32_t px = x - ((__ldg(rbits + x * 8 + (d >> 5)) >> (d & 31)) & 1u);
-                    const uint32_t py = y - ((__ldg(rbits + (g.W + y) * 8 + (d >> 5)) >> (d & 31)) & 1u);
-                    s_list[cnt * RC_THREADS + tid] = (px & 0x7FFu) | ((py & 0x7FFu) << 11) | (hue << 22);
-                    ++cnt;
-                }
+            }
+            const uint32_t bal = __ballot_sync(0xffffffffu, near);
+            if (near) stage[(head + fill + __popc(bal & lt_mask)) & 63u] = r[k];
+            fill += __popc(bal);
+            if (fill >= 32u) {
+                __syncwarp();
+                dense(stage[(head + lane) & 63u], true);
+                wcnt += 32; head += 32u; fill -= 32u;
+                __syncwarp();
             }
         }
     }
+    __syncwarp();
+    if (fill) dense(stage[(head + lane) & 63u], (uint32_t)lane < fill);
+    wcnt += (int)fill;
     __syncthreads();
     cluster_arrive();
     cluster_wait();
@@ -614,12 +640,12 @@ road_cluster_kernel(const uint64_t *__restrict__ cloud, const int32_t *__restric
     __syncthreads();
     cluster_arrive();
 
-    // D: colour filter + scatter of my near list
+    // D: colour filter + scatter of the warp's near list
     uint8_t *mask = road_mask + (int64_t)f * g.H * g.W;
     uint8_t *ovl = OVERLAY ? overlay + (int64_t)f * g.H * g.W * 3 : nullptr;
     int rcount = 0;
-    for (int k = 0; k < cnt; ++k) {
-        uint32_t w = s_list[k * RC_THREADS + tid];
+    for (int k = lane; k < wcnt; k += 32) {
+        uint32_t w = wlist[k];
         if (s_tot[w >> 22] > colour_threshold) {
             ++rcount;
             int px = (int)(w & 0x7FFu), py = (int)((w >> 11) & 0x7FFu);
@@ -632,14 +658,10 @@ road_cluster_kernel(const uint64_t *__restrict__ cloud, const int32_t *__restric
             }
         }
     }
-    int kcount = cnt;
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        rcount += __shfl_xor_sync(0xffffffffu, rcount, o);
-        kcount += __shfl_xor_sync(0xffffffffu, kcount, o);
-    }
+    for (int o = 16; o > 0; o >>= 1) rcount += __shfl_xor_sync(0xffffffffu, rcount, o);
     if (lane == 0) {
-        if (kcount) atomicAdd(&s_k, kcount);
+        if (wcnt) atomicAdd(&s_k, wcnt);
         if (rcount) atomicAdd(&s_r, rcount);
     }
     __syncthreads();
@@ -668,8 +690,9 @@ extern "C" int svb_road_points(const uint64_t *cloud, const int32_t *counts, con
     RoadGeom g = make_road_geom(H, W, step);
     CamD c = make_camd(cam);
     // fused cluster kernel when the displacement table is given and a CTA's near list fits in shared memory
-    const int64_t part_max = (g.slab + RC_PARTS - 1) / RC_PARTS + 2;             // records of one CTA, at most
-    const int64_t list_cap = (part_max + RC_ROUND - 1) / RC_ROUND * RC_ROUND;   // RC_PER_ROUND slots per round per thread
+    const int64_t rounds = (g.slab + RC_ROUND - 1) / RC_ROUND;                   // rounds of a frame, dealt round-robin
+    const int64_t list_cap = (rounds + RC_PARTS - 1) / RC_PARTS * RC_ROUND;      // records one CTA can meet
+    const int warp_cap = (int)(list_cap / RC_WARPS);                             // ... and one warp
     const size_t list_bytes = (size_t)list_cap * sizeof(uint32_t);
     const bool mask_no_wrap = (H <= 2048 && W <= 2048);
     if (reproj_bits && mask_no_wrap && list_bytes <= 160 * 1024 && !g_svb_force_two_pass) {
@@ -689,12 +712,12 @@ extern "C" int svb_road_points(const uint64_t *cloud, const int32_t *counts, con
             e = cudaFuncSetAttribute(road_cluster_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)list_bytes);
             if (e == cudaSuccess)
                 e = cudaLaunchKernelEx(&cfg, road_cluster_kernel<true>, cloud, counts, planes, g, c, colour_threshold,
-                                       reproj_bits, hist, road_mask, overlay, counts_out);
+                                       reproj_bits, hist, road_mask, overlay, counts_out, warp_cap);
         } else {
             e = cudaFuncSetAttribute(road_cluster_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)list_bytes);
             if (e == cudaSuccess)
                 e = cudaLaunchKernelEx(&cfg, road_cluster_kernel<false>, cloud, counts, planes, g, c, colour_threshold,
-                                       reproj_bits, hist, road_mask, (uint8_t *)nullptr, counts_out);
+                                       reproj_bits, hist, road_mask, (uint8_t *)nullptr, counts_out, warp_cap);
         }
         if (e != cudaSuccess) return (int)e;
         SVB_LAUNCH_CHECK();

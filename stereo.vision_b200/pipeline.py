@@ -102,7 +102,7 @@ class RoadPath:
         if int(ok.item()) != 1 or not use_reproj_table:
             self.reproj_bits = None
         # svb_road_points takes its fused cluster path when a CTA's near list fits in shared memory
-        self.fused_road = self.reproj_bits is not None and (((self.L + 7) // 8 + 2 + 2047) // 2048 * 2048) * 4 <= 160 * 1024
+        self.fused_road = self.reproj_bits is not None and ((self.L + 2047) // 2048 + 7) // 8 * 2048 * 4 <= 160 * 1024
 
     # ------------------------------------------------------------------
     def process(self, disp, bgr, prev=None, seed=0, frame0=0, indices=None, overlay=None,
