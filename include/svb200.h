@@ -65,9 +65,18 @@ int svb_lattice_cols(int W, int step);
 /* ---- a1  fillDisparity / disparityCleaning('previous')            functions.py:130-147
  * filled[t] = sat_add_u8(raw[t], (raw[t] <= 2) ? filled[t-1] : 0), filled[-1] = prev0.
  * prev0 == NULL: frame 0 is copied unchanged (prev_disp is None, functions.py:134).
- * The recurrence over t runs inside one launch (one thread owns 16 pixels for all F frames). */
+ * The recurrence over t runs inside one launch (one thread owns 16 pixels for all F frames and keeps
+ * the loads of the next 12 frames in flight). */
 int svb_fill_sequence(const uint8_t *raw, const uint8_t *prev0, uint8_t *filled,
                       int F, int H, int W, void *stream);
+
+/* a1 fused with the counting pass of a4: also leaves in `scratch` the per-row-group site counts of the
+ * FILLED frames (the bytes are in registers anyway), so that svb_project_compact_counted() can skip its
+ * own counting pass.  carmask may be NULL.  scratch: svb_project_scratch_bytes(F,H,W,step) bytes; it must
+ * reach svb_project_compact_counted() untouched, with the same F,H,W,step and carmask. */
+int svb_fill_sequence_counted(const uint8_t *raw, const uint8_t *prev0, uint8_t *filled,
+                              const uint8_t *carmask, int F, int H, int W, int step,
+                              void *scratch, int64_t scratch_bytes, void *stream);
 
 /* ---- a2  maskDisparity                                             functions.py:169-172
  * out = d where carmask != 0 else 0.  (a3 capDisparity is the identity, functions.py:164-167.) */
@@ -75,7 +84,7 @@ int svb_mask_disparity(const uint8_t *d, const uint8_t *carmask, uint8_t *out,
                        int F, int H, int W, void *stream);
 
 /* ---- a4  projectDisparityTo3d (both calls of stereovision.py:84-85)  functions.py:178-198
- * For each frame: cloud  = lattice sites with d > 0, with RGB = bgr[y,x,2..0] and the hue bin;
+ * For each frame: cloud  = lattice sites with d > 0, with RGB = bgr[y,x,2..0];
  *                 mcloud = lattice sites with d > 0 and carmask != 0 (no colour).
  * Any of cloud / mcloud may be NULL (that output is skipped); bgr NULL -> colour bits are 0;
  * carmask NULL -> every site counts as inside the mask.
@@ -86,6 +95,12 @@ int svb_project_compact(const uint8_t *disp, const uint8_t *carmask, const uint8
                         int F, int H, int W, int step, const svb_camera *cam,
                         uint64_t *cloud, uint32_t *mcloud, int32_t *counts,
                         void *scratch, int64_t scratch_bytes, void *stream);
+
+/* Same, for frames that came out of svb_fill_sequence_counted() (scratch already holds the counts). */
+int svb_project_compact_counted(const uint8_t *filled, const uint8_t *carmask, const uint8_t *bgr,
+                                int F, int H, int W, int step, const svb_camera *cam,
+                                uint64_t *cloud, uint32_t *mcloud, int32_t *counts,
+                                void *scratch, int64_t scratch_bytes, void *stream);
 
 /* Materialise what the reference's list holds: xyz float64 [n,3] (functions.py:191-193, bit-exact),
  * rgb uint8 [n,3] (functions.py:195), sites int32 [n,2] as (y,x), disparity uint8 [n].

@@ -17,7 +17,7 @@ LIB_PATH = os.path.join(_PKG, "libsvb200.so")
 HUE_BINS = 1001
 HIST_STRIDE = 1024
 PLANE_STRIDE = 8
-ABI_VERSION = 3
+ABI_VERSION = 4
 
 
 class SvbError(RuntimeError):
@@ -48,9 +48,11 @@ SIGNATURES = {
     "svb_lattice_rows": (I, [I, I]),
     "svb_lattice_cols": (I, [I, I]),
     "svb_fill_sequence": (I, [P, P, P, I, I, I, P]),
+    "svb_fill_sequence_counted": (I, [P, P, P, P, I, I, I, I, P, L, P]),
     "svb_mask_disparity": (I, [P, P, P, I, I, I, P]),
     "svb_project_scratch_bytes": (L, [I, I, I, I]),
     "svb_project_compact": (I, [P, P, P, I, I, I, I, CAMP, P, P, P, P, L, P]),
+    "svb_project_compact_counted": (I, [P, P, P, I, I, I, I, CAMP, P, P, P, P, L, P]),
     "svb_cloud_export": (I, [P, I, I, CAMP, P, P, P, P, P, P, P]),
     "svb_ransac_score": (I, [P, I, L, P, I, I, I, I, I, I, CAMP, P, P, U64, I, P, P]),
     "svb_ransac_dump_indices": (I, [P, I, L, P, I, I, I, I, I, CAMP, U64, I, P, P, P]),

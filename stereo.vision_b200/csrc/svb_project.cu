@@ -15,87 +15,6 @@
 #define PROJ_THREADS 256
 #define CHUNK 16
 
-// ------------------------------------------------------------------ a1 fill
-// d' = sat_add(d, (d <= 2) ? prev : 0) on 4 bytes at once           functions.py:142-146
-__device__ __forceinline__ uint32_t fill4(uint32_t d, uint32_t prev) {
-    uint32_t hole = __vcmpleu4(d, 0x02020202u);        // 0xff where d <= 2
-    return __vaddus4(d, prev & hole);                  // cv2.add saturates
-}
-__device__ __forceinline__ uint4 fill16(uint4 d, uint4 p) {
-    return make_uint4(fill4(d.x, p.x), fill4(d.y, p.y), fill4(d.z, p.z), fill4(d.w, p.w));
-}
-
-// One thread = 16 pixels for all F frames; the loads of up to UNROLL future frames are in flight
-// while the recurrence advances (they do not depend on it).
-template <int UNROLL>
-__global__ void __launch_bounds__(256)
-fill_seq_v16(const uint4 *__restrict__ raw, const uint4 *__restrict__ prev0, uint4 *__restrict__ filled,
-             int F, int64_t chunks) {
-    int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= chunks) return;
-    bool have = prev0 != nullptr;
-    uint4 prev = have ? __ldg(prev0 + p) : make_uint4(0, 0, 0, 0);
-    int t = 0;
-    for (; t + UNROLL <= F; t += UNROLL) {
-        uint4 d[UNROLL];
-#pragma unroll
-        for (int u = 0; u < UNROLL; ++u) d[u] = __ldcs(raw + (int64_t)(t + u) * chunks + p);
-#pragma unroll
-        for (int u = 0; u < UNROLL; ++u) {
-            uint4 v = have ? fill16(d[u], prev) : d[u];
-            __stcs(filled + (int64_t)(t + u) * chunks + p, v);
-            prev = v;
-            have = true;
-        }
-    }
-    for (; t < F; ++t) {
-        uint4 d = __ldcs(raw + (int64_t)t * chunks + p);
-        uint4 v = have ? fill16(d, prev) : d;
-        __stcs(filled + (int64_t)t * chunks + p, v);
-        prev = v;
-        have = true;
-    }
-}
-
-// any-size fallback, one pixel per thread
-__global__ void fill_seq_scalar(const uint8_t *__restrict__ raw, const uint8_t *__restrict__ prev0,
-                                uint8_t *__restrict__ filled, int F, int64_t pixels) {
-    int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= pixels) return;
-    bool have = prev0 != nullptr;
-    int prev = have ? prev0[p] : 0;
-    for (int t = 0; t < F; ++t) {
-        int d = raw[(int64_t)t * pixels + p];
-        if (have && d <= 2) d = min(d + prev, 255);
-        filled[(int64_t)t * pixels + p] = (uint8_t)d;
-        prev = d;
-        have = true;
-    }
-}
-
-extern "C" int svb_fill_sequence(const uint8_t *raw, const uint8_t *prev0, uint8_t *filled,
-                                 int F, int H, int W, void *stream) {
-    if (!raw || !filled) return SVB_E_NULL;
-    if (F < 1 || H < 1 || W < 1) return SVB_E_SHAPE;
-    cudaStream_t st = (cudaStream_t)stream;
-    int64_t pixels = (int64_t)H * W;
-    bool aligned = (pixels % 16 == 0) && (((uintptr_t)raw | (uintptr_t)filled | (uintptr_t)prev0) % 16 == 0);
-    ProfScope ps(K_FILL, st);
-    if (aligned) {
-        int64_t chunks = pixels / 16;
-        int threads = 128;
-        int64_t blocks = (chunks + threads - 1) / threads;
-        fill_seq_v16<8><<<(unsigned)blocks, threads, 0, st>>>((const uint4 *)raw, (const uint4 *)prev0,
-                                                             (uint4 *)filled, F, chunks);
-    } else {
-        int threads = 256;
-        int64_t blocks = (pixels + threads - 1) / threads;
-        fill_seq_scalar<<<(unsigned)blocks, threads, 0, st>>>(raw, prev0, filled, F, pixels);
-    }
-    SVB_LAUNCH_CHECK();
-    return SVB_OK;
-}
-
 // ------------------------------------------------------------------ a2 mask
 __global__ void mask_disp_kernel(const uint8_t *__restrict__ d, const uint8_t *__restrict__ cm,
                                  uint8_t *__restrict__ out, int64_t pixels, int64_t total) {
@@ -177,6 +96,21 @@ __device__ __forceinline__ uint32_t nz4(uint32_t w) {
     return (m | (m >> 7) | (m >> 14) | (m >> 21)) & 0xFu;
 }
 
+// lattice sites among the 16 pixels starting at x0 (x % step == 0 and x < W-1)
+__device__ __forceinline__ uint32_t site_bits(int x0, int W, int step) {
+    uint32_t site;
+    if (step == 1) site = 0xFFFFu;
+    else if (step == 2) site = 0x5555u;                 // x0 is a multiple of 16, hence even
+    else {
+        site = 0;
+#pragma unroll
+        for (int j = 0; j < CHUNK; ++j) if ((x0 + j) % step == 0) site |= 1u << j;
+    }
+    int lim = W - 1 - x0;                               // pixels of this chunk with x < W-1
+    if (lim < CHUNK) site &= (lim <= 0) ? 0u : ((1u << lim) - 1u);
+    return site;
+}
+
 template <bool HAS_MASK>
 __device__ __forceinline__ ChunkBits load_chunk(const uint8_t *__restrict__ drow, const uint8_t *__restrict__ mrow,
                                                 int x0, int W, int step, bool vec_ok) {
@@ -206,17 +140,7 @@ __device__ __forceinline__ ChunkBits load_chunk(const uint8_t *__restrict__ drow
         }
     }
     uint32_t nzd = nz4(c.d[0]) | (nz4(c.d[1]) << 4) | (nz4(c.d[2]) << 8) | (nz4(c.d[3]) << 12);
-    // lattice sites of this chunk: x % step == 0 and x < W-1
-    uint32_t site;
-    if (step == 1) site = 0xFFFFu;
-    else if (step == 2) site = 0x5555u;                 // x0 is a multiple of 16, hence even
-    else {
-        site = 0;
-#pragma unroll
-        for (int j = 0; j < CHUNK; ++j) if ((x0 + j) % step == 0) site |= 1u << j;
-    }
-    int lim = W - 1 - x0;                               // pixels of this chunk with x < W-1
-    if (lim < CHUNK) site &= (lim <= 0) ? 0u : ((1u << lim) - 1u);
+    uint32_t site = site_bits(x0, W, step);
     c.vm = nzd & site;
     if (HAS_MASK) {
         uint32_t nzm = nz4(m[0]) | (nz4(m[1]) << 4) | (nz4(m[2]) << 8) | (nz4(m[3]) << 12);
@@ -225,6 +149,147 @@ __device__ __forceinline__ ChunkBits load_chunk(const uint8_t *__restrict__ drow
         c.mm = c.vm;
     }
     return c;
+}
+
+// ------------------------------------------------------------------ a1 fill
+// d' = sat_add(d, (d <= 2) ? prev : 0) on 4 bytes at once           functions.py:142-146
+__device__ __forceinline__ uint32_t fill4(uint32_t d, uint32_t prev) {
+    uint32_t hole = __vcmpleu4(d, 0x02020202u);        // 0xff where d <= 2
+    return __vaddus4(d, prev & hole);                  // cv2.add saturates
+}
+// One thread = 16 pixels for all F frames; the loads of the next U frames are issued back to back
+// (they do not depend on the recurrence) and then consumed in order.  A rolling window of loads does
+// not work here: a warp tracks outstanding loads with six scoreboards, so waiting for the oldest of
+// twelve loads also waits for younger ones.
+// COUNT: the kernel also leaves, per (frame, row group), the number of valid / masked-valid lattice
+// sites of the FILLED frame, i.e. what proj_count_kernel would compute from `filled` -- the bytes are
+// already in registers here, so the projection needs no counting pass of its own.  Site and carmask
+// membership are kept as 0x80-per-byte masks, so a word's counts are two popc.
+#define FILL_THREADS 64
+__device__ __forceinline__ uint32_t nz80(uint32_t w) { return ((w & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | w; }   // bit 7 of a byte: byte != 0
+__device__ __forceinline__ uint4 fill16(uint4 d, uint4 p) {
+    return make_uint4(fill4(d.x, p.x), fill4(d.y, p.y), fill4(d.z, p.z), fill4(d.w, p.w));
+}
+template <int U, bool COUNT>
+__global__ void __launch_bounds__(FILL_THREADS)
+fill_seq_v16(const uint4 *__restrict__ raw, const uint4 *__restrict__ prev0, uint4 *__restrict__ filled,
+             int F, int64_t chunks, const uint4 *__restrict__ carmask, ProjGeom g, uint32_t *__restrict__ group_counts) {
+    int64_t p = (int64_t)blockIdx.x * FILL_THREADS + threadIdx.x;
+    const bool active = p < chunks;
+    if (!active) p = chunks - 1;                        // keep the lane for the shuffles; it stores nothing
+    bool have = prev0 != nullptr;
+    uint4 prev = have ? __ldg(prev0 + p) : make_uint4(0, 0, 0, 0);
+
+    // counting set-up: is this chunk on a lattice row, which group, which bytes are sites / inside carmask
+    bool lat = false, uni = false;
+    int grp = 0;
+    uint4 site80 = make_uint4(0, 0, 0, 0), in80 = make_uint4(0, 0, 0, 0);
+    if (COUNT) {
+        int y = (int)(p / g.cpr), x0 = (int)(p % g.cpr) * CHUNK;
+        int ly = y / g.step;
+        lat = active && (y % g.step == 0) && ly < g.LH;
+        grp = ly / g.rpb;
+        if (lat) {
+            uint32_t sb = site_bits(x0, g.W, g.step), w[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                uint32_t n = (sb >> (4 * k)) & 0xFu;   // 4 site bits -> 0x80 per byte
+                w[k] = ((n & 1u) << 7) | ((n & 2u) << 14) | ((n & 4u) << 21) | ((n & 8u) << 28);
+            }
+            site80 = make_uint4(w[0], w[1], w[2], w[3]);
+            uint4 m = carmask ? __ldg(carmask + p) : make_uint4(~0u, ~0u, ~0u, ~0u);
+            in80 = make_uint4(nz80(m.x) & w[0], nz80(m.y) & w[1], nz80(m.z) & w[2], nz80(m.w) & w[3]);
+        }
+        int lat0 = __shfl_sync(0xffffffffu, (int)lat, 0), grp0 = __shfl_sync(0xffffffffu, grp, 0);
+        uni = __all_sync(0xffffffffu, (int)lat == lat0 && (!lat || grp == grp0));
+    }
+    auto count = [&](const uint4 &v, int t) {
+        if (uni && !lat) return;                        // whole warp off the lattice (odd rows at step 2)
+        uint32_t a = nz80(v.x), b = nz80(v.y), c4 = nz80(v.z), d4 = nz80(v.w);
+        uint32_t c = (uint32_t)(__popc(a & site80.x) + __popc(b & site80.y) + __popc(c4 & site80.z) + __popc(d4 & site80.w)) |
+                     ((uint32_t)(__popc(a & in80.x) + __popc(b & in80.y) + __popc(c4 & in80.z) + __popc(d4 & in80.w)) << 16);
+        if (uni) {
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+            if ((threadIdx.x & 31) == 0 && c) atomicAdd(group_counts + (int64_t)t * g.groups + grp, c);
+        } else if (lat && c) {
+            atomicAdd(group_counts + (int64_t)t * g.groups + grp, c);
+        }
+    };
+
+    int t = 0;
+    for (; t + U <= F; t += U) {
+        uint4 d[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) d[u] = __ldcs(raw + (int64_t)(t + u) * chunks + p);
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            uint4 v = have ? fill16(d[u], prev) : d[u];
+            if (active) __stcs(filled + (int64_t)(t + u) * chunks + p, v);
+            prev = v;
+            have = true;
+            if (COUNT) count(v, t + u);
+        }
+    }
+    for (; t < F; ++t) {
+        uint4 d = __ldcs(raw + (int64_t)t * chunks + p);
+        uint4 v = have ? fill16(d, prev) : d;
+        if (active) __stcs(filled + (int64_t)t * chunks + p, v);
+        prev = v;
+        have = true;
+        if (COUNT) count(v, t);
+    }
+}
+
+// any-size fallback, one pixel per thread
+__global__ void fill_seq_scalar(const uint8_t *__restrict__ raw, const uint8_t *__restrict__ prev0,
+                                uint8_t *__restrict__ filled, int F, int64_t pixels) {
+    int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= pixels) return;
+    bool have = prev0 != nullptr;
+    int prev = have ? prev0[p] : 0;
+    for (int t = 0; t < F; ++t) {
+        int d = raw[(int64_t)t * pixels + p];
+        if (have && d <= 2) d = min(d + prev, 255);
+        filled[(int64_t)t * pixels + p] = (uint8_t)d;
+        prev = d;
+        have = true;
+    }
+}
+
+#define FILL_UNROLL 8
+static int launch_fill(const uint8_t *raw, const uint8_t *prev0, uint8_t *filled, int F, int H, int W,
+                       const uint8_t *carmask, const ProjGeom *g, uint32_t *group_counts, cudaStream_t st) {
+    int64_t pixels = (int64_t)H * W;
+    bool aligned = (pixels % 16 == 0) && (((uintptr_t)raw | (uintptr_t)filled | (uintptr_t)prev0) % 16 == 0);
+    if (!aligned) {
+        if (g) return SVB_E_ARG;                        // the caller checks can_count_in_fill() first
+        int threads = 256;
+        int64_t blocks = (pixels + threads - 1) / threads;
+        fill_seq_scalar<<<(unsigned)blocks, threads, 0, st>>>(raw, prev0, filled, F, pixels);
+        return SVB_OK;
+    }
+    int64_t chunks = pixels / 16;
+    unsigned blocks = (unsigned)((chunks + FILL_THREADS - 1) / FILL_THREADS);
+    if (g)
+        fill_seq_v16<FILL_UNROLL, true><<<blocks, FILL_THREADS, 0, st>>>((const uint4 *)raw, (const uint4 *)prev0, (uint4 *)filled,
+                                                                         F, chunks, (const uint4 *)carmask, *g, group_counts);
+    else
+        fill_seq_v16<FILL_UNROLL, false><<<blocks, FILL_THREADS, 0, st>>>((const uint4 *)raw, (const uint4 *)prev0, (uint4 *)filled,
+                                                                          F, chunks, nullptr, ProjGeom(), nullptr);
+    return SVB_OK;
+}
+
+extern "C" int svb_fill_sequence(const uint8_t *raw, const uint8_t *prev0, uint8_t *filled,
+                                 int F, int H, int W, void *stream) {
+    if (!raw || !filled) return SVB_E_NULL;
+    if (F < 1 || H < 1 || W < 1) return SVB_E_SHAPE;
+    cudaStream_t st = (cudaStream_t)stream;
+    ProfScope ps(K_FILL, st);
+    int rc = launch_fill(raw, prev0, filled, F, H, W, nullptr, nullptr, nullptr, st);
+    if (rc != SVB_OK) return rc;
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
 }
 
 // exclusive scan of one packed (cloud | mcloud << 16) count per thread over the 256-thread block
@@ -434,11 +499,46 @@ extern "C" int64_t svb_project_scratch_bytes(int F, int H, int W, int step) {
     return (int64_t)2 * F * g.groups * (int64_t)sizeof(uint32_t);
 }
 
-extern "C" int svb_project_compact(const uint8_t *disp, const uint8_t *carmask, const uint8_t *bgr,
-                                   int F, int H, int W, int step, const svb_camera *cam,
-                                   uint64_t *cloud, uint32_t *mcloud, int32_t *counts,
-                                   void *scratch, int64_t scratch_bytes, void *stream) {
-    (void)cam;
+static bool can_count_in_fill(int H, int W, const void *a, const void *b, const void *c, const void *d) {
+    return ((int64_t)H * W) % 16 == 0 && W % CHUNK == 0 &&
+           (((uintptr_t)a | (uintptr_t)b | (uintptr_t)c | (uintptr_t)d) % 16 == 0);
+}
+
+extern "C" int svb_fill_sequence_counted(const uint8_t *raw, const uint8_t *prev0, uint8_t *filled,
+                                         const uint8_t *carmask, int F, int H, int W, int step,
+                                         void *scratch, int64_t scratch_bytes, void *stream) {
+    if (!raw || !filled || !scratch) return SVB_E_NULL;
+    if (F < 1 || H < 2 || W < 2 || H > SVB_MAX_DIM || W > SVB_MAX_DIM || step < 1) return SVB_E_SHAPE;
+    if (scratch_bytes < svb_project_scratch_bytes(F, H, W, step)) return SVB_E_SCRATCH;
+    cudaStream_t st = (cudaStream_t)stream;
+    ProjGeom g = make_geom(H, W, step, true);
+    if (g.cpr > PROJ_THREADS) return SVB_E_SHAPE;
+    uint32_t *gc = (uint32_t *)scratch;
+    if (can_count_in_fill(H, W, raw, prev0, filled, carmask)) {
+        ProfScope ps(K_FILL, st);
+        cudaError_t e = cudaMemsetAsync(gc, 0, (size_t)F * g.groups * sizeof(uint32_t), st);
+        if (e != cudaSuccess) return (int)e;
+        int rc = launch_fill(raw, prev0, filled, F, H, W, carmask, &g, gc, st);
+        if (rc != SVB_OK) return rc;
+        SVB_LAUNCH_CHECK();
+        return SVB_OK;
+    }
+    // shapes the vector kernel cannot take: plain fill, then the stand-alone counting pass
+    int rc = svb_fill_sequence(raw, prev0, filled, F, H, W, stream);
+    if (rc != SVB_OK) return rc;
+    bool aligned = (((uintptr_t)filled | (uintptr_t)carmask) % 16 == 0);
+    g = make_geom(H, W, step, aligned);
+    dim3 grid(g.groups, F);
+    ProfScope ps(K_PROJ_COUNT, st);
+    if (carmask) proj_count_kernel<true><<<grid, PROJ_THREADS, 0, st>>>(filled, carmask, g, gc);
+    else         proj_count_kernel<false><<<grid, PROJ_THREADS, 0, st>>>(filled, carmask, g, gc);
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
+}
+
+static int project_compact_impl(const uint8_t *disp, const uint8_t *carmask, const uint8_t *bgr,
+                                int F, int H, int W, int step, uint64_t *cloud, uint32_t *mcloud, int32_t *counts,
+                                void *scratch, int64_t scratch_bytes, void *stream, bool counts_ready) {
     if (!disp || !counts || !scratch) return SVB_E_NULL;
     if (F < 1 || H < 2 || W < 2 || H > SVB_MAX_DIM || W > SVB_MAX_DIM || step < 1) return SVB_E_SHAPE;
     if (scratch_bytes < svb_project_scratch_bytes(F, H, W, step)) return SVB_E_SCRATCH;
@@ -448,12 +548,12 @@ extern "C" int svb_project_compact(const uint8_t *disp, const uint8_t *carmask, 
     if (g.cpr > PROJ_THREADS) return SVB_E_SHAPE;
     uint32_t *gc = (uint32_t *)scratch;
     dim3 grid(g.groups, F);
-    {
+    if (!counts_ready) {
         ProfScope ps(K_PROJ_COUNT, st);
         if (carmask) proj_count_kernel<true><<<grid, PROJ_THREADS, 0, st>>>(disp, carmask, g, gc);
         else         proj_count_kernel<false><<<grid, PROJ_THREADS, 0, st>>>(disp, carmask, g, gc);
+        SVB_LAUNCH_CHECK();
     }
-    SVB_LAUNCH_CHECK();
     {
         ProfScope ps(K_PROJ_SCAN, st);
         proj_scan_kernel<<<F, 256, 0, st>>>(gc, g.groups, counts);
@@ -481,6 +581,22 @@ extern "C" int svb_project_compact(const uint8_t *disp, const uint8_t *carmask, 
 #undef LAUNCH_W
     SVB_LAUNCH_CHECK();
     return SVB_OK;
+}
+
+extern "C" int svb_project_compact(const uint8_t *disp, const uint8_t *carmask, const uint8_t *bgr,
+                                   int F, int H, int W, int step, const svb_camera *cam,
+                                   uint64_t *cloud, uint32_t *mcloud, int32_t *counts,
+                                   void *scratch, int64_t scratch_bytes, void *stream) {
+    (void)cam;
+    return project_compact_impl(disp, carmask, bgr, F, H, W, step, cloud, mcloud, counts, scratch, scratch_bytes, stream, false);
+}
+
+extern "C" int svb_project_compact_counted(const uint8_t *filled, const uint8_t *carmask, const uint8_t *bgr,
+                                           int F, int H, int W, int step, const svb_camera *cam,
+                                           uint64_t *cloud, uint32_t *mcloud, int32_t *counts,
+                                           void *scratch, int64_t scratch_bytes, void *stream) {
+    (void)cam;
+    return project_compact_impl(filled, carmask, bgr, F, H, W, step, cloud, mcloud, counts, scratch, scratch_bytes, stream, true);
 }
 
 // ------------------------------------------------------------------ export of what the reference's list holds

@@ -1,15 +1,15 @@
-// a5-a7: RANSAC plane fit.  One warp scores one hypothesis; a block holds 8 hypotheses of one frame
-// and shares the 255-entry table Z(d) = (f*B)/d in shared memory.  The masked cloud of a frame is
-// at most 4 bytes x lattice sites (128 KB at the reference size), i.e. L2-resident: the S gathers
-// of a hypothesis are 4-byte L2 reads, the sample-index stream (explicit mode) is read coalesced.
+// a5-a7: RANSAC plane fit.  One warp scores one hypothesis; persistent blocks (one per SM) walk
+// contiguous ranges of (frame, trial) pairs and stage the current frame's masked cloud -- at most
+// 4 bytes x lattice sites inside carmask, 128 KB at the reference size -- in shared memory with bulk
+// (TMA) copies, so the S gathers of a hypothesis are shared-memory reads; the sample-index stream
+// (explicit mode) is read coalesced.
 //
-// Arithmetic.  The three points of a hypothesis are expanded with the path's exact float64
-// expressions (svb_common.cuh) because the "exactly collinear -> draw again" rule of
-// functions.py:251-259 is an exact-zero test, and the plane is abc = inv([P1;P2;P3]).1 evaluated
-// with the adjugate (fp64).  The S point-plane distances of the score use the factored form
-// |Z(d)*(a/f*(x-cw) + b/f*(y-ch) + c) - 1| (5 flops, no division); it differs from the reference
-// expression by ~1e-16 relative, far below the gap between two hypotheses' mean errors, and only
-// the arg-min (not the error value) is an observable.
+// Arithmetic.  The score of a hypothesis is evaluated in pixel coordinates with integer
+// determinants (see "Arithmetic of the score" below): no float64 point expansion, division or square
+// root per hypothesis, 4 float64 operations per sample.  The "exactly collinear -> draw again" rule
+// of functions.py:251-259 (an exact-zero test on float64 points) and the winning plane itself
+// (abc = inv([P1;P2;P3]).1, adjugate in fp64, svb_ransac_finalize) still use the path's exact
+// float64 expressions (svb_common.cuh).
 #include "svb_common.cuh"
 #include "svb_prof.cuh"
 #include <math.h>
@@ -31,8 +31,8 @@ __host__ __device__ __forceinline__ uint32_t trial_key(uint64_t seed, int frame,
     return k;
 }
 // keyed bijection of [0, 2^bits): (odd multiply + add) and xor-shift by >= bits/2 are both invertible
-// modulo 2^bits; two rounds of each, then cycle-walk into [0, m).  The three multipliers/offset are
-// derived once per hypothesis from its key, so a draw costs ~10 integer instructions.
+// modulo 2^bits; multiply-add, xor-shift, multiply, then cycle-walk into [0, m).  The three
+// multipliers/offset are derived once per hypothesis from its key, so a draw costs ~8 integer instructions.
 struct PermKey { uint32_t A, B, C, mask; int sh; };
 __host__ __device__ __forceinline__ PermKey make_perm(uint32_t key, int bits) {
     PermKey k;
@@ -49,7 +49,6 @@ __host__ __device__ __forceinline__ uint32_t perm_draw(const PermKey &k, uint32_
         v = (v * k.A + k.B) & k.mask;
         v ^= v >> k.sh;
         v = (v * k.C) & k.mask;
-        v ^= v >> k.sh;
     } while (v >= m);
     return v;
 }
@@ -136,173 +135,250 @@ __device__ __forceinline__ bool trial_triple(const uint32_t *__restrict__ rec, i
 }
 
 // ------------------------------------------------------------------ score: one warp per hypothesis
+// Arithmetic of the score.  With Z = fB/d, X = (x-cw) Z/f, Y = (y-ch) Z/f the plane a X + b Y + c Z = 1
+// through three points reads, in pixel coordinates,  al x + be y + ga = d/fB  (al = a/f, be = b/f,
+// ga = c - al cw - be ch): a 3x3 system with the INTEGER matrix [x_i y_i 1] and right-hand side d_i/fB.
+// Cramer's rule gives  (al, be, ga) = (Na, Nb, Ng) / (fB det)  with the integer determinants
+//   det = |x y 1|,  Na = |d y 1|,  Nb = |x d 1|,  Ng = |x y d|       (exact in int32 / float64)
+// and for a sample point (x, y, d):   P.abc - 1 = ((Na x + Nb y + Ng)/d - det) / det,
+//   mean_j |P_j.abc - 1| / |abc| = fB sum_j |(Na x_j + Nb y_j + Ng)/d_j - det| / (S sqrt(A^2 + B^2 + C^2)),
+//   A = f Na, B = f Nb, C = Ng + cw Na + ch Nb                        (det cancels).
+// Na x + Nb y + Ng is an exact integer (< 2^35) in float64, so the only roundings per sample are the
+// product with the table value 1/d and the sum: ~1e-14 relative on the score, against the reference's
+// inv()/dot() float64 chain (functions.py:267-275) which itself is only reproducible to ~1e-12 (SURVEY
+// 7.1-4).  No division, square root or float64 point expansion per hypothesis; det == 0 is exactly
+// "image-collinear" (the singular case).
 // int -> double without the (quarter-rate) conversion instruction: 2^52 + x has x in its low mantissa bits
 __device__ __forceinline__ double u2d(uint32_t x) { return __hiloint2double(0x43300000, (int)x) - 4503599627370496.0; }
 
-__device__ __forceinline__ double bcast(double v, int src) {
-    return __hiloint2double(__shfl_sync(0xffffffffu, __double2hiint(v), src), __shfl_sync(0xffffffffu, __double2loint(v), src));
+__device__ __forceinline__ int img_det(uint32_t r1, uint32_t r2, uint32_t r3) {
+    int x1 = rec_x(r1), y1 = rec_y(r1), x2 = rec_x(r2), y2 = rec_y(r2), x3 = rec_x(r3), y3 = rec_y(r3);
+    return x1 * (y2 - y3) + x2 * (y3 - y1) + x3 * (y1 - y2);
 }
 
-// Warp-cooperative version of trial_triple: lanes 0..2 each fetch and expand one point (one division
-// sequence per coordinate for the whole warp instead of three), then the nine values are broadcast.
+// Warp-cooperative draw of the triple of one trial: lanes 0..2 fetch one record each.  Returns false when the
+// trial has no plane (bad explicit index, image-collinear triple, retry budget exhausted).  Same decisions as
+// trial_triple(): an exactly collinear triple (np.cross == 0, functions.py:256-259) is necessarily
+// image-collinear, so the float64 expansion is only needed -- to tell "draw again" from "skip" -- when det == 0.
+template <bool EXPLICIT>
 __device__ __forceinline__ bool warp_triple(const uint32_t *__restrict__ rec, int stride, uint32_t M, const CamD &cam,
                                             const int32_t *__restrict__ triple, uint32_t key, int lane,
-                                            P3 &p1, P3 &p2, P3 &p3) {
-    const int rounds = triple ? 1 : MAX_TRIPLE_ROUNDS;
+                                            uint32_t &r1, uint32_t &r2, uint32_t &r3) {
+    const int rounds = EXPLICIT ? 1 : MAX_TRIPLE_ROUNDS;
     for (int round = 0; round < rounds; ++round) {
         uint32_t idx;
-        bool valid = true;
-        if (triple) {
-            int i = lane < 3 ? triple[lane] : 0;
-            valid = i >= 0 && (uint32_t)i < M;
-            idx = valid ? (uint32_t)i : 0u;
+        if (EXPLICIT) {
+            int i = lane < 3 ? __ldg(triple + lane) : 0;
+            bool valid = i >= 0 && (uint32_t)i < M;
             if (__any_sync(0xffffffffu, !valid)) return false;
+            idx = (uint32_t)i;
         } else {
             idx = uniform_draw(key, 3u * round + (lane < 3 ? lane : 0), M);
         }
         uint32_t r = __ldg(rec + (int64_t)idx * stride);
-        P3 p = expand_point(cam, r | (lane < 3 ? 0u : (1u << 22)));     // idle lanes: d >= 1, no division by zero
-        p1.x = bcast(p.x, 0); p1.y = bcast(p.y, 0); p1.z = bcast(p.z, 0);
-        p2.x = bcast(p.x, 1); p2.y = bcast(p.y, 1); p2.z = bcast(p.z, 1);
-        p3.x = bcast(p.x, 2); p3.y = bcast(p.y, 2); p3.z = bcast(p.z, 2);
-        if (triple || !exactly_collinear(p1, p2, p3)) {
-            uint32_t r1 = __shfl_sync(0xffffffffu, r, 0), r2 = __shfl_sync(0xffffffffu, r, 1), r3 = __shfl_sync(0xffffffffu, r, 2);
-            return !image_collinear(r1, r2, r3);
-        }
+        r1 = __shfl_sync(0xffffffffu, r, 0); r2 = __shfl_sync(0xffffffffu, r, 1); r3 = __shfl_sync(0xffffffffu, r, 2);
+        if (img_det(r1, r2, r3) != 0) return true;
+        if (EXPLICIT) return false;
+        P3 p1 = expand_point(cam, r1), p2 = expand_point(cam, r2), p3 = expand_point(cam, r3);   // rare (3.5e-4 of draws)
+        if (!exactly_collinear(p1, p2, p3)) return false;
     }
     return false;
 }
 
-// plane as in plane_of, with one reciprocal of the determinant instead of three divisions (the result
-// moves by ~1 ulp; only the arg-min of the scores and abc to 1e-5 are observables)
-__device__ __forceinline__ bool plane_fast(const P3 &p1, const P3 &p2, const P3 &p3, double &a, double &b, double &c) {
-    double c23x = p2.y * p3.z - p2.z * p3.y, c23y = p2.z * p3.x - p2.x * p3.z, c23z = p2.x * p3.y - p2.y * p3.x;
-    double c31x = p3.y * p1.z - p3.z * p1.y, c31y = p3.z * p1.x - p3.x * p1.z, c31z = p3.x * p1.y - p3.y * p1.x;
-    double c12x = p1.y * p2.z - p1.z * p2.y, c12y = p1.z * p2.x - p1.x * p2.z, c12z = p1.x * p2.y - p1.y * p2.x;
-    double det = p1.x * c23x + p1.y * c23y + p1.z * c23z;
-    if (det == 0.0 || !isfinite(det)) return false;
-    double inv = 1.0 / det;
-    a = (c23x + c31x + c12x) * inv;
-    b = (c23y + c31y + c12y) * inv;
-    c = (c23z + c31z + c12z) * inv;
-    return isfinite(a) && isfinite(b) && isfinite(c);
+// One warp scores one trial.  STAGED: the S sample gathers read the frame's records from shared memory
+// (s_rec, stride 1); otherwise from global memory (L2).  Writes the mean error (or +inf) to *err_out.
+// Per sample: one keyed-permutation draw (6 integer instructions + a shared check for the rare cycle
+// walk), one gather, and  |(Na x + Nb y + Ng)/d - det|  as two 32x32+64 integer multiply-adds whose
+// 64-bit result IS the bit pattern of the double 2^52 + 2^40 + (Na x + Nb y + Ng) (the bias and the
+// exponent are folded into the addend), one subtraction, one fma with the table value 1/d, one add.
+__device__ __forceinline__ uint32_t perm_once(const PermKey &k, uint32_t v) {
+    v = (v * k.A + k.B) & k.mask;
+    v ^= v >> k.sh;
+    return (v * k.C) & k.mask;
+}
+__device__ __forceinline__ long long mad_wide(int a, int b, long long c) {       // a * b + c, signed 32 x 32 + 64
+    long long r;
+    asm("mad.wide.s32 %0, %1, %2, %3;" : "=l"(r) : "r"(a), "r"(b), "l"(c));
+    return r;
+}
+__device__ __forceinline__ uint32_t lds_u32(uint32_t addr) {
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ double lds_f64(uint32_t addr) {
+    double v;
+    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(addr));
+    return v;
 }
 
-// One warp scores trial t of one frame.  `src` = where the S sample gathers read the 4-byte records:
-// global memory (stride words apart) or the frame's cloud staged in shared memory (stride 1).
-template <bool EXPLICIT>
-__device__ __forceinline__ void score_trial(const uint32_t *__restrict__ rec, int stride, const uint32_t *src, int src_stride,
-                                            uint32_t M, int bits, int S, const CamD &cam, double inv_f, const double *s_Z,
+struct TrialPlane {             // the hypothesis in the integer form the sample loop consumes
+    int na, nb;
+    long long base;             // Ng + 2^40 with the exponent bits of 2^52 on top
+    double det;
+};
+
+// |(Na x + Nb y + Ng)/d - det| for the record r
+template <bool STAGED>
+__device__ __forceinline__ double sample_term(const TrialPlane &h, uint32_t idx, const uint32_t *__restrict__ rec, int stride,
+                                              uint32_t s_rec_addr, uint32_t s_invd_addr) {
+    const uint32_t r = STAGED ? lds_u32(s_rec_addr + idx * 4u) : __ldg(rec + (int64_t)idx * stride);
+    const long long L = mad_wide(h.nb, (int)((r >> 11) & 0x7FFu), mad_wide(h.na, (int)(r & 0x7FFu), h.base));
+    const double lin = __longlong_as_double(L) - 4504699138998272.0;             // 2^52 + 2^40
+    return fabs(fma(lin, lds_f64(s_invd_addr + ((r >> 19) & 0x7F8u)), -h.det));
+}
+
+template <bool EXPLICIT, bool STAGED>
+__device__ __forceinline__ void score_trial(const uint32_t *__restrict__ rec, int stride, uint32_t s_rec_addr,
+                                            uint32_t M, int bits, int S, const CamD &cam, double fB_over_S, uint32_t s_invd_addr,
                                             const int32_t *__restrict__ samp, const int32_t *__restrict__ trip,
                                             uint32_t key, int lane, double *err_out) {
-    P3 p1, p2, p3;
-    double a, b, c;
-    bool ok = warp_triple(rec, stride, M, cam, trip, key, lane, p1, p2, p3);
-    ok = ok && plane_fast(p1, p2, p3, a, b, c);
-    if (!ok) {
+    uint32_t r1, r2, r3;
+    if (!warp_triple<EXPLICIT>(rec, stride, M, cam, trip, key, lane, r1, r2, r3)) {
         if (lane == 0) *err_out = INFINITY;
         return;
     }
-    // |Z(d) * (a/f*(x-cw) + b/f*(y-ch) + c) - 1| with the constant terms folded into c2
-    const double af = a * inv_f, bf = b * inv_f;
-    const double c2 = c - af * cam.cw - bf * cam.ch;
-    const PermKey pk = make_perm(key, bits);
-    double acc = 0.0;
+    const int x1 = rec_x(r1), y1 = rec_y(r1), d1 = rec_d(r1);
+    const int x2 = rec_x(r2), y2 = rec_y(r2), d2 = rec_d(r2);
+    const int x3 = rec_x(r3), y3 = rec_y(r3), d3 = rec_d(r3);
+    const int det_i = x1 * (y2 - y3) + x2 * (y3 - y1) + x3 * (y1 - y2);          // != 0 here
+    const long long ng_i = (long long)(d1 * (x2 * y3 - x3 * y2)) + (long long)(d2 * (x3 * y1 - x1 * y3)) +
+                           (long long)(d3 * (x1 * y2 - x2 * y1));                 // each product < 2^31, sum < 2^33
+    TrialPlane h;
+    h.na = d1 * (y2 - y3) + d2 * (y3 - y1) + d3 * (y1 - y2);                      // |.| < 2^21
+    h.nb = d1 * (x3 - x2) + d2 * (x1 - x3) + d3 * (x2 - x1);
+    // |Na x + Nb y + Ng| < 2^35, so 2^40 + it is a positive integer below 2^52: put it in the mantissa of 2^52
+    h.base = ng_i + (1ll << 40) + (0x43300000ll << 32);
+    h.det = (double)det_i;
+    double acc0 = 0.0, acc1 = 0.0;
     bool bad = false;
-#pragma unroll 4
-    for (int j = lane; j < S; j += 32) {
-        uint32_t idx;
-        if (EXPLICIT) {
+    if (EXPLICIT) {
+        for (int j = lane; j < S; j += 32) {
             int i = __ldg(samp + j);
             bad |= (i < 0 || (uint32_t)i >= M);
-            idx = bad ? 0u : (uint32_t)i;
-        } else {
-            idx = perm_draw(pk, (uint32_t)j, M);
+            acc0 += sample_term<STAGED>(h, bad ? 0u : (uint32_t)i, rec, stride, s_rec_addr, s_invd_addr);
         }
-        uint32_t r = src[(int64_t)idx * src_stride];
-        double s = s_Z[r >> 22 & 0xFFu] * fma(af, u2d(r & 0x7FFu), fma(bf, u2d(r >> 11 & 0x7FFu), c2));
-        acc += fabs(s - 1.0);
+    } else {
+        const PermKey pk = make_perm(key, bits);
+        int j0 = lane;
+        for (; j0 + 96 < S; j0 += 128) {                                          // four draws per lane, no bounds to test
+            uint32_t v0 = perm_once(pk, (uint32_t)j0), v1 = perm_once(pk, (uint32_t)j0 + 32u),
+                     v2 = perm_once(pk, (uint32_t)j0 + 64u), v3 = perm_once(pk, (uint32_t)j0 + 96u);
+            if (max(max(v0, v1), max(v2, v3)) >= M) {                             // cycle walk, rare (2^bits - M of 2^bits draws)
+                while (v0 >= M) v0 = perm_once(pk, v0);
+                while (v1 >= M) v1 = perm_once(pk, v1);
+                while (v2 >= M) v2 = perm_once(pk, v2);
+                while (v3 >= M) v3 = perm_once(pk, v3);
+            }
+            const double t0 = sample_term<STAGED>(h, v0, rec, stride, s_rec_addr, s_invd_addr);
+            const double t1 = sample_term<STAGED>(h, v1, rec, stride, s_rec_addr, s_invd_addr);
+            const double t2 = sample_term<STAGED>(h, v2, rec, stride, s_rec_addr, s_invd_addr);
+            const double t3 = sample_term<STAGED>(h, v3, rec, stride, s_rec_addr, s_invd_addr);
+            acc0 += t0 + t2;
+            acc1 += t1 + t3;
+        }
+        for (; j0 < S; j0 += 32) {                                                // the ragged end
+            uint32_t v = perm_once(pk, (uint32_t)j0);
+            while (v >= M) v = perm_once(pk, v);
+            acc0 += sample_term<STAGED>(h, v, rec, stride, s_rec_addr, s_invd_addr);
+        }
     }
-    acc = warp_sum(acc);
+    double acc = warp_sum(acc0 + acc1);
     bad = __any_sync(0xffffffffu, bad);
     if (lane == 0) {
-        double e = acc / ((double)S * sqrt(a * a + b * b + c * c));
-        *err_out = (bad || isnan(e)) ? INFINITY : e;              // NaN never beats bestError, :291
+        const double Na = (double)h.na, Nb = (double)h.nb, Ng = (double)ng_i;
+        const double A = cam.f * Na, B = cam.f * Nb, C = Ng + cam.cw * Na + cam.ch * Nb;
+        const double e = acc * fB_over_S * rsqrt(A * A + B * B + C * C);
+        *err_out = (bad || !(e < INFINITY)) ? INFINITY : e;       // NaN never beats bestError, :291
     }
 }
 
-// variant 1: gathers from global memory (L2); 8 hypotheses per block
-template <bool EXPLICIT>
-__global__ void __launch_bounds__(RANSAC_THREADS)
-ransac_score_kernel(const uint32_t *__restrict__ mcloud, int stride, int64_t slab_records,
-                    const int32_t *__restrict__ counts, int cstride, int ccol,
-                    int T, int S, CamD cam,
-                    const int32_t *__restrict__ sample_idx, const int32_t *__restrict__ triple_idx,
-                    uint64_t seed, int frame0, double *__restrict__ errors) {
-    __shared__ double s_Z[256];
-    s_Z[threadIdx.x] = threadIdx.x ? exact_Z(cam, threadIdx.x) : 0.0;
-    __syncthreads();
-    const int f = blockIdx.y;
-    const int lane = threadIdx.x & 31;
-    const int t = blockIdx.x * RANSAC_WARPS + (threadIdx.x >> 5);
-    if (t >= T) return;
-    const int Mi = counts[(int64_t)f * cstride + ccol];
-    double *err_out = errors + (int64_t)f * T + t;
-    if (Mi < S || Mi < 1 || S < 1) {                              // random.sample raises, :286,294
-        if (lane == 0) *err_out = INFINITY;
-        return;
-    }
-    const uint32_t *rec = mcloud + (int64_t)f * slab_records * stride;
-    score_trial<EXPLICIT>(rec, stride, rec, stride, (uint32_t)Mi, bits_for((uint32_t)Mi), S, cam, 1.0 / cam.f, s_Z,
-                          EXPLICIT ? sample_idx + ((int64_t)f * T + t) * S : nullptr,
-                          EXPLICIT ? triple_idx + ((int64_t)f * T + t) * 3 : nullptr,
-                          trial_key(seed, frame0 + f, t), lane, err_out);
+// ---- bulk (TMA) staging helpers: one elected thread copies global -> shared and an mbarrier counts the bytes
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t *bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
 }
 
-// variant 2: the frame's masked cloud (<= 4 bytes x max_m) is staged once per block in shared memory
-// and the block's warps share it for T/gridDim.x hypotheses each; the S gathers of a hypothesis are
-// shared-memory reads (no 32-byte-sector over-fetch from L2).
+// Persistent kernel: block b owns the contiguous range [b, b+1) * F*T/gridDim.x of the (frame, trial) pairs,
+// i.e. a few consecutive frames.  Entering a frame it stages that frame's masked cloud (<= 4 bytes x max_m)
+// in shared memory with bulk copies (TMA), then its 32 warps share it: the S gathers of a hypothesis are
+// shared-memory reads (no 32-byte-sector over-fetch from L2).  Frames that do not fit (or whose records
+// are strided) gather from global memory instead.
 #define RANSAC_SMEM_THREADS 1024
+#define RANSAC_BULK_BYTES 32768u
 template <bool EXPLICIT>
 __global__ void __launch_bounds__(RANSAC_SMEM_THREADS, 1)
-ransac_score_smem_kernel(const uint32_t *__restrict__ mcloud, int stride, int64_t slab_records,
-                         const int32_t *__restrict__ counts, int cstride, int ccol,
-                         int T, int S, int cap, CamD cam,
-                         const int32_t *__restrict__ sample_idx, const int32_t *__restrict__ triple_idx,
-                         uint64_t seed, int frame0, double *__restrict__ errors) {
-    extern __shared__ __align__(16) uint32_t s_rec[];
-    __shared__ double s_Z[256];
-    const int f = blockIdx.y;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = RANSAC_SMEM_THREADS / 32;
-    const int Mi = counts[(int64_t)f * cstride + ccol];
-    const uint32_t *rec = mcloud + (int64_t)f * slab_records * stride;
-    const bool none = (Mi < S || Mi < 1 || S < 1);
-    const bool staged = !none && Mi <= cap;
-    const int bits = bits_for((uint32_t)max(Mi, 1));
-    const double inv_f = 1.0 / cam.f;
-    if (threadIdx.x < 256) s_Z[threadIdx.x] = threadIdx.x ? exact_Z(cam, threadIdx.x) : 0.0;
-    if (staged) {
-        if (stride == 1 && ((((uintptr_t)rec) & 15) == 0)) {
-            const uint4 *src = (const uint4 *)rec;
-            int n4 = Mi >> 2;
-            for (int i = threadIdx.x; i < n4; i += RANSAC_SMEM_THREADS) ((uint4 *)s_rec)[i] = __ldg(src + i);
-            for (int i = (n4 << 2) + threadIdx.x; i < Mi; i += RANSAC_SMEM_THREADS) s_rec[i] = __ldg(rec + i);
-        } else {
-            for (int i = threadIdx.x; i < Mi; i += RANSAC_SMEM_THREADS) s_rec[i] = __ldg(rec + (int64_t)i * stride);
-        }
-    }
+ransac_score_persistent(const uint32_t *__restrict__ mcloud, int stride, int64_t slab_records,
+                        const int32_t *__restrict__ counts, int cstride, int ccol,
+                        int F, int T, int S, int cap, CamD cam,
+                        const int32_t *__restrict__ sample_idx, const int32_t *__restrict__ triple_idx,
+                        uint64_t seed, int frame0, double *__restrict__ errors) {
+    extern __shared__ __align__(128) uint32_t s_rec[];
+    __shared__ double s_invd[256];
+    __shared__ __align__(8) uint64_t s_bar;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = RANSAC_SMEM_THREADS / 32;
+    const int64_t total = (int64_t)F * T;
+    const int64_t w0 = total * blockIdx.x / gridDim.x, w1 = total * (blockIdx.x + 1) / gridDim.x;
+    if (tid < 256) s_invd[tid] = tid ? __ddiv_rn(1.0, (double)tid) : 0.0;
+    if (tid == 0) mbar_init(&s_bar, 1);
     __syncthreads();
-    // trials of this block: t = blockIdx.x + k * gridDim.x, dealt to the warps round-robin
-    for (int t = blockIdx.x + warp * gridDim.x; t < T; t += nwarps * gridDim.x) {
-        double *err_out = errors + (int64_t)f * T + t;
-        if (none) {
-            if (lane == 0) *err_out = INFINITY;
-            continue;
+    const double fB_over_S = cam.fB / (double)S;
+    const uint32_t s_rec_addr = smem_u32(s_rec), s_invd_addr = smem_u32(s_invd);
+    uint32_t phase = 0;
+    for (int64_t w = w0; w < w1;) {
+        const int f = (int)(w / T);
+        const int tb = (int)(w - (int64_t)f * T);                     // first trial of this segment
+        const int te = (int)min((int64_t)T, w1 - (int64_t)f * T);     // one past its last trial
+        const int Mi = counts[(int64_t)f * cstride + ccol];
+        const uint32_t *rec = mcloud + (int64_t)f * slab_records * stride;
+        const bool none = (Mi < S || Mi < 1 || S < 1);                // random.sample raises, :286,294
+        const bool staged = !none && Mi <= cap;
+        if (staged) {
+            const bool bulk = stride == 1 && ((((uintptr_t)rec) & 15) == 0);
+            const int nb = bulk ? (Mi & ~3) : 0;                      // records moved by bulk copies
+            if (bulk && tid == 0 && nb > 0) {
+                const uint32_t bytes = (uint32_t)nb * 4u;
+                mbar_expect_tx(&s_bar, bytes);
+                for (uint32_t o = 0; o < bytes; o += RANSAC_BULK_BYTES)
+                    bulk_g2s((char *)s_rec + o, (const char *)rec + o, min(RANSAC_BULK_BYTES, bytes - o), &s_bar);
+            }
+            for (int i = nb + tid; i < Mi; i += RANSAC_SMEM_THREADS) s_rec[i] = __ldg(rec + (int64_t)i * stride);
+            if (bulk && nb > 0) { mbar_wait(&s_bar, phase); phase ^= 1u; }
+            __syncthreads();
         }
-        score_trial<EXPLICIT>(rec, stride, staged ? s_rec : rec, staged ? 1 : stride, (uint32_t)Mi, bits, S, cam, inv_f, s_Z,
-                              EXPLICIT ? sample_idx + ((int64_t)f * T + t) * S : nullptr,
-                              EXPLICIT ? triple_idx + ((int64_t)f * T + t) * 3 : nullptr,
-                              trial_key(seed, frame0 + f, t), lane, err_out);
+        const int bits = bits_for((uint32_t)max(Mi, 1));
+        for (int t = tb + warp; t < te; t += nwarps) {
+            double *err_out = errors + (int64_t)f * T + t;
+            if (none) {
+                if (lane == 0) *err_out = INFINITY;
+                continue;
+            }
+            const int32_t *samp = EXPLICIT ? sample_idx + ((int64_t)f * T + t) * S : nullptr;
+            const int32_t *trip = EXPLICIT ? triple_idx + ((int64_t)f * T + t) * 3 : nullptr;
+            const uint32_t key = trial_key(seed, frame0 + f, t);
+            if (staged) score_trial<EXPLICIT, true>(rec, stride, s_rec_addr, (uint32_t)Mi, bits, S, cam, fB_over_S, s_invd_addr, samp, trip, key, lane, err_out);
+            else        score_trial<EXPLICIT, false>(rec, stride, s_rec_addr, (uint32_t)Mi, bits, S, cam, fB_over_S, s_invd_addr, samp, trip, key, lane, err_out);
+        }
+        w = (int64_t)f * T + te;
+        if (w < w1) __syncthreads();                                  // everyone is done with this frame's records
     }
 }
 
@@ -319,42 +395,31 @@ extern "C" int svb_ransac_score(const uint32_t *mcloud, int rec_stride_words, in
     cudaStream_t st = (cudaStream_t)stream;
     CamD c = make_camd(cam);
     ProfScope ps(K_RANSAC_SCORE, st);
-    const size_t smem = (((size_t)max_m + 3) & ~(size_t)3) * sizeof(uint32_t);
-    if (max_m > 0 && smem <= 200 * 1024 && T >= 64) {
-        // blocks per frame: enough blocks for ~8 rounds over the SMs (1 block per SM), at least 32 trials each
-        int dev = 0, sms = 148;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        int per_frame = (8 * sms + F - 1) / F;
-        if (per_frame > T / 32) per_frame = T / 32;
-        if (per_frame < 1) per_frame = 1;
-        dim3 grid(per_frame, F);
-        cudaError_t e;
-        if (sample_idx) {
-            e = cudaFuncSetAttribute(ransac_score_smem_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-            if (e != cudaSuccess) return (int)e;
-            ransac_score_smem_kernel<true><<<grid, RANSAC_SMEM_THREADS, smem, st>>>(
-                mcloud, rec_stride_words, slab_stride_records, counts, counts_stride, counts_col, T, S, max_m, c,
-                sample_idx, triple_idx, rng_seed, frame0, errors);
-        } else {
-            e = cudaFuncSetAttribute(ransac_score_smem_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-            if (e != cudaSuccess) return (int)e;
-            ransac_score_smem_kernel<false><<<grid, RANSAC_SMEM_THREADS, smem, st>>>(
-                mcloud, rec_stride_words, slab_stride_records, counts, counts_stride, counts_col, T, S, max_m, c,
-                nullptr, nullptr, rng_seed, frame0, errors);
-        }
-        SVB_LAUNCH_CHECK();
-        return SVB_OK;
+    // shared-memory staging when the largest frame fits; otherwise cap = 0 and every gather goes to L2
+    size_t smem = (((size_t)max_m + 3) & ~(size_t)3) * sizeof(uint32_t);
+    int cap = max_m;
+    if (max_m == 0 || smem > 200 * 1024) { smem = 16; cap = 0; }
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    // one persistent block per SM, but never fewer than ~2 trials per warp in a block
+    int64_t total = (int64_t)F * T;
+    int blocks = (int)min((int64_t)sms, (total + 63) / 64);
+    if (blocks < 1) blocks = 1;
+    cudaError_t e;
+    if (sample_idx) {
+        e = cudaFuncSetAttribute(ransac_score_persistent<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return (int)e;
+        ransac_score_persistent<true><<<blocks, RANSAC_SMEM_THREADS, smem, st>>>(
+            mcloud, rec_stride_words, slab_stride_records, counts, counts_stride, counts_col, F, T, S, cap, c,
+            sample_idx, triple_idx, rng_seed, frame0, errors);
+    } else {
+        e = cudaFuncSetAttribute(ransac_score_persistent<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return (int)e;
+        ransac_score_persistent<false><<<blocks, RANSAC_SMEM_THREADS, smem, st>>>(
+            mcloud, rec_stride_words, slab_stride_records, counts, counts_stride, counts_col, F, T, S, cap, c,
+            nullptr, nullptr, rng_seed, frame0, errors);
     }
-    dim3 grid((T + RANSAC_WARPS - 1) / RANSAC_WARPS, F);
-    if (sample_idx)
-        ransac_score_kernel<true><<<grid, RANSAC_THREADS, 0, st>>>(mcloud, rec_stride_words, slab_stride_records, counts,
-                                                                   counts_stride, counts_col, T, S, c, sample_idx,
-                                                                   triple_idx, rng_seed, frame0, errors);
-    else
-        ransac_score_kernel<false><<<grid, RANSAC_THREADS, 0, st>>>(mcloud, rec_stride_words, slab_stride_records, counts,
-                                                                    counts_stride, counts_col, T, S, c, nullptr,
-                                                                    nullptr, rng_seed, frame0, errors);
     SVB_LAUNCH_CHECK();
     return SVB_OK;
 }

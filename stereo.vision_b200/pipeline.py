@@ -4,8 +4,9 @@
 (functions.py of this package).  One call enqueues, on the current CUDA stream and without any host
 synchronisation:
 
-    svb_fill_sequence    a1      temporal fill (the only cross-frame dependency, walked in-kernel)
-    svb_project_compact  a2-a4   count / scan / write: cloud (8 B records) + masked cloud (4 B)
+    svb_fill_sequence_counted    a1    temporal fill (the only cross-frame dependency, walked in-kernel)
+                                       + the site counts of a4 (the bytes are in registers anyway)
+    svb_project_compact_counted  a2-a4 scan / write: cloud (8 B records) + masked cloud (4 B)
     svb_ransac_score     a5-a7   T hypotheses x S samples per frame, one warp per hypothesis
     svb_ransac_finalize          first-minimum arg-min, winning plane, exact threshold cutoff
     svb_road_points      a8-a14  near-plane test + hue histogram, colour filter + reprojection + mask
@@ -20,7 +21,7 @@ import torch
 from . import _native as N
 from .camera import DEFAULT_CAMERA, Camera
 
-KERNELS_PER_BATCH = 7      # fill, count, scan, write, score, finalize, fused road kernel (8 on the two-pass road path)
+KERNELS_PER_BATCH = 6      # fill+count, scan, write, score, finalize, fused road kernel (+1 on the two-pass road path)
 
 
 def _as_cuda_u8(x, device):
@@ -127,15 +128,19 @@ class RoadPath:
         H, W, st = self.H, self.W, N.stream_ptr()
         res = BatchResult(self, F)
         if fill:
+            # a1 + the counting pass of a4 in one kernel; the scratch carries the counts to the projection
             prev_t = _as_cuda_u8(prev, dev) if prev is not None else None
-            N.check(lib.svb_fill_sequence(N.ptr(disp), N.ptr(prev_t), N.ptr(self.filled), F, H, W, st), "svb_fill_sequence")
-            src = self.filled
+            N.check(lib.svb_fill_sequence_counted(N.ptr(disp), N.ptr(prev_t), N.ptr(self.filled), N.ptr(self.carmask),
+                                                  F, H, W, self.step, N.ptr(self.scratch), self.scratch.numel(), st),
+                    "svb_fill_sequence_counted")
+            project = lib.svb_project_compact_counted
         else:
             self.filled[:F].copy_(disp)
-            src = self.filled
-        N.check(lib.svb_project_compact(N.ptr(src), N.ptr(self.carmask), N.ptr(bgr), F, H, W, self.step,
-                                        C.byref(self._cam), N.ptr(self.cloud), N.ptr(self.mcloud), N.ptr(self.counts),
-                                        N.ptr(self.scratch), self.scratch.numel(), st), "svb_project_compact")
+            project = lib.svb_project_compact
+        src = self.filled
+        N.check(project(N.ptr(src), N.ptr(self.carmask), N.ptr(bgr), F, H, W, self.step,
+                        C.byref(self._cam), N.ptr(self.cloud), N.ptr(self.mcloud), N.ptr(self.counts),
+                        N.ptr(self.scratch), self.scratch.numel(), st), "svb_project_compact")
         si = ti = None
         if indices is not None:
             si = indices[0] if torch.is_tensor(indices[0]) else torch.from_numpy(np.ascontiguousarray(indices[0], dtype=np.int32))
@@ -156,7 +161,7 @@ class RoadPath:
                                     C.byref(self._cam), self.colour_threshold, N.ptr(self.reproj_bits), N.ptr(self.hist), N.ptr(self.road_mask),
                                     N.ptr(ov), N.ptr(self.counts), N.ptr(self.scratch), self.scratch.numel(), st),
                 "svb_road_points")
-        N.count(KERNELS_PER_BATCH if self.fused_road else KERNELS_PER_BATCH + 1)
+        N.count(KERNELS_PER_BATCH + (0 if self.fused_road else 1) + (0 if fill else 2))   # no fill: copy + count kernels
         return res
 
     def dump_indices(self, F, seed=0, frame0=0):
