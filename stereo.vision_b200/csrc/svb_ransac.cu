@@ -30,32 +30,41 @@ __host__ __device__ __forceinline__ uint32_t trial_key(uint64_t seed, int frame,
     k = mix32(k ^ (uint32_t)trial ^ 0x85EBCA6Bu);
     return k;
 }
-// keyed bijection of [0, 2^bits): (odd multiply + add) and xor-shift by >= bits/2 are both invertible
-// modulo 2^bits; multiply-add, xor-shift, multiply, then cycle-walk into [0, m).  The three
-// multipliers/offset are derived once per hypothesis from its key, so a draw costs ~8 integer instructions.
-struct PermKey { uint32_t A, B, C, mask; int sh; };
-__host__ __device__ __forceinline__ PermKey make_perm(uint32_t key, int bits) {
-    PermKey k;
-    k.A = mix32(key ^ 0x51ED270Bu) | 1u;
-    k.B = mix32(key + 0x9E3779B9u);
-    k.C = mix32(key + 0x3C6EF372u) | 1u;
-    k.mask = (bits >= 32) ? 0xFFFFFFFFu : ((1u << bits) - 1u);
-    k.sh = (bits + 1) >> 1;
-    return k;
+// The S sample points of a trial (throughput mode): a systematic sample of the masked cloud,
+//   index_j = (start + j * stride) mod M,   j = 0 .. S-1,
+// with a per-trial uniform start and a per-trial stride drawn from 256 primes in (1024, 8300).  A prime
+// that does not divide M is coprime to it, so the S <= M indices are distinct (random.sample draws without
+// replacement, functions.py:286) and every point has the same chance S/M of being in a trial's sample.
+// A draw costs three integer instructions (add, subtract, min) instead of a hash per sample, and the 32
+// lanes of a warp hit 32 different shared-memory banks (the stride is odd).
+__constant__ uint32_t c_stride_primes[256] = {
+    1031, 1049, 1063, 1093, 1109, 1129, 1171, 1193, 1223, 1237, 1277, 1291, 1303, 1327, 1373, 1409,
+    1433, 1451, 1481, 1489, 1511, 1549, 1567, 1597, 1609, 1621, 1663, 1693, 1721, 1741, 1759, 1789,
+    1823, 1867, 1877, 1901, 1933, 1973, 1997, 2011, 2029, 2069, 2087, 2113, 2137, 2153, 2207, 2237,
+    2267, 2281, 2297, 2339, 2351, 2381, 2393, 2417, 2447, 2473, 2531, 2549, 2579, 2617, 2647, 2671,
+    2687, 2699, 2719, 2741, 2777, 2797, 2819, 2851, 2879, 2909, 2939, 2963, 3001, 3023, 3061, 3083,
+    3119, 3167, 3187, 3217, 3251, 3259, 3307, 3323, 3347, 3371, 3391, 3449, 3463, 3499, 3527, 3539,
+    3559, 3583, 3617, 3637, 3671, 3697, 3719, 3761, 3779, 3803, 3847, 3863, 3907, 3919, 3931, 3989,
+    4007, 4027, 4057, 4091, 4127, 4139, 4177, 4217, 4231, 4259, 4273, 4327, 4349, 4373, 4421, 4447,
+    4481, 4507, 4519, 4561, 4591, 4621, 4649, 4663, 4703, 4729, 4759, 4793, 4813, 4871, 4903, 4931,
+    4951, 4969, 4999, 5011, 5039, 5081, 5101, 5147, 5171, 5197, 5233, 5273, 5303, 5333, 5381, 5407,
+    5419, 5443, 5477, 5501, 5521, 5557, 5581, 5639, 5651, 5669, 5693, 5737, 5749, 5791, 5821, 5843,
+    5861, 5879, 5903, 5953, 6007, 6043, 6067, 6089, 6121, 6143, 6197, 6211, 6229, 6269, 6287, 6317,
+    6337, 6359, 6379, 6421, 6469, 6491, 6547, 6569, 6581, 6637, 6661, 6689, 6709, 6737, 6781, 6803,
+    6829, 6863, 6883, 6917, 6959, 6971, 6997, 7019, 7057, 7103, 7127, 7177, 7207, 7229, 7247, 7297,
+    7331, 7351, 7417, 7457, 7481, 7507, 7529, 7549, 7573, 7589, 7621, 7649, 7687, 7703, 7727, 7759,
+    7817, 7853, 7877, 7901, 7933, 7951, 8011, 8053, 8081, 8101, 8123, 8171, 8209, 8231, 8263, 8287};
+struct Draws { uint32_t start, stride; };
+__device__ __forceinline__ Draws make_draws(uint32_t key, uint32_t M) {
+    Draws d;
+    d.start = __umulhi(mix32(key ^ 0x51ED270Bu), M);
+    uint32_t k = mix32(key + 0x9E3779B9u) & 255u, p = c_stride_primes[k];
+    for (int tries = 0; tries < 256 && M % p == 0u; ++tries) { k = (k + 1u) & 255u; p = c_stride_primes[k]; }
+    d.stride = p % M;                                   // gcd(p mod M, M) = gcd(p, M) = 1
+    return d;
 }
-__host__ __device__ __forceinline__ uint32_t perm_draw(const PermKey &k, uint32_t i, uint32_t m) {
-    uint32_t v = i;
-    do {
-        v = (v * k.A + k.B) & k.mask;
-        v ^= v >> k.sh;
-        v = (v * k.C) & k.mask;
-    } while (v >= m);
-    return v;
-}
-__host__ __device__ __forceinline__ int bits_for(uint32_t m) {       // smallest b >= 2 with 2^b >= m
-    int b = 2;
-    while ((1u << b) < m) ++b;
-    return b;
+__device__ __forceinline__ uint32_t draw_index(const Draws &d, uint32_t j, uint32_t M) {
+    return (uint32_t)(((unsigned long long)d.start + (unsigned long long)j * d.stride) % M);
 }
 __device__ __forceinline__ uint32_t uniform_draw(uint32_t key, uint32_t ctr, uint32_t m) {
     return __umulhi(mix32(key ^ mix32(ctr + 0x632BE5ABu)), m);
@@ -187,15 +196,9 @@ __device__ __forceinline__ bool warp_triple(const uint32_t *__restrict__ rec, in
 
 // One warp scores one trial.  STAGED: the S sample gathers read the frame's records from shared memory
 // (s_rec, stride 1); otherwise from global memory (L2).  Writes the mean error (or +inf) to *err_out.
-// Per sample: one keyed-permutation draw (6 integer instructions + a shared check for the rare cycle
-// walk), one gather, and  |(Na x + Nb y + Ng)/d - det|  as two 32x32+64 integer multiply-adds whose
+// Per sample: one draw (add, subtract, min), one gather, and  |(Na x + Nb y + Ng)/d - det|  as two 32x32+64 integer multiply-adds whose
 // 64-bit result IS the bit pattern of the double 2^52 + 2^40 + (Na x + Nb y + Ng) (the bias and the
 // exponent are folded into the addend), one subtraction, one fma with the table value 1/d, one add.
-__device__ __forceinline__ uint32_t perm_once(const PermKey &k, uint32_t v) {
-    v = (v * k.A + k.B) & k.mask;
-    v ^= v >> k.sh;
-    return (v * k.C) & k.mask;
-}
 __device__ __forceinline__ long long mad_wide(int a, int b, long long c) {       // a * b + c, signed 32 x 32 + 64
     long long r;
     asm("mad.wide.s32 %0, %1, %2, %3;" : "=l"(r) : "r"(a), "r"(b), "l"(c));
@@ -230,7 +233,7 @@ __device__ __forceinline__ double sample_term(const TrialPlane &h, uint32_t idx,
 
 template <bool EXPLICIT, bool STAGED>
 __device__ __forceinline__ void score_trial(const uint32_t *__restrict__ rec, int stride, uint32_t s_rec_addr,
-                                            uint32_t M, int bits, int S, const CamD &cam, double fB_over_S, uint32_t s_invd_addr,
+                                            uint32_t M, int S, const CamD &cam, double fB_over_S, uint32_t s_invd_addr,
                                             const int32_t *__restrict__ samp, const int32_t *__restrict__ trip,
                                             uint32_t key, int lane, double *err_out) {
     uint32_t r1, r2, r3;
@@ -259,17 +262,14 @@ __device__ __forceinline__ void score_trial(const uint32_t *__restrict__ rec, in
             acc0 += sample_term<STAGED>(h, bad ? 0u : (uint32_t)i, rec, stride, s_rec_addr, s_invd_addr);
         }
     } else {
-        const PermKey pk = make_perm(key, bits);
+        const Draws dr = make_draws(key, M);
+        uint32_t v = draw_index(dr, (uint32_t)lane, M);                           // this lane's first index
+        const uint32_t hop = (uint32_t)((32ull * dr.stride) % M);                // index_{j+32} - index_j (mod M)
+        auto next = [&](uint32_t x) { x += hop; return min(x, x - M); };         // x < M: x - M wraps above x
         int j0 = lane;
         for (; j0 + 96 < S; j0 += 128) {                                          // four draws per lane, no bounds to test
-            uint32_t v0 = perm_once(pk, (uint32_t)j0), v1 = perm_once(pk, (uint32_t)j0 + 32u),
-                     v2 = perm_once(pk, (uint32_t)j0 + 64u), v3 = perm_once(pk, (uint32_t)j0 + 96u);
-            if (max(max(v0, v1), max(v2, v3)) >= M) {                             // cycle walk, rare (2^bits - M of 2^bits draws)
-                while (v0 >= M) v0 = perm_once(pk, v0);
-                while (v1 >= M) v1 = perm_once(pk, v1);
-                while (v2 >= M) v2 = perm_once(pk, v2);
-                while (v3 >= M) v3 = perm_once(pk, v3);
-            }
+            const uint32_t v0 = v, v1 = next(v0), v2 = next(v1), v3 = next(v2);
+            v = next(v3);
             const double t0 = sample_term<STAGED>(h, v0, rec, stride, s_rec_addr, s_invd_addr);
             const double t1 = sample_term<STAGED>(h, v1, rec, stride, s_rec_addr, s_invd_addr);
             const double t2 = sample_term<STAGED>(h, v2, rec, stride, s_rec_addr, s_invd_addr);
@@ -278,9 +278,8 @@ __device__ __forceinline__ void score_trial(const uint32_t *__restrict__ rec, in
             acc1 += t1 + t3;
         }
         for (; j0 < S; j0 += 32) {                                                // the ragged end
-            uint32_t v = perm_once(pk, (uint32_t)j0);
-            while (v >= M) v = perm_once(pk, v);
             acc0 += sample_term<STAGED>(h, v, rec, stride, s_rec_addr, s_invd_addr);
+            v = next(v);
         }
     }
     double acc = warp_sum(acc0 + acc1);
@@ -364,7 +363,6 @@ ransac_score_persistent(const uint32_t *__restrict__ mcloud, int stride, int64_t
             if (bulk && nb > 0) { mbar_wait(&s_bar, phase); phase ^= 1u; }
             __syncthreads();
         }
-        const int bits = bits_for((uint32_t)max(Mi, 1));
         for (int t = tb + warp; t < te; t += nwarps) {
             double *err_out = errors + (int64_t)f * T + t;
             if (none) {
@@ -374,8 +372,8 @@ ransac_score_persistent(const uint32_t *__restrict__ mcloud, int stride, int64_t
             const int32_t *samp = EXPLICIT ? sample_idx + ((int64_t)f * T + t) * S : nullptr;
             const int32_t *trip = EXPLICIT ? triple_idx + ((int64_t)f * T + t) * 3 : nullptr;
             const uint32_t key = trial_key(seed, frame0 + f, t);
-            if (staged) score_trial<EXPLICIT, true>(rec, stride, s_rec_addr, (uint32_t)Mi, bits, S, cam, fB_over_S, s_invd_addr, samp, trip, key, lane, err_out);
-            else        score_trial<EXPLICIT, false>(rec, stride, s_rec_addr, (uint32_t)Mi, bits, S, cam, fB_over_S, s_invd_addr, samp, trip, key, lane, err_out);
+            if (staged) score_trial<EXPLICIT, true>(rec, stride, s_rec_addr, (uint32_t)Mi, S, cam, fB_over_S, s_invd_addr, samp, trip, key, lane, err_out);
+            else        score_trial<EXPLICIT, false>(rec, stride, s_rec_addr, (uint32_t)Mi, S, cam, fB_over_S, s_invd_addr, samp, trip, key, lane, err_out);
         }
         w = (int64_t)f * T + te;
         if (w < w1) __syncthreads();                                  // everyone is done with this frame's records
@@ -444,9 +442,8 @@ __global__ void ransac_dump_kernel(const uint32_t *__restrict__ mcloud, int stri
     const uint32_t M = (uint32_t)Mi;
     const uint32_t *rec = mcloud + (int64_t)f * slab_records * stride;
     const uint32_t key = trial_key(seed, frame0 + f, t);
-    const int bits = bits_for(M);
-    const PermKey pk = make_perm(key, bits);
-    for (int j = lane; j < S; j += 32) samp[j] = (int32_t)perm_draw(pk, (uint32_t)j, M);
+    const Draws dr = make_draws(key, M);
+    for (int j = lane; j < S; j += 32) samp[j] = (int32_t)draw_index(dr, (uint32_t)j, M);
     P3 p1, p2, p3;
     int tri[3] = {-1, -1, -1};
     bool ok = trial_triple(rec, stride, M, cam, nullptr, key, p1, p2, p3, tri);
