@@ -25,7 +25,7 @@ bool g_svb_prof_on = false;
 static const char *k_names[K_COUNT_] = {
     "fill_seq", "mask_disp", "proj_count", "proj_scan", "proj_write", "cloud_export", "ransac_score",
     "ransac_dump", "ransac_finalize", "point_errors", "compact_cloud", "hue_hist", "hue_bins", "reproject",
-    "scatter_points", "road_pass1", "road_pass2", "road_clear", "road_cluster"};
+    "scatter_points", "road_pass1", "road_pass2", "road_clear", "road_cluster", "road_table", "road_near", "road_scatter"};
 struct EvPair { int id; cudaEvent_t a, b; };
 static std::vector<EvPair> g_events;
 static cudaEvent_t g_pending[K_COUNT_];

@@ -15,8 +15,11 @@
 #include <cooperative_groups.h>
 namespace cg = cooperative_groups;
 
-bool g_svb_force_two_pass = false;     // test hook: svb_debug_force_two_pass()
-extern "C" int svb_debug_force_two_pass(int on) { g_svb_force_two_pass = on != 0; return SVB_OK; }
+// test hook: 0 = automatic (displacement table given: cluster kernel when a CTA's near list fits in shared
+// memory, else the streamed path; no table: legacy two-pass kernels), 1 = legacy two-pass kernels,
+// 2 = cluster kernel if it fits, 3 = streamed path
+int g_svb_road_mode = 0;
+extern "C" int svb_debug_force_two_pass(int mode) { g_svb_road_mode = (mode < 0 || mode > 3) ? 0 : mode; return SVB_OK; }
 
 #define ROAD_THREADS 256
 #define ROAD_CHUNK 8192          // records per block in the fused passes
@@ -672,10 +675,361 @@ road_cluster_kernel(const uint64_t *__restrict__ cloud, const int32_t *__restric
     cluster_wait();
 }
 
+// ------------------------------------------------------------------ the streamed road path (any lattice size)
+// Three launches for all F frames, no inter-CTA synchronisation inside a kernel:
+//   road_params   (one CTA per frame)   pixel-form plane + candidate-test constants; zeroes the frame's histogram
+//   road_near     (one CTA per 8192 records, every warp its own pipeline) bulk-copies (TMA) 256-record slices
+//                                       into shared memory; per record one integer interval test on d; the
+//                                       candidates (about a third) are compacted per warp and finished DENSE:
+//                                       filtered float64 plane test, hue bin + histogram, reprojection -> one
+//                                       word per near point, stored coalesced into the slice's part of the list
+//   road_scatter  (4 slices per warp)   colour filter of the listed points, 255 into the mask
+// A record is read from HBM once; a near point costs 4 more bytes written and read back.
+#define RS_THREADS 256
+#define RS_WARPS (RS_THREADS / 32)
+#define RS_CHUNK 2048                    // records per CTA
+#define RS_PER_WARP (RS_CHUNK / RS_WARPS)
+
+struct StreamGeom {
+    int H, W;
+    int64_t slab;        // records per frame slab (= lattice size)
+    int chunks;          // RS_CHUNK-record chunks per frame
+    int ctas;            // CTAs per frame in road_near (RS_NCH chunks each)
+    int sctas;           // CTAs per frame in road_scatter
+    int step;
+    int64_t mask_per;    // mask bytes cleared by one road_near CTA (multiple of 16)
+};
+#define RS_NCH 4                         // chunks per road_near CTA (double-buffered)
+#define RS_FP_STRIDE 8                   // doubles per frame in the parameter block, see road_params_kernel
+
+static StreamGeom make_stream_geom(int H, int W, int step) {
+    StreamGeom g;
+    g.H = H; g.W = W; g.step = step;
+    int LH = svb_lattice_rows(H, step), LW = svb_lattice_cols(W, step);
+    g.slab = (int64_t)LH * LW;
+    g.chunks = (int)((g.slab + RS_CHUNK - 1) / RS_CHUNK);
+    if (g.chunks < 1) g.chunks = 1;
+    g.ctas = (g.chunks + RS_NCH - 1) / RS_NCH;
+    g.sctas = (g.chunks * RS_WARPS + RS_WARPS * 4 - 1) / (RS_WARPS * 4);      // RS_SC_SLICES slices per warp
+    int64_t bytes = (int64_t)H * W;
+    g.mask_per = ((bytes + g.ctas - 1) / g.ctas + 15) & ~(int64_t)15;
+    return g;
+}
+
+// the frame's plane in pixel form:  P.abc - 1 = Z(d) (af x + bf y + c2) - 1
+struct PixPlane { double af, bf, c2, cut_lo, cut_hi; };
+__device__ __forceinline__ PixPlane pix_plane(const double *pl, const CamD &cam, int H, int W) {
+    PixPlane q;
+    const double a = pl[0], b = pl[1], c = pl[2], cutoff = pl[4];
+    q.af = a / cam.f; q.bf = b / cam.f;
+    q.c2 = c - q.af * cam.cw - q.bf * cam.ch;
+    // ~1e5 x the worst-case rounding difference between this factored form and the reference's operation sequence
+    const double band = 1e-11 * fma(cam.fB, fabs(q.af) * (double)(W + cam.cw) + fabs(q.bf) * (double)(H + cam.ch) + fabs(c) + fabs(q.c2), 1.0);
+    q.cut_lo = cutoff - band; q.cut_hi = cutoff + band;
+    return q;
+}
+
+// Per frame: the pixel-form plane and what the candidate test of road_near needs (fparam), Z(d) (ztab,
+// block 0); zeroes the frame's histogram and its K / R counters.
+//   fparam[f] = af, bf, c2, cut_lo, cut_hi, fB/(1+cut) (1-1e-9), fB/(1-cut) (1+1e-9), bounds_ok
+// Candidate test.  From |Z t - 1| < cut with Z = fB/d, t = af x + bf y + c2:  t > 0 and
+// fB t/(1+cut) < d < fB t/(1-cut).  road_near bounds t over the pixel box of a 256-record slice (t is linear,
+// so its extremes sit at the box corners) and keeps the records whose d lies in the resulting interval.  Only a
+// SUPERSET of the near sites is needed -- the candidates are tested again with the filtered float64 predicate --
+// so the bounds are widened by 1e-9 relative and anything unusual (bounds_ok = 0) keeps every d.
+__global__ void __launch_bounds__(256)
+road_params_kernel(const double *__restrict__ planes, StreamGeom g, CamD cam,
+                   double *__restrict__ fparam, double *__restrict__ ztab,
+                   uint32_t *__restrict__ hist, int32_t *__restrict__ counts_out) {
+    const int f = blockIdx.x;
+    if (f == 0) ztab[threadIdx.x] = threadIdx.x ? exact_Z(cam, threadIdx.x) : 0.0;
+    for (int k = threadIdx.x; k < SVB_HIST_STRIDE; k += blockDim.x) hist[(int64_t)f * SVB_HIST_STRIDE + k] = 0;
+    if (threadIdx.x != 0) return;
+    counts_out[f * 4 + 2] = 0; counts_out[f * 4 + 3] = 0;
+    const double *pl = planes + (int64_t)f * SVB_PLANE_STRIDE;
+    double *fp = fparam + (int64_t)f * RS_FP_STRIDE;
+    if (pl[7] == 0.0) {
+        for (int k = 0; k < RS_FP_STRIDE; ++k) fp[k] = 0.0;
+        return;
+    }
+    const PixPlane q = pix_plane(pl, cam, g.H, g.W);
+    const double cut = q.cut_hi;
+    const bool ok = cut > 0.0 && cut < 0.5 && isfinite(q.af) && isfinite(q.bf) && isfinite(q.c2);
+    fp[0] = q.af; fp[1] = q.bf; fp[2] = q.c2; fp[3] = q.cut_lo; fp[4] = q.cut_hi;
+    fp[5] = ok ? cam.fB / (1.0 + cut) * (1.0 - 1e-9) : 0.0;
+    fp[6] = ok ? cam.fB / (1.0 - cut) * (1.0 + 1e-9) : 0.0;
+    fp[7] = ok ? 1.0 : 0.0;
+}
+
+// bulk (TMA) copy helpers: one elected thread copies global -> shared and an mbarrier counts the bytes
+__device__ __forceinline__ uint32_t rs_smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void rs_mbar_init(uint64_t *bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(rs_smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void rs_mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(rs_smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void rs_bulk_g2s(void *dst, const void *src, uint32_t bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(rs_smem_u32(dst)), "l"(src), "r"(bytes), "r"(rs_smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void rs_mbar_wait(uint64_t *bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(rs_smem_u32(bar)), "r"(parity) : "memory");
+}
+
+// Every WARP runs its own two-stage pipeline: lane 0 bulk-copies (TMA) the warp's next 256-record slice
+// into the warp's second buffer while the warp tests the current one; an mbarrier per buffer counts the
+// bytes.  No block-wide barrier in the loop -- a warp that meets many near points does not hold up the
+// other seven.  A CTA covers RS_NCH chunks = 32 slices; warp w takes slices w, w + 8, w + 16, w + 24.
+#define RS_SLICES (RS_NCH * RS_WARPS)    // slices per CTA
+__device__ __forceinline__ void rs_sts64(uint32_t addr, uint64_t v) {
+    asm volatile("st.shared.u64 [%0], %1;" ::"r"(addr), "l"(v) : "memory");
+}
+__device__ __forceinline__ uint64_t rs_lds64(uint32_t addr) {
+    uint64_t v;
+    asm volatile("ld.shared.u64 %0, [%1];" : "=l"(v) : "r"(addr) : "memory");
+    return v;
+}
+
+__global__ void __launch_bounds__(RS_THREADS, 4)
+road_near_kernel(const uint64_t *__restrict__ cloud, const int32_t *__restrict__ counts,
+                 const double *__restrict__ planes, StreamGeom g, CamD cam,
+                 const uint32_t *__restrict__ rbits,
+                 const double *__restrict__ fparam, const double *__restrict__ ztab,
+                 uint32_t *__restrict__ hist, uint8_t *__restrict__ road_mask,
+                 uint32_t *__restrict__ list, int32_t *__restrict__ warp_counts, int32_t *__restrict__ counts_out) {
+    __shared__ __align__(128) uint64_t s_rec[RS_WARPS][2][RS_PER_WARP];
+    __shared__ double s_Z[256];
+    __shared__ uint64_t s_stage[RS_WARPS][64];
+    __shared__ uint32_t s_h[SVB_HIST_STRIDE];
+    __shared__ __align__(8) uint64_t s_bar[RS_WARPS][2];
+    const int f = blockIdx.y, cta = blockIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const double *pl = planes + (int64_t)f * SVB_PLANE_STRIDE;
+    const bool valid = pl[7] != 0.0;
+    const int n = valid ? counts[f * 4 + 0] : 0;
+    const int slice0 = cta * RS_SLICES;                           // first slice of this CTA
+    const int frame_slices = g.chunks * RS_WARPS;
+    const uint64_t *frame = cloud + (int64_t)f * g.slab;
+    const bool bulk = ((((uintptr_t)frame) & 15) == 0);           // slice starts are multiples of 2 KB from here
+    const uint32_t rec_addr = rs_smem_u32(&s_rec[warp][0][0]), stage_addr = rs_smem_u32(&s_stage[warp][0]);
+
+    // records of the warp's i-th slice -> buffer i & 1: one bulk copy (the even part), an odd straggler by a plain load
+    auto issue = [&](int i) {
+        const int begin = (slice0 + warp + i * RS_WARPS) * RS_PER_WARP, m = min(RS_PER_WARP, n - begin);
+        if (m <= 0) return;
+        const int mb = bulk ? (m & ~1) : 0;
+        if (lane == 0 && mb > 0) {
+            rs_mbar_expect_tx(&s_bar[warp][i & 1], (uint32_t)mb * 8u);
+            rs_bulk_g2s(&s_rec[warp][i & 1][0], frame + begin, (uint32_t)mb * 8u, &s_bar[warp][i & 1]);
+        }
+        for (int k = mb + lane; k < m; k += 32) s_rec[warp][i & 1][k] = __ldcs((const unsigned long long *)(frame + begin + k));
+    };
+    if (lane == 0) {
+        rs_mbar_init(&s_bar[warp][0], 1);
+        rs_mbar_init(&s_bar[warp][1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
+    issue(0);
+    for (int k = tid; k < SVB_HIST_STRIDE; k += RS_THREADS) s_h[k] = 0;
+    s_Z[tid] = __ldg(ztab + tid);
+
+    // this CTA's share of the mask clear (replaces a memset launch)
+    {
+        const int64_t bytes = (int64_t)g.H * g.W;
+        uint8_t *mask = road_mask + (int64_t)f * bytes;
+        const int64_t b0 = min(bytes, g.mask_per * cta), b1 = min(bytes, b0 + g.mask_per);
+        if ((((uintptr_t)mask) & 15) == 0) {
+            const uint4 z = make_uint4(0, 0, 0, 0);
+            const int64_t v1 = b0 + ((b1 - b0) & ~(int64_t)15);
+            for (int64_t o = b0 + (int64_t)tid * 16; o < v1; o += RS_THREADS * 16) *(uint4 *)(mask + o) = z;
+            for (int64_t o = v1 + tid; o < b1; o += RS_THREADS) mask[o] = 0;
+        } else {
+            for (int64_t o = b0 + tid; o < b1; o += RS_THREADS) mask[o] = 0;
+        }
+    }
+    __syncthreads();                                              // histogram zeroed, Z(d) staged
+
+    const double *fp = fparam + (int64_t)f * RS_FP_STRIDE;
+    const double af = fp[0], bf = fp[1], c2 = fp[2], cut_lo = fp[3], cut_hi = fp[4];
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    int ktotal = 0;
+
+    for (int i = 0; i < RS_NCH; ++i) {
+        const int slice = slice0 + warp + i * RS_WARPS;
+        if (slice >= frame_slices) break;
+        const int begin = slice * RS_PER_WARP, m = min(RS_PER_WARP, n - begin);
+        int wcnt = 0;                                             // warp-uniform: near points listed so far
+        if (m > 0) {
+            if (i + 1 < RS_NCH) issue(i + 1);                     // the other buffer: this warp finished with it a slice ago
+            if (bulk && (m & ~1) > 0) rs_mbar_wait(&s_bar[warp][i & 1], (uint32_t)(i >> 1) & 1u);
+            __syncwarp();                                         // plain-load stragglers
+            const uint32_t buf = rec_addr + (uint32_t)(i & 1) * (RS_PER_WARP * 8u) + (uint32_t)lane * 8u;
+            uint32_t *wlist = list + (int64_t)f * g.slab + begin;
+            uint32_t fill = 0, head = 0;                          // warp-uniform: candidates waiting, ring position
+            // DENSE step: every lane takes one waiting candidate
+            auto dense = [&](uint64_t rc, bool on) {
+                bool near = false;
+                uint32_t word = 0;
+                if (on) {
+                    const uint32_t lo = (uint32_t)rc, hi = (uint32_t)(rc >> 32);
+                    const uint32_t x = lo & 0x7FFu, y = (lo >> 11) & 0x7FFu, d = lo >> 22;
+                    const double Z = s_Z[d];
+                    const double e = fabs(fma(Z, fma(af, road_u2d(x), fma(bf, road_u2d(y), c2)), -1.0));
+                    near = e < cut_lo;
+                    if (!near && e < cut_hi) near = exact_near(cam, lo, Z, pl[0], pl[1], pl[2], pl[4]);   // rare
+                    if (near) {
+                        const uint32_t hue = (uint32_t)hue_of_hi(hi);
+                        atomicAdd(&s_h[hue], 1u);
+                        const uint32_t px = x - ((__ldg(rbits + x * 8 + (d >> 5)) >> (d & 31)) & 1u);
+                        const uint32_t py = y - ((__ldg(rbits + (g.W + y) * 8 + (d >> 5)) >> (d & 31)) & 1u);
+                        word = px | (py << 11) | (hue << 22);
+                    }
+                }
+                const uint32_t bal = __ballot_sync(0xffffffffu, near);
+                if (near) __stcs(wlist + wcnt + __popc(bal & lt_mask), word);
+                wcnt += __popc(bal);
+            };
+            // the slice's candidate interval [dlo, dlo + dw] (warp-uniform): the records are in row-major order,
+            // so the first and the last one bound the slice's pixel box
+            uint32_t dlo = 1u, dw = 254u;                         // keep everything unless the bounds are clean
+            {
+                const uint32_t la = (uint32_t)rs_lds64(buf - (uint32_t)lane * 8u);
+                const uint32_t lb = (uint32_t)rs_lds64(buf - (uint32_t)lane * 8u + (uint32_t)(m - 1) * 8u);
+                const uint32_t ya = (la >> 11) & 0x7FFu, yb = (lb >> 11) & 0x7FFu;
+                const double xa = ya == yb ? road_u2d(la & 0x7FFu) : 0.0, xb = ya == yb ? road_u2d(lb & 0x7FFu) : (double)(g.W - 1);
+                const double t1 = af * xa, t2 = af * xb, u1 = bf * road_u2d(ya), u2 = bf * road_u2d(yb);
+                const double tmin = c2 + fmin(t1, t2) + fmin(u1, u2), tmax = c2 + fmax(t1, t2) + fmax(u1, u2);
+                if (fp[7] != 0.0 && isfinite(tmin) && isfinite(tmax)) {
+                    if (tmax <= 0.0) { dlo = 255u; dw = 0u; }     // Z t <= 0: |Z t - 1| >= 1 > cut, nothing is near
+                    else {
+                        const double Al = fmin(fmax(floor(fmax(tmin, 0.0) * fp[5]), 1.0), 255.0);
+                        const double Bh = fmax(fmin(ceil(tmax * fp[6]), 255.0), Al);
+                        dlo = (uint32_t)Al; dw = (uint32_t)Bh - dlo;
+                    }
+                }
+            }
+            auto round = [&](uint64_t r, bool cand) {
+                const uint32_t bal = __ballot_sync(0xffffffffu, cand);
+                if (cand) rs_sts64(stage_addr + (((head + fill + __popc(bal & lt_mask)) & 63u) << 3), r);
+                fill += __popc(bal);
+                if (fill >= 32u) {
+                    __syncwarp();
+                    dense(rs_lds64(stage_addr + (((head + lane) & 63u) << 3)), true);
+                    head += 32u; fill -= 32u;
+                    __syncwarp();
+                }
+            };
+            if (m == RS_PER_WARP) {                               // full slice: no bounds to test
+#pragma unroll 2
+                for (int k = 0; k < RS_PER_WARP / 32; ++k) {
+                    const uint64_t r = rs_lds64(buf + (uint32_t)k * 256u);
+                    round(r, ((uint32_t)r >> 22) - dlo <= dw);
+                }
+            } else {
+                for (int k = 0; k * 32 < m; ++k) {
+                    uint64_t r = 0;
+                    bool cand = false;
+                    if (k * 32 + lane < m) {
+                        r = rs_lds64(buf + (uint32_t)k * 256u);
+                        cand = ((uint32_t)r >> 22) - dlo <= dw;
+                    }
+                    round(r, cand);
+                }
+            }
+            __syncwarp();
+            if (fill) dense(rs_lds64(stage_addr + (((head + lane) & 63u) << 3)), (uint32_t)lane < fill);
+            __syncwarp();
+        }
+        if (lane == 0) warp_counts[(int64_t)f * frame_slices + slice] = wcnt;
+        ktotal += wcnt;
+    }
+    if (lane == 0 && ktotal) atomicAdd(&counts_out[f * 4 + 2], ktotal);
+    __syncthreads();
+    if (!valid) return;
+    uint32_t *gh = hist + (int64_t)f * SVB_HIST_STRIDE;
+    for (int k = tid; k < SVB_HUE_BINS; k += RS_THREADS) {
+        const uint32_t v = s_h[k];
+        if (v) atomicAdd(&gh[k], v);
+    }
+}
+
+// Colour filter + scatter.  A warp takes RS_SC_SLICES consecutive slices and has all of their list entries
+// (up to 8 words per lane and slice) in flight at once: the kernel is a chain of three dependent memory
+// round trips (slice counts, entries, mask stores), so the only lever is how much each trip carries.
+#define RS_SC_SLICES 4
+template <bool OVERLAY>
+__global__ void __launch_bounds__(RS_THREADS)
+road_scatter_kernel(const int32_t *__restrict__ warp_counts, const uint32_t *__restrict__ list, StreamGeom g,
+                    const int32_t *__restrict__ counts_k, const uint32_t *__restrict__ hist, uint32_t colour_threshold,
+                    uint8_t *__restrict__ road_mask, uint8_t *__restrict__ overlay, int32_t *__restrict__ counts_out) {
+    __shared__ uint32_t s_pop[32];                                // bit per hue bin: count > colour_threshold
+    const int f = blockIdx.y;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (counts_k[f * 4 + 2] == 0) return;                         // no near point in this frame
+    const int slices = g.chunks * RS_WARPS;
+    const int sl0 = (blockIdx.x * RS_WARPS + warp) * RS_SC_SLICES;
+    int cnt[RS_SC_SLICES];
+#pragma unroll
+    for (int q = 0; q < RS_SC_SLICES; ++q) cnt[q] = sl0 + q < slices ? __ldg(warp_counts + (int64_t)f * slices + sl0 + q) : 0;
+    const uint32_t *gh = hist + (int64_t)f * SVB_HIST_STRIDE;
+#pragma unroll
+    for (int k = 0; k < SVB_HIST_STRIDE / RS_THREADS; ++k) {
+        const int bin = k * RS_THREADS + tid;
+        const uint32_t bal = __ballot_sync(0xffffffffu, __ldg(gh + bin) > colour_threshold);
+        if (lane == 0) s_pop[bin >> 5] = bal;
+    }
+    uint32_t w[RS_SC_SLICES][RS_PER_WARP / 32];
+    const uint32_t *wl = list + (int64_t)f * g.slab + (int64_t)sl0 * RS_PER_WARP + lane;
+#pragma unroll
+    for (int q = 0; q < RS_SC_SLICES; ++q)
+#pragma unroll
+        for (int k = 0; k < RS_PER_WARP / 32; ++k)
+            w[q][k] = (k * 32 + lane < cnt[q]) ? __ldcs(wl + q * RS_PER_WARP + k * 32) : 0xFFFFFFFFu;   // hue 1023: never popular
+    __syncthreads();
+    uint8_t *mask = road_mask + (int64_t)f * g.H * g.W;
+    uint8_t *ovl = OVERLAY ? overlay + (int64_t)f * g.H * g.W * 3 : nullptr;
+    int rcount = 0;
+#pragma unroll
+    for (int q = 0; q < RS_SC_SLICES; ++q)
+#pragma unroll
+        for (int k = 0; k < RS_PER_WARP / 32; ++k) {
+            const uint32_t v = w[q][k], hue = v >> 22;
+            if ((s_pop[hue >> 5] >> (hue & 31)) & 1u) {
+                ++rcount;
+                const uint32_t off = ((v >> 11) & 0x7FFu) * (uint32_t)g.W + (v & 0x7FFu);
+                mask[off] = 255;
+                if (OVERLAY) {
+                    uint8_t *o = ovl + (int64_t)off * 3;
+                    o[0] = 0; o[1] = 255; o[2] = 0;               // [0,255,0], stereovision.py:133
+                }
+            }
+        }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) rcount += __shfl_xor_sync(0xffffffffu, rcount, o);
+    if (lane == 0 && rcount) atomicAdd(&counts_out[f * 4 + 3], rcount);
+}
+
+static int64_t stream_fp_bytes(int F) { return ((int64_t)F * RS_FP_STRIDE + 256) * 8; }            // frame parameters + Z(d) table
+static int64_t stream_wc_bytes(int F, const StreamGeom &g) { return (((int64_t)F * g.chunks * RS_WARPS * 4) + 255) & ~(int64_t)255; }
+static int64_t stream_list_bytes(int F, const StreamGeom &g) { return (int64_t)F * g.slab * 4; }
+
 extern "C" int64_t svb_road_scratch_bytes(int F, int H, int W, int step) {
     if (F < 1 || H < 2 || W < 2 || step < 1) return 0;
     RoadGeom g = make_road_geom(H, W, step);
-    return (int64_t)F * g.words * (int64_t)sizeof(uint32_t);
+    StreamGeom sg = make_stream_geom(H, W, step);
+    int64_t legacy = (int64_t)F * g.words * (int64_t)sizeof(uint32_t);
+    int64_t streamed = stream_fp_bytes(F) + stream_wc_bytes(F, sg) + stream_list_bytes(F, sg);
+    return legacy > streamed ? legacy : streamed;
 }
 
 extern "C" int svb_road_points(const uint64_t *cloud, const int32_t *counts, const double *planes,
@@ -689,13 +1043,40 @@ extern "C" int svb_road_points(const uint64_t *cloud, const int32_t *counts, con
     cudaStream_t st = (cudaStream_t)stream;
     RoadGeom g = make_road_geom(H, W, step);
     CamD c = make_camd(cam);
-    // fused cluster kernel when the displacement table is given and a CTA's near list fits in shared memory
     const int64_t rounds = (g.slab + RC_ROUND - 1) / RC_ROUND;                   // rounds of a frame, dealt round-robin
     const int64_t list_cap = (rounds + RC_PARTS - 1) / RC_PARTS * RC_ROUND;      // records one CTA can meet
     const int warp_cap = (int)(list_cap / RC_WARPS);                             // ... and one warp
     const size_t list_bytes = (size_t)list_cap * sizeof(uint32_t);
-    const bool mask_no_wrap = (H <= 2048 && W <= 2048);
-    if (reproj_bits && mask_no_wrap && list_bytes <= 160 * 1024 && !g_svb_force_two_pass) {
+    const bool cluster_fits = list_bytes <= 160 * 1024;
+    // the streamed path (needs the displacement table and 16-byte aligned scratch)
+    if (reproj_bits && (((uintptr_t)scratch) & 15) == 0 && (g_svb_road_mode == 3 || (g_svb_road_mode == 0 && !cluster_fits))) {
+        StreamGeom sg = make_stream_geom(H, W, step);
+        double *fparam = (double *)scratch;
+        double *ztab = fparam + (int64_t)F * RS_FP_STRIDE;
+        int32_t *wcounts = (int32_t *)((char *)fparam + stream_fp_bytes(F));
+        uint32_t *list = (uint32_t *)((char *)wcounts + stream_wc_bytes(F, sg));
+        {
+            ProfScope ps(K_ROAD_TABLE, st);
+            road_params_kernel<<<F, 256, 0, st>>>(planes, sg, c, fparam, ztab, hist, counts_out);
+        }
+        SVB_LAUNCH_CHECK();
+        {
+            ProfScope ps(K_ROAD_NEAR, st);
+            road_near_kernel<<<dim3(sg.ctas, F), RS_THREADS, 0, st>>>(cloud, counts, planes, sg, c, reproj_bits, fparam, ztab,
+                                                                    hist, road_mask, list, wcounts, counts_out);
+        }
+        SVB_LAUNCH_CHECK();
+        {
+            ProfScope ps(K_ROAD_SCATTER, st);
+            dim3 sgrid(sg.sctas, F);
+            if (overlay) road_scatter_kernel<true><<<sgrid, RS_THREADS, 0, st>>>(wcounts, list, sg, counts_out, hist, colour_threshold, road_mask, overlay, counts_out);
+            else         road_scatter_kernel<false><<<sgrid, RS_THREADS, 0, st>>>(wcounts, list, sg, counts_out, hist, colour_threshold, road_mask, nullptr, counts_out);
+        }
+        SVB_LAUNCH_CHECK();
+        return SVB_OK;
+    }
+    // the cluster kernel: displacement table given and a CTA's near list fits in shared memory
+    if (reproj_bits && cluster_fits && (g_svb_road_mode == 0 || g_svb_road_mode == 2)) {
         cudaError_t e = cudaMemset2DAsync(counts_out + 2, 4 * sizeof(int32_t), 0, 2 * sizeof(int32_t), F, st);
         if (e != cudaSuccess) return (int)e;
         cudaLaunchConfig_t cfg = {};

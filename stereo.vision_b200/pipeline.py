@@ -21,7 +21,7 @@ import torch
 from . import _native as N
 from .camera import DEFAULT_CAMERA, Camera
 
-KERNELS_PER_BATCH = 6      # fill+count, scan, write, score, finalize, fused road kernel (+1 on the two-pass road path)
+KERNELS_PER_BATCH = 6      # fill+count, scan, write, score, finalize, road cluster kernel
 
 
 def _as_cuda_u8(x, device):
@@ -102,8 +102,10 @@ class RoadPath:
                 "svb_reproject_bits")
         if int(ok.item()) != 1 or not use_reproj_table:
             self.reproj_bits = None
-        # svb_road_points takes its fused cluster path when a CTA's near list fits in shared memory
+        # svb_road_points: one cluster kernel when a CTA's near list fits in shared memory, else the streamed path
+        # (params, near, scatter kernels); without the displacement table the legacy two-pass kernels
         self.fused_road = self.reproj_bits is not None and ((self.L + 2047) // 2048 + 7) // 8 * 2048 * 4 <= 160 * 1024
+        self.road_launches = 1 if self.fused_road else (3 if self.reproj_bits is not None else 2)
 
     # ------------------------------------------------------------------
     def process(self, disp, bgr, prev=None, seed=0, frame0=0, indices=None, overlay=None,
@@ -161,7 +163,7 @@ class RoadPath:
                                     C.byref(self._cam), self.colour_threshold, N.ptr(self.reproj_bits), N.ptr(self.hist), N.ptr(self.road_mask),
                                     N.ptr(ov), N.ptr(self.counts), N.ptr(self.scratch), self.scratch.numel(), st),
                 "svb_road_points")
-        N.count(KERNELS_PER_BATCH + (0 if self.fused_road else 1) + (0 if fill else 2))   # no fill: copy + count kernels
+        N.count(KERNELS_PER_BATCH - 1 + self.road_launches + (0 if fill else 2))   # no fill: copy + count kernels
         return res
 
     def dump_indices(self, F, seed=0, frame0=0):

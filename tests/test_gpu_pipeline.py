@@ -72,6 +72,15 @@ def test_small_ragged_shapes(cuda, shape, step):
                           step=step, threshold=0.5, colour_threshold=0)
     for t in range(F):
         check_frame(res, t, orc[t])
+    # the streamed road path (used for lattices too large for the cluster kernel) on the same ragged input
+    import stereo.vision_b200._native as N
+    N.load().svb_debug_force_two_pass(3)
+    try:
+        res3 = to_host(eng.process(disp, bgr, seed=9))
+    finally:
+        N.load().svb_debug_force_two_pass(0)
+    for k in ("road_mask", "counts", "hist"):
+        assert np.array_equal(res[k], res3[k]), k
 
 
 def test_no_plane_when_masked_cloud_too_small(cuda):
@@ -152,8 +161,8 @@ def test_road_points_without_reprojection_table(cuda):
     assert ra["road_mask"].any()
 
 
-def test_two_pass_road_path_matches_fused(cuda):
-    """svb_road_points' two-kernel path (large lattices / no table) equals the fused cluster kernel."""
+def test_road_paths_agree(cuda):
+    """svb_road_points' three implementations -- cluster kernel (default at this size), legacy two-pass, streamed -- agree."""
     import stereo.vision_b200._native as N
     from stereo.vision_b200.pipeline import RoadPath
     F = 3
@@ -162,11 +171,45 @@ def test_two_pass_road_path_matches_fused(cuda):
     eng = RoadPath(carmask=cm, max_frames=F, samples=400)
     assert eng.fused_road
     ra = to_host(eng.process(disp, bgr, seed=5))
-    N.load().svb_debug_force_two_pass(1)
-    try:
-        rb = to_host(eng.process(disp, bgr, seed=5))
-    finally:
-        N.load().svb_debug_force_two_pass(0)
-    for k in ("road_mask", "counts", "hist"):
-        assert np.array_equal(ra[k], rb[k]), k
+    for mode in (1, 3):
+        N.load().svb_debug_force_two_pass(mode)
+        try:
+            rb = to_host(eng.process(disp, bgr, seed=5))
+        finally:
+            N.load().svb_debug_force_two_pass(0)
+        for k in ("road_mask", "counts", "hist"):
+            assert np.array_equal(ra[k], rb[k]), (mode, k)
     assert ra["road_mask"].any()
+
+
+def test_config3_full_density_step1(cuda):
+    """BASELINE config 3: step 1 (555 489 lattice sites), RGB attach, masked-cloud RANSAC; the road points
+    take the streamed path (the near list of a frame no longer fits a cluster's shared memory)."""
+    from stereo.vision_b200.pipeline import RoadPath
+    F, T, S = 2, 600, 400
+    disp, bgr = synth.make_sequence(8, F)
+    cm = _carmask(disp.shape[1:])
+    eng = RoadPath(step=1, trials=T, samples=S, carmask=cm, max_frames=F)
+    assert not eng.fused_road and eng.road_launches == 3
+    r = eng.process(disp, bgr, seed=31)
+    si, ti = eng.dump_indices(F, seed=31)
+    res = to_host(r)
+    orc = oracle_sequence(disp, bgr, cm, indices=(si.cpu().numpy(), ti.cpu().numpy()), trials=T, n_samples=S, step=1)
+    for t in range(F):
+        check_frame(res, t, orc[t])
+
+
+def test_config5_stress_2048x1088(cuda):
+    """BASELINE config 5: 2048x1088 frames (masks scaled x2), larger RANSAC (2000 hypotheses x 1000 samples)."""
+    from stereo.vision_b200.pipeline import RoadPath
+    shape, F, T, S = (1088, 2048), 2, 2000, 1000
+    disp, bgr = synth.make_sequence(9, F, shape=shape)
+    cm = _carmask(shape)
+    eng = RoadPath(shape=shape, step=2, trials=T, samples=S, carmask=cm, max_frames=F)
+    r = eng.process(disp, bgr, seed=77)
+    si, ti = eng.dump_indices(F, seed=77)
+    res = to_host(r)
+    orc = oracle_sequence(disp, bgr, cm, indices=(si.cpu().numpy(), ti.cpu().numpy()), trials=T, n_samples=S, step=2)
+    for t in range(F):
+        check_frame(res, t, orc[t])
+    assert res["planes"][:, 7].all()
