@@ -127,7 +127,7 @@ class ClockSampler:
                         self.reasons.add(k)
             except Exception:
                 pass
-            self._stop.wait(0.02)
+            self._stop.wait(0.002)
 
     def __enter__(self):
         if self.nv:
@@ -150,10 +150,13 @@ def algorithmic_bytes(kernel, L, N, M, K, R, T, S):
     """Algorithmic bytes per FRAME of each kernel (DESIGN.md "Kernels"; SURVEY 8d restated for the
     8-byte cloud / 4-byte mcloud records).  N, M, K, R are per-frame means."""
     table = {
-        "fill_seq": 2.0 * H * W,                              # raw in + filled out (prev lives in registers)
-        "proj_count": 2.0 * L,                                # d + carmask at lattice sites
+        "fill_seq": 2.0 * H * W,                              # raw in + filled out (prev lives in registers); also counts sites
+        "proj_count": 2.0 * L,                                # d + carmask at lattice sites (stand-alone projection only)
         "proj_write": 2.0 * L + 3.0 * N + 8.0 * N + 4.0 * M,  # d, carmask, rgb in; cloud + mcloud out
-        "ransac_score": 4.0 * T * (S + 3) + 8.0 * T,          # gathered records (L2) + errors out
+        "ransac_score": 4.0 * T * (S + 3) + 8.0 * T,          # gathered records (shared memory / L2) + errors out
+        "road_cluster": 8.0 * N + 1.0 * H * W + 1.0 * R,      # records in, mask cleared, road bytes out
+        "road_near": 8.0 * N + 1.0 * H * W + 4.0 * K,         # records in, mask cleared, near list out
+        "road_scatter": 4.0 * K + 1.0 * R,                    # near list in, road bytes out
         "road_pass1": 8.0 * N + N / 8.0,                      # records in, near bits out
         "road_pass2": N / 8.0 + 8.0 * K + 1.0 * R,            # near bits, near records in, mask bytes out
         "road_clear": 1.0 * H * W,                            # mask clear (memset node)
@@ -227,7 +230,9 @@ def run_b200(args):
     # ---- end to end: pinned host frames in, masks / planes / counts out, chunked + double buffered
     e2e = None
     if not args.no_e2e:
-        e2e = run_e2e(args, torch, dev, eng.camera, cm, disp_p, bgr_p, seed, ref_counts)
+        with ClockSampler(local) as clk2:
+            e2e = run_e2e(args, torch, dev, eng.camera, cm, disp_p, bgr_p, seed, ref_counts)
+        e2e["clocks"] = clk2.summary()
 
     # ---- max over ranks
     ms_max, e2e_ms_max = shard.max_over_ranks([ms, e2e["ms"] if e2e else 0.0], dev)
@@ -266,7 +271,10 @@ def run_b200(args):
         if e2e:
             out["e2e"] = {"value": F * world / (e2e_ms_max * 1e-3), "unit": "frames/s",
                           "h2d_bytes_per_step": e2e["h2d"], "d2h_bytes_per_step": e2e["d2h"],
-                          "ms_per_step": e2e_ms_max, "chunk_frames": args.chunk, "matches_resident_run": e2e["match"]}
+                          "ms_per_step": e2e_ms_max, "chunk_frames": args.chunk, "matches_resident_run": e2e["match"],
+                          "api": "stereo.vision_b200.pipeline.SequenceStreamer.run (pinned host frames -> pinned host masks/planes/counts; "
+                                 "of the colour image only the lattice rows are uploaded)",
+                          "gpu_launches_per_step": e2e["launches_per_step"], "clocks": e2e["clocks"]}
         if world == 1 and not args.no_cpu_baseline:
             procs = ncpu
             fpp = args.cpu_frames or 4
@@ -279,65 +287,29 @@ def run_b200(args):
     return out
 
 
-def run_e2e(args, torch, dev, camera, cm, disp_p, bgr_p, seed, ref_counts):
-    """One sequence through RoadPath.process from pinned HOST buffers: per chunk, H2D copy of the
-    frames (copy stream), the path (compute stream), D2H of road masks + planes + counts (output
-    stream) into pinned host memory; two engines/buffers alternate so copies overlap compute."""
-    from stereo.vision_b200.pipeline import RoadPath
+def run_e2e(args, torch, dev, camera, cm, disp_p, bgr_p, seed, ref_counts, clk=None):
+    """One sequence through the public host-to-host entry point (pipeline.SequenceStreamer.run): pinned
+    HOST frames in, road masks + planes + counts in pinned host memory out; per chunk the H2D copy of
+    the frames, the path and the D2H copy of the results run on three streams, double buffered."""
+    from stereo.vision_b200.pipeline import SequenceStreamer
     F, C = args.frames, min(args.chunk, args.frames)
-    engs = [RoadPath((H, W), step=args.step, trials=args.trials, samples=args.samples, carmask=cm, max_frames=C,
-                     device=dev, camera=camera) for _ in range(2)]
-    din = [torch.empty((C, H, W), dtype=torch.uint8, device=dev) for _ in range(2)]
-    cin = [torch.empty((C, H, W, 3), dtype=torch.uint8, device=dev) for _ in range(2)]
-    mask_o = torch.empty((F, H, W), dtype=torch.uint8).pin_memory()
-    plane_o = torch.empty((F, 8), dtype=torch.float64).pin_memory()
-    count_o = torch.empty((F, 4), dtype=torch.int32).pin_memory()
-    s_in, s_cmp, s_out = torch.cuda.Stream(dev), torch.cuda.Stream(dev), torch.cuda.Stream(dev)
-    chunks = [(a, min(F, a + C)) for a in range(0, F, C)]
-
-    def one_pass():
-        ev_in, ev_cmp, ev_out = {}, {}, {}
-        for i, (a, b) in enumerate(chunks):
-            k, n = i % 2, b - a
-            with torch.cuda.stream(s_in):
-                if i >= 2:
-                    s_in.wait_event(ev_cmp[i - 2])            # buffer k is free once chunk i-2 was computed
-                din[k][:n].copy_(disp_p[a:b], non_blocking=True)
-                cin[k][:n].copy_(bgr_p[a:b], non_blocking=True)
-                ev_in[i] = torch.cuda.Event()
-                ev_in[i].record(s_in)
-            with torch.cuda.stream(s_cmp):
-                s_cmp.wait_event(ev_in[i])
-                if i >= 2:
-                    s_cmp.wait_event(ev_out[i - 2])           # engine k's outputs were read back
-                prev = engs[1 - k].filled[chunks[i - 1][1] - chunks[i - 1][0] - 1] if i else None
-                r = engs[k].process(din[k][:n], cin[k][:n], prev=prev, seed=seed, frame0=a)
-                ev_cmp[i] = torch.cuda.Event()
-                ev_cmp[i].record(s_cmp)
-            with torch.cuda.stream(s_out):
-                s_out.wait_event(ev_cmp[i])
-                mask_o[a:b].copy_(r.road_mask, non_blocking=True)
-                plane_o[a:b].copy_(r.planes, non_blocking=True)
-                count_o[a:b].copy_(r.counts, non_blocking=True)
-                ev_out[i] = torch.cuda.Event()
-                ev_out[i].record(s_out)
-
+    sr = SequenceStreamer((H, W), step=args.step, trials=args.trials, samples=args.samples, carmask=cm, camera=camera,
+                          chunk=C, device=dev)
+    out = None
     for _ in range(2):
-        one_pass()
+        out = sr.run(disp_p, bgr_p, seed=seed, out=out)
     torch.cuda.synchronize()
     steps = max(3, min(args.steps, 10))
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record(s_in)
+    e0.record()
     for _ in range(steps):
-        one_pass()
-    s_out.wait_stream(s_cmp)
-    e1.record(s_out)
+        out = sr.run(disp_p, bgr_p, seed=seed, out=out)
+    e1.record()
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / steps
-    match = bool(np.array_equal(count_o.numpy().astype(np.float64), ref_counts))
-    h2d = int(disp_p.nbytes + bgr_p.nbytes)
-    d2h = int(mask_o.nbytes + plane_o.nbytes + count_o.nbytes)
-    return {"ms": ms, "h2d": h2d, "d2h": d2h, "match": match}
+    match = bool(np.array_equal(out["counts"].numpy().astype(np.float64), ref_counts))
+    return {"ms": ms, "h2d": sr.h2d_bytes, "d2h": sr.d2h_bytes, "match": match,
+            "launches_per_step": len(range(0, F, C)) * (sr.engines[0].road_launches + 5)}
 
 
 # ------------------------------------------------------------------ reference arm (CPU)

@@ -214,6 +214,13 @@ int svb_road_points(const uint64_t *cloud, const int32_t *counts, const double *
                     uint32_t *hist, uint8_t *road_mask, uint8_t *overlay, int32_t *counts_out,
                     void *scratch, int64_t scratch_bytes, void *stream);
 
+/* ---- host -> device upload of the rows the path reads
+ * The projection reads the colour image only on lattice rows (every step-th row), so an end-to-end caller
+ * need not send the others: this copies `rows` rows of `width_bytes` bytes, `pitch_bytes` apart in BOTH the
+ * (pinned) host source and the device destination (cudaMemcpy2DAsync), i.e. the rows land where a full-frame
+ * copy would have put them and the rows in between are left untouched (never read). */
+int svb_upload_rows(const void *h_src, void *d_dst, int64_t pitch_bytes, int64_t width_bytes, int64_t rows, void *stream);
+
 /* ---- tracing: per-kernel CUDA-event timing, off by default.
  * svb_profile_enable(1) clears the records and brackets every later kernel launch of this library
  * with two events on its stream; after the caller has synchronised, svb_profile_get(id, ..) returns

@@ -70,6 +70,7 @@ SIGNATURES = {
     "svb_road_points": (I, [P, P, P, I, I, I, I, CAMP, U32, P, P, P, P, P, P, L, P]),
     "svb_reproject_bits_words": (L, [I, I]),
     "svb_reproject_bits": (I, [I, I, CAMP, P, P, P]),
+    "svb_upload_rows": (I, [P, P, L, L, L, P]),
     "svb_profile_enable": (I, [I]),
     "svb_debug_force_two_pass": (I, [I]),
     "svb_profile_kernels": (I, []),

@@ -16,6 +16,15 @@ extern "C" const char *svb_error_string(int code) {
     return "unknown error";
 }
 
+// ------------------------------------------------------------------ strided host -> device upload
+extern "C" int svb_upload_rows(const void *h_src, void *d_dst, int64_t pitch_bytes, int64_t width_bytes, int64_t rows, void *stream) {
+    if (!h_src || !d_dst) return SVB_E_NULL;
+    if (pitch_bytes < width_bytes || width_bytes < 1 || rows < 1) return SVB_E_ARG;
+    cudaError_t e = cudaMemcpy2DAsync(d_dst, (size_t)pitch_bytes, h_src, (size_t)pitch_bytes, (size_t)width_bytes, (size_t)rows,
+                                      cudaMemcpyHostToDevice, (cudaStream_t)stream);
+    return e == cudaSuccess ? SVB_OK : (int)e;
+}
+
 // ------------------------------------------------------------------ per-kernel event tracing
 #include "svb_prof.cuh"
 #include <vector>

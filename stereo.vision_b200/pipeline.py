@@ -175,3 +175,108 @@ class RoadPath:
                                                  N.stream_ptr()), "svb_ransac_dump_indices")
         N.count(1)
         return si, ti
+
+
+class SequenceStreamer:
+    """End-to-end entry point: a sequence that lives in HOST memory in, road masks / planes / counts in
+    (pinned) host memory out -- what loop.py does frame by frame (loop.py:57-78), for a whole sequence.
+
+    The sequence is cut into chunks of `chunk` frames.  Three streams overlap, per chunk, the host->device
+    copy of the frames, the path (RoadPath.process, chained through the filled disparity of the previous
+    chunk) and the device->host copy of the results; two engines / input buffers alternate.  Of the colour
+    image only the lattice rows are sent (svb_upload_rows): the path never reads the others, and at step 2
+    that is a quarter of all input bytes.  `h2d_bytes` / `d2h_bytes` report what one run() moves.
+    """
+
+    def __init__(self, shape=(544, 1024), step=2, trials=600, samples=600, carmask=None,
+                 camera: Camera = DEFAULT_CAMERA, chunk=60, device="cuda:0", **kw):
+        self.H, self.W = int(shape[0]), int(shape[1])
+        self.step, self.chunk = int(step), int(chunk)
+        self.device = torch.device(device)
+        self.engines = [RoadPath(shape, step=step, trials=trials, samples=samples, carmask=carmask, camera=camera,
+                                 max_frames=self.chunk, device=device, **kw) for _ in range(2)]
+        H, W, C_, dev = self.H, self.W, self.chunk, self.device
+        self.din = [torch.empty((C_, H, W), dtype=torch.uint8, device=dev) for _ in range(2)]
+        self.cin = [torch.zeros((C_, H, W, 3), dtype=torch.uint8, device=dev) for _ in range(2)]
+        self.s_in, self.s_cmp, self.s_out = (torch.cuda.Stream(dev) for _ in range(3))
+        self.lib = N.load()
+        self.h2d_bytes = self.d2h_bytes = 0
+
+    def _upload_colour(self, dst, src, n):
+        """Lattice rows of src [n,H,W,3] (host) -> the same rows of dst (device), on the current stream."""
+        H, W, st = self.H, self.W, self.step
+        LH = self.engines[0].LH
+        row = W * 3
+        if st == 1 or not src.is_contiguous():
+            dst[:n].copy_(src, non_blocking=True)
+            return n * H * row
+        sp = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        if H % st == 0:                                   # rows y = 0, st, 2 st, ... run on across frame boundaries
+            rows = n * (H // st)
+            N.check(self.lib.svb_upload_rows(C.c_void_p(src.data_ptr()), N.ptr(dst), st * row, row, rows, sp), "svb_upload_rows")
+            return rows * row
+        for f in range(n):
+            N.check(self.lib.svb_upload_rows(C.c_void_p(src[f].data_ptr()), C.c_void_p(dst[f].data_ptr()), st * row, row, LH, sp),
+                    "svb_upload_rows")
+        return n * LH * row
+
+    def run(self, disp, bgr, seed=0, out=None):
+        """disp uint8 [F,H,W], bgr uint8 [F,H,W,3]: CPU tensors (pin them for asynchronous copies).
+        Returns dict(road_mask uint8 [F,H,W], planes float64 [F,8], counts int32 [F,4]) of pinned CPU tensors
+        (pass the previous result as `out` to reuse them).  Asynchronous: the current stream waits for the
+        result; synchronise (or use run_sync) before reading it on the host."""
+        if isinstance(disp, np.ndarray):
+            disp = torch.from_numpy(disp)
+        if isinstance(bgr, np.ndarray):
+            bgr = torch.from_numpy(bgr)
+        F, H, W, Cn = disp.shape[0], self.H, self.W, self.chunk
+        if tuple(disp.shape) != (F, H, W) or tuple(bgr.shape) != (F, H, W, 3):
+            raise ValueError("bad sequence shape %s / %s" % (tuple(disp.shape), tuple(bgr.shape)))
+        if out is None or out["road_mask"].shape[0] != F:
+            out = {"road_mask": torch.empty((F, H, W), dtype=torch.uint8).pin_memory(),
+                   "planes": torch.empty((F, N.PLANE_STRIDE), dtype=torch.float64).pin_memory(),
+                   "counts": torch.empty((F, 4), dtype=torch.int32).pin_memory()}
+        s_in, s_cmp, s_out = self.s_in, self.s_cmp, self.s_out
+        chunks = [(a, min(F, a + Cn)) for a in range(0, F, Cn)]
+        ev_in, ev_cmp, ev_out = {}, {}, {}
+        h2d = 0
+        start = torch.cuda.Event()
+        start.record(torch.cuda.current_stream(self.device))
+        for s in (s_in, s_cmp, s_out):
+            s.wait_event(start)
+        for i, (a, b) in enumerate(chunks):
+            k, n = i % 2, b - a
+            with torch.cuda.stream(s_in):
+                if i >= 2:
+                    s_in.wait_event(ev_cmp[i - 2])            # input buffer k is free once chunk i-2 was computed
+                self.din[k][:n].copy_(disp[a:b], non_blocking=True)
+                h2d += n * H * W + self._upload_colour(self.cin[k], bgr[a:b], n)
+                ev_in[i] = torch.cuda.Event()
+                ev_in[i].record(s_in)
+            with torch.cuda.stream(s_cmp):
+                s_cmp.wait_event(ev_in[i])
+                if i >= 2:
+                    s_cmp.wait_event(ev_out[i - 2])           # engine k's outputs were read back
+                prev = self.engines[1 - k].filled[chunks[i - 1][1] - chunks[i - 1][0] - 1] if i else None
+                r = self.engines[k].process(self.din[k][:n], self.cin[k][:n], prev=prev, seed=seed, frame0=a)
+                ev_cmp[i] = torch.cuda.Event()
+                ev_cmp[i].record(s_cmp)
+            with torch.cuda.stream(s_out):
+                s_out.wait_event(ev_cmp[i])
+                out["road_mask"][a:b].copy_(r.road_mask, non_blocking=True)
+                out["planes"][a:b].copy_(r.planes, non_blocking=True)
+                out["counts"][a:b].copy_(r.counts, non_blocking=True)
+                ev_out[i] = torch.cuda.Event()
+                ev_out[i].record(s_out)
+        cur = torch.cuda.current_stream(self.device)
+        for s in (s_in, s_cmp, s_out):
+            cur.wait_stream(s)
+        self.h2d_bytes = int(h2d)
+        self.d2h_bytes = int(sum(t.numel() * t.element_size() for t in out.values()))
+        self._last = out
+        return out
+
+    def run_sync(self, disp, bgr, seed=0, out=None):
+        out = self.run(disp, bgr, seed=seed, out=out)
+        torch.cuda.synchronize(self.device)
+        return out

@@ -213,3 +213,23 @@ def test_config5_stress_2048x1088(cuda):
     for t in range(F):
         check_frame(res, t, orc[t])
     assert res["planes"][:, 7].all()
+
+
+def test_sequence_streamer_matches_resident_path(cuda):
+    """The host-to-host entry point (chunked, three streams, lattice-row upload of the colour image) gives the
+    results of one resident RoadPath.process call over the same sequence."""
+    import torch
+    from stereo.vision_b200.pipeline import RoadPath, SequenceStreamer
+    F, T, S = 7, 200, 300
+    disp, bgr = synth.make_sequence(4, F)
+    cm = _carmask(disp.shape[1:])
+    eng = RoadPath(trials=T, samples=S, carmask=cm, max_frames=F)
+    ref = to_host(eng.process(disp, bgr, seed=21))
+    sr = SequenceStreamer(trials=T, samples=S, carmask=cm, chunk=3)
+    out = sr.run_sync(torch.from_numpy(disp).pin_memory(), torch.from_numpy(bgr).pin_memory(), seed=21)
+    assert np.array_equal(out["counts"].numpy(), ref["counts"])
+    assert np.array_equal(out["road_mask"].numpy(), ref["road_mask"])
+    assert np.array_equal(out["planes"].numpy(), ref["planes"])
+    assert sr.h2d_bytes == F * (544 * 1024 + 272 * 1024 * 3) and ref["road_mask"].any()
+    out2 = sr.run_sync(disp, bgr, seed=21, out=out)               # pageable numpy input, buffers reused
+    assert np.array_equal(out2["road_mask"].numpy(), ref["road_mask"])
