@@ -38,7 +38,7 @@ def parse_args():
     ap.add_argument("--trials", type=int, default=600)
     ap.add_argument("--samples", type=int, default=400)
     ap.add_argument("--step", type=int, default=2)
-    ap.add_argument("--chunk", type=int, default=60, help="frames per host->device chunk in the e2e leg")
+    ap.add_argument("--chunk", type=int, default=30, help="frames per host->device chunk in the e2e leg")
     ap.add_argument("--cpu-frames", type=int, default=0, help="frames of the CPU baseline sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -295,15 +295,16 @@ def run_e2e(args, torch, dev, camera, cm, disp_p, bgr_p, seed, ref_counts, clk=N
     F, C = args.frames, min(args.chunk, args.frames)
     sr = SequenceStreamer((H, W), step=args.step, trials=args.trials, samples=args.samples, carmask=cm, camera=camera,
                           chunk=C, device=dev)
-    out = None
-    for _ in range(2):
-        out = sr.run(disp_p, bgr_p, seed=seed, out=out)
+    outs = [None, None]                                   # two result sets alternate: a step's results stay readable
+    for i in range(2):                                    # while the next step's uploads have already begun
+        outs[i] = sr.run(disp_p, bgr_p, seed=seed, out=outs[i])
     torch.cuda.synchronize()
     steps = max(3, min(args.steps, 10))
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    for _ in range(steps):
-        out = sr.run(disp_p, bgr_p, seed=seed, out=out)
+    for i in range(steps):
+        outs[i % 2] = sr.run(disp_p, bgr_p, seed=seed, out=outs[i % 2])
+    out = outs[(steps - 1) % 2]
     e1.record()
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / steps

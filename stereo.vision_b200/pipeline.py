@@ -189,7 +189,7 @@ class SequenceStreamer:
     """
 
     def __init__(self, shape=(544, 1024), step=2, trials=600, samples=600, carmask=None,
-                 camera: Camera = DEFAULT_CAMERA, chunk=60, device="cuda:0", **kw):
+                 camera: Camera = DEFAULT_CAMERA, chunk=30, device="cuda:0", **kw):
         self.H, self.W = int(shape[0]), int(shape[1])
         self.step, self.chunk = int(step), int(chunk)
         self.device = torch.device(device)
@@ -201,6 +201,7 @@ class SequenceStreamer:
         self.s_in, self.s_cmp, self.s_out = (torch.cuda.Stream(dev) for _ in range(3))
         self.lib = N.load()
         self.h2d_bytes = self.d2h_bytes = 0
+        self._last_cmp, self._last_out = [None, None], [None, None]      # last use of buffer / engine k, across run() calls
 
     def _upload_colour(self, dst, src, n):
         """Lattice rows of src [n,H,W,3] (host) -> the same rows of dst (device), on the current stream."""
@@ -240,23 +241,24 @@ class SequenceStreamer:
         chunks = [(a, min(F, a + Cn)) for a in range(0, F, Cn)]
         ev_in, ev_cmp, ev_out = {}, {}, {}
         h2d = 0
-        start = torch.cuda.Event()
-        start.record(torch.cuda.current_stream(self.device))
-        for s in (s_in, s_cmp, s_out):
-            s.wait_event(start)
+        # The inputs live in host memory, so the copy stream does not wait for the caller's stream: the first
+        # uploads of this call overlap the tail of the previous one.  Buffers and engines are guarded by the
+        # events of their last use, within and across calls.
         for i, (a, b) in enumerate(chunks):
             k, n = i % 2, b - a
+            busy_cmp = ev_cmp[i - 2] if i >= 2 else self._last_cmp[k]
+            busy_out = ev_out[i - 2] if i >= 2 else self._last_out[k]
             with torch.cuda.stream(s_in):
-                if i >= 2:
-                    s_in.wait_event(ev_cmp[i - 2])            # input buffer k is free once chunk i-2 was computed
+                if busy_cmp is not None:
+                    s_in.wait_event(busy_cmp)                 # input buffer k is free once its last chunk was computed
                 self.din[k][:n].copy_(disp[a:b], non_blocking=True)
                 h2d += n * H * W + self._upload_colour(self.cin[k], bgr[a:b], n)
                 ev_in[i] = torch.cuda.Event()
                 ev_in[i].record(s_in)
             with torch.cuda.stream(s_cmp):
                 s_cmp.wait_event(ev_in[i])
-                if i >= 2:
-                    s_cmp.wait_event(ev_out[i - 2])           # engine k's outputs were read back
+                if busy_out is not None:
+                    s_cmp.wait_event(busy_out)                # engine k's outputs were read back
                 prev = self.engines[1 - k].filled[chunks[i - 1][1] - chunks[i - 1][0] - 1] if i else None
                 r = self.engines[k].process(self.din[k][:n], self.cin[k][:n], prev=prev, seed=seed, frame0=a)
                 ev_cmp[i] = torch.cuda.Event()
@@ -268,9 +270,8 @@ class SequenceStreamer:
                 out["counts"][a:b].copy_(r.counts, non_blocking=True)
                 ev_out[i] = torch.cuda.Event()
                 ev_out[i].record(s_out)
-        cur = torch.cuda.current_stream(self.device)
-        for s in (s_in, s_cmp, s_out):
-            cur.wait_stream(s)
+            self._last_cmp[k], self._last_out[k] = ev_cmp[i], ev_out[i]
+        torch.cuda.current_stream(self.device).wait_stream(s_out)   # the caller's stream sees the results
         self.h2d_bytes = int(h2d)
         self.d2h_bytes = int(sum(t.numel() * t.element_size() for t in out.values()))
         self._last = out
