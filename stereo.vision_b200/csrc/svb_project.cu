@@ -167,6 +167,11 @@ __device__ __forceinline__ uint32_t fill4(uint32_t d, uint32_t prev) {
 // membership are kept as 0x80-per-byte masks, so a word's counts are two popc.
 #define FILL_THREADS 64
 __device__ __forceinline__ uint32_t nz80(uint32_t w) { return ((w & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | w; }   // bit 7 of a byte: byte != 0
+// nonzero-byte map of 16 bytes in one word: bit 8 j + k = byte j of word k is nonzero (k = 0..3)
+__device__ __forceinline__ uint32_t merge_nz(uint4 v) {
+    return ((nz80(v.x) >> 7) & 0x01010101u) | ((nz80(v.y) >> 6) & 0x02020202u) |
+           ((nz80(v.z) >> 5) & 0x04040404u) | ((nz80(v.w) >> 4) & 0x08080808u);
+}
 __device__ __forceinline__ uint4 fill16(uint4 d, uint4 p) {
     return make_uint4(fill4(d.x, p.x), fill4(d.y, p.y), fill4(d.z, p.z), fill4(d.w, p.w));
 }
@@ -190,27 +195,25 @@ fill_seq_v16(const uint4 *__restrict__ raw, const uint4 *__restrict__ prev0, uin
         lat = active && (y % g.step == 0) && ly < g.LH;
         grp = ly / g.rpb;
         if (lat) {
-            uint32_t sb = site_bits(x0, g.W, g.step), w[4];
+            // bit 8 j + k of the merged word = pixel 4 k + j of the chunk (see count below)
+            const uint32_t sb = site_bits(x0, g.W, g.step);
+            uint32_t sm = 0;
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                uint32_t n = (sb >> (4 * k)) & 0xFu;   // 4 site bits -> 0x80 per byte
-                w[k] = ((n & 1u) << 7) | ((n & 2u) << 14) | ((n & 4u) << 21) | ((n & 8u) << 28);
-            }
-            site80 = make_uint4(w[0], w[1], w[2], w[3]);
-            uint4 m = carmask ? __ldg(carmask + p) : make_uint4(~0u, ~0u, ~0u, ~0u);
-            in80 = make_uint4(nz80(m.x) & w[0], nz80(m.y) & w[1], nz80(m.z) & w[2], nz80(m.w) & w[3]);
+            for (int px = 0; px < 16; ++px)
+                if (sb & (1u << px)) sm |= 1u << (8 * (px & 3) + (px >> 2));
+            site80.x = sm;
+            const uint4 m = carmask ? __ldg(carmask + p) : make_uint4(~0u, ~0u, ~0u, ~0u);
+            in80.x = merge_nz(m) & sm;
         }
         int lat0 = __shfl_sync(0xffffffffu, (int)lat, 0), grp0 = __shfl_sync(0xffffffffu, grp, 0);
         uni = __all_sync(0xffffffffu, (int)lat == lat0 && (!lat || grp == grp0));
     }
     auto count = [&](const uint4 &v, int t) {
         if (uni && !lat) return;                        // whole warp off the lattice (odd rows at step 2)
-        uint32_t a = nz80(v.x), b = nz80(v.y), c4 = nz80(v.z), d4 = nz80(v.w);
-        uint32_t c = (uint32_t)(__popc(a & site80.x) + __popc(b & site80.y) + __popc(c4 & site80.z) + __popc(d4 & site80.w)) |
-                     ((uint32_t)(__popc(a & in80.x) + __popc(b & in80.y) + __popc(c4 & in80.z) + __popc(d4 & in80.w)) << 16);
+        const uint32_t nz = merge_nz(v);
+        uint32_t c = (uint32_t)__popc(nz & site80.x) | ((uint32_t)__popc(nz & in80.x) << 16);
         if (uni) {
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+            c = __reduce_add_sync(0xffffffffu, c);          // one REDUX; 32 x 8 sites fit the 16-bit halves
             if ((threadIdx.x & 31) == 0 && c) atomicAdd(group_counts + (int64_t)t * g.groups + grp, c);
         } else if (lat && c) {
             atomicAdd(group_counts + (int64_t)t * g.groups + grp, c);
