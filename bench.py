@@ -249,6 +249,14 @@ def run_b200(args):
         dom = max(hbm_kernels, key=lambda k: hbm_kernels[k]["ms_per_launch"])
         top = max(kern, key=lambda k: kern[k]["ms_per_launch"])
         d = kern[dom]
+        traffic, traffic_src = None, None                 # DRAM bytes per launch of that kernel from the committed ncu capture
+        try:
+            tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+            if tj.get("frames") == F and dom in tj["kernels"]:
+                traffic = tj["kernels"][dom]["dram_read_bytes"] + tj["kernels"][dom]["dram_write_bytes"]
+                traffic_src = tj["source"]
+        except Exception:
+            pass
         out = {
             "metric": METRIC, "value": F * args.steps * world / (ms_max * 1e-3), "unit": "frames/s",
             "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
@@ -263,7 +271,7 @@ def run_b200(args):
             "gpu_launches": launches,
             "clocks": clk.summary(),
             "roofline": {"kernel": dom, "bound": "hbm", "achieved": d["gbs"], "peak": peak, "unit": "GB/s",
-                         "frac": d["gbs"] / peak, "traffic": None, "peak_source": peak_src,
+                         "frac": d["gbs"] / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                          "alg_bytes_per_launch": d["alg_bytes"], "ms_per_launch": d["ms_per_launch"],
                          "share_of_step": d["share"], "longest_kernel": top},
             "kernels": {k: {kk: (round(vv, 6) if isinstance(vv, float) else vv) for kk, vv in v.items()} for k, v in kern.items()},
