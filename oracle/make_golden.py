@@ -167,9 +167,57 @@ def reproject_fixture():
     print("wrote reproject_table.npz: %d (x,d) and %d (y,d) pairs land one pixel before" % (dx.sum(), dy.sum()))
 
 
+def sanitise_inputs():
+    """Seeded road images for the cleaning fixture: the three reference road masks of seq0 (read back
+    from their own fixture), speckle at several densities over a dense patch, and shapes built to sit
+    on the edges of ParticleCleansing's 70 px^2 rule (rings around 7..11 px holes, blobs at the border)."""
+    out = []
+    z = np.load(os.path.join(OUT, "seq0_step2_s600.npz"))
+    for i in range(int(z["n_frames"])):
+        out.append(("seq0_f%d" % i, np.unpackbits(z["f%d_road_mask_bits" % i])[:544 * 1024].reshape(544, 1024) * np.uint8(255)))
+    rng = np.random.default_rng(2024)
+    for dens in (0.002, 0.03, 0.3):
+        img = ((rng.random((544, 1024)) < dens) * 255).astype(np.uint8)
+        img[330:520, 150:900] |= ((rng.random((190, 750)) < 0.55) * 255).astype(np.uint8)
+        out.append(("speckle_%g" % dens, img))
+    img = np.zeros((544, 1024), np.uint8)
+    for j, hole in enumerate((7, 8, 9, 10, 11, 13)):
+        y0, x0 = 300, 60 + 150 * j
+        img[y0:y0 + 60, x0:x0 + 60] = 255
+        img[y0 + 25:y0 + 25 + hole, x0 + 25:x0 + 25 + hole] = 0          # a hole of hole x hole px
+    img[400:430, 0:30] = 255; img[514:544, 500:530] = 255; img[350:380, 994:1024] = 255   # touching borders
+    img[450:452, 300:302] = 255; img[460:469, 340:349] = 255; img[480:505, 400:425] = 255   # small blobs
+    out.append(("shapes", img))
+    return out
+
+
+def sanitise_fixture():
+    f = rh.load_reference()
+    recs = []
+    for name, img in sanitise_inputs():
+        t0 = time.perf_counter()
+        cleaned, pts = rh.run_sanitise(f, img)
+        recs.append({"name": name, "in_bits": np.packbits(img != 0), "in_sha": sha(img),
+                     "out_bits": np.packbits(cleaned != 0), "out_sha": sha(cleaned), "out_values": np.unique(cleaned),
+                     "n_pts": len(pts), "pts_sha": sha(pts), "pts_head": pts[:64].copy(), "pts_tail": pts[-64:].copy(),
+                     "ref_seconds": time.perf_counter() - t0})
+        print("  sanitise %-14s in=%d out=%d  %.2fs" % (name, int((img != 0).sum()), len(pts), recs[-1]["ref_seconds"]))
+    # a small frame with its own threshold mask (module global swapped, functions.py:33)
+    rng = np.random.default_rng(9)
+    img = ((rng.random((70, 101)) < 0.35) * 255).astype(np.uint8)
+    img[20:60, 10:90] |= ((rng.random((40, 80)) < 0.7) * 255).astype(np.uint8)
+    tm = np.zeros((70, 101), np.uint8); tm[15:, :] = 128; tm[40:, 5:97] = 255
+    cleaned, pts = rh.run_sanitise(f, img, tm)
+    recs.append({"name": "small_70x101", "in_bits": np.packbits(img != 0), "in_sha": sha(img), "in_tmask": tm,
+                 "out_bits": np.packbits(cleaned != 0), "out_sha": sha(cleaned), "out_values": np.unique(cleaned),
+                 "n_pts": len(pts), "pts_sha": sha(pts), "pts_head": pts[:64].copy(), "pts_tail": pts[-64:].copy(),
+                 "ref_seconds": 0.0, "pts": pts})
+    save("sanitise.npz", recs)
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
-    which = sys.argv[1:] or ["seq", "s400", "step1", "small", "noplane", "reproject", "hue"]
+    which = sys.argv[1:] or ["seq", "s400", "step1", "small", "noplane", "reproject", "hue", "sanitise"]
     if "seq" in which:
         sequence_fixture("seq0_step2_s600.npz", 0, 3)
     if "s400" in which:
@@ -184,3 +232,5 @@ if __name__ == "__main__":
         reproject_fixture()
     if "hue" in which:
         hue_fixture()
+    if "sanitise" in which:
+        sanitise_fixture()

@@ -261,3 +261,53 @@ def run_frame(disparity, bgr, prev, carmask, seed=None, trials=600, n_samples=60
     rp = road_points(cloud, abc, threshold, colour_threshold, disparity.shape[:2], camera)
     return {"filled": filled, "cloud": cloud, "mcloud": mcloud, "indices": indices, "best": best,
             "abc": abc, "errors": errs, "road": rp}
+
+
+# ---------------------------------------------------------------- f1: road-mask cleaning
+def _rect_morph(img, k, is_dilate):
+    """cv2.dilate / cv2.erode with a k x k all-ones kernel, anchor at the centre and OpenCV's
+    default border (morphologyDefaultBorderValue: pixels outside the image never win the max / min).
+    Separable running max / min over the in-image part of the window."""
+    r = k // 2
+    H, W = img.shape
+    op = np.maximum if is_dilate else np.minimum
+    out = img.copy()
+    for s in range(1, r + 1):                       # rows: out[y] = op(img[y-r .. y+r])
+        op(out[s:], img[:H - s], out=out[s:])
+        op(out[:H - s], img[s:], out=out[:H - s])
+    src = out
+    out = src.copy()
+    for s in range(1, r + 1):                       # columns
+        op(out[:, s:], src[:, :W - s], out=out[:, s:])
+        op(out[:, :W - s], src[:, s:], out=out[:, :W - s])
+    return out
+
+
+def sanitise_road_image(img, road_threshold_mask):
+    """functions.py:346-366 (sanitiseRoadImage) on a uint8 image; returns (cleaned image, pts).
+
+    :350-351  closing with a 9x9 kernel (dilate then erode)
+    :353      erode, 9x9, iterations=2
+    :355      bitwise_and(img, img, mask=road_threshold_mask): kept where the mask is non-zero
+    :356      closing again
+    :358      ParticleCleansing (functions.py:378-384) paints every external contour whose area is
+              below 70 px^2 *white*.  After a 9x9 closing that cannot change a pixel: the black set of
+              a closed image is a union of 9x9 black squares, so a hole inside a white component holds
+              at least 81 px and the contour around it has area >= 98 > 70; a component whose contour
+              area is below 70 therefore has no hole, and painting the polygon through its own border
+              pixels only touches pixels that are white already.  The golden fixtures, produced with
+              the step left in, confirm it (tests/test_oracle_golden.py).
+    :359-365  pts = [x, y] of every non-zero pixel, rows outermost (row-major), as an (N,2) matrix.
+    """
+    img = np.ascontiguousarray(img, dtype=np.uint8)
+    a = _rect_morph(_rect_morph(img, 9, True), 9, False)
+    a = _rect_morph(_rect_morph(a, 9, False), 9, False)
+    a = np.where(np.asarray(road_threshold_mask) != 0, a, np.uint8(0))
+    a = _rect_morph(_rect_morph(a, 9, True), 9, False)
+    return a, nonzero_points(a)
+
+
+def nonzero_points(img):
+    """functions.py:359-365: (x, y) of the non-zero pixels in row-major order, int32 [N,2]."""
+    ys, xs = np.nonzero(img)
+    return np.stack([xs, ys], axis=1).astype(np.int32)

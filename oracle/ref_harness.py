@@ -161,6 +161,36 @@ def run_frame(f, disparity, bgr, prev_disp, seed, trials=600, point_threshold=0.
     return out
 
 
+
+class _Cv2Compat:
+    """cv2 as the reference expects it: functions.py:379 unpacks three values from findContours
+    (the OpenCV 3 signature); OpenCV 4 returns (contours, hierarchy).  Everything else passes through."""
+
+    def __init__(self, cv2):
+        self._cv2 = cv2
+
+    def __getattr__(self, name):
+        return getattr(self._cv2, name)
+
+    def findContours(self, image, mode, method, **kw):
+        res = self._cv2.findContours(image, mode, method, **kw)
+        if len(res) == 2:
+            return image, res[0], res[1]
+        return res
+
+
+def run_sanitise(f, road_image, road_threshold_mask=None):
+    """stereovision.py:156: the unmodified sanitiseRoadImage (functions.py:346-366) on one road image.
+    Returns (cleaned uint8 image, pts int32 [N,2] as (x,y), calls made by ParticleCleansing's fill)."""
+    if not isinstance(f.cv2, _Cv2Compat):
+        f.cv2 = _Cv2Compat(f.cv2)
+    if road_threshold_mask is not None:
+        f.road_threshold_mask = np.ascontiguousarray(road_threshold_mask)
+    H, W = road_image.shape
+    img, pts = f.sanitiseRoadImage(np.array(road_image, copy=True), (H, W))
+    pts = np.asarray(pts, dtype=np.int32).reshape(-1, 2) if pts.size else np.zeros((0, 2), np.int32)
+    return np.asarray(img), pts
+
 def hist_to_bins(hist: dict) -> np.ndarray:
     """Reference histogram dict (keys = str(round(hue,3))) -> 1001 counts indexed by rint(hue*1000)."""
     bins = np.zeros(1001, dtype=np.int64)

@@ -71,3 +71,25 @@ def check_frame(res, t, o, abc_rtol=1e-9):
 def to_host(res):
     return {k: getattr(res, k).cpu().numpy() for k in
             ("filled", "counts", "planes", "errors", "hist", "road_mask", "cloud", "mcloud")}
+
+
+def sanitise_cases():
+    """(name, input image, threshold mask, golden record) of tests/golden/sanitise.npz: inputs are
+    stored bit-packed ({0,255} images), the small case brings its own threshold mask."""
+    import os
+    from stereo.vision_b200.masks import default_road_threshold_mask
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "sanitise.npz")
+    with np.load(path, allow_pickle=False) as z:
+        g = {k: z[k] for k in z.files}
+    out = []
+    for i in range(int(g["n_frames"])):
+        p = "f%d_" % i
+        r = {k[len(p):]: v for k, v in g.items() if k.startswith(p)}
+        if "in_tmask" in r:
+            tm = r["in_tmask"]
+        else:
+            tm = default_road_threshold_mask()
+        H, W = tm.shape
+        img = np.unpackbits(r["in_bits"])[:H * W].reshape(H, W) * np.uint8(255)
+        out.append((str(r["name"]), img, tm, r))
+    return out

@@ -113,3 +113,19 @@ def test_reprojection_table():
         _, pi = no.reproject(xyz, cam)
         delta = (np.arange(n)[:, None] - pi[:, 0].reshape(n, 255)).astype(np.uint8)
         assert np.array_equal(np.packbits(delta), g[key]) and int(delta.sum()) == int(g[moved])
+
+
+def test_sanitise_road_image():
+    """oracle f1 (road-mask cleaning) vs the unmodified sanitiseRoadImage, ParticleCleansing included."""
+    from helpers import sanitise_cases
+    cases = sanitise_cases()
+    assert len(cases) == 8
+    for name, img, tm, r in cases:
+        assert sha(img) == str(r["in_sha"]), name
+        out, pts = no.sanitise_road_image(img, tm)
+        assert sha(out) == str(r["out_sha"]), name
+        assert set(np.unique(out)) <= {0, 255}
+        assert len(pts) == int(r["n_pts"]) and sha(pts) == str(r["pts_sha"]), name
+        assert np.array_equal(pts[:64], r["pts_head"]) and np.array_equal(pts[-64:], r["pts_tail"])
+        if "pts" in r:
+            assert np.array_equal(pts, r["pts"])
