@@ -199,6 +199,32 @@ int svb_reproject_bits(int H, int W, const svb_camera *cam, uint32_t *bits, int3
 int svb_scatter_points(const int32_t *pts, int n, uint8_t *img, int H, int W, int channels,
                        const uint8_t *h_value, int32_t *oob, void *stream);
 
+/* ---- f1  sanitiseRoadImage: road-mask cleaning + point list            functions.py:346-366
+ * Bit rows: an H x W mask as uint32 [H, ceil(W/32)], bit (x & 31) of word (x >> 5) = pixel x, unused
+ * bits of a row's last word zero.  svb_bits_words(H,W) = words of one image. */
+int64_t svb_bits_words(int H, int W);
+/* bits[f] = (img[f] != 0); rowcnt (int32 [F*H], may be NULL) = set pixels per row.  Used once per
+ * run on road_threshold_mask (functions.py:33, only its non-zero-ness is read at :355), and to list
+ * the points of any byte mask with svb_mask_points. */
+int svb_pack_mask(const uint8_t *img, int F, int H, int W, uint32_t *bits, int32_t *rowcnt, void *stream);
+/* cleaned[f] = closing 9x9 -> erode 9x9 twice -> keep where threshold != 0 -> closing 9x9 of road[f]
+ * (functions.py:349-356; OpenCV default border: outside pixels never win).  road [F,H,W] holds 0 / 255
+ * as generatePointsAsImage writes it; any non-zero byte counts as set, and *status (device int32, may
+ * be NULL) gets bit 0 when a byte other than 0 / 255 was seen -- the reference would then run grey
+ * morphology and its result is NOT reproduced.  ParticleCleansing (:358) provably leaves a closed image
+ * unchanged and is not run.  Outputs, each optional but not both image forms NULL:
+ * cleaned uint8 [F,H,W] (0 / 255, must not alias road), cleaned_bits (bit rows), rowcnt int32 [F,H]. */
+int svb_clean_road(const uint8_t *road, const uint32_t *threshold_bits, int F, int H, int W, uint8_t *cleaned,
+                   uint32_t *cleaned_bits, int32_t *rowcnt, int32_t *status, void *stream);
+/* the same from bit rows (a producer that already holds the road image packed) */
+int svb_clean_road_bits(const uint32_t *road_bits, const uint32_t *threshold_bits, int F, int H, int W,
+                        uint8_t *cleaned, uint32_t *cleaned_bits, int32_t *rowcnt, void *stream);
+/* pts[f] int32 [cap,2] = (x,y) of the set pixels of bits[f] in row-major order (the double loop of
+ * functions.py:359-365); counts[f] = their number, also when it exceeds cap (then only the first cap
+ * points are written).  rowcnt as left by svb_clean_road / svb_pack_mask. */
+int svb_mask_points(const uint32_t *bits, const int32_t *rowcnt, int F, int H, int W, int32_t cap, int32_t *pts,
+                    int32_t *counts, void *stream);
+
 /* ---- a8-a14 fused, batched: the road points of F frames               stereovision.py:97-140
  * reproj_bits: table of svb_reproject_bits or NULL.
  * pass 1: near = |P.abc-1| < cutoff ; per-frame hue histogram of the near points (shared memory,

@@ -272,12 +272,12 @@ def _rect_morph(img, k, is_dilate):
     H, W = img.shape
     op = np.maximum if is_dilate else np.minimum
     out = img.copy()
-    for s in range(1, r + 1):                       # rows: out[y] = op(img[y-r .. y+r])
+    for s in range(1, min(r, H - 1) + 1):           # rows: out[y] = op(img[y-r .. y+r])
         op(out[s:], img[:H - s], out=out[s:])
         op(out[:H - s], img[s:], out=out[:H - s])
     src = out
     out = src.copy()
-    for s in range(1, r + 1):                       # columns
+    for s in range(1, min(r, W - 1) + 1):           # columns
         op(out[:, s:], src[:, :W - s], out=out[:, s:])
         op(out[:, :W - s], src[:, s:], out=out[:, :W - s])
     return out

@@ -17,7 +17,8 @@ LIB_PATH = os.path.join(_PKG, "libsvb200.so")
 HUE_BINS = 1001
 HIST_STRIDE = 1024
 PLANE_STRIDE = 8
-ABI_VERSION = 4
+ABI_VERSION = 5
+SVB_OK, SVB_E_NULL, SVB_E_SHAPE, SVB_E_ARG, SVB_E_SCRATCH = 0, -1, -2, -3, -4      # include/svb200.h
 
 
 class SvbError(RuntimeError):
@@ -66,6 +67,11 @@ SIGNATURES = {
     "svb_reproject": (I, [P, I, I, CAMP, P, P, P]),
     "svb_reproject_table": (I, [I, I, CAMP, P, P]),
     "svb_scatter_points": (I, [P, I, P, I, I, I, P, P, P]),
+    "svb_bits_words": (L, [I, I]),
+    "svb_pack_mask": (I, [P, I, I, I, P, P, P]),
+    "svb_clean_road": (I, [P, P, I, I, I, P, P, P, P, P]),
+    "svb_clean_road_bits": (I, [P, P, I, I, I, P, P, P, P]),
+    "svb_mask_points": (I, [P, P, I, I, I, I, P, P, P]),
     "svb_road_scratch_bytes": (L, [I, I, I, I]),
     "svb_road_points": (I, [P, P, P, I, I, I, I, CAMP, U32, P, P, P, P, P, P, L, P]),
     "svb_reproject_bits_words": (L, [I, I]),

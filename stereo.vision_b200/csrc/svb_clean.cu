@@ -1,0 +1,454 @@
+// Road-mask cleaning: sanitiseRoadImage, functions.py:346-366, on bit-packed rows.
+//
+// The reference runs closing(9x9) -> erode(9x9) x2 -> AND road_threshold_mask -> closing(9x9) ->
+// ParticleCleansing on a {0,255} byte image and then lists the non-zero pixels in row-major order.
+// With OpenCV's default border (outside pixels never win a max or a min) and square kernels this is
+//
+//      dH9 dV9 | eV25 eH25 | & T | dH9 dV9 | eV9 eH9          (d = dilate, e = erode, H/V = 1-D pass)
+//
+// because two erosions by 9 after the closing's erosion by 9 are one erosion by 25, and each square
+// pass splits into a row pass and a column pass in either order.  ParticleCleansing paints contours of
+// area < 70 white, which cannot change a closed image (the golden fixtures keep the step).
+//
+// One CTA cleans a band of rows of one frame: it loads the band plus a 24-row halo (4+12+4+4), packs
+// bytes to bits (32 pixels per word, LSB = leftmost), runs the nine passes between two shared-memory
+// planes, and writes the cleaned bytes, the cleaned bit rows and the per-row population counts.  A
+// second kernel turns bit rows + row counts into the (x,y) list in the reference's order.
+#include "svb_common.cuh"
+#include "svb_prof.cuh"
+
+#define CL_THREADS 256
+#define CL_HALO 24
+#define CL_SEG 12               // rows per thread in a column pass
+#define CL_PLANE_WORDS 6144     // target size of one shared-memory plane (24 KB)
+
+// ------------------------------------------------------------------ bytes <-> bits
+// high bit of every non-zero byte
+__device__ __forceinline__ uint32_t nz_high(uint32_t v) {
+    return (((v & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | v) & 0x80808080u;
+}
+// 4 bytes -> 4 bits (bit i = byte i non-zero); *odd collects bytes that are neither 0 nor 255
+__device__ __forceinline__ uint32_t pack4(uint32_t v, uint32_t &odd) {
+    uint32_t one = nz_high(v) >> 7;                 // 0x01 per non-zero byte
+    odd |= v ^ (one * 255u);
+    return (one * 0x01020408u) >> 24;               // bits 0,8,16,24 -> 24,25,26,27 (no carries)
+}
+__device__ __forceinline__ uint32_t pack16(uint4 q, uint32_t &odd) {
+    return pack4(q.x, odd) | (pack4(q.y, odd) << 4) | (pack4(q.z, odd) << 8) | (pack4(q.w, odd) << 12);
+}
+// 4 bits -> 4 bytes of 0 / 255
+__device__ __forceinline__ uint32_t spread4(uint32_t nib) {
+    return ((nib * 0x00204081u) & 0x01010101u) * 255u;
+}
+__device__ __forceinline__ uint4 spread16(uint32_t h) {
+    return make_uint4(spread4(h & 15u), spread4((h >> 4) & 15u), spread4((h >> 8) & 15u), spread4((h >> 12) & 15u));
+}
+
+// 32 pixels of a row starting at x0 as one word; vec = row base and W allow 16-byte loads
+__device__ __forceinline__ uint32_t load_word(const uint8_t *row, int x0, int W, bool vec, uint32_t &odd) {
+    if (vec && x0 + 32 <= W) {
+        const uint4 *p = reinterpret_cast<const uint4 *>(row + x0);
+        uint4 a = __ldg(p), b = __ldg(p + 1);
+        return pack16(a, odd) | (pack16(b, odd) << 16);
+    }
+    uint32_t w = 0;
+    int n = min(32, W - x0);
+    for (int i = 0; i < n; ++i) {
+        uint32_t v = row[x0 + i];
+        w |= (uint32_t)(v != 0) << i;
+        odd |= (v != 0 && v != 255) ? 1u : 0u;
+    }
+    return w;
+}
+__device__ __forceinline__ void store_word(uint8_t *row, int x0, int W, bool vec, uint32_t w) {
+    if (vec && x0 + 32 <= W) {
+        uint4 *p = reinterpret_cast<uint4 *>(row + x0);
+        p[0] = spread16(w & 0xFFFFu);
+        p[1] = spread16(w >> 16);
+        return;
+    }
+    int n = min(32, W - x0);
+    for (int i = 0; i < n; ++i) row[x0 + i] = ((w >> i) & 1u) ? 255 : 0;
+}
+
+// ------------------------------------------------------------------ row passes (bits of l | c | r)
+// OR of the bits x-R .. x+R for the 32 positions of c; bits outside the row are 0
+template <int R>
+__device__ __forceinline__ uint32_t hdilate(uint32_t l, uint32_t c, uint32_t r) {
+    if constexpr (R <= 4) {
+        uint32_t o = c;
+#pragma unroll
+        for (int k = 1; k <= R; ++k) o |= __funnelshift_l(l, c, k) | __funnelshift_r(c, r, k);
+        return o;
+    } else {
+        static_assert(R == 12, "row pass radius");
+        // left side on the pair (hi = c, lo = l): windows of 2, 4, 8 then 8 | 4 << 8 | 1 << 12 = 13
+        uint32_t h1 = c | __funnelshift_l(l, c, 1), l1 = l | (l << 1);
+        uint32_t h2 = h1 | __funnelshift_l(l1, h1, 2), l2 = l1 | (l1 << 2);
+        uint32_t h4 = h2 | __funnelshift_l(l2, h2, 4);
+        uint32_t left = h4 | __funnelshift_l(l2, h2, 8) | __funnelshift_l(l, c, 12);
+        // right side on the pair (hi = r, lo = c)
+        uint32_t g1 = c | __funnelshift_r(c, r, 1), r1 = r | (r >> 1);
+        uint32_t g2 = g1 | __funnelshift_r(g1, r1, 2), r2 = r1 | (r1 >> 2);
+        uint32_t g4 = g2 | __funnelshift_r(g2, r2, 4);
+        uint32_t right = g4 | __funnelshift_r(g2, r2, 8) | __funnelshift_r(c, r, 12);
+        return left | right;
+    }
+}
+
+// one row pass over a plane: dst = op(src); ERODE works on the complement (outside bits = 0 there too)
+template <int R, bool ERODE>
+__device__ __forceinline__ uint32_t hpass_word(const uint32_t *srow, int c, int WW, uint32_t tail) {
+    uint32_t l = c > 0 ? srow[c - 1] : (ERODE ? ~0u : 0u);
+    uint32_t m = srow[c];
+    uint32_t r = c + 1 < WW ? srow[c + 1] : (ERODE ? ~0u : 0u);
+    if (ERODE) {
+        l = ~l; m = ~m; r = ~r;
+        if (c + 1 == WW) m &= tail; else if (c + 2 == WW) r &= tail;
+        uint32_t o = ~hdilate<R>(l, m, r);
+        return c + 1 == WW ? (o & tail) : o;
+    }
+    uint32_t o = hdilate<R>(l, m, r);          // the tail bits of src are 0 by construction
+    return c + 1 == WW ? (o & tail) : o;
+}
+
+// ------------------------------------------------------------------ column passes
+struct OrOp  { static __device__ __forceinline__ uint32_t f(uint32_t a, uint32_t b) { return a | b; } static constexpr uint32_t id = 0u; };
+struct AndOp { static __device__ __forceinline__ uint32_t f(uint32_t a, uint32_t b) { return a & b; } static constexpr uint32_t id = ~0u; };
+
+// dst[y] = op over src[y-R .. y+R] (rows outside [0,NR) skipped) for CL_SEG rows of one word column
+template <int R, class Op>
+__device__ __forceinline__ void vpass_item(const uint32_t *src, uint32_t *dst, int c, int WW, int y0, int NR) {
+    constexpr int N = CL_SEG + 2 * R;
+    uint32_t s[N];
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+        int y = y0 - R + i;
+        s[i] = (y >= 0 && y < NR) ? src[y * WW + c] : Op::id;
+    }
+    if constexpr (R == 4) {
+        uint32_t t1[N - 1], t2[N - 3], t4[N - 7];
+#pragma unroll
+        for (int i = 0; i < N - 1; ++i) t1[i] = Op::f(s[i], s[i + 1]);
+#pragma unroll
+        for (int i = 0; i < N - 3; ++i) t2[i] = Op::f(t1[i], t1[i + 2]);
+#pragma unroll
+        for (int i = 0; i < N - 7; ++i) t4[i] = Op::f(t2[i], t2[i + 4]);
+#pragma unroll
+        for (int i = 0; i < CL_SEG; ++i) {
+            int y = y0 + i;
+            if (y < NR) dst[y * WW + c] = Op::f(t4[i], s[i + 8]);
+        }
+    } else {
+        static_assert(R == 4 || R == 12, "column pass radius");
+        uint32_t t1[N - 1], t2[N - 3], t4[N - 7], t16[CL_SEG];
+#pragma unroll
+        for (int i = 0; i < N - 1; ++i) t1[i] = Op::f(s[i], s[i + 1]);
+#pragma unroll
+        for (int i = 0; i < N - 3; ++i) t2[i] = Op::f(t1[i], t1[i + 2]);
+#pragma unroll
+        for (int i = 0; i < N - 7; ++i) t4[i] = Op::f(t2[i], t2[i + 4]);       // rows i .. i+7
+#pragma unroll
+        for (int i = 0; i < CL_SEG; ++i) t16[i] = Op::f(t4[i], t4[i + 8]);      // rows i .. i+15
+#pragma unroll
+        for (int i = 0; i < CL_SEG; ++i) {
+            int y = y0 + i;
+            // 25 = 16 + 8 + 1
+            if (y < NR) dst[y * WW + c] = Op::f(Op::f(t16[i], t4[i + 16]), s[i + 24]);
+        }
+    }
+}
+
+template <int R, class Op>
+__device__ __forceinline__ void vpass(const uint32_t *src, uint32_t *dst, int WW, int NR) {
+    int segs = (NR + CL_SEG - 1) / CL_SEG;
+    for (int it = threadIdx.x; it < segs * WW; it += CL_THREADS) {
+        int seg = it / WW, c = it - seg * WW;
+        vpass_item<R, Op>(src, dst, c, WW, seg * CL_SEG, NR);
+    }
+}
+
+template <int R, bool ERODE>
+__device__ __forceinline__ void hpass(const uint32_t *src, uint32_t *dst, int WW, int NR, uint32_t tail) {
+    for (int it = threadIdx.x; it < NR * WW; it += CL_THREADS) {
+        int y = it / WW, c = it - y * WW;
+        dst[it] = hpass_word<R, ERODE>(src + y * WW, c, WW, tail);
+    }
+}
+
+// ------------------------------------------------------------------ the band kernel
+struct CleanGeom {
+    int H, W, WW;        // WW = words per row
+    int band;            // rows per band
+    int vec;             // rows are 16-byte loadable
+    uint32_t tail;       // valid bits of a row's last word
+};
+
+template <bool PACKED_IN>
+__global__ void __launch_bounds__(CL_THREADS)
+clean_band_kernel(const uint8_t *__restrict__ road, const uint32_t *__restrict__ road_bits, const uint32_t *__restrict__ tbits,
+                  CleanGeom g, uint8_t *__restrict__ cleaned, uint32_t *__restrict__ cleaned_bits,
+                  int32_t *__restrict__ rowcnt, int32_t *__restrict__ status) {
+    extern __shared__ uint32_t s_mem[];
+    const int WW = g.WW, f = blockIdx.y;
+    const int y0 = blockIdx.x * g.band, y1 = min(g.H, y0 + g.band);
+    const int ylo = max(0, y0 - CL_HALO), yhi = min(g.H, y1 + CL_HALO);
+    const int NR = yhi - ylo;
+    uint32_t *A = s_mem, *B = s_mem + (g.band + 2 * CL_HALO) * WW;
+    __shared__ int s_cnt[SVB_MAX_DIM / 8];      // per-row counts of this band (band <= 256 rows)
+
+    // ---- load + pack
+    uint32_t odd = 0;
+    if (PACKED_IN) {
+        const uint32_t *src = road_bits + ((int64_t)f * g.H + ylo) * WW;
+        for (int it = threadIdx.x; it < NR * WW; it += CL_THREADS) A[it] = __ldg(src + it);
+    } else {
+        const uint8_t *src = road + ((int64_t)f * g.H + ylo) * g.W;
+#pragma unroll 2
+        for (int it = threadIdx.x; it < NR * WW; it += CL_THREADS) {
+            int y = it / WW, c = it - y * WW;
+            A[it] = load_word(src + (int64_t)y * g.W, c * 32, g.W, g.vec, odd);
+        }
+    }
+    for (int i = threadIdx.x; i < g.band; i += CL_THREADS) s_cnt[i] = 0;
+    __syncthreads();
+    hpass<4, false>(A, B, WW, NR, g.tail);              // dH9
+    __syncthreads();
+    vpass<4, OrOp>(B, A, WW, NR);                       // dV9
+    __syncthreads();
+    vpass<12, AndOp>(A, B, WW, NR);                     // eV25
+    __syncthreads();
+    {                                                   // eH25, & T
+        const uint32_t *t = tbits + (int64_t)ylo * WW;
+        for (int it = threadIdx.x; it < NR * WW; it += CL_THREADS) {
+            int y = it / WW, c = it - y * WW;
+            A[it] = hpass_word<12, true>(B + y * WW, c, WW, g.tail) & __ldg(t + it);
+        }
+    }
+    __syncthreads();
+    hpass<4, false>(A, B, WW, NR, g.tail);              // dH9
+    __syncthreads();
+    vpass<4, OrOp>(B, A, WW, NR);                       // dV9
+    __syncthreads();
+    vpass<4, AndOp>(A, B, WW, NR);                      // eV9
+    __syncthreads();
+    // ---- eH9 on the band's own rows, store
+    {
+        const int r0 = y0 - ylo, rows = y1 - y0;
+        const bool warp_rows = (WW & 31) == 0;          // a warp's 32 words lie in one row
+        uint8_t *dst = cleaned ? cleaned + ((int64_t)f * g.H + y0) * g.W : nullptr;
+        uint32_t *dbits = cleaned_bits ? cleaned_bits + ((int64_t)f * g.H + y0) * WW : nullptr;
+        const int total = rows * WW, padded = (total + 31) & ~31;
+        for (int it = threadIdx.x; it < padded; it += CL_THREADS) {
+            uint32_t w = 0;
+            int y = 0, c = 0;
+            if (it < total) {
+                y = it / WW; c = it - y * WW;
+                w = hpass_word<4, true>(B + (r0 + y) * WW, c, WW, g.tail);
+                if (dbits) dbits[it] = w;
+                if (dst) store_word(dst + (int64_t)y * g.W, c * 32, g.W, g.vec, w);
+            }
+            int n = __popc(w);
+            if (warp_rows) {
+                n = __reduce_add_sync(0xFFFFFFFFu, n);
+                if ((threadIdx.x & 31) == 0 && n) atomicAdd(&s_cnt[y], n);
+            } else if (n) {
+                atomicAdd(&s_cnt[y], n);
+            }
+        }
+        __syncthreads();
+        if (rowcnt)
+            for (int i = threadIdx.x; i < rows; i += CL_THREADS) rowcnt[(int64_t)f * g.H + y0 + i] = s_cnt[i];
+    }
+    if (!PACKED_IN && status) {
+        odd = __reduce_or_sync(0xFFFFFFFFu, odd);
+        if ((threadIdx.x & 31) == 0 && odd) atomicOr(status, 1);
+    }
+}
+
+static CleanGeom make_clean_geom(int H, int W, const void *img, const void *out) {
+    CleanGeom g;
+    g.H = H; g.W = W; g.WW = (W + 31) / 32;
+    int room = CL_PLANE_WORDS / g.WW - 2 * CL_HALO;
+    int band = room < 32 ? 32 : (room > 256 ? 256 : room);
+    int bands = (H + band - 1) / band;
+    g.band = (H + bands - 1) / bands;               // even split
+    g.vec = (W % 16 == 0) && (((uintptr_t)img | (uintptr_t)out) % 16 == 0);
+    g.tail = (W & 31) ? ((1u << (W & 31)) - 1u) : ~0u;
+    return g;
+}
+
+static int launch_clean(const uint8_t *road, const uint32_t *road_bits, const uint32_t *tbits, int F, int H, int W, uint8_t *cleaned,
+                        uint32_t *cleaned_bits, int32_t *rowcnt, int32_t *status, cudaStream_t st) {
+    if (!tbits || (!road && !road_bits)) return SVB_E_NULL;
+    if (!cleaned && !cleaned_bits) return SVB_E_NULL;
+    if (F < 1 || H < 2 || W < 2 || H > SVB_MAX_DIM || W > SVB_MAX_DIM) return SVB_E_SHAPE;
+    if (road && (const void *)road == (const void *)cleaned) return SVB_E_ARG;      // bands read each other's halo rows
+    if (road_bits && road_bits == cleaned_bits) return SVB_E_ARG;
+    CleanGeom g = make_clean_geom(H, W, road, cleaned);
+    size_t smem = (size_t)2 * (g.band + 2 * CL_HALO) * g.WW * sizeof(uint32_t);
+    dim3 grid((H + g.band - 1) / g.band, F);
+    if (status && road) {
+        cudaError_t e = cudaMemsetAsync(status, 0, sizeof(int32_t), st);
+        if (e != cudaSuccess) return (int)e;
+    }
+    ProfScope ps(K_CLEAN_BAND, st);
+    if (road) {
+        static bool once = false;
+        if (!once) { cudaFuncSetAttribute(clean_band_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024); once = true; }
+        clean_band_kernel<false><<<grid, CL_THREADS, smem, st>>>(road, nullptr, tbits, g, cleaned, cleaned_bits, rowcnt, status);
+    } else {
+        static bool once = false;
+        if (!once) { cudaFuncSetAttribute(clean_band_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024); once = true; }
+        clean_band_kernel<true><<<grid, CL_THREADS, smem, st>>>(nullptr, road_bits, tbits, g, cleaned, cleaned_bits, rowcnt, status);
+    }
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
+}
+
+extern "C" int64_t svb_bits_words(int H, int W) {
+    if (H < 1 || W < 1) return 0;
+    return (int64_t)H * ((W + 31) / 32);
+}
+
+extern "C" int svb_clean_road(const uint8_t *road, const uint32_t *threshold_bits, int F, int H, int W, uint8_t *cleaned,
+                              uint32_t *cleaned_bits, int32_t *rowcnt, int32_t *status, void *stream) {
+    if (!road) return SVB_E_NULL;
+    return launch_clean(road, nullptr, threshold_bits, F, H, W, cleaned, cleaned_bits, rowcnt, status, (cudaStream_t)stream);
+}
+
+extern "C" int svb_clean_road_bits(const uint32_t *road_bits, const uint32_t *threshold_bits, int F, int H, int W, uint8_t *cleaned,
+                                   uint32_t *cleaned_bits, int32_t *rowcnt, void *stream) {
+    if (!road_bits) return SVB_E_NULL;
+    return launch_clean(nullptr, road_bits, threshold_bits, F, H, W, cleaned, cleaned_bits, rowcnt, nullptr, (cudaStream_t)stream);
+}
+
+// ------------------------------------------------------------------ byte mask -> bit rows (+ row counts)
+__global__ void __launch_bounds__(CL_THREADS)
+pack_mask_kernel(const uint8_t *__restrict__ img, int64_t rows, int W, int WW, int vec, uint32_t *__restrict__ bits, int32_t *__restrict__ rowcnt) {
+    int64_t total = rows * WW, padded = (total + 31) & ~(int64_t)31;
+    const bool warp_rows = (WW & 31) == 0;
+    for (int64_t it = (int64_t)blockIdx.x * CL_THREADS + threadIdx.x; it < padded; it += (int64_t)gridDim.x * CL_THREADS) {
+        uint32_t w = 0, odd = 0;
+        int64_t y = 0;
+        if (it < total) {
+            y = it / WW;
+            int c = (int)(it - y * WW);
+            w = load_word(img + y * W, c * 32, W, vec, odd);
+            bits[it] = w;
+        }
+        if (rowcnt) {
+            int n = __popc(w);
+            if (warp_rows) {
+                n = __reduce_add_sync(0xFFFFFFFFu, n);
+                if ((threadIdx.x & 31) == 0 && n) atomicAdd(&rowcnt[y], n);
+            } else if (n) {
+                atomicAdd(&rowcnt[y], n);
+            }
+        }
+    }
+}
+
+extern "C" int svb_pack_mask(const uint8_t *img, int F, int H, int W, uint32_t *bits, int32_t *rowcnt, void *stream) {
+    if (!img || !bits) return SVB_E_NULL;
+    if (F < 1 || H < 1 || W < 1 || H > SVB_MAX_DIM || W > SVB_MAX_DIM) return SVB_E_SHAPE;
+    cudaStream_t st = (cudaStream_t)stream;
+    int WW = (W + 31) / 32;
+    int64_t rows = (int64_t)F * H, total = rows * WW;
+    if (rowcnt) {
+        cudaError_t e = cudaMemsetAsync(rowcnt, 0, sizeof(int32_t) * rows, st);
+        if (e != cudaSuccess) return (int)e;
+    }
+    int vec = (W % 16 == 0) && ((uintptr_t)img % 16 == 0);
+    int64_t blocks = (total + CL_THREADS - 1) / CL_THREADS;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    ProfScope ps(K_PACK_MASK, st);
+    pack_mask_kernel<<<(int)blocks, CL_THREADS, 0, st>>>(img, rows, W, WW, vec, bits, rowcnt);
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
+}
+
+// ------------------------------------------------------------------ bit rows -> (x,y) list, row-major
+#define MP_THREADS 256
+#define MP_ROWS 32              // rows per CTA, four per warp
+
+__global__ void __launch_bounds__(MP_THREADS)
+mask_points_kernel(const uint32_t *__restrict__ bits, const int32_t *__restrict__ rowcnt, int H, int WW, int cap,
+                   int32_t *__restrict__ pts, int32_t *__restrict__ counts) {
+    const int f = blockIdx.y, row0 = blockIdx.x * MP_ROWS;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int32_t *rc = rowcnt + (int64_t)f * H;
+    __shared__ int s_part[MP_THREADS / 32];
+    __shared__ int s_row[MP_ROWS];
+    // points before this CTA's first row, and (first CTA of the frame) the frame's total
+    int before = 0, all = 0;
+    for (int y = threadIdx.x; y < H; y += MP_THREADS) {
+        int n = rc[y];
+        all += n;
+        if (y < row0) before += n;
+    }
+    before = __reduce_add_sync(0xFFFFFFFFu, before);
+    all = __reduce_add_sync(0xFFFFFFFFu, all);
+    __shared__ int s_all[MP_THREADS / 32];
+    if (lane == 0) { s_part[warp] = before; s_all[warp] = all; }
+    __syncthreads();
+    if (warp == 0) {
+        int b = lane < MP_THREADS / 32 ? s_part[lane] : 0;
+        int a = lane < MP_THREADS / 32 ? s_all[lane] : 0;
+        b = __reduce_add_sync(0xFFFFFFFFu, b);
+        a = __reduce_add_sync(0xFFFFFFFFu, a);
+        // exclusive scan of the CTA's row counts (MP_ROWS == 32: one per lane)
+        int y = row0 + lane;
+        int n = y < H ? rc[y] : 0, inc = n;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            int v = __shfl_up_sync(0xFFFFFFFFu, inc, o);
+            if (lane >= o) inc += v;
+        }
+        s_row[lane] = b + inc - n;
+        if (blockIdx.x == 0 && lane == 0 && counts) counts[f] = a;
+    }
+    __syncthreads();
+    int2 *out = reinterpret_cast<int2 *>(pts) + (int64_t)f * cap;
+    for (int r = warp; r < MP_ROWS; r += MP_THREADS / 32) {
+        int y = row0 + r;
+        if (y >= H) break;
+        int base = s_row[r];
+        const uint32_t *row = bits + ((int64_t)f * H + y) * WW;
+        for (int c0 = 0; c0 < WW; c0 += 32) {
+            uint32_t w = c0 + lane < WW ? __ldg(row + c0 + lane) : 0u;
+            int n = __popc(w), inc = n;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                int v = __shfl_up_sync(0xFFFFFFFFu, inc, o);
+                if (lane >= o) inc += v;
+            }
+            int excl = inc - n;
+            uint32_t live = __ballot_sync(0xFFFFFFFFu, w != 0);
+            while (live) {
+                int j = __ffs(live) - 1;
+                live &= live - 1;
+                uint32_t wj = __shfl_sync(0xFFFFFFFFu, w, j);
+                int oj = __shfl_sync(0xFFFFFFFFu, excl, j);
+                if ((wj >> lane) & 1u) {
+                    int idx = base + oj + __popc(wj & ((1u << lane) - 1u));
+                    if (idx < cap) out[idx] = make_int2((c0 + j) * 32 + lane, y);
+                }
+            }
+            base += __shfl_sync(0xFFFFFFFFu, inc, 31);
+        }
+    }
+}
+
+extern "C" int svb_mask_points(const uint32_t *bits, const int32_t *rowcnt, int F, int H, int W, int32_t cap, int32_t *pts,
+                               int32_t *counts, void *stream) {
+    if (!bits || !rowcnt || (!pts && cap > 0)) return SVB_E_NULL;
+    if (F < 1 || H < 1 || W < 1 || H > SVB_MAX_DIM || W > SVB_MAX_DIM) return SVB_E_SHAPE;
+    if (cap < 0) return SVB_E_ARG;
+    cudaStream_t st = (cudaStream_t)stream;
+    dim3 grid((H + MP_ROWS - 1) / MP_ROWS, F);
+    ProfScope ps(K_MASK_POINTS, st);
+    mask_points_kernel<<<grid, MP_THREADS, 0, st>>>(bits, rowcnt, H, (W + 31) / 32, cap, pts, counts);
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
+}

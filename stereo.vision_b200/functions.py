@@ -6,7 +6,8 @@ signatures and error behaviour), executed by the sm_100a kernels behind libsvb20
 Covered: the calls of stereovision.py:58-140 -- disparityCleaning / fillDisparity, maskDisparity,
 capDisparity, projectDisparityTo3d, RANSAC, calculatePointErrors, computePlanarThreshold,
 calculateColourHistogram, filterPointsByHistogram, project3DPointsTo2DImagePoints,
-generatePointsAsImage -- plus the module constants they read.  Clouds are returned as device handles
+generatePointsAsImage -- plus the module constants they read, and the first consumer of the road image,
+sanitiseRoadImage (stereovision.py:156).  Clouds are returned as device handles
 (handles.py) that behave like the reference's lists for everything the orchestrator does with them.
 There is no CPU fallback: without a CUDA device every helper raises.
 
@@ -22,7 +23,7 @@ import torch
 from . import _native as N
 from .camera import DEFAULT_CAMERA, Camera
 from .handles import DeviceColumn, HueHistogram, ImagePoints, PointCloud, bins_from_dict
-from .masks import default_carmask
+from .masks import default_carmask, default_road_threshold_mask
 
 # ---- constants, functions.py:15-24
 camera_focal_length_px = DEFAULT_CAMERA.focal_px
@@ -34,6 +35,7 @@ max_disparity = 128
 # ---- masks, functions.py:29-35 (masks/*.png of the CWD when present, else the packaged arrays)
 carmask = default_carmask((544, 1024))
 blackImg = np.zeros((544, 1024), dtype=np.uint8)
+road_threshold_mask = default_road_threshold_mask((544, 1024))
 # ---- literals of the reference exposed as settings
 lattice_step = 2
 ransac_samples = 600
@@ -264,6 +266,58 @@ def generatePointsAsImage(points):
         if int(oob.item()):
             raise IndexError("road point outside the %dx%d image" % (H, W))
     return img.cpu().numpy()
+
+
+# ---------------------------------------------------------------- f1
+def _threshold_bits(H, W):
+    key = (id(road_threshold_mask), road_threshold_mask.shape)
+    if _state.get("tb_key") != key:
+        if road_threshold_mask.shape != (H, W):
+            raise ValueError("road_threshold_mask is %s, the image %s" % (road_threshold_mask.shape, (H, W)))
+        m = torch.from_numpy(np.ascontiguousarray(road_threshold_mask, dtype=np.uint8)).to(_dev())
+        bits = torch.empty((N.load().svb_bits_words(H, W),), dtype=torch.int32, device=m.device)
+        N.check(N.load().svb_pack_mask(N.ptr(m), 1, H, W, N.ptr(bits), 0, N.stream_ptr()), "svb_pack_mask")
+        N.count(1)
+        _state["tb"], _state["tb_key"] = bits, key
+    return _state["tb"]
+
+
+def sanitiseRoadImage(img, size):
+    """functions.py:346-366: closing, two erosions, road_threshold_mask, closing (9x9), then the (x,y)
+    list of the non-zero pixels as an (N,2) matrix, rows outermost.  `size` = (height, width) as in the
+    reference (opt['img_size']); the image must be the 0 / 255 mask generatePointsAsImage returns."""
+    (height, width) = size
+    t, was_tensor = _to_dev_u8(img)
+    if t.dim() != 2:
+        raise ValueError("sanitiseRoadImage expects a single-channel image")
+    H, W = t.shape
+    if height > H or width > W:
+        raise IndexError("size %s exceeds the %dx%d image" % (size, H, W))      # img[i][j] at :361
+    lib, st, dev = N.load(), N.stream_ptr(), t.device
+    tb = _threshold_bits(H, W)
+    out = torch.empty_like(t)
+    bits = torch.empty((lib.svb_bits_words(H, W),), dtype=torch.int32, device=dev)
+    rowcnt = torch.empty((H,), dtype=torch.int32, device=dev)
+    status = torch.zeros((1,), dtype=torch.int32, device=dev)
+    N.check(lib.svb_clean_road(N.ptr(t), N.ptr(tb), 1, H, W, N.ptr(out), N.ptr(bits), N.ptr(rowcnt), N.ptr(status), st),
+            "svb_clean_road")
+    if (height, width) != (H, W):
+        # the reference scans only the top-left height x width window (:359-361)
+        win = torch.zeros_like(out)
+        win[:height, :width] = out[:height, :width]
+        N.check(lib.svb_pack_mask(N.ptr(win), 1, H, W, N.ptr(bits), N.ptr(rowcnt), st), "svb_pack_mask")
+        N.count(1)
+    counts = torch.empty((1,), dtype=torch.int32, device=dev)
+    N.check(lib.svb_mask_points(N.ptr(bits), N.ptr(rowcnt), 1, H, W, 0, 0, N.ptr(counts), st), "svb_mask_points")
+    n = int(counts.item())
+    if int(status.item()) & 1:
+        raise ValueError("sanitiseRoadImage: the image holds values other than 0 and 255")
+    pts = torch.empty((max(n, 1), 2), dtype=torch.int32, device=dev)
+    N.check(lib.svb_mask_points(N.ptr(bits), N.ptr(rowcnt), 1, H, W, n, N.ptr(pts), N.ptr(counts), st), "svb_mask_points")
+    N.count(3)
+    # np.matrix([]) has shape (1,0) in the reference when nothing is left (:365)
+    mat = np.matrix(pts[:n].cpu().numpy().astype(np.int64)) if n else np.matrix([])
+    return _back(out, was_tensor), mat
 
 
 def getBlackImage():

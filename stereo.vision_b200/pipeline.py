@@ -281,3 +281,59 @@ class SequenceStreamer:
         out = self.run(disp, bgr, seed=seed, out=out)
         torch.cuda.synchronize(self.device)
         return out
+
+
+class RoadCleaner:
+    """The consumer of the road masks: sanitiseRoadImage (functions.py:346-366, called at
+    stereovision.py:156) for F frames per call -- closing, two erosions, road_threshold_mask, closing
+    on bit-packed rows, then the row-major (x,y) list of what is left.
+
+    clean(masks) enqueues two kernels on the current stream (svb_clean_road, svb_mask_points) and
+    returns device tensors: cleaned [F,H,W] uint8, counts [F] int32, points [F,cap,2] int32 of which
+    the first counts[f] rows of frame f are valid.  Buffers are allocated once.
+    """
+
+    def __init__(self, shape=(544, 1024), threshold_mask=None, max_frames=300, cap=None, device="cuda:0",
+                 want_bytes=True):
+        from .masks import default_road_threshold_mask
+        N.require_cuda()
+        self.H, self.W = int(shape[0]), int(shape[1])
+        self.device = torch.device(device)
+        self.lib = N.load()
+        self.F = int(max_frames)
+        H, W, F, dev = self.H, self.W, self.F, self.device
+        self.words = int(self.lib.svb_bits_words(H, W))
+        tm = default_road_threshold_mask((H, W)) if threshold_mask is None else np.ascontiguousarray(threshold_mask, dtype=np.uint8)
+        if tm.shape != (H, W):
+            raise ValueError("threshold mask is %s, frames are %s" % (tm.shape, (H, W)))
+        self.cap = int(cap) if cap is not None else int((tm != 0).sum())        # nothing survives outside the mask
+        self.tbits = torch.empty((self.words,), dtype=torch.int32, device=dev)
+        with torch.cuda.device(dev):
+            t = torch.from_numpy(tm).to(dev)
+            N.check(self.lib.svb_pack_mask(N.ptr(t), 1, H, W, N.ptr(self.tbits), 0, N.stream_ptr()), "svb_pack_mask")
+            torch.cuda.current_stream().synchronize()
+        self.cleaned = torch.empty((F, H, W), dtype=torch.uint8, device=dev) if want_bytes else None
+        self.bits = torch.empty((F, self.words), dtype=torch.int32, device=dev)
+        self.rowcnt = torch.empty((F, H), dtype=torch.int32, device=dev)
+        self.counts = torch.empty((F,), dtype=torch.int32, device=dev)
+        self.points = torch.empty((F, max(self.cap, 1), 2), dtype=torch.int32, device=dev)
+        self.status = torch.zeros((1,), dtype=torch.int32, device=dev)
+
+    def clean(self, masks, points=True):
+        masks = _as_cuda_u8(masks, self.device)
+        if masks.dim() == 2:
+            masks = masks[None]
+        F = masks.shape[0]
+        if tuple(masks.shape[1:]) != (self.H, self.W) or F > self.F:
+            raise ValueError("expected up to %d masks of %dx%d, got %s" % (self.F, self.H, self.W, tuple(masks.shape)))
+        st = N.stream_ptr()
+        N.check(self.lib.svb_clean_road(N.ptr(masks), N.ptr(self.tbits), F, self.H, self.W,
+                                        N.ptr(self.cleaned) if self.cleaned is not None else 0, N.ptr(self.bits),
+                                        N.ptr(self.rowcnt), N.ptr(self.status), st), "svb_clean_road")
+        N.count(1)
+        if points:
+            N.check(self.lib.svb_mask_points(N.ptr(self.bits), N.ptr(self.rowcnt), F, self.H, self.W, self.cap,
+                                             N.ptr(self.points), N.ptr(self.counts), st), "svb_mask_points")
+            N.count(1)
+        cleaned = self.cleaned[:F] if self.cleaned is not None else None
+        return cleaned, self.counts[:F], self.points[:F]
