@@ -209,7 +209,7 @@ int64_t svb_bits_words(int H, int W);
 int svb_pack_mask(const uint8_t *img, int F, int H, int W, uint32_t *bits, int32_t *rowcnt, void *stream);
 /* cleaned[f] = closing 9x9 -> erode 9x9 twice -> keep where threshold != 0 -> closing 9x9 of road[f]
  * (functions.py:349-356; OpenCV default border: outside pixels never win).  road [F,H,W] holds 0 / 255
- * as generatePointsAsImage writes it; any non-zero byte counts as set, and *status (device int32, may
+ * as generatePointsAsImage writes it; a pixel is read by its top bit, and *status (device int32, may
  * be NULL) gets bit 0 when a byte other than 0 / 255 was seen -- the reference would then run grey
  * morphology and its result is NOT reproduced.  ParticleCleansing (:358) provably leaves a closed image
  * unchanged and is not run.  Outputs, each optional but not both image forms NULL:
@@ -255,6 +255,8 @@ int svb_upload_rows(const void *h_src, void *d_dst, int64_t pitch_bytes, int64_t
 int svb_profile_enable(int on);
 /* test hook: force svb_road_points onto its two-kernel path even when the fused cluster kernel applies */
 int svb_debug_force_two_pass(int on);
+/* test hook: row bands per frame of the 1024-wide cleaning kernel (default 4); 0 = use the general kernel */
+int svb_debug_clean_bands(int bands);
 int svb_profile_kernels(void);
 int svb_profile_get(int id, char *name, int name_cap, double *ms_total, int *launches);
 

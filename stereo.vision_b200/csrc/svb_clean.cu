@@ -23,39 +23,57 @@
 #define CL_PLANE_WORDS 6144     // target size of one shared-memory plane (24 KB)
 
 // ------------------------------------------------------------------ bytes <-> bits
-// high bit of every non-zero byte
-__device__ __forceinline__ uint32_t nz_high(uint32_t v) {
-    return (((v & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | v) & 0x80808080u;
+// A pixel is read by its top bit; *odd collects every byte that is neither 0 nor 255 (the caller's
+// status flag: such an image is not a mask and the result is then not the reference's).
+// 4 bytes -> 4 bits in the top nibble: bits 7,15,23,31 times (1 + 2^7 + 2^14 + 2^21) land on 28..31 and
+// no two partial products share a position, so nothing carries.
+// every byte -> 0x00 / 0xFF by its top bit (prmt with selector bit 3 set replicates the sign)
+__device__ __forceinline__ uint32_t byte_signs(uint32_t v) {
+    uint32_t r;
+    asm("prmt.b32 %0, %1, %1, 0xBA98;" : "=r"(r) : "r"(v));
+    return r;
 }
-// 4 bytes -> 4 bits (bit i = byte i non-zero); *odd collects bytes that are neither 0 nor 255
-__device__ __forceinline__ uint32_t pack4(uint32_t v, uint32_t &odd) {
-    uint32_t one = nz_high(v) >> 7;                 // 0x01 per non-zero byte
-    odd |= v ^ (one * 255u);
-    return (one * 0x01020408u) >> 24;               // bits 0,8,16,24 -> 24,25,26,27 (no carries)
+__device__ __forceinline__ uint32_t pack4_top(uint32_t v, uint32_t &odd) {
+    odd |= v ^ byte_signs(v);
+    return (v & 0x80808080u) * 0x00204081u;
 }
 __device__ __forceinline__ uint32_t pack16(uint4 q, uint32_t &odd) {
-    return pack4(q.x, odd) | (pack4(q.y, odd) << 4) | (pack4(q.z, odd) << 8) | (pack4(q.w, odd) << 12);
+    uint32_t a = pack4_top(q.x, odd) >> 28, b = pack4_top(q.y, odd) >> 28, c = pack4_top(q.z, odd) >> 28, d = pack4_top(q.w, odd) >> 28;
+    return a + (b << 4) + (c << 8) + (d << 12);
 }
-// 4 bits -> 4 bytes of 0 / 255
+// the same for any non-zero byte (svb_pack_mask: a cv2 mask argument is read by non-zero-ness)
+__device__ __forceinline__ uint32_t pack4_any(uint32_t v) {
+    uint32_t hi = (((v & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | v) & 0x80808080u;      // top bit of every non-zero byte
+    return (hi * 0x00204081u) >> 28;
+}
+__device__ __forceinline__ uint32_t pack16_any(uint4 q) {
+    return pack4_any(q.x) + (pack4_any(q.y) << 4) + (pack4_any(q.z) << 8) + (pack4_any(q.w) << 12);
+}
+// 4 bits -> 4 bytes of 0 / 255: move bit k to bit 8k+7 with one multiply, then replicate the signs.
+// `nib` holds the four bits at 0..3 (LOW) or at 4..7 (!LOW), everything else zero.
+template <bool LOW>
 __device__ __forceinline__ uint32_t spread4(uint32_t nib) {
-    return ((nib * 0x00204081u) & 0x01010101u) * 255u;
+    return byte_signs(nib * (LOW ? 0x10204080u : 0x01020408u));
 }
-__device__ __forceinline__ uint4 spread16(uint32_t h) {
-    return make_uint4(spread4(h & 15u), spread4((h >> 4) & 15u), spread4((h >> 8) & 15u), spread4((h >> 12) & 15u));
+__device__ __forceinline__ uint4 spread16(uint32_t h) {          // h < 65536
+    uint32_t g = h >> 8;
+    return make_uint4(spread4<true>(h & 0xFu), spread4<false>(h & 0xF0u), spread4<true>(g & 0xFu), spread4<false>(g & 0xF0u));
 }
 
 // 32 pixels of a row starting at x0 as one word; vec = row base and W allow 16-byte loads
+template <bool ANY_NONZERO>
 __device__ __forceinline__ uint32_t load_word(const uint8_t *row, int x0, int W, bool vec, uint32_t &odd) {
     if (vec && x0 + 32 <= W) {
         const uint4 *p = reinterpret_cast<const uint4 *>(row + x0);
         uint4 a = __ldg(p), b = __ldg(p + 1);
+        if (ANY_NONZERO) return pack16_any(a) | (pack16_any(b) << 16);
         return pack16(a, odd) | (pack16(b, odd) << 16);
     }
     uint32_t w = 0;
     int n = min(32, W - x0);
     for (int i = 0; i < n; ++i) {
         uint32_t v = row[x0 + i];
-        w |= (uint32_t)(v != 0) << i;
+        w |= (ANY_NONZERO ? (uint32_t)(v != 0) : (v >> 7)) << i;
         odd |= (v != 0 && v != 255) ? 1u : 0u;
     }
     return w;
@@ -207,7 +225,7 @@ clean_band_kernel(const uint8_t *__restrict__ road, const uint32_t *__restrict__
 #pragma unroll 2
         for (int it = threadIdx.x; it < NR * WW; it += CL_THREADS) {
             int y = it / WW, c = it - y * WW;
-            A[it] = load_word(src + (int64_t)y * g.W, c * 32, g.W, g.vec, odd);
+            A[it] = load_word<false>(src + (int64_t)y * g.W, c * 32, g.W, g.vec, odd);
         }
     }
     for (int i = threadIdx.x; i < g.band; i += CL_THREADS) s_cnt[i] = 0;
@@ -266,6 +284,160 @@ clean_band_kernel(const uint8_t *__restrict__ road, const uint32_t *__restrict__
     }
 }
 
+// ------------------------------------------------------------------ the band kernel for 1024-pixel rows
+// A row is exactly one word per lane: the row passes run in registers with the neighbours' words taken
+// by shuffle (so consecutive row passes fuse, and a row is rewritten in place by the warp that owns it),
+// and the planes carry rows of the pass's identity above and below the data, so the column passes load
+// without bounds tests (plane A feeds the dilations: zeros, plane B the erosions: ones).
+#define C32_TOP 12                       // identity rows above the data (largest column radius)
+#define C32_BOT (12 + CL_SEG)            // below: radius + the overhang of the last row segment
+#define C32_WW 32
+
+template <int R, class Op, int THREADS>
+__device__ __forceinline__ void vpass32(const uint32_t *src, uint32_t *dst, int NR) {
+    constexpr int N = CL_SEG + 2 * R;
+    const int segs = (NR + CL_SEG - 1) / CL_SEG;
+    for (int it = threadIdx.x; it < segs * C32_WW; it += THREADS) {
+        const int y0 = (it >> 5) * CL_SEG, c = it & 31;
+        const uint32_t *s0 = src + (y0 - R + C32_TOP) * C32_WW + c;
+        uint32_t *d0 = dst + (y0 + C32_TOP) * C32_WW + c;
+        uint32_t s[N], o[CL_SEG];
+#pragma unroll
+        for (int i = 0; i < N; ++i) s[i] = s0[i * C32_WW];
+        uint32_t t1[N - 1], t2[N - 3], t4[N - 7];
+#pragma unroll
+        for (int i = 0; i < N - 1; ++i) t1[i] = Op::f(s[i], s[i + 1]);
+#pragma unroll
+        for (int i = 0; i < N - 3; ++i) t2[i] = Op::f(t1[i], t1[i + 2]);
+#pragma unroll
+        for (int i = 0; i < N - 7; ++i) t4[i] = Op::f(t2[i], t2[i + 4]);               // rows i .. i+7
+        if constexpr (R == 4) {
+#pragma unroll
+            for (int i = 0; i < CL_SEG; ++i) o[i] = Op::f(t4[i], s[i + 8]);
+        } else {
+            static_assert(R == 4 || R == 12, "column pass radius");
+#pragma unroll
+            for (int i = 0; i < CL_SEG; ++i) o[i] = Op::f(Op::f(Op::f(t4[i], t4[i + 8]), t4[i + 16]), s[i + 24]);
+        }
+#pragma unroll
+        for (int i = 0; i < CL_SEG; ++i)
+            if (y0 + i < NR) d0[i * C32_WW] = o[i];
+    }
+}
+
+// row passes on one word per lane
+template <int R>
+__device__ __forceinline__ uint32_t hdilate32(uint32_t m, int lane) {
+    uint32_t l = __shfl_up_sync(0xFFFFFFFFu, m, 1), r = __shfl_down_sync(0xFFFFFFFFu, m, 1);
+    if (lane == 0) l = 0u;
+    if (lane == 31) r = 0u;
+    return hdilate<R>(l, m, r);
+}
+template <int R>
+__device__ __forceinline__ uint32_t herode32(uint32_t m, int lane) { return ~hdilate32<R>(~m, lane); }
+
+template <bool PACKED_IN, int THREADS>
+__global__ void __launch_bounds__(THREADS)
+clean_rows32_kernel(const uint8_t *__restrict__ road, const uint32_t *__restrict__ road_bits, const uint32_t *__restrict__ tbits,
+                    int H, int band, uint8_t *__restrict__ cleaned, uint32_t *__restrict__ cleaned_bits,
+                    int32_t *__restrict__ rowcnt, int32_t *__restrict__ status) {
+    extern __shared__ uint32_t s_mem[];
+    constexpr int W = 1024, NW = THREADS / 32;
+    const int f = blockIdx.y, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int y0 = blockIdx.x * band, y1 = min(H, y0 + band);
+    const int ylo = max(0, y0 - CL_HALO), yhi = min(H, y1 + CL_HALO);
+    const int NR = yhi - ylo;
+    const int plane = (band + 2 * CL_HALO + C32_TOP + C32_BOT) * C32_WW;
+    uint32_t *A = s_mem, *B = s_mem + plane;
+    uint32_t *Ad = A + C32_TOP * C32_WW, *Bd = B + C32_TOP * C32_WW;        // first data row
+    for (int i = threadIdx.x; i < C32_TOP * C32_WW; i += THREADS) { A[i] = 0u; B[i] = ~0u; }
+    for (int i = threadIdx.x; i < C32_BOT * C32_WW; i += THREADS) { Ad[NR * C32_WW + i] = 0u; Bd[NR * C32_WW + i] = ~0u; }
+
+    // ---- load, pack, dH9 -> A
+    uint32_t odd = 0;
+    if (PACKED_IN) {
+        const uint32_t *src = road_bits + ((int64_t)f * H + ylo) * C32_WW;
+        for (int y = warp; y < NR; y += NW) Ad[y * C32_WW + lane] = hdilate32<4>(__ldg(src + y * C32_WW + lane), lane);
+    } else {
+        const uint4 *src = reinterpret_cast<const uint4 *>(road + ((int64_t)f * H + ylo) * W) + lane * 2;
+        int y = warp;
+        for (; y + NW < NR; y += 2 * NW) {                                 // two rows in flight per warp
+            const uint4 *p = src + (int64_t)y * (W / 16), *q = p + NW * (W / 16);
+            uint4 a0 = __ldg(p), a1 = __ldg(p + 1), b0 = __ldg(q), b1 = __ldg(q + 1);
+            uint32_t wa = pack16(a0, odd) | (pack16(a1, odd) << 16), wb = pack16(b0, odd) | (pack16(b1, odd) << 16);
+            Ad[y * C32_WW + lane] = hdilate32<4>(wa, lane);
+            Ad[(y + NW) * C32_WW + lane] = hdilate32<4>(wb, lane);
+        }
+        for (; y < NR; y += NW) {
+            const uint4 *p = src + (int64_t)y * (W / 16);
+            uint4 a0 = __ldg(p), a1 = __ldg(p + 1);
+            Ad[y * C32_WW + lane] = hdilate32<4>(pack16(a0, odd) | (pack16(a1, odd) << 16), lane);
+        }
+    }
+    __syncthreads();
+    vpass32<4, OrOp, THREADS>(A, B, NR);                 // dV9
+    __syncthreads();
+    vpass32<12, AndOp, THREADS>(B, A, NR);               // eV25
+    __syncthreads();
+    {                                                    // eH25, & T, dH9: in place, a warp owns its rows
+        const uint32_t *t = tbits + (int64_t)ylo * C32_WW + lane;
+        for (int y = warp; y < NR; y += NW) {
+            uint32_t m = herode32<12>(Ad[y * C32_WW + lane], lane) & __ldg(t + y * C32_WW);
+            Ad[y * C32_WW + lane] = hdilate32<4>(m, lane);
+        }
+    }
+    __syncthreads();
+    vpass32<4, OrOp, THREADS>(A, B, NR);                 // dV9
+    __syncthreads();
+    vpass32<4, AndOp, THREADS>(B, A, NR);                // eV9
+    __syncthreads();
+    {                                                    // eH9 on the band's own rows, store
+        const int r0 = y0 - ylo, rows = y1 - y0;
+        uint4 *dst = cleaned ? reinterpret_cast<uint4 *>(cleaned + ((int64_t)f * H + y0) * W) + lane * 2 : nullptr;
+        uint32_t *dbits = cleaned_bits ? cleaned_bits + ((int64_t)f * H + y0) * C32_WW + lane : nullptr;
+        int32_t *rc = rowcnt ? rowcnt + (int64_t)f * H + y0 : nullptr;
+        for (int y = warp; y < rows; y += NW) {
+            uint32_t w = herode32<4>(Ad[(r0 + y) * C32_WW + lane], lane);
+            if (dbits) dbits[y * C32_WW] = w;
+            if (dst) {
+                uint4 *p = dst + (int64_t)y * (W / 16);
+                p[0] = spread16(w & 0xFFFFu);
+                p[1] = spread16(w >> 16);
+            }
+            if (rc) {
+                int n = __reduce_add_sync(0xFFFFFFFFu, __popc(w));
+                if (lane == 0) rc[y] = n;
+            }
+        }
+    }
+    if (!PACKED_IN && status) {
+        odd = __reduce_or_sync(0xFFFFFFFFu, odd);
+        if (lane == 0 && odd) atomicOr(status, 1);
+    }
+}
+
+static int g_clean_bands32 = 4;          // row bands per 1024-wide frame (svb_debug_clean_bands)
+extern "C" int svb_debug_clean_bands(int bands) {
+    if (bands < 0 || bands > 16) return SVB_E_ARG;
+    g_clean_bands32 = bands;             // 0 = the general kernel
+    return SVB_OK;
+}
+
+template <bool PACKED_IN, int THREADS>
+static int launch_rows32(const uint8_t *road, const uint32_t *road_bits, const uint32_t *tbits, int F, int H, int bands,
+                         uint8_t *cleaned, uint32_t *cleaned_bits, int32_t *rowcnt, int32_t *status, cudaStream_t st) {
+    int band = (H + bands - 1) / bands;
+    size_t smem = (size_t)2 * (band + 2 * CL_HALO + C32_TOP + C32_BOT) * C32_WW * sizeof(uint32_t);
+    static bool once = false;
+    if (!once) {
+        cudaFuncSetAttribute(clean_rows32_kernel<PACKED_IN, THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        once = true;
+    }
+    dim3 grid((H + band - 1) / band, F);
+    clean_rows32_kernel<PACKED_IN, THREADS><<<grid, THREADS, smem, st>>>(road, road_bits, tbits, H, band, cleaned, cleaned_bits, rowcnt, status);
+    return SVB_OK;
+}
+
 static CleanGeom make_clean_geom(int H, int W, const void *img, const void *out) {
     CleanGeom g;
     g.H = H; g.W = W; g.WW = (W + 31) / 32;
@@ -293,6 +465,20 @@ static int launch_clean(const uint8_t *road, const uint32_t *road_bits, const ui
         if (e != cudaSuccess) return (int)e;
     }
     ProfScope ps(K_CLEAN_BAND, st);
+    const bool aligned = (((uintptr_t)road | (uintptr_t)cleaned) % 16) == 0;
+    if (W == 1024 && aligned && g_clean_bands32 > 0) {
+        int bands = g_clean_bands32;
+        while ((H + bands - 1) / bands + 2 * CL_HALO + C32_TOP + C32_BOT > 200 * 1024 / (2 * C32_WW * 4)) ++bands;
+        if ((H + bands - 1) / bands > 160) {
+            if (road) launch_rows32<false, 512>(road, nullptr, tbits, F, H, bands, cleaned, cleaned_bits, rowcnt, status, st);
+            else launch_rows32<true, 512>(nullptr, road_bits, tbits, F, H, bands, cleaned, cleaned_bits, rowcnt, status, st);
+        } else {
+            if (road) launch_rows32<false, 256>(road, nullptr, tbits, F, H, bands, cleaned, cleaned_bits, rowcnt, status, st);
+            else launch_rows32<true, 256>(nullptr, road_bits, tbits, F, H, bands, cleaned, cleaned_bits, rowcnt, status, st);
+        }
+        SVB_LAUNCH_CHECK();
+        return SVB_OK;
+    }
     if (road) {
         static bool once = false;
         if (!once) { cudaFuncSetAttribute(clean_band_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024); once = true; }
@@ -334,7 +520,7 @@ pack_mask_kernel(const uint8_t *__restrict__ img, int64_t rows, int W, int WW, i
         if (it < total) {
             y = it / WW;
             int c = (int)(it - y * WW);
-            w = load_word(img + y * W, c * 32, W, vec, odd);
+            w = load_word<true>(img + y * W, c * 32, W, vec, odd);
             bits[it] = w;
         }
         if (rowcnt) {
@@ -370,7 +556,7 @@ extern "C" int svb_pack_mask(const uint8_t *img, int F, int H, int W, uint32_t *
 
 // ------------------------------------------------------------------ bit rows -> (x,y) list, row-major
 #define MP_THREADS 256
-#define MP_ROWS 32              // rows per CTA, four per warp
+#define MP_ROWS 64              // rows per CTA, eight per warp, two per lane in the row scan
 
 __global__ void __launch_bounds__(MP_THREADS)
 mask_points_kernel(const uint32_t *__restrict__ bits, const int32_t *__restrict__ rowcnt, int H, int WW, int cap,
@@ -378,18 +564,18 @@ mask_points_kernel(const uint32_t *__restrict__ bits, const int32_t *__restrict_
     const int f = blockIdx.y, row0 = blockIdx.x * MP_ROWS;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int32_t *rc = rowcnt + (int64_t)f * H;
-    __shared__ int s_part[MP_THREADS / 32];
+    __shared__ int s_part[MP_THREADS / 32], s_all[MP_THREADS / 32];
     __shared__ int s_row[MP_ROWS];
     // points before this CTA's first row, and (first CTA of the frame) the frame's total
     int before = 0, all = 0;
-    for (int y = threadIdx.x; y < H; y += MP_THREADS) {
+    const int upto = blockIdx.x == 0 ? H : row0;
+    for (int y = threadIdx.x; y < upto; y += MP_THREADS) {
         int n = rc[y];
         all += n;
         if (y < row0) before += n;
     }
     before = __reduce_add_sync(0xFFFFFFFFu, before);
     all = __reduce_add_sync(0xFFFFFFFFu, all);
-    __shared__ int s_all[MP_THREADS / 32];
     if (lane == 0) { s_part[warp] = before; s_all[warp] = all; }
     __syncthreads();
     if (warp == 0) {
@@ -397,15 +583,17 @@ mask_points_kernel(const uint32_t *__restrict__ bits, const int32_t *__restrict_
         int a = lane < MP_THREADS / 32 ? s_all[lane] : 0;
         b = __reduce_add_sync(0xFFFFFFFFu, b);
         a = __reduce_add_sync(0xFFFFFFFFu, a);
-        // exclusive scan of the CTA's row counts (MP_ROWS == 32: one per lane)
-        int y = row0 + lane;
-        int n = y < H ? rc[y] : 0, inc = n;
+        // exclusive scan of the CTA's row counts, two rows per lane
+        int ya = row0 + 2 * lane;
+        int na = ya < H ? rc[ya] : 0, nb = ya + 1 < H ? rc[ya + 1] : 0;
+        int n = na + nb, inc = n;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
             int v = __shfl_up_sync(0xFFFFFFFFu, inc, o);
             if (lane >= o) inc += v;
         }
-        s_row[lane] = b + inc - n;
+        s_row[2 * lane] = b + inc - n;
+        s_row[2 * lane + 1] = b + inc - n + na;
         if (blockIdx.x == 0 && lane == 0 && counts) counts[f] = a;
     }
     __syncthreads();
@@ -417,6 +605,8 @@ mask_points_kernel(const uint32_t *__restrict__ bits, const int32_t *__restrict_
         const uint32_t *row = bits + ((int64_t)f * H + y) * WW;
         for (int c0 = 0; c0 < WW; c0 += 32) {
             uint32_t w = c0 + lane < WW ? __ldg(row + c0 + lane) : 0u;
+            uint32_t live = __ballot_sync(0xFFFFFFFFu, w != 0);
+            if (live == 0) continue;
             int n = __popc(w), inc = n;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
@@ -424,14 +614,14 @@ mask_points_kernel(const uint32_t *__restrict__ bits, const int32_t *__restrict_
                 if (lane >= o) inc += v;
             }
             int excl = inc - n;
-            uint32_t live = __ballot_sync(0xFFFFFFFFu, w != 0);
+            const uint32_t below = (1u << lane) - 1u;
             while (live) {
                 int j = __ffs(live) - 1;
                 live &= live - 1;
                 uint32_t wj = __shfl_sync(0xFFFFFFFFu, w, j);
                 int oj = __shfl_sync(0xFFFFFFFFu, excl, j);
                 if ((wj >> lane) & 1u) {
-                    int idx = base + oj + __popc(wj & ((1u << lane) - 1u));
+                    int idx = base + oj + __popc(wj & below);
                     if (idx < cap) out[idx] = make_int2((c0 + j) * 32 + lane, y);
                 }
             }

@@ -70,7 +70,15 @@ def check_against_oracle(res, imgs, tm):
         assert np.array_equal(res["pts"][f, :n], wpts), "frame %d point order" % f
 
 
-def test_golden_cases(cuda):
+@pytest.fixture(params=[4, 2, 1, 0], ids=lambda b: "bands%d" % b)
+def bands(request):
+    """row bands per frame of the 1024-wide kernel; 0 = the general kernel"""
+    N.check(N.load().svb_debug_clean_bands(request.param), "bands")
+    yield request.param
+    N.check(N.load().svb_debug_clean_bands(4), "bands")
+
+
+def test_golden_cases(cuda, bands):
     """every case of the reference fixture: image sha, point count, point list sha -- bit exact"""
     cases = sanitise_cases()
     full = [(n, i, t, r) for n, i, t, r in cases if i.shape == (544, 1024)]
@@ -106,7 +114,7 @@ def test_shapes_against_oracle(cuda, shape):
     assert np.array_equal(res2["bits"], res["bits"]) and np.array_equal(res2["pts"], res["pts"])
 
 
-def test_empty_full_and_flagged_inputs(cuda):
+def test_empty_full_and_flagged_inputs(cuda, bands):
     tm = default_road_threshold_mask()
     imgs = np.zeros((3, 544, 1024), np.uint8)
     imgs[1] = 255

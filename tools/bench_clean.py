@@ -38,12 +38,13 @@ def timeit(fn, n=10):
     return a.elapsed_time(b) / n * 1e3
 
 
-for want_bytes in (True, False):
+for bands, want_bytes in ((0, True), (4, True), (3, True), (2, True), (1, True), (4, False), (2, False)):
+    N.check(N.load().svb_debug_clean_bands(bands), "bands")
     cl = RoadCleaner((H, W), max_frames=F, device=dev, want_bytes=want_bytes)
     t_all = timeit(lambda: cl.clean(masks))
     t_clean = timeit(lambda: cl.clean(masks, points=False))
     torch.cuda.synchronize()
     n = int(cl.counts.sum().item())
     by = masks.numel() * (2 if want_bytes else 1) + cl.bits.numel() * 4
-    print("bytes out=%s: clean %.1f us (%.0f GB/s algorithmic), clean+points %.1f us, %d points/frame, status %d"
-          % (want_bytes, t_clean, by / t_clean / 1e3, t_all, n // F, int(cl.status.item())))
+    print("bands %d bytes out=%s: clean %.1f us (%.0f GB/s algorithmic), clean+points %.1f us, %d points/frame, status %d"
+          % (bands, want_bytes, t_clean, by / t_clean / 1e3, t_all, n // F, int(cl.status.item())))
