@@ -155,6 +155,7 @@ def algorithmic_bytes(kernel, L, N, M, K, R, T, S):
         "proj_write": 2.0 * L + 3.0 * N + 8.0 * N + 4.0 * M,  # d, carmask, rgb in; cloud + mcloud out
         "ransac_score": 4.0 * T * (S + 3) + 8.0 * T,          # gathered records (shared memory / L2) + errors out
         "road_cluster": 8.0 * N + 1.0 * H * W + 1.0 * R,      # records in, mask cleared, road bytes out
+        "road_sites": 1.0 * L + 3.0 * K + 1.0 * H * W + 1.0 * R,  # lattice disparities + colour of the near points in, mask cleared, road bytes out
         "road_near": 8.0 * N + 1.0 * H * W + 4.0 * K,         # records in, mask cleared, near list out
         "road_scatter": 4.0 * K + 1.0 * R,                    # near list in, road bytes out
         "road_pass1": 8.0 * N + N / 8.0,                      # records in, near bits out

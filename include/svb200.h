@@ -240,6 +240,21 @@ int svb_road_points(const uint64_t *cloud, const int32_t *counts, const double *
                     uint32_t *hist, uint8_t *road_mask, uint8_t *overlay, int32_t *counts_out,
                     void *scratch, int64_t scratch_bytes, void *stream);
 
+/* ---- a8-a14 fused, batched, straight from the path's inputs
+ * The same outputs as svb_road_points, computed from the filled disparity (a1's output) and the colour
+ * image instead of the cloud records: near-plane membership depends on (x, y, d) only, so the lattice
+ * sites are read at 1 byte each and the colour only where a near point sits (functions.py:195 reads the
+ * same pixel).  filled uint8 [F,H,W]; bgr uint8 [F,H,W,3] (lattice rows suffice); reproj_bits is required.
+ * counts[f*4+2] = K_f, counts[f*4+3] = R_f; counts[f*4+0..1] are not touched.  Applies when
+ * svb_road_sites_supported(H,W,step) = 1 (step 1 or 2); otherwise SVB_E_ARG and the caller uses
+ * svb_road_points.  scratch: svb_road_sites_scratch_bytes(F,H,W,step), 4-byte aligned. */
+int svb_road_sites_supported(int H, int W, int step);
+int64_t svb_road_sites_scratch_bytes(int F, int H, int W, int step);
+int svb_road_points_sites(const uint8_t *filled, const uint8_t *bgr, const double *planes, int F, int H, int W, int step,
+                          const svb_camera *cam, uint32_t colour_threshold, const uint32_t *reproj_bits, uint32_t *hist,
+                          uint8_t *road_mask, uint8_t *overlay, int32_t *counts, void *scratch, int64_t scratch_bytes,
+                          void *stream);
+
 /* ---- host -> device upload of the rows the path reads
  * The projection reads the colour image only on lattice rows (every step-th row), so an end-to-end caller
  * need not send the others: this copies `rows` rows of `width_bytes` bytes, `pitch_bytes` apart in BOTH the

@@ -17,7 +17,7 @@ LIB_PATH = os.path.join(_PKG, "libsvb200.so")
 HUE_BINS = 1001
 HIST_STRIDE = 1024
 PLANE_STRIDE = 8
-ABI_VERSION = 5
+ABI_VERSION = 6
 SVB_OK, SVB_E_NULL, SVB_E_SHAPE, SVB_E_ARG, SVB_E_SCRATCH = 0, -1, -2, -3, -4      # include/svb200.h
 
 
@@ -74,6 +74,9 @@ SIGNATURES = {
     "svb_mask_points": (I, [P, P, I, I, I, I, P, P, P]),
     "svb_road_scratch_bytes": (L, [I, I, I, I]),
     "svb_road_points": (I, [P, P, P, I, I, I, I, CAMP, U32, P, P, P, P, P, P, L, P]),
+    "svb_road_sites_supported": (I, [I, I, I]),
+    "svb_road_sites_scratch_bytes": (L, [I, I, I, I]),
+    "svb_road_points_sites": (I, [P, P, P, I, I, I, I, CAMP, U32, P, P, P, P, P, P, L, P]),
     "svb_reproject_bits_words": (L, [I, I]),
     "svb_reproject_bits": (I, [I, I, CAMP, P, P, P]),
     "svb_upload_rows": (I, [P, P, L, L, L, P]),

@@ -60,7 +60,9 @@ class BatchResult:
 class RoadPath:
     def __init__(self, shape=(544, 1024), step=2, trials=600, samples=600, point_threshold=0.05,
                  colour_threshold=10, carmask=None, camera: Camera = DEFAULT_CAMERA, max_frames=1,
-                 device="cuda:0", use_reproj_table=True):
+                 device="cuda:0", use_reproj_table=True, road_path="sites"):
+        if road_path not in ("sites", "records"):
+            raise ValueError("road_path is 'sites' or 'records'")
         N.require_cuda()
         self.lib = N.load()
         self.device = torch.device(device)
@@ -93,7 +95,8 @@ class RoadPath:
         self.hist = torch.zeros((F, N.HIST_STRIDE), dtype=torch.int32, device=dev)
         self.road_mask = torch.empty((F, H, W), dtype=torch.uint8, device=dev)
         nb = max(self.lib.svb_project_scratch_bytes(F, H, W, self.step),
-                 self.lib.svb_road_scratch_bytes(F, H, W, self.step))
+                 self.lib.svb_road_scratch_bytes(F, H, W, self.step),
+                 self.lib.svb_road_sites_scratch_bytes(F, H, W, self.step))
         self.scratch = torch.empty(((nb + 15) // 16 * 16,), dtype=torch.uint8, device=dev)
         # reprojection displacement bits (built once; used only if every (coordinate, d) moves by 0 or -1)
         self.reproj_bits = torch.empty((self.lib.svb_reproject_bits_words(H, W),), dtype=torch.int32, device=dev)
@@ -106,6 +109,12 @@ class RoadPath:
         # (params, near, scatter kernels); without the displacement table the legacy two-pass kernels
         self.fused_road = self.reproj_bits is not None and ((self.L + 2047) // 2048 + 7) // 8 * 2048 * 4 <= 160 * 1024
         self.road_launches = 1 if self.fused_road else (3 if self.reproj_bits is not None else 2)
+        # svb_road_points_sites: the same outputs from the filled disparity + colour image (1 byte per lattice site
+        # instead of an 8-byte record); road_path = "records" keeps svb_road_points
+        self.sites_road = (road_path == "sites" and self.reproj_bits is not None
+                           and bool(self.lib.svb_road_sites_supported(H, W, self.step)))
+        if self.sites_road:
+            self.road_launches = 2
 
     # ------------------------------------------------------------------
     def process(self, disp, bgr, prev=None, seed=0, frame0=0, indices=None, overlay=None,
@@ -159,10 +168,16 @@ class RoadPath:
         if overlay is not None:
             ov = _as_cuda_u8(overlay, dev)
             res.overlay = ov
-        N.check(lib.svb_road_points(N.ptr(self.cloud), N.ptr(self.counts), N.ptr(self.planes), F, H, W, self.step,
-                                    C.byref(self._cam), self.colour_threshold, N.ptr(self.reproj_bits), N.ptr(self.hist), N.ptr(self.road_mask),
-                                    N.ptr(ov), N.ptr(self.counts), N.ptr(self.scratch), self.scratch.numel(), st),
-                "svb_road_points")
+        if self.sites_road:
+            N.check(lib.svb_road_points_sites(N.ptr(src), N.ptr(bgr), N.ptr(self.planes), F, H, W, self.step, C.byref(self._cam),
+                                              self.colour_threshold, N.ptr(self.reproj_bits), N.ptr(self.hist), N.ptr(self.road_mask),
+                                              N.ptr(ov), N.ptr(self.counts), N.ptr(self.scratch), self.scratch.numel(), st),
+                    "svb_road_points_sites")
+        else:
+            N.check(lib.svb_road_points(N.ptr(self.cloud), N.ptr(self.counts), N.ptr(self.planes), F, H, W, self.step,
+                                        C.byref(self._cam), self.colour_threshold, N.ptr(self.reproj_bits), N.ptr(self.hist), N.ptr(self.road_mask),
+                                        N.ptr(ov), N.ptr(self.counts), N.ptr(self.scratch), self.scratch.numel(), st),
+                    "svb_road_points")
         N.count(KERNELS_PER_BATCH - 1 + self.road_launches + (0 if fill else 2))   # no fill: copy + count kernels
         return res
 

@@ -162,15 +162,21 @@ def test_road_points_without_reprojection_table(cuda):
 
 
 def test_road_paths_agree(cuda):
-    """svb_road_points' three implementations -- cluster kernel (default at this size), legacy two-pass, streamed -- agree."""
+    """svb_road_points' three implementations -- cluster kernel, legacy two-pass, streamed -- and
+    svb_road_points_sites (the default of RoadPath) agree."""
     import stereo.vision_b200._native as N
     from stereo.vision_b200.pipeline import RoadPath
     F = 3
     disp, bgr = synth.make_sequence(5, F)
     cm = _carmask(disp.shape[1:])
-    eng = RoadPath(carmask=cm, max_frames=F, samples=400)
-    assert eng.fused_road
+    eng = RoadPath(carmask=cm, max_frames=F, samples=400, road_path="records")
+    assert eng.fused_road and not eng.sites_road
     ra = to_host(eng.process(disp, bgr, seed=5))
+    sites = RoadPath(carmask=cm, max_frames=F, samples=400)           # the default: a8-a14 from disparity + colour
+    assert sites.sites_road
+    rs = to_host(sites.process(disp, bgr, seed=5))
+    for k in ("road_mask", "counts", "hist", "planes"):
+        assert np.array_equal(ra[k], rs[k]), ("sites", k)
     for mode in (1, 3):
         N.load().svb_debug_force_two_pass(mode)
         try:
@@ -182,15 +188,18 @@ def test_road_paths_agree(cuda):
     assert ra["road_mask"].any()
 
 
-def test_config3_full_density_step1(cuda):
-    """BASELINE config 3: step 1 (555 489 lattice sites), RGB attach, masked-cloud RANSAC; the road points
-    take the streamed path (the near list of a frame no longer fits a cluster's shared memory)."""
+@pytest.mark.parametrize("road_path", ["sites", "records"])
+def test_config3_full_density_step1(cuda, road_path):
+    """BASELINE config 3: step 1 (555 489 lattice sites), RGB attach, masked-cloud RANSAC.  The road points
+    come from the disparity + colour image (default), or from the cloud records on the streamed path (the near
+    list of a frame no longer fits a cluster's shared memory)."""
     from stereo.vision_b200.pipeline import RoadPath
     F, T, S = 2, 600, 400
     disp, bgr = synth.make_sequence(8, F)
     cm = _carmask(disp.shape[1:])
-    eng = RoadPath(step=1, trials=T, samples=S, carmask=cm, max_frames=F)
-    assert not eng.fused_road and eng.road_launches == 3
+    eng = RoadPath(step=1, trials=T, samples=S, carmask=cm, max_frames=F, road_path=road_path)
+    assert not eng.fused_road and eng.road_launches == (2 if road_path == "sites" else 3)
+    assert eng.sites_road == (road_path == "sites")
     r = eng.process(disp, bgr, seed=31)
     si, ti = eng.dump_indices(F, seed=31)
     res = to_host(r)

@@ -38,7 +38,7 @@ def timeit(fn, n=10):
     return a.elapsed_time(b) / n * 1e3
 
 
-for bands, want_bytes in ((0, True), (4, True), (3, True), (2, True), (1, True), (4, False), (2, False)):
+for bands, want_bytes in ((0, True), (4, True), (2, True), (4, False)):
     N.check(N.load().svb_debug_clean_bands(bands), "bands")
     cl = RoadCleaner((H, W), max_frames=F, device=dev, want_bytes=want_bytes)
     t_all = timeit(lambda: cl.clean(masks))
