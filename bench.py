@@ -155,7 +155,8 @@ def algorithmic_bytes(kernel, L, N, M, K, R, T, S):
         "proj_write": 2.0 * L + 3.0 * N + 8.0 * N + 4.0 * M,  # d, carmask, rgb in; cloud + mcloud out
         "ransac_score": 4.0 * T * (S + 3) + 8.0 * T,          # gathered records (shared memory / L2) + errors out
         "road_cluster": 8.0 * N + 1.0 * H * W + 1.0 * R,      # records in, mask cleared, road bytes out
-        "road_sites": 1.0 * L + 3.0 * K + 1.0 * H * W + 1.0 * R,  # lattice disparities + colour of the near points in, mask cleared, road bytes out
+        "road_sites": 1.0 * L + 3.0 * K + 1.0 * H * W + 4.0 * K,  # lattice disparities + colour of the near points in, mask cleared, near list out
+        "road_sites_scatter": 4.0 * K + 1.0 * R,              # listed near points in, road bytes out
         "road_near": 8.0 * N + 1.0 * H * W + 4.0 * K,         # records in, mask cleared, near list out
         "road_scatter": 4.0 * K + 1.0 * R,                    # near list in, road bytes out
         "road_pass1": 8.0 * N + N / 8.0,                      # records in, near bits out
@@ -228,6 +229,33 @@ def run_b200(args):
             v["alg_bytes"] = ab * F
             v["gbs"] = ab * F / (v["ms_per_launch"] * 1e-3) / 1e9
 
+    # ---- SURVEY 8(f)-1, the consumer of the road masks (sanitiseRoadImage): timed beside the path, not part of `value`
+    next_rows = None
+    if rank == 0:
+        from stereo.vision_b200.pipeline import RoadCleaner
+        cl = RoadCleaner((H, W), max_frames=F, device=dev)
+        masks = res.road_mask
+        for _ in range(3):
+            cl.clean(masks)
+        torch.cuda.synchronize()
+        N.profile_enable(True)
+        for _ in range(5):
+            cl.clean(masks)
+        torch.cuda.synchronize()
+        cprof = N.profile_read()
+        N.profile_enable(False)
+        pts = float(cl.counts[:F].float().mean().item())
+        calg = {"clean_band": 2.0 * H * W + 4.0 * ((W + 31) // 32) * H + 4.0 * H,     # mask in, cleaned bytes + bit rows + row counts out
+                "mask_points": 4.0 * ((W + 31) // 32) * H + 4.0 * H + 8.0 * pts}       # bit rows + row counts in, (x,y) int32 pairs out
+        next_rows = {"row": "SURVEY 8(f)-1 sanitiseRoadImage on the step's %d road masks (not part of `value`)" % F,
+                     "mean_points": pts, "status": int(cl.status.item()), "kernels": {}}
+        for k, v in cprof.items():
+            if k in calg:
+                t_ms = v[0] / v[1]
+                next_rows["kernels"][k] = {"ms_per_launch": round(t_ms, 6), "alg_bytes": calg[k] * F,
+                                           "gbs": round(calg[k] * F / (t_ms * 1e-3) / 1e9, 3)}
+        del cl
+
     # ---- end to end: pinned host frames in, masks / planes / counts out, chunked + double buffered
     e2e = None
     if not args.no_e2e:
@@ -277,6 +305,10 @@ def run_b200(args):
                          "share_of_step": d["share"], "longest_kernel": top},
             "kernels": {k: {kk: (round(vv, 6) if isinstance(vv, float) else vv) for kk, vv in v.items()} for k, v in kern.items()},
         }
+        if next_rows:
+            for v in next_rows["kernels"].values():
+                v["frac_of_peak"] = round(v["gbs"] / peak, 4)
+            out["next_rows"] = next_rows
         if e2e:
             out["e2e"] = {"value": F * world / (e2e_ms_max * 1e-3), "unit": "frames/s",
                           "h2d_bytes_per_step": e2e["h2d"], "d2h_bytes_per_step": e2e["d2h"],
