@@ -215,9 +215,62 @@ def sanitise_fixture():
     save("sanitise.npz", recs)
 
 
+def preprocess_inputs():
+    """Seeded colour pairs for the front-end fixture: two synthetic frames (the right image is the left
+    shifted by 12 px), a low-contrast pair (few grey levels: the equalisation LUT is mostly steps), a
+    single-colour image (equalizeHist's degenerate branch) and a 37x53 pair."""
+    out = []
+    for t in range(2):
+        _, bgr = synth.make_frame(0, t)
+        out.append(("seq0_f%d" % t, bgr, np.roll(bgr, -12, axis=1)))
+    rng = np.random.default_rng(4242)
+    low = (100 + rng.integers(0, 9, (544, 1024, 3))).astype(np.uint8)
+    out.append(("low_contrast", low, low[:, ::-1].copy()))
+    flat = np.full((544, 1024, 3), 77, np.uint8)
+    out.append(("flat", flat, (flat // 2).astype(np.uint8)))
+    small = rng.integers(0, 256, (37, 53, 3), dtype=np.uint8)
+    out.append(("small_37x53", small, small[::-1].copy()))
+    return out
+
+
+def preprocess_fixture():
+    f = rh.load_reference()
+    flat = {}
+    # gamma tables straight from the reference's expression (functions.py:62-65) through cv2.LUT on a ramp
+    ramp = np.arange(256, dtype=np.uint8).reshape(16, 16)
+    gammas = np.array([1.4, 1.0, 2.2, 0.5, 1.8])
+    flat["gammas"] = gammas
+    flat["gamma_tables"] = np.stack([f.gammaChange(ramp, float(g)).reshape(256) for g in gammas])
+    # BGR2GRAY over all 2^24 colours, through the reference's greyscale() minus equalisation: cv2 itself
+    import cv2
+    r, g, b = np.meshgrid(np.arange(256, dtype=np.uint8), np.arange(256, dtype=np.uint8), np.arange(256, dtype=np.uint8), indexing="ij")
+    cube = np.stack([b, g, r], axis=-1).reshape(4096, 4096, 3)          # index = r*65536 + g*256 + b, channels B,G,R
+    gray = cv2.cvtColor(cube, cv2.COLOR_BGR2GRAY)
+    flat["gray_all_sha"] = sha(gray)
+    flat["gray_r128"] = gray.reshape(256, 256, 256)[128].copy()          # the red = 128 plane verbatim
+    recs = []
+    for name, imgL, imgR in preprocess_inputs():
+        gl, gr, yl, yr = rh.run_preprocess(f, imgL, imgR)
+        recs.append({"name": name, "inL_sha": sha(imgL), "inR_sha": sha(imgR), "gammaL_sha": sha(gl), "gammaR_sha": sha(gr),
+                     "grayL_sha": sha(yl), "grayR_sha": sha(yr),
+                     "grayL_hist": np.bincount(yl.ravel(), minlength=256), "grayR_hist": np.bincount(yr.ravel(), minlength=256),
+                     "grayL_head": yl[:2, :64].copy()})
+        print("  preprocess %-13s %s" % (name, sha(yl)[:12]))
+    small = preprocess_inputs()[-1]
+    gl, gr, yl, yr = rh.run_preprocess(f, small[1], small[2])
+    recs[-1].update(inL=small[1], inR=small[2], gammaL=gl, grayL=yl, grayR=yr)
+    flat["n_frames"] = len(recs)
+    for i, r_ in enumerate(recs):
+        for k, v in r_.items():
+            flat["f%d_%s" % (i, k)] = v
+    path = os.path.join(OUT, "preprocess.npz")
+    np.savez_compressed(path, **flat)
+    print("wrote preprocess.npz (%.1f KB)" % (os.path.getsize(path) / 1024))
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
-    which = sys.argv[1:] or ["seq", "s400", "step1", "small", "noplane", "reproject", "hue", "sanitise"]
+    which = sys.argv[1:] or ["seq", "s400", "step1", "small", "noplane", "reproject", "hue", "sanitise", "preprocess"]
     if "seq" in which:
         sequence_fixture("seq0_step2_s600.npz", 0, 3)
     if "s400" in which:
@@ -234,3 +287,5 @@ if __name__ == "__main__":
         hue_fixture()
     if "sanitise" in which:
         sanitise_fixture()
+    if "preprocess" in which:
+        preprocess_fixture()

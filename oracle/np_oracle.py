@@ -311,3 +311,54 @@ def nonzero_points(img):
     """functions.py:359-365: (x, y) of the non-zero pixels in row-major order, int32 [N,2]."""
     ys, xs = np.nonzero(img)
     return np.stack([xs, ys], axis=1).astype(np.int32)
+
+
+# ---------------------------------------------------------------- f2: pre-processing front end
+def gamma_table(gamma=1.0):
+    """functions.py:62-65: table[i] = uint8(((i / 255.0) ** (1 / gamma)) * 255), truncated, evaluated value by
+    value in float64 as the reference's list comprehension does."""
+    inv = 1.0 / gamma
+    return np.array([((i / 255.0) ** inv) * 255 for i in np.arange(0, 256)]).astype("uint8")
+
+
+def gamma_change(image, gamma=1.0):
+    """functions.py:61-67 (cv2.LUT over every channel byte)."""
+    return gamma_table(gamma)[np.asarray(image, dtype=np.uint8)]
+
+
+def bgr_to_gray(bgr):
+    """cv2.cvtColor(..., COLOR_BGR2GRAY) on uint8 (functions.py:93): OpenCV's fixed point,
+    (B*3735 + G*19235 + R*9798 + 2^14) >> 15 (coefficients 0.114, 0.587, 0.299 in 15 bits)."""
+    b = bgr[..., 0].astype(np.int32)
+    g = bgr[..., 1].astype(np.int32)
+    r = bgr[..., 2].astype(np.int32)
+    return ((b * 3735 + g * 19235 + r * 9798 + (1 << 14)) >> 15).astype(np.uint8)
+
+
+def equalize_lut(hist):
+    """The look-up table of cv2.equalizeHist (functions.py:95) from a 256-bin histogram: first populated
+    bin i0 maps to 0; lut[i] = saturate(rint(float32(sum_{i0<k<=i} hist[k]) * scale)) with the float32
+    scale = 255 / (total - hist[i0]); an image of one value maps to itself."""
+    hist = np.asarray(hist, dtype=np.int64)
+    total = int(hist.sum())
+    i0 = int(np.nonzero(hist)[0][0])
+    if hist[i0] == total:
+        return np.arange(256, dtype=np.uint8) * 0 + np.uint8(i0)
+    scale = np.float32(255.0) / np.float32(total - hist[i0])
+    s = np.cumsum(hist) - np.cumsum(hist)[i0]
+    v = np.rint(s.astype(np.float32) * scale)
+    lut = np.clip(v, 0, 255).astype(np.uint8)
+    lut[:i0 + 1] = 0
+    return lut
+
+
+def equalize_hist(gray):
+    gray = np.asarray(gray, dtype=np.uint8)
+    return equalize_lut(np.bincount(gray.ravel(), minlength=256))[gray]
+
+
+def preprocess_pair(imgL, imgR, gamma=1.4):
+    """stereovision.py:44,46: gamma-corrected colour images (functions.py:80-86) and their equalised
+    grey versions (functions.py:88-96)."""
+    gl, gr = gamma_change(imgL, gamma), gamma_change(imgR, gamma)
+    return gl, gr, equalize_hist(bgr_to_gray(gl)), equalize_hist(bgr_to_gray(gr))

@@ -191,6 +191,13 @@ def run_sanitise(f, road_image, road_threshold_mask=None):
     pts = np.asarray(pts, dtype=np.int32).reshape(-1, 2) if pts.size else np.zeros((0, 2), np.int32)
     return np.asarray(img), pts
 
+
+def run_preprocess(f, imgL, imgR):
+    """stereovision.py:44,46: the unmodified preProcessImages + greyscale (functions.py:80-96)."""
+    gl, gr = f.preProcessImages(np.array(imgL, copy=True), np.array(imgR, copy=True))
+    yl, yr = f.greyscale(gl, gr)
+    return np.asarray(gl), np.asarray(gr), np.asarray(yl), np.asarray(yr)
+
 def hist_to_bins(hist: dict) -> np.ndarray:
     """Reference histogram dict (keys = str(round(hue,3))) -> 1001 counts indexed by rint(hue*1000)."""
     bins = np.zeros(1001, dtype=np.int64)

@@ -93,3 +93,29 @@ def sanitise_cases():
         img = np.unpackbits(r["in_bits"])[:H * W].reshape(H, W) * np.uint8(255)
         out.append((str(r["name"]), img, tm, r))
     return out
+
+
+def preprocess_cases():
+    """(name, left BGR, right BGR, golden record) of tests/golden/preprocess.npz, inputs regenerated from seeds
+    exactly as oracle/make_golden.py:preprocess_inputs builds them, plus the fixture's global tables."""
+    import os
+    import stereo.vision_b200.synth as synth
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "preprocess.npz")
+    with np.load(path, allow_pickle=False) as z:
+        g = {k: z[k] for k in z.files}
+    ins = []
+    for t in range(2):
+        _, bgr = synth.make_frame(0, t)
+        ins.append((bgr, np.roll(bgr, -12, axis=1)))
+    rng = np.random.default_rng(4242)
+    low = (100 + rng.integers(0, 9, (544, 1024, 3))).astype(np.uint8)
+    ins.append((low, low[:, ::-1].copy()))
+    flat = np.full((544, 1024, 3), 77, np.uint8)
+    ins.append((flat, (flat // 2).astype(np.uint8)))
+    small = rng.integers(0, 256, (37, 53, 3), dtype=np.uint8)
+    ins.append((small, small[::-1].copy()))
+    out = []
+    for i, (a, b) in enumerate(ins):
+        p = "f%d_" % i
+        out.append((str(g[p + "name"]), a, b, {k[len(p):]: v for k, v in g.items() if k.startswith(p)}))
+    return out, g

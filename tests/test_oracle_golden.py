@@ -129,3 +129,20 @@ def test_sanitise_road_image():
         assert np.array_equal(pts[:64], r["pts_head"]) and np.array_equal(pts[-64:], r["pts_tail"])
         if "pts" in r:
             assert np.array_equal(pts, r["pts"])
+
+
+def test_preprocess_front_end():
+    """oracle f2 (gamma LUT, BGR->gray, equalizeHist) vs the unmodified preProcessImages / greyscale and cv2."""
+    from helpers import preprocess_cases
+    cases, g = preprocess_cases()
+    for k, gamma in enumerate(g["gammas"]):
+        assert np.array_equal(no.gamma_table(float(gamma)), g["gamma_tables"][k]), gamma
+    r, gg, b = np.meshgrid(np.arange(256, dtype=np.uint8), np.arange(256, dtype=np.uint8), np.arange(256, dtype=np.uint8), indexing="ij")
+    gray = no.bgr_to_gray(np.stack([b, gg, r], axis=-1).reshape(4096, 4096, 3))
+    assert sha(gray) == str(g["gray_all_sha"]), "BGR2GRAY over all 2^24 colours"
+    assert np.array_equal(gray.reshape(256, 256, 256)[128], g["gray_r128"])
+    for name, imgL, imgR, rec in cases:
+        assert sha(imgL) == str(rec["inL_sha"]) and sha(imgR) == str(rec["inR_sha"]), name
+        gl, gr, yl, yr = no.preprocess_pair(imgL, imgR, 1.4)
+        assert sha(gl) == str(rec["gammaL_sha"]) and sha(gr) == str(rec["gammaR_sha"]), name
+        assert sha(yl) == str(rec["grayL_sha"]) and sha(yr) == str(rec["grayR_sha"]), name
