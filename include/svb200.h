@@ -225,6 +225,20 @@ int svb_clean_road_bits(const uint32_t *road_bits, const uint32_t *threshold_bit
 int svb_mask_points(const uint32_t *bits, const int32_t *rowcnt, int F, int H, int W, int32_t cap, int32_t *pts,
                     int32_t *counts, void *stream);
 
+/* ---- f2  gammaChange / greyscale: the front end                         functions.py:61-67, 80-96
+ * For F images bgr uint8 [F,H,W,3]: every byte through table (HOST pointer to 256 bytes, cv2.LUT with
+ * the table of functions.py:62-65; NULL = identity) -> bgr_out; gray uint8 [F,H,W] of the corrected
+ * colours (COLOR_BGR2GRAY: (3735 B + 19235 G + 9798 R + 2^14) >> 15); hist uint32 [F,256] of gray,
+ * zeroed here.  Each output may be NULL, not all three. */
+int svb_gamma_gray_hist(const uint8_t *bgr, int F, int H, int W, const uint8_t *h_table, uint8_t *bgr_out, uint8_t *gray,
+                        uint32_t *hist, void *stream);
+/* cv2.equalizeHist's table per image from its histogram: lut uint8 [F,256] (functions.py:95) */
+int svb_equalize_lut(const uint32_t *hist, int F, uint8_t *lut, void *stream);
+/* dst[f][i] = lut[f][src[f][i]], i < n_per_frame (lut: device, uint8 [F,256]) */
+int svb_apply_lut_frames(const uint8_t *src, int F, int64_t n_per_frame, const uint8_t *lut, uint8_t *dst, void *stream);
+/* dst[i] = lut[src[i]], i < n (lut: device, 256 bytes): cv2.LUT on any byte array */
+int svb_lut_bytes(const uint8_t *src, int64_t n, const uint8_t *lut, uint8_t *dst, void *stream);
+
 /* ---- a8-a14 fused, batched: the road points of F frames               stereovision.py:97-140
  * reproj_bits: table of svb_reproject_bits or NULL.
  * pass 1: near = |P.abc-1| < cutoff ; per-frame hue histogram of the near points (shared memory,

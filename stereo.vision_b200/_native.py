@@ -17,7 +17,7 @@ LIB_PATH = os.path.join(_PKG, "libsvb200.so")
 HUE_BINS = 1001
 HIST_STRIDE = 1024
 PLANE_STRIDE = 8
-ABI_VERSION = 6
+ABI_VERSION = 7
 SVB_OK, SVB_E_NULL, SVB_E_SHAPE, SVB_E_ARG, SVB_E_SCRATCH = 0, -1, -2, -3, -4      # include/svb200.h
 
 
@@ -67,6 +67,10 @@ SIGNATURES = {
     "svb_reproject": (I, [P, I, I, CAMP, P, P, P]),
     "svb_reproject_table": (I, [I, I, CAMP, P, P]),
     "svb_scatter_points": (I, [P, I, P, I, I, I, P, P, P]),
+    "svb_gamma_gray_hist": (I, [P, I, I, I, P, P, P, P, P]),
+    "svb_equalize_lut": (I, [P, I, P, P]),
+    "svb_apply_lut_frames": (I, [P, I, L, P, P, P]),
+    "svb_lut_bytes": (I, [P, L, P, P, P]),
     "svb_bits_words": (L, [I, I]),
     "svb_pack_mask": (I, [P, I, I, I, P, P, P]),
     "svb_clean_road": (I, [P, P, I, I, I, P, P, P, P, P]),

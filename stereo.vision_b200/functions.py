@@ -6,8 +6,9 @@ signatures and error behaviour), executed by the sm_100a kernels behind libsvb20
 Covered: the calls of stereovision.py:58-140 -- disparityCleaning / fillDisparity, maskDisparity,
 capDisparity, projectDisparityTo3d, RANSAC, calculatePointErrors, computePlanarThreshold,
 calculateColourHistogram, filterPointsByHistogram, project3DPointsTo2DImagePoints,
-generatePointsAsImage -- plus the module constants they read, and the first consumer of the road image,
-sanitiseRoadImage (stereovision.py:156).  Clouds are returned as device handles
+generatePointsAsImage -- plus the module constants they read, the first consumer of the road image,
+sanitiseRoadImage (stereovision.py:156), and the front end gammaChange / preProcessImages / greyscale
+(stereovision.py:44,46).  Clouds are returned as device handles
 (handles.py) that behave like the reference's lists for everything the orchestrator does with them.
 There is no CPU fallback: without a CUDA device every helper raises.
 
@@ -318,6 +319,50 @@ def sanitiseRoadImage(img, size):
     # np.matrix([]) has shape (1,0) in the reference when nothing is left (:365)
     mat = np.matrix(pts[:n].cpu().numpy().astype(np.int64)) if n else np.matrix([])
     return _back(out, was_tensor), mat
+
+
+# ---------------------------------------------------------------- f2
+def _gamma_table(gamma):
+    """functions.py:62-65, value by value in float64 (host side in the reference as well)."""
+    inv = 1.0 / gamma
+    return np.array([((i / 255.0) ** inv) * 255 for i in np.arange(0, 256)]).astype("uint8")
+
+
+def gammaChange(image, gamma=1.0):
+    """functions.py:61-67: every byte of the image through the gamma table (cv2.LUT)."""
+    t, was_tensor = _to_dev_u8(image)
+    table = np.ascontiguousarray(_gamma_table(gamma))
+    lut = torch.from_numpy(table).to(t.device)
+    out = torch.empty_like(t)
+    if t.numel():
+        N.check(N.load().svb_lut_bytes(N.ptr(t), t.numel(), N.ptr(lut), N.ptr(out), N.stream_ptr()), "svb_lut_bytes")
+        N.count(1)
+    return _back(out, was_tensor)
+
+
+def preProcessImages(imgL, imgR):
+    """functions.py:80-86: gamma 1.4 on both images."""
+    return (gammaChange(imgL, 1.4), gammaChange(imgR, 1.4))
+
+
+def greyscale(imgL, imgR):
+    """functions.py:88-96: COLOR_BGR2GRAY then equalizeHist, per image."""
+    lib, st, out = N.load(), N.stream_ptr(), []
+    for img in (imgL, imgR):
+        t, was_tensor = _to_dev_u8(img)
+        if t.dim() != 3 or t.shape[2] != 3:
+            raise ValueError("greyscale expects BGR images")
+        H, W = int(t.shape[0]), int(t.shape[1])
+        gray = torch.empty((H, W), dtype=torch.uint8, device=t.device)
+        hist = torch.empty((256,), dtype=torch.int32, device=t.device)
+        lut = torch.empty((256,), dtype=torch.uint8, device=t.device)
+        N.check(lib.svb_gamma_gray_hist(N.ptr(t), 1, H, W, None, 0, N.ptr(gray), N.ptr(hist), st), "svb_gamma_gray_hist")
+        N.check(lib.svb_equalize_lut(N.ptr(hist), 1, N.ptr(lut), st), "svb_equalize_lut")
+        eq = torch.empty_like(gray)
+        N.check(lib.svb_apply_lut_frames(N.ptr(gray), 1, H * W, N.ptr(lut), N.ptr(eq), st), "svb_apply_lut_frames")
+        N.count(3)
+        out.append(_back(eq, was_tensor))
+    return (out[0], out[1])
 
 
 def getBlackImage():

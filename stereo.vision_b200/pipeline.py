@@ -352,3 +352,42 @@ class RoadCleaner:
             N.count(1)
         cleaned = self.cleaned[:F] if self.cleaned is not None else None
         return cleaned, self.counts[:F], self.points[:F]
+
+
+class FrontEnd:
+    """The producer of the path's colour input: preProcessImages + greyscale (functions.py:80-96, called at
+    stereovision.py:44,46) for F images per call -- gamma table on every BGR byte, gray of the corrected
+    colours, per-image histogram, equalizeHist's table, equalised gray.  Three kernels per call
+    (svb_gamma_gray_hist, svb_equalize_lut, svb_apply_lut_frames); buffers are allocated once."""
+
+    def __init__(self, shape=(544, 1024), gamma=1.4, max_frames=300, device="cuda:0"):
+        N.require_cuda()
+        self.H, self.W, self.F = int(shape[0]), int(shape[1]), int(max_frames)
+        self.device = torch.device(device)
+        self.lib = N.load()
+        inv = 1.0 / gamma
+        self.table = np.ascontiguousarray(np.array([((i / 255.0) ** inv) * 255 for i in np.arange(0, 256)]).astype("uint8"))
+        self._tp = self.table.ctypes.data_as(C.c_void_p)
+        F, H, W, dev = self.F, self.H, self.W, self.device
+        self.bgr = torch.empty((F, H, W, 3), dtype=torch.uint8, device=dev)
+        self.gray = torch.empty((F, H, W), dtype=torch.uint8, device=dev)
+        self.eq = torch.empty((F, H, W), dtype=torch.uint8, device=dev)
+        self.hist = torch.empty((F, 256), dtype=torch.int32, device=dev)
+        self.lut = torch.empty((F, 256), dtype=torch.uint8, device=dev)
+
+    def process(self, bgr):
+        """bgr uint8 [F,H,W,3] -> (gamma-corrected bgr [F,H,W,3], equalised gray [F,H,W]) device tensors."""
+        bgr = _as_cuda_u8(bgr, self.device)
+        if bgr.dim() == 3:
+            bgr = bgr[None]
+        F = bgr.shape[0]
+        if tuple(bgr.shape[1:]) != (self.H, self.W, 3) or F > self.F:
+            raise ValueError("expected up to %d images of %dx%dx3, got %s" % (self.F, self.H, self.W, tuple(bgr.shape)))
+        st = N.stream_ptr()
+        N.check(self.lib.svb_gamma_gray_hist(N.ptr(bgr), F, self.H, self.W, self._tp, N.ptr(self.bgr), N.ptr(self.gray),
+                                             N.ptr(self.hist), st), "svb_gamma_gray_hist")
+        N.check(self.lib.svb_equalize_lut(N.ptr(self.hist), F, N.ptr(self.lut), st), "svb_equalize_lut")
+        N.check(self.lib.svb_apply_lut_frames(N.ptr(self.gray), F, self.H * self.W, N.ptr(self.lut), N.ptr(self.eq), st),
+                "svb_apply_lut_frames")
+        N.count(3)
+        return self.bgr[:F], self.eq[:F]
