@@ -255,6 +255,29 @@ def run_b200(args):
                 next_rows["kernels"][k] = {"ms_per_launch": round(t_ms, 6), "alg_bytes": calg[k] * F,
                                            "gbs": round(calg[k] * F / (t_ms * 1e-3) / 1e9, 3)}
         del cl
+        # SURVEY 8(f)-2, the producer of the colour input (preProcessImages + greyscale) on the step's left images
+        from stereo.vision_b200.pipeline import FrontEnd
+        fe = FrontEnd((H, W), max_frames=F, device=dev)
+        for _ in range(2):
+            fe.process(bgr_d)
+        torch.cuda.synchronize()
+        N.profile_enable(True)
+        for _ in range(3):
+            fe.process(bgr_d)
+        torch.cuda.synchronize()
+        fprof = N.profile_read()
+        N.profile_enable(False)
+        falg = {"prep_gamma_gray": 7.0 * H * W + 1024.0,      # BGR in, corrected BGR + gray out, histogram
+                "prep_apply_lut": 2.0 * H * W + 256.0}        # gray in, equalised gray out
+        front = {"row": "SURVEY 8(f)-2 preProcessImages + greyscale on the step's %d left images (not part of `value`)" % F, "kernels": {}}
+        for k, v in fprof.items():
+            if k.startswith("prep_"):
+                t_ms = v[0] / v[1]
+                front["kernels"][k] = {"ms_per_launch": round(t_ms, 6)}
+                if k in falg:
+                    front["kernels"][k].update(alg_bytes=falg[k] * F, gbs=round(falg[k] * F / (t_ms * 1e-3) / 1e9, 3))
+        next_rows = {"f1_road_mask_cleaning": next_rows, "f2_front_end": front}
+        del fe
 
     # ---- end to end: pinned host frames in, masks / planes / counts out, chunked + double buffered
     e2e = None
@@ -306,8 +329,10 @@ def run_b200(args):
             "kernels": {k: {kk: (round(vv, 6) if isinstance(vv, float) else vv) for kk, vv in v.items()} for k, v in kern.items()},
         }
         if next_rows:
-            for v in next_rows["kernels"].values():
-                v["frac_of_peak"] = round(v["gbs"] / peak, 4)
+            for row in next_rows.values():
+                for v in row["kernels"].values():
+                    if "gbs" in v:
+                        v["frac_of_peak"] = round(v["gbs"] / peak, 4)
             out["next_rows"] = next_rows
         if e2e:
             out["e2e"] = {"value": F * world / (e2e_ms_max * 1e-3), "unit": "frames/s",
