@@ -239,6 +239,19 @@ int svb_apply_lut_frames(const uint8_t *src, int F, int64_t n_per_frame, const u
 /* dst[i] = lut[src[i]], i < n (lut: device, 256 bytes): cv2.LUT on any byte array */
 int svb_lut_bytes(const uint8_t *src, int64_t n, const uint8_t *lut, uint8_t *dst, void *stream);
 
+/* ---- f3  fillAltDisparity ('mean' option)                              functions.py:149-162
+ * filled[f][y][x] = d where d >= 2, else trunc(mean of the row's non-zero entries) (0 for an empty row).
+ * filled may alias disparity (a row is summed completely before the warp that owns it rewrites it). */
+int svb_fill_row_mean(const uint8_t *disparity, int F, int H, int W, uint8_t *filled, void *stream);
+/* ---- f3  getNormalVectorLine                                            functions.py:396-416
+ * out_xy[f] = int(x'), int(y') of the reference's float64 sequence for base point base_xy[f] = (x, y), plane
+ * abc[f*abc_stride .. +2] and the disparity under the base point: disparity uint8 [F,H,W], or NULL and
+ * d_values uint8 [F].  status[f]: 0 ok, 1 a conversion would raise ValueError (nan), 2 OverflowError (inf),
+ * 4 the base point is outside the image (IndexError).  All device pointers. */
+int svb_normal_line(const int32_t *base_xy, const double *abc, int abc_stride, const uint8_t *disparity,
+                    const uint8_t *d_values, int F, int H, int W, const svb_camera *cam, int32_t *out_xy,
+                    int32_t *status, void *stream);
+
 /* ---- a8-a14 fused, batched: the road points of F frames               stereovision.py:97-140
  * reproj_bits: table of svb_reproject_bits or NULL.
  * pass 1: near = |P.abc-1| < cutoff ; per-frame hue histogram of the near points (shared memory,

@@ -268,9 +268,53 @@ def preprocess_fixture():
     print("wrote preprocess.npz (%.1f KB)" % (os.path.getsize(path) / 1024))
 
 
+def option_fixture():
+    """fillAltDisparity on seeded disparities (rows without any value, rows of ones, a ragged
+    width) and getNormalVectorLine on a grid of base points x planes x disparities."""
+    f = rh.load_reference()
+    flat = {}
+    rng = np.random.default_rng(808)
+    imgs = []
+    d, _ = synth.make_frame(4, 0)
+    imgs.append(d)
+    e = rng.integers(0, 6, (544, 1024), dtype=np.uint8)            # many values below 2, small means
+    e[10] = 0; e[11] = 1; e[12, :500] = 0; e[13] = 255; e[14, ::2] = 0
+    imgs.append(e)
+    imgs.append(rng.integers(0, 256, (37, 53), dtype=np.uint8) * (rng.random((37, 53)) < 0.6))
+    flat["n_fill"] = len(imgs)
+    for i, im in enumerate(imgs):
+        im = np.ascontiguousarray(im, dtype=np.uint8)
+        out = rh.run_fill_alt(f, im)
+        if im.size <= 4096:
+            flat["fill%d_in" % i] = im
+        flat["fill%d_in_sha" % i] = sha(im)
+        flat["fill%d_shape" % i] = np.array(im.shape)
+        flat["fill%d_out_sha" % i] = sha(out)
+        flat["fill%d_out_rows" % i] = out[:16].copy()
+        print("  fillAlt %d: %s" % (i, sha(out)[:12]))
+    # the normal glyph
+    planes = [np.array([0.002, 0.9, 0.03]), np.array([-0.05, 1.1, 0.01]), np.array([0.0, 0.0, 0.5]), np.array([0.3, -0.2, 0.04])]
+    pts, res = [], []
+    disp = np.zeros((544, 1024), np.uint8)
+    for k, abc in enumerate(planes):
+        for (x, y) in [(0, 0), (512, 300), (1023, 543), (474, 262), (100, 500), (900, 400)]:
+            for dv in (0, 1, 7, 40, 128, 255):
+                disp[y, x] = dv
+                r = rh.run_normal_line(f, (x, y), abc, disp)
+                pts.append((k, x, y, dv))
+                res.append(r if isinstance(r, tuple) else (-(2 ** 31), {"ValueError": 1, "OverflowError": 2}.get(r, 3)))
+    flat["normal_planes"] = np.stack(planes)
+    flat["normal_cases"] = np.array(pts, dtype=np.int64)
+    flat["normal_results"] = np.array(res, dtype=np.int64)
+    path = os.path.join(OUT, "options.npz")
+    np.savez_compressed(path, **flat)
+    print("wrote options.npz (%.1f KB), %d normal-line cases, %d raise" % (os.path.getsize(path) / 1024, len(res),
+                                                                            sum(1 for r in res if r[0] == -(2 ** 31))))
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
-    which = sys.argv[1:] or ["seq", "s400", "step1", "small", "noplane", "reproject", "hue", "sanitise", "preprocess"]
+    which = sys.argv[1:] or ["seq", "s400", "step1", "small", "noplane", "reproject", "hue", "sanitise", "preprocess", "options"]
     if "seq" in which:
         sequence_fixture("seq0_step2_s600.npz", 0, 3)
     if "s400" in which:
@@ -289,3 +333,5 @@ if __name__ == "__main__":
         sanitise_fixture()
     if "preprocess" in which:
         preprocess_fixture()
+    if "options" in which:
+        option_fixture()

@@ -362,3 +362,37 @@ def preprocess_pair(imgL, imgR, gamma=1.4):
     grey versions (functions.py:88-96)."""
     gl, gr = gamma_change(imgL, gamma), gamma_change(imgR, gamma)
     return gl, gr, equalize_hist(bgr_to_gray(gl)), equalize_hist(bgr_to_gray(gr))
+
+
+# ---------------------------------------------------------------- f3: 'mean' fill and the normal glyph
+def fill_alt_disparity(d):
+    """functions.py:149-162 (threshold_option 'mean'): every row's entries below 2 become the row's mean over
+    its non-zero entries (float64 mean, 0.0 for an empty row, truncated by the uint8 store).  Returns a new
+    array; the reference writes into its argument."""
+    d = np.array(d, dtype=np.uint8, copy=True)
+    for i in range(d.shape[0]):
+        row = d[i]
+        nz = row[row != 0]
+        mean = nz.mean() if len(nz) else 0.0
+        row[row < 2] = np.uint8(mean)                 # C-style truncation, as the element-wise store does
+    return d
+
+
+def normal_vector_line(base_point, abc, d_at_base, camera=None):
+    """functions.py:396-416 (getNormalVectorLine): the image point of the road point under `base_point`
+    lifted 0.7 m along -Y and dropped back onto ... the reference's own formula, operation by operation in
+    float64.  Returns (int, int) truncated toward zero; raises like int() does on nan / inf."""
+    c = cam_of(camera)
+    x, y = base_point
+    a, b, cc = (np.float64(v) for v in np.asarray(abc, dtype=np.float64).reshape(3))
+    with np.errstate(all="ignore"):
+        Z = np.float64(c.f * c.B) / np.float64(d_at_base)
+        X = ((x - c.cw) * Z) / c.f
+        Y = ((y - c.ch) * Z) / c.f
+        newY = Y - 0.7
+        newX = X + 0.0
+        dd = np.sqrt(a * a + b * b + cc * cc)
+        Z = dd - ((a * newX) + (b * newY))
+        newX = ((newX * c.f) / Z) + c.cw
+        newY = ((newY * c.f) / Z) + c.ch
+    return (int(newX), int(newY))

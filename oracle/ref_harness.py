@@ -198,6 +198,24 @@ def run_preprocess(f, imgL, imgR):
     yl, yr = f.greyscale(gl, gr)
     return np.asarray(gl), np.asarray(gr), np.asarray(yl), np.asarray(yr)
 
+
+def run_fill_alt(f, disparity):
+    """stereovision.py:58 with threshold_option 'mean': disparityCleaning -> fillAltDisparity (functions.py:136-137,
+    149-162) on a copy (the reference writes into its argument)."""
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")          # mean of an empty slice
+        return np.asarray(f.disparityCleaning(np.array(disparity, copy=True), 'mean', None))
+
+
+def run_normal_line(f, base_point, abc, disparity):
+    """functions.py:396-416 on a (3,1) plane as RANSAC returns it; (x, y) or the exception's class name."""
+    try:
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            return tuple(int(v) for v in f.getNormalVectorLine(base_point, np.asarray(abc, dtype=np.float64).reshape(3, 1), disparity))
+    except Exception as e:                       # int(nan) -> ValueError, int(inf) -> OverflowError
+        return type(e).__name__
+
 def hist_to_bins(hist: dict) -> np.ndarray:
     """Reference histogram dict (keys = str(round(hue,3))) -> 1001 counts indexed by rint(hue*1000)."""
     bins = np.zeros(1001, dtype=np.int64)

@@ -78,7 +78,7 @@ def disparityCleaning(disparity, option, prev_disp=None):
         if prev_disp is not None:
             disparity = fillDisparity(disparity, prev_disp)
     elif option == 'mean':
-        raise NotImplementedError("threshold_option 'mean' (fillAltDisparity) is outside the hot path")
+        disparity = fillAltDisparity(disparity)
     return disparity
 
 
@@ -363,6 +363,50 @@ def greyscale(imgL, imgR):
         N.count(3)
         out.append(_back(eq, was_tensor))
     return (out[0], out[1])
+
+
+# ---------------------------------------------------------------- f3
+def fillAltDisparity(disparity):
+    """functions.py:149-162: entries below 2 become the row's mean over its non-zero entries.  The reference
+    writes into its argument and returns it; so does this (a numpy argument is updated in place)."""
+    t, was_tensor = _to_dev_u8(disparity)
+    if t.dim() != 2:
+        raise ValueError("fillAltDisparity expects a single-channel image")
+    H, W = t.shape
+    out = t if was_tensor else torch.empty_like(t)
+    N.check(N.load().svb_fill_row_mean(N.ptr(t), 1, H, W, N.ptr(out), N.stream_ptr()), "svb_fill_row_mean")
+    N.count(1)
+    if was_tensor:
+        return out
+    res = out.cpu().numpy()
+    if isinstance(disparity, np.ndarray) and disparity.dtype == np.uint8 and disparity.flags.writeable:
+        disparity[...] = res
+        return disparity
+    return res
+
+
+def getNormalVectorLine(basePoint, abc, disparity):
+    """functions.py:396-416: end point of the normal glyph for base point (x, y).  `disparity` is indexed
+    [y, x] as in the reference; raises what the reference's int() conversions raise."""
+    x, y = basePoint
+    dv = int(disparity[y, x])                              # IndexError for a point outside, as in the reference
+    dev = _dev()
+    base = torch.tensor([[int(x), int(y)]], dtype=torch.int32, device=dev)
+    pl = torch.from_numpy(np.ascontiguousarray(np.asarray(abc, dtype=np.float64).reshape(3))).to(dev)
+    dval = torch.tensor([dv], dtype=torch.uint8, device=dev)
+    out = torch.empty((1, 2), dtype=torch.int32, device=dev)
+    status = torch.empty((1,), dtype=torch.int32, device=dev)
+    cc = N.ccam(_camera())
+    N.check(N.load().svb_normal_line(N.ptr(base), N.ptr(pl), 3, 0, N.ptr(dval), 1, 1, 1, C.byref(cc), N.ptr(out), N.ptr(status),
+                                     N.stream_ptr()), "svb_normal_line")
+    N.count(1)
+    st = int(status.item())
+    if st == 1:
+        raise ValueError("cannot convert float NaN to integer")
+    if st == 2:
+        raise OverflowError("cannot convert float infinity to integer")
+    o = out.cpu().numpy()
+    return (int(o[0, 0]), int(o[0, 1]))
 
 
 def getBlackImage():

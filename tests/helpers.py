@@ -119,3 +119,21 @@ def preprocess_cases():
         p = "f%d_" % i
         out.append((str(g[p + "name"]), a, b, {k[len(p):]: v for k, v in g.items() if k.startswith(p)}))
     return out, g
+
+
+def option_cases():
+    """inputs of tests/golden/options.npz rebuilt as oracle/make_golden.py:option_fixture builds them"""
+    import os
+    import stereo.vision_b200.synth as synth
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "options.npz")
+    with np.load(path, allow_pickle=False) as z:
+        g = {k: z[k] for k in z.files}
+    rng = np.random.default_rng(808)
+    imgs = []
+    d, _ = synth.make_frame(4, 0)
+    imgs.append(d)
+    e = rng.integers(0, 6, (544, 1024), dtype=np.uint8)
+    e[10] = 0; e[11] = 1; e[12, :500] = 0; e[13] = 255; e[14, ::2] = 0
+    imgs.append(e)
+    imgs.append(rng.integers(0, 256, (37, 53), dtype=np.uint8) * (rng.random((37, 53)) < 0.6))
+    return [np.ascontiguousarray(i, dtype=np.uint8) for i in imgs], g

@@ -146,3 +146,25 @@ def test_preprocess_front_end():
         gl, gr, yl, yr = no.preprocess_pair(imgL, imgR, 1.4)
         assert sha(gl) == str(rec["gammaL_sha"]) and sha(gr) == str(rec["gammaR_sha"]), name
         assert sha(yl) == str(rec["grayL_sha"]) and sha(yr) == str(rec["grayR_sha"]), name
+
+
+def test_fill_alt_and_normal_line():
+    """oracle f3 vs the unmodified fillAltDisparity ('mean' option) and getNormalVectorLine"""
+    from helpers import option_cases
+    imgs, g = option_cases()
+    assert len(imgs) == int(g["n_fill"])
+    for i, im in enumerate(imgs):
+        assert sha(im) == str(g["fill%d_in_sha" % i]), i
+        out = no.fill_alt_disparity(im)
+        assert sha(out) == str(g["fill%d_out_sha" % i]), i
+        assert np.array_equal(out[:16], g["fill%d_out_rows" % i])
+    planes, cases, results = g["normal_planes"], g["normal_cases"], g["normal_results"]
+    raised = 0
+    for (k, x, y, dv), want in zip(cases, results):
+        try:
+            got = no.normal_vector_line((int(x), int(y)), planes[k], int(dv))
+        except (ValueError, OverflowError) as e:
+            got = (-(2 ** 31), 1 if isinstance(e, ValueError) else 2)
+            raised += 1
+        assert tuple(int(v) for v in want) == got, (k, x, y, dv)
+    assert raised == 24
