@@ -565,7 +565,7 @@ mask_points_kernel(const uint32_t *__restrict__ bits, const int32_t *__restrict_
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int32_t *rc = rowcnt + (int64_t)f * H;
     __shared__ int s_part[MP_THREADS / 32], s_all[MP_THREADS / 32];
-    __shared__ int s_row[MP_ROWS];
+    __shared__ int s_row[MP_ROWS], s_cnt[MP_ROWS];
     // points before this CTA's first row, and (first CTA of the frame) the frame's total
     int before = 0, all = 0;
     const int upto = blockIdx.x == 0 ? H : row0;
@@ -594,6 +594,8 @@ mask_points_kernel(const uint32_t *__restrict__ bits, const int32_t *__restrict_
         }
         s_row[2 * lane] = b + inc - n;
         s_row[2 * lane + 1] = b + inc - n + na;
+        s_cnt[2 * lane] = na;
+        s_cnt[2 * lane + 1] = nb;
         if (blockIdx.x == 0 && lane == 0 && counts) counts[f] = a;
     }
     __syncthreads();
@@ -601,6 +603,7 @@ mask_points_kernel(const uint32_t *__restrict__ bits, const int32_t *__restrict_
     for (int r = warp; r < MP_ROWS; r += MP_THREADS / 32) {
         int y = row0 + r;
         if (y >= H) break;
+        if (s_cnt[r] == 0) continue;                                 // most rows of a road mask are empty
         int base = s_row[r];
         const uint32_t *row = bits + ((int64_t)f * H + y) * WW;
         for (int c0 = 0; c0 < WW; c0 += 32) {

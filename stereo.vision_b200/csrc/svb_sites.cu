@@ -34,7 +34,6 @@ struct SitesGeom {
     int H, W, step;
     int LH;              // lattice rows
     int chunks;          // 512-pixel units per row
-    int csh;             // log2(chunks) when it is a power of two, else -1
     int units;           // LH * chunks
     int dvec, cvec;      // 16-byte loads allowed on the disparity / the colour image
     int seg_cap;         // list entries per (CTA, warp) segment
@@ -49,15 +48,17 @@ static __device__ __noinline__ bool exact_near_site(CamD cam, int x, int y, int 
 }
 
 // byte k of the 16 held in four words, as a float (0x4B0000dd - 2^23: no conversion instruction)
+// unit -> (lattice row, 512-pixel chunk); CSH = log2(chunks per row) when that is a power of two, else -1
+template <int CSH>
 __device__ __forceinline__ void unit_row_chunk(const SitesGeom &g, int u, int &ly, int &ch) {
-    if (g.csh >= 0) { ly = u >> g.csh; ch = u & (g.chunks - 1); }
+    if (CSH >= 0) { ly = u >> CSH; ch = u & ((1 << CSH) - 1); }
     else { ly = u / g.chunks; ch = u - ly * g.chunks; }
 }
 __device__ __forceinline__ float byte_as_float(uint32_t w, int k) {
     return __int_as_float((int)__byte_perm(w, 0x4B000000u, 0x7440 + k)) - 8388608.0f;
 }
 
-template <int STEP>
+template <int STEP, int CSH>
 __global__ void __launch_bounds__(ST_THREADS, 4)
 road_sites_near_kernel(const uint8_t *__restrict__ filled, const uint8_t *__restrict__ bgr, const double *__restrict__ planes,
                        SitesGeom g, CamD cam, const uint32_t *__restrict__ rbits, uint32_t *__restrict__ hist,
@@ -80,9 +81,9 @@ road_sites_near_kernel(const uint8_t *__restrict__ filled, const uint8_t *__rest
         uint4 v = make_uint4(0, 0, 0, 0);
         if (k >= my_units) return v;
         int ly, ch;
-        unit_row_chunk(g, part + k * ST_PARTS, ly, ch);
+        unit_row_chunk<CSH>(g, part + k * ST_PARTS, ly, ch);
         const int x0 = ch * 512 + lane * 16;
-        const uint8_t *p = drow0 + (int64_t)(ly * STEP) * g.W + x0;
+        const uint8_t *p = drow0 + ((uint32_t)(ly * STEP) * (uint32_t)g.W + (uint32_t)x0);
         if (g.dvec && x0 + 16 <= g.W) return __ldg(reinterpret_cast<const uint4 *>(p));
         uint32_t w[4] = {0, 0, 0, 0};
 #pragma unroll
@@ -130,22 +131,23 @@ road_sites_near_kernel(const uint8_t *__restrict__ filled, const uint8_t *__rest
     uint2 *buf = s_buf[warp];
     uint32_t *seg = list + (((int64_t)f * ST_PARTS + part) * ST_WARPS + warp) * g.seg_cap;
     int fill = 0, written = 0;                                   // warp-uniform: staged records, list entries written
-    auto dense = [&](uint2 rc, bool on) {
+    const uint32_t *rb_y = rbits + (size_t)g.W * 8;                // the (y, d) rows of the displacement table
+    auto dense = [&](uint2 rc, bool on) {                        // rc.x = x | y << 16, rc.y = B | G << 8 | R << 16 | d << 24
         if (on) {
-            const uint32_t lo = rc.x, c3 = rc.y;
-            const uint32_t x = lo & 0x7FFu, y = (lo >> 11) & 0x7FFu, d = (lo >> 22) & 0xFFu;
+            const uint32_t x = rc.x & 0xFFFFu, y = rc.x >> 16, d = rc.y >> 24, c3 = rc.y;
             const uint32_t hue = (uint32_t)hue_bin((int)((c3 >> 16) & 0xFFu), (int)((c3 >> 8) & 0xFFu), (int)(c3 & 0xFFu));
             atomicAdd(&s_h[hue], 1u);
-            const uint32_t px = x - ((__ldg(rbits + x * 8 + (d >> 5)) >> (d & 31)) & 1u);
-            const uint32_t py = y - ((__ldg(rbits + (g.W + y) * 8 + (d >> 5)) >> (d & 31)) & 1u);
-            seg[written + lane] = (px & 0x7FFu) | ((py & 0x7FFu) << 11) | (hue << 22);
+            const uint32_t dw = d >> 5;
+            const uint32_t px = x - ((__ldg(rbits + (x * 8u + dw)) >> (d & 31)) & 1u);
+            const uint32_t py = y - ((__ldg(rb_y + (y * 8u + dw)) >> (d & 31)) & 1u);
+            seg[written + lane] = px | (py << 11) | (hue << 22);
         }
     };
     for (int k = warp; k < my_units; k += ST_WARPS) {
         const uint4 dv = dnext;
         dnext = load_d(k + ST_WARPS);
         int ly, ch;
-        unit_row_chunk(g, part + k * ST_PARTS, ly, ch);
+        unit_row_chunk<CSH>(g, part + k * ST_PARTS, ly, ch);
         const int y = ly * STEP, x0 = ch * 512 + lane * 16;
 
         // near test of my SP sites
@@ -183,7 +185,7 @@ road_sites_near_kernel(const uint8_t *__restrict__ filled, const uint8_t *__rest
 #pragma unroll
         for (int w = 0; w < 12; ++w) cw[w] = 0;
         if (nb) {
-            const uint8_t *cp = crow0 + ((int64_t)y * g.W + x0) * 3;
+            const uint8_t *cp = crow0 + ((uint32_t)y * (uint32_t)g.W + (uint32_t)x0) * 3u;
             if (g.cvec && x0 + 16 <= g.W) {
                 const uint4 *q = reinterpret_cast<const uint4 *>(cp);
                 uint4 c0 = __ldg(q), c1 = __ldg(q + 1), c2v = __ldg(q + 2);
@@ -210,15 +212,15 @@ road_sites_near_kernel(const uint8_t *__restrict__ filled, const uint8_t *__rest
         }
         int slot = fill + inc - cnt;
         fill += __shfl_sync(0xffffffffu, inc, 31);
-        const uint32_t lo_base = pack_xyd(x0, y, 0);
+        const uint32_t lo_base = (uint32_t)x0 | ((uint32_t)y << 16);
 #pragma unroll
         for (int j = 0; j < SP; ++j) {
             if ((nb >> j) & 1u) {
                 const int o = j * STEP, bo = 3 * o;
-                const uint32_t d = (dw[o >> 2] >> (8 * (o & 3))) & 0xFFu;
-                // B, G, R at bytes 3o .. 3o+2 of the span
+                // B, G, R at bytes 3o .. 3o+2 of the span, the disparity byte on top: one permute each
                 const uint32_t c3 = __byte_perm(cw[bo >> 2], cw[(bo >> 2) + ((bo & 3) > 1 ? 1 : 0)], 0x3210 + 0x1111 * (bo & 3));
-                buf[slot++] = make_uint2(lo_base + (uint32_t)o + (d << 22), c3);
+                const uint32_t hi = __byte_perm(c3, dw[o >> 2], 0x4210 + 0x1000 * (o & 3));
+                buf[slot++] = make_uint2(lo_base + (uint32_t)o, hi);
             }
         }
         __syncwarp();
@@ -327,7 +329,6 @@ static bool sites_geom(int H, int W, int step, const void *filled, const void *b
     g.LH = svb_lattice_rows(H, step);
     g.chunks = (W + 511) / 512;
     g.units = g.LH * g.chunks;
-    g.csh = (g.chunks & (g.chunks - 1)) ? -1 : (g.chunks == 1 ? 0 : g.chunks == 2 ? 1 : g.chunks == 4 ? 2 : 3);
     g.dvec = (W % 16 == 0) && (((uintptr_t)filled) % 16 == 0);
     g.cvec = (W % 16 == 0) && (((uintptr_t)bgr) % 16 == 0);
     const int units_per_part = (g.units + ST_PARTS - 1) / ST_PARTS;
@@ -369,8 +370,13 @@ extern "C" int svb_road_points_sites(const uint8_t *filled, const uint8_t *bgr, 
     dim3 grid(ST_PARTS, F);
     {
         ProfScope ps(K_ROAD_SITES, st);
-        if (step == 1) road_sites_near_kernel<1><<<grid, ST_THREADS, 0, st>>>(filled, bgr, planes, g, c, reproj_bits, hist, road_mask, list, seg_counts, counts_out);
-        else           road_sites_near_kernel<2><<<grid, ST_THREADS, 0, st>>>(filled, bgr, planes, g, c, reproj_bits, hist, road_mask, list, seg_counts, counts_out);
+#define LAUNCH_NEAR(S, C)                                                                                                   \
+        road_sites_near_kernel<S, C><<<grid, ST_THREADS, 0, st>>>(filled, bgr, planes, g, c, reproj_bits, hist, road_mask, list, \
+                                                                   seg_counts, counts_out)
+        const int csh = (g.chunks & (g.chunks - 1)) ? -1 : (g.chunks == 1 ? 0 : g.chunks == 2 ? 1 : 2);
+        if (step == 1) { if (csh == 0) LAUNCH_NEAR(1, 0); else if (csh == 1) LAUNCH_NEAR(1, 1); else if (csh == 2) LAUNCH_NEAR(1, 2); else LAUNCH_NEAR(1, -1); }
+        else           { if (csh == 0) LAUNCH_NEAR(2, 0); else if (csh == 1) LAUNCH_NEAR(2, 1); else if (csh == 2) LAUNCH_NEAR(2, 2); else LAUNCH_NEAR(2, -1); }
+#undef LAUNCH_NEAR
     }
     SVB_LAUNCH_CHECK();
     ProfScope ps(K_ROAD_SITES_SCATTER, st);
