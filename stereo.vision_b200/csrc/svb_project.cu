@@ -220,23 +220,63 @@ fill_seq_v16(const uint4 *__restrict__ raw, const uint4 *__restrict__ prev0, uin
         }
     };
 
+    // two batches of U frames in flight: the loads of batch t + U are issued before batch t is consumed (the kernel
+    // has only ~7 warps per SM -- one thread walks all F frames of its 16 pixels -- so the bytes in flight per
+    // thread are what fills the memory pipe)
     int t = 0;
-    for (; t + U <= F; t += U) {
-        uint4 d[U];
+    uint4 d[U], e[U];
+    if (U <= F) {
 #pragma unroll
-        for (int u = 0; u < U; ++u) d[u] = __ldcs(raw + (int64_t)(t + u) * chunks + p);
+        for (int u = 0; u < U; ++u) d[u] = __ldcs(raw + (int64_t)u * chunks + p);
+    }
+    const int lane = threadIdx.x & 31;
+    auto consume = [&](const uint4 (&q)[U], int t0) {
+        uint32_t cpk[U];                                // my sites / masked sites of the batch's frames, 16-bit halves
 #pragma unroll
         for (int u = 0; u < U; ++u) {
-            uint4 v = have ? fill16(d[u], prev) : d[u];
-            if (active) __stcs(filled + (int64_t)(t + u) * chunks + p, v);
+            uint4 v = have ? fill16(q[u], prev) : q[u];
+            if (active) __stcs(filled + (int64_t)(t0 + u) * chunks + p, v);
             prev = v;
             have = true;
-            if (COUNT) count(v, t + u);
+            if (COUNT) {
+                if (uni) {
+                    const uint32_t nz = lat ? merge_nz(v) : 0u;
+                    cpk[u] = (uint32_t)__popc(nz & site80.x) | ((uint32_t)__popc(nz & in80.x) << 16);
+                } else count(v, t0 + u);
+            }
         }
+        if (COUNT && uni && lat) {
+            // the warp's sums of the U frames: U REDUX back to back, lane u keeps frame u's, one RED for the batch
+            uint32_t mine = 0;
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const uint32_t r = __reduce_add_sync(0xffffffffu, cpk[u]);   // 32 x 8 sites fit the 16-bit halves
+                if (lane == u) mine = r;
+            }
+            if (lane < U && mine) atomicAdd(group_counts + (int64_t)(t0 + lane) * g.groups + grp, mine);
+        }
+    };
+    while (t + U <= F) {                                // d holds batch t
+        const bool more = t + 2 * U <= F;
+        if (more) {
+#pragma unroll
+            for (int u = 0; u < U; ++u) e[u] = __ldcs(raw + (int64_t)(t + U + u) * chunks + p);
+        }
+        consume(d, t);
+        t += U;
+        if (!more) break;
+        const bool more2 = t + 2 * U <= F;              // e holds batch t
+        if (more2) {
+#pragma unroll
+            for (int u = 0; u < U; ++u) d[u] = __ldcs(raw + (int64_t)(t + U + u) * chunks + p);
+        }
+        consume(e, t);
+        t += U;
+        if (!more2) break;
     }
     for (; t < F; ++t) {
-        uint4 d = __ldcs(raw + (int64_t)t * chunks + p);
-        uint4 v = have ? fill16(d, prev) : d;
+        uint4 dt = __ldcs(raw + (int64_t)t * chunks + p);
+        uint4 v = have ? fill16(dt, prev) : dt;
         if (active) __stcs(filled + (int64_t)t * chunks + p, v);
         prev = v;
         have = true;
@@ -260,7 +300,155 @@ __global__ void fill_seq_scalar(const uint8_t *__restrict__ raw, const uint8_t *
     }
 }
 
-#define FILL_UNROLL 8
+#define FILL_UNROLL 16
+// ------------------------------------------------------------------ a1 fill + a4 counts, step 2, balanced
+// fill_seq_v16<.., COUNT> is bound by its slowest warps: a thread walks all F frames of its pixels, so the kernel
+// lasts as long as one warp's serial instruction stream, and the warps on lattice rows carry the counting on top of
+// the fill (85 against 50 instructions per frame).  Here a lattice (even) row is cut into 8-pixel pieces and an odd
+// row into 16-pixel pieces: twice the threads where the counting is, the same serial length everywhere.  Warps never
+// straddle rows (W % 512 == 0); 6 warps per 1024 pixels of a row pair.
+#define FS_WARPS 6                                      // warps per CTA (any number works: warps are independent)
+template <int U>
+__global__ void __launch_bounds__(FS_WARPS * 32)
+fill_seq_split(const uint8_t *__restrict__ raw, const uint8_t *__restrict__ prev0, uint8_t *__restrict__ filled, int F,
+               int H, int W, const uint8_t *__restrict__ carmask, ProjGeom g, uint32_t *__restrict__ group_counts) {
+    const int lane = threadIdx.x & 31;
+    const int64_t wid = (int64_t)blockIdx.x * FS_WARPS + (threadIdx.x >> 5);
+    const int wpe = W / 256, wpo = W / 512, wpp = wpe + wpo;          // warps per even row, odd row, row pair
+    const int64_t rp = wid / wpp;
+    const int k = (int)(wid - rp * wpp);
+    if (rp * 2 >= H) return;
+    const int64_t frame = (int64_t)H * W;
+    bool have = prev0 != nullptr;
+    if (k < wpe) {
+        // ---- a lattice row, 8 pixels per thread, with the site counts
+        const int y = (int)rp * 2, x0 = (k * 32 + lane) * 8;
+        const int64_t off = (int64_t)y * W + x0;
+        const uint2 *src = reinterpret_cast<const uint2 *>(raw + off);
+        uint2 *dst = reinterpret_cast<uint2 *>(filled + off);
+        const int64_t stride = frame / 8;
+        uint2 prev = have ? __ldg(reinterpret_cast<const uint2 *>(prev0 + off)) : make_uint2(0, 0);
+        const int ly = y / 2;
+        const bool lat = ly < g.LH;                                    // the last even row of an odd-height image is no lattice row
+        const int grp = ly / g.rpb;
+        // sites = even x below W - 1: bytes 0 and 2 of both words; bit 8 / 24 of (w & 0x00FF00FF) + 0x00FF00FF says non-zero
+        uint32_t in_bits = 0x01000100u | (0x01000100u << 1);
+        if (carmask) {
+            const uint2 m = __ldg(reinterpret_cast<const uint2 *>(carmask + off));
+            in_bits = (((m.x & 0x00FF00FFu) + 0x00FF00FFu) & 0x01000100u) | ((((m.y & 0x00FF00FFu) + 0x00FF00FFu) & 0x01000100u) << 1);
+        }
+        auto consume = [&](const uint2 (&q)[U], int t0) {
+            uint32_t cpk[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                uint2 v = q[u];
+                if (have) { v.x = fill4(v.x, prev.x); v.y = fill4(v.y, prev.y); }
+                __stcs(dst + (int64_t)(t0 + u) * stride, v);
+                prev = v;
+                have = true;
+                const uint32_t nz = (((v.x & 0x00FF00FFu) + 0x00FF00FFu) & 0x01000100u) | ((((v.y & 0x00FF00FFu) + 0x00FF00FFu) & 0x01000100u) << 1);
+                cpk[u] = (uint32_t)__popc(nz) | ((uint32_t)__popc(nz & in_bits) << 16);
+            }
+            if (lat) {
+                uint32_t mine = 0;
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    const uint32_t r = __reduce_add_sync(0xffffffffu, cpk[u]);      // 32 x 4 sites fit the 16-bit halves
+                    if (lane == u) mine = r;
+                }
+                if (lane < U && mine) atomicAdd(group_counts + (int64_t)(t0 + lane) * g.groups + grp, mine);
+            }
+        };
+        int t = 0;
+        uint2 d[U], e[U];
+        if (U <= F) {
+#pragma unroll
+            for (int u = 0; u < U; ++u) d[u] = __ldcs(src + (int64_t)u * stride);
+        }
+        while (t + U <= F) {                                           // d holds batch t
+            const bool more = t + 2 * U <= F;
+            if (more) {
+#pragma unroll
+                for (int u = 0; u < U; ++u) e[u] = __ldcs(src + (int64_t)(t + U + u) * stride);
+            }
+            consume(d, t);
+            t += U;
+            if (!more) break;
+            const bool more2 = t + 2 * U <= F;
+            if (more2) {
+#pragma unroll
+                for (int u = 0; u < U; ++u) d[u] = __ldcs(src + (int64_t)(t + U + u) * stride);
+            }
+            consume(e, t);
+            t += U;
+            if (!more2) break;
+        }
+        for (; t < F; ++t) {
+            uint2 v = __ldcs(src + (int64_t)t * stride);
+            if (have) { v.x = fill4(v.x, prev.x); v.y = fill4(v.y, prev.y); }
+            __stcs(dst + (int64_t)t * stride, v);
+            prev = v;
+            have = true;
+            if (lat) {
+                const uint32_t nz = (((v.x & 0x00FF00FFu) + 0x00FF00FFu) & 0x01000100u) | ((((v.y & 0x00FF00FFu) + 0x00FF00FFu) & 0x01000100u) << 1);
+                uint32_t c = (uint32_t)__popc(nz) | ((uint32_t)__popc(nz & in_bits) << 16);
+                c = __reduce_add_sync(0xffffffffu, c);
+                if (lane == 0 && c) atomicAdd(group_counts + (int64_t)t * g.groups + grp, c);
+            }
+        }
+    } else {
+        // ---- an odd row, 16 pixels per thread, fill only
+        const int y = (int)rp * 2 + 1;
+        if (y >= H) return;
+        const int x0 = ((k - wpe) * 32 + lane) * 16;
+        const int64_t off = (int64_t)y * W + x0;
+        const uint4 *src = reinterpret_cast<const uint4 *>(raw + off);
+        uint4 *dst = reinterpret_cast<uint4 *>(filled + off);
+        const int64_t stride = frame / 16;
+        uint4 prev = have ? __ldg(reinterpret_cast<const uint4 *>(prev0 + off)) : make_uint4(0, 0, 0, 0);
+        auto consume = [&](const uint4 (&q)[U], int t0) {
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                uint4 v = have ? fill16(q[u], prev) : q[u];
+                __stcs(dst + (int64_t)(t0 + u) * stride, v);
+                prev = v;
+                have = true;
+            }
+        };
+        int t = 0;
+        uint4 d[U], e[U];
+        if (U <= F) {
+#pragma unroll
+            for (int u = 0; u < U; ++u) d[u] = __ldcs(src + (int64_t)u * stride);
+        }
+        while (t + U <= F) {
+            const bool more = t + 2 * U <= F;
+            if (more) {
+#pragma unroll
+                for (int u = 0; u < U; ++u) e[u] = __ldcs(src + (int64_t)(t + U + u) * stride);
+            }
+            consume(d, t);
+            t += U;
+            if (!more) break;
+            const bool more2 = t + 2 * U <= F;
+            if (more2) {
+#pragma unroll
+                for (int u = 0; u < U; ++u) d[u] = __ldcs(src + (int64_t)(t + U + u) * stride);
+            }
+            consume(e, t);
+            t += U;
+            if (!more2) break;
+        }
+        for (; t < F; ++t) {
+            uint4 dt = __ldcs(src + (int64_t)t * stride);
+            uint4 v = have ? fill16(dt, prev) : dt;
+            __stcs(dst + (int64_t)t * stride, v);
+            prev = v;
+            have = true;
+        }
+    }
+}
+
 static int launch_fill(const uint8_t *raw, const uint8_t *prev0, uint8_t *filled, int F, int H, int W,
                        const uint8_t *carmask, const ProjGeom *g, uint32_t *group_counts, cudaStream_t st) {
     int64_t pixels = (int64_t)H * W;
@@ -274,6 +462,12 @@ static int launch_fill(const uint8_t *raw, const uint8_t *prev0, uint8_t *filled
     }
     int64_t chunks = pixels / 16;
     unsigned blocks = (unsigned)((chunks + FILL_THREADS - 1) / FILL_THREADS);
+    if (g && g->step == 2 && W % 512 == 0 && (carmask == nullptr || ((uintptr_t)carmask % 16) == 0)) {
+        const int64_t warps = (int64_t)((H + 1) / 2) * (W / 256 + W / 512);
+        fill_seq_split<FILL_UNROLL><<<(unsigned)((warps + FS_WARPS - 1) / FS_WARPS), FS_WARPS * 32, 0, st>>>(raw, prev0, filled, F, H, W,
+                                                                                                             carmask, *g, group_counts);
+        return SVB_OK;
+    }
     if (g)
         fill_seq_v16<FILL_UNROLL, true><<<blocks, FILL_THREADS, 0, st>>>((const uint4 *)raw, (const uint4 *)prev0, (uint4 *)filled,
                                                                          F, chunks, (const uint4 *)carmask, *g, group_counts);
