@@ -317,7 +317,10 @@ def sanitiseRoadImage(img, size):
     N.check(lib.svb_mask_points(N.ptr(bits), N.ptr(rowcnt), 1, H, W, n, N.ptr(pts), N.ptr(counts), st), "svb_mask_points")
     N.count(3)
     # np.matrix([]) has shape (1,0) in the reference when nothing is left (:365)
-    mat = np.matrix(pts[:n].cpu().numpy().astype(np.int64)) if n else np.matrix([])
+    import warnings
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore", PendingDeprecationWarning)          # np.matrix is what the reference returns (:365)
+        mat = np.matrix(pts[:n].cpu().numpy().astype(np.int64)) if n else np.matrix([])
     return _back(out, was_tensor), mat
 
 

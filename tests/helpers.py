@@ -137,3 +137,29 @@ def option_cases():
     imgs.append(e)
     imgs.append(rng.integers(0, 256, (37, 53), dtype=np.uint8) * (rng.random((37, 53)) < 0.6))
     return [np.ascontiguousarray(i, dtype=np.uint8) for i in imgs], g
+
+
+class RedZone:
+    """Device buffers with 4 KB of sentinel bytes on both sides (compute-sanitizer is not available on the GPU
+    pool): alloc() hands out a tensor view, check() asserts that no kernel wrote outside any of them."""
+    PAD = 4096
+
+    def __init__(self, device):
+        import torch
+        self.torch, self.device, self.bufs = torch, device, []
+
+    def alloc(self, shape, dtype, fill=None):
+        torch = self.torch
+        n = int(np.prod(shape)) * torch.empty((), dtype=dtype).element_size()
+        n_al = (n + 15) // 16 * 16
+        raw = torch.full((self.PAD + n_al + self.PAD,), 0xA5, dtype=torch.uint8, device=self.device)
+        view = raw[self.PAD:self.PAD + n].view(dtype).view(*shape)
+        if fill is not None:
+            view.fill_(fill)
+        self.bufs.append((raw, n))
+        return view
+
+    def check(self):
+        for raw, n in self.bufs:
+            head, tail = raw[:self.PAD], raw[self.PAD + n:]
+            assert bool((head == 0xA5).all()) and bool((tail == 0xA5).all()), "a kernel wrote outside its buffer"

@@ -9,7 +9,7 @@ import torch
 
 import np_oracle as no
 import stereo.vision_b200._native as N
-from helpers import sanitise_cases
+from helpers import RedZone, sanitise_cases
 from stereo.vision_b200.masks import default_road_threshold_mask
 from stereo.vision_b200.pipeline import RoadCleaner
 from test_oracle_golden import sha
@@ -35,10 +35,11 @@ def run_clean(cuda, imgs, tm, cap=None, packed=False, want_bytes=True):
     d_tm = torch.from_numpy(np.ascontiguousarray(tm)).to(cuda)
     tb = torch.empty((words,), dtype=torch.int32, device=cuda)
     N.check(lib.svb_pack_mask(N.ptr(d_tm), 1, H, W, N.ptr(tb), 0, 0), "pack")
-    out = torch.full((F, H, W), 7, dtype=torch.uint8, device=cuda) if want_bytes else None
-    bits = torch.empty((F, words), dtype=torch.int32, device=cuda)
-    rowcnt = torch.empty((F, H), dtype=torch.int32, device=cuda)
-    status = torch.full((1,), -1, dtype=torch.int32, device=cuda)
+    rz = RedZone(cuda)
+    out = rz.alloc((F, H, W), torch.uint8, 7) if want_bytes else None
+    bits = rz.alloc((F, words), torch.int32)
+    rowcnt = rz.alloc((F, H), torch.int32)
+    status = rz.alloc((1,), torch.int32, -1)
     if packed:
         ib = torch.empty((F, words), dtype=torch.int32, device=cuda)
         N.check(lib.svb_pack_mask(N.ptr(d_in), F, H, W, N.ptr(ib), 0, 0), "pack")
@@ -51,9 +52,10 @@ def run_clean(cuda, imgs, tm, cap=None, packed=False, want_bytes=True):
     counts = torch.empty((F,), dtype=torch.int32, device=cuda)
     N.check(lib.svb_mask_points(N.ptr(bits), N.ptr(rowcnt), F, H, W, 0, 0, N.ptr(counts), 0), "svb_mask_points")
     cap = int(counts.max().item()) if cap is None else cap
-    pts = torch.full((F, max(cap, 1), 2), -5, dtype=torch.int32, device=cuda)
+    pts = rz.alloc((F, max(cap, 1), 2), torch.int32, -5)
     N.check(lib.svb_mask_points(N.ptr(bits), N.ptr(rowcnt), F, H, W, cap, N.ptr(pts), N.ptr(counts), 0), "svb_mask_points")
     torch.cuda.synchronize()
+    rz.check()
     return {"out": out.cpu().numpy() if want_bytes else None, "bits": bits.cpu().numpy().view(np.uint32).reshape(F, H, -1),
             "rowcnt": rowcnt.cpu().numpy(), "counts": counts.cpu().numpy(), "pts": pts.cpu().numpy(), "status": int(status.item())}
 

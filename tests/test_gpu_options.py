@@ -8,7 +8,7 @@ import torch
 
 import np_oracle as no
 import stereo.vision_b200._native as N
-from helpers import option_cases
+from helpers import RedZone, option_cases
 from stereo.vision_b200.camera import DEFAULT_CAMERA
 from test_oracle_golden import sha
 
@@ -30,8 +30,11 @@ def test_fill_row_mean_golden_and_shapes(cuda):
         batch = (rng.integers(0, 256, (3, H, W), dtype=np.uint8) * (rng.random((3, H, W)) < 0.5)).astype(np.uint8)
         batch[1, :, :] = rng.integers(0, 3, (H, W), dtype=np.uint8)
         d = torch.from_numpy(batch).to(cuda)
-        out = torch.empty_like(d)
+        rz = RedZone(cuda)
+        out = rz.alloc((3, H, W), torch.uint8)
         N.check(lib.svb_fill_row_mean(N.ptr(d), 3, H, W, N.ptr(out), 0), "svb_fill_row_mean")
+        torch.cuda.synchronize()
+        rz.check()
         got = out.cpu().numpy()
         for f in range(3):
             assert np.array_equal(got[f], no.fill_alt_disparity(batch[f])), (H, W, f)

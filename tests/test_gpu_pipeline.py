@@ -242,3 +242,42 @@ def test_sequence_streamer_matches_resident_path(cuda):
     assert sr.h2d_bytes == F * (544 * 1024 + 272 * 1024 * 3) and ref["road_mask"].any()
     out2 = sr.run_sync(disp, bgr, seed=21, out=out)               # pageable numpy input, buffers reused
     assert np.array_equal(out2["road_mask"].numpy(), ref["road_mask"])
+
+
+def test_road_sites_writes_stay_inside_their_buffers(cuda):
+    """svb_road_points_sites through the C-ABI with sentinel margins around every output and the scratch
+    (no compute-sanitizer on the GPU pool), for the reference size and a ragged one; results equal RoadPath's."""
+    import ctypes as C
+    import torch
+    import stereo.vision_b200._native as N
+    from helpers import RedZone
+    from stereo.vision_b200.pipeline import RoadPath
+    lib = N.load()
+    for shape, step in (((544, 1024), 2), ((75, 130), 1), ((64, 1040), 2)):
+        H, W = shape
+        F = 2
+        if shape == (544, 1024):
+            disp, bgr = synth.make_sequence(9, F)
+            cm = _carmask(shape)
+        else:
+            rng = np.random.default_rng(H)
+            disp = rng.integers(20, 60, size=(F, H, W), dtype=np.uint8)
+            disp[rng.random((F, H, W)) < 0.2] = 0
+            bgr = rng.integers(0, 256, size=(F, H, W, 3), dtype=np.uint8)
+            cm = np.full((H, W), 255, np.uint8)
+        eng = RoadPath(shape=shape, step=step, trials=64, samples=40, carmask=cm, max_frames=F, point_threshold=0.3, colour_threshold=1)
+        assert eng.sites_road
+        r = eng.process(disp, bgr, seed=3)
+        torch.cuda.synchronize()
+        rz = RedZone(cuda)
+        hist = rz.alloc((F, 1024), torch.int32, -1)
+        mask = rz.alloc((F, H, W), torch.uint8, 9)
+        counts = rz.alloc((F, 4), torch.int32, 0)
+        nb = lib.svb_road_sites_scratch_bytes(F, H, W, step)
+        scratch = rz.alloc((nb,), torch.uint8)
+        N.check(lib.svb_road_points_sites(N.ptr(eng.filled), N.ptr(torch.from_numpy(bgr).to(cuda)), N.ptr(eng.planes), F, H, W, step,
+                                          C.byref(eng._cam), eng.colour_threshold, N.ptr(eng.reproj_bits), N.ptr(hist), N.ptr(mask), 0,
+                                          N.ptr(counts), N.ptr(scratch), nb, 0), "svb_road_points_sites")
+        torch.cuda.synchronize()
+        rz.check()
+        assert torch.equal(mask, r.road_mask) and torch.equal(hist, r.hist[:F]) and torch.equal(counts[:, 2:], r.counts[:, 2:])

@@ -8,7 +8,7 @@ import torch
 
 import np_oracle as no
 import stereo.vision_b200._native as N
-from helpers import preprocess_cases
+from helpers import RedZone, preprocess_cases
 from stereo.vision_b200.pipeline import FrontEnd
 from test_oracle_golden import sha
 
@@ -21,16 +21,18 @@ def run_front(cuda, imgs, table):
     imgs = np.ascontiguousarray(imgs)
     F, H, W, _ = imgs.shape
     d = torch.from_numpy(imgs).to(cuda)
-    out = torch.full_like(d, 9)
-    gray = torch.full((F, H, W), 9, dtype=torch.uint8, device=cuda)
-    hist = torch.full((F, 256), -1, dtype=torch.int32, device=cuda)
-    lut = torch.empty((F, 256), dtype=torch.uint8, device=cuda)
-    eq = torch.empty_like(gray)
+    rz = RedZone(cuda)
+    out = rz.alloc((F, H, W, 3), torch.uint8, 9)
+    gray = rz.alloc((F, H, W), torch.uint8, 9)
+    hist = rz.alloc((F, 256), torch.int32, -1)
+    lut = rz.alloc((F, 256), torch.uint8)
+    eq = rz.alloc((F, H, W), torch.uint8)
     tp = None if table is None else np.ascontiguousarray(table).ctypes.data_as(C.c_void_p)
     N.check(lib.svb_gamma_gray_hist(N.ptr(d), F, H, W, tp, N.ptr(out), N.ptr(gray), N.ptr(hist), 0), "svb_gamma_gray_hist")
     N.check(lib.svb_equalize_lut(N.ptr(hist), F, N.ptr(lut), 0), "svb_equalize_lut")
     N.check(lib.svb_apply_lut_frames(N.ptr(gray), F, H * W, N.ptr(lut), N.ptr(eq), 0), "svb_apply_lut_frames")
     torch.cuda.synchronize()
+    rz.check()
     return [t.cpu().numpy() for t in (out, gray, hist, lut, eq)]
 
 
