@@ -303,151 +303,141 @@ __global__ void fill_seq_scalar(const uint8_t *__restrict__ raw, const uint8_t *
 #define FILL_UNROLL 16
 // ------------------------------------------------------------------ a1 fill + a4 counts, step 2, balanced
 // fill_seq_v16<.., COUNT> is bound by its slowest warps: a thread walks all F frames of its pixels, so the kernel
-// lasts as long as one warp's serial instruction stream, and the warps on lattice rows carry the counting on top of
-// the fill (85 against 50 instructions per frame).  Here a lattice (even) row is cut into 8-pixel pieces and an odd
-// row into 16-pixel pieces: twice the threads where the counting is, the same serial length everywhere.  Warps never
-// straddle rows (W % 512 == 0); 6 warps per 1024 pixels of a row pair.
-#define FS_WARPS 6                                      // warps per CTA (any number works: warps are independent)
-template <int U>
+// lasts as long as one warp's serial instruction stream (a warp issues once per ~5.6 cycles on the dependent
+// SIMD-in-word chain, ncu), and the warps on lattice rows carry the counting on top of the fill.  Here the row kind
+// decides the pixels per thread -- PE on lattice (even) rows, PO on odd rows -- so that more, shorter threads sit
+// where the counting is.  Warps never straddle rows (W % (32 max(PE, PO)) == 0).
+template <int P> struct PixVec;
+template <> struct PixVec<4>  { typedef uint32_t T; };
+template <> struct PixVec<8>  { typedef uint2 T; };
+template <> struct PixVec<16> { typedef uint4 T; };
+template <int P> struct Words { uint32_t w[P / 4]; };
+template <int P>
+__device__ __forceinline__ Words<P> ld_words(const uint8_t *p, bool streaming) {
+    typedef typename PixVec<P>::T V;
+    union { V v; Words<P> w; } u;
+    u.v = streaming ? __ldcs(reinterpret_cast<const V *>(p)) : __ldg(reinterpret_cast<const V *>(p));
+    return u.w;
+}
+template <int P>
+__device__ __forceinline__ void st_words(uint8_t *p, const Words<P> &w) {
+    typedef typename PixVec<P>::T V;
+    union { V v; Words<P> w; } u;
+    u.w = w;
+    __stcs(reinterpret_cast<V *>(p), u.v);
+}
+// sites of a lattice row at step 2 = even x: bytes 0 and 2 of every word; bit 8 / 24 of (w & 0x00FF00FF) + 0x00FF00FF
+// says non-zero.  The P/4 words' bits are interleaved into one word (shifts 0 .. 3).
+template <int P>
+__device__ __forceinline__ uint32_t even_nonzero_bits(const Words<P> &v) {
+    uint32_t r = 0;
+#pragma unroll
+    for (int i = 0; i < P / 4; ++i) r |= (((v.w[i] & 0x00FF00FFu) + 0x00FF00FFu) & 0x01000100u) << i;
+    return r;
+}
+
+// one thread's P pixels over all F frames; COUNT: leave the (valid | masked valid << 16) site counts of every frame
+template <int U, int P, bool COUNT>
+__device__ __forceinline__ void fill_walk(const uint8_t *__restrict__ raw, const uint8_t *__restrict__ prev0, uint8_t *__restrict__ filled,
+                                          int F, int64_t frame, int64_t off, uint32_t in_bits, bool lat, int lane,
+                                          uint32_t *__restrict__ counts_row, int groups) {
+    bool have = prev0 != nullptr;
+    Words<P> prev;
+#pragma unroll
+    for (int i = 0; i < P / 4; ++i) prev.w[i] = 0;
+    if (have) prev = ld_words<P>(prev0 + off, false);
+    const uint8_t *src = raw + off;
+    uint8_t *dst = filled + off;
+    auto step = [&](Words<P> v, int t) -> uint32_t {
+        if (have) {
+#pragma unroll
+            for (int i = 0; i < P / 4; ++i) v.w[i] = fill4(v.w[i], prev.w[i]);
+        }
+        st_words<P>(dst + (int64_t)t * frame, v);
+        prev = v;
+        have = true;
+        if (!COUNT) return 0u;
+        const uint32_t nz = even_nonzero_bits<P>(v);
+        return (uint32_t)__popc(nz) | ((uint32_t)__popc(nz & in_bits) << 16);
+    };
+    auto consume = [&](const Words<P> (&q)[U], int t0) {
+        uint32_t cpk[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) cpk[u] = step(q[u], t0 + u);
+        if (COUNT && lat) {
+            // the warp's sums of the U frames: U REDUX back to back, lane u keeps frame u's, one RED for the batch
+            uint32_t mine = 0;
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const uint32_t r = __reduce_add_sync(0xffffffffu, cpk[u]);      // at most 32 x 8 sites: fits the 16-bit halves
+                if (lane == u) mine = r;
+            }
+            if (lane < U && mine) atomicAdd(counts_row + (int64_t)(t0 + lane) * groups, mine);
+        }
+    };
+    int t = 0;
+    Words<P> d[U], e[U];
+    if (U <= F) {
+#pragma unroll
+        for (int u = 0; u < U; ++u) d[u] = ld_words<P>(src + (int64_t)u * frame, true);
+    }
+    while (t + U <= F) {                                               // d holds batch t; the next batch is already in flight
+        const bool more = t + 2 * U <= F;
+        if (more) {
+#pragma unroll
+            for (int u = 0; u < U; ++u) e[u] = ld_words<P>(src + (int64_t)(t + U + u) * frame, true);
+        }
+        consume(d, t);
+        t += U;
+        if (!more) break;
+        const bool more2 = t + 2 * U <= F;
+        if (more2) {
+#pragma unroll
+            for (int u = 0; u < U; ++u) d[u] = ld_words<P>(src + (int64_t)(t + U + u) * frame, true);
+        }
+        consume(e, t);
+        t += U;
+        if (!more2) break;
+    }
+    for (; t < F; ++t) {
+        uint32_t c = step(ld_words<P>(src + (int64_t)t * frame, true), t);
+        if (COUNT && lat) {
+            c = __reduce_add_sync(0xffffffffu, c);
+            if (lane == 0 && c) atomicAdd(counts_row + (int64_t)t * groups, c);
+        }
+    }
+}
+
+#define FS_WARPS 4                                      // warps per CTA (warps are independent)
+template <int U, int PE, int PO>
 __global__ void __launch_bounds__(FS_WARPS * 32)
 fill_seq_split(const uint8_t *__restrict__ raw, const uint8_t *__restrict__ prev0, uint8_t *__restrict__ filled, int F,
                int H, int W, const uint8_t *__restrict__ carmask, ProjGeom g, uint32_t *__restrict__ group_counts) {
     const int lane = threadIdx.x & 31;
     const int64_t wid = (int64_t)blockIdx.x * FS_WARPS + (threadIdx.x >> 5);
-    const int wpe = W / 256, wpo = W / 512, wpp = wpe + wpo;          // warps per even row, odd row, row pair
+    const int wpe = W / (32 * PE), wpo = W / (32 * PO), wpp = wpe + wpo;   // warps per even row, odd row, row pair
     const int64_t rp = wid / wpp;
     const int k = (int)(wid - rp * wpp);
     if (rp * 2 >= H) return;
     const int64_t frame = (int64_t)H * W;
-    bool have = prev0 != nullptr;
     if (k < wpe) {
-        // ---- a lattice row, 8 pixels per thread, with the site counts
-        const int y = (int)rp * 2, x0 = (k * 32 + lane) * 8;
+        const int y = (int)rp * 2, x0 = (k * 32 + lane) * PE;
         const int64_t off = (int64_t)y * W + x0;
-        const uint2 *src = reinterpret_cast<const uint2 *>(raw + off);
-        uint2 *dst = reinterpret_cast<uint2 *>(filled + off);
-        const int64_t stride = frame / 8;
-        uint2 prev = have ? __ldg(reinterpret_cast<const uint2 *>(prev0 + off)) : make_uint2(0, 0);
         const int ly = y / 2;
         const bool lat = ly < g.LH;                                    // the last even row of an odd-height image is no lattice row
-        const int grp = ly / g.rpb;
-        // sites = even x below W - 1: bytes 0 and 2 of both words; bit 8 / 24 of (w & 0x00FF00FF) + 0x00FF00FF says non-zero
-        uint32_t in_bits = 0x01000100u | (0x01000100u << 1);
-        if (carmask) {
-            const uint2 m = __ldg(reinterpret_cast<const uint2 *>(carmask + off));
-            in_bits = (((m.x & 0x00FF00FFu) + 0x00FF00FFu) & 0x01000100u) | ((((m.y & 0x00FF00FFu) + 0x00FF00FFu) & 0x01000100u) << 1);
-        }
-        auto consume = [&](const uint2 (&q)[U], int t0) {
-            uint32_t cpk[U];
-#pragma unroll
-            for (int u = 0; u < U; ++u) {
-                uint2 v = q[u];
-                if (have) { v.x = fill4(v.x, prev.x); v.y = fill4(v.y, prev.y); }
-                __stcs(dst + (int64_t)(t0 + u) * stride, v);
-                prev = v;
-                have = true;
-                const uint32_t nz = (((v.x & 0x00FF00FFu) + 0x00FF00FFu) & 0x01000100u) | ((((v.y & 0x00FF00FFu) + 0x00FF00FFu) & 0x01000100u) << 1);
-                cpk[u] = (uint32_t)__popc(nz) | ((uint32_t)__popc(nz & in_bits) << 16);
-            }
-            if (lat) {
-                uint32_t mine = 0;
-#pragma unroll
-                for (int u = 0; u < U; ++u) {
-                    const uint32_t r = __reduce_add_sync(0xffffffffu, cpk[u]);      // 32 x 4 sites fit the 16-bit halves
-                    if (lane == u) mine = r;
-                }
-                if (lane < U && mine) atomicAdd(group_counts + (int64_t)(t0 + lane) * g.groups + grp, mine);
-            }
-        };
-        int t = 0;
-        uint2 d[U], e[U];
-        if (U <= F) {
-#pragma unroll
-            for (int u = 0; u < U; ++u) d[u] = __ldcs(src + (int64_t)u * stride);
-        }
-        while (t + U <= F) {                                           // d holds batch t
-            const bool more = t + 2 * U <= F;
-            if (more) {
-#pragma unroll
-                for (int u = 0; u < U; ++u) e[u] = __ldcs(src + (int64_t)(t + U + u) * stride);
-            }
-            consume(d, t);
-            t += U;
-            if (!more) break;
-            const bool more2 = t + 2 * U <= F;
-            if (more2) {
-#pragma unroll
-                for (int u = 0; u < U; ++u) d[u] = __ldcs(src + (int64_t)(t + U + u) * stride);
-            }
-            consume(e, t);
-            t += U;
-            if (!more2) break;
-        }
-        for (; t < F; ++t) {
-            uint2 v = __ldcs(src + (int64_t)t * stride);
-            if (have) { v.x = fill4(v.x, prev.x); v.y = fill4(v.y, prev.y); }
-            __stcs(dst + (int64_t)t * stride, v);
-            prev = v;
-            have = true;
-            if (lat) {
-                const uint32_t nz = (((v.x & 0x00FF00FFu) + 0x00FF00FFu) & 0x01000100u) | ((((v.y & 0x00FF00FFu) + 0x00FF00FFu) & 0x01000100u) << 1);
-                uint32_t c = (uint32_t)__popc(nz) | ((uint32_t)__popc(nz & in_bits) << 16);
-                c = __reduce_add_sync(0xffffffffu, c);
-                if (lane == 0 && c) atomicAdd(group_counts + (int64_t)t * g.groups + grp, c);
-            }
-        }
+        uint32_t in_bits = 0xFFFFFFFFu;
+        if (carmask) in_bits = even_nonzero_bits<PE>(ld_words<PE>(carmask + off, false));
+        fill_walk<U, PE, true>(raw, prev0, filled, F, frame, off, in_bits, lat, lane, group_counts + ly / g.rpb, g.groups);
     } else {
-        // ---- an odd row, 16 pixels per thread, fill only
         const int y = (int)rp * 2 + 1;
         if (y >= H) return;
-        const int x0 = ((k - wpe) * 32 + lane) * 16;
-        const int64_t off = (int64_t)y * W + x0;
-        const uint4 *src = reinterpret_cast<const uint4 *>(raw + off);
-        uint4 *dst = reinterpret_cast<uint4 *>(filled + off);
-        const int64_t stride = frame / 16;
-        uint4 prev = have ? __ldg(reinterpret_cast<const uint4 *>(prev0 + off)) : make_uint4(0, 0, 0, 0);
-        auto consume = [&](const uint4 (&q)[U], int t0) {
-#pragma unroll
-            for (int u = 0; u < U; ++u) {
-                uint4 v = have ? fill16(q[u], prev) : q[u];
-                __stcs(dst + (int64_t)(t0 + u) * stride, v);
-                prev = v;
-                have = true;
-            }
-        };
-        int t = 0;
-        uint4 d[U], e[U];
-        if (U <= F) {
-#pragma unroll
-            for (int u = 0; u < U; ++u) d[u] = __ldcs(src + (int64_t)u * stride);
-        }
-        while (t + U <= F) {
-            const bool more = t + 2 * U <= F;
-            if (more) {
-#pragma unroll
-                for (int u = 0; u < U; ++u) e[u] = __ldcs(src + (int64_t)(t + U + u) * stride);
-            }
-            consume(d, t);
-            t += U;
-            if (!more) break;
-            const bool more2 = t + 2 * U <= F;
-            if (more2) {
-#pragma unroll
-                for (int u = 0; u < U; ++u) d[u] = __ldcs(src + (int64_t)(t + U + u) * stride);
-            }
-            consume(e, t);
-            t += U;
-            if (!more2) break;
-        }
-        for (; t < F; ++t) {
-            uint4 dt = __ldcs(src + (int64_t)t * stride);
-            uint4 v = have ? fill16(dt, prev) : dt;
-            __stcs(dst + (int64_t)t * stride, v);
-            prev = v;
-            have = true;
-        }
+        const int x0 = ((k - wpe) * 32 + lane) * PO;
+        fill_walk<U, PO, false>(raw, prev0, filled, F, frame, (int64_t)y * W + x0, 0u, false, lane, nullptr, 0);
     }
 }
+
+static int g_fill_split = 0;                            // tuning hook (svb_debug_fill_split): 0 = default
+extern "C" int svb_debug_fill_split(int mode) { g_fill_split = mode; return SVB_OK; }
 
 static int launch_fill(const uint8_t *raw, const uint8_t *prev0, uint8_t *filled, int F, int H, int W,
                        const uint8_t *carmask, const ProjGeom *g, uint32_t *group_counts, cudaStream_t st) {
@@ -463,9 +453,19 @@ static int launch_fill(const uint8_t *raw, const uint8_t *prev0, uint8_t *filled
     int64_t chunks = pixels / 16;
     unsigned blocks = (unsigned)((chunks + FILL_THREADS - 1) / FILL_THREADS);
     if (g && g->step == 2 && W % 512 == 0 && (carmask == nullptr || ((uintptr_t)carmask % 16) == 0)) {
-        const int64_t warps = (int64_t)((H + 1) / 2) * (W / 256 + W / 512);
-        fill_seq_split<FILL_UNROLL><<<(unsigned)((warps + FS_WARPS - 1) / FS_WARPS), FS_WARPS * 32, 0, st>>>(raw, prev0, filled, F, H, W,
-                                                                                                             carmask, *g, group_counts);
+#define LAUNCH_SPLIT(PE, PO)                                                                                              \
+        do {                                                                                                              \
+            const int64_t warps = (int64_t)((H + 1) / 2) * (W / (32 * PE) + W / (32 * PO));                               \
+            fill_seq_split<FILL_UNROLL, PE, PO><<<(unsigned)((warps + FS_WARPS - 1) / FS_WARPS), FS_WARPS * 32, 0, st>>>( \
+                raw, prev0, filled, F, H, W, carmask, *g, group_counts);                                                  \
+        } while (0)
+        switch (g_fill_split) {                         // 300 frames of 1024 x 544: 87.6 / 94.1 / 88.6 / 92.1 us
+            case 1: LAUNCH_SPLIT(8, 16); break;
+            case 2: LAUNCH_SPLIT(4, 8); break;
+            case 3: LAUNCH_SPLIT(4, 4); break;
+            default: LAUNCH_SPLIT(8, 8); break;
+        }
+#undef LAUNCH_SPLIT
         return SVB_OK;
     }
     if (g)
