@@ -312,9 +312,50 @@ def option_fixture():
                                                                             sum(1 for r in res if r[0] == -(2 ** 31))))
 
 
+def obstacle_fixture():
+    """hull of the road points, hull mask, obstacle mask and hull centre on the cleaned images of
+    the sanitise fixture (stereovision.py:170-200), plus the hull-mask rule against cv2 on random hulls."""
+    import cv2
+    import np_oracle as no
+    f = rh.load_reference()
+    flat, n = {}, 0
+    for name, img in sanitise_inputs():
+        cleaned, pts = rh.run_sanitise(f, img)
+        if len(pts) == 0:
+            continue
+        hull, hmask, obst, centre = rh.run_obstacles(f, cleaned, pts)
+        flat["c%d_name" % n] = name
+        flat["c%d_hull" % n] = hull.astype(np.int32)
+        flat["c%d_hull_mask_sha" % n] = sha(hmask)
+        flat["c%d_obstacle_sha" % n] = sha(obst)
+        flat["c%d_obstacle_px" % n] = int((obst != 0).sum())
+        flat["c%d_centre" % n] = np.array(centre)
+        print("  obstacles %-14s hull %d vertices, %d obstacle px, centre %s" % (name, len(hull), int((obst != 0).sum()), centre))
+        n += 1
+    flat["n_cases"] = n
+    # the span rule of np_oracle.hull_fill against drawContours on random hulls, segments and points
+    rng = np.random.default_rng(77)
+    cases, ok = [], 0
+    for trial in range(300):
+        k = [30, 3, 2, 1][trial % 4]
+        pts = np.stack([rng.integers(0, 1024, k), rng.integers(0, 544, k)], 1).astype(np.int32)
+        cvh = cv2.convexHull(pts)
+        ref = cv2.drawContours(np.zeros((544, 1024), np.uint8), [cvh], 0, 255, -100)
+        ok += int(np.array_equal(ref, no.hull_fill(no.convex_hull(pts), (544, 1024))))
+        if trial < 24:
+            cases.append((pts, sha(ref), tuple(int(v) for v in f.getCenterPoint(cvh))))
+    assert ok == 300, ok
+    flat["n_random"] = len(cases)
+    for i, (pts, h, c) in enumerate(cases):
+        flat["r%d_pts" % i], flat["r%d_fill_sha" % i], flat["r%d_centre" % i] = pts, h, np.array(c)
+    path = os.path.join(OUT, "obstacles.npz")
+    np.savez_compressed(path, **flat)
+    print("wrote obstacles.npz (%.1f KB)" % (os.path.getsize(path) / 1024))
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
-    which = sys.argv[1:] or ["seq", "s400", "step1", "small", "noplane", "reproject", "hue", "sanitise", "preprocess", "options"]
+    which = sys.argv[1:] or ["seq", "s400", "step1", "small", "noplane", "reproject", "hue", "sanitise", "preprocess", "options", "obstacles"]
     if "seq" in which:
         sequence_fixture("seq0_step2_s600.npz", 0, 3)
     if "s400" in which:
@@ -335,3 +376,5 @@ if __name__ == "__main__":
         preprocess_fixture()
     if "options" in which:
         option_fixture()
+    if "obstacles" in which:
+        obstacle_fixture()

@@ -396,3 +396,130 @@ def normal_vector_line(base_point, abc, d_at_base, camera=None):
         newX = ((newX * c.f) / Z) + c.cw
         newY = ((newY * c.f) / Z) + c.ch
     return (int(newX), int(newY))
+
+
+# ---------------------------------------------------------------- f3: convex hull, hull / obstacle masks, centre
+def convex_hull(points):
+    """cv2.convexHull of integer (x, y) points (stereovision.py:172, functions.py:392): the strict hull (no
+    collinear vertices), in OpenCV's orientation, rotated to start at the lexicographically largest (x, y).
+    OpenCV starts at a vertex of its own choosing (usually this one); callers compare up to rotation."""
+    P = sorted(set((int(a), int(b)) for a, b in np.asarray(points).reshape(-1, 2)))
+    if len(P) <= 1:
+        return np.array(P, dtype=np.int32).reshape(-1, 2)
+
+    def cross(o, a, b):
+        return (a[0] - o[0]) * (b[1] - o[1]) - (a[1] - o[1]) * (b[0] - o[0])
+    lo, up = [], []
+    for p in P:
+        while len(lo) >= 2 and cross(lo[-2], lo[-1], p) <= 0:
+            lo.pop()
+        lo.append(p)
+    for p in reversed(P):
+        while len(up) >= 2 and cross(up[-2], up[-1], p) <= 0:
+            up.pop()
+        up.append(p)
+    return np.array(up[:-1] + lo[:-1], dtype=np.int32)
+
+
+def _line_pixels(p1, p2):
+    """cv::LineIterator, 8-connected, left to right (what drawContours uses for a polygon's edges)."""
+    (x1, y1), (x2, y2) = p1, p2
+    dx, dy = x2 - x1, y2 - y1
+    if dx < 0:
+        x1, y1, dx, dy = x2, y2, -dx, -dy
+    ystep = 1
+    if dy < 0:
+        dy, ystep = -dy, -1
+    out, x, y = [], x1, y1
+    if dy > dx:
+        err, plus, minus = dy - (dx + dx), dy + dy, -(dx + dx)
+        for _ in range(dy + 1):
+            out.append((x, y))
+            if err < 0:
+                err += minus + plus
+                x += 1
+            else:
+                err += minus
+            y += ystep
+    else:
+        err, plus, minus = dx - (dy + dy), dx + dx, -(dy + dy)
+        for _ in range(dx + 1):
+            out.append((x, y))
+            if err < 0:
+                err += minus + plus
+                y += ystep
+            else:
+                err += minus
+            x += 1
+    return out
+
+
+def hull_fill(hull, shape):
+    """cv2.drawContours(zeros, [hull], 0, 255, -100) for a convex polygon (stereovision.py:176): OpenCV draws
+    every edge with its 8-connected line iterator and scan-fills the interior, and for a convex polygon the
+    union is, row by row, the span between the leftmost and the rightmost edge pixel (checked against cv2 on
+    random hulls, segments and single points in the golden script)."""
+    H, W = shape
+    img = np.zeros((H, W), dtype=np.uint8)
+    h = [tuple(int(v) for v in p) for p in np.asarray(hull).reshape(-1, 2)]
+    if not h:
+        return img
+    lo, hi = np.full(H, 1 << 30), np.full(H, -1)
+    for i in range(len(h)):
+        for x, y in _line_pixels(h[i], h[(i + 1) % len(h)]):
+            if 0 <= y < H:
+                lo[y], hi[y] = min(lo[y], x), max(hi[y], x)
+    for y in range(H):
+        if hi[y] >= 0:
+            img[y, max(lo[y], 0):min(hi[y], W - 1) + 1] = 255
+    return img
+
+
+def obstacle_stage(cleaned, points):
+    """stereovision.py:172-180: hull of the road points, hull mask drawn over a copy of the cleaned image,
+    obstacles = NOT cleaned, kept inside the hull mask.  Returns (hull, hull_mask, obstacle_mask)."""
+    hull = convex_hull(points)
+    fill = hull_fill(hull, cleaned.shape)
+    hull_mask = np.where(fill != 0, np.uint8(255), cleaned)
+    obstacles = np.where(hull_mask != 0, ~cleaned, np.uint8(0)).astype(np.uint8)
+    return hull, hull_mask, obstacles
+
+
+def enclosing_centre(hull):
+    """functions.py:418-421 (getCenterPoint): int(x), int(y) of cv2.minEnclosingCircle's centre.  The circle
+    itself is unique; OpenCV finds it in float32, this is the incremental algorithm in float64 (equal after
+    int() on every fixture; they can differ when a coordinate of the centre lies within ~1e-4 of an integer)."""
+    import math
+    P = [(float(x), float(y)) for x, y in np.asarray(hull).reshape(-1, 2)]
+
+    def two(a, b):
+        cx, cy = (a[0] + b[0]) / 2, (a[1] + b[1]) / 2
+        return cx, cy, math.hypot(a[0] - cx, a[1] - cy)
+
+    def three(a, b, c):
+        (ax, ay), (bx, by), (cx, cy) = a, b, c
+        d = 2 * (ax * (by - cy) + bx * (cy - ay) + cx * (ay - by))
+        if d == 0:
+            return None
+        ux = ((ax * ax + ay * ay) * (by - cy) + (bx * bx + by * by) * (cy - ay) + (cx * cx + cy * cy) * (ay - by)) / d
+        uy = ((ax * ax + ay * ay) * (cx - bx) + (bx * bx + by * by) * (ax - cx) + (cx * cx + cy * cy) * (bx - ax)) / d
+        return ux, uy, math.hypot(ax - ux, ay - uy)
+
+    def inside(c, p):
+        return math.hypot(p[0] - c[0], p[1] - c[1]) <= c[2] * (1 + 1e-12) + 1e-12
+    c = (P[0][0], P[0][1], 0.0)
+    for i, p in enumerate(P):
+        if inside(c, p):
+            continue
+        c = (p[0], p[1], 0.0)
+        for j in range(i):
+            if inside(c, P[j]):
+                continue
+            c = two(p, P[j])
+            for k in range(j):
+                if inside(c, P[k]):
+                    continue
+                cc = three(p, P[j], P[k])
+                if cc:
+                    c = cc
+    return (int(c[0]), int(c[1]))

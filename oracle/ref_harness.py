@@ -216,6 +216,21 @@ def run_normal_line(f, base_point, abc, disparity):
     except Exception as e:                       # int(nan) -> ValueError, int(inf) -> OverflowError
         return type(e).__name__
 
+
+def run_obstacles(f, cleaned, pts):
+    """stereovision.py:170-200: the orchestrator's own cv2 calls (these lines are not helpers of functions.py),
+    then the reference's drawRoadLine / getCenterPoint.  Returns (hull (n,2), hull mask, obstacle mask, centre)."""
+    cv2 = f.cv2
+    pts = np.asarray(pts, dtype=np.int32).reshape(-1, 1, 2)
+    roadHull = cv2.convexHull(pts)                                                   # :172
+    hullMask = cv2.drawContours(cleaned.copy(), [roadHull], 0, 255, -100)           # :174,176
+    obstacleImage = cv2.bitwise_not(cleaned.copy())                                  # :175,178
+    obstacleImage = cv2.bitwise_and(obstacleImage, obstacleImage, mask=hullMask)     # :180
+    _, hull = f.drawRoadLine(np.zeros(cleaned.shape + (3,), np.uint8), pts)          # :198 (functions.py:390-394)
+    centre = f.getCenterPoint(hull)                                                  # :200 (functions.py:418-421)
+    assert np.array_equal(hull, roadHull)
+    return roadHull.reshape(-1, 2), hullMask, obstacleImage, tuple(int(v) for v in centre)
+
 def hist_to_bins(hist: dict) -> np.ndarray:
     """Reference histogram dict (keys = str(round(hue,3))) -> 1001 counts indexed by rint(hue*1000)."""
     bins = np.zeros(1001, dtype=np.int64)

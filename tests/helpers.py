@@ -163,3 +163,36 @@ class RedZone:
         for raw, n in self.bufs:
             head, tail = raw[:self.PAD], raw[self.PAD + n:]
             assert bool((head == 0xA5).all()) and bool((tail == 0xA5).all()), "a kernel wrote outside its buffer"
+
+
+def same_cycle(a, b):
+    """two vertex lists describe the same oriented polygon (equal up to rotation)"""
+    a, b = [tuple(int(v) for v in p) for p in a], [tuple(int(v) for v in p) for p in b]
+    if len(a) != len(b):
+        return False
+    if not a:
+        return True
+    if b[0] not in a:
+        return False
+    k = a.index(b[0])
+    return a[k:] + a[:k] == b
+
+
+def obstacle_cases():
+    """(name, cleaned image, road points, golden record) for tests/golden/obstacles.npz: the cleaned images are
+    rebuilt with the oracle from the sanitise fixture's inputs; plus the fixture's random hull cases."""
+    import os
+    import np_oracle as no
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "obstacles.npz")
+    with np.load(path, allow_pickle=False) as z:
+        g = {k: z[k] for k in z.files}
+    by_name = {c[0]: c for c in sanitise_cases()}
+    out = []
+    for i in range(int(g["n_cases"])):
+        p = "c%d_" % i
+        name = str(g[p + "name"])
+        _, img, tm, _ = by_name[name]
+        cleaned, pts = no.sanitise_road_image(img, tm)
+        out.append((name, cleaned, pts, {k[len(p):]: v for k, v in g.items() if k.startswith(p)}))
+    rnd = [(g["r%d_pts" % i], str(g["r%d_fill_sha" % i]), tuple(int(v) for v in g["r%d_centre" % i])) for i in range(int(g["n_random"]))]
+    return out, rnd

@@ -168,3 +168,19 @@ def test_fill_alt_and_normal_line():
             raised += 1
         assert tuple(int(v) for v in want) == got, (k, x, y, dv)
     assert raised == 24
+
+
+def test_obstacle_stage():
+    """oracle f3 (hull, hull mask, obstacle mask, hull centre) vs cv2 as stereovision.py:170-200 calls it"""
+    from helpers import obstacle_cases, same_cycle
+    cases, rnd = obstacle_cases()
+    assert len(cases) == 7
+    for name, cleaned, pts, r in cases:
+        hull, hmask, obst = no.obstacle_stage(cleaned, pts)
+        assert same_cycle(hull, r["hull"]), name
+        assert sha(hmask) == str(r["hull_mask_sha"]) and sha(obst) == str(r["obstacle_sha"]), name
+        assert no.enclosing_centre(hull) == tuple(int(v) for v in r["centre"]), name
+    for pts, fill_sha, centre in rnd:
+        hull = no.convex_hull(pts)
+        assert sha(no.hull_fill(hull, (544, 1024))) == fill_sha
+        assert no.enclosing_centre(hull) == centre
