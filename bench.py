@@ -237,17 +237,20 @@ def run_b200(args):
         masks = res.road_mask
         for _ in range(3):
             cl.clean(masks)
+            cl.obstacles()
         torch.cuda.synchronize()
         N.profile_enable(True)
         for _ in range(5):
             cl.clean(masks)
+            cl.obstacles()
         torch.cuda.synchronize()
         cprof = N.profile_read()
         N.profile_enable(False)
         pts = float(cl.counts[:F].float().mean().item())
         calg = {"clean_band": 2.0 * H * W + 4.0 * ((W + 31) // 32) * H + 4.0 * H,     # mask in, cleaned bytes + bit rows + row counts out
-                "mask_points": 4.0 * ((W + 31) // 32) * H + 4.0 * H + 8.0 * pts}       # bit rows + row counts in, (x,y) int32 pairs out
-        next_rows = {"row": "SURVEY 8(f)-1 sanitiseRoadImage on the step's %d road masks (not part of `value`)" % F,
+                "mask_points": 4.0 * ((W + 31) // 32) * H + 4.0 * H + 8.0 * pts,       # bit rows + row counts in, (x,y) int32 pairs out
+                "road_hull": 4.0 * ((W + 31) // 32) * H + 4.0 * H + 2.0 * H * W}       # 8(f)-3: bit rows + row counts in, hull mask + obstacle image out
+        next_rows = {"row": "SURVEY 8(f)-1 sanitiseRoadImage and 8(f)-3 the obstacle stage on the step's %d road masks (not part of `value`)" % F,
                      "mean_points": pts, "status": int(cl.status.item()), "kernels": {}}
         for k, v in cprof.items():
             if k in calg:

@@ -252,6 +252,19 @@ int svb_normal_line(const int32_t *base_xy, const double *abc, int abc_stride, c
                     const uint8_t *d_values, int F, int H, int W, const svb_camera *cam, int32_t *out_xy,
                     int32_t *status, void *stream);
 
+/* ---- f3  the obstacle stage                                              stereovision.py:170-200
+ * From the cleaned road image as bit rows (+ row counts, as svb_clean_road leaves them), per frame:
+ *   hull_xy [F,cap,2] / hull_n [F]  cv2.convexHull of the road points: strict hull in OpenCV's orientation, starting
+ *                                   at the lexicographically largest (x, y) (OpenCV picks its own start vertex);
+ *                                   hull_n is the true size also when it exceeds cap;
+ *   hull_mask uint8 [F,H,W]         drawContours(cleaned.copy(), [hull], 0, 255, -100)      (:174-176)
+ *   obstacles uint8 [F,H,W]         NOT cleaned, kept inside hull_mask                        (:178-180)
+ *   centre_xy int32 [F,2]           int() of minEnclosingCircle(hull)'s centre, functions.py:418-421; (-1,-1) when
+ *                                   the image is empty (the reference's convexHull raises and the stage is skipped).
+ * Every output is optional. */
+int svb_road_hull(const uint32_t *bits, const int32_t *rowcnt, int F, int H, int W, int cap, int32_t *hull_xy,
+                  int32_t *hull_n, int32_t *centre_xy, uint8_t *hull_mask, uint8_t *obstacles, void *stream);
+
 /* ---- a8-a14 fused, batched: the road points of F frames               stereovision.py:97-140
  * reproj_bits: table of svb_reproject_bits or NULL.
  * pass 1: near = |P.abc-1| < cutoff ; per-frame hue histogram of the near points (shared memory,

@@ -17,8 +17,9 @@ LIB_PATH = os.path.join(_PKG, "libsvb200.so")
 HUE_BINS = 1001
 HIST_STRIDE = 1024
 PLANE_STRIDE = 8
-ABI_VERSION = 8
+ABI_VERSION = 9
 SVB_OK, SVB_E_NULL, SVB_E_SHAPE, SVB_E_ARG, SVB_E_SCRATCH = 0, -1, -2, -3, -4      # include/svb200.h
+SVB_MAX_DIM = 2048                                                                  # csrc/svb_common.cuh
 
 
 class SvbError(RuntimeError):
@@ -73,6 +74,7 @@ SIGNATURES = {
     "svb_lut_bytes": (I, [P, L, P, P, P]),
     "svb_fill_row_mean": (I, [P, I, I, I, P, P]),
     "svb_normal_line": (I, [P, P, I, P, P, I, I, I, CAMP, P, P, P]),
+    "svb_road_hull": (I, [P, P, I, I, I, I, P, P, P, P, P, P]),
     "svb_bits_words": (L, [I, I]),
     "svb_pack_mask": (I, [P, I, I, I, P, P, P]),
     "svb_clean_road": (I, [P, P, I, I, I, P, P, P, P, P]),

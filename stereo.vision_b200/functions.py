@@ -324,6 +324,56 @@ def sanitiseRoadImage(img, size):
     return _back(out, was_tensor), mat
 
 
+# ---------------------------------------------------------------- f3 (obstacle stage)
+def _hull_stage(t, masks, want_hull=True):
+    lib, st, dev = N.load(), N.stream_ptr(), t.device
+    H, W = t.shape
+    bits = torch.empty((lib.svb_bits_words(H, W),), dtype=torch.int32, device=dev)
+    rowcnt = torch.empty((H,), dtype=torch.int32, device=dev)
+    N.check(lib.svb_pack_mask(N.ptr(t), 1, H, W, N.ptr(bits), N.ptr(rowcnt), st), "svb_pack_mask")
+    cap = 2 * H
+    hull = torch.empty((cap, 2), dtype=torch.int32, device=dev)
+    meta = torch.empty((3,), dtype=torch.int32, device=dev)             # n, cx, cy
+    hm = torch.empty_like(t) if masks else None
+    ob = torch.empty_like(t) if masks else None
+    N.check(lib.svb_road_hull(N.ptr(bits), N.ptr(rowcnt), 1, H, W, cap, N.ptr(hull), N.ptr(meta), N.ptr(meta[1:]),
+                              N.ptr(hm) if masks else 0, N.ptr(ob) if masks else 0, st), "svb_road_hull")
+    N.count(2)
+    n, cx, cy = (int(v) for v in meta.cpu())
+    return hull[:n], (cx, cy), hm, ob
+
+
+def roadObstacles(cleaned):
+    """stereovision.py:170-180 as one call on the cleaned road image (0 / non-zero): returns
+    (roadHull, hullMask, obstacleImage) -- cv2.convexHull of the road points as an (n,1,2) int32 array,
+    drawContours(cleaned.copy(), [hull], 0, 255, -100), and NOT cleaned kept inside the hull mask.
+    Raises ValueError for an empty image (the reference's convexHull fails on the empty matrix and the
+    orchestrator skips the stage, stereovision.py:171,203)."""
+    t, was_tensor = _to_dev_u8(cleaned)
+    if t.dim() != 2:
+        raise ValueError("roadObstacles expects a single-channel image")
+    hull, _, hm, ob = _hull_stage(t, True)
+    if hull.shape[0] == 0:
+        raise ValueError("roadObstacles: no road points")
+    h = hull.cpu().numpy().reshape(-1, 1, 2)
+    return h, _back(hm, was_tensor), _back(ob, was_tensor)
+
+
+def getCenterPoint(hull):
+    """functions.py:418-421: int(x), int(y) of cv2.minEnclosingCircle(hull)'s centre.  The circle of a point
+    set is the circle of its hull, so the points are drawn into a bit image and go through svb_road_hull."""
+    p = np.asarray(hull.cpu() if torch.is_tensor(hull) else hull).reshape(-1, 2).astype(np.int64)
+    if p.shape[0] == 0:
+        raise ValueError("getCenterPoint: empty hull")
+    if p.min() < 0 or p[:, 0].max() >= N.SVB_MAX_DIM or p[:, 1].max() >= N.SVB_MAX_DIM:
+        raise ValueError("getCenterPoint: coordinates outside [0, %d)" % N.SVB_MAX_DIM)
+    N.require_cuda()
+    img = np.zeros((int(p[:, 1].max()) + 1, int(p[:, 0].max()) + 1), dtype=np.uint8)
+    img[p[:, 1], p[:, 0]] = 255
+    _, centre, _, _ = _hull_stage(torch.from_numpy(img).cuda(), False)
+    return centre
+
+
 # ---------------------------------------------------------------- f2
 def _gamma_table(gamma):
     """functions.py:62-65, value by value in float64 (host side in the reference as well)."""

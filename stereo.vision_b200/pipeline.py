@@ -351,7 +351,35 @@ class RoadCleaner:
                                              N.ptr(self.points), N.ptr(self.counts), st), "svb_mask_points")
             N.count(1)
         cleaned = self.cleaned[:F] if self.cleaned is not None else None
+        self._last = F
         return cleaned, self.counts[:F], self.points[:F]
+
+    def obstacles(self, masks=True, hull_cap=512):
+        """The obstacle stage (stereovision.py:170-200) of the frames of the last clean(): one kernel
+        (svb_road_hull).  Returns a dict of device tensors: hull [F,hull_cap,2] int32 (x,y) with hull_n [F]
+        valid rows each (cv2.convexHull's vertices and orientation), centre [F,2] int32 (getCenterPoint;
+        -1,-1 for an empty image) and, with masks=True, hull_mask and obstacles uint8 [F,H,W]."""
+        F = getattr(self, "_last", 0)
+        if F < 1:
+            raise RuntimeError("obstacles() follows clean()")
+        dev = self.device
+        if getattr(self, "_hull_cap", None) != int(hull_cap):
+            self._hull_cap = int(hull_cap)
+            self.hull = torch.empty((self.F, self._hull_cap, 2), dtype=torch.int32, device=dev)
+            self.hull_n = torch.empty((self.F,), dtype=torch.int32, device=dev)
+            self.centre = torch.empty((self.F, 2), dtype=torch.int32, device=dev)
+        if masks and getattr(self, "hull_mask", None) is None:
+            self.hull_mask = torch.empty((self.F, self.H, self.W), dtype=torch.uint8, device=dev)
+            self.obstacle_mask = torch.empty((self.F, self.H, self.W), dtype=torch.uint8, device=dev)
+        N.check(self.lib.svb_road_hull(N.ptr(self.bits), N.ptr(self.rowcnt), F, self.H, self.W, self._hull_cap,
+                                       N.ptr(self.hull), N.ptr(self.hull_n), N.ptr(self.centre),
+                                       N.ptr(self.hull_mask) if masks else 0, N.ptr(self.obstacle_mask) if masks else 0,
+                                       N.stream_ptr()), "svb_road_hull")
+        N.count(1)
+        out = {"hull": self.hull[:F], "hull_n": self.hull_n[:F], "centre": self.centre[:F]}
+        if masks:
+            out["hull_mask"], out["obstacles"] = self.hull_mask[:F], self.obstacle_mask[:F]
+        return out
 
 
 class FrontEnd:

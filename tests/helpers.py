@@ -167,7 +167,7 @@ class RedZone:
 
 def same_cycle(a, b):
     """two vertex lists describe the same oriented polygon (equal up to rotation)"""
-    a, b = [tuple(int(v) for v in p) for p in a], [tuple(int(v) for v in p) for p in b]
+    a, b = ([tuple(int(v) for v in p) for p in np.asarray(q).reshape(-1, 2)] for q in (a, b))
     if len(a) != len(b):
         return False
     if not a:
