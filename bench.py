@@ -249,7 +249,8 @@ def run_b200(args):
         pts = float(cl.counts[:F].float().mean().item())
         calg = {"clean_band": 2.0 * H * W + 4.0 * ((W + 31) // 32) * H + 4.0 * H,     # mask in, cleaned bytes + bit rows + row counts out
                 "mask_points": 4.0 * ((W + 31) // 32) * H + 4.0 * H + 8.0 * pts,       # bit rows + row counts in, (x,y) int32 pairs out
-                "road_hull": 4.0 * ((W + 31) // 32) * H + 4.0 * H + 2.0 * H * W}       # 8(f)-3: bit rows + row counts in, hull mask + obstacle image out
+                "road_hull": 4.0 * ((W + 31) // 32) * H + 4.0 * H,                     # 8(f)-3: bit rows in, row spans out (latency-bound: one CTA per frame)
+                "hull_masks": 4.0 * ((W + 31) // 32) * H + 4.0 * H + 2.0 * H * W}      # bit rows + spans in, hull mask + obstacle image out
         next_rows = {"row": "SURVEY 8(f)-1 sanitiseRoadImage and 8(f)-3 the obstacle stage on the step's %d road masks (not part of `value`)" % F,
                      "mean_points": pts, "status": int(cl.status.item()), "kernels": {}}
         for k, v in cprof.items():

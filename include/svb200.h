@@ -253,7 +253,7 @@ int svb_normal_line(const int32_t *base_xy, const double *abc, int abc_stride, c
                     int32_t *status, void *stream);
 
 /* ---- f3  the obstacle stage                                              stereovision.py:170-200
- * From the cleaned road image as bit rows (+ row counts, as svb_clean_road leaves them), per frame:
+ * From the cleaned road image as bit rows (as svb_clean_road / svb_pack_mask leave them), per frame:
  *   hull_xy [F,cap,2] / hull_n [F]  cv2.convexHull of the road points: strict hull in OpenCV's orientation, starting
  *                                   at the lexicographically largest (x, y) (OpenCV picks its own start vertex);
  *                                   hull_n is the true size also when it exceeds cap;
@@ -261,9 +261,12 @@ int svb_normal_line(const int32_t *base_xy, const double *abc, int abc_stride, c
  *   obstacles uint8 [F,H,W]         NOT cleaned, kept inside hull_mask                        (:178-180)
  *   centre_xy int32 [F,2]           int() of minEnclosingCircle(hull)'s centre, functions.py:418-421; (-1,-1) when
  *                                   the image is empty (the reference's convexHull raises and the stage is skipped).
- * Every output is optional. */
-int svb_road_hull(const uint32_t *bits, const int32_t *rowcnt, int F, int H, int W, int cap, int32_t *hull_xy,
-                  int32_t *hull_n, int32_t *centre_xy, uint8_t *hull_mask, uint8_t *obstacles, void *stream);
+ * Every output is optional.  Two kernels: the hull of each frame (one CTA per frame), then the masks from the rows'
+ * spans, which travel through `scratch` (svb_road_hull_scratch_bytes; needed only when a mask is asked for). */
+int64_t svb_road_hull_scratch_bytes(int F, int H);
+int svb_road_hull(const uint32_t *bits, int F, int H, int W, int cap, int32_t *hull_xy, int32_t *hull_n,
+                  int32_t *centre_xy, uint8_t *hull_mask, uint8_t *obstacles, void *scratch, int64_t scratch_bytes,
+                  void *stream);
 
 /* ---- a8-a14 fused, batched: the road points of F frames               stereovision.py:97-140
  * reproj_bits: table of svb_reproject_bits or NULL.

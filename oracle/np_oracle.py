@@ -487,14 +487,18 @@ def obstacle_stage(cleaned, points):
 
 def enclosing_centre(hull):
     """functions.py:418-421 (getCenterPoint): int(x), int(y) of cv2.minEnclosingCircle's centre.  The circle
-    itself is unique; OpenCV finds it in float32, this is the incremental algorithm in float64 (equal after
-    int() on every fixture; they can differ when a coordinate of the centre lies within ~1e-4 of an integer)."""
-    import math
+    itself is unique; OpenCV finds it in float32, this is the incremental algorithm in float64 on squared
+    distances (equal after int() on every fixture; they can differ when a coordinate of the centre lies within
+    ~1e-4 of an integer).  Every operation is a single rounded float64 one, so the CUDA kernel repeats it exactly."""
     P = [(float(x), float(y)) for x, y in np.asarray(hull).reshape(-1, 2)]
+
+    def dist(ax, ay, bx, by):                    # squared
+        dx, dy = ax - bx, ay - by
+        return dx * dx + dy * dy
 
     def two(a, b):
         cx, cy = (a[0] + b[0]) / 2, (a[1] + b[1]) / 2
-        return cx, cy, math.hypot(a[0] - cx, a[1] - cy)
+        return cx, cy, dist(a[0], a[1], cx, cy)
 
     def three(a, b, c):
         (ax, ay), (bx, by), (cx, cy) = a, b, c
@@ -503,10 +507,10 @@ def enclosing_centre(hull):
             return None
         ux = ((ax * ax + ay * ay) * (by - cy) + (bx * bx + by * by) * (cy - ay) + (cx * cx + cy * cy) * (ay - by)) / d
         uy = ((ax * ax + ay * ay) * (cx - bx) + (bx * bx + by * by) * (ax - cx) + (cx * cx + cy * cy) * (bx - ax)) / d
-        return ux, uy, math.hypot(ax - ux, ay - uy)
+        return ux, uy, dist(ax, ay, ux, uy)
 
     def inside(c, p):
-        return math.hypot(p[0] - c[0], p[1] - c[1]) <= c[2] * (1 + 1e-12) + 1e-12
+        return dist(p[0], p[1], c[0], c[1]) <= c[2] * (1 + 1e-11) + 1e-9      # c[2] = radius squared
     c = (P[0][0], P[0][1], 0.0)
     for i, p in enumerate(P):
         if inside(c, p):

@@ -74,7 +74,8 @@ SIGNATURES = {
     "svb_lut_bytes": (I, [P, L, P, P, P]),
     "svb_fill_row_mean": (I, [P, I, I, I, P, P]),
     "svb_normal_line": (I, [P, P, I, P, P, I, I, I, CAMP, P, P, P]),
-    "svb_road_hull": (I, [P, P, I, I, I, I, P, P, P, P, P, P]),
+    "svb_road_hull": (I, [P, I, I, I, I, P, P, P, P, P, P, L, P]),
+    "svb_road_hull_scratch_bytes": (L, [I, I]),
     "svb_bits_words": (L, [I, I]),
     "svb_pack_mask": (I, [P, I, I, I, P, P, P]),
     "svb_clean_road": (I, [P, P, I, I, I, P, P, P, P, P]),

@@ -36,7 +36,7 @@ static const char *k_names[K_COUNT_] = {
     "ransac_dump", "ransac_finalize", "point_errors", "compact_cloud", "hue_hist", "hue_bins", "reproject",
     "scatter_points", "road_pass1", "road_pass2", "road_clear", "road_cluster", "road_table", "road_near", "road_scatter",
     "clean_band", "pack_mask", "mask_points", "road_sites", "road_sites_scatter",
-    "prep_gamma_gray", "prep_equalize_lut", "prep_apply_lut", "fill_row_mean", "normal_line", "road_hull"};
+    "prep_gamma_gray", "prep_equalize_lut", "prep_apply_lut", "fill_row_mean", "normal_line", "road_hull", "hull_masks"};
 struct EvPair { int id; cudaEvent_t a, b; };
 static std::vector<EvPair> g_events;
 static cudaEvent_t g_pending[K_COUNT_];

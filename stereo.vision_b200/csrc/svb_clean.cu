@@ -359,19 +359,26 @@ clean_rows32_kernel(const uint8_t *__restrict__ road, const uint32_t *__restrict
         const uint32_t *src = road_bits + ((int64_t)f * H + ylo) * C32_WW;
         for (int y = warp; y < NR; y += NW) Ad[y * C32_WW + lane] = hdilate32<4>(__ldg(src + y * C32_WW + lane), lane);
     } else {
-        const uint4 *src = reinterpret_cast<const uint4 *>(road + ((int64_t)f * H + ylo) * W) + lane * 2;
+        // a lane loads the row's 16-byte chunks `lane` and `32 + lane`, so that each load instruction of the warp
+        // covers 512 contiguous bytes (whole sectors); two shuffles bring word `lane`'s halves (chunks 2 lane, 2 lane + 1)
+        const uint4 *src = reinterpret_cast<const uint4 *>(road + ((int64_t)f * H + ylo) * W) + lane;
+        const int s0 = (2 * lane) & 31, s1 = s0 + 1;
+        auto gather = [&](uint32_t v) {
+            const uint32_t a = __shfl_sync(0xFFFFFFFFu, v, s0), b = __shfl_sync(0xFFFFFFFFu, v, s1);
+            return lane < 16 ? (a & 0xFFFFu) | (b << 16) : (a >> 16) | (b & 0xFFFF0000u);
+        };
         int y = warp;
         for (; y + NW < NR; y += 2 * NW) {                                 // two rows in flight per warp
             const uint4 *p = src + (int64_t)y * (W / 16), *q = p + NW * (W / 16);
-            uint4 a0 = __ldg(p), a1 = __ldg(p + 1), b0 = __ldg(q), b1 = __ldg(q + 1);
-            uint32_t wa = pack16(a0, odd) | (pack16(a1, odd) << 16), wb = pack16(b0, odd) | (pack16(b1, odd) << 16);
+            uint4 a0 = __ldg(p), a1 = __ldg(p + 32), b0 = __ldg(q), b1 = __ldg(q + 32);
+            uint32_t wa = gather(pack16(a0, odd) | (pack16(a1, odd) << 16)), wb = gather(pack16(b0, odd) | (pack16(b1, odd) << 16));
             Ad[y * C32_WW + lane] = hdilate32<4>(wa, lane);
             Ad[(y + NW) * C32_WW + lane] = hdilate32<4>(wb, lane);
         }
         for (; y < NR; y += NW) {
             const uint4 *p = src + (int64_t)y * (W / 16);
-            uint4 a0 = __ldg(p), a1 = __ldg(p + 1);
-            Ad[y * C32_WW + lane] = hdilate32<4>(pack16(a0, odd) | (pack16(a1, odd) << 16), lane);
+            uint4 a0 = __ldg(p), a1 = __ldg(p + 32);
+            Ad[y * C32_WW + lane] = hdilate32<4>(gather(pack16(a0, odd) | (pack16(a1, odd) << 16)), lane);
         }
     }
     __syncthreads();
@@ -393,16 +400,19 @@ clean_rows32_kernel(const uint8_t *__restrict__ road, const uint32_t *__restrict
     __syncthreads();
     {                                                    // eH9 on the band's own rows, store
         const int r0 = y0 - ylo, rows = y1 - y0;
-        uint4 *dst = cleaned ? reinterpret_cast<uint4 *>(cleaned + ((int64_t)f * H + y0) * W) + lane * 2 : nullptr;
+        uint4 *dst = cleaned ? reinterpret_cast<uint4 *>(cleaned + ((int64_t)f * H + y0) * W) + lane : nullptr;
+        const int sh = (lane & 1) * 16;
         uint32_t *dbits = cleaned_bits ? cleaned_bits + ((int64_t)f * H + y0) * C32_WW + lane : nullptr;
         int32_t *rc = rowcnt ? rowcnt + (int64_t)f * H + y0 : nullptr;
         for (int y = warp; y < rows; y += NW) {
             uint32_t w = herode32<4>(Ad[(r0 + y) * C32_WW + lane], lane);
             if (dbits) dbits[y * C32_WW] = w;
             if (dst) {
+                // chunk `lane` is half (lane & 1) of word lane / 2, chunk 32 + lane of word 16 + lane / 2: whole sectors per store
+                const uint32_t wa = __shfl_sync(0xFFFFFFFFu, w, lane >> 1), wb = __shfl_sync(0xFFFFFFFFu, w, 16 + (lane >> 1));
                 uint4 *p = dst + (int64_t)y * (W / 16);
-                p[0] = spread16(w & 0xFFFFu);
-                p[1] = spread16(w >> 16);
+                p[0] = spread16((wa >> sh) & 0xFFFFu);
+                p[32] = spread16((wb >> sh) & 0xFFFFu);
             }
             if (rc) {
                 int n = __reduce_add_sync(0xFFFFFFFFu, __popc(w));

@@ -329,16 +329,17 @@ def _hull_stage(t, masks, want_hull=True):
     lib, st, dev = N.load(), N.stream_ptr(), t.device
     H, W = t.shape
     bits = torch.empty((lib.svb_bits_words(H, W),), dtype=torch.int32, device=dev)
-    rowcnt = torch.empty((H,), dtype=torch.int32, device=dev)
-    N.check(lib.svb_pack_mask(N.ptr(t), 1, H, W, N.ptr(bits), N.ptr(rowcnt), st), "svb_pack_mask")
+    N.check(lib.svb_pack_mask(N.ptr(t), 1, H, W, N.ptr(bits), None, st), "svb_pack_mask")
     cap = 2 * H
     hull = torch.empty((cap, 2), dtype=torch.int32, device=dev)
     meta = torch.empty((3,), dtype=torch.int32, device=dev)             # n, cx, cy
     hm = torch.empty_like(t) if masks else None
     ob = torch.empty_like(t) if masks else None
-    N.check(lib.svb_road_hull(N.ptr(bits), N.ptr(rowcnt), 1, H, W, cap, N.ptr(hull), N.ptr(meta), N.ptr(meta[1:]),
-                              N.ptr(hm) if masks else 0, N.ptr(ob) if masks else 0, st), "svb_road_hull")
-    N.count(2)
+    sb = int(lib.svb_road_hull_scratch_bytes(1, H))
+    scratch = torch.empty((sb,), dtype=torch.uint8, device=dev) if masks else None
+    N.check(lib.svb_road_hull(N.ptr(bits), 1, H, W, cap, N.ptr(hull), N.ptr(meta), N.ptr(meta[1:]),
+                              N.ptr(hm), N.ptr(ob), N.ptr(scratch), sb if masks else 0, st), "svb_road_hull")
+    N.count(3 if masks else 2)
     n, cx, cy = (int(v) for v in meta.cpu())
     return hull[:n], (cx, cy), hm, ob
 

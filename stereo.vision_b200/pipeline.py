@@ -355,8 +355,8 @@ class RoadCleaner:
         return cleaned, self.counts[:F], self.points[:F]
 
     def obstacles(self, masks=True, hull_cap=512):
-        """The obstacle stage (stereovision.py:170-200) of the frames of the last clean(): one kernel
-        (svb_road_hull).  Returns a dict of device tensors: hull [F,hull_cap,2] int32 (x,y) with hull_n [F]
+        """The obstacle stage (stereovision.py:170-200) of the frames of the last clean(): svb_road_hull,
+        two kernels (one without masks).  Returns a dict of device tensors: hull [F,hull_cap,2] int32 (x,y) with hull_n [F]
         valid rows each (cv2.convexHull's vertices and orientation), centre [F,2] int32 (getCenterPoint;
         -1,-1 for an empty image) and, with masks=True, hull_mask and obstacles uint8 [F,H,W]."""
         F = getattr(self, "_last", 0)
@@ -371,11 +371,15 @@ class RoadCleaner:
         if masks and getattr(self, "hull_mask", None) is None:
             self.hull_mask = torch.empty((self.F, self.H, self.W), dtype=torch.uint8, device=dev)
             self.obstacle_mask = torch.empty((self.F, self.H, self.W), dtype=torch.uint8, device=dev)
-        N.check(self.lib.svb_road_hull(N.ptr(self.bits), N.ptr(self.rowcnt), F, self.H, self.W, self._hull_cap,
+        sb = int(self.lib.svb_road_hull_scratch_bytes(self.F, self.H))
+        if masks and getattr(self, "_hull_scratch", None) is None:
+            self._hull_scratch = torch.empty((sb,), dtype=torch.uint8, device=dev)
+        N.check(self.lib.svb_road_hull(N.ptr(self.bits), F, self.H, self.W, self._hull_cap,
                                        N.ptr(self.hull), N.ptr(self.hull_n), N.ptr(self.centre),
-                                       N.ptr(self.hull_mask) if masks else 0, N.ptr(self.obstacle_mask) if masks else 0,
+                                       N.ptr(self.hull_mask) if masks else None, N.ptr(self.obstacle_mask) if masks else None,
+                                       N.ptr(self._hull_scratch) if masks else None, sb if masks else 0,
                                        N.stream_ptr()), "svb_road_hull")
-        N.count(1)
+        N.count(2 if masks else 1)
         out = {"hull": self.hull[:F], "hull_n": self.hull_n[:F], "centre": self.centre[:F]}
         if masks:
             out["hull_mask"], out["obstacles"] = self.hull_mask[:F], self.obstacle_mask[:F]

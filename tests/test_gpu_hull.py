@@ -21,15 +21,17 @@ def run_hull(cuda, imgs, cap=None, masks=True):
     t = torch.from_numpy(imgs).to(cuda)
     rz = RedZone(cuda)
     bits = rz.alloc((F, int(lib.svb_bits_words(H, W))), torch.int32)
-    rowcnt = rz.alloc((F, H), torch.int32)
-    N.check(lib.svb_pack_mask(N.ptr(t), F, H, W, N.ptr(bits), N.ptr(rowcnt), 0), "svb_pack_mask")
+    N.check(lib.svb_pack_mask(N.ptr(t), F, H, W, N.ptr(bits), None, 0), "svb_pack_mask")
+    sb = int(lib.svb_road_hull_scratch_bytes(F, H))
+    assert sb == 4 * F * H
+    scratch = rz.alloc((sb,), torch.uint8) if masks else None
     hull = rz.alloc((F, max(cap, 1), 2), torch.int32, fill=-7)
     hn = rz.alloc((F,), torch.int32)
     centre = rz.alloc((F, 2), torch.int32)
     hm = rz.alloc((F, H, W), torch.uint8, fill=3) if masks else None
     ob = rz.alloc((F, H, W), torch.uint8, fill=3) if masks else None
-    N.check(lib.svb_road_hull(N.ptr(bits), N.ptr(rowcnt), F, H, W, cap, N.ptr(hull), N.ptr(hn), N.ptr(centre),
-                              N.ptr(hm), N.ptr(ob), 0), "svb_road_hull")
+    N.check(lib.svb_road_hull(N.ptr(bits), F, H, W, cap, N.ptr(hull), N.ptr(hn), N.ptr(centre),
+                              N.ptr(hm), N.ptr(ob), N.ptr(scratch), sb if masks else 0, 0), "svb_road_hull")
     torch.cuda.synchronize()
     rz.check()
     hn = hn.cpu().numpy()
@@ -105,10 +107,13 @@ def test_cap_and_optional_outputs(cuda):
     assert np.array_equal(full[0][:3], hulls[0])
     lib = N.load()
     z = torch.zeros((4,), dtype=torch.int32, device=cuda)
-    assert lib.svb_road_hull(N.ptr(z), N.ptr(z), 1, 1, 1, 0, None, None, None, None, None, 0) == N.SVB_E_NULL
-    assert lib.svb_road_hull(None, N.ptr(z), 1, 1, 1, 0, None, N.ptr(z), None, None, None, 0) == N.SVB_E_NULL
-    assert lib.svb_road_hull(N.ptr(z), N.ptr(z), 1, 1, 4096, 0, None, N.ptr(z), None, None, None, 0) == N.SVB_E_SHAPE
-    assert lib.svb_road_hull(N.ptr(z), N.ptr(z), 1, 1, 1, 0, N.ptr(z), N.ptr(z), None, None, None, 0) == N.SVB_E_ARG
+    assert lib.svb_road_hull(N.ptr(z), 1, 1, 1, 0, None, None, None, None, None, None, 0, 0) == N.SVB_E_NULL
+    assert lib.svb_road_hull(None, 1, 1, 1, 0, None, N.ptr(z), None, None, None, None, 0, 0) == N.SVB_E_NULL
+    assert lib.svb_road_hull(N.ptr(z), 1, 1, 4096, 0, None, N.ptr(z), None, None, None, None, 0, 0) == N.SVB_E_SHAPE
+    assert lib.svb_road_hull(N.ptr(z), 1, 1, 1, 0, N.ptr(z), N.ptr(z), None, None, None, None, 0, 0) == N.SVB_E_ARG
+    m = torch.zeros((16,), dtype=torch.uint8, device=cuda)
+    assert lib.svb_road_hull(N.ptr(z), 1, 1, 1, 0, None, None, None, N.ptr(m), None, None, 0, 0) == N.SVB_E_SCRATCH
+    assert lib.svb_road_hull(N.ptr(z), 1, 1, 1, 0, None, None, None, N.ptr(m), None, N.ptr(z), 3, 0) == N.SVB_E_SCRATCH
 
 
 def test_drop_ins_and_cleaner(cuda):
