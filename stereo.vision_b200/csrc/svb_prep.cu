@@ -16,6 +16,14 @@
 
 struct ByteTable { uint8_t v[256]; };
 
+// the same through a table replicated per lane (entry i of lane l in word 32 i + l): a warp's 32 look-ups fall into
+// 32 different banks whatever the bytes are
+__device__ __forceinline__ uint32_t lut4_lane(const uint32_t *t, uint32_t w) {
+    // one PRMT per byte index, one per pair of results: the entries are words with the value in byte 0
+    const uint32_t r0 = t[__byte_perm(w, 0, 0x4440) * 32], r1 = t[__byte_perm(w, 0, 0x4441) * 32];
+    const uint32_t r2 = t[__byte_perm(w, 0, 0x4442) * 32], r3 = t[__byte_perm(w, 0, 0x4443) * 32];
+    return __byte_perm(__byte_perm(r0, r1, 0x1140), __byte_perm(r2, r3, 0x1140), 0x5410);
+}
 // four table look-ups on the bytes of w
 __device__ __forceinline__ uint32_t lut4(const uint8_t *t, uint32_t w) {
     return (uint32_t)t[w & 0xFFu] | ((uint32_t)t[(w >> 8) & 0xFFu] << 8) | ((uint32_t)t[(w >> 16) & 0xFFu] << 16) | ((uint32_t)t[w >> 24] << 24);
@@ -29,9 +37,14 @@ __global__ void __launch_bounds__(PP_THREADS)
 prep_gamma_gray_kernel(const uint8_t *__restrict__ bgr, int64_t pixels_per_image, ByteTable table, uint8_t *__restrict__ bgr_out,
                        uint8_t *__restrict__ gray, uint32_t *__restrict__ hist, int vec) {
     __shared__ uint8_t s_t[256];
+    __shared__ uint32_t s_rep[HAS_TABLE ? 256 * 32 : 1];
     __shared__ uint32_t s_h[PP_WARPS][256];
     const int f = blockIdx.y, tid = threadIdx.x, warp = tid >> 5;
-    if (HAS_TABLE) s_t[tid] = table.v[tid];
+    if (HAS_TABLE) {
+        s_t[tid] = table.v[tid];
+        for (int k = tid; k < 256 * 32; k += PP_THREADS) s_rep[k] = table.v[k >> 5];
+    }
+    const uint32_t *my_t = s_rep + (tid & 31);
     for (int k = tid; k < PP_WARPS * 256; k += PP_THREADS) (&s_h[0][0])[k] = 0;
     __syncthreads();
     const uint8_t *src = bgr + (int64_t)f * pixels_per_image * 3;
@@ -55,7 +68,7 @@ prep_gamma_gray_kernel(const uint8_t *__restrict__ bgr, int64_t pixels_per_image
         }
         if (HAS_TABLE) {
 #pragma unroll
-            for (int k = 0; k < 12; ++k) w[k] = lut4(s_t, w[k]);
+            for (int k = 0; k < 12; ++k) w[k] = lut4_lane(my_t, w[k]);
         }
         if (dst) {
             if (vec) {
@@ -68,15 +81,21 @@ prep_gamma_gray_kernel(const uint8_t *__restrict__ bgr, int64_t pixels_per_image
                 for (int k = 0; k < 48; ++k) dst[gidx * 48 + k] = (uint8_t)(w[k >> 2] >> (8 * (k & 3)));
             }
         }
-        // 16 pixels: pixel i sits at bytes 3i .. 3i+2
-        uint32_t gq[4] = {0, 0, 0, 0};
+        // 16 pixels: pixel i sits at bytes 3i .. 3i+2.  gray = (3735 B + 19235 G + 9798 R + 2^14) >> 15 as two DP2A on the
+        // 32-bit window that starts at the pixel (its fourth byte meets a zero coefficient)
+        uint32_t gq[4];
 #pragma unroll
-        for (int i = 0; i < 16; ++i) {
-            const int o = 3 * i;
-            const uint32_t three = __byte_perm(w[o >> 2], w[(o >> 2) + ((o & 3) > 1 ? 1 : 0)], 0x3210 + 0x1111 * (o & 3));
-            const uint32_t y = gray_of(three & 0xFFu, (three >> 8) & 0xFFu, (three >> 16) & 0xFFu);
-            gq[i >> 2] |= y << (8 * (i & 3));
-            atomicAdd(&h[y], 1u);
+        for (int q = 0; q < 4; ++q) {
+            uint32_t y4[4];
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                const int o = 3 * (4 * q + r);
+                const uint32_t win = (o & 3) ? __funnelshift_r(w[o >> 2], w[(o >> 2) + 1 < 12 ? (o >> 2) + 1 : 11], 8 * (o & 3)) : w[o >> 2];
+                const uint32_t y = __dp2a_hi(9798u, win, __dp2a_lo(3735u | (19235u << 16), win, 16384u)) >> 15;
+                atomicAdd(&h[y], 1u);
+                y4[r] = y;
+            }
+            gq[q] = __byte_perm(__byte_perm(y4[0], y4[1], 0x1140), __byte_perm(y4[2], y4[3], 0x1140), 0x5410);
         }
         if (gdst) {
             if (vec) __stcs(reinterpret_cast<uint4 *>(gdst + gidx * 16), make_uint4(gq[0], gq[1], gq[2], gq[3]));
@@ -190,9 +209,17 @@ prep_apply_lut_kernel(const uint8_t *__restrict__ src, int64_t n, const uint8_t 
     const uint8_t *s = src + (int64_t)f * n;
     uint8_t *d = dst + (int64_t)f * n;
     const int64_t groups = vec ? n / 16 : 0;
-    for (int64_t g = (int64_t)blockIdx.x * PP_THREADS + tid; g < groups; g += (int64_t)gridDim.x * PP_THREADS) {
-        uint4 v = __ldcs(reinterpret_cast<const uint4 *>(s) + g);
-        __stcs(reinterpret_cast<uint4 *>(d) + g, make_uint4(lut4(s_t, v.x), lut4(s_t, v.y), lut4(s_t, v.z), lut4(s_t, v.w)));
+    const int64_t stride = (int64_t)gridDim.x * PP_THREADS;
+    for (int64_t g = (int64_t)blockIdx.x * PP_THREADS + tid; g < groups; g += 4 * stride) {        // four loads in flight
+        uint4 v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            if (g + u * stride < groups) v[u] = __ldcs(reinterpret_cast<const uint4 *>(s) + g + u * stride);
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            if (g + u * stride < groups)
+                __stcs(reinterpret_cast<uint4 *>(d) + g + u * stride,
+                       make_uint4(lut4(s_t, v[u].x), lut4(s_t, v[u].y), lut4(s_t, v[u].z), lut4(s_t, v[u].w)));
     }
     for (int64_t i = groups * 16 + (int64_t)blockIdx.x * PP_THREADS + tid; i < n; i += (int64_t)gridDim.x * PP_THREADS) d[i] = s_t[s[i]];
 }
