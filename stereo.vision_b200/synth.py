@@ -107,3 +107,38 @@ def scale_mask(mask: np.ndarray, s: int) -> np.ndarray:
     if s == 1:
         return mask
     return np.repeat(np.repeat(mask, s, axis=0), s, axis=1)
+
+
+def _box3(a: np.ndarray) -> np.ndarray:
+    """One 3x3 box blur with edge replication (float32)."""
+    p = np.pad(a, 1, mode="edge")
+    h = p[:, :-2] + p[:, 1:-1] + p[:, 2:]
+    return (h[:-2] + h[1:-1] + h[2:]) / np.float32(9.0)
+
+
+def make_stereo_pair(seq: int, frame: int, shape=(544, 1024), camera: Camera = None):
+    """Return (grayL, grayR) uint8 [H,W]: a rectified pair whose true disparity is `make_frame`'s scene.
+
+    Input of the matcher stage (functions.py:104-128).  The right view is a random texture
+    (blurred noise plus a coarse pattern, so that both the gradient and the raw term of the matching cost
+    carry signal); the left view looks it up at x - disparity (disparity in pixels = half of make_frame's
+    units); pixels without a match (make_frame's holes) are independent noise in the left view, which is
+    what gives the speckle filter and the left-right check work to do.
+    """
+    H, W = shape
+    d, _ = make_frame(seq, frame, shape, camera)
+    rng = np.random.default_rng(frame_seed(seq, frame) + 500009)
+    fine = rng.integers(0, 256, size=(H, W), dtype=np.uint8).astype(np.float32)
+    coarse = rng.integers(0, 256, size=((H + 7) // 8, (W + 7) // 8), dtype=np.uint8).astype(np.float32)
+    coarse = np.repeat(np.repeat(coarse, 8, axis=0), 8, axis=1)[:H, :W]
+    tex = 0.55 * _box3(_box3(fine)) + 0.45 * _box3(_box3(_box3(coarse)))
+    tex = (tex - tex.min()) / max(float(tex.max() - tex.min()), 1.0) * 255.0
+    right = tex.astype(np.uint8)
+    px = (d.astype(np.int32) + 1) // 2
+    xs = np.arange(W, dtype=np.int32)[None, :] - px
+    left = np.take_along_axis(right, np.clip(xs, 0, W - 1), axis=1)
+    lost = (d == 0) | (xs < 0)
+    left = np.where(lost, rng.integers(0, 256, size=(H, W), dtype=np.uint8), left)
+    glare = rng.integers(-2, 3, size=(H, W)).astype(np.int16)          # sensor noise on one view
+    left = np.clip(left.astype(np.int16) + glare, 0, 255).astype(np.uint8)
+    return np.ascontiguousarray(left), np.ascontiguousarray(right)

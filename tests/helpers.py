@@ -196,3 +196,32 @@ def obstacle_cases():
         out.append((name, cleaned, pts, {k[len(p):]: v for k, v in g.items() if k.startswith(p)}))
     rnd = [(g["r%d_pts" % i], str(g["r%d_fill_sha" % i]), tuple(int(v) for v in g["r%d_centre" % i])) for i in range(int(g["n_random"]))]
     return out, rnd
+
+
+def sgbm_inputs():
+    """(name, grayL, grayR, crop_disparity) of tests/golden/sgbm.npz: synthetic pairs of several shapes plus inputs
+    that stress ties and saturation (flat images, independent noise, a pair with a single row)."""
+    rng = np.random.default_rng(4242)
+    cases = []
+    for name, seq, t, shape in [("full_a", 0, 0, (544, 1024)), ("full_b", 5, 9, (544, 1024)), ("mid", 1, 2, (120, 400)),
+                                ("narrow", 2, 1, (64, 150)), ("short", 3, 3, (9, 300)), ("odd", 4, 4, (77, 333))]:
+        big = shape if shape[0] >= 120 else (120, 400)           # small cases are crops of a 120x400 pair
+        L, R = synth.make_stereo_pair(seq, t, big)
+        L, R = (np.ascontiguousarray(a[big[0] - shape[0]:, :shape[1]]) for a in (L, R))
+        cases.append((name, L, R, False))
+    L, R = synth.make_stereo_pair(6, 6, (544, 1024))
+    cases.append(("full_crop", L, R, True))
+    cases.append(("flat", np.full((40, 200), 90, np.uint8), np.full((40, 200), 90, np.uint8), False))
+    cases.append(("noise", rng.integers(0, 256, (48, 260), dtype=np.uint8), rng.integers(0, 256, (48, 260), dtype=np.uint8), False))
+    hi = (rng.integers(0, 2, (60, 280), dtype=np.uint8) * 255)
+    cases.append(("binary", hi, np.roll(hi, -7, axis=1).copy(), False))
+    L, R = synth.make_stereo_pair(7, 0, (120, 400))
+    cases.append(("one_row", np.ascontiguousarray(L[100:101]), np.ascontiguousarray(R[100:101]), False))
+    return cases
+
+
+def sgbm_golden():
+    import os
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "sgbm.npz")
+    with np.load(path, allow_pickle=False) as z:
+        return {k: z[k] for k in z.files}

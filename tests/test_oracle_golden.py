@@ -184,3 +184,29 @@ def test_obstacle_stage():
         hull = no.convex_hull(pts)
         assert sha(no.hull_fill(hull, (544, 1024))) == fill_sha
         assert no.enclosing_centre(hull) == centre
+
+
+# ---------------------------------------------------------------- the matcher stage
+def test_sgbm_disparity_stage():
+    """oracle/sgbm_oracle.c against the unmodified functions.disparity (cv2.StereoSGBM + filterSpeckles + scaling,
+    functions.py:26,104-128) on every case of tests/golden/sgbm.npz: raw int16 matcher output, speckle-filtered
+    image and final uint8 disparity bit for bit."""
+    import sgbm_oracle as so
+    from helpers import sgbm_golden, sgbm_inputs
+    g = sgbm_golden()
+    cases = sgbm_inputs()
+    assert [c[0] for c in cases] == [str(n) for n in g["names"]]
+    for name, L, R, crop in cases:
+        p = name + "_"
+        assert sha(L) + sha(R) == str(g[p + "in_sha"]), "synthetic input drifted: " + name
+        raw = so.sgbm_compute(L, R, 128, 21)
+        assert sha(raw) == str(g[p + "raw_sha"]), name
+        assert int((raw >= 0).sum()) == int(g[p + "valid"])
+        assert sha(so.filter_speckles(raw.copy(), 0, 60, 40)) == str(g[p + "speckle60_sha"]), name
+        spk = so.filter_speckles(raw.copy(), 0, 4000, 123)
+        assert sha(spk) == str(g[p + "speckle_sha"]), name
+        final = so.scale_disparity(spk, 128, crop)
+        assert final.shape == tuple(g[p + "shape"]) and sha(final) == str(g[p + "final_sha"]), name
+        if p + "final" in g:
+            assert sha(so.disparity(L, R, 128, crop)) == str(g[p + "final_sha"])
+            assert np.array_equal(final, g[p + "final"]) and np.array_equal(raw, g[p + "raw"])
