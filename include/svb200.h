@@ -268,6 +268,27 @@ int svb_road_hull(const uint32_t *bits, int F, int H, int W, int cap, int32_t *h
                   int32_t *centre_xy, uint8_t *hull_mask, uint8_t *obstacles, void *scratch, int64_t scratch_bytes,
                   void *stream);
 
+/* ---- f4  the matcher stage                                               functions.py:26, 104-128
+ * svb_sgbm_compute    = stereoProcessor.compute(grayL, grayR) with the module's matcher
+ *                       cv2.StereoSGBM_create(0, 128, 21) (functions.py:26,108): OpenCV's MODE_SGBM semi-global block
+ *                       matcher (P1 = 2, P2 = 5, preFilterCap 15, uniquenessRatio 0, disp12MaxDiff 1 as OpenCV resolves
+ *                       the zeros) followed by its 3x3 median.  grayL, grayR uint8 [F,H,W] -> disp16 int16 [F,H,W]
+ *                       (disparity x 16, -16 = no match).  num_disparities must be 128 (svb_sgbm_supported),
+ *                       block odd in [1,31], W - 128 > block / 2.  The cost volumes travel through `scratch`:
+ *                       svb_sgbm_scratch_bytes(f, H, W, 128) is what f frames in flight need (250 MB per 1024x544
+ *                       frame); any size from one frame up is accepted and the batch is processed in chunks.
+ * svb_filter_speckles = cv2.filterSpeckles(disp16, new_val, max_size, max_diff) in place      (functions.py:111)
+ * svb_disparity_scale = threshold-to-zero, (d / 16.) -> uint8, x (256. / max_disparity) -> uint8 (functions.py:117-127;
+ *                       the crop of functions.py:121-123 is a view the host takes). */
+int     svb_sgbm_supported(int H, int W, int num_disparities, int block);
+int64_t svb_sgbm_scratch_bytes(int F, int H, int W, int num_disparities);
+int     svb_sgbm_compute(const uint8_t *grayL, const uint8_t *grayR, int F, int H, int W, int num_disparities, int block,
+                         int16_t *disp16, void *scratch, int64_t scratch_bytes, void *stream);
+int64_t svb_speckle_scratch_bytes(int F, int H, int W);
+int     svb_filter_speckles(int16_t *img16, int F, int H, int W, int new_val, int max_size, int max_diff, void *scratch,
+                            int64_t scratch_bytes, void *stream);
+int     svb_disparity_scale(const int16_t *disp16, int64_t n, int max_disparity, uint8_t *out, void *stream);
+
 /* ---- a8-a14 fused, batched: the road points of F frames               stereovision.py:97-140
  * reproj_bits: table of svb_reproject_bits or NULL.
  * pass 1: near = |P.abc-1| < cutoff ; per-frame hue histogram of the near points (shared memory,

@@ -17,7 +17,7 @@ LIB_PATH = os.path.join(_PKG, "libsvb200.so")
 HUE_BINS = 1001
 HIST_STRIDE = 1024
 PLANE_STRIDE = 8
-ABI_VERSION = 9
+ABI_VERSION = 10
 SVB_OK, SVB_E_NULL, SVB_E_SHAPE, SVB_E_ARG, SVB_E_SCRATCH = 0, -1, -2, -3, -4      # include/svb200.h
 SVB_MAX_DIM = 2048                                                                  # csrc/svb_common.cuh
 
@@ -76,6 +76,12 @@ SIGNATURES = {
     "svb_normal_line": (I, [P, P, I, P, P, I, I, I, CAMP, P, P, P]),
     "svb_road_hull": (I, [P, I, I, I, I, P, P, P, P, P, P, L, P]),
     "svb_road_hull_scratch_bytes": (L, [I, I]),
+    "svb_sgbm_supported": (I, [I, I, I, I]),
+    "svb_sgbm_scratch_bytes": (L, [I, I, I, I]),
+    "svb_sgbm_compute": (I, [P, P, I, I, I, I, I, P, P, L, P]),
+    "svb_speckle_scratch_bytes": (L, [I, I, I]),
+    "svb_filter_speckles": (I, [P, I, I, I, I, I, I, P, L, P]),
+    "svb_disparity_scale": (I, [P, L, I, P, P]),
     "svb_bits_words": (L, [I, I]),
     "svb_pack_mask": (I, [P, I, I, I, P, P, P]),
     "svb_clean_road": (I, [P, P, I, I, I, P, P, P, P, P]),

@@ -6,7 +6,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 PKG = os.path.dirname(HERE)
 OUT = os.path.join(PKG, "libsvb200.so")
-SOURCES = ["svb_abi.cu", "svb_project.cu", "svb_ransac.cu", "svb_road.cu", "svb_clean.cu", "svb_sites.cu", "svb_prep.cu", "svb_options.cu", "svb_hull.cu"]
+SOURCES = ["svb_abi.cu", "svb_project.cu", "svb_ransac.cu", "svb_road.cu", "svb_clean.cu", "svb_sites.cu", "svb_prep.cu", "svb_options.cu", "svb_hull.cu", "svb_sgbm.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
          "-shared", "-Xcompiler", "-fPIC,-ffp-contract=off", "--use_fast_math=false"]

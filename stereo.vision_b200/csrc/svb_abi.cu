@@ -1,7 +1,7 @@
 // ABI bookkeeping: version and error strings.
 #include "svb_common.cuh"
 
-extern "C" int svb_version(void) { return 9; }
+extern "C" int svb_version(void) { return 10; }
 
 extern "C" const char *svb_error_string(int code) {
     switch (code) {
@@ -36,7 +36,8 @@ static const char *k_names[K_COUNT_] = {
     "ransac_dump", "ransac_finalize", "point_errors", "compact_cloud", "hue_hist", "hue_bins", "reproject",
     "scatter_points", "road_pass1", "road_pass2", "road_clear", "road_cluster", "road_table", "road_near", "road_scatter",
     "clean_band", "pack_mask", "mask_points", "road_sites", "road_sites_scatter",
-    "prep_gamma_gray", "prep_equalize_lut", "prep_apply_lut", "fill_row_mean", "normal_line", "road_hull", "hull_masks"};
+    "prep_gamma_gray", "prep_equalize_lut", "prep_apply_lut", "fill_row_mean", "normal_line", "road_hull", "hull_masks",
+    "sgbm_cost", "sgbm_paths", "sgbm_final", "speckle", "disparity_scale"};
 struct EvPair { int id; cudaEvent_t a, b; };
 static std::vector<EvPair> g_events;
 static cudaEvent_t g_pending[K_COUNT_];

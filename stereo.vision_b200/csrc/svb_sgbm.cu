@@ -1,0 +1,512 @@
+// Matcher stage: functions.disparity, functions.py:104-128, with the module's matcher
+// cv2.StereoSGBM_create(0, 128, 21) (functions.py:26): semi-global block matching in OpenCV's MODE_SGBM,
+// 3x3 median, cv2.filterSpeckles(.., 0, 4000, 123), scaling to the path's uint8 half-pixel disparity.
+//
+// OpenCV walks the image once, row by row, with cyclic row buffers; a row depends on the row above through
+// three of the five path directions.  Here the five directions are five sets of INDEPENDENT 1-D paths
+// (vertical columns, two diagonal families, rows left-to-right, rows right-to-left): a path that enters the
+// image through a side border starts from the same all-zero state as one entering through the top row, and
+// L_r(p,.) only depends on L_r(p-r,.).  One warp walks one path, lane l holding disparities 4l..4l+3, so
+// the d-1 / d+1 neighbours are two shuffles and min_k L_r one REDUX.  Volumes live in HBM as
+// [frame][y][x1][d] int16 (x1 = x - D; 256 B per pixel at D = 128):
+//   hsum  horizontal block sums of the Birchfield-Tomasi pixel costs          (sgbm_hsum)
+//   C     block costs = vertical running sum of hsum                            (sgbm_vsum)
+//   S     sum of the path costs, saturating int16 adds (aliases hsum)           (sgbm_path<dir>)
+// The right-to-left kernel does not write S: it adds its own L, finds the winner, refines it, scatters the
+// right-view disparity for the left-right check and emits the row (sgbm_final).  All integer; results are
+// bit-identical to cv2 4.13 through the oracle (oracle/sgbm_oracle.c) as long as no block cost exceeds
+// 32767 - P2 (OpenCV's own int16 stores wrap or saturate beyond that depending on its SIMD path).
+#include "svb_common.cuh"
+#include "svb_prof.cuh"
+
+#define SG_MAXC 32767
+#define SG_FULL 0xffffffffu
+
+namespace {
+
+constexpr int SG_D = 128;          // numDisparities of functions.py:26; lane l owns d = 4l..4l+3
+constexpr int SG_P1 = 2, SG_P2 = 5, SG_FTZERO = 15, SG_LRDIFF = 1;   // StereoSGBM_create(0,128,21) resolved
+
+// ------------------------------------------------------------------ prefilter
+// per pixel three words (grad | raw << 16): value, lower and upper end of its half-pixel interval.
+// planes: [img(2)][kind(3)][F][H][W] uint32
+__global__ void sgbm_prefilter_kernel(const uint8_t *__restrict__ L, const uint8_t *__restrict__ R, int F, int H, int W,
+                                      uint32_t *__restrict__ planes) {
+    int64_t n = (int64_t)F * H * W;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < 2 * n; i += (int64_t)gridDim.x * blockDim.x) {
+        int img = i >= n;
+        int64_t p = img ? i - n : i;
+        int x = (int)(p % W);
+        int y = (int)((p / W) % H);
+        const uint8_t *src = (img ? R : L) + (p - (int64_t)y * W - x);       // frame base
+        int g[3], r[3];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            int xx = x + k - 1;
+            if (xx < 0 || xx >= W) { g[k] = SG_FTZERO; r[k] = SG_FTZERO; continue; }   // never used (ends handled below)
+            if (xx == 0 || xx == W - 1) { g[k] = SG_FTZERO; r[k] = SG_FTZERO; continue; }
+            const uint8_t *row = src + (int64_t)y * W;
+            const uint8_t *rn = y > 0 ? row - W : row;
+            const uint8_t *rs = y < H - 1 ? row + W : row;
+            int v = ((int)row[xx + 1] - (int)row[xx - 1]) * 2 + (int)rn[xx + 1] - (int)rn[xx - 1] + (int)rs[xx + 1] - (int)rs[xx - 1];
+            g[k] = min(max(v, -SG_FTZERO), SG_FTZERO) + SG_FTZERO;
+            r[k] = row[xx];
+        }
+        int gl = x > 0 ? (g[1] + g[0]) / 2 : g[1], gr = x < W - 1 ? (g[1] + g[2]) / 2 : g[1];
+        int rl = x > 0 ? (r[1] + r[0]) / 2 : r[1], rr = x < W - 1 ? (r[1] + r[2]) / 2 : r[1];
+        uint32_t v = (uint32_t)g[1] | ((uint32_t)r[1] << 16);
+        uint32_t lo = (uint32_t)min(g[1], min(gl, gr)) | ((uint32_t)min(r[1], min(rl, rr)) << 16);
+        uint32_t hi = (uint32_t)max(g[1], max(gl, gr)) | ((uint32_t)max(r[1], max(rl, rr)) << 16);
+        uint32_t *o = planes + (int64_t)img * 3 * n + p;
+        o[0] = v; o[n] = lo; o[2 * n] = hi;
+    }
+}
+
+// Birchfield-Tomasi cost of the gradient half plus a quarter of the raw half (both halves at once)
+__device__ __forceinline__ int bt_cost(uint32_t u, uint32_t u0, uint32_t u1, uint32_t v, uint32_t v0, uint32_t v1) {
+    uint32_t c0 = __vimax_s16x2_relu(__vsub2(u, v1), __vsub2(v0, u));
+    uint32_t c1 = __vimax_s16x2_relu(__vsub2(v, u1), __vsub2(u0, v));
+    uint32_t m = __vmins2(c0, c1);
+    return (int)(m & 0xffffu) + (int)(m >> 18);
+}
+
+// ------------------------------------------------------------------ horizontal block sums
+// grid (x tiles, H, F), 256 threads.  Pixel costs of TX + 2*SW2 + 1 columns (clamped to [0, w1)) are
+// built in shared memory, then every (x1, d pair) sums its window.
+constexpr int SG_TX = 32;
+__global__ void __launch_bounds__(256) sgbm_hsum_kernel(const uint32_t *__restrict__ planes, int F, int H, int W, int SW2,
+                                                        uint32_t *__restrict__ hsum) {
+    extern __shared__ uint32_t sm[];
+    const int w1 = W - SG_D;
+    const int ncol = SG_TX + 2 * SW2;
+    uint32_t *pix = sm;                             // [ncol][64] packed pairs of int16
+    uint32_t *sl = pix + ncol * 64;                 // [3][ncol] left words
+    uint32_t *sr = sl + 3 * ncol;                   // [3][ncol + SG_D] right words
+    const int t0 = blockIdx.x * SG_TX, y = blockIdx.y, f = blockIdx.z;
+    const int64_t n = (int64_t)F * H * W;
+    const uint32_t *PL = planes + ((int64_t)f * H + y) * W;
+    const uint32_t *PR = PL + 3 * n;
+    const int c0 = t0 - SW2;                        // first (unclamped) column of the tile's window
+    for (int i = threadIdx.x; i < 3 * ncol; i += 256) {
+        int k = i / ncol, j = i - k * ncol;
+        int col = min(max(c0 + j, 0), w1 - 1);
+        sl[i] = PL[k * n + col + SG_D];
+    }
+    // right pixels x - d for x = col + D: x - d in [col + 1, col + D]; window base = clamp(c0) + 1
+    const int rbase = max(c0, 0) + 1;
+    for (int i = threadIdx.x; i < 3 * (ncol + SG_D); i += 256) {
+        int k = i / (ncol + SG_D), j = i - k * (ncol + SG_D);
+        int xr = min(rbase + j, W - 1);
+        sr[i] = PR[k * n + xr];
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < ncol * 64; i += 256) {
+        int j = i >> 6, dp = i & 63;
+        int col = min(max(c0 + j, 0), w1 - 1);
+        uint32_t u = sl[j], u0 = sl[ncol + j], u1 = sl[2 * ncol + j];
+        int xr = col + SG_D - 2 * dp - rbase;       // right pixel of d = 2*dp
+        const uint32_t *q = sr + xr;
+        int a = bt_cost(u, u0, u1, q[0], q[ncol + SG_D], q[2 * (ncol + SG_D)]);
+        int b = bt_cost(u, u0, u1, q[-1], q[ncol + SG_D - 1], q[2 * (ncol + SG_D) - 1]);
+        pix[i] = (uint32_t)a | ((uint32_t)b << 16);
+    }
+    __syncthreads();
+    uint32_t *out = hsum + (((int64_t)f * H + y) * w1) * 64;
+    for (int i = threadIdx.x; i < SG_TX * 64; i += 256) {
+        int j = i >> 6, dp = i & 63;
+        int x1 = t0 + j;
+        if (x1 >= w1) break;
+        uint32_t s = 0;
+        for (int k = 0; k <= 2 * SW2; ++k) s += pix[(j + k) * 64 + dp];     // halves stay below 2^16: no carry
+        out[(int64_t)x1 * 64 + dp] = s;
+    }
+}
+
+// ------------------------------------------------------------------ vertical running sum -> C
+// thread = (x1, d pair), a segment of rows; C(y) = C(y-1) + hsum(min(y+SH2, H-1)) - hsum(max(y-SH2-1, 0)),
+// int16 wrap-around like OpenCV's CostType stores.
+__global__ void __launch_bounds__(256) sgbm_vsum_kernel(const uint32_t *__restrict__ hsum, int H, int w1, int SH2, int seg,
+                                                        uint32_t *__restrict__ C) {
+    int64_t col = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;          // (x1, dp) flattened
+    int64_t ncols = (int64_t)w1 * 64;
+    if (col >= ncols) return;
+    int f = blockIdx.z;
+    int y0 = blockIdx.y * seg, y1 = min(y0 + seg, H);
+    const uint32_t *h = hsum + (int64_t)f * H * ncols + col;
+    uint32_t *c = C + (int64_t)f * H * ncols + col;
+    uint32_t acc = 0;
+    for (int k = y0 - SH2; k <= y0 + SH2; ++k) acc = __vadd2(acc, __ldg(h + (int64_t)min(max(k, 0), H - 1) * ncols));
+    c[(int64_t)y0 * ncols] = acc;
+    for (int y = y0 + 1; y < y1; ++y) {
+        uint32_t a = __ldg(h + (int64_t)min(y + SH2, H - 1) * ncols);
+        uint32_t b = __ldg(h + (int64_t)max(y - SH2 - 1, 0) * ncols);
+        acc = __vsub2(__vadd2(acc, a), b);
+        c[(int64_t)y * ncols] = acc;
+    }
+}
+
+// ------------------------------------------------------------------ one step of a path
+struct PathState { int l0, l1, l2, l3, mn; };
+
+__device__ __forceinline__ void unpack4(uint2 w, int &a, int &b, int &c, int &d) {
+    a = (int)(short)(w.x & 0xffffu); b = (int)(short)(w.x >> 16);
+    c = (int)(short)(w.y & 0xffffu); d = (int)(short)(w.y >> 16);
+}
+__device__ __forceinline__ uint2 pack4(int a, int b, int c, int d) {
+    return make_uint2(((uint32_t)a & 0xffffu) | ((uint32_t)b << 16), ((uint32_t)c & 0xffffu) | ((uint32_t)d << 16));
+}
+// L_r(p,d) = C(p,d) + min(L(d), L(d-1)+P1, L(d+1)+P1, min L + P2) - min L   (see the oracle's note on the shift)
+__device__ __forceinline__ void path_step(PathState &s, uint2 cw, int lane) {
+    int c0, c1, c2, c3;
+    unpack4(cw, c0, c1, c2, c3);
+    int left = __shfl_up_sync(SG_FULL, s.l3, 1);
+    int right = __shfl_down_sync(SG_FULL, s.l0, 1);
+    if (lane == 0) left = SG_MAXC;
+    if (lane == 31) right = SG_MAXC;
+    int cap = s.mn + SG_P2;
+    int n0 = c0 + min(min(s.l0, cap), min(left, s.l1) + SG_P1) - s.mn;
+    int n1 = c1 + min(min(s.l1, cap), min(s.l0, s.l2) + SG_P1) - s.mn;
+    int n2 = c2 + min(min(s.l2, cap), min(s.l1, s.l3) + SG_P1) - s.mn;
+    int n3 = c3 + min(min(s.l3, cap), min(s.l2, right) + SG_P1) - s.mn;
+    int m = __reduce_min_sync(SG_FULL, min(min(n0, n1), min(n2, n3)));
+    s.l0 = n0; s.l1 = n1; s.l2 = n2; s.l3 = n3; s.mn = m;
+}
+
+// DIR 0: rows, left to right (RMW S).  DIR 1: from (x-1, y-1).  DIR 2: from (x, y-1), first writer of S.
+// DIR 3: from (x+1, y-1).  One warp per path; 8 warps per CTA.
+template <int DIR>
+__global__ void __launch_bounds__(256) sgbm_path_kernel(const uint2 *__restrict__ C, uint2 *__restrict__ S, int F, int H, int w1) {
+    const int lane = threadIdx.x & 31;
+    const int npaths = DIR == 0 ? H : DIR == 2 ? w1 : w1 + H - 1;
+    int64_t wid = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+    if (wid >= (int64_t)F * npaths) return;
+    int f = (int)(wid / npaths), p = (int)(wid - (int64_t)f * npaths);
+    int x, y, dx, dy;
+    if (DIR == 0) { x = 0; y = p; dx = 1; dy = 0; }
+    else if (DIR == 2) { x = p; y = 0; dx = 0; dy = 1; }
+    else if (DIR == 1) { dx = 1; dy = 1; if (p < w1) { x = p; y = 0; } else { x = 0; y = p - w1 + 1; } }
+    else { dx = -1; dy = 1; if (p < w1) { x = p; y = 0; } else { x = w1 - 1; y = p - w1 + 1; } }
+    int len;
+    if (DIR == 0) len = w1;
+    else if (DIR == 2) len = H;
+    else if (DIR == 1) len = min(w1 - x, H - y);
+    else len = min(x + 1, H - y);
+    const int64_t stride = ((int64_t)dy * w1 + dx) * 32;                     // in uint2 (4 disparities) units
+    int64_t idx = (((int64_t)f * H + y) * w1 + x) * 32 + lane;
+    PathState s = {0, 0, 0, 0, 0};
+    int i = 0;
+    for (; i + 4 <= len; i += 4) {
+        uint2 c[4], sv[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            c[k] = __ldg(C + idx + k * stride);
+            if (DIR != 2) sv[k] = S[idx + k * stride];
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            path_step(s, c[k], lane);
+            uint2 l = pack4(s.l0, s.l1, s.l2, s.l3);
+            if (DIR != 2) { l.x = __vaddss2(sv[k].x, l.x); l.y = __vaddss2(sv[k].y, l.y); }
+            S[idx + k * stride] = l;
+        }
+        idx += 4 * stride;
+    }
+    for (; i < len; ++i) {
+        uint2 c = __ldg(C + idx);
+        path_step(s, c, lane);
+        uint2 l = pack4(s.l0, s.l1, s.l2, s.l3);
+        if (DIR != 2) { uint2 sv = S[idx]; l.x = __vaddss2(sv.x, l.x); l.y = __vaddss2(sv.y, l.y); }
+        S[idx] = l;
+        idx += stride;
+    }
+}
+
+// ------------------------------------------------------------------ right-to-left sweep + winner + checks
+// one warp per row, 4 warps per CTA; per warp W x (disp1, disp2, disp2cost) int16 in shared memory.
+__global__ void __launch_bounds__(128) sgbm_final_kernel(const uint2 *__restrict__ C, const uint2 *__restrict__ S, int F, int H, int W,
+                                                         int16_t *__restrict__ disp) {
+    extern __shared__ int16_t sh16[];
+    const int w1 = W - SG_D;
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    int64_t wid = blockIdx.x * 4 + wib;
+    if (wid >= (int64_t)F * H) return;
+    int16_t *d1 = sh16 + (size_t)wib * 3 * W, *d2 = d1 + W, *d2c = d2 + W;
+    for (int x = lane; x < W; x += 32) { d1[x] = -16; d2[x] = -16; d2c[x] = SG_MAXC; }
+    __syncwarp();
+    int64_t idx = (wid * w1 + (w1 - 1)) * 32 + lane;
+    PathState s = {0, 0, 0, 0, 0};
+    uint2 cn = __ldg(C + idx), sn = __ldg(S + idx);
+    for (int x1 = w1 - 1; x1 >= 0; --x1) {
+        uint2 c = cn, sv = sn;
+        if (x1 > 0) { cn = __ldg(C + idx - 32); sn = __ldg(S + idx - 32); }
+        idx -= 32;
+        path_step(s, c, lane);
+        int a0, a1, a2, a3;
+        unpack4(sv, a0, a1, a2, a3);
+        a0 = min(a0 + s.l0, SG_MAXC); a1 = min(a1 + s.l1, SG_MAXC); a2 = min(a2 + s.l2, SG_MAXC); a3 = min(a3 + s.l3, SG_MAXC);
+        a0 = max(a0, -32768); a1 = max(a1, -32768); a2 = max(a2, -32768); a3 = max(a3, -32768);
+        // first minimum over ascending d: key = (S + 32768) << 8 | d
+        uint32_t k0 = ((uint32_t)(a0 + 32768) << 8) | (uint32_t)(4 * lane);
+        uint32_t k1 = ((uint32_t)(a1 + 32768) << 8) | (uint32_t)(4 * lane + 1);
+        uint32_t k2 = ((uint32_t)(a2 + 32768) << 8) | (uint32_t)(4 * lane + 2);
+        uint32_t k3 = ((uint32_t)(a3 + 32768) << 8) | (uint32_t)(4 * lane + 3);
+        uint32_t key = __reduce_min_sync(SG_FULL, min(min(k0, k1), min(k2, k3)));
+        int minS = (int)(key >> 8) - 32768, best = (int)(key & 0xffu);
+        if (minS >= SG_MAXC) continue;                  // every S saturated: OpenCV finds no winner, pixel stays invalid
+        // S[best-1], S[best+1] for the parabola
+        int lo = best - 1, hi = best + 1;
+        int pick_lo = (lo & 3) == 0 ? a0 : (lo & 3) == 1 ? a1 : (lo & 3) == 2 ? a2 : a3;
+        int pick_hi = (hi & 3) == 0 ? a0 : (hi & 3) == 1 ? a1 : (hi & 3) == 2 ? a2 : a3;
+        int s_lo = __shfl_sync(SG_FULL, pick_lo, (lo >> 2) & 31);
+        int s_hi = __shfl_sync(SG_FULL, pick_hi, (hi >> 2) & 31);
+        if (lane == 0) {
+            int x2 = x1 + SG_D - best;
+            if (d2c[x2] > minS) { d2c[x2] = (int16_t)minS; d2[x2] = (int16_t)best; }
+            int d;
+            if (0 < best && best < SG_D - 1) {
+                int den = max(s_lo + s_hi - 2 * minS, 1);
+                d = best * 16 + ((s_lo - s_hi) * 16 + den) / (den * 2);
+            } else d = best * 16;
+            d1[x1 + SG_D] = (int16_t)d;
+        }
+    }
+    __syncwarp();
+    int16_t *out = disp + wid * W;
+    for (int x = lane; x < W; x += 32) {
+        int v = d1[x];
+        if (x >= SG_D && v != -16) {
+            int da = v >> 4, db = (v + 15) >> 4;
+            int xa = x - da, xb = x - db;
+            if (xa >= 0 && xa < W && d2[xa] >= 0 && abs(d2[xa] - da) > SG_LRDIFF &&
+                xb >= 0 && xb < W && d2[xb] >= 0 && abs(d2[xb] - db) > SG_LRDIFF) v = -16;
+        }
+        out[x] = (int16_t)v;
+    }
+}
+
+// ------------------------------------------------------------------ 3x3 median (replicated border), int16
+__device__ __forceinline__ void cswap(int &a, int &b) { int t = min(a, b); b = max(a, b); a = t; }
+__global__ void sgbm_median3_kernel(const int16_t *__restrict__ src, int F, int H, int W, int16_t *__restrict__ dst) {
+    int64_t n = (int64_t)F * H * W;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        int x = (int)(i % W), y = (int)((i / W) % H);
+        const int16_t *base = src + (i - (int64_t)y * W - x);
+        int v[9];
+#pragma unroll
+        for (int dy = -1; dy <= 1; ++dy)
+#pragma unroll
+            for (int dx = -1; dx <= 1; ++dx)
+                v[(dy + 1) * 3 + dx + 1] = base[(int64_t)min(max(y + dy, 0), H - 1) * W + min(max(x + dx, 0), W - 1)];
+        // median-of-9 network
+        cswap(v[1], v[2]); cswap(v[4], v[5]); cswap(v[7], v[8]); cswap(v[0], v[1]); cswap(v[3], v[4]); cswap(v[6], v[7]);
+        cswap(v[1], v[2]); cswap(v[4], v[5]); cswap(v[7], v[8]); cswap(v[0], v[3]); cswap(v[5], v[8]); cswap(v[4], v[7]);
+        cswap(v[3], v[6]); cswap(v[1], v[4]); cswap(v[2], v[5]); cswap(v[4], v[7]); cswap(v[4], v[2]); cswap(v[6], v[4]);
+        cswap(v[4], v[2]);
+        dst[i] = (int16_t)v[4];
+    }
+}
+
+// ------------------------------------------------------------------ cv2.filterSpeckles: union-find labelling
+// label = index of the component's smallest pixel.  Rows are pre-linked into runs by one warp per row
+// (ballot of the run starts), vertical links are merged with atomicMin union-find.
+__device__ __forceinline__ bool sp_linked(int a, int b, int newVal, int maxDiff) {
+    return a != newVal && b != newVal && abs(a - b) <= maxDiff;
+}
+__global__ void __launch_bounds__(256) speckle_rows_kernel(const int16_t *__restrict__ img, int F, int H, int W, int newVal, int maxDiff,
+                                                           int32_t *__restrict__ label, int32_t *__restrict__ size) {
+    const int lane = threadIdx.x & 31;
+    int64_t row = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+    if (row >= (int64_t)F * H) return;
+    const int16_t *r = img + row * W;
+    int32_t *lab = label + row * W, *sz = size + row * W;
+    int base = (int)((row % H) * W);                  // labels are per-frame pixel indices
+    int carry = -1;
+    for (int x0 = 0; x0 < W; x0 += 32) {
+        int x = x0 + lane;
+        int v = x < W ? r[x] : newVal;
+        int pv = (x > 0 && x < W) ? r[x - 1] : newVal;
+        bool valid = x < W && v != newVal;
+        bool start = valid && !sp_linked(v, pv, newVal, maxDiff);
+        uint32_t starts = __ballot_sync(SG_FULL, start);
+        uint32_t m = starts & (0xffffffffu >> (31 - lane));
+        int st = m ? x0 + 31 - __clz(m) : carry;
+        if (x < W) { lab[x] = valid ? base + st : -1; sz[x] = 0; }
+        int last = __shfl_sync(SG_FULL, valid ? st : -1, 31);
+        carry = last;
+    }
+}
+__device__ __forceinline__ int sp_find(const int32_t *lab, int i) {
+    int p = ((volatile const int32_t *)lab)[i];
+    while (p != i) { i = p; p = ((volatile const int32_t *)lab)[i]; }
+    return i;
+}
+__device__ void sp_unite(int32_t *lab, int a, int b) {
+    while (true) {
+        a = sp_find(lab, a); b = sp_find(lab, b);
+        if (a == b) return;
+        if (a > b) { int t = a; a = b; b = t; }
+        int old = atomicMin(lab + b, a);
+        if (old == b) return;
+        b = old;
+    }
+}
+__global__ void speckle_merge_kernel(const int16_t *__restrict__ img, int F, int H, int W, int newVal, int maxDiff, int32_t *__restrict__ label) {
+    int64_t n = (int64_t)F * H * W, hw = (int64_t)H * W;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        int p = (int)(i % hw);
+        if (p < W) continue;
+        int v = img[i], u = img[i - W];
+        if (!sp_linked(v, u, newVal, maxDiff)) continue;
+        // skip when the pixel to the left has the same two links (its merge covers this one)
+        int x = p % W;
+        if (x > 0) {
+            int vl = img[i - 1], ul = img[i - W - 1];
+            if (sp_linked(v, vl, newVal, maxDiff) && sp_linked(u, ul, newVal, maxDiff) && sp_linked(vl, ul, newVal, maxDiff)) continue;
+        }
+        sp_unite(label + (i - p), p, p - W);
+    }
+}
+__global__ void speckle_count_kernel(int F, int H, int W, int32_t *__restrict__ label, int32_t *__restrict__ size) {
+    int64_t n = (int64_t)F * H * W, hw = (int64_t)H * W;
+    const int lane = threadIdx.x & 31;
+    int64_t warp0 = ((blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5) * 32;
+    for (int64_t i0 = warp0; i0 < n; i0 += (int64_t)gridDim.x * blockDim.x) {          // warp-uniform trip count
+        int64_t i = i0 + lane;
+        long long key = -1 - lane;                      // unique per lane: no match
+        if (i < n) {
+            int p = (int)(i % hw);
+            int32_t *lab = label + (i - p);
+            if (lab[p] >= 0) {
+                int r = sp_find(lab, p);
+                lab[p] = r;                             // compression: the root is an ancestor, concurrent finds stay valid
+                key = (i - p) + r;
+            }
+        }
+        uint32_t same = __match_any_sync(SG_FULL, key);
+        if (key >= 0 && (__ffs(same) - 1) == lane) atomicAdd(size + key, __popc(same));
+    }
+}
+__global__ void speckle_apply_kernel(int16_t *__restrict__ img, int F, int H, int W, int newVal, int maxSize, const int32_t *__restrict__ label,
+                                     const int32_t *__restrict__ size) {
+    int64_t n = (int64_t)F * H * W, hw = (int64_t)H * W;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        int p = (int)(i % hw);
+        int l = label[i];
+        if (l < 0) continue;
+        if (size[(i - p) + l] <= maxSize) img[i] = (int16_t)newVal;
+    }
+}
+
+// ------------------------------------------------------------------ functions.py:117-127
+__global__ void disparity_scale_kernel(const int16_t *__restrict__ d16, int64_t n, double factor, uint8_t *__restrict__ out) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        int v = d16[i];
+        v = v > 0 ? v : 0;                              // THRESH_TOZERO
+        int s = (v >> 4) & 0xff;                        // (d / 16.).astype(uint8): truncation, then uint8 wrap
+        out[i] = (uint8_t)((long long)__dmul_rn((double)s, factor) & 0xff);
+    }
+}
+
+int grid_for(int64_t n, int threads) {
+    int64_t b = (n + threads - 1) / threads;
+    return (int)(b < 1 ? 1 : (b > 148 * 32 ? 148 * 32 : b));
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------ C ABI
+extern "C" int svb_sgbm_supported(int H, int W, int num_disparities, int block) {
+    return (num_disparities == SG_D && block >= 1 && block <= 31 && (block & 1) && H >= 1 && H <= SVB_MAX_DIM && W <= SVB_MAX_DIM &&
+            W - SG_D > block / 2) ? 1 : 0;
+}
+
+// bytes of scratch per frame held at once: 6 prefilter planes + the hsum/S volume + the C volume + one int16 image
+static int64_t sgbm_frame_bytes(int H, int W) {
+    int64_t w1 = W - SG_D;
+    int64_t vol = (int64_t)H * w1 * SG_D * 2;
+    return 6 * (int64_t)H * W * 4 + 2 * vol + (int64_t)H * W * 2;
+}
+extern "C" int64_t svb_sgbm_scratch_bytes(int F, int H, int W, int num_disparities) {
+    if (F < 1 || num_disparities != SG_D || W <= SG_D) return 0;
+    return (int64_t)F * sgbm_frame_bytes(H, W) + 256;
+}
+
+extern "C" int svb_sgbm_compute(const uint8_t *grayL, const uint8_t *grayR, int F, int H, int W, int num_disparities, int block,
+                                int16_t *disp16, void *scratch, int64_t scratch_bytes, void *stream) {
+    if (!grayL || !grayR || !disp16 || !scratch) return SVB_E_NULL;
+    if (F < 1) return SVB_E_SHAPE;
+    if (!svb_sgbm_supported(H, W, num_disparities, block)) return SVB_E_ARG;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int64_t per = sgbm_frame_bytes(H, W);
+    int fc = (int)((scratch_bytes - 256) / per);
+    if (fc < 1) return SVB_E_SCRATCH;
+    if (fc > F) fc = F;
+    const int w1 = W - SG_D, SW2 = block / 2;
+    char *base = (char *)(((uintptr_t)scratch + 255) & ~(uintptr_t)255);
+    for (int f0 = 0; f0 < F; f0 += fc) {
+        int n = F - f0 < fc ? F - f0 : fc;
+        int64_t vol = (int64_t)n * H * w1 * SG_D * 2;
+        uint32_t *planes = (uint32_t *)base;
+        uint32_t *hs = (uint32_t *)(base + 6 * (int64_t)n * H * W * 4);
+        uint32_t *Cv = (uint32_t *)((char *)hs + vol);
+        int16_t *raw = (int16_t *)((char *)Cv + vol);
+        const uint8_t *L = grayL + (int64_t)f0 * H * W, *R = grayR + (int64_t)f0 * H * W;
+        {
+            ProfScope ps(K_SGBM_COST, st);
+            sgbm_prefilter_kernel<<<grid_for(2 * (int64_t)n * H * W, 256), 256, 0, st>>>(L, R, n, H, W, planes);
+            int ncol = SG_TX + 2 * SW2;
+            size_t smem = ((size_t)ncol * 64 + 3 * ncol + 3 * (ncol + SG_D)) * 4;
+            sgbm_hsum_kernel<<<dim3((w1 + SG_TX - 1) / SG_TX, H, n), 256, smem, st>>>(planes, n, H, W, SW2, hs);
+            int seg = 68;
+            sgbm_vsum_kernel<<<dim3((unsigned)(((int64_t)w1 * 64 + 255) / 256), (H + seg - 1) / seg, n), 256, 0, st>>>(hs, H, w1, SW2, seg, Cv);
+            SVB_LAUNCH_CHECK();
+        }
+        {
+            ProfScope ps(K_SGBM_PATHS, st);
+            const uint2 *C2 = (const uint2 *)Cv;
+            uint2 *S2 = (uint2 *)hs;
+            sgbm_path_kernel<2><<<(unsigned)(((int64_t)n * w1 + 7) / 8), 256, 0, st>>>(C2, S2, n, H, w1);
+            sgbm_path_kernel<1><<<(unsigned)(((int64_t)n * (w1 + H - 1) + 7) / 8), 256, 0, st>>>(C2, S2, n, H, w1);
+            sgbm_path_kernel<3><<<(unsigned)(((int64_t)n * (w1 + H - 1) + 7) / 8), 256, 0, st>>>(C2, S2, n, H, w1);
+            sgbm_path_kernel<0><<<(unsigned)(((int64_t)n * H + 7) / 8), 256, 0, st>>>(C2, S2, n, H, w1);
+            SVB_LAUNCH_CHECK();
+        }
+        {
+            ProfScope ps(K_SGBM_FINAL, st);
+            sgbm_final_kernel<<<(unsigned)(((int64_t)n * H + 3) / 4), 128, (size_t)4 * 3 * W * 2, st>>>((const uint2 *)Cv, (const uint2 *)hs, n, H, W, raw);
+            sgbm_median3_kernel<<<grid_for((int64_t)n * H * W, 256), 256, 0, st>>>(raw, n, H, W, disp16 + (int64_t)f0 * H * W);
+            SVB_LAUNCH_CHECK();
+        }
+    }
+    return SVB_OK;
+}
+
+extern "C" int64_t svb_speckle_scratch_bytes(int F, int H, int W) { return F < 1 ? 0 : (int64_t)F * H * W * 8 + 256; }
+
+extern "C" int svb_filter_speckles(int16_t *img16, int F, int H, int W, int new_val, int max_size, int max_diff, void *scratch,
+                                   int64_t scratch_bytes, void *stream) {
+    if (!img16 || !scratch) return SVB_E_NULL;
+    if (F < 1 || H < 1 || W < 1 || (int64_t)H * W >= (1 << 30)) return SVB_E_SHAPE;
+    if (scratch_bytes < svb_speckle_scratch_bytes(F, H, W)) return SVB_E_SCRATCH;
+    cudaStream_t st = (cudaStream_t)stream;
+    int32_t *label = (int32_t *)(((uintptr_t)scratch + 255) & ~(uintptr_t)255);
+    int32_t *size = label + (int64_t)F * H * W;
+    int64_t n = (int64_t)F * H * W;
+    ProfScope ps(K_SPECKLE, st);
+    speckle_rows_kernel<<<(unsigned)(((int64_t)F * H + 7) / 8), 256, 0, st>>>(img16, F, H, W, new_val, max_diff, label, size);
+    speckle_merge_kernel<<<grid_for(n, 256), 256, 0, st>>>(img16, F, H, W, new_val, max_diff, label);
+    speckle_count_kernel<<<grid_for(n, 256), 256, 0, st>>>(F, H, W, label, size);
+    speckle_apply_kernel<<<grid_for(n, 256), 256, 0, st>>>(img16, F, H, W, new_val, max_size, label, size);
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
+}
+
+extern "C" int svb_disparity_scale(const int16_t *disp16, int64_t n, int max_disparity, uint8_t *out, void *stream) {
+    if (!disp16 || !out) return SVB_E_NULL;
+    if (n < 1 || max_disparity < 1) return SVB_E_ARG;
+    cudaStream_t st = (cudaStream_t)stream;
+    ProfScope ps(K_DISP_SCALE, st);
+    disparity_scale_kernel<<<grid_for(n, 256), 256, 0, st>>>(disp16, n, 256.0 / (double)max_disparity, out);
+    SVB_LAUNCH_CHECK();
+    return SVB_OK;
+}

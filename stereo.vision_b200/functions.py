@@ -419,6 +419,27 @@ def greyscale(imgL, imgR):
     return (out[0], out[1])
 
 
+# ---------------------------------------------------------------- f4
+def disparity(grayL, grayR, max_disparity, crop_disparity):
+    """functions.py:104-128 with the module's matcher StereoSGBM_create(0, 128, 21) (functions.py:26): semi-global
+    matching + 3x3 median, filterSpeckles(.., 0, 4000, max_disparity - 5), threshold to zero, /16 -> uint8,
+    optional crop [0:390, 135:], x (256 / max_disparity) -> uint8."""
+    from .pipeline import Matcher
+    L, was_tensor = _to_dev_u8(grayL)
+    R, _ = _to_dev_u8(grayR)
+    if L.dim() != 2 or L.shape != R.shape:
+        raise ValueError("disparity expects two gray images of one shape")
+    key = ("matcher", tuple(L.shape), int(max_disparity), str(L.device))
+    if _state.get("matcher_key") != key:
+        _state["matcher"] = Matcher(shape=tuple(L.shape), max_disparity=int(max_disparity), max_frames=1, frames_in_flight=1,
+                                    device=L.device)
+        _state["matcher_key"] = key
+    out = _state["matcher"].disparity(L, R)[0]
+    if crop_disparity:
+        out = out[0:390, 135:out.shape[1]]
+    return _back(out.clone(), was_tensor)
+
+
 # ---------------------------------------------------------------- f3
 def fillAltDisparity(disparity):
     """functions.py:149-162: entries below 2 become the row's mean over its non-zero entries.  The reference

@@ -423,3 +423,50 @@ class FrontEnd:
                 "svb_apply_lut_frames")
         N.count(3)
         return self.bgr[:F], self.eq[:F]
+
+
+class Matcher:
+    """The producer of the path's disparity input: functions.disparity (functions.py:104-128, called at
+    stereovision.py:56) for F rectified gray pairs per call -- the module's StereoSGBM_create(0, 128, 21)
+    (functions.py:26) with its 3x3 median, filterSpeckles(.., 0, 4000, max_disparity - 5), threshold, /16 and
+    the x (256 / max_disparity) scaling that makes the uint8 disparity the path consumes.  The cost volumes
+    (250 MB per 1024x544 frame) live in a scratch buffer sized for `frames_in_flight` frames; a longer batch is
+    walked in chunks inside svb_sgbm_compute."""
+
+    def __init__(self, shape=(544, 1024), max_disparity=128, block=21, max_frames=32, frames_in_flight=8, device="cuda:0"):
+        N.require_cuda()
+        self.H, self.W, self.F = int(shape[0]), int(shape[1]), int(max_frames)
+        self.device = torch.device(device)
+        self.lib = N.load()
+        self.max_disparity, self.block = int(max_disparity), int(block)
+        if not self.lib.svb_sgbm_supported(self.H, self.W, 128, self.block):
+            raise ValueError("matcher: 128 disparities, odd block <= 31 and W - 128 > block / 2 are supported")
+        fl = max(1, min(int(frames_in_flight), self.F))
+        nb = max(self.lib.svb_sgbm_scratch_bytes(fl, self.H, self.W, 128), self.lib.svb_speckle_scratch_bytes(self.F, self.H, self.W))
+        self.scratch = torch.empty((nb,), dtype=torch.uint8, device=self.device)
+        self.disp16 = torch.empty((self.F, self.H, self.W), dtype=torch.int16, device=self.device)
+        self.disp8 = torch.empty((self.F, self.H, self.W), dtype=torch.uint8, device=self.device)
+
+    def compute(self, grayL, grayR):
+        """stereoProcessor.compute for F pairs: int16 [F,H,W], disparity x 16, -16 = no match."""
+        L, R = _as_cuda_u8(grayL, self.device), _as_cuda_u8(grayR, self.device)
+        if L.dim() == 2:
+            L, R = L[None], R[None]
+        F = L.shape[0]
+        if tuple(L.shape[1:]) != (self.H, self.W) or L.shape != R.shape or F > self.F:
+            raise ValueError("expected up to %d pairs of %dx%d, got %s / %s" % (self.F, self.H, self.W, tuple(L.shape), tuple(R.shape)))
+        N.check(self.lib.svb_sgbm_compute(N.ptr(L), N.ptr(R), F, self.H, self.W, 128, self.block, N.ptr(self.disp16),
+                                          N.ptr(self.scratch), self.scratch.numel(), N.stream_ptr()), "svb_sgbm_compute")
+        N.count(9)
+        return self.disp16[:F]
+
+    def disparity(self, grayL, grayR):
+        """functions.disparity for F pairs: uint8 [F,H,W] in half pixels, 0 = no match (crop: a view the caller takes)."""
+        d16 = self.compute(grayL, grayR)
+        F, st = d16.shape[0], N.stream_ptr()
+        N.check(self.lib.svb_filter_speckles(N.ptr(d16), F, self.H, self.W, 0, 4000, self.max_disparity - 5, N.ptr(self.scratch),
+                                             self.scratch.numel(), st), "svb_filter_speckles")
+        N.check(self.lib.svb_disparity_scale(N.ptr(d16), F * self.H * self.W, self.max_disparity, N.ptr(self.disp8), st),
+                "svb_disparity_scale")
+        N.count(5)
+        return self.disp8[:F]
