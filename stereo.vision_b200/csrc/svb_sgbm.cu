@@ -451,32 +451,31 @@ extern "C" int svb_sgbm_compute(const uint8_t *grayL, const uint8_t *grayR, int 
         uint32_t *Cv = (uint32_t *)((char *)hs + vol);
         int16_t *raw = (int16_t *)((char *)Cv + vol);
         const uint8_t *L = grayL + (int64_t)f0 * H * W, *R = grayR + (int64_t)f0 * H * W;
-        {
-            ProfScope ps(K_SGBM_COST, st);
-            sgbm_prefilter_kernel<<<grid_for(2 * (int64_t)n * H * W, 256), 256, 0, st>>>(L, R, n, H, W, planes);
-            int ncol = SG_TX + 2 * SW2;
-            size_t smem = ((size_t)ncol * 64 + 3 * ncol + 3 * (ncol + SG_D)) * 4;
-            sgbm_hsum_kernel<<<dim3((w1 + SG_TX - 1) / SG_TX, H, n), 256, smem, st>>>(planes, n, H, W, SW2, hs);
-            int seg = 68;
-            sgbm_vsum_kernel<<<dim3((unsigned)(((int64_t)w1 * 64 + 255) / 256), (H + seg - 1) / seg, n), 256, 0, st>>>(hs, H, w1, SW2, seg, Cv);
-            SVB_LAUNCH_CHECK();
-        }
-        {
-            ProfScope ps(K_SGBM_PATHS, st);
-            const uint2 *C2 = (const uint2 *)Cv;
-            uint2 *S2 = (uint2 *)hs;
-            sgbm_path_kernel<2><<<(unsigned)(((int64_t)n * w1 + 7) / 8), 256, 0, st>>>(C2, S2, n, H, w1);
-            sgbm_path_kernel<1><<<(unsigned)(((int64_t)n * (w1 + H - 1) + 7) / 8), 256, 0, st>>>(C2, S2, n, H, w1);
-            sgbm_path_kernel<3><<<(unsigned)(((int64_t)n * (w1 + H - 1) + 7) / 8), 256, 0, st>>>(C2, S2, n, H, w1);
-            sgbm_path_kernel<0><<<(unsigned)(((int64_t)n * H + 7) / 8), 256, 0, st>>>(C2, S2, n, H, w1);
-            SVB_LAUNCH_CHECK();
-        }
-        {
-            ProfScope ps(K_SGBM_FINAL, st);
-            sgbm_final_kernel<<<(unsigned)(((int64_t)n * H + 3) / 4), 128, (size_t)4 * 3 * W * 2, st>>>((const uint2 *)Cv, (const uint2 *)hs, n, H, W, raw);
-            sgbm_median3_kernel<<<grid_for((int64_t)n * H * W, 256), 256, 0, st>>>(raw, n, H, W, disp16 + (int64_t)f0 * H * W);
-            SVB_LAUNCH_CHECK();
-        }
+        const uint2 *C2 = (const uint2 *)Cv;
+        uint2 *S2 = (uint2 *)hs;
+        const unsigned diag_blocks = (unsigned)(((int64_t)n * (w1 + H - 1) + 7) / 8);
+        { ProfScope ps(K_SGBM_PREFILTER, st);
+          sgbm_prefilter_kernel<<<grid_for(2 * (int64_t)n * H * W, 256), 256, 0, st>>>(L, R, n, H, W, planes); }
+        { ProfScope ps(K_SGBM_HSUM, st);
+          int ncol = SG_TX + 2 * SW2;
+          size_t smem = ((size_t)ncol * 64 + 3 * ncol + 3 * (ncol + SG_D)) * 4;
+          sgbm_hsum_kernel<<<dim3((w1 + SG_TX - 1) / SG_TX, H, n), 256, smem, st>>>(planes, n, H, W, SW2, hs); }
+        { ProfScope ps(K_SGBM_VSUM, st);
+          int seg = 68;
+          sgbm_vsum_kernel<<<dim3((unsigned)(((int64_t)w1 * 64 + 255) / 256), (H + seg - 1) / seg, n), 256, 0, st>>>(hs, H, w1, SW2, seg, Cv); }
+        SVB_LAUNCH_CHECK();
+        { ProfScope ps(K_SGBM_PATH_V, st);
+          sgbm_path_kernel<2><<<(unsigned)(((int64_t)n * w1 + 7) / 8), 256, 0, st>>>(C2, S2, n, H, w1); }
+        { ProfScope ps(K_SGBM_PATH_D1, st); sgbm_path_kernel<1><<<diag_blocks, 256, 0, st>>>(C2, S2, n, H, w1); }
+        { ProfScope ps(K_SGBM_PATH_D3, st); sgbm_path_kernel<3><<<diag_blocks, 256, 0, st>>>(C2, S2, n, H, w1); }
+        { ProfScope ps(K_SGBM_PATH_H, st);
+          sgbm_path_kernel<0><<<(unsigned)(((int64_t)n * H + 7) / 8), 256, 0, st>>>(C2, S2, n, H, w1); }
+        SVB_LAUNCH_CHECK();
+        { ProfScope ps(K_SGBM_FINAL, st);
+          sgbm_final_kernel<<<(unsigned)(((int64_t)n * H + 3) / 4), 128, (size_t)4 * 3 * W * 2, st>>>(C2, S2, n, H, W, raw); }
+        { ProfScope ps(K_SGBM_MEDIAN, st);
+          sgbm_median3_kernel<<<grid_for((int64_t)n * H * W, 256), 256, 0, st>>>(raw, n, H, W, disp16 + (int64_t)f0 * H * W); }
+        SVB_LAUNCH_CHECK();
     }
     return SVB_OK;
 }
