@@ -28,10 +28,10 @@ constexpr int SG_D = 128;          // numDisparities of functions.py:26; lane l 
 constexpr int SG_P1 = 2, SG_P2 = 5, SG_FTZERO = 15, SG_LRDIFF = 1;   // StereoSGBM_create(0,128,21) resolved
 
 // ------------------------------------------------------------------ prefilter
-// per pixel three words (grad | raw << 16): value, lower and upper end of its half-pixel interval.
-// planes: [img(2)][kind(3)][F][H][W] uint32
+// per pixel one 16-byte record of three words (grad | raw << 16): value, lower and upper end of its half-pixel
+// interval (fourth word unused).  recs: [img(2)][F][H][W] uint4
 __global__ void sgbm_prefilter_kernel(const uint8_t *__restrict__ L, const uint8_t *__restrict__ R, int F, int H, int W,
-                                      uint32_t *__restrict__ planes) {
+                                      uint4 *__restrict__ recs) {
     int64_t n = (int64_t)F * H * W;
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < 2 * n; i += (int64_t)gridDim.x * blockDim.x) {
         int img = i >= n;
@@ -57,68 +57,79 @@ __global__ void sgbm_prefilter_kernel(const uint8_t *__restrict__ L, const uint8
         uint32_t v = (uint32_t)g[1] | ((uint32_t)r[1] << 16);
         uint32_t lo = (uint32_t)min(g[1], min(gl, gr)) | ((uint32_t)min(r[1], min(rl, rr)) << 16);
         uint32_t hi = (uint32_t)max(g[1], max(gl, gr)) | ((uint32_t)max(r[1], max(rl, rr)) << 16);
-        uint32_t *o = planes + (int64_t)img * 3 * n + p;
-        o[0] = v; o[n] = lo; o[2 * n] = hi;
+        recs[i] = make_uint4(v, lo, hi, 0u);
     }
 }
 
-// Birchfield-Tomasi cost of the gradient half plus a quarter of the raw half (both halves at once)
-__device__ __forceinline__ int bt_cost(uint32_t u, uint32_t u0, uint32_t u1, uint32_t v, uint32_t v0, uint32_t v1) {
-    uint32_t c0 = __vimax_s16x2_relu(__vsub2(u, v1), __vsub2(v0, u));
-    uint32_t c1 = __vimax_s16x2_relu(__vsub2(v, u1), __vsub2(u0, v));
-    uint32_t m = __vmins2(c0, c1);
-    return (int)(m & 0xffffu) + (int)(m >> 18);
+// Birchfield-Tomasi cost of the gradient half plus a quarter of the raw half (both 16-bit halves at once).
+// Halves are biased by 0x8000 so that one 32-bit subtraction never borrows across them and the differences
+// compare as unsigned halves: c0 = max(0, u - v1, v0 - u), c1 = max(0, v - u1, u0 - v), cost = min(c0, c1).
+#define SG_BIAS 0x80008000u
+__device__ __forceinline__ uint32_t bt_cost(uint32_t u, uint32_t ub, uint32_t u0b, uint32_t u1, uint32_t v, uint32_t vb, uint32_t v0b,
+                                            uint32_t v1) {
+    uint32_t c0 = __vimax3_u16x2(ub - v1, v0b - u, SG_BIAS);
+    uint32_t c1 = __vimax3_u16x2(vb - u1, u0b - v, SG_BIAS);
+    uint32_t m = __vminu2(c0, c1);
+    return (m & 0x7fffu) + ((m >> 18) & 0x1fffu);
 }
 
 // ------------------------------------------------------------------ horizontal block sums
-// grid (x tiles, H, F), 256 threads.  Pixel costs of TX + 2*SW2 + 1 columns (clamped to [0, w1)) are
-// built in shared memory, then every (x1, d pair) sums its window.
-constexpr int SG_TX = 32;
-__global__ void __launch_bounds__(256) sgbm_hsum_kernel(const uint32_t *__restrict__ planes, int F, int H, int W, int SW2,
+// thread = (row, pair of disparities), 4 rows per CTA; it walks the row once.  The pixel cost of a column is
+// computed on the fly from two 16-byte records (the right pixel of d = 2dp + 1 is the one d = 2dp used a column
+// earlier); a ring of the last 32 cost pairs (one byte each) in shared memory feeds the sliding window, whose ends
+// repeat the border columns (window clamped to [0, w1)).
+struct HsumState { uint32_t s, pix0; uint4 pv; };
+__device__ __forceinline__ uint32_t hsum_cost(const uint4 *__restrict__ Lp, const uint4 *__restrict__ Rp, uint4 &pv) {
+    uint4 u = __ldg(Lp), v = __ldg(Rp);
+    uint32_t ub = u.x | SG_BIAS, u0b = u.y | SG_BIAS;
+    uint32_t a = bt_cost(u.x, ub, u0b, u.z, v.x, v.x | SG_BIAS, v.y | SG_BIAS, v.z);
+    uint32_t b = bt_cost(u.x, ub, u0b, u.z, pv.x, pv.x | SG_BIAS, pv.y | SG_BIAS, pv.z);
+    pv = v;
+    return a | (b << 16);
+}
+__device__ __forceinline__ uint32_t ring_get(const uint16_t *slot) {
+    uint32_t p = *slot;
+    return (p & 0xffu) | ((p & 0xff00u) << 8);
+}
+__global__ void __launch_bounds__(256) sgbm_hsum_kernel(const uint4 *__restrict__ recs, int F, int H, int W, int SW2,
                                                         uint32_t *__restrict__ hsum) {
-    extern __shared__ uint32_t sm[];
+    __shared__ uint16_t ring[32][256];
     const int w1 = W - SG_D;
-    const int ncol = SG_TX + 2 * SW2;
-    uint32_t *pix = sm;                             // [ncol][64] packed pairs of int16
-    uint32_t *sl = pix + ncol * 64;                 // [3][ncol] left words
-    uint32_t *sr = sl + 3 * ncol;                   // [3][ncol + SG_D] right words
-    const int t0 = blockIdx.x * SG_TX, y = blockIdx.y, f = blockIdx.z;
+    const int dp = threadIdx.x & 63, tx = threadIdx.x;
+    const int64_t row = (int64_t)blockIdx.x * 4 + (threadIdx.x >> 6);
+    if (row >= (int64_t)F * H) return;
     const int64_t n = (int64_t)F * H * W;
-    const uint32_t *PL = planes + ((int64_t)f * H + y) * W;
-    const uint32_t *PR = PL + 3 * n;
-    const int c0 = t0 - SW2;                        // first (unclamped) column of the tile's window
-    for (int i = threadIdx.x; i < 3 * ncol; i += 256) {
-        int k = i / ncol, j = i - k * ncol;
-        int col = min(max(c0 + j, 0), w1 - 1);
-        sl[i] = PL[k * n + col + SG_D];
+    const uint4 *Lp = recs + row * W + SG_D;                      // left pixel of column c: Lp[c]
+    const uint4 *Rp = recs + n + row * W + SG_D - 2 * dp;         // right pixel of (c, d = 2dp): Rp[c]
+    uint32_t *out = hsum + row * w1 * 64 + dp;
+    uint4 pv = __ldg(Rp - 1);
+    // columns 0 .. SW2: fill the window (the border column counts SW2 + 1 times), first output at c = SW2
+    uint32_t pc = hsum_cost(Lp, Rp, pv);
+    const uint32_t pix0 = pc;
+    uint32_t s = pc * (uint32_t)(SW2 + 1);                         // halves stay below 2^16: no carry
+    ring[0][tx] = (uint16_t)((pc & 0xffu) | (pc >> 8));
+    int c = 1;
+    for (; c <= SW2; ++c) {
+        pc = hsum_cost(Lp + c, Rp + c, pv);
+        ring[c & 31][tx] = (uint16_t)((pc & 0xffu) | (pc >> 8));
+        s += pc;
     }
-    // right pixels x - d for x = col + D: x - d in [col + 1, col + D]; window base = clamp(c0) + 1
-    const int rbase = max(c0, 0) + 1;
-    for (int i = threadIdx.x; i < 3 * (ncol + SG_D); i += 256) {
-        int k = i / (ncol + SG_D), j = i - k * (ncol + SG_D);
-        int xr = min(rbase + j, W - 1);
-        sr[i] = PR[k * n + xr];
+    out[0] = s;
+    // steady state: output x1 = c - SW2 after adding column c; the column leaving is x1 - 1 - SW2 (or the border)
+#pragma unroll 4
+    for (; c < w1; ++c) {
+        int lv = c - 2 * SW2 - 1;
+        s -= lv >= 0 ? ring_get(&ring[lv & 31][tx]) : pix0;
+        pc = hsum_cost(Lp + c, Rp + c, pv);
+        ring[c & 31][tx] = (uint16_t)((pc & 0xffu) | (pc >> 8));
+        s += pc;
+        out[(int64_t)(c - SW2) * 64] = s;
     }
-    __syncthreads();
-    for (int i = threadIdx.x; i < ncol * 64; i += 256) {
-        int j = i >> 6, dp = i & 63;
-        int col = min(max(c0 + j, 0), w1 - 1);
-        uint32_t u = sl[j], u0 = sl[ncol + j], u1 = sl[2 * ncol + j];
-        int xr = col + SG_D - 2 * dp - rbase;       // right pixel of d = 2*dp
-        const uint32_t *q = sr + xr;
-        int a = bt_cost(u, u0, u1, q[0], q[ncol + SG_D], q[2 * (ncol + SG_D)]);
-        int b = bt_cost(u, u0, u1, q[-1], q[ncol + SG_D - 1], q[2 * (ncol + SG_D) - 1]);
-        pix[i] = (uint32_t)a | ((uint32_t)b << 16);
-    }
-    __syncthreads();
-    uint32_t *out = hsum + (((int64_t)f * H + y) * w1) * 64;
-    for (int i = threadIdx.x; i < SG_TX * 64; i += 256) {
-        int j = i >> 6, dp = i & 63;
-        int x1 = t0 + j;
-        if (x1 >= w1) break;
-        uint32_t s = 0;
-        for (int k = 0; k <= 2 * SW2; ++k) s += pix[(j + k) * 64 + dp];     // halves stay below 2^16: no carry
-        out[(int64_t)x1 * 64 + dp] = s;
+    for (; c < w1 + SW2; ++c) {                                    // right border: the last column again
+        int lv = c - 2 * SW2 - 1;
+        s -= lv >= 0 ? ring_get(&ring[lv & 31][tx]) : pix0;
+        s += pc;
+        out[(int64_t)(c - SW2) * 64] = s;
     }
 }
 
@@ -222,20 +233,26 @@ __global__ void __launch_bounds__(256) sgbm_path_kernel(const uint2 *__restrict_
 }
 
 // ------------------------------------------------------------------ right-to-left sweep + winner + checks
-// one warp per row, 4 warps per CTA; per warp W x (disp1, disp2, disp2cost) int16 in shared memory.
+// one warp per row, 4 warps per CTA.  Per step the warp only finds (min S, its first d, the two neighbours of the
+// minimum); lane (x1 & 31) keeps that result and every 32 steps the lanes finish their columns in parallel:
+// sub-pixel division, disp1, and the right-view entry disp2[x - d] = d where min S is smallest (first visited,
+// i.e. largest x, on ties) as one shared-memory atomicMin on (min S, -x).  Per warp: W x (uint32 + int16).
 __global__ void __launch_bounds__(128) sgbm_final_kernel(const uint2 *__restrict__ C, const uint2 *__restrict__ S, int F, int H, int W,
                                                          int16_t *__restrict__ disp) {
-    extern __shared__ int16_t sh16[];
+    extern __shared__ uint32_t sh32[];
     const int w1 = W - SG_D;
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     int64_t wid = blockIdx.x * 4 + wib;
     if (wid >= (int64_t)F * H) return;
-    int16_t *d1 = sh16 + (size_t)wib * 3 * W, *d2 = d1 + W, *d2c = d2 + W;
-    for (int x = lane; x < W; x += 32) { d1[x] = -16; d2[x] = -16; d2c[x] = SG_MAXC; }
+    uint32_t *d2k = sh32 + (size_t)wib * W;                                   // (min S + 32768) << 16 | (0xffff - x)
+    int16_t *d1 = (int16_t *)(sh32 + (size_t)4 * W) + (size_t)wib * W;
+    for (int x = lane; x < W; x += 32) { d1[x] = -16; d2k[x] = 0xffffffffu; }
     __syncwarp();
     int64_t idx = (wid * w1 + (w1 - 1)) * 32 + lane;
     PathState s = {0, 0, 0, 0, 0};
     uint2 cn = __ldg(C + idx), sn = __ldg(S + idx);
+    uint32_t mykey = 0xffffffffu;
+    int mylo = 0, myhi = 0;
     for (int x1 = w1 - 1; x1 >= 0; --x1) {
         uint2 c = cn, sv = sn;
         if (x1 > 0) { cn = __ldg(C + idx - 32); sn = __ldg(S + idx - 32); }
@@ -243,31 +260,35 @@ __global__ void __launch_bounds__(128) sgbm_final_kernel(const uint2 *__restrict
         path_step(s, c, lane);
         int a0, a1, a2, a3;
         unpack4(sv, a0, a1, a2, a3);
-        a0 = min(a0 + s.l0, SG_MAXC); a1 = min(a1 + s.l1, SG_MAXC); a2 = min(a2 + s.l2, SG_MAXC); a3 = min(a3 + s.l3, SG_MAXC);
-        a0 = max(a0, -32768); a1 = max(a1, -32768); a2 = max(a2, -32768); a3 = max(a3, -32768);
+        a0 = max(min(a0 + s.l0, SG_MAXC), -32768); a1 = max(min(a1 + s.l1, SG_MAXC), -32768);
+        a2 = max(min(a2 + s.l2, SG_MAXC), -32768); a3 = max(min(a3 + s.l3, SG_MAXC), -32768);
         // first minimum over ascending d: key = (S + 32768) << 8 | d
         uint32_t k0 = ((uint32_t)(a0 + 32768) << 8) | (uint32_t)(4 * lane);
         uint32_t k1 = ((uint32_t)(a1 + 32768) << 8) | (uint32_t)(4 * lane + 1);
         uint32_t k2 = ((uint32_t)(a2 + 32768) << 8) | (uint32_t)(4 * lane + 2);
         uint32_t k3 = ((uint32_t)(a3 + 32768) << 8) | (uint32_t)(4 * lane + 3);
         uint32_t key = __reduce_min_sync(SG_FULL, min(min(k0, k1), min(k2, k3)));
-        int minS = (int)(key >> 8) - 32768, best = (int)(key & 0xffu);
-        if (minS >= SG_MAXC) continue;                  // every S saturated: OpenCV finds no winner, pixel stays invalid
-        // S[best-1], S[best+1] for the parabola
-        int lo = best - 1, hi = best + 1;
+        int lo = (int)(key & 0xffu) - 1, hi = lo + 2;
         int pick_lo = (lo & 3) == 0 ? a0 : (lo & 3) == 1 ? a1 : (lo & 3) == 2 ? a2 : a3;
         int pick_hi = (hi & 3) == 0 ? a0 : (hi & 3) == 1 ? a1 : (hi & 3) == 2 ? a2 : a3;
         int s_lo = __shfl_sync(SG_FULL, pick_lo, (lo >> 2) & 31);
         int s_hi = __shfl_sync(SG_FULL, pick_hi, (hi >> 2) & 31);
-        if (lane == 0) {
-            int x2 = x1 + SG_D - best;
-            if (d2c[x2] > minS) { d2c[x2] = (int16_t)minS; d2[x2] = (int16_t)best; }
-            int d;
-            if (0 < best && best < SG_D - 1) {
-                int den = max(s_lo + s_hi - 2 * minS, 1);
-                d = best * 16 + ((s_lo - s_hi) * 16 + den) / (den * 2);
-            } else d = best * 16;
-            d1[x1 + SG_D] = (int16_t)d;
+        if (lane == (x1 & 31)) { mykey = key; mylo = s_lo; myhi = s_hi; }
+        if ((x1 & 31) == 0) {
+            // lanes finish columns x1 + lane (those below w1); every S saturated = no winner, the pixel stays invalid
+            int minS = (int)(mykey >> 8) - 32768, best = (int)(mykey & 0xffu);
+            int xx1 = x1 + lane;
+            if (xx1 < w1 && mykey != 0xffffffffu && minS < SG_MAXC) {
+                int x = xx1 + SG_D;
+                atomicMin(d2k + (x - best), ((uint32_t)(minS + 32768) << 16) | (uint32_t)(0xffff - x));
+                int d;
+                if (0 < best && best < SG_D - 1) {
+                    int den = max(mylo + myhi - 2 * minS, 1);
+                    d = best * 16 + ((mylo - myhi) * 16 + den) / (den * 2);
+                } else d = best * 16;
+                d1[x] = (int16_t)d;
+            }
+            mykey = 0xffffffffu;
         }
     }
     __syncwarp();
@@ -276,9 +297,10 @@ __global__ void __launch_bounds__(128) sgbm_final_kernel(const uint2 *__restrict
         int v = d1[x];
         if (x >= SG_D && v != -16) {
             int da = v >> 4, db = (v + 15) >> 4;
-            int xa = x - da, xb = x - db;
-            if (xa >= 0 && xa < W && d2[xa] >= 0 && abs(d2[xa] - da) > SG_LRDIFF &&
-                xb >= 0 && xb < W && d2[xb] >= 0 && abs(d2[xb] - db) > SG_LRDIFF) v = -16;
+            int xa = x - da, xb = x - db;                        // both inside the row: 0 <= d < D <= x
+            uint32_t ka = d2k[xa], kb = d2k[xb];
+            int ra = (0xffff - (int)(ka & 0xffffu)) - xa, rb = (0xffff - (int)(kb & 0xffffu)) - xb;   // right-view disparities
+            if (ka != 0xffffffffu && abs(ra - da) > SG_LRDIFF && kb != 0xffffffffu && abs(rb - db) > SG_LRDIFF) v = -16;
         }
         out[x] = (int16_t)v;
     }
@@ -420,11 +442,11 @@ extern "C" int svb_sgbm_supported(int H, int W, int num_disparities, int block) 
             W - SG_D > block / 2) ? 1 : 0;
 }
 
-// bytes of scratch per frame held at once: 6 prefilter planes + the hsum/S volume + the C volume + one int16 image
+// bytes of scratch per frame held at once: 2 images of 16-byte records + the hsum/S volume + the C volume + one int16 image
 static int64_t sgbm_frame_bytes(int H, int W) {
     int64_t w1 = W - SG_D;
     int64_t vol = (int64_t)H * w1 * SG_D * 2;
-    return 6 * (int64_t)H * W * 4 + 2 * vol + (int64_t)H * W * 2;
+    return 2 * (int64_t)H * W * 16 + 2 * vol + (int64_t)H * W * 2;
 }
 extern "C" int64_t svb_sgbm_scratch_bytes(int F, int H, int W, int num_disparities) {
     if (F < 1 || num_disparities != SG_D || W <= SG_D) return 0;
@@ -446,8 +468,8 @@ extern "C" int svb_sgbm_compute(const uint8_t *grayL, const uint8_t *grayR, int 
     for (int f0 = 0; f0 < F; f0 += fc) {
         int n = F - f0 < fc ? F - f0 : fc;
         int64_t vol = (int64_t)n * H * w1 * SG_D * 2;
-        uint32_t *planes = (uint32_t *)base;
-        uint32_t *hs = (uint32_t *)(base + 6 * (int64_t)n * H * W * 4);
+        uint4 *recs = (uint4 *)base;
+        uint32_t *hs = (uint32_t *)(base + 2 * (int64_t)n * H * W * 16);
         uint32_t *Cv = (uint32_t *)((char *)hs + vol);
         int16_t *raw = (int16_t *)((char *)Cv + vol);
         const uint8_t *L = grayL + (int64_t)f0 * H * W, *R = grayR + (int64_t)f0 * H * W;
@@ -455,11 +477,9 @@ extern "C" int svb_sgbm_compute(const uint8_t *grayL, const uint8_t *grayR, int 
         uint2 *S2 = (uint2 *)hs;
         const unsigned diag_blocks = (unsigned)(((int64_t)n * (w1 + H - 1) + 7) / 8);
         { ProfScope ps(K_SGBM_PREFILTER, st);
-          sgbm_prefilter_kernel<<<grid_for(2 * (int64_t)n * H * W, 256), 256, 0, st>>>(L, R, n, H, W, planes); }
+          sgbm_prefilter_kernel<<<grid_for(2 * (int64_t)n * H * W, 256), 256, 0, st>>>(L, R, n, H, W, recs); }
         { ProfScope ps(K_SGBM_HSUM, st);
-          int ncol = SG_TX + 2 * SW2;
-          size_t smem = ((size_t)ncol * 64 + 3 * ncol + 3 * (ncol + SG_D)) * 4;
-          sgbm_hsum_kernel<<<dim3((w1 + SG_TX - 1) / SG_TX, H, n), 256, smem, st>>>(planes, n, H, W, SW2, hs); }
+          sgbm_hsum_kernel<<<(unsigned)(((int64_t)n * H + 3) / 4), 256, 0, st>>>(recs, n, H, W, SW2, hs); }
         { ProfScope ps(K_SGBM_VSUM, st);
           int seg = 68;
           sgbm_vsum_kernel<<<dim3((unsigned)(((int64_t)w1 * 64 + 255) / 256), (H + seg - 1) / seg, n), 256, 0, st>>>(hs, H, w1, SW2, seg, Cv); }
@@ -472,7 +492,7 @@ extern "C" int svb_sgbm_compute(const uint8_t *grayL, const uint8_t *grayR, int 
           sgbm_path_kernel<0><<<(unsigned)(((int64_t)n * H + 7) / 8), 256, 0, st>>>(C2, S2, n, H, w1); }
         SVB_LAUNCH_CHECK();
         { ProfScope ps(K_SGBM_FINAL, st);
-          sgbm_final_kernel<<<(unsigned)(((int64_t)n * H + 3) / 4), 128, (size_t)4 * 3 * W * 2, st>>>(C2, S2, n, H, W, raw); }
+          sgbm_final_kernel<<<(unsigned)(((int64_t)n * H + 3) / 4), 128, (size_t)4 * W * 6, st>>>(C2, S2, n, H, W, raw); }
         { ProfScope ps(K_SGBM_MEDIAN, st);
           sgbm_median3_kernel<<<grid_for((int64_t)n * H * W, 256), 256, 0, st>>>(raw, n, H, W, disp16 + (int64_t)f0 * H * W); }
         SVB_LAUNCH_CHECK();
