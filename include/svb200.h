@@ -338,8 +338,6 @@ int svb_debug_force_two_pass(int on);
 int svb_debug_clean_bands(int bands);
 /* tuning hook: pixels per thread on lattice / odd rows of the balanced fill kernel (0 = default) */
 int svb_debug_fill_split(int mode);
-/* test hook: 1 = four path directions of the matcher in one raster kernel (slower, see svb_sgbm.cu), 0 (default) = one kernel per direction */
-int svb_debug_sgbm_fused(int on);
 int svb_profile_kernels(void);
 int svb_profile_get(int id, char *name, int name_cap, double *ms_total, int *launches);
 

@@ -99,7 +99,6 @@ SIGNATURES = {
     "svb_debug_force_two_pass": (I, [I]),
     "svb_debug_clean_bands": (I, [I]),
     "svb_debug_fill_split": (I, [I]),
-    "svb_debug_sgbm_fused": (I, [I]),
     "svb_profile_kernels": (I, []),
     "svb_profile_get": (I, [I, C.c_char_p, I, C.POINTER(D), C.POINTER(I)]),
 }

@@ -37,7 +37,7 @@ static const char *k_names[K_COUNT_] = {
     "scatter_points", "road_pass1", "road_pass2", "road_clear", "road_cluster", "road_table", "road_near", "road_scatter",
     "clean_band", "pack_mask", "mask_points", "road_sites", "road_sites_scatter",
     "prep_gamma_gray", "prep_equalize_lut", "prep_apply_lut", "fill_row_mean", "normal_line", "road_hull", "hull_masks",
-    "sgbm_prefilter", "sgbm_hsum", "sgbm_vsum", "sgbm_path_v", "sgbm_path_d1", "sgbm_path_d3", "sgbm_path_h", "sgbm_raster", "sgbm_final",
+    "sgbm_prefilter", "sgbm_hsum", "sgbm_vsum", "sgbm_path_v", "sgbm_path_d1", "sgbm_path_d3", "sgbm_path_h", "sgbm_final",
     "sgbm_median", "speckle", "disparity_scale"};
 struct EvPair { int id; cudaEvent_t a, b; };
 static std::vector<EvPair> g_events;

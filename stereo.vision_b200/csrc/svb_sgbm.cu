@@ -11,8 +11,8 @@
 // [frame][y][x1][d] int16 (x1 = x - D; 256 B per pixel at D = 128):
 //   hsum  horizontal block sums of the Birchfield-Tomasi pixel costs          (sgbm_hsum)
 //   C     block costs = vertical running sum of hsum                            (sgbm_vsum)
-//   S     sum of the path costs, saturating int16 adds (aliases hsum)           (sgbm_path<dir>)
-// The right-to-left kernel does not write S: it adds its own L, finds the winner, refines it, scatters the
+//   E     per direction the excess L_r - C in [0, P2], 4 bits each (aliases hsum) (sgbm_path<dir>)
+// The right-to-left kernel rebuilds S = 5 C + excesses with its own L, finds the winner, refines it, scatters the
 // right-view disparity for the left-right check and emits the row (sgbm_final).  All integer; results are
 // bit-identical to cv2 4.13 through the oracle (oracle/sgbm_oracle.c) as long as no block cost exceeds
 // 32767 - P2 (OpenCV's own int16 stores wrap or saturate beyond that depending on its SIMD path).
@@ -183,10 +183,20 @@ __device__ __forceinline__ void path_step(PathState &s, uint2 cw, int lane) {
     s.l0 = n0; s.l1 = n1; s.l2 = n2; s.l3 = n3; s.mn = m;
 }
 
-// DIR 0: rows, left to right (RMW S).  DIR 1: from (x-1, y-1).  DIR 2: from (x, y-1), first writer of S.
-// DIR 3: from (x+1, y-1).  One warp per path; 8 warps per CTA.
+// L_r - C lies in [0, P2] (the minimum term is at least min L and at most min L + P2), so a direction does not
+// have to accumulate a 16-bit S volume: it leaves its four 4-bit excesses per lane as one uint16 (a quarter of a
+// volume, written once, never read back by another direction) and the final kernel rebuilds
+// S = 5 C + sum of the excesses.  Saturating the total once equals OpenCV's chain of saturating adds because all
+// terms have one sign.
+__device__ __forceinline__ uint32_t excess4(const PathState &s, uint2 cw) {
+    int c0, c1, c2, c3;
+    unpack4(cw, c0, c1, c2, c3);
+    return (uint32_t)(s.l0 - c0) | ((uint32_t)(s.l1 - c1) << 4) | ((uint32_t)(s.l2 - c2) << 8) | ((uint32_t)(s.l3 - c3) << 12);
+}
+// DIR 0: rows, left to right.  DIR 1: from (x-1, y-1).  DIR 2: from (x, y-1).  DIR 3: from (x+1, y-1).
+// One warp per path; 8 warps per CTA.  E: this direction's excess plane [frame][y][x1][lane] uint16.
 template <int DIR>
-__global__ void __launch_bounds__(256) sgbm_path_kernel(const uint2 *__restrict__ C, uint2 *__restrict__ S, int F, int H, int w1) {
+__global__ void __launch_bounds__(256) sgbm_path_kernel(const uint2 *__restrict__ C, uint16_t *__restrict__ E, int F, int H, int w1) {
     const int lane = threadIdx.x & 31;
     const int npaths = DIR == 0 ? H : DIR == 2 ? w1 : w1 + H - 1;
     int64_t wid = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
@@ -202,149 +212,26 @@ __global__ void __launch_bounds__(256) sgbm_path_kernel(const uint2 *__restrict_
     else if (DIR == 2) len = H;
     else if (DIR == 1) len = min(w1 - x, H - y);
     else len = min(x + 1, H - y);
-    const int64_t stride = ((int64_t)dy * w1 + dx) * 32;                     // in uint2 (4 disparities) units
+    const int64_t stride = ((int64_t)dy * w1 + dx) * 32;                     // in lanes (4 disparities each)
     int64_t idx = (((int64_t)f * H + y) * w1 + x) * 32 + lane;
     PathState s = {0, 0, 0, 0, 0};
     int i = 0;
-    for (; i + 4 <= len; i += 4) {
-        uint2 c[4], sv[4];
+    for (; i + 8 <= len; i += 8) {
+        uint2 c[8];
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            c[k] = __ldg(C + idx + k * stride);
-            if (DIR != 2) sv[k] = S[idx + k * stride];
-        }
+        for (int k = 0; k < 8; ++k) c[k] = __ldg(C + idx + k * stride);
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
+        for (int k = 0; k < 8; ++k) {
             path_step(s, c[k], lane);
-            uint2 l = pack4(s.l0, s.l1, s.l2, s.l3);
-            if (DIR != 2) { l.x = __vaddss2(sv[k].x, l.x); l.y = __vaddss2(sv[k].y, l.y); }
-            S[idx + k * stride] = l;
+            E[idx + k * stride] = (uint16_t)excess4(s, c[k]);
         }
-        idx += 4 * stride;
+        idx += 8 * stride;
     }
     for (; i < len; ++i) {
         uint2 c = __ldg(C + idx);
         path_step(s, c, lane);
-        uint2 l = pack4(s.l0, s.l1, s.l2, s.l3);
-        if (DIR != 2) { uint2 sv = S[idx]; l.x = __vaddss2(sv.x, l.x); l.y = __vaddss2(sv.y, l.y); }
-        S[idx] = l;
+        E[idx] = (uint16_t)excess4(s, c);
         idx += stride;
-    }
-}
-
-// ------------------------------------------------------------------ four directions in one raster pass
-// DIR 0 (from the left), 1, 2, 3 (from the row above) together, i.e. everything OpenCV's forward sweep computes:
-// C is read once and S written once (2 volume passes instead of 11).  A CTA owns a band of SG_RB rows, one warp per
-// row, and walks the columns with the rows skewed by two steps (row r is at column t - 2r at step t), so that the
-// row above has always finished column x + 1.  A warp keeps its left-to-right state in registers and leaves its
-// L_1, L_2, L_3 of the last four columns in shared memory for the row below (one barrier per step).  The last row
-// of a band writes them to global memory for the band below and publishes its progress every 8 columns
-// (release / acquire on a per-band column counter); bands of a frame are launched top to bottom, so the band below
-// trails by about 2*SG_RB columns and only waits while the pipeline fills.  Every wait is bounded (err flag).
-// MEASURED (8 frames in flight): 489 us per frame against 248 us for the four per-direction kernels -- the last
-// band of a frame starts 2*H steps after the first (all frames of a launch fill and drain together: 45 % duty) and
-// a step costs 3.7 us with one barrier per column.  Kept behind svb_debug_sgbm_fused(1) and in the tests; not the
-// default.
-constexpr int SG_RB = 16;
-__device__ __forceinline__ int ld_acquire(const int *p) {
-    int v;
-    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ void st_release(int *p, int v) {
-    asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-// `seen` caches the last counter value read (warp-uniform), so the counter is only polled when it matters
-__device__ __forceinline__ void wait_cols(const int *flag, int need, int &seen, int *err, int lane) {
-    if (seen >= need) return;
-    int v = 0;
-    if (lane == 0) {
-        int spins = 0;
-        while ((v = ld_acquire(flag)) < need) {
-            if (++spins > (1 << 22) || ((spins & 1023) == 0 && *(volatile int *)err)) { *(volatile int *)err = 1; v = 1 << 30; break; }
-        }
-    }
-    seen = __shfl_sync(SG_FULL, v, 0);
-}
-__global__ void __launch_bounds__(SG_RB * 32) sgbm_raster_kernel(const uint2 *__restrict__ C, uint2 *__restrict__ S, int F, int H, int w1,
-                                                                 int nbands, uint2 *xrow, int *xmn, int *flags, int *err) {
-    __shared__ uint2 shL[SG_RB - 1][3][4][32];      // [row of the band, but its last][L_1, L_2, L_3][column & 3][lane]
-    __shared__ int shM[SG_RB - 1][3][4];
-    const int lane = threadIdx.x & 31, r = threadIdx.x >> 5;
-    const int f = blockIdx.x / nbands, band = blockIdx.x - f * nbands;
-    const int y = band * SG_RB + r;
-    const bool live = y < H;
-    const int64_t fb = (int64_t)f * nbands + band;
-    uint2 *my_row = xrow + fb * 3 * (int64_t)w1 * 32;        // [dir][col][lane], written by the band's last row
-    int *my_mn = xmn + fb * 3 * (int64_t)w1;
-    const uint2 *up_row = my_row - 3 * (int64_t)w1 * 32;     // the band above
-    const int *up_mn = my_mn - 3 * (int64_t)w1;
-    const bool from_global = r == 0 && band > 0;
-    const bool publish = r == SG_RB - 1 && band < nbands - 1;
-    PathState h = {0, 0, 0, 0, 0};
-    int64_t idx = ((int64_t)f * H + (live ? y : 0)) * w1 * 32 + lane;       // column 0 of the row
-    uint2 c0 = make_uint2(0, 0), c1 = make_uint2(0, 0);
-    if (live) { c0 = __ldg(C + idx); if (w1 > 1) c1 = __ldg(C + idx + 32); }
-    // next step's vectors of the band above (edge warp only), loaded one step ahead
-    uint2 ga = make_uint2(0, 0), gv = ga, gb = ga;
-    int gm = 0, seen = 0;                                      // lane 0,1,2: min of L_1(x-1), L_2(x), L_3(x+1)
-    if (from_global) {
-        wait_cols(flags + fb - 1, min(2, w1), seen, err, lane);
-        gv = __ldcg(up_row + ((int64_t)1 * w1 + 0) * 32 + lane);
-        if (w1 > 1) gb = __ldcg(up_row + ((int64_t)2 * w1 + 1) * 32 + lane);
-        if (lane == 1) gm = __ldcg(up_mn + w1);
-        if (lane == 2 && w1 > 1) gm = __ldcg(up_mn + 2 * w1 + 1);
-    }
-    const int steps = w1 + 2 * (SG_RB - 1);
-    for (int t = 0; t < steps; ++t) {
-        const int x = t - 2 * r;
-        if (live && x >= 0 && x < w1) {
-            uint2 c = c0;
-            c0 = c1;
-            if (x + 2 < w1) c1 = __ldg(C + idx + 64);
-            PathState a = {0, 0, 0, 0, 0}, v = {0, 0, 0, 0, 0}, b = {0, 0, 0, 0, 0};
-            if (from_global) {
-                unpack4(ga, a.l0, a.l1, a.l2, a.l3); unpack4(gv, v.l0, v.l1, v.l2, v.l3); unpack4(gb, b.l0, b.l1, b.l2, b.l3);
-                a.mn = __shfl_sync(SG_FULL, gm, 0); v.mn = __shfl_sync(SG_FULL, gm, 1); b.mn = __shfl_sync(SG_FULL, gm, 2);
-                if (x + 1 < w1) {                              // vectors for column x + 1: L_1(x), L_2(x+1), L_3(x+2)
-                    wait_cols(flags + fb - 1, min(x + 3, w1), seen, err, lane);
-                    ga = __ldcg(up_row + ((int64_t)0 * w1 + x) * 32 + lane);
-                    gv = __ldcg(up_row + ((int64_t)1 * w1 + x + 1) * 32 + lane);
-                    gb = x + 2 < w1 ? __ldcg(up_row + ((int64_t)2 * w1 + x + 2) * 32 + lane) : make_uint2(0, 0);
-                    gm = 0;
-                    if (lane == 0) gm = __ldcg(up_mn + x);
-                    if (lane == 1) gm = __ldcg(up_mn + w1 + x + 1);
-                    if (lane == 2 && x + 2 < w1) gm = __ldcg(up_mn + 2 * w1 + x + 2);
-                }
-            } else if (r > 0) {
-                if (x > 0) { unpack4(shL[r - 1][0][(x - 1) & 3][lane], a.l0, a.l1, a.l2, a.l3); a.mn = shM[r - 1][0][(x - 1) & 3]; }
-                unpack4(shL[r - 1][1][x & 3][lane], v.l0, v.l1, v.l2, v.l3); v.mn = shM[r - 1][1][x & 3];
-                if (x + 1 < w1) { unpack4(shL[r - 1][2][(x + 1) & 3][lane], b.l0, b.l1, b.l2, b.l3); b.mn = shM[r - 1][2][(x + 1) & 3]; }
-            }
-            path_step(h, c, lane);
-            path_step(a, c, lane);
-            path_step(v, c, lane);
-            path_step(b, c, lane);
-            uint2 ph = pack4(h.l0, h.l1, h.l2, h.l3), pa = pack4(a.l0, a.l1, a.l2, a.l3);
-            uint2 pv = pack4(v.l0, v.l1, v.l2, v.l3), pb = pack4(b.l0, b.l1, b.l2, b.l3);
-            S[idx] = make_uint2(__vaddss2(__vaddss2(ph.x, pa.x), __vaddss2(pv.x, pb.x)), __vaddss2(__vaddss2(ph.y, pa.y), __vaddss2(pv.y, pb.y)));
-            if (publish) {
-                my_row[((int64_t)0 * w1 + x) * 32 + lane] = pa;
-                my_row[((int64_t)1 * w1 + x) * 32 + lane] = pv;
-                my_row[((int64_t)2 * w1 + x) * 32 + lane] = pb;
-                if (lane == 0) { my_mn[x] = a.mn; my_mn[w1 + x] = v.mn; my_mn[2 * w1 + x] = b.mn; }
-                if ((x & 7) == 7 || x == w1 - 1) {
-                    __threadfence();
-                    __syncwarp();
-                    if (lane == 0) st_release(flags + fb, x + 1);
-                }
-            } else if (r < SG_RB - 1) {
-                shL[r][0][x & 3][lane] = pa; shL[r][1][x & 3][lane] = pv; shL[r][2][x & 3][lane] = pb;
-                if (lane == 0) { shM[r][0][x & 3] = a.mn; shM[r][1][x & 3] = v.mn; shM[r][2][x & 3] = b.mn; }
-            }
-            idx += 32;
-        }
-        __syncthreads();
     }
 }
 
@@ -353,8 +240,13 @@ __global__ void __launch_bounds__(SG_RB * 32) sgbm_raster_kernel(const uint2 *__
 // minimum); lane (x1 & 31) keeps that result and every 32 steps the lanes finish their columns in parallel:
 // sub-pixel division, disp1, and the right-view entry disp2[x - d] = d where min S is smallest (first visited,
 // i.e. largest x, on ties) as one shared-memory atomicMin on (min S, -x).  Per warp: W x (uint32 + int16).
-__global__ void __launch_bounds__(128) sgbm_final_kernel(const uint2 *__restrict__ C, const uint2 *__restrict__ S, int F, int H, int W,
-                                                         int16_t *__restrict__ disp) {
+// nibbles of a uint16 (each at most 10 here) to the bytes of a word
+__device__ __forceinline__ uint32_t nib2bytes(uint32_t w) {
+    uint32_t t = (w | (w << 8)) & 0x00ff00ffu;
+    return (t | (t << 4)) & 0x0f0f0f0fu;
+}
+__global__ void __launch_bounds__(128) sgbm_final_kernel(const uint2 *__restrict__ C, const uint16_t *__restrict__ E, int64_t plane, int F, int H,
+                                                         int W, int16_t *__restrict__ disp) {
     extern __shared__ uint32_t sh32[];
     const int w1 = W - SG_D;
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
@@ -366,18 +258,28 @@ __global__ void __launch_bounds__(128) sgbm_final_kernel(const uint2 *__restrict
     __syncwarp();
     int64_t idx = (wid * w1 + (w1 - 1)) * 32 + lane;
     PathState s = {0, 0, 0, 0, 0};
-    uint2 cn = __ldg(C + idx), sn = __ldg(S + idx);
+    uint2 cn = __ldg(C + idx);
+    uint32_t en01 = (uint32_t)__ldg(E + idx) + __ldg(E + plane + idx), en23 = (uint32_t)__ldg(E + 2 * plane + idx) + __ldg(E + 3 * plane + idx);
     uint32_t mykey = 0xffffffffu;
     int mylo = 0, myhi = 0;
     for (int x1 = w1 - 1; x1 >= 0; --x1) {
-        uint2 c = cn, sv = sn;
-        if (x1 > 0) { cn = __ldg(C + idx - 32); sn = __ldg(S + idx - 32); }
+        uint2 c = cn;
+        uint32_t e01 = en01, e23 = en23;
+        if (x1 > 0) {
+            cn = __ldg(C + idx - 32);
+            en01 = (uint32_t)__ldg(E + idx - 32) + __ldg(E + plane + idx - 32);          // nibbles <= 5 each: no carry
+            en23 = (uint32_t)__ldg(E + 2 * plane + idx - 32) + __ldg(E + 3 * plane + idx - 32);
+        }
         idx -= 32;
         path_step(s, c, lane);
+        // S = 4 C + the four directions' excesses + this direction's L, saturated once
+        uint32_t eb = nib2bytes(e01) + nib2bytes(e23);
         int a0, a1, a2, a3;
-        unpack4(sv, a0, a1, a2, a3);
-        a0 = max(min(a0 + s.l0, SG_MAXC), -32768); a1 = max(min(a1 + s.l1, SG_MAXC), -32768);
-        a2 = max(min(a2 + s.l2, SG_MAXC), -32768); a3 = max(min(a3 + s.l3, SG_MAXC), -32768);
+        unpack4(c, a0, a1, a2, a3);
+        a0 = 4 * a0 + (int)(eb & 0xffu) + s.l0; a1 = 4 * a1 + (int)((eb >> 8) & 0xffu) + s.l1;
+        a2 = 4 * a2 + (int)((eb >> 16) & 0xffu) + s.l2; a3 = 4 * a3 + (int)(eb >> 24) + s.l3;
+        a0 = max(min(a0, SG_MAXC), -32768); a1 = max(min(a1, SG_MAXC), -32768);
+        a2 = max(min(a2, SG_MAXC), -32768); a3 = max(min(a3, SG_MAXC), -32768);
         // first minimum over ascending d: key = (S + 32768) << 8 | d
         uint32_t k0 = ((uint32_t)(a0 + 32768) << 8) | (uint32_t)(4 * lane);
         uint32_t k1 = ((uint32_t)(a1 + 32768) << 8) | (uint32_t)(4 * lane + 1);
@@ -550,12 +452,9 @@ int grid_for(int64_t n, int threads) {
     return (int)(b < 1 ? 1 : (b > 148 * 32 ? 148 * 32 : b));
 }
 
-bool g_sgbm_fused_down = false;      // the raster kernel is correct but slower than one kernel per direction
-
 }  // namespace
 
 // ------------------------------------------------------------------ C ABI
-extern "C" int svb_debug_sgbm_fused(int on) { g_sgbm_fused_down = on != 0; return SVB_OK; }
 
 extern "C" int svb_sgbm_supported(int H, int W, int num_disparities, int block) {
     return (num_disparities == SG_D && block >= 1 && block <= 31 && (block & 1) && H >= 1 && H <= SVB_MAX_DIM && W <= SVB_MAX_DIM &&
@@ -566,9 +465,7 @@ extern "C" int svb_sgbm_supported(int H, int W, int num_disparities, int block) 
 static int64_t sgbm_frame_bytes(int H, int W) {
     int64_t w1 = W - SG_D;
     int64_t vol = (int64_t)H * w1 * SG_D * 2;
-    int64_t nb = (H + SG_RB - 1) / SG_RB;
-    int64_t xch = nb * (3 * w1 * (32 * 8 + 4) + 4) + 512;                 // rows handed from band to band, their minima, column counters
-    return 2 * (int64_t)H * W * 16 + 2 * vol + (int64_t)H * W * 2 + ((xch + 255) & ~(int64_t)255);
+    return 2 * (int64_t)H * W * 16 + 2 * vol + (int64_t)H * W * 2;
 }
 extern "C" int64_t svb_sgbm_scratch_bytes(int F, int H, int W, int num_disparities) {
     if (F < 1 || num_disparities != SG_D || W <= SG_D) return 0;
@@ -594,15 +491,10 @@ extern "C" int svb_sgbm_compute(const uint8_t *grayL, const uint8_t *grayR, int 
         uint32_t *hs = (uint32_t *)(base + 2 * (int64_t)n * H * W * 16);
         uint32_t *Cv = (uint32_t *)((char *)hs + vol);
         int16_t *raw = (int16_t *)((char *)Cv + vol);
-        const int nb = (H + SG_RB - 1) / SG_RB;
-        char *xch = (char *)raw + (((int64_t)n * H * W * 2 + 255) & ~(int64_t)255);
-        uint2 *xrow = (uint2 *)xch;
-        int *xmn = (int *)(xch + (int64_t)n * nb * 3 * w1 * 32 * 8);
-        int *xflags = xmn + (int64_t)n * nb * 3 * w1;
-        int *xerr = xflags + (int64_t)n * nb;
         const uint8_t *L = grayL + (int64_t)f0 * H * W, *R = grayR + (int64_t)f0 * H * W;
         const uint2 *C2 = (const uint2 *)Cv;
-        uint2 *S2 = (uint2 *)hs;
+        uint16_t *E = (uint16_t *)hs;                          // four excess planes of a quarter volume each, over the dead hsum
+        const int64_t plane = (int64_t)n * H * w1 * 32;
         const unsigned diag_blocks = (unsigned)(((int64_t)n * (w1 + H - 1) + 7) / 8);
         { ProfScope ps(K_SGBM_PREFILTER, st);
           sgbm_prefilter_kernel<<<grid_for(2 * (int64_t)n * H * W, 256), 256, 0, st>>>(L, R, n, H, W, recs); }
@@ -612,21 +504,15 @@ extern "C" int svb_sgbm_compute(const uint8_t *grayL, const uint8_t *grayR, int 
           int seg = 68;
           sgbm_vsum_kernel<<<dim3((unsigned)(((int64_t)w1 * 64 + 255) / 256), (H + seg - 1) / seg, n), 256, 0, st>>>(hs, H, w1, SW2, seg, Cv); }
         SVB_LAUNCH_CHECK();
-        if (g_sgbm_fused_down) {
-            ProfScope ps(K_SGBM_PATH_DOWN, st);
-            cudaMemsetAsync(xflags, 0, ((int64_t)n * nb + 1) * 4, st);
-            sgbm_raster_kernel<<<(unsigned)(n * nb), SG_RB * 32, 0, st>>>(C2, S2, n, H, w1, nb, xrow, xmn, xflags, xerr);
-        } else {
-            { ProfScope ps(K_SGBM_PATH_V, st);
-              sgbm_path_kernel<2><<<(unsigned)(((int64_t)n * w1 + 7) / 8), 256, 0, st>>>(C2, S2, n, H, w1); }
-            { ProfScope ps(K_SGBM_PATH_D1, st); sgbm_path_kernel<1><<<diag_blocks, 256, 0, st>>>(C2, S2, n, H, w1); }
-            { ProfScope ps(K_SGBM_PATH_D3, st); sgbm_path_kernel<3><<<diag_blocks, 256, 0, st>>>(C2, S2, n, H, w1); }
-            { ProfScope ps(K_SGBM_PATH_H, st);
-              sgbm_path_kernel<0><<<(unsigned)(((int64_t)n * H + 7) / 8), 256, 0, st>>>(C2, S2, n, H, w1); }
-        }
+        { ProfScope ps(K_SGBM_PATH_V, st);
+          sgbm_path_kernel<2><<<(unsigned)(((int64_t)n * w1 + 7) / 8), 256, 0, st>>>(C2, E + 0 * plane, n, H, w1); }
+        { ProfScope ps(K_SGBM_PATH_D1, st); sgbm_path_kernel<1><<<diag_blocks, 256, 0, st>>>(C2, E + 1 * plane, n, H, w1); }
+        { ProfScope ps(K_SGBM_PATH_D3, st); sgbm_path_kernel<3><<<diag_blocks, 256, 0, st>>>(C2, E + 2 * plane, n, H, w1); }
+        { ProfScope ps(K_SGBM_PATH_H, st);
+          sgbm_path_kernel<0><<<(unsigned)(((int64_t)n * H + 7) / 8), 256, 0, st>>>(C2, E + 3 * plane, n, H, w1); }
         SVB_LAUNCH_CHECK();
         { ProfScope ps(K_SGBM_FINAL, st);
-          sgbm_final_kernel<<<(unsigned)(((int64_t)n * H + 3) / 4), 128, (size_t)4 * W * 6, st>>>(C2, S2, n, H, W, raw); }
+          sgbm_final_kernel<<<(unsigned)(((int64_t)n * H + 3) / 4), 128, (size_t)4 * W * 6, st>>>(C2, E, plane, n, H, W, raw); }
         { ProfScope ps(K_SGBM_MEDIAN, st);
           sgbm_median3_kernel<<<grid_for((int64_t)n * H * W, 256), 256, 0, st>>>(raw, n, H, W, disp16 + (int64_t)f0 * H * W); }
         SVB_LAUNCH_CHECK();

@@ -81,24 +81,6 @@ def test_block_sizes_against_oracle(cuda, block):
     assert np.array_equal(got, want)
 
 
-def test_fused_and_separate_path_kernels_agree(cuda):
-    """the raster kernel (four directions in one pass, test hook) against one kernel per direction, on a full-size
-    pair, heights that leave a partial row band, and a batch"""
-    lib = N.load()
-    for shape, F in [((544, 1024), 1), ((120, 400), 3), ((77, 333), 2), ((3, 300), 1)]:
-        big = shape if shape[0] >= 120 else (120, 400)
-        pairs = [synth.make_stereo_pair(4, t, big) for t in range(F)]
-        L = np.stack([np.ascontiguousarray(p[0][:shape[0], :shape[1]]) for p in pairs])
-        R = np.stack([np.ascontiguousarray(p[1][:shape[0], :shape[1]]) for p in pairs])
-        want = gpu_compute(cuda, L, R)
-        try:
-            N.check(lib.svb_debug_sgbm_fused(1), "hook")
-            got = gpu_compute(cuda, L, R)
-        finally:
-            N.check(lib.svb_debug_sgbm_fused(0), "hook")
-        assert np.array_equal(got, want), shape
-
-
 def test_batch_in_chunks(cuda):
     """five pairs with room for two frames of cost volume: three chunks, every frame equal to its single run"""
     pairs = [synth.make_stereo_pair(9, t, (120, 400)) for t in range(5)]
