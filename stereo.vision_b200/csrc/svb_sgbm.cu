@@ -256,30 +256,26 @@ __global__ void __launch_bounds__(128) sgbm_final_kernel(const uint2 *__restrict
     int16_t *d1 = (int16_t *)(sh32 + (size_t)4 * W) + (size_t)wib * W;
     for (int x = lane; x < W; x += 32) { d1[x] = -16; d2k[x] = 0xffffffffu; }
     __syncwarp();
-    int64_t idx = (wid * w1 + (w1 - 1)) * 32 + lane;
     PathState s = {0, 0, 0, 0, 0};
-    uint2 cn = __ldg(C + idx);
-    uint32_t en01 = (uint32_t)__ldg(E + idx) + __ldg(E + plane + idx), en23 = (uint32_t)__ldg(E + 2 * plane + idx) + __ldg(E + 3 * plane + idx);
     uint32_t mykey = 0xffffffffu;
     int mylo = 0, myhi = 0;
-    for (int x1 = w1 - 1; x1 >= 0; --x1) {
-        uint2 c = cn;
-        uint32_t e01 = en01, e23 = en23;
-        if (x1 > 0) {
-            cn = __ldg(C + idx - 32);
-            en01 = (uint32_t)__ldg(E + idx - 32) + __ldg(E + plane + idx - 32);          // nibbles <= 5 each: no carry
-            en23 = (uint32_t)__ldg(E + 2 * plane + idx - 32) + __ldg(E + 3 * plane + idx - 32);
-        }
-        idx -= 32;
+    const int64_t rowbase = wid * w1 * 32 + lane;
+    // loads of one column: C and the pairwise sums of the four excess words (nibbles <= 5 each: no carry)
+    auto fetch = [&](int col, uint2 &c, uint32_t &e01, uint32_t &e23) {
+        int64_t i = rowbase + (int64_t)col * 32;
+        c = __ldg(C + i);
+        e01 = (uint32_t)__ldg(E + i) + __ldg(E + plane + i);
+        e23 = (uint32_t)__ldg(E + 2 * plane + i) + __ldg(E + 3 * plane + i);
+    };
+    auto step = [&](int x1, uint2 c, uint32_t e01, uint32_t e23) {
         path_step(s, c, lane);
         // S = 4 C + the four directions' excesses + this direction's L, saturated once
         uint32_t eb = nib2bytes(e01) + nib2bytes(e23);
         int a0, a1, a2, a3;
         unpack4(c, a0, a1, a2, a3);
-        a0 = 4 * a0 + (int)(eb & 0xffu) + s.l0; a1 = 4 * a1 + (int)((eb >> 8) & 0xffu) + s.l1;
-        a2 = 4 * a2 + (int)((eb >> 16) & 0xffu) + s.l2; a3 = 4 * a3 + (int)(eb >> 24) + s.l3;
-        a0 = max(min(a0, SG_MAXC), -32768); a1 = max(min(a1, SG_MAXC), -32768);
-        a2 = max(min(a2, SG_MAXC), -32768); a3 = max(min(a3, SG_MAXC), -32768);
+        a0 = min(4 * a0 + (int)(eb & 0xffu) + s.l0, SG_MAXC); a1 = min(4 * a1 + (int)((eb >> 8) & 0xffu) + s.l1, SG_MAXC);
+        a2 = min(4 * a2 + (int)((eb >> 16) & 0xffu) + s.l2, SG_MAXC); a3 = min(4 * a3 + (int)(eb >> 24) + s.l3, SG_MAXC);
+        a0 = max(a0, -32768); a1 = max(a1, -32768); a2 = max(a2, -32768); a3 = max(a3, -32768);
         // first minimum over ascending d: key = (S + 32768) << 8 | d
         uint32_t k0 = ((uint32_t)(a0 + 32768) << 8) | (uint32_t)(4 * lane);
         uint32_t k1 = ((uint32_t)(a1 + 32768) << 8) | (uint32_t)(4 * lane + 1);
@@ -308,6 +304,31 @@ __global__ void __launch_bounds__(128) sgbm_final_kernel(const uint2 *__restrict
             }
             mykey = 0xffffffffu;
         }
+    };
+    constexpr int G = 8;                                    // columns whose loads are in flight while a group is computed
+    int x1 = w1 - 1;
+    for (int k = w1 % G; k > 0; --k, --x1) {               // leading remainder, one column at a time
+        uint2 c; uint32_t e01, e23;
+        fetch(x1, c, e01, e23);
+        step(x1, c, e01, e23);
+    }
+    uint2 cA[G], cB[G];
+    uint32_t pA[G], qA[G], pB[G], qB[G];
+    if (x1 >= 0) {
+#pragma unroll
+        for (int k = 0; k < G; ++k) fetch(x1 - k, cA[k], pA[k], qA[k]);
+    }
+    while (x1 >= 0) {
+        const bool more = x1 - G >= 0;
+        if (more) {
+#pragma unroll
+            for (int k = 0; k < G; ++k) fetch(x1 - G - k, cB[k], pB[k], qB[k]);
+        }
+#pragma unroll
+        for (int k = 0; k < G; ++k) step(x1 - k, cA[k], pA[k], qA[k]);
+        x1 -= G;
+#pragma unroll
+        for (int k = 0; k < G; ++k) { cA[k] = cB[k]; pA[k] = pB[k]; qA[k] = qB[k]; }
     }
     __syncwarp();
     int16_t *out = disp + wid * W;
