@@ -533,6 +533,10 @@ extern "C" int svb_sgbm_compute(const uint8_t *grayL, const uint8_t *grayR, int 
           sgbm_path_kernel<0><<<(unsigned)(((int64_t)n * H + 7) / 8), 256, 0, st>>>(C2, E + 3 * plane, n, H, w1); }
         SVB_LAUNCH_CHECK();
         { ProfScope ps(K_SGBM_FINAL, st);
+          if ((size_t)4 * W * 6 > 48 * 1024) {              // wide frames: more than the default dynamic shared memory
+              cudaError_t e = cudaFuncSetAttribute(sgbm_final_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * W * 6);
+              if (e != cudaSuccess) return (int)e;
+          }
           sgbm_final_kernel<<<(unsigned)(((int64_t)n * H + 3) / 4), 128, (size_t)4 * W * 6, st>>>(C2, E, plane, n, H, W, raw); }
         { ProfScope ps(K_SGBM_MEDIAN, st);
           sgbm_median3_kernel<<<grid_for((int64_t)n * H * W, 256), 256, 0, st>>>(raw, n, H, W, disp16 + (int64_t)f0 * H * W); }

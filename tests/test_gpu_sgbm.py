@@ -81,6 +81,15 @@ def test_block_sizes_against_oracle(cuda, block):
     assert np.array_equal(got, want)
 
 
+def test_stress_frame_2048x1088(cuda):
+    """BASELINE config 5's frame size: one 2048x1088 pair (more shared memory per row than the default limit,
+    1.07 GB of cost volume) against the oracle"""
+    L, R = synth.make_stereo_pair(5, 0, (1088, 2048))
+    got = gpu_compute(cuda, L, R)[0]
+    assert np.array_equal(got, so.sgbm_compute(L, R))
+    assert np.array_equal(gpu_speckles(cuda, got, 0, 4000, 123)[0], so.filter_speckles(got.copy(), 0, 4000, 123))
+
+
 def test_batch_in_chunks(cuda):
     """five pairs with room for two frames of cost volume: three chunks, every frame equal to its single run"""
     pairs = [synth.make_stereo_pair(9, t, (120, 400)) for t in range(5)]
