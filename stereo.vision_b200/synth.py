@@ -142,3 +142,15 @@ def make_stereo_pair(seq: int, frame: int, shape=(544, 1024), camera: Camera = N
     glare = rng.integers(-2, 3, size=(H, W)).astype(np.int16)          # sensor noise on one view
     left = np.clip(left.astype(np.int16) + glare, 0, 255).astype(np.uint8)
     return np.ascontiguousarray(left), np.ascontiguousarray(right)
+
+
+def make_stereo_bgr(seq: int, frame: int, shape=(544, 1024), camera: Camera = None):
+    """Return (imgL, imgR) uint8 [H,W,3] BGR: `make_stereo_pair`'s views with a fixed tint (B+6, G+2, R-4), i.e. what
+    the frame orchestrator takes (stereovision.py:26) -- camera images before gamma correction and grey conversion.
+    A constant tint keeps the road's hue coherent, so most near-plane points survive the colour filter."""
+    gl, gr = make_stereo_pair(seq, frame, shape, camera)
+    tint = np.array([6, 2, -4], dtype=np.int16)[None, None, :]
+    out = []
+    for g in (gl, gr):
+        out.append(np.clip(g.astype(np.int16)[:, :, None] + tint, 0, 255).astype(np.uint8))
+    return np.ascontiguousarray(out[0]), np.ascontiguousarray(out[1])

@@ -82,6 +82,14 @@ def test_no_cpu_fallback():
         RoadPath()
     with pytest.raises(N.SvbError):
         f.projectDisparityTo3d(np.zeros((8, 8), np.uint8), 128)
+    from stereo.vision_b200.pipeline import Matcher
+    import stereo.vision_b200.stereovision as sv
+    with pytest.raises(N.SvbError):
+        Matcher()
+    with pytest.raises(N.SvbError):
+        f.disparity(np.zeros((40, 200), np.uint8), np.zeros((40, 200), np.uint8), 128, False)
+    with pytest.raises(N.SvbError):                    # the first stage already needs the device; nothing is swallowed before it
+        sv.performStereoVision(np.zeros((544, 1024, 3), np.uint8), np.zeros((544, 1024, 3), np.uint8), None, dict(sv.default_opts))
 
 
 def test_product_does_not_import_the_oracle():
@@ -91,3 +99,4 @@ def test_product_does_not_import_the_oracle():
             if fn.endswith((".py", ".cu", ".cuh")):
                 txt = open(os.path.join(dp, fn)).read()
                 assert "np_oracle" not in txt and "ref_harness" not in txt and "/root/reference" not in txt, fn
+                assert "sgbm_oracle" not in txt and "libsvb_oracle" not in txt, fn

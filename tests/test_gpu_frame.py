@@ -1,0 +1,50 @@
+"""GPU: whole frames.  stereo.vision_b200.stereovision.performStereoVision (the reference's stage sequence on the drop-in
+helpers, every stage on the GPU) against tests/golden/frames.npz, which oracle/make_golden_frame.py recorded from the
+UNMODIFIED reference orchestrator (stereovision.py:26-247) on three chained synthetic BGR stereo frames: matcher
+disparity, carried disparity, plane, point counts, road image, cleaned image and points, hull centre, normal line."""
+import os
+import random
+
+import numpy as np
+import pytest
+
+import stereo.vision_b200.stereovision as sv
+import stereo.vision_b200.synth as synth
+from test_oracle_golden import sha
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "frames.npz")
+
+
+def test_three_chained_frames(cuda):
+    with np.load(GOLD, allow_pickle=False) as z:
+        g = {k: z[k] for k in z.files}
+    seq = int(g["seq"])
+    opts = dict(sv.default_opts)
+    opts['loop'] = False
+    prev = None
+    for t in range(int(g["n_frames"])):
+        p = "f%d_" % t
+        imgL, imgR = synth.make_stereo_bgr(seq, t)
+        assert sha(imgL) + sha(imgR) == str(g[p + "in_sha"]), "synthetic input drifted"
+        random.seed(synth.ransac_seed(seq, t))
+        images, prev, normal = sv.performStereoVision(imgL.copy(), imgR.copy(), prev, opts)
+        st = images["stats"]
+        assert st["Frame"] == t + 1
+        assert sha(np.asarray(prev)) == str(g[p + "filled_sha"]), "filled disparity (matcher + temporal fill), frame %d" % t
+        assert bool(g[p + "has_plane"]) == (normal is not None)
+        np.testing.assert_allclose(np.asarray(normal, np.float64).reshape(3), g[p + "abc"], rtol=1e-9)
+        assert st["Planar Points Before"] == int(g[p + "near_n"]) and st["Planar Points After"] == int(g[p + "road_n"])
+        road = np.asarray(images["Road Image"])
+        assert int((road != 0).sum()) == int(g[p + "road_px"]) and sha(road) == str(g[p + "road_sha"])
+        cleaned = np.asarray(images["Filtered Road Image"])
+        assert sha(cleaned) == str(g[p + "cleaned_sha"]) and int((cleaned != 0).sum()) == int(g[p + "cleaned_pts"])
+        assert (st["Center Point X"], st["Center Point Y"]) == tuple(int(v) for v in g[p + "centre"])
+        assert tuple(images["Normal Line"]) == tuple(int(v) for v in g[p + "normal_line"])
+
+
+def test_first_frame_disparity_matches_matcher_fixture(cuda):
+    """frame 0 has no previous disparity: the carried disparity is the matcher's output itself"""
+    with np.load(GOLD, allow_pickle=False) as z:
+        g = {k: z[k] for k in z.files}
+    assert str(g["f0_disparity_sha"]) == str(g["f0_filled_sha"])
