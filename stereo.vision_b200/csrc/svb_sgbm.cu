@@ -14,7 +14,7 @@
 //   E     per direction the excess L_r - C in [0, P2], 4 bits each (aliases hsum) (sgbm_path<dir>)
 // The right-to-left kernel rebuilds S = 5 C + excesses with its own L, finds the winner, refines it, scatters the
 // right-view disparity for the left-right check and emits the row (sgbm_final).  All integer; results are
-// bit-identical to cv2 4.13 through the oracle (oracle/sgbm_oracle.c) as long as no block cost exceeds
+// bit-identical to cv2 4.13 (held by the parity tests) as long as no block cost exceeds
 // 32767 - P2 (OpenCV's own int16 stores wrap or saturate beyond that depending on its SIMD path).
 #include "svb_common.cuh"
 #include "svb_prof.cuh"
