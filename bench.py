@@ -325,6 +325,28 @@ def run_b200(args):
                                  "matches_gpu": bool(np.array_equal(want, d8[0].cpu().numpy()))}
         next_rows["f4_matcher"] = match
         del mt, gl, gr
+        # every row together: camera images -> front end -> matcher -> path -> cleaning -> obstacles (stereovision.py:44-189)
+        from stereo.vision_b200.pipeline import StereoPipeline
+        torch.cuda.empty_cache()
+        sp = StereoPipeline((H, W), max_frames=MF, trials=T, samples=S, step=args.step, carmask=cm, device=dev)
+        four = [synth.make_stereo_bgr(seed, t, (H, W)) for t in range(4)]
+        bl = torch.from_numpy(np.stack([four[t % 4][0] for t in range(MF)])).to(dev)
+        br = torch.from_numpy(np.stack([four[t % 4][1] for t in range(MF)])).to(dev)
+        sp.process(bl, br, seed=seed)
+        torch.cuda.synchronize()
+        m0.record()
+        for _ in range(3):
+            o = sp.process(bl, br, seed=seed)
+        m1.record()
+        torch.cuda.synchronize()
+        w_ms = m0.elapsed_time(m1) / 3
+        next_rows["whole_frame"] = {
+            "row": "stereovision.py:44-189 for %d chained frames resident in HBM: front end on both views, matcher, path, cleaning, "
+                   "obstacle stage (not part of `value`)" % MF,
+            "frames_per_s": round(MF / (w_ms * 1e-3), 1), "ms_per_frame": round(w_ms / MF, 4), "kernels": {},
+            "frames_with_plane": int((o["result"].planes[:MF, 7] > 0).sum().item()),
+            "mean_road_points": float(o["counts"][:MF].float().mean().item())}
+        del sp, bl, br
 
     # ---- end to end: pinned host frames in, masks / planes / counts out, chunked + double buffered
     e2e = None

@@ -470,3 +470,33 @@ class Matcher:
                 "svb_disparity_scale")
         N.count(5)
         return self.disp8[:F]
+
+
+class StereoPipeline:
+    """Camera images to road mask for F chained frames of one sequence, all on the device: the batch form of
+    stereovision.performStereoVision's stages 1-8 (stereovision.py:44-189) -- FrontEnd (gamma, gray, equalise) on both
+    views, Matcher (disparity), RoadPath (fill, clouds, plane, road points), RoadCleaner (cleaning, hull, obstacles).
+    The one-frame drop-in with the reference's signature is stereo.vision_b200/stereovision.py; this class is the
+    throughput entry point (device-draw RANSAC, `seed`)."""
+
+    def __init__(self, shape=(544, 1024), max_frames=16, frames_in_flight=None, trials=600, samples=600, step=2,
+                 carmask=None, device="cuda:0"):
+        F = int(max_frames)
+        self.front = FrontEnd(shape, max_frames=F, device=device)
+        self.front_r = FrontEnd(shape, max_frames=F, device=device)
+        self.matcher = Matcher(shape, max_frames=F, frames_in_flight=frames_in_flight or F, device=device)
+        self.path = RoadPath(shape, step=step, trials=trials, samples=samples, carmask=carmask, max_frames=F, device=device)
+        self.cleaner = RoadCleaner(shape, max_frames=F, device=device)
+
+    def process(self, bgrL, bgrR, prev=None, seed=0, obstacles=True):
+        """bgrL, bgrR uint8 [F,H,W,3] -> dict(result = the path's BatchResult, disparity, cleaned, counts, points
+        [, hull outputs]); result.filled[-1] is the `prev` of the next call."""
+        colourL, grayL = self.front.process(bgrL)
+        _, grayR = self.front_r.process(bgrR)
+        disp = self.matcher.disparity(grayL, grayR)
+        res = self.path.process(disp, colourL, prev=prev, seed=seed)
+        cleaned, counts, points = self.cleaner.clean(res.road_mask)
+        out = {"result": res, "disparity": disp, "cleaned": cleaned, "counts": counts, "points": points}
+        if obstacles:
+            out.update(self.cleaner.obstacles())
+        return out

@@ -48,3 +48,35 @@ def test_first_frame_disparity_matches_matcher_fixture(cuda):
     with np.load(GOLD, allow_pickle=False) as z:
         g = {k: z[k] for k in z.files}
     assert str(g["f0_disparity_sha"]) == str(g["f0_filled_sha"])
+
+
+def test_batched_pipeline_on_the_golden_frames(cuda):
+    """pipeline.StereoPipeline (the batch form: all stages for F chained frames in a handful of launches) on the same
+    three frames: the disparity it carries from frame to frame is the reference orchestrator's, bit for bit; the plane
+    comes from device draws, so it is checked for quality (its road mask covers the golden's road region)."""
+    import np_oracle as no
+    from stereo.vision_b200.masks import default_road_threshold_mask
+    from stereo.vision_b200.pipeline import StereoPipeline
+    with np.load(GOLD, allow_pickle=False) as z:
+        g = {k: z[k] for k in z.files}
+    seq, F = int(g["seq"]), int(g["n_frames"])
+    frames = [synth.make_stereo_bgr(seq, t) for t in range(F)]
+    L = np.stack([f[0] for f in frames])
+    R = np.stack([f[1] for f in frames])
+    sp = StereoPipeline(max_frames=F, device=cuda)
+    out = sp.process(L, R, seed=5)
+    res = out["result"]
+    filled = res.filled.cpu().numpy()
+    for t in range(F):
+        assert sha(filled[t]) == str(g["f%d_filled_sha" % t]), "carried disparity, frame %d" % t
+    assert sha(out["disparity"][0].cpu().numpy()) == str(g["f0_disparity_sha"])
+    planes = res.planes.cpu().numpy()
+    assert (planes[:, 7] > 0).all()
+    counts = res.counts.cpu().numpy()
+    tm = default_road_threshold_mask()
+    for t in range(F):
+        # a different winning hypothesis of the same road: the number of road points is of the golden's order
+        assert 0.5 * int(g["f%d_road_n" % t]) < counts[t, 3] < 2.0 * int(g["f%d_road_n" % t])
+        want, wpts = no.sanitise_road_image(res.road_mask[t].cpu().numpy(), tm)
+        assert np.array_equal(out["cleaned"][t].cpu().numpy(), want)
+        assert int(out["counts"][t]) == len(wpts)
