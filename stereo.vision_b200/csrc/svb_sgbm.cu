@@ -133,38 +133,12 @@ __global__ void __launch_bounds__(256) sgbm_hsum_kernel(const uint4 *__restrict_
     }
 }
 
-// ------------------------------------------------------------------ vertical running sum -> C
-// thread = (x1, d pair), a segment of rows; C(y) = C(y-1) + hsum(min(y+SH2, H-1)) - hsum(max(y-SH2-1, 0)),
-// int16 wrap-around like OpenCV's CostType stores.
-__global__ void __launch_bounds__(256) sgbm_vsum_kernel(const uint32_t *__restrict__ hsum, int H, int w1, int SH2, int seg,
-                                                        uint32_t *__restrict__ C) {
-    int64_t col = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;          // (x1, dp) flattened
-    int64_t ncols = (int64_t)w1 * 64;
-    if (col >= ncols) return;
-    int f = blockIdx.z;
-    int y0 = blockIdx.y * seg, y1 = min(y0 + seg, H);
-    const uint32_t *h = hsum + (int64_t)f * H * ncols + col;
-    uint32_t *c = C + (int64_t)f * H * ncols + col;
-    uint32_t acc = 0;
-    for (int k = y0 - SH2; k <= y0 + SH2; ++k) acc = __vadd2(acc, __ldg(h + (int64_t)min(max(k, 0), H - 1) * ncols));
-    c[(int64_t)y0 * ncols] = acc;
-    for (int y = y0 + 1; y < y1; ++y) {
-        uint32_t a = __ldg(h + (int64_t)min(y + SH2, H - 1) * ncols);
-        uint32_t b = __ldg(h + (int64_t)max(y - SH2 - 1, 0) * ncols);
-        acc = __vsub2(__vadd2(acc, a), b);
-        c[(int64_t)y * ncols] = acc;
-    }
-}
-
 // ------------------------------------------------------------------ one step of a path
 struct PathState { int l0, l1, l2, l3, mn; };
 
 __device__ __forceinline__ void unpack4(uint2 w, int &a, int &b, int &c, int &d) {
     a = (int)(short)(w.x & 0xffffu); b = (int)(short)(w.x >> 16);
     c = (int)(short)(w.y & 0xffffu); d = (int)(short)(w.y >> 16);
-}
-__device__ __forceinline__ uint2 pack4(int a, int b, int c, int d) {
-    return make_uint2(((uint32_t)a & 0xffffu) | ((uint32_t)b << 16), ((uint32_t)c & 0xffffu) | ((uint32_t)d << 16));
 }
 // L_r(p,d) = C(p,d) + min(L(d), L(d-1)+P1, L(d+1)+P1, min L + P2) - min L   (see the oracle's note on the shift)
 __device__ __forceinline__ void path_step(PathState &s, uint2 cw, int lane) {
@@ -240,13 +214,61 @@ __global__ void __launch_bounds__(256) sgbm_path_kernel(const uint2 *__restrict_
 // minimum); lane (x1 & 31) keeps that result and every 32 steps the lanes finish their columns in parallel:
 // sub-pixel division, disp1, and the right-view entry disp2[x - d] = d where min S is smallest (first visited,
 // i.e. largest x, on ties) as one shared-memory atomicMin on (min S, -x).  Per warp: W x (uint32 + int16).
+// ------------------------------------------------------------------ block cost + vertical direction in one walk
+// One warp per column (lane = 4 disparities) walks down the rows: the block cost is the running sum
+// C(y) = C(y-1) + hsum(min(y+SH2, H-1)) - hsum(max(y-SH2-1, 0)) (int16 wrap-around like OpenCV's CostType stores;
+// the row that leaves was read 2*SH2+1 rows earlier and usually still sits in L2), written once for the other
+// directions, and feeds the vertical path (DIR 2) on the spot: C is not read back for it.
+__global__ void __launch_bounds__(256) sgbm_vsum_v_kernel(const uint2 *__restrict__ hsum, int F, int H, int w1, int SH2,
+                                                          uint2 *__restrict__ C, uint16_t *__restrict__ E) {
+    const int lane = threadIdx.x & 31;
+    int64_t wid = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+    if (wid >= (int64_t)F * w1) return;
+    const int f = (int)(wid / w1), x = (int)(wid - (int64_t)f * w1);
+    const int64_t rs = (int64_t)w1 * 32;                           // row stride in lanes
+    const int64_t base = ((int64_t)f * H * w1 + x) * 32 + lane;    // row 0 of the column
+    uint2 acc = make_uint2(0, 0);
+    for (int k = -SH2; k <= SH2; ++k) {
+        uint2 h = __ldg(hsum + base + (int64_t)min(max(k, 0), H - 1) * rs);
+        acc.x = __vadd2(acc.x, h.x); acc.y = __vadd2(acc.y, h.y);
+    }
+    PathState s = {0, 0, 0, 0, 0};
+    C[base] = acc;
+    path_step(s, acc, lane);
+    E[base] = (uint16_t)excess4(s, acc);
+    int y = 1;
+    for (; y + 4 <= H; y += 4) {
+        uint2 a[4], b[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            a[k] = __ldg(hsum + base + (int64_t)min(y + k + SH2, H - 1) * rs);
+            b[k] = __ldg(hsum + base + (int64_t)max(y + k - SH2 - 1, 0) * rs);
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            acc.x = __vsub2(__vadd2(acc.x, a[k].x), b[k].x); acc.y = __vsub2(__vadd2(acc.y, a[k].y), b[k].y);
+            C[base + (int64_t)(y + k) * rs] = acc;
+            path_step(s, acc, lane);
+            E[base + (int64_t)(y + k) * rs] = (uint16_t)excess4(s, acc);
+        }
+    }
+    for (; y < H; ++y) {
+        uint2 a = __ldg(hsum + base + (int64_t)min(y + SH2, H - 1) * rs);
+        uint2 b = __ldg(hsum + base + (int64_t)max(y - SH2 - 1, 0) * rs);
+        acc.x = __vsub2(__vadd2(acc.x, a.x), b.x); acc.y = __vsub2(__vadd2(acc.y, a.y), b.y);
+        C[base + (int64_t)y * rs] = acc;
+        path_step(s, acc, lane);
+        E[base + (int64_t)y * rs] = (uint16_t)excess4(s, acc);
+    }
+}
+
 // nibbles of a uint16 (each at most 10 here) to the bytes of a word
 __device__ __forceinline__ uint32_t nib2bytes(uint32_t w) {
     uint32_t t = (w | (w << 8)) & 0x00ff00ffu;
     return (t | (t << 4)) & 0x0f0f0f0fu;
 }
-__global__ void __launch_bounds__(128) sgbm_final_kernel(const uint2 *__restrict__ C, const uint16_t *__restrict__ E, int64_t plane, int F, int H,
-                                                         int W, int16_t *__restrict__ disp) {
+__global__ void __launch_bounds__(128) sgbm_final_kernel(const uint2 *__restrict__ C, const uint16_t *__restrict__ E0, const uint16_t *__restrict__ E,
+                                                         int64_t plane, int F, int H, int W, int16_t *__restrict__ disp) {
     extern __shared__ uint32_t sh32[];
     const int w1 = W - SG_D;
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
@@ -264,8 +286,8 @@ __global__ void __launch_bounds__(128) sgbm_final_kernel(const uint2 *__restrict
     auto fetch = [&](int col, uint2 &c, uint32_t &e01, uint32_t &e23) {
         int64_t i = rowbase + (int64_t)col * 32;
         c = __ldg(C + i);
-        e01 = (uint32_t)__ldg(E + i) + __ldg(E + plane + i);
-        e23 = (uint32_t)__ldg(E + 2 * plane + i) + __ldg(E + 3 * plane + i);
+        e01 = (uint32_t)__ldg(E0 + i) + __ldg(E + i);
+        e23 = (uint32_t)__ldg(E + plane + i) + __ldg(E + 2 * plane + i);
     };
     auto step = [&](int x1, uint2 c, uint32_t e01, uint32_t e23) {
         path_step(s, c, lane);
@@ -305,7 +327,7 @@ __global__ void __launch_bounds__(128) sgbm_final_kernel(const uint2 *__restrict
             mykey = 0xffffffffu;
         }
     };
-    constexpr int G = 8;                                    // columns whose loads are in flight while a group is computed
+    constexpr int G = 4;                                    // columns whose loads are in flight while a group is computed
     int x1 = w1 - 1;
     for (int k = w1 % G; k > 0; --k, --x1) {               // leading remainder, one column at a time
         uint2 c; uint32_t e01, e23;
@@ -486,7 +508,7 @@ extern "C" int svb_sgbm_supported(int H, int W, int num_disparities, int block) 
 static int64_t sgbm_frame_bytes(int H, int W) {
     int64_t w1 = W - SG_D;
     int64_t vol = (int64_t)H * w1 * SG_D * 2;
-    return 2 * (int64_t)H * W * 16 + 2 * vol + (int64_t)H * W * 2;
+    return 2 * (int64_t)H * W * 16 + 2 * vol + vol / 4 + (int64_t)H * W * 2 + 256;
 }
 extern "C" int64_t svb_sgbm_scratch_bytes(int F, int H, int W, int num_disparities) {
     if (F < 1 || num_disparities != SG_D || W <= SG_D) return 0;
@@ -514,7 +536,8 @@ extern "C" int svb_sgbm_compute(const uint8_t *grayL, const uint8_t *grayR, int 
         int16_t *raw = (int16_t *)((char *)Cv + vol);
         const uint8_t *L = grayL + (int64_t)f0 * H * W, *R = grayR + (int64_t)f0 * H * W;
         const uint2 *C2 = (const uint2 *)Cv;
-        uint16_t *E = (uint16_t *)hs;                          // four excess planes of a quarter volume each, over the dead hsum
+        uint16_t *E = (uint16_t *)hs;                          // excess planes of DIR 1, 3, 0 (a quarter volume each) over the dead hsum
+        uint16_t *E0 = (uint16_t *)((char *)raw + (((int64_t)n * H * W * 2 + 255) & ~(int64_t)255));   // DIR 2's plane: hsum is still live
         const int64_t plane = (int64_t)n * H * w1 * 32;
         const unsigned diag_blocks = (unsigned)(((int64_t)n * (w1 + H - 1) + 7) / 8);
         { ProfScope ps(K_SGBM_PREFILTER, st);
@@ -522,22 +545,19 @@ extern "C" int svb_sgbm_compute(const uint8_t *grayL, const uint8_t *grayR, int 
         { ProfScope ps(K_SGBM_HSUM, st);
           sgbm_hsum_kernel<<<(unsigned)(((int64_t)n * H + 3) / 4), 256, 0, st>>>(recs, n, H, W, SW2, hs); }
         { ProfScope ps(K_SGBM_VSUM, st);
-          int seg = 68;
-          sgbm_vsum_kernel<<<dim3((unsigned)(((int64_t)w1 * 64 + 255) / 256), (H + seg - 1) / seg, n), 256, 0, st>>>(hs, H, w1, SW2, seg, Cv); }
+          sgbm_vsum_v_kernel<<<(unsigned)(((int64_t)n * w1 + 7) / 8), 256, 0, st>>>((const uint2 *)hs, n, H, w1, SW2, (uint2 *)Cv, E0); }
         SVB_LAUNCH_CHECK();
-        { ProfScope ps(K_SGBM_PATH_V, st);
-          sgbm_path_kernel<2><<<(unsigned)(((int64_t)n * w1 + 7) / 8), 256, 0, st>>>(C2, E + 0 * plane, n, H, w1); }
-        { ProfScope ps(K_SGBM_PATH_D1, st); sgbm_path_kernel<1><<<diag_blocks, 256, 0, st>>>(C2, E + 1 * plane, n, H, w1); }
-        { ProfScope ps(K_SGBM_PATH_D3, st); sgbm_path_kernel<3><<<diag_blocks, 256, 0, st>>>(C2, E + 2 * plane, n, H, w1); }
+        { ProfScope ps(K_SGBM_PATH_D1, st); sgbm_path_kernel<1><<<diag_blocks, 256, 0, st>>>(C2, E + 0 * plane, n, H, w1); }
+        { ProfScope ps(K_SGBM_PATH_D3, st); sgbm_path_kernel<3><<<diag_blocks, 256, 0, st>>>(C2, E + 1 * plane, n, H, w1); }
         { ProfScope ps(K_SGBM_PATH_H, st);
-          sgbm_path_kernel<0><<<(unsigned)(((int64_t)n * H + 7) / 8), 256, 0, st>>>(C2, E + 3 * plane, n, H, w1); }
+          sgbm_path_kernel<0><<<(unsigned)(((int64_t)n * H + 7) / 8), 256, 0, st>>>(C2, E + 2 * plane, n, H, w1); }
         SVB_LAUNCH_CHECK();
         { ProfScope ps(K_SGBM_FINAL, st);
           if ((size_t)4 * W * 6 > 48 * 1024) {              // wide frames: more than the default dynamic shared memory
               cudaError_t e = cudaFuncSetAttribute(sgbm_final_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * W * 6);
               if (e != cudaSuccess) return (int)e;
           }
-          sgbm_final_kernel<<<(unsigned)(((int64_t)n * H + 3) / 4), 128, (size_t)4 * W * 6, st>>>(C2, E, plane, n, H, W, raw); }
+          sgbm_final_kernel<<<(unsigned)(((int64_t)n * H + 3) / 4), 128, (size_t)4 * W * 6, st>>>(C2, E0, E, plane, n, H, W, raw); }
         { ProfScope ps(K_SGBM_MEDIAN, st);
           sgbm_median3_kernel<<<grid_for((int64_t)n * H * W, 256), 256, 0, st>>>(raw, n, H, W, disp16 + (int64_t)f0 * H * W); }
         SVB_LAUNCH_CHECK();
