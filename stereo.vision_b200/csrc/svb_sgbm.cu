@@ -65,32 +65,39 @@ __global__ void sgbm_prefilter_kernel(const uint8_t *__restrict__ L, const uint8
 // Halves are biased by 0x8000 so that one 32-bit subtraction never borrows across them and the differences
 // compare as unsigned halves: c0 = max(0, u - v1, v0 - u), c1 = max(0, v - u1, u0 - v), cost = min(c0, c1).
 #define SG_BIAS 0x80008000u
-__device__ __forceinline__ uint32_t bt_cost(uint32_t u, uint32_t ub, uint32_t u0b, uint32_t u1, uint32_t v, uint32_t vb, uint32_t v0b,
-                                            uint32_t v1) {
+// biased minimum of the two one-sided costs, both halves: BIAS + (cost_grad | cost_raw << 16)
+__device__ __forceinline__ uint32_t bt_min(uint32_t u, uint32_t ub, uint32_t u0b, uint32_t u1, uint32_t v, uint32_t vb, uint32_t v0b,
+                                           uint32_t v1) {
     uint32_t c0 = __vimax3_u16x2(ub - v1, v0b - u, SG_BIAS);
     uint32_t c1 = __vimax3_u16x2(vb - u1, u0b - v, SG_BIAS);
-    uint32_t m = __vminu2(c0, c1);
-    return (m & 0x7fffu) + ((m >> 18) & 0x1fffu);
+    return __vminu2(c0, c1);
 }
 
 // ------------------------------------------------------------------ horizontal block sums
 // thread = (row, pair of disparities), 4 rows per CTA; it walks the row once.  The pixel cost of a column is
 // computed on the fly from two 16-byte records (the right pixel of d = 2dp + 1 is the one d = 2dp used a column
-// earlier); a ring of the last 32 cost pairs (one byte each) in shared memory feeds the sliding window, whose ends
-// repeat the border columns (window clamped to [0, w1)).
-struct HsumState { uint32_t s, pix0; uint4 pv; };
-__device__ __forceinline__ uint32_t hsum_cost(const uint4 *__restrict__ Lp, const uint4 *__restrict__ Rp, uint4 &pv) {
-    uint4 u = __ldg(Lp), v = __ldg(Rp);
+// earlier, its biased words are carried); a ring of the last 32 cost pairs (one byte each) in shared memory feeds
+// the sliding window, whose ends repeat the border columns (window clamped to [0, w1)).
+struct RightPix { uint32_t v, vb, v0b, v1; };
+__device__ __forceinline__ RightPix right_pix(const uint4 *__restrict__ p) {
+    uint4 r = __ldg(p);
+    RightPix q = {r.x, r.x | SG_BIAS, r.y | SG_BIAS, r.z};
+    return q;
+}
+// cost pair of a column: cost(d = 2dp) | cost(d = 2dp + 1) << 16, cost = grad part + raw part / 4
+__device__ __forceinline__ uint32_t hsum_cost(const uint4 *__restrict__ Lp, const uint4 *__restrict__ Rp, RightPix &pv) {
+    uint4 u = __ldg(Lp);
+    RightPix q = right_pix(Rp);
     uint32_t ub = u.x | SG_BIAS, u0b = u.y | SG_BIAS;
-    uint32_t a = bt_cost(u.x, ub, u0b, u.z, v.x, v.x | SG_BIAS, v.y | SG_BIAS, v.z);
-    uint32_t b = bt_cost(u.x, ub, u0b, u.z, pv.x, pv.x | SG_BIAS, pv.y | SG_BIAS, pv.z);
-    pv = v;
-    return a | (b << 16);
+    uint32_t ma = bt_min(u.x, ub, u0b, u.z, q.v, q.vb, q.v0b, q.v1);
+    uint32_t mb = bt_min(u.x, ub, u0b, u.z, pv.v, pv.vb, pv.v0b, pv.v1);
+    pv = q;
+    uint32_t g = __byte_perm(ma, mb, 0x5410) & 0x7fff7fffu;              // gradient halves of both
+    uint32_t r = (__byte_perm(ma, mb, 0x7632) >> 2) & 0x1fff1fffu;       // raw halves of both, quartered
+    return g + r;
 }
-__device__ __forceinline__ uint32_t ring_get(const uint16_t *slot) {
-    uint32_t p = *slot;
-    return (p & 0xffu) | ((p & 0xff00u) << 8);
-}
+__device__ __forceinline__ uint16_t ring_put(uint32_t pc) { return (uint16_t)__byte_perm(pc, 0, 0x4420); }   // bytes 0 and 2
+__device__ __forceinline__ uint32_t ring_get(const uint16_t *slot) { return __byte_perm((uint32_t)*slot, 0, 0x4140); }
 __global__ void __launch_bounds__(256) sgbm_hsum_kernel(const uint4 *__restrict__ recs, int F, int H, int W, int SW2,
                                                         uint32_t *__restrict__ hsum) {
     __shared__ uint16_t ring[32][256];
@@ -102,16 +109,16 @@ __global__ void __launch_bounds__(256) sgbm_hsum_kernel(const uint4 *__restrict_
     const uint4 *Lp = recs + row * W + SG_D;                      // left pixel of column c: Lp[c]
     const uint4 *Rp = recs + n + row * W + SG_D - 2 * dp;         // right pixel of (c, d = 2dp): Rp[c]
     uint32_t *out = hsum + row * w1 * 64 + dp;
-    uint4 pv = __ldg(Rp - 1);
+    RightPix pv = right_pix(Rp - 1);
     // columns 0 .. SW2: fill the window (the border column counts SW2 + 1 times), first output at c = SW2
     uint32_t pc = hsum_cost(Lp, Rp, pv);
     const uint32_t pix0 = pc;
     uint32_t s = pc * (uint32_t)(SW2 + 1);                         // halves stay below 2^16: no carry
-    ring[0][tx] = (uint16_t)((pc & 0xffu) | (pc >> 8));
+    ring[0][tx] = ring_put(pc);
     int c = 1;
     for (; c <= SW2; ++c) {
         pc = hsum_cost(Lp + c, Rp + c, pv);
-        ring[c & 31][tx] = (uint16_t)((pc & 0xffu) | (pc >> 8));
+        ring[c & 31][tx] = ring_put(pc);
         s += pc;
     }
     out[0] = s;
@@ -121,7 +128,7 @@ __global__ void __launch_bounds__(256) sgbm_hsum_kernel(const uint4 *__restrict_
         int lv = c - 2 * SW2 - 1;
         s -= lv >= 0 ? ring_get(&ring[lv & 31][tx]) : pix0;
         pc = hsum_cost(Lp + c, Rp + c, pv);
-        ring[c & 31][tx] = (uint16_t)((pc & 0xffu) | (pc >> 8));
+        ring[c & 31][tx] = ring_put(pc);
         s += pc;
         out[(int64_t)(c - SW2) * 64] = s;
     }
@@ -274,7 +281,7 @@ __global__ void __launch_bounds__(128) sgbm_final_kernel(const uint2 *__restrict
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     int64_t wid = blockIdx.x * 4 + wib;
     if (wid >= (int64_t)F * H) return;
-    uint32_t *d2k = sh32 + (size_t)wib * W;                                   // (min S + 32768) << 16 | (0xffff - x)
+    uint32_t *d2k = sh32 + (size_t)wib * W;                                   // min S << 16 | (0xffff - x)
     int16_t *d1 = (int16_t *)(sh32 + (size_t)4 * W) + (size_t)wib * W;
     for (int x = lane; x < W; x += 32) { d1[x] = -16; d2k[x] = 0xffffffffu; }
     __syncwarp();
@@ -291,32 +298,32 @@ __global__ void __launch_bounds__(128) sgbm_final_kernel(const uint2 *__restrict
     };
     auto step = [&](int x1, uint2 c, uint32_t e01, uint32_t e23) {
         path_step(s, c, lane);
-        // S = 4 C + the four directions' excesses + this direction's L, saturated once
+        // S = 4 C + the four directions' excesses + this direction's L, saturated once at 32767.  Two disparities per
+        // word: with C clamped to 8191 and L to 32747 the sum stays below 2^16 per half and still reaches 32767 exactly
+        // when the unclamped sum does (L >= C; all terms are non-negative below the cost limit of this file's header).
         uint32_t eb = nib2bytes(e01) + nib2bytes(e23);
-        int a0, a1, a2, a3;
-        unpack4(c, a0, a1, a2, a3);
-        a0 = min(4 * a0 + (int)(eb & 0xffu) + s.l0, SG_MAXC); a1 = min(4 * a1 + (int)((eb >> 8) & 0xffu) + s.l1, SG_MAXC);
-        a2 = min(4 * a2 + (int)((eb >> 16) & 0xffu) + s.l2, SG_MAXC); a3 = min(4 * a3 + (int)(eb >> 24) + s.l3, SG_MAXC);
-        a0 = max(a0, -32768); a1 = max(a1, -32768); a2 = max(a2, -32768); a3 = max(a3, -32768);
-        // first minimum over ascending d: key = (S + 32768) << 8 | d
-        uint32_t k0 = ((uint32_t)(a0 + 32768) << 8) | (uint32_t)(4 * lane);
-        uint32_t k1 = ((uint32_t)(a1 + 32768) << 8) | (uint32_t)(4 * lane + 1);
-        uint32_t k2 = ((uint32_t)(a2 + 32768) << 8) | (uint32_t)(4 * lane + 2);
-        uint32_t k3 = ((uint32_t)(a3 + 32768) << 8) | (uint32_t)(4 * lane + 3);
+        uint32_t l01 = __vminu2(__byte_perm((uint32_t)s.l0, (uint32_t)s.l1, 0x5410), 0x7feb7febu);
+        uint32_t l23 = __vminu2(__byte_perm((uint32_t)s.l2, (uint32_t)s.l3, 0x5410), 0x7feb7febu);
+        uint32_t s01 = __vminu2((__vminu2(c.x, 0x1fff1fffu) << 2) + __byte_perm(eb, 0, 0x4140) + l01, 0x7fff7fffu);
+        uint32_t s23 = __vminu2((__vminu2(c.y, 0x1fff1fffu) << 2) + __byte_perm(eb, 0, 0x4342) + l23, 0x7fff7fffu);
+        // first minimum over ascending d: key = S << 8 | d
+        const uint32_t d0 = (uint32_t)(4 * lane);
+        uint32_t k0 = ((s01 << 8) & 0x00ffff00u) | d0, k1 = ((s01 >> 8) & 0x00ffff00u) | (d0 + 1);
+        uint32_t k2 = ((s23 << 8) & 0x00ffff00u) | (d0 + 2), k3 = ((s23 >> 8) & 0x00ffff00u) | (d0 + 3);
         uint32_t key = __reduce_min_sync(SG_FULL, min(min(k0, k1), min(k2, k3)));
         int lo = (int)(key & 0xffu) - 1, hi = lo + 2;
-        int pick_lo = (lo & 3) == 0 ? a0 : (lo & 3) == 1 ? a1 : (lo & 3) == 2 ? a2 : a3;
-        int pick_hi = (hi & 3) == 0 ? a0 : (hi & 3) == 1 ? a1 : (hi & 3) == 2 ? a2 : a3;
+        uint32_t wlo = (lo & 2) ? s23 : s01, whi = (hi & 2) ? s23 : s01;
+        int pick_lo = (int)((lo & 1) ? wlo >> 16 : wlo & 0xffffu), pick_hi = (int)((hi & 1) ? whi >> 16 : whi & 0xffffu);
         int s_lo = __shfl_sync(SG_FULL, pick_lo, (lo >> 2) & 31);
         int s_hi = __shfl_sync(SG_FULL, pick_hi, (hi >> 2) & 31);
         if (lane == (x1 & 31)) { mykey = key; mylo = s_lo; myhi = s_hi; }
         if ((x1 & 31) == 0) {
             // lanes finish columns x1 + lane (those below w1); every S saturated = no winner, the pixel stays invalid
-            int minS = (int)(mykey >> 8) - 32768, best = (int)(mykey & 0xffu);
+            int minS = (int)(mykey >> 8), best = (int)(mykey & 0xffu);
             int xx1 = x1 + lane;
             if (xx1 < w1 && mykey != 0xffffffffu && minS < SG_MAXC) {
                 int x = xx1 + SG_D;
-                atomicMin(d2k + (x - best), ((uint32_t)(minS + 32768) << 16) | (uint32_t)(0xffff - x));
+                atomicMin(d2k + (x - best), ((uint32_t)minS << 16) | (uint32_t)(0xffff - x));
                 int d;
                 if (0 < best && best < SG_D - 1) {
                     int den = max(mylo + myhi - 2 * minS, 1);

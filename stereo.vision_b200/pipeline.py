@@ -457,7 +457,9 @@ class Matcher:
             raise ValueError("expected up to %d pairs of %dx%d, got %s / %s" % (self.F, self.H, self.W, tuple(L.shape), tuple(R.shape)))
         N.check(self.lib.svb_sgbm_compute(N.ptr(L), N.ptr(R), F, self.H, self.W, 128, self.block, N.ptr(self.disp16),
                                           N.ptr(self.scratch), self.scratch.numel(), N.stream_ptr()), "svb_sgbm_compute")
-        N.count(9)
+        per = self.lib.svb_sgbm_scratch_bytes(1, self.H, self.W, 128) - 256           # bytes one frame in flight needs
+        in_flight = max(1, min(F, (self.scratch.numel() - 256) // per))
+        N.count(8 * ((F + in_flight - 1) // in_flight))      # per chunk: prefilter, hsum, vsum_v, d1, d3, h, final, median
         return self.disp16[:F]
 
     def disparity(self, grayL, grayR):
