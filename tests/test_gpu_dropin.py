@@ -73,7 +73,8 @@ def f(cuda):
     mod = importlib.reload(mod)
     from stereo.vision_b200.masks import default_carmask
     mod.carmask = default_carmask((544, 1024), prefer_cwd=False)
-    return mod
+    yield mod
+    importlib.reload(mod)                     # the tests rebind module settings (masks, step, sample size): leave none behind
 
 
 def test_reference_sequence_s600(f):

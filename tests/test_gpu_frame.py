@@ -13,6 +13,17 @@ import stereo.vision_b200.synth as synth
 from test_oracle_golden import sha
 
 pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(autouse=True)
+def fresh_helpers():
+    """the helper module carries rebindable settings (masks, lattice step, sample size): start from its defaults"""
+    import importlib
+    import stereo.vision_b200.functions as mod
+    importlib.reload(mod)
+    yield
+
+
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "frames.npz")
 
 
