@@ -285,7 +285,7 @@ def run_b200(args):
         # SURVEY 8(f)-4, the producer of the disparity input (functions.disparity = StereoSGBM + filterSpeckles + scaling)
         from stereo.vision_b200.pipeline import Matcher
         import stereo.vision_b200.synth as synth
-        MF = 16                                            # all in flight: 4 GB of cost volumes
+        MF = 32                                            # all in flight: 9 GB of cost volumes
         pairs = [synth.make_stereo_pair(seed, t, (H, W)) for t in range(4)]
         gl = torch.from_numpy(np.stack([pairs[t % 4][0] for t in range(MF)])).to(dev)
         gr = torch.from_numpy(np.stack([pairs[t % 4][1] for t in range(MF)])).to(dev)

@@ -244,15 +244,15 @@ __global__ void __launch_bounds__(256) sgbm_vsum_v_kernel(const uint2 *__restric
     path_step(s, acc, lane);
     E[base] = (uint16_t)excess4(s, acc);
     int y = 1;
-    for (; y + 4 <= H; y += 4) {
-        uint2 a[4], b[4];
+    for (; y + 8 <= H; y += 8) {
+        uint2 a[8], b[8];
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
+        for (int k = 0; k < 8; ++k) {
             a[k] = __ldg(hsum + base + (int64_t)min(y + k + SH2, H - 1) * rs);
             b[k] = __ldg(hsum + base + (int64_t)max(y + k - SH2 - 1, 0) * rs);
         }
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
+        for (int k = 0; k < 8; ++k) {
             acc.x = __vsub2(__vadd2(acc.x, a[k].x), b[k].x); acc.y = __vsub2(__vadd2(acc.y, a[k].y), b[k].y);
             C[base + (int64_t)(y + k) * rs] = acc;
             path_step(s, acc, lane);
