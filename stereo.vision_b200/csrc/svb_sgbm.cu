@@ -223,50 +223,56 @@ __global__ void __launch_bounds__(256) sgbm_path_kernel(const uint2 *__restrict_
 // i.e. largest x, on ties) as one shared-memory atomicMin on (min S, -x).  Per warp: W x (uint32 + int16).
 // ------------------------------------------------------------------ block cost + vertical direction in one walk
 // One warp per column (lane = 4 disparities) walks down the rows: the block cost is the running sum
-// C(y) = C(y-1) + hsum(min(y+SH2, H-1)) - hsum(max(y-SH2-1, 0)) (int16 wrap-around like OpenCV's CostType stores;
-// the row that leaves was read 2*SH2+1 rows earlier and usually still sits in L2), written once for the other
-// directions, and feeds the vertical path (DIR 2) on the spot: C is not read back for it.
+// C(y) = C(y-1) + hsum(min(y+SH2, H-1)) - hsum(max(y-SH2-1, 0)) (int16 wrap-around like OpenCV's CostType stores),
+// written once for the other directions, and feeds the vertical path (DIR 2) on the spot: C is not read back for
+// it.  The row that leaves the window was read 2*SH2+1 rows earlier: it waits in a per-warp ring in shared memory
+// (lane-private slots, no synchronisation), so hsum is read from memory exactly once.
 __global__ void __launch_bounds__(256) sgbm_vsum_v_kernel(const uint2 *__restrict__ hsum, int F, int H, int w1, int SH2,
                                                           uint2 *__restrict__ C, uint16_t *__restrict__ E) {
+    extern __shared__ uint2 vring[];                               // [warp of the CTA][slot][lane]
+    const int RING = 2 * SH2 + 2;
     const int lane = threadIdx.x & 31;
     int64_t wid = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
     if (wid >= (int64_t)F * w1) return;
+    uint2 *ring = vring + (size_t)(threadIdx.x >> 5) * RING * 32 + lane;      // slot k: ring[k * 32]
     const int f = (int)(wid / w1), x = (int)(wid - (int64_t)f * w1);
     const int64_t rs = (int64_t)w1 * 32;                           // row stride in lanes
     const int64_t base = ((int64_t)f * H * w1 + x) * 32 + lane;    // row 0 of the column
+    // rows 0 .. SH2 (clamped to the image): row 0 counts SH2 + 1 times
+    const uint2 h0 = __ldg(hsum + base);
+    uint2 hlast = h0;
+    ring[0] = h0;
     uint2 acc = make_uint2(0, 0);
-    for (int k = -SH2; k <= SH2; ++k) {
-        uint2 h = __ldg(hsum + base + (int64_t)min(max(k, 0), H - 1) * rs);
-        acc.x = __vadd2(acc.x, h.x); acc.y = __vadd2(acc.y, h.y);
+    for (int k = 0; k <= SH2; ++k) acc = make_uint2(__vadd2(acc.x, h0.x), __vadd2(acc.y, h0.y));
+    for (int k = 1; k <= SH2; ++k) {
+        if (k <= H - 1) { hlast = __ldg(hsum + base + (int64_t)k * rs); ring[k * 32] = hlast; }
+        acc.x = __vadd2(acc.x, hlast.x); acc.y = __vadd2(acc.y, hlast.y);
     }
     PathState s = {0, 0, 0, 0, 0};
     C[base] = acc;
     path_step(s, acc, lane);
     E[base] = (uint16_t)excess4(s, acc);
-    int y = 1;
-    for (; y + 8 <= H; y += 8) {
-        uint2 a[8], b[8];
-#pragma unroll
-        for (int k = 0; k < 8; ++k) {
-            a[k] = __ldg(hsum + base + (int64_t)min(y + k + SH2, H - 1) * rs);
-            b[k] = __ldg(hsum + base + (int64_t)max(y + k - SH2 - 1, 0) * rs);
-        }
-#pragma unroll
-        for (int k = 0; k < 8; ++k) {
-            acc.x = __vsub2(__vadd2(acc.x, a[k].x), b[k].x); acc.y = __vsub2(__vadd2(acc.y, a[k].y), b[k].y);
-            C[base + (int64_t)(y + k) * rs] = acc;
-            path_step(s, acc, lane);
-            E[base + (int64_t)(y + k) * rs] = (uint16_t)excess4(s, acc);
-        }
-    }
-    for (; y < H; ++y) {
-        uint2 a = __ldg(hsum + base + (int64_t)min(y + SH2, H - 1) * rs);
-        uint2 b = __ldg(hsum + base + (int64_t)max(y - SH2 - 1, 0) * rs);
-        acc.x = __vsub2(__vadd2(acc.x, a.x), b.x); acc.y = __vsub2(__vadd2(acc.y, a.y), b.y);
+    int ni = (SH2 + 1) % RING;                                     // slot of the row entering at y = 1
+    int oi = 0;                                                    // slot of row y - SH2 - 1 once that is >= 0
+    auto advance = [&](int y, uint2 a) {                           // a = hsum row y + SH2 (unused past the image)
+        if (y + SH2 <= H - 1) { hlast = a; ring[ni * 32] = a; }
+        ni = ni + 1 == RING ? 0 : ni + 1;
+        uint2 b = h0;
+        if (y - SH2 - 1 >= 0) { b = ring[oi * 32]; oi = oi + 1 == RING ? 0 : oi + 1; }
+        acc.x = __vsub2(__vadd2(acc.x, hlast.x), b.x); acc.y = __vsub2(__vadd2(acc.y, hlast.y), b.y);
         C[base + (int64_t)y * rs] = acc;
         path_step(s, acc, lane);
         E[base + (int64_t)y * rs] = (uint16_t)excess4(s, acc);
+    };
+    int y = 1;
+    for (; y + 8 <= H; y += 8) {
+        uint2 a[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) a[k] = __ldg(hsum + base + (int64_t)min(y + k + SH2, H - 1) * rs);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) advance(y + k, a[k]);
     }
+    for (; y < H; ++y) advance(y, __ldg(hsum + base + (int64_t)min(y + SH2, H - 1) * rs));
 }
 
 // nibbles of a uint16 (each at most 10 here) to the bytes of a word
@@ -552,7 +558,12 @@ extern "C" int svb_sgbm_compute(const uint8_t *grayL, const uint8_t *grayR, int 
         { ProfScope ps(K_SGBM_HSUM, st);
           sgbm_hsum_kernel<<<(unsigned)(((int64_t)n * H + 3) / 4), 256, 0, st>>>(recs, n, H, W, SW2, hs); }
         { ProfScope ps(K_SGBM_VSUM, st);
-          sgbm_vsum_v_kernel<<<(unsigned)(((int64_t)n * w1 + 7) / 8), 256, 0, st>>>((const uint2 *)hs, n, H, w1, SW2, (uint2 *)Cv, E0); }
+          size_t vs = (size_t)8 * (2 * SW2 + 2) * 32 * sizeof(uint2);
+          if (vs > 48 * 1024) {
+              cudaError_t e = cudaFuncSetAttribute(sgbm_vsum_v_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)vs);
+              if (e != cudaSuccess) return (int)e;
+          }
+          sgbm_vsum_v_kernel<<<(unsigned)(((int64_t)n * w1 + 7) / 8), 256, vs, st>>>((const uint2 *)hs, n, H, w1, SW2, (uint2 *)Cv, E0); }
         SVB_LAUNCH_CHECK();
         { ProfScope ps(K_SGBM_PATH_D1, st); sgbm_path_kernel<1><<<diag_blocks, 256, 0, st>>>(C2, E + 0 * plane, n, H, w1); }
         { ProfScope ps(K_SGBM_PATH_D3, st); sgbm_path_kernel<3><<<diag_blocks, 256, 0, st>>>(C2, E + 1 * plane, n, H, w1); }
