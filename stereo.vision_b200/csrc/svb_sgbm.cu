@@ -29,7 +29,9 @@ constexpr int SG_P1 = 2, SG_P2 = 5, SG_FTZERO = 15, SG_LRDIFF = 1;   // StereoSG
 
 // ------------------------------------------------------------------ prefilter
 // per pixel one 16-byte record of three words (grad | raw << 16): value, lower and upper end of its half-pixel
-// interval (fourth word unused).  recs: [img(2)][F][H][W] uint4
+// interval (fourth word unused).  recs: [img(2)][F][H][W] uint4; rows of the RIGHT image hold their even pixels
+// first, then the odd ones (pixel x at (x & 1) * ceil(W/2) + x / 2): the lanes of sgbm_hsum read every second
+// pixel, which makes their 16-byte loads contiguous.
 __global__ void sgbm_prefilter_kernel(const uint8_t *__restrict__ L, const uint8_t *__restrict__ R, int F, int H, int W,
                                       uint4 *__restrict__ recs) {
     int64_t n = (int64_t)F * H * W;
@@ -57,7 +59,7 @@ __global__ void sgbm_prefilter_kernel(const uint8_t *__restrict__ L, const uint8
         uint32_t v = (uint32_t)g[1] | ((uint32_t)r[1] << 16);
         uint32_t lo = (uint32_t)min(g[1], min(gl, gr)) | ((uint32_t)min(r[1], min(rl, rr)) << 16);
         uint32_t hi = (uint32_t)max(g[1], max(gl, gr)) | ((uint32_t)max(r[1], max(rl, rr)) << 16);
-        recs[i] = make_uint4(v, lo, hi, 0u);
+        recs[img ? i - x + (x & 1) * ((W + 1) >> 1) + (x >> 1) : i] = make_uint4(v, lo, hi, 0u);
     }
 }
 
@@ -107,17 +109,19 @@ __global__ void __launch_bounds__(256) sgbm_hsum_kernel(const uint4 *__restrict_
     if (row >= (int64_t)F * H) return;
     const int64_t n = (int64_t)F * H * W;
     const uint4 *Lp = recs + row * W + SG_D;                      // left pixel of column c: Lp[c]
-    const uint4 *Rp = recs + n + row * W + SG_D - 2 * dp;         // right pixel of (c, d = 2dp): Rp[c]
+    // right pixel of (c, d = 2dp) is pixel c + D - 2dp: parity of c, index (c >> 1) + D/2 - dp in its half of the row
+    const uint4 *Re = recs + n + row * W + SG_D / 2 - dp, *Ro = Re + ((W + 1) >> 1);
+#define RP(c) (((c) & 1 ? Ro : Re) + ((c) >> 1))
     uint32_t *out = hsum + row * w1 * 64 + dp;
-    RightPix pv = right_pix(Rp - 1);
+    RightPix pv = right_pix(Ro - 1);                               // pixel D - 2dp - 1, the partner of d = 2dp + 1 at column 0
     // columns 0 .. SW2: fill the window (the border column counts SW2 + 1 times), first output at c = SW2
-    uint32_t pc = hsum_cost(Lp, Rp, pv);
+    uint32_t pc = hsum_cost(Lp, RP(0), pv);
     const uint32_t pix0 = pc;
     uint32_t s = pc * (uint32_t)(SW2 + 1);                         // halves stay below 2^16: no carry
     ring[0][tx] = ring_put(pc);
     int c = 1;
     for (; c <= SW2; ++c) {
-        pc = hsum_cost(Lp + c, Rp + c, pv);
+        pc = hsum_cost(Lp + c, RP(c), pv);
         ring[c & 31][tx] = ring_put(pc);
         s += pc;
     }
@@ -127,7 +131,7 @@ __global__ void __launch_bounds__(256) sgbm_hsum_kernel(const uint4 *__restrict_
     for (; c < w1; ++c) {
         int lv = c - 2 * SW2 - 1;
         s -= lv >= 0 ? ring_get(&ring[lv & 31][tx]) : pix0;
-        pc = hsum_cost(Lp + c, Rp + c, pv);
+        pc = hsum_cost(Lp + c, RP(c), pv);
         ring[c & 31][tx] = ring_put(pc);
         s += pc;
         out[(int64_t)(c - SW2) * 64] = s;
@@ -138,6 +142,7 @@ __global__ void __launch_bounds__(256) sgbm_hsum_kernel(const uint4 *__restrict_
         s += pc;
         out[(int64_t)(c - SW2) * 64] = s;
     }
+#undef RP
 }
 
 // ------------------------------------------------------------------ one step of a path
