@@ -32,35 +32,34 @@ constexpr int SG_P1 = 2, SG_P2 = 5, SG_FTZERO = 15, SG_LRDIFF = 1;   // StereoSG
 // interval (fourth word unused).  recs: [img(2)][F][H][W] uint4; rows of the RIGHT image hold their even pixels
 // first, then the odd ones (pixel x at (x & 1) * ceil(W/2) + x / 2): the lanes of sgbm_hsum read every second
 // pixel, which makes their 16-byte loads contiguous.
-__global__ void sgbm_prefilter_kernel(const uint8_t *__restrict__ L, const uint8_t *__restrict__ R, int F, int H, int W,
-                                      uint4 *__restrict__ recs) {
-    int64_t n = (int64_t)F * H * W;
-    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < 2 * n; i += (int64_t)gridDim.x * blockDim.x) {
-        int img = i >= n;
-        int64_t p = img ? i - n : i;
-        int x = (int)(p % W);
-        int y = (int)((p / W) % H);
-        const uint8_t *src = (img ? R : L) + (p - (int64_t)y * W - x);       // frame base
-        int g[3], r[3];
-#pragma unroll
-        for (int k = 0; k < 3; ++k) {
-            int xx = x + k - 1;
-            if (xx < 0 || xx >= W) { g[k] = SG_FTZERO; r[k] = SG_FTZERO; continue; }   // never used (ends handled below)
-            if (xx == 0 || xx == W - 1) { g[k] = SG_FTZERO; r[k] = SG_FTZERO; continue; }
-            const uint8_t *row = src + (int64_t)y * W;
-            const uint8_t *rn = y > 0 ? row - W : row;
-            const uint8_t *rs = y < H - 1 ? row + W : row;
-            int v = ((int)row[xx + 1] - (int)row[xx - 1]) * 2 + (int)rn[xx + 1] - (int)rn[xx - 1] + (int)rs[xx + 1] - (int)rs[xx - 1];
-            g[k] = min(max(v, -SG_FTZERO), SG_FTZERO) + SG_FTZERO;
-            r[k] = row[xx];
-        }
-        int gl = x > 0 ? (g[1] + g[0]) / 2 : g[1], gr = x < W - 1 ? (g[1] + g[2]) / 2 : g[1];
-        int rl = x > 0 ? (r[1] + r[0]) / 2 : r[1], rr = x < W - 1 ? (r[1] + r[2]) / 2 : r[1];
-        uint32_t v = (uint32_t)g[1] | ((uint32_t)r[1] << 16);
-        uint32_t lo = (uint32_t)min(g[1], min(gl, gr)) | ((uint32_t)min(r[1], min(rl, rr)) << 16);
-        uint32_t hi = (uint32_t)max(g[1], max(gl, gr)) | ((uint32_t)max(r[1], max(rl, rr)) << 16);
-        recs[img ? i - x + (x & 1) * ((W + 1) >> 1) + (x >> 1) : i] = make_uint4(v, lo, hi, 0u);
-    }
+// (gradient through the clip table) | raw << 16 of pixel xx; the first and last column hold the table's centre
+__device__ __forceinline__ uint32_t prefilter_px(const uint8_t *row, const uint8_t *rn, const uint8_t *rs, int xx, int W) {
+    if (xx <= 0 || xx >= W - 1) return (uint32_t)SG_FTZERO | ((uint32_t)SG_FTZERO << 16);
+    int v = ((int)row[xx + 1] - (int)row[xx - 1]) * 2 + (int)rn[xx + 1] - (int)rn[xx - 1] + (int)rs[xx + 1] - (int)rs[xx - 1];
+    return (uint32_t)(min(max(v, -SG_FTZERO), SG_FTZERO) + SG_FTZERO) | ((uint32_t)row[xx] << 16);
+}
+// grid (rows of both images of all frames, chunks of 256 columns); a lane takes its neighbours' values by shuffle,
+// the first and last lane of a warp compute the pixel beyond the warp themselves.
+__global__ void __launch_bounds__(256) sgbm_prefilter_kernel(const uint8_t *__restrict__ L, const uint8_t *__restrict__ R, int F, int H, int W,
+                                                             uint4 *__restrict__ recs) {
+    const int lane = threadIdx.x & 31;
+    const int64_t r = blockIdx.x;                                   // row index over [img][frame][y]
+    const int64_t nrows = (int64_t)F * H;
+    const int img = r >= nrows;
+    const int64_t fr = img ? r - nrows : r;
+    const int y = (int)(fr % H);
+    const uint8_t *row = (img ? R : L) + fr * W;
+    const uint8_t *rn = y > 0 ? row - W : row, *rs = y < H - 1 ? row + W : row;
+    const int x = blockIdx.y * 256 + threadIdx.x;
+    uint32_t c = x < W ? prefilter_px(row, rn, rs, x, W) : 0u;
+    uint32_t lft = __shfl_up_sync(SG_FULL, c, 1), rgt = __shfl_down_sync(SG_FULL, c, 1);
+    if (x >= W) return;
+    if (lane == 0 && x > 0) lft = prefilter_px(row, rn, rs, x - 1, W);
+    if (lane == 31 && x < W - 1) rgt = prefilter_px(row, rn, rs, x + 1, W);
+    // halves of (c + neighbour) / 2: both halves are below 2^9, so one shift serves both after masking the carry-out bit
+    uint32_t hl = x > 0 ? ((c + lft) >> 1) & 0x00ff00ffu : c, hr = x < W - 1 ? ((c + rgt) >> 1) & 0x00ff00ffu : c;
+    uint32_t lo = __vminu2(c, __vminu2(hl, hr)), hi = __vmaxu2(c, __vmaxu2(hl, hr));
+    recs[r * W + (img ? (x & 1) * ((W + 1) >> 1) + (x >> 1) : x)] = make_uint4(c, lo, hi, 0u);
 }
 
 // Birchfield-Tomasi cost of the gradient half plus a quarter of the raw half (both 16-bit halves at once).
@@ -559,7 +558,7 @@ extern "C" int svb_sgbm_compute(const uint8_t *grayL, const uint8_t *grayR, int 
         const int64_t plane = (int64_t)n * H * w1 * 32;
         const unsigned diag_blocks = (unsigned)(((int64_t)n * (w1 + H - 1) + 7) / 8);
         { ProfScope ps(K_SGBM_PREFILTER, st);
-          sgbm_prefilter_kernel<<<grid_for(2 * (int64_t)n * H * W, 256), 256, 0, st>>>(L, R, n, H, W, recs); }
+          sgbm_prefilter_kernel<<<dim3((unsigned)(2 * (int64_t)n * H), (W + 255) / 256), 256, 0, st>>>(L, R, n, H, W, recs); }
         { ProfScope ps(K_SGBM_HSUM, st);
           sgbm_hsum_kernel<<<(unsigned)(((int64_t)n * H + 3) / 4), 256, 0, st>>>(recs, n, H, W, SW2, hs); }
         { ProfScope ps(K_SGBM_VSUM, st);
