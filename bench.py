@@ -303,7 +303,7 @@ def run_b200(args):
         N.profile_enable(False)
         m_ms = m0.elapsed_time(m1) / 2
         vol = 2.0 * H * (W - 128) * 128                   # one int16 cost volume of a frame
-        malg = {"sgbm_prefilter": 2.0 * H * W * 17, "sgbm_hsum": 32.0 * H * W + vol, "sgbm_vsum": 3.25 * vol,
+        malg = {"sgbm_prefilter": 2.0 * H * W * 17, "sgbm_hsum": 32.0 * H * W + vol, "sgbm_vsum": 2.25 * vol,
                 "sgbm_path_v": 1.25 * vol, "sgbm_path_d1": 1.25 * vol, "sgbm_path_d3": 1.25 * vol, "sgbm_path_h": 1.25 * vol,
                 "sgbm_final": 2 * vol + 2.0 * H * W, "sgbm_median": 4.0 * H * W, "speckle": 30.0 * H * W, "disparity_scale": 3.0 * H * W}
         match = {"row": "SURVEY 8(f)-4 functions.disparity (StereoSGBM 128 x block 21 + median + filterSpeckles + scaling) on %d synthetic "

@@ -31,7 +31,7 @@ N.profile_enable(False)
 tot = e0.elapsed_time(e1) / reps
 w1 = W - 128
 vol = H * w1 * 128 * 2
-alg = {"sgbm_prefilter": 2 * H * W * (1 + 16), "sgbm_hsum": 2 * H * W * 16 + vol, "sgbm_vsum": 3.25 * vol, "sgbm_path_v": 1.25 * vol,
+alg = {"sgbm_prefilter": 2 * H * W * (1 + 16), "sgbm_hsum": 2 * H * W * 16 + vol, "sgbm_vsum": 2.25 * vol, "sgbm_path_v": 1.25 * vol,
        "sgbm_path_d1": 1.25 * vol, "sgbm_path_d3": 1.25 * vol, "sgbm_path_h": 1.25 * vol, "sgbm_final": 2 * vol + 2 * H * W,
        "sgbm_median": 4 * H * W, "speckle": H * W * (2 * 3 + 8 * 3), "disparity_scale": 3 * H * W}
 print("F %d in flight %d: %.3f ms per call, %.3f ms per frame, %.0f frames/s" % (F, fl, tot, tot / F, F / tot * 1e3))
