@@ -90,6 +90,30 @@ def test_stress_frame_2048x1088(cuda):
     assert np.array_equal(gpu_speckles(cuda, got, 0, 4000, 123)[0], so.filter_speckles(got.copy(), 0, 4000, 123))
 
 
+@pytest.mark.parametrize("shift", [0, 5, 37, 100])
+def test_shifted_pair_known_answer(cuda, shift):
+    """size-independent property at the full frame size: the right view is the left view moved by `shift` pixels, so
+    the block cost at d = shift is exactly zero wherever the window stays inside both views; the winner is `shift`
+    there and the sub-pixel term (at most half a pixel) is all that can move the x16 value; shift 0 gives exactly 0."""
+    rng = np.random.default_rng(31 + shift)
+    H, W = 544, 1024
+    tex = rng.integers(0, 256, (H, W + 128), dtype=np.uint8).astype(np.float32)
+    tex = (tex + np.roll(tex, 1, 1) + np.roll(tex, 1, 0) + np.roll(np.roll(tex, 1, 0), 1, 1)) / 4
+    tex = tex.astype(np.uint8)
+    L = np.ascontiguousarray(tex[:, :W])
+    R = np.ascontiguousarray(tex[:, shift:shift + W])                 # R[x] = L[x + shift]: left pixel x matches right pixel x - shift
+    raw = gpu_compute(cuda, np.stack([L, L]), np.stack([R, R]))
+    assert np.array_equal(raw[0], raw[1]), "frames of a batch are independent"
+    inner = raw[0][16:-16, 128 + 16:W - 16].astype(np.int32)
+    assert (inner >= 0).all()
+    if shift == 0:
+        assert (inner == 0).all()
+    else:
+        assert np.abs(inner - 16 * shift).max() <= 8
+    d8 = sf.disparity(L, R, 128, False)
+    assert set(np.unique(d8[16:-16, 128 + 16:W - 16]).tolist()) <= {2 * shift - 2, 2 * shift}
+
+
 def test_batch_in_chunks(cuda):
     """five pairs with room for two frames of cost volume: three chunks, every frame equal to its single run"""
     pairs = [synth.make_stereo_pair(9, t, (120, 400)) for t in range(5)]
