@@ -269,12 +269,21 @@ __global__ void __launch_bounds__(256) sgbm_vsum_v_kernel(const uint2 *__restric
         E[base + (int64_t)y * rs] = (uint16_t)excess4(s, acc);
     };
     int y = 1;
-    for (; y + 8 <= H; y += 8) {
-        uint2 a[8];
+    // eight rows per group; the loads of the next group are issued before the current one is consumed
+    uint2 a[8], an[8];
+    if (y + 8 <= H) {
 #pragma unroll
         for (int k = 0; k < 8; ++k) a[k] = __ldg(hsum + base + (int64_t)min(y + k + SH2, H - 1) * rs);
+    }
+    for (; y + 8 <= H; y += 8) {
+        if (y + 16 <= H) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) an[k] = __ldg(hsum + base + (int64_t)min(y + 8 + k + SH2, H - 1) * rs);
+        }
 #pragma unroll
         for (int k = 0; k < 8; ++k) advance(y + k, a[k]);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) a[k] = an[k];
     }
     for (; y < H; ++y) advance(y, __ldg(hsum + base + (int64_t)min(y + SH2, H - 1) * rs));
 }
