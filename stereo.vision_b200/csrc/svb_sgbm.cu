@@ -360,8 +360,16 @@ __global__ void __launch_bounds__(128) sgbm_final_kernel(const uint2 *__restrict
         fetch(x1, c, e01, e23);
         step(x1, c, e01, e23);
     }
+    // group A is being computed while the loads of group B are in flight; B's four excess words are only added up
+    // when B becomes A, a whole group of steps after they were issued (adding at the load would wait for it)
     uint2 cA[G], cB[G];
-    uint32_t pA[G], qA[G], pB[G], qB[G];
+    uint32_t pA[G], qA[G];
+    uint16_t r0[G], r1[G], r2[G], r3[G];
+    auto fetch_raw = [&](int col, int k) {
+        int64_t i = rowbase + (int64_t)col * 32;
+        cB[k] = __ldg(C + i);
+        r0[k] = __ldg(E0 + i); r1[k] = __ldg(E + i); r2[k] = __ldg(E + plane + i); r3[k] = __ldg(E + 2 * plane + i);
+    };
     if (x1 >= 0) {
 #pragma unroll
         for (int k = 0; k < G; ++k) fetch(x1 - k, cA[k], pA[k], qA[k]);
@@ -370,13 +378,13 @@ __global__ void __launch_bounds__(128) sgbm_final_kernel(const uint2 *__restrict
         const bool more = x1 - G >= 0;
         if (more) {
 #pragma unroll
-            for (int k = 0; k < G; ++k) fetch(x1 - G - k, cB[k], pB[k], qB[k]);
+            for (int k = 0; k < G; ++k) fetch_raw(x1 - G - k, k);
         }
 #pragma unroll
         for (int k = 0; k < G; ++k) step(x1 - k, cA[k], pA[k], qA[k]);
         x1 -= G;
 #pragma unroll
-        for (int k = 0; k < G; ++k) { cA[k] = cB[k]; pA[k] = pB[k]; qA[k] = qB[k]; }
+        for (int k = 0; k < G; ++k) { cA[k] = cB[k]; pA[k] = (uint32_t)r0[k] + r1[k]; qA[k] = (uint32_t)r2[k] + r3[k]; }
     }
     __syncwarp();
     int16_t *out = disp + wid * W;
