@@ -201,16 +201,25 @@ __global__ void __launch_bounds__(256) sgbm_path_kernel(const uint2 *__restrict_
     int64_t idx = (((int64_t)f * H + y) * w1 + x) * 32 + lane;
     PathState s = {0, 0, 0, 0, 0};
     int i = 0;
-    for (; i + 8 <= len; i += 8) {
-        uint2 c[8];
+    // eight steps per group; the loads of the next group are issued before the current one is consumed
+    uint2 c[8], cn[8];
+    if (len >= 8) {
 #pragma unroll
         for (int k = 0; k < 8; ++k) c[k] = __ldg(C + idx + k * stride);
+    }
+    for (; i + 8 <= len; i += 8) {
+        if (i + 16 <= len) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) cn[k] = __ldg(C + idx + (8 + k) * stride);
+        }
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
             path_step(s, c[k], lane);
             E[idx + k * stride] = (uint16_t)excess4(s, c[k]);
         }
         idx += 8 * stride;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) c[k] = cn[k];
     }
     for (; i < len; ++i) {
         uint2 c = __ldg(C + idx);
