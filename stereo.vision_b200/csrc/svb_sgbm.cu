@@ -374,11 +374,11 @@ __global__ void __launch_bounds__(128) sgbm_final_kernel(const uint2 *__restrict
     uint2 cA[G], cB[G];
     uint32_t pA[G], qA[G];
     uint16_t r0[G], r1[G], r2[G], r3[G];
-    auto fetch_raw = [&](int col, int k) {
-        int64_t i = rowbase + (int64_t)col * 32;
-        cB[k] = __ldg(C + i);
-        r0[k] = __ldg(E0 + i); r1[k] = __ldg(E + i); r2[k] = __ldg(E + plane + i); r3[k] = __ldg(E + 2 * plane + i);
-    };
+    // running pointers to column x1 - G of this row (the next group's first column): the group's loads then differ by
+    // constant offsets only, and one 64-bit subtraction per pointer and group replaces an address per load
+    const uint2 *pc = C + rowbase + (int64_t)(x1 - G) * 32;
+    const uint16_t *p0 = E0 + rowbase + (int64_t)(x1 - G) * 32, *p1 = E + rowbase + (int64_t)(x1 - G) * 32;
+    const uint16_t *p2 = p1 + plane, *p3 = p2 + plane;
     if (x1 >= 0) {
 #pragma unroll
         for (int k = 0; k < G; ++k) fetch(x1 - k, cA[k], pA[k], qA[k]);
@@ -387,8 +387,12 @@ __global__ void __launch_bounds__(128) sgbm_final_kernel(const uint2 *__restrict
         const bool more = x1 - G >= 0;
         if (more) {
 #pragma unroll
-            for (int k = 0; k < G; ++k) fetch_raw(x1 - G - k, k);
+            for (int k = 0; k < G; ++k) {
+                cB[k] = __ldg(pc - k * 32);
+                r0[k] = __ldg(p0 - k * 32); r1[k] = __ldg(p1 - k * 32); r2[k] = __ldg(p2 - k * 32); r3[k] = __ldg(p3 - k * 32);
+            }
         }
+        pc -= G * 32; p0 -= G * 32; p1 -= G * 32; p2 -= G * 32; p3 -= G * 32;
 #pragma unroll
         for (int k = 0; k < G; ++k) step(x1 - k, cA[k], pA[k], qA[k]);
         x1 -= G;
