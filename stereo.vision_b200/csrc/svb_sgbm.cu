@@ -125,21 +125,29 @@ __global__ void __launch_bounds__(256) sgbm_hsum_kernel(const uint4 *__restrict_
         s += pc;
     }
     out[0] = s;
-    // steady state: output x1 = c - SW2 after adding column c; the column leaving is x1 - 1 - SW2 (or the border)
-#pragma unroll 4
-    for (; c < w1; ++c) {
-        int lv = c - 2 * SW2 - 1;
-        s -= lv >= 0 ? ring_get(&ring[lv & 31][tx]) : pix0;
+    // output x1 = c - SW2 after adding column c; the column leaving is x1 - 1 - SW2: the border column while that is
+    // negative (the first SW2 + 1 outputs after x1 = 0), a ring slot afterwards
+    uint32_t *op = out + 64;                                       // running output pointer (x1 = 1 next)
+    for (; c < w1 && c <= 2 * SW2; ++c) {
+        s -= pix0;
         pc = hsum_cost(Lp + c, RP(c), pv);
         ring[c & 31][tx] = ring_put(pc);
         s += pc;
-        out[(int64_t)(c - SW2) * 64] = s;
+        *op = s; op += 64;
+    }
+#pragma unroll 4
+    for (; c < w1; ++c) {
+        s -= ring_get(&ring[(c - 2 * SW2 - 1) & 31][tx]);
+        pc = hsum_cost(Lp + c, RP(c), pv);
+        ring[c & 31][tx] = ring_put(pc);
+        s += pc;
+        *op = s; op += 64;
     }
     for (; c < w1 + SW2; ++c) {                                    // right border: the last column again
         int lv = c - 2 * SW2 - 1;
         s -= lv >= 0 ? ring_get(&ring[lv & 31][tx]) : pix0;
         s += pc;
-        out[(int64_t)(c - SW2) * 64] = s;
+        *op = s; op += 64;
     }
 #undef RP
 }
