@@ -42,6 +42,7 @@ def parse_args():
     ap.add_argument("--cpu-frames", type=int, default=0, help="frames of the CPU baseline sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--path-only", action="store_true", help="skip the next_rows legs (cleaning, front end, matcher, whole frame)")
     return ap.parse_args()
 
 
@@ -231,7 +232,7 @@ def run_b200(args):
 
     # ---- SURVEY 8(f)-1, the consumer of the road masks (sanitiseRoadImage): timed beside the path, not part of `value`
     next_rows = None
-    if rank == 0:
+    if rank == 0 and not args.path_only:
         from stereo.vision_b200.pipeline import RoadCleaner
         cl = RoadCleaner((H, W), max_frames=F, device=dev)
         masks = res.road_mask

@@ -136,6 +136,30 @@ int svb_ransac_dump_indices(const uint32_t *mcloud, int rec_stride_words, int64_
                             int F, int T, int S, const svb_camera *cam,
                             uint64_t rng_seed, int frame0,
                             int32_t *sample_idx, int32_t *triple_idx, void *stream);
+/* ---- a5 / a7, the draws: CPython's `random` stream replayed on the device      functions.py:286, 252-254
+ * The reference draws, per trial, one random.sample(points, S) and then rounds of three random.sample(points, 1)
+ * until np.cross(P1-P2, P2-P3) is not exactly zero, all from Python's global Mersenne Twister.  This entry point
+ * replays that stream (CPython 3.12: MT19937, getrandbits/_randbelow rejection, random.sample's pool and set paths
+ * with setsize = 21 + 4**ceil(log(3k,4))) on the device, one warp per generator, and writes the indices
+ * svb_ransac_score / svb_ransac_finalize take as explicit draws: sample_idx int32 [F,T,S], triple_idx int32 [F,T,3]
+ * (-1 everywhere for a frame with M_f < S: random.sample raises before it draws, functions.py:286,294).
+ *   seeds != NULL : device uint64 [F] (chain: [1]); generator f starts as after random.seed(seeds[f]);
+ *   seeds == NULL : mt_state (device uint32 [F][625], chain: [1][625]) holds random.getstate()[1] -- 624 words + index;
+ *   mt_state != NULL: on return it holds the generator where the reference's RANSAC call would leave it
+ *                   (random.setstate-able), whichever way it was started;
+ *   chain = 0     : frame f uses generator f (the parity protocol of SURVEY 8c: random.seed(s_f) before each frame);
+ *   chain = 1     : ONE generator serves frames 0..F-1 in order (random.seed(s) once before loop.py's frame loop;
+ *                   sequential by construction: one warp).
+ * max_m: upper bound of every frame's cloud size (bitmap / pool sizing); scratch: svb_ransac_replay_scratch_bytes. */
+int64_t svb_pyrandom_setsize(int k);
+int64_t svb_ransac_replay_scratch_bytes(int F, int S, int max_m);
+int svb_ransac_replay_draws(const uint32_t *mcloud, int rec_stride_words, int64_t slab_stride_records,
+                            const int32_t *counts, int counts_stride, int counts_col,
+                            int F, int T, int S, int max_m, const svb_camera *cam,
+                            const uint64_t *seeds, uint32_t *mt_state, int chain,
+                            int32_t *sample_idx, int32_t *triple_idx,
+                            void *scratch, int64_t scratch_bytes, void *stream);
+
 /* First strict minimum over the T errors of each frame (functions.py:291) and the winning plane.
  * planes[f*8 + ..] = { a, b, c, |abc|, cutoff, best_error, best_trial, valid }
  *   cutoff = the smallest double v with fl(v/|abc|) >= point_threshold, so that
@@ -332,12 +356,6 @@ int svb_upload_rows(const void *h_src, void *d_dst, int64_t pitch_bytes, int64_t
  * the kernel's name, the summed device time in ms and the number of launches, id in
  * [0, svb_profile_kernels()).  Process-global; not for concurrent use from several threads. */
 int svb_profile_enable(int on);
-/* test hook: force svb_road_points onto its two-kernel path even when the fused cluster kernel applies */
-int svb_debug_force_two_pass(int on);
-/* test hook: row bands per frame of the 1024-wide cleaning kernel (default 4); 0 = use the general kernel */
-int svb_debug_clean_bands(int bands);
-/* tuning hook: pixels per thread on lattice / odd rows of the balanced fill kernel (0 = default) */
-int svb_debug_fill_split(int mode);
 int svb_profile_kernels(void);
 int svb_profile_get(int id, char *name, int name_cap, double *ms_total, int *launches);
 

@@ -17,7 +17,7 @@ LIB_PATH = os.path.join(_PKG, "libsvb200.so")
 HUE_BINS = 1001
 HIST_STRIDE = 1024
 PLANE_STRIDE = 8
-ABI_VERSION = 10
+ABI_VERSION = 11
 SVB_OK, SVB_E_NULL, SVB_E_SHAPE, SVB_E_ARG, SVB_E_SCRATCH = 0, -1, -2, -3, -4      # include/svb200.h
 SVB_MAX_DIM = 2048                                                                  # csrc/svb_common.cuh
 
@@ -58,6 +58,9 @@ SIGNATURES = {
     "svb_cloud_export": (I, [P, I, I, CAMP, P, P, P, P, P, P, P]),
     "svb_ransac_score": (I, [P, I, L, P, I, I, I, I, I, I, CAMP, P, P, U64, I, P, P]),
     "svb_ransac_dump_indices": (I, [P, I, L, P, I, I, I, I, I, CAMP, U64, I, P, P, P]),
+    "svb_pyrandom_setsize": (L, [I]),
+    "svb_ransac_replay_scratch_bytes": (L, [I, I, I]),
+    "svb_ransac_replay_draws": (I, [P, I, L, P, I, I, I, I, I, I, CAMP, P, P, I, P, P, P, L, P]),
     "svb_ransac_finalize": (I, [P, I, L, P, I, I, I, I, I, CAMP, P, U64, I, P, D, P, P]),
     "svb_plane_from_abc": (I, [P, D, P]),
     "svb_point_errors": (I, [P, I, I, CAMP, P, P, P]),
@@ -96,11 +99,15 @@ SIGNATURES = {
     "svb_reproject_bits": (I, [I, I, CAMP, P, P, P]),
     "svb_upload_rows": (I, [P, P, L, L, L, P]),
     "svb_profile_enable": (I, [I]),
+    "svb_profile_kernels": (I, []),
+    "svb_profile_get": (I, [I, C.c_char_p, I, C.POINTER(D), C.POINTER(I)]),
+}
+
+# include/svb200_debug.h: test / tuning hooks, not part of the boundary
+DEBUG_SIGNATURES = {
     "svb_debug_force_two_pass": (I, [I]),
     "svb_debug_clean_bands": (I, [I]),
     "svb_debug_fill_split": (I, [I]),
-    "svb_profile_kernels": (I, []),
-    "svb_profile_get": (I, [I, C.c_char_p, I, C.POINTER(D), C.POINTER(I)]),
 }
 
 _lib = None
@@ -121,7 +128,7 @@ def load(build_if_missing: bool = True):
     if not os.path.isfile(LIB_PATH):
         raise SvbError("libsvb200.so is missing: run `python __graft_entry__.py build`")
     lib = C.CDLL(LIB_PATH)
-    for name, (res, args) in SIGNATURES.items():
+    for name, (res, args) in list(SIGNATURES.items()) + list(DEBUG_SIGNATURES.items()):
         fn = getattr(lib, name)           # AttributeError if the .so lacks a declared symbol
         fn.restype = res
         fn.argtypes = args

@@ -1,39 +1,86 @@
-"""Build libsvb200.so in-tree with nvcc for sm_100a (no JIT cache, the .so travels with the repo)."""
+"""Build libsvb200.so in-tree with nvcc for sm_100a (no JIT cache, the .so travels with the repo).
+
+Every .cu is compiled to an object under csrc/build/ (in parallel) and the objects are linked into
+stereo.vision_b200/libsvb200.so.  An object is reused only when the hash of its source, of every header
+and of the flags is the one it was built from, so `build()` never trusts time stamps; `force=True`
+(what __graft_entry__.build() asks for) recompiles everything.
+"""
+import hashlib
 import os
 import subprocess
 import sys
+from concurrent.futures import ThreadPoolExecutor
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 PKG = os.path.dirname(HERE)
 OUT = os.path.join(PKG, "libsvb200.so")
-SOURCES = ["svb_abi.cu", "svb_project.cu", "svb_ransac.cu", "svb_road.cu", "svb_clean.cu", "svb_sites.cu", "svb_prep.cu", "svb_options.cu", "svb_hull.cu", "svb_sgbm.cu"]
+OBJ_DIR = os.path.join(HERE, "build")
+SOURCES = ["svb_abi.cu", "svb_project.cu", "svb_ransac.cu", "svb_pyrandom.cu", "svb_road.cu", "svb_clean.cu", "svb_sites.cu",
+           "svb_prep.cu", "svb_options.cu", "svb_hull.cu", "svb_sgbm.cu"]
+HEADERS = [os.path.join(HERE, h) for h in ("svb_common.cuh", "svb_prof.cuh", "svb_geom.cuh")] + \
+          [os.path.join(os.path.dirname(PKG), "include", h) for h in ("svb200.h", "svb200_debug.h")]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-         "-shared", "-Xcompiler", "-fPIC,-ffp-contract=off", "--use_fast_math=false"]
+         "-Xcompiler", "-fPIC,-ffp-contract=off"]
+LINK_LIBS = ["-lnvToolsExt"] if os.path.isfile("/usr/local/cuda/lib64/libnvToolsExt.so") else []
+
+
+def _digest(src: str) -> str:
+    h = hashlib.sha256(" ".join(FLAGS).encode())
+    for p in [src] + [x for x in HEADERS if os.path.isfile(x)]:
+        with open(p, "rb") as f:
+            h.update(f.read())
+    return h.hexdigest()
+
+
+def _stale():
+    """sources whose object is missing or was built from other bytes"""
+    out = []
+    for s in SOURCES:
+        obj = os.path.join(OBJ_DIR, s[:-3] + ".o")
+        tag = obj + ".sha"
+        want = _digest(os.path.join(HERE, s))
+        if not (os.path.isfile(obj) and os.path.isfile(tag) and open(tag).read() == want):
+            out.append((s, obj, tag, want))
+    return out
 
 
 def needs_build() -> bool:
-    if not os.path.isfile(OUT):
-        return True
-    t = os.path.getmtime(OUT)
-    deps = [os.path.join(HERE, s) for s in SOURCES] + [os.path.join(HERE, "svb_common.cuh"), os.path.join(HERE, "svb_prof.cuh"),
-            os.path.join(os.path.dirname(PKG), "include", "svb200.h")]
-    return any(os.path.getmtime(d) > t for d in deps)
+    return not os.path.isfile(OUT) or bool(_stale())
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
-    if not force and not needs_build():
+    os.makedirs(OBJ_DIR, exist_ok=True)
+    if force:
+        for f in os.listdir(OBJ_DIR):
+            os.remove(os.path.join(OBJ_DIR, f))
+    todo = _stale()
+    if not todo and os.path.isfile(OUT):
         return OUT
-    flags = [f for f in FLAGS if not f.startswith("--use_fast_math")]
-    if verbose:
-        flags += ["-Xptxas", "-v"]
-    cmd = [NVCC] + flags + ["-o", OUT] + [os.path.join(HERE, s) for s in SOURCES]
-    r = subprocess.run(cmd, capture_output=True, text=True)
+    flags = FLAGS + (["-Xptxas", "-v"] if verbose else [])
+
+    def one(job):
+        s, obj, tag, want = job
+        r = subprocess.run([NVCC] + flags + ["-c", "-o", obj, os.path.join(HERE, s)], capture_output=True, text=True)
+        if r.returncode == 0:
+            with open(tag, "w") as f:
+                f.write(want)
+        return s, r
+
+    with ThreadPoolExecutor(max_workers=min(len(todo), os.cpu_count() or 1) or 1) as ex:
+        results = list(ex.map(one, todo))
+    for s, r in results:
+        if r.returncode != 0:
+            sys.stderr.write(r.stdout + r.stderr)
+            raise RuntimeError("nvcc failed on %s" % s)
+        if verbose:
+            print(r.stdout + r.stderr)
+    objs = [os.path.join(OBJ_DIR, s[:-3] + ".o") for s in SOURCES]
+    r = subprocess.run([NVCC, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", OUT] + objs + LINK_LIBS,
+                       capture_output=True, text=True)
     if r.returncode != 0:
         sys.stderr.write(r.stdout + r.stderr)
-        raise RuntimeError("nvcc failed building libsvb200.so")
-    if verbose:
-        print(r.stdout + r.stderr)
+        raise RuntimeError("linking libsvb200.so failed")
     return OUT
 
 

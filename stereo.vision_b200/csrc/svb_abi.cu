@@ -1,7 +1,7 @@
 // ABI bookkeeping: version and error strings.
 #include "svb_common.cuh"
 
-extern "C" int svb_version(void) { return 10; }
+extern "C" int svb_version(void) { return 11; }
 
 extern "C" const char *svb_error_string(int code) {
     switch (code) {
@@ -38,7 +38,7 @@ static const char *k_names[K_COUNT_] = {
     "clean_band", "pack_mask", "mask_points", "road_sites", "road_sites_scatter",
     "prep_gamma_gray", "prep_equalize_lut", "prep_apply_lut", "fill_row_mean", "normal_line", "road_hull", "hull_masks",
     "sgbm_prefilter", "sgbm_hsum", "sgbm_vsum", "sgbm_path_v", "sgbm_path_d1", "sgbm_path_d3", "sgbm_path_h", "sgbm_final",
-    "sgbm_median", "speckle", "disparity_scale"};
+    "sgbm_median", "speckle", "disparity_scale", "ransac_replay"};
 struct EvPair { int id; cudaEvent_t a, b; };
 static std::vector<EvPair> g_events;
 static cudaEvent_t g_pending[K_COUNT_];

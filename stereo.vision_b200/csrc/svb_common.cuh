@@ -9,6 +9,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include "../../include/svb200.h"
+#include "../../include/svb200_debug.h"
 
 #define SVB_MAX_DIM 2048
 

@@ -11,7 +11,7 @@ enum SvbKernelId {
     K_PACK_MASK, K_MASK_POINTS, K_ROAD_SITES, K_ROAD_SITES_SCATTER,
     K_PREP_GRAY, K_PREP_EQ_LUT, K_PREP_APPLY, K_FILL_MEAN, K_NORMAL_LINE, K_ROAD_HULL, K_HULL_MASKS,
     K_SGBM_PREFILTER, K_SGBM_HSUM, K_SGBM_VSUM, K_SGBM_PATH_V, K_SGBM_PATH_D1, K_SGBM_PATH_D3, K_SGBM_PATH_H, K_SGBM_FINAL,
-    K_SGBM_MEDIAN, K_SPECKLE, K_DISP_SCALE, K_COUNT_
+    K_SGBM_MEDIAN, K_SPECKLE, K_DISP_SCALE, K_RANSAC_REPLAY, K_COUNT_
 };
 
 void svb_prof_begin(int id, cudaStream_t st);

@@ -40,6 +40,7 @@ road_threshold_mask = default_road_threshold_mask((544, 1024))
 # ---- literals of the reference exposed as settings
 lattice_step = 2
 ransac_samples = 600
+ransac_replay = "device"      # where Python's `random` stream is replayed: "device" (svb_ransac_replay_draws) or "host"
 
 _state = {}
 
@@ -223,16 +224,44 @@ def _replay_draws(xyz, trials, S):
     return samp, trip
 
 
+def _device_draws(points, T, S, M):
+    """The same draws as _replay_draws, made on the device from random.getstate() (svb_ransac_replay_draws);
+    the global generator is left where the reference's RANSAC call would leave it (random.setstate)."""
+    lib, dev = N.load(), points.records.device
+    state = random.getstate()
+    if state[0] != 3:
+        raise N.SvbError("unexpected random.getstate() version %r" % (state[0],))
+    mt = torch.from_numpy(np.array(state[1], dtype=np.uint32).view(np.int32)).to(dev).view(1, 625)
+    si = torch.empty((1, T, S), dtype=torch.int32, device=dev)
+    ti = torch.empty((1, T, 3), dtype=torch.int32, device=dev)
+    nb = int(lib.svb_ransac_replay_scratch_bytes(1, S, M))
+    scratch = torch.empty((nb,), dtype=torch.uint8, device=dev)
+    counts = torch.tensor([[M]], dtype=torch.int32, device=dev)
+    cc = N.ccam(points.camera)
+    N.check(lib.svb_ransac_replay_draws(N.ptr(points.records), 2, 0, N.ptr(counts), 1, 0, 1, T, S, M, C.byref(cc), None,
+                                        N.ptr(mt), 0, N.ptr(si), N.ptr(ti), N.ptr(scratch), nb, N.stream_ptr()),
+            "svb_ransac_replay_draws")
+    N.count(1)
+    words = mt.cpu().numpy().view(np.uint32).reshape(-1)
+    random.setstate((3, tuple(int(v) for v in words), state[2]))
+    return si, ti
+
+
 def RANSAC(points, trials):
     """functions.py:278-298.  Returns (normal, coefficients): the same (3,1) float64 array twice, or
-    (None, None) when no trial produced a plane (e.g. fewer than `ransac_samples` points)."""
+    (None, None) when no trial produced a plane (e.g. fewer than `ransac_samples` points).  The draws are the
+    reference's: Python's global `random` stream, replayed on the device (`ransac_replay = "host"` keeps the
+    Python loop, its checker)."""
     _need_cloud(points)
     lib, S, T, M = N.load(), int(ransac_samples), int(trials), len(points)
     if M < S or T < 1:
         return (None, None)                   # random.sample raises in every trial, swallowed at :294
-    samp, trip = _replay_draws(points.xyz, T, S)
     dev = points.records.device
-    si, ti = torch.from_numpy(samp).to(dev), torch.from_numpy(trip).to(dev)
+    if ransac_replay == "host":
+        samp, trip = _replay_draws(points.xyz, T, S)
+        si, ti = torch.from_numpy(samp).to(dev), torch.from_numpy(trip).to(dev)
+    else:
+        si, ti = _device_draws(points, T, S, M)
     counts = torch.tensor([[M]], dtype=torch.int32, device=dev)
     errors = torch.empty((1, T), dtype=torch.float64, device=dev)
     planes = torch.zeros((1, N.PLANE_STRIDE), dtype=torch.float64, device=dev)
@@ -243,10 +272,10 @@ def RANSAC(points, trials):
                                     0, 0, N.ptr(errors), 0.0, N.ptr(planes), st), "svb_ransac_finalize")
     N.count(2)
     row = planes[0].cpu().numpy()
+    RANSAC.last = {"best_trial": int(row[6]), "best_error": float(row[5]), "errors": errors, "sample_idx": si, "triple_idx": ti}
     if row[7] == 0.0:
         return (None, None)
     abc = row[:3].reshape(3, 1).copy()
-    RANSAC.last = {"best_trial": int(row[6]), "best_error": float(row[5]), "errors": errors}
     return (abc, abc)
 
 

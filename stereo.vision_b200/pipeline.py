@@ -24,6 +24,18 @@ from .camera import DEFAULT_CAMERA, Camera
 KERNELS_PER_BATCH = 6      # fill+count, scan, write, score, finalize, road cluster kernel
 
 
+def _on_device(fn):
+    """Run a method with the object's device current: the library launches on the current device's stream, so an
+    engine built for cuda:1 must not launch on cuda:0 because the caller never called set_device."""
+    import functools
+
+    @functools.wraps(fn)
+    def wrapped(self, *a, **kw):
+        with torch.cuda.device(self.device):
+            return fn(self, *a, **kw)
+    return wrapped
+
+
 def _as_cuda_u8(x, device):
     if isinstance(x, np.ndarray):
         x = torch.from_numpy(np.ascontiguousarray(x))
@@ -48,6 +60,7 @@ class BatchResult:
         self.cloud = eng.cloud[:F]            # int64 [F,L] (uint64 records)
         self.mcloud = eng.mcloud[:F]          # int32 [F,L] (uint32 records)
         self.overlay = None
+        self.indices = None                   # (sample_idx, triple_idx) when the draws were explicit or replayed
 
     def abc(self):
         """Host float64 [F,3]; NaN rows where no plane was found (RANSAC -> (None, None))."""
@@ -66,6 +79,12 @@ class RoadPath:
         N.require_cuda()
         self.lib = N.load()
         self.device = torch.device(device)
+        with torch.cuda.device(self.device):
+            self._init(shape, step, trials, samples, point_threshold, colour_threshold, carmask, camera, max_frames,
+                       use_reproj_table, road_path)
+
+    def _init(self, shape, step, trials, samples, point_threshold, colour_threshold, carmask, camera, max_frames,
+              use_reproj_table, road_path):
         self.H, self.W = int(shape[0]), int(shape[1])
         self.step, self.T, self.S = int(step), int(trials), int(samples)
         self.point_threshold = float(point_threshold)
@@ -115,16 +134,34 @@ class RoadPath:
                            and bool(self.lib.svb_road_sites_supported(H, W, self.step)))
         if self.sites_road:
             self.road_launches = 2
+        self._si = self._ti = self._replay_scratch = None      # reference-identical draws (py_seeds): allocated on first use
 
     # ------------------------------------------------------------------
+    def _replay_buffers(self, F):
+        if self._si is None:
+            dev = self.device
+            self._si = torch.empty((self.Fmax, self.T, self.S), dtype=torch.int32, device=dev)
+            self._ti = torch.empty((self.Fmax, self.T, 3), dtype=torch.int32, device=dev)
+            nb = int(self.lib.svb_ransac_replay_scratch_bytes(self.Fmax, self.S, max(self.max_m, 1)))
+            self._replay_scratch = torch.empty((nb,), dtype=torch.uint8, device=dev)
+            self._mt = torch.empty((self.Fmax, 625), dtype=torch.int32, device=dev)
+        return self._si[:F], self._ti[:F]
+
+    @_on_device
     def process(self, disp, bgr, prev=None, seed=0, frame0=0, indices=None, overlay=None,
-                fill=True) -> BatchResult:
+                fill=True, py_seeds=None, py_stream=None) -> BatchResult:
         """Run the path on disp uint8 [F,H,W] + bgr uint8 [F,H,W,3].
 
         prev     : filled disparity of the frame before disp[0] (None at the start of a sequence);
         indices  : (sample_idx int32 [F,T,S], triple_idx int32 [F,T,3]) -> parity mode (explicit
                    draws, e.g. the replay of Python's `random`); None -> counter-based on-device
                    draws keyed by (seed, frame0 + t, trial);
+        py_seeds : F integers -> REFERENCE-IDENTICAL draws: frame t picks the hypotheses the reference picks after
+                   `random.seed(py_seeds[t])` (functions.py:286, 252-254), replayed on the device
+                   (svb_ransac_replay_draws); the generators' end states are left in self.mt_state [F,625];
+        py_stream: one integer seed, or a random.getstate() tuple -> ONE generator serves the F frames in order, as
+                   after `random.seed(s)` before loop.py's frame loop (sequential on the device: one warp);
+                   self.mt_state[0] then holds the end state (see mt_getstate) and can be passed on;
         overlay  : optional uint8 [F,H,W,3] CUDA tensor pre-filled with imgL; road sites get (0,255,0);
         fill     : False skips the temporal fill entirely (threshold_option other than 'previous').
         """
@@ -141,6 +178,10 @@ class RoadPath:
         if fill:
             # a1 + the counting pass of a4 in one kernel; the scratch carries the counts to the projection
             prev_t = _as_cuda_u8(prev, dev) if prev is not None else None
+            if prev_t is not None and tuple(prev_t.shape) != (H, W):
+                raise ValueError("prev is %s, the frames are %s" % (tuple(prev_t.shape), (H, W)))
+            if prev_t is not None and prev_t.untyped_storage().data_ptr() == self.filled.untyped_storage().data_ptr():
+                prev_t = prev_t.clone()     # result.filled[-1] of the last call: the fill kernel is about to overwrite it
             N.check(lib.svb_fill_sequence_counted(N.ptr(disp), N.ptr(prev_t), N.ptr(self.filled), N.ptr(self.carmask),
                                                   F, H, W, self.step, N.ptr(self.scratch), self.scratch.numel(), st),
                     "svb_fill_sequence_counted")
@@ -158,6 +199,23 @@ class RoadPath:
             ti = indices[1] if torch.is_tensor(indices[1]) else torch.from_numpy(np.ascontiguousarray(indices[1], dtype=np.int32))
             si = si.to(dev).contiguous().view(F, self.T, self.S)
             ti = ti.to(dev).contiguous().view(F, self.T, 3)
+        elif py_seeds is not None or py_stream is not None:
+            si, ti = self._replay_buffers(F)
+            chain = py_stream is not None
+            seeds_t = None
+            if chain and not isinstance(py_stream, int):
+                self.mt_setstate(py_stream)
+            else:
+                vals = [int(py_stream)] if chain else [int(v) for v in py_seeds]
+                if len(vals) != (1 if chain else F) or min(vals) < 0 or max(vals) >= 1 << 64:
+                    raise ValueError("py_seeds: one non-negative 64-bit integer per frame")
+                seeds_t = torch.tensor([v - (1 << 64) if v >= 1 << 63 else v for v in vals], dtype=torch.int64).to(dev)
+            N.check(lib.svb_ransac_replay_draws(N.ptr(self.mcloud), 1, self.L, N.ptr(self.counts), 4, 1, F, self.T, self.S,
+                                                max(self.max_m, 1), C.byref(self._cam), N.ptr(seeds_t), N.ptr(self._mt),
+                                                1 if chain else 0, N.ptr(si), N.ptr(ti), N.ptr(self._replay_scratch),
+                                                self._replay_scratch.numel(), st), "svb_ransac_replay_draws")
+            N.count(1)
+        res.indices = (si, ti) if si is not None else None
         N.check(lib.svb_ransac_score(N.ptr(self.mcloud), 1, self.L, N.ptr(self.counts), 4, 1, F, self.T, self.S,
                                      self.max_m, C.byref(self._cam), N.ptr(si), N.ptr(ti), seed, frame0, N.ptr(self.errors), st),
                 "svb_ransac_score")
@@ -181,6 +239,24 @@ class RoadPath:
         N.count(KERNELS_PER_BATCH - 1 + self.road_launches + (0 if fill else 2))   # no fill: copy + count kernels
         return res
 
+    # the generator state of the reference-identical mode, in random.getstate() / setstate() form
+    @property
+    def mt_state(self):
+        return self._mt
+
+    def mt_setstate(self, state, row=0):
+        self._replay_buffers(1)
+        ver, words, _ = state
+        if ver != 3 or len(words) != 625:
+            raise ValueError("expected a random.getstate() tuple")
+        w = np.array(words, dtype=np.uint32).view(np.int32)
+        self._mt[row].copy_(torch.from_numpy(w))
+
+    def mt_getstate(self, row=0):
+        w = self._mt[row].cpu().numpy().view(np.uint32)
+        return (3, tuple(int(v) for v in w), None)
+
+    @_on_device
     def dump_indices(self, F, seed=0, frame0=0):
         """The counter-based draws the last process() call used (for the oracle): int32 [F,T,S], [F,T,3]."""
         si = torch.empty((F, self.T, self.S), dtype=torch.int32, device=self.device)
@@ -236,8 +312,10 @@ class SequenceStreamer:
                     "svb_upload_rows")
         return n * LH * row
 
-    def run(self, disp, bgr, seed=0, out=None):
+    @_on_device
+    def run(self, disp, bgr, seed=0, out=None, py_seeds=None):
         """disp uint8 [F,H,W], bgr uint8 [F,H,W,3]: CPU tensors (pin them for asynchronous copies).
+        py_seeds: F integers -> the reference's own draws per frame (RoadPath.process), else device draws keyed by `seed`.
         Returns dict(road_mask uint8 [F,H,W], planes float64 [F,8], counts int32 [F,4]) of pinned CPU tensors
         (pass the previous result as `out` to reuse them).  Asynchronous: the current stream waits for the
         result; synchronise (or use run_sync) before reading it on the host."""
@@ -275,7 +353,8 @@ class SequenceStreamer:
                 if busy_out is not None:
                     s_cmp.wait_event(busy_out)                # engine k's outputs were read back
                 prev = self.engines[1 - k].filled[chunks[i - 1][1] - chunks[i - 1][0] - 1] if i else None
-                r = self.engines[k].process(self.din[k][:n], self.cin[k][:n], prev=prev, seed=seed, frame0=a)
+                r = self.engines[k].process(self.din[k][:n], self.cin[k][:n], prev=prev, seed=seed, frame0=a,
+                                            py_seeds=None if py_seeds is None else py_seeds[a:b])
                 ev_cmp[i] = torch.cuda.Event()
                 ev_cmp[i].record(s_cmp)
             with torch.cuda.stream(s_out):
@@ -292,8 +371,8 @@ class SequenceStreamer:
         self._last = out
         return out
 
-    def run_sync(self, disp, bgr, seed=0, out=None):
-        out = self.run(disp, bgr, seed=seed, out=out)
+    def run_sync(self, disp, bgr, seed=0, out=None, py_seeds=None):
+        out = self.run(disp, bgr, seed=seed, out=out, py_seeds=py_seeds)
         torch.cuda.synchronize(self.device)
         return out
 
@@ -334,6 +413,7 @@ class RoadCleaner:
         self.points = torch.empty((F, max(self.cap, 1), 2), dtype=torch.int32, device=dev)
         self.status = torch.zeros((1,), dtype=torch.int32, device=dev)
 
+    @_on_device
     def clean(self, masks, points=True):
         masks = _as_cuda_u8(masks, self.device)
         if masks.dim() == 2:
@@ -354,6 +434,7 @@ class RoadCleaner:
         self._last = F
         return cleaned, self.counts[:F], self.points[:F]
 
+    @_on_device
     def obstacles(self, masks=True, hull_cap=512):
         """The obstacle stage (stereovision.py:170-200) of the frames of the last clean(): svb_road_hull,
         two kernels (one without masks).  Returns a dict of device tensors: hull [F,hull_cap,2] int32 (x,y) with hull_n [F]
@@ -407,6 +488,7 @@ class FrontEnd:
         self.hist = torch.empty((F, 256), dtype=torch.int32, device=dev)
         self.lut = torch.empty((F, 256), dtype=torch.uint8, device=dev)
 
+    @_on_device
     def process(self, bgr):
         """bgr uint8 [F,H,W,3] -> (gamma-corrected bgr [F,H,W,3], equalised gray [F,H,W]) device tensors."""
         bgr = _as_cuda_u8(bgr, self.device)
@@ -447,6 +529,7 @@ class Matcher:
         self.disp16 = torch.empty((self.F, self.H, self.W), dtype=torch.int16, device=self.device)
         self.disp8 = torch.empty((self.F, self.H, self.W), dtype=torch.uint8, device=self.device)
 
+    @_on_device
     def compute(self, grayL, grayR):
         """stereoProcessor.compute for F pairs: int16 [F,H,W], disparity x 16, -16 = no match."""
         L, R = _as_cuda_u8(grayL, self.device), _as_cuda_u8(grayR, self.device)
@@ -462,6 +545,7 @@ class Matcher:
         N.count(8 * ((F + in_flight - 1) // in_flight))      # per chunk: prefilter, hsum, vsum_v, d1, d3, h, final, median
         return self.disp16[:F]
 
+    @_on_device
     def disparity(self, grayL, grayR):
         """functions.disparity for F pairs: uint8 [F,H,W] in half pixels, 0 = no match (crop: a view the caller takes)."""
         d16 = self.compute(grayL, grayR)

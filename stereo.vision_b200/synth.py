@@ -21,6 +21,13 @@ def ransac_seed(seq: int, frame: int) -> int:
     return 100003 * int(seq) + int(frame)
 
 
+def true_plane(seq: int, frame: int):
+    """(a, b, c) of the road plane a*X + b*Y + c*Z = 1 that make_frame renders for this frame"""
+    rng = np.random.default_rng(frame_seed(seq, frame))
+    jit = 1.0 + 0.05 * (rng.random(3) * 2.0 - 1.0)
+    return np.array([0.02 * jit[0] * (1 if (seq + frame) % 2 == 0 else -1), (1.0 / 0.6) * jit[1], 0.03 * jit[2]])
+
+
 def make_frame(seq: int, frame: int, shape=(544, 1024), camera: Camera = None, holes: float = 0.10):
     """Return (disparity uint8 [H,W], bgr uint8 [H,W,3]) of one synthetic frame.
 

@@ -1,0 +1,170 @@
+"""BASELINE.json's configurations at their real sizes: the 300-frame chained sequence (config 2) frame by frame
+against the oracle, resident and streamed; the overlay half of a14; the 10 000 x 4 000 corner of config 5;
+and the per-sequence result hash that bench.py prints per rank (config 4)."""
+import hashlib
+
+import numpy as np
+import pytest
+
+import np_oracle as no
+import stereo.vision_b200.synth as synth
+from helpers import check_frame, oracle_sequence, to_host
+
+pytestmark = pytest.mark.gpu
+
+
+def _carmask(shape):
+    from stereo.vision_b200.masks import default_carmask
+    return default_carmask(shape, prefer_cwd=False)
+
+
+def _make_sequence_parallel(seq, F, shape=(544, 1024)):
+    import multiprocessing as mp
+    import os
+    H, W = shape
+    disp = np.empty((F, H, W), np.uint8)
+    bgr = np.empty((F, H, W, 3), np.uint8)
+    with mp.get_context("fork").Pool(min(16, os.cpu_count() or 1)) as pool:
+        for t, (d, c) in enumerate(pool.starmap(synth.make_frame, [(seq, t, shape) for t in range(F)], chunksize=4)):
+            disp[t], bgr[t] = d, c
+    return disp, bgr
+
+
+def _oracle_frame(args):
+    d, c, prev_filled, cm, si, ti, T, S = args
+    # the temporal fill is recomputed by the caller's chain; here the frame is judged on its own filled disparity
+    o = no.run_frame(d, c, prev_filled, cm, indices=(si, ti), trials=T, n_samples=S)
+    rd = o["road"]
+    return {"filled": o["filled"], "N": len(o["cloud"]["d"]), "M": len(o["mcloud"]["d"]), "best": o["best"], "abc": o["abc"],
+            "K": rd["near_n"], "R": rd["road_n"], "mask": np.packbits(rd["mask"]), "hist": rd["hist"]}
+
+
+def test_config2_300_chained_frames_resident_and_streamed(cuda):
+    """loop.py:57-78 at its real length: one 300-frame sequence (previous-disparity fill chained through all of
+    it), (a) resident in one RoadPath.process call and (b) through SequenceStreamer.run in chunks of 30 (ten
+    chunk boundaries), EVERY frame compared with the oracle: filled disparity, N, M, the winning hypothesis and
+    plane, K, the hue histogram, R and the road mask.  Draws: the reference's own (`random.seed(ransac_seed)` per
+    frame, replayed on the device; 12 frames of them are checked against CPython directly)."""
+    import multiprocessing as mp
+    import os
+    import random
+    import torch
+    from stereo.vision_b200.pipeline import RoadPath, SequenceStreamer
+    F, T, S, seq = 300, 600, 400, 6
+    disp, bgr = _make_sequence_parallel(seq, F)
+    cm = _carmask(disp.shape[1:])
+    seeds = [synth.ransac_seed(seq, t) for t in range(F)]
+    eng = RoadPath(trials=T, samples=S, carmask=cm, max_frames=F)
+    r = eng.process(disp, bgr, py_seeds=seeds)
+    si, ti = (a.cpu().numpy() for a in r.indices)
+    res = to_host(r)
+    del r
+    # the chain of filled disparities (a1) is sequential; everything else of a frame is independent given it
+    filled = [None] * F
+    prev = None
+    for t in range(F):
+        prev = filled[t] = no.fill_disparity(disp[t], prev)
+        assert np.array_equal(res["filled"][t], prev), "filled disparity, frame %d" % t
+    for t in range(0, F, 25):                                   # the replayed draws against CPython itself
+        mc = no.project(no.mask_disparity(filled[t], cm))
+        rng = random.Random()
+        rng.seed(seeds[t])
+        ws, wt = no.replay_indices(mc["xyz"], T, S, rng=rng)
+        assert np.array_equal(si[t], ws) and np.array_equal(ti[t], wt), "draws of frame %d" % t
+    jobs = [(disp[t], bgr[t], filled[t - 1] if t else None, cm, si[t], ti[t], T, S) for t in range(F)]
+    with mp.get_context("fork").Pool(min(16, os.cpu_count() or 1)) as pool:
+        orc = pool.map(_oracle_frame, jobs, chunksize=4)
+    for t, o in enumerate(orc):
+        N_, M_, K_, R_ = (int(v) for v in res["counts"][t])
+        assert (N_, M_, K_, R_) == (o["N"], o["M"], o["K"], o["R"]), ("counts, frame %d" % t, (N_, M_, K_, R_), o)
+        assert int(res["planes"][t][6]) == o["best"], "winning hypothesis, frame %d" % t
+        np.testing.assert_allclose(res["planes"][t][:3], o["abc"], rtol=1e-9, atol=1e-13 * float(np.linalg.norm(o["abc"])))
+        assert np.array_equal(res["hist"][t][:no.HUE_BINS].astype(np.int64), o["hist"]), "hue histogram, frame %d" % t
+        assert np.array_equal(np.packbits(res["road_mask"][t]), o["mask"]), "road mask, frame %d" % t
+    assert res["planes"][:, 7].all() and res["road_mask"].any()
+    # (b) streamed: 10 chunks of 30, same seeds
+    del eng
+    torch.cuda.empty_cache()
+    sr = SequenceStreamer(trials=T, samples=S, carmask=cm, chunk=30)
+    out = sr.run_sync(torch.from_numpy(disp).pin_memory(), torch.from_numpy(bgr).pin_memory(), py_seeds=seeds)
+    assert np.array_equal(out["counts"].numpy(), res["counts"])
+    assert np.array_equal(out["planes"].numpy(), res["planes"])
+    assert np.array_equal(out["road_mask"].numpy(), res["road_mask"])
+    # ... and the throughput mode's draws give the same results streamed as resident (keyed by the frame number)
+    eng = RoadPath(trials=T, samples=S, carmask=cm, max_frames=F)
+    dev = to_host(eng.process(disp, bgr, seed=20260000))
+    out = sr.run_sync(torch.from_numpy(disp).pin_memory(), torch.from_numpy(bgr).pin_memory(), seed=20260000)
+    assert np.array_equal(out["counts"].numpy(), dev["counts"])
+    assert np.array_equal(out["planes"].numpy(), dev["planes"])
+    assert np.array_equal(out["road_mask"].numpy(), dev["road_mask"])
+
+
+@pytest.mark.parametrize("road_path", ["sites", "records"])
+def test_overlay_image_road_map(cuda, road_path):
+    """stereovision.py:131-133: imageRoadMap = imgL.copy(); imageRoadMap[y][x] = [0,255,0] for every road point"""
+    import torch
+    from stereo.vision_b200.pipeline import RoadPath
+    F, T, S = 3, 300, 400
+    disp, bgr = synth.make_sequence(11, F)
+    cm = _carmask(disp.shape[1:])
+    eng = RoadPath(trials=T, samples=S, carmask=cm, max_frames=F, road_path=road_path)
+    ov = torch.from_numpy(bgr).to(cuda).clone()
+    r = eng.process(disp, bgr, seed=8, overlay=ov)
+    si, ti = eng.dump_indices(F, seed=8)
+    res = to_host(r)
+    got = r.overlay.cpu().numpy()
+    orc = oracle_sequence(disp, bgr, cm, indices=(si.cpu().numpy(), ti.cpu().numpy()), trials=T, n_samples=S)
+    for t in range(F):
+        check_frame(res, t, orc[t])
+        want = bgr[t].copy()
+        for x, y in orc[t]["road"]["pts"]:                      # the reference's loop, point by point
+            want[y][x] = [0, 255, 0]
+        assert orc[t]["road"]["road_n"] > 1000
+        assert np.array_equal(got[t], want), "Image Road Map, frame %d" % t
+
+
+def test_config5_corner_10000_hypotheses_4000_samples(cuda):
+    """BASELINE config 5's far corner: one 2048x1088 frame, 10 000 hypotheses x 4 000 samples -- with the reference's
+    draws (random.seed, replayed on the device; set path with a 16 405-entry setsize) and with device draws."""
+    import random
+    from stereo.vision_b200.pipeline import RoadPath
+    shape, T, S = (1088, 2048), 10000, 4000
+    disp, bgr = synth.make_sequence(12, 1, shape=shape)
+    cm = _carmask(shape)
+    eng = RoadPath(shape=shape, step=2, trials=T, samples=S, carmask=cm, max_frames=1)
+    r = eng.process(disp, bgr, py_seeds=[31337])
+    si, ti = (a.cpu().numpy() for a in r.indices)
+    res = to_host(r)
+    mc = no.project(no.mask_disparity(disp[0], cm))
+    rng = random.Random()
+    rng.seed(31337)
+    ws, wt = no.replay_indices(mc["xyz"][:, :], 40, S, rng=rng)          # the first 40 trials against CPython (2 s)
+    assert np.array_equal(si[0][:40], ws) and np.array_equal(ti[0][:40], wt)
+    orc = oracle_sequence(disp, bgr, cm, indices=(si, ti), trials=T, n_samples=S)
+    check_frame(res, 0, orc[0])
+    r = eng.process(disp, bgr, seed=5)
+    si, ti = eng.dump_indices(1, seed=5)
+    res = to_host(r)
+    orc = oracle_sequence(disp, bgr, cm, indices=(si.cpu().numpy(), ti.cpu().numpy()), trials=T, n_samples=S)
+    check_frame(res, 0, orc[0])
+    assert res["planes"][0, 7] == 1.0
+
+
+def test_result_hash_is_the_single_gpu_hash(cuda):
+    """a rank's results must be the single-GPU results for the same sequence id.  bench.py prints
+    shard.result_sha per rank; tests/golden/result_sha.json holds the hashes of sequences 0-7 (32 frames, the
+    oracle's masks, planes' winning trials and counts, made by oracle/make_result_sha.py on the CPU), so every rank of
+    a multi-GPU run is compared with a value no GPU produced."""
+    import json
+    import os
+    import stereo.vision_b200.shard as shard
+    from stereo.vision_b200.pipeline import RoadPath
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "result_sha.json")
+    gold = json.load(open(path))
+    F, T, S = gold["frames"], gold["trials"], gold["samples"]
+    cm = _carmask((544, 1024))
+    eng = RoadPath(trials=T, samples=S, carmask=cm, max_frames=F)
+    for seq in (0, 3, 7):
+        disp, bgr = synth.make_sequence(seq, F)
+        r = eng.process(disp, bgr, py_seeds=[synth.ransac_seed(seq, t) for t in range(F)])
+        assert shard.result_sha(r.road_mask, r.planes, r.counts) == gold["sha"][str(seq)], seq

@@ -1,0 +1,179 @@
+"""The reference-identical RANSAC mode at speed: CPython's `random` stream replayed on the device
+(svb_ransac_replay_draws) against CPython itself, and the statistics of the throughput mode's
+counter-based draws against it (functions.py:286, 252-254)."""
+import random
+
+import numpy as np
+import pytest
+
+import np_oracle as no
+import stereo.vision_b200.synth as synth
+from helpers import check_frame, oracle_sequence, to_host
+
+pytestmark = pytest.mark.gpu
+
+
+def _carmask(shape):
+    from stereo.vision_b200.masks import default_carmask
+    return default_carmask(shape, prefer_cwd=False)
+
+
+def _python_draws(rng, mask_xyz, T, S):
+    """(sample_idx, triple_idx) drawn from `rng` exactly as functions.py:286,252-259 consume it"""
+    return no.replay_indices(mask_xyz, T, S, rng=rng)
+
+
+def _state_words(rng):
+    return np.array(rng.getstate()[1], dtype=np.uint32)
+
+
+@pytest.mark.parametrize("S", [400, 600])
+def test_replay_equals_cpython_per_frame_seeds(cuda, S):
+    """set path (M ~ 28 k > setsize): indices, triples and the generator's end state, frame by frame"""
+    from stereo.vision_b200.pipeline import RoadPath
+    F, T = 3, 600
+    disp, bgr = synth.make_sequence(2, F)
+    cm = _carmask(disp.shape[1:])
+    seeds = [synth.ransac_seed(2, t) for t in range(F - 1)] + [(1 << 40) + 12345]      # a two-digit key as well
+    eng = RoadPath(trials=T, samples=S, carmask=cm, max_frames=F)
+    r = eng.process(disp, bgr, py_seeds=seeds)
+    si, ti = (a.cpu().numpy() for a in r.indices)
+    res = to_host(r)
+    prev = None
+    want_s, want_t = [], []
+    for t in range(F):
+        filled = no.fill_disparity(disp[t], prev)
+        prev = filled
+        mc = no.project(no.mask_disparity(filled, cm))
+        rng = random.Random()
+        rng.seed(seeds[t])
+        ws, wt = _python_draws(rng, mc["xyz"], T, S)
+        assert np.array_equal(si[t], ws), "sample indices, frame %d" % t
+        assert np.array_equal(ti[t], wt), "triple indices, frame %d" % t
+        assert np.array_equal(eng.mt_state[t].cpu().numpy().view(np.uint32), _state_words(rng)), "end state, frame %d" % t
+        want_s.append(ws)
+        want_t.append(wt)
+    orc = oracle_sequence(disp, bgr, cm, indices=(np.stack(want_s), np.stack(want_t)), trials=T, n_samples=S)
+    for t in range(F):
+        check_frame(res, t, orc[t])
+
+
+def test_replay_chained_stream(cuda):
+    """one generator for the whole sequence (random.seed once, then loop.py's frame loop), handed on through getstate"""
+    from stereo.vision_b200.pipeline import RoadPath
+    F, T, S = 4, 200, 600
+    disp, bgr = synth.make_sequence(5, F)
+    cm = _carmask(disp.shape[1:])
+    eng = RoadPath(trials=T, samples=S, carmask=cm, max_frames=F)
+    r = eng.process(disp[:2], bgr[:2], py_stream=777)
+    si0, ti0 = (a.cpu().numpy().copy() for a in r.indices)
+    state = eng.mt_getstate()
+    filled1 = r.filled[1].clone()
+    r = eng.process(disp[2:], bgr[2:], prev=filled1, py_stream=state)
+    si1, ti1 = (a.cpu().numpy() for a in r.indices)
+    si, ti = np.concatenate([si0, si1]), np.concatenate([ti0, ti1])
+    rng = random.Random()
+    rng.seed(777)
+    prev = None
+    for t in range(F):
+        filled = no.fill_disparity(disp[t], prev)
+        prev = filled
+        mc = no.project(no.mask_disparity(filled, cm))
+        ws, wt = _python_draws(rng, mc["xyz"], T, S)
+        assert np.array_equal(si[t], ws) and np.array_equal(ti[t], wt), "frame %d" % t
+    assert eng.mt_getstate()[1] == rng.getstate()[1]
+
+
+@pytest.mark.parametrize("shape,step,S,keep", [((64, 96), 1, 40, 0.04), ((64, 96), 1, 40, 0.9), ((37, 53), 2, 5, 0.5),
+                                               ((37, 53), 1, 6, 0.012), ((48, 80), 2, 300, 1.0)])
+def test_replay_small_clouds(cuda, shape, step, S, keep):
+    """pool path (M <= setsize), the switch between the paths, k <= 5, M < S (nothing drawn), collinear redraws"""
+    import ctypes as C
+    import torch
+    import stereo.vision_b200._native as N
+    from stereo.vision_b200.pipeline import RoadPath
+    rng0 = np.random.default_rng(11)
+    F, T = 4, 50
+    H, W = shape
+    disp = rng0.integers(1, 9, size=(F, H, W), dtype=np.uint8)          # few disparity levels: many exactly collinear triples
+    disp[3] = 0                                                         # a frame without points
+    bgr = rng0.integers(0, 256, size=(F, H, W, 3), dtype=np.uint8)
+    cm = (rng0.random((H, W)) < keep).astype(np.uint8) * 255
+    eng = RoadPath(shape=shape, step=step, trials=T, samples=S, carmask=cm, max_frames=F, point_threshold=0.5, colour_threshold=0)
+    seeds = [5, 6, 7, 8]
+    r = eng.process(disp, bgr, py_seeds=seeds, fill=False)
+    si, ti = (a.cpu().numpy() for a in r.indices)
+    res = to_host(r)
+    lib = N.load()
+    seen_pool = seen_set = False
+    for t in range(F):
+        mc = no.project(no.mask_disparity(disp[t], cm), step=step)
+        M = len(mc["d"])
+        rng = random.Random()
+        rng.seed(seeds[t])
+        ws, wt = _python_draws(rng, mc["xyz"], T, S)
+        assert np.array_equal(si[t], ws) and np.array_equal(ti[t], wt), ("frame", t, "M", M)
+        assert np.array_equal(eng.mt_state[t].cpu().numpy().view(np.uint32), _state_words(rng))
+        if M >= S:
+            seen_pool |= M <= lib.svb_pyrandom_setsize(S)
+            seen_set |= M > lib.svb_pyrandom_setsize(S)
+    assert seen_pool or seen_set
+
+
+def test_dropin_ransac_device_draws_equal_host_replay(cuda):
+    """functions.RANSAC with the stream replayed on the device: same plane, same draws, and Python's global generator
+    left exactly where the host loop (and so the reference) leaves it"""
+    import stereo.vision_b200.functions as f
+    disp, bgr = synth.make_sequence(0, 1)
+    f.carmask = _carmask(disp.shape[1:])
+    pts = f.projectDisparityTo3d(f.maskDisparity(disp[0]), 128)
+    out = {}
+    for mode in ("host", "device"):
+        f.ransac_replay = mode
+        random.seed(4242)
+        random.random()                                   # a generator that is mid-block when RANSAC starts
+        normal, abc = f.RANSAC(pts, 120)
+        out[mode] = (abc.copy(), f.RANSAC.last["best_trial"], f.RANSAC.last["sample_idx"].cpu().numpy().reshape(120, -1),
+                     f.RANSAC.last["triple_idx"].cpu().numpy().reshape(120, 3), random.getstate())
+    f.ransac_replay = "device"
+    a, b = out["host"], out["device"]
+    assert np.array_equal(a[2], b[2]) and np.array_equal(a[3], b[3])
+    assert a[1] == b[1] and np.array_equal(a[0], b[0])
+    assert a[4] == b[4], "random.getstate() after RANSAC"
+
+
+def test_device_draws_are_statistically_the_references(cuda):
+    """The throughput mode draws a systematic sample per trial instead of random.sample's.  Over 240 frames (8
+    sequences x 30 chained frames) the observables that depend on the draws -- the winner's mean error, K (near
+    points), R (road points), the angle between the fitted and the rendered road plane -- must be distributed as
+    with the reference's own draws (two-sample Kolmogorov-Smirnov, p > 0.01), and both modes must find the road
+    (median angle below 3 degrees; the oracle with Python's draws gives 0.1 - 2.1 degrees on these frames)."""
+    from scipy.stats import ks_2samp
+    from stereo.vision_b200.pipeline import RoadPath
+    NSEQ, F, T, S = 8, 30, 600, 400
+    cm = _carmask((544, 1024))
+    eng = RoadPath(trials=T, samples=S, carmask=cm, max_frames=F)
+    obs = {"ref": [], "dev": []}
+    for seq in range(NSEQ):
+        disp, bgr = synth.make_sequence(20 + seq, F)
+        truth = np.stack([synth.true_plane(20 + seq, t) for t in range(F)])
+        truth /= np.linalg.norm(truth, axis=1, keepdims=True)
+        for mode in ("ref", "dev"):
+            if mode == "ref":
+                r = eng.process(disp, bgr, py_seeds=[synth.ransac_seed(20 + seq, t) for t in range(F)])
+            else:
+                r = eng.process(disp, bgr, seed=99 + seq)
+            pl = r.planes.cpu().numpy()
+            cn = r.counts.cpu().numpy()
+            assert (pl[:, 7] == 1.0).all()
+            ang = np.degrees(np.arccos(np.clip(np.abs(((pl[:, :3] / pl[:, 3:4]) * truth).sum(axis=1)), 0, 1)))
+            obs[mode].append(np.stack([pl[:, 5], cn[:, 2].astype(np.float64), cn[:, 3].astype(np.float64), ang], axis=1))
+    ref, dev = np.concatenate(obs["ref"]), np.concatenate(obs["dev"])
+    report = {}
+    for k, name in enumerate(("best_error", "K", "R", "angle_deg")):
+        report[name] = (float(ks_2samp(ref[:, k], dev[:, k]).pvalue), float(np.median(ref[:, k])), float(np.median(dev[:, k])))
+    print("KS p-value, median with the reference's draws, median with device draws:", report)
+    for name, (p, _, _) in report.items():
+        assert p > 0.01, (name, report)
+    for m in (ref, dev):
+        assert np.median(m[:, 3]) < 3.0 and (m[:, 3] < 6.0).mean() > 0.95, report

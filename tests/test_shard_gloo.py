@@ -19,8 +19,12 @@ WORKER = textwrap.dedent("""
     shard.barrier()
     mx = shard.max_over_ranks(ms)
     frames = shard.sum_over_ranks([7.0])
+    import numpy as np
+    planes = np.zeros((1, 8)); planes[0, 6] = rank; planes[0, 7] = 1.0
+    mine = shard.result_sha((d > 40).astype(np.uint8) * 255, planes, np.full((1, 4), seq, np.int32))
+    everyone = shard.gather_strings(mine)
     print(json.dumps({"rank": rank, "world": world, "seq": seq, "sha": hashlib.sha256(d.tobytes()).hexdigest(),
-                      "max": mx, "frames": frames}), flush=True)
+                      "max": mx, "frames": frames, "result_sha": mine, "gathered": everyone}), flush=True)
     shard.finish()
 """) % ROOT
 
@@ -42,3 +46,5 @@ def test_two_ranks_gloo(tmp_path):
     assert [o["seq"] for o in outs] == [0, 1] and outs[0]["sha"] != outs[1]["sha"]
     for o in outs:
         assert o["world"] == 2 and o["max"] == [15.0, 3.0] and o["frames"] == [14.0]
+        assert o["gathered"] == [outs[0]["result_sha"], outs[1]["result_sha"]]      # every rank sees every rank's hash
+    assert len(outs[0]["result_sha"]) == 64 and outs[0]["result_sha"] != outs[1]["result_sha"]
