@@ -68,7 +68,58 @@ def make_sequence_parallel(seq, n_frames, workers):
     return disp, bgr
 
 
-# ------------------------------------------------------------------ CPU arm: the oracle port
+# ------------------------------------------------------------------ CPU arm: the reference itself, else the oracle port
+def _reference_kind(samples, step):
+    """ "reference": oracle/_ref holds the reference's own byte code (oracle/build_ref.py) for this configuration;
+    "port": the numpy restatement (oracle/np_oracle.py)."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    try:
+        import ref_compiled as rc
+        if rc.available() and samples in (400, 600) and step == 2:
+            return "reference"
+    except Exception:
+        pass
+    return "port"
+
+
+def _reference_chain(job):
+    """`n` chained frames of sequence `seq` through the REFERENCE's helpers in the orchestrator's order
+    (stereovision.py:58-140; functions.py compiled to byte code by oracle/build_ref.py); returns seconds spent."""
+    seq, n, trials, samples, step = job
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import random
+    import warnings
+    import ref_compiled as rc
+    import stereo.vision_b200.synth as synth
+    f = rc.load_functions(samples)
+    frames = [synth.make_frame(seq, t, (H, W)) for t in range(n)]
+    prev = None
+    t0 = time.perf_counter()
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        for t, (disparity, imgL) in enumerate(frames):
+            random.seed(synth.ransac_seed(seq, t))
+            disparity = f.disparityCleaning(disparity.copy(), 'previous', prev)          # :58
+            prev = disparity                                                              # :60
+            maskedDisparity = f.maskDisparity(disparity)                                  # :74
+            cappedDisparity = f.capDisparity(disparity)                                   # :76
+            points = f.projectDisparityTo3d(cappedDisparity, 128, imgL)                   # :84
+            maskpoints = f.projectDisparityTo3d(maskedDisparity, 128)                     # :85
+            planePoints = []
+            try:
+                normal, abc = f.RANSAC(maskpoints, trials)                                # :94
+                pointDifferences = f.calculatePointErrors(abc, points)                    # :97
+                points = f.computePlanarThreshold(points, pointDifferences, 0.05)         # :100
+                histogram = f.calculateColourHistogram(points)                            # :103
+                points = f.filterPointsByHistogram(points, histogram, 10)                 # :106
+                planePoints = f.project3DPointsTo2DImagePoints(points)                    # :111
+                planePoints = np.array(planePoints, np.int32).reshape((-1, 1, 2))         # :112-113
+            except Exception:
+                pass
+            f.generatePointsAsImage(planePoints)                                          # :140
+    return time.perf_counter() - t0
+
+
 def _oracle_chain(job):
     """Run `n` chained frames of sequence `seq` through the numpy oracle; returns seconds spent."""
     seq, n, trials, samples, step = job
@@ -86,18 +137,25 @@ def _oracle_chain(job):
     return time.perf_counter() - t0
 
 
-def cpu_oracle_throughput(frames_per_proc, procs, trials, samples, step):
-    """frames/s of the oracle port with one independent sequence per process."""
+def cpu_throughput(kind, frames_per_proc, procs, trials, samples, step):
+    """frames/s of the CPU arm with one independent sequence per process."""
     import multiprocessing as mp
+    fn = _reference_chain if kind == "reference" else _oracle_chain
     jobs = [(1000 + p, frames_per_proc, trials, samples, step) for p in range(procs)]
     if procs == 1:
-        times = [_oracle_chain(jobs[0])]
+        times = [fn(jobs[0])]
     else:
         with mp.get_context("fork").Pool(procs) as pool:
-            times = pool.map(_oracle_chain, jobs)
-    # every worker times only its oracle calls (frame synthesis excluded); the job ends with the slowest
+            times = pool.map(fn, jobs)
+    # every worker times only its helper calls (frame synthesis excluded); the job ends with the slowest
     wall = max(times)
     return frames_per_proc * procs / wall, wall
+
+
+def cpu_sample_text(kind, procs, fpp, wall):
+    what = ("the reference's own helpers (functions.py compiled to byte code under oracle/_ref/, stereovision.py:58-140's order, "
+            "random.seed per frame)" if kind == "reference" else "oracle/np_oracle.py (numpy float64 restatement)")
+    return "%d independent sequences x %d chained frames through %s, one process per core, %.1f s wall" % (procs, fpp, what, wall)
 
 
 # ------------------------------------------------------------------ clocks during the timed region
@@ -349,6 +407,44 @@ def run_b200(args):
             "mean_road_points": float(o["counts"][:MF].float().mean().item())}
         del sp, bl, br
 
+    # ---- result identity: this rank's hash of the step's results; rank 0 compares every rank's with the
+    # single-GPU hashes of tests/golden/bench_sha.json (tools/make_bench_sha.py, one GPU, sequences 0-7)
+    my_sha = shard.result_sha(res.road_mask, res.planes, res.counts) + ":" + shard.planes_sha(res.planes)[:16]
+
+    # ---- the reference-identical mode: hypotheses = what `random.seed(ransac_seed(seq, t)); RANSAC(...)` draws in the
+    # reference, replayed on the device (svb_ransac_replay_draws), everything else as in `value`
+    parity = None
+    if rank == 0 and not args.path_only:
+        import stereo.vision_b200.synth as synth
+        seeds = [synth.ransac_seed(shard.sequence_of_rank(rank), t) for t in range(F)]
+        for _ in range(2):
+            rp = eng.process(disp_d, bgr_d, prev=None, py_seeds=seeds)
+        torch.cuda.synchronize()
+        N.profile_enable(True)
+        p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        p0.record()
+        for _ in range(3):
+            rp = eng.process(disp_d, bgr_d, prev=None, py_seeds=seeds)
+        p1.record()
+        torch.cuda.synchronize()
+        pprof = N.profile_read()
+        N.profile_enable(False)
+        p_ms = p0.elapsed_time(p1) / 3
+        parity = {"row": "reference-identical hypotheses: CPython's random stream under random.seed(100003 seq + t) per frame, replayed on the "
+                         "device; same %d-frame resident sequence" % F,
+                  "frames_per_s": round(F / (p_ms * 1e-3), 1), "ms_per_step": round(p_ms, 4),
+                  "kernels_ms": {k: round(v[0] / v[1], 5) for k, v in pprof.items()},
+                  "result_sha": shard.result_sha(rp.road_mask, rp.planes, rp.counts),
+                  "frames_with_plane": int((rp.planes[:, 7] > 0).sum().item())}
+        eng._si = eng._ti = eng._replay_scratch = None          # 290 MB of index buffers back to the allocator
+        del rp
+        torch.cuda.empty_cache()
+
+    # ---- the other configurations of BASELINE.json (single GPU; not part of `value`)
+    configs = None
+    if rank == 0 and not args.path_only:
+        configs = extra_configs(args, torch, dev, N, cm, disp_d, bgr_d, seed)
+
     # ---- end to end: pinned host frames in, masks / planes / counts out, chunked + double buffered
     e2e = None
     if not args.no_e2e:
@@ -358,6 +454,8 @@ def run_b200(args):
 
     # ---- max over ranks
     ms_max, e2e_ms_max = shard.max_over_ranks([ms, e2e["ms"] if e2e else 0.0], dev)
+    all_sha = shard.gather_strings(my_sha, dev)
+    link_min = shard.min_over_ranks([e2e["link"]["h2d_gbs"], e2e["link"]["d2h_gbs"]], dev) if e2e else None
     out = None
     if rank == 0:
         peaks = {}
@@ -398,6 +496,23 @@ def run_b200(args):
                          "share_of_step": d["share"], "longest_kernel": top},
             "kernels": {k: {kk: (round(vv, 6) if isinstance(vv, float) else vv) for kk, vv in v.items()} for k, v in kern.items()},
         }
+        gold, match = None, None
+        try:
+            gold = json.load(open(os.path.join(ROOT, "tests", "golden", "bench_sha.json")))
+            same_cfg = (gold["frames"], gold["trials"], gold["samples"], gold["step"]) == (F, T, S, args.step)
+            match = bool(same_cfg and all(all_sha[r] == gold["sha"][str(shard.sequence_of_rank(r))] for r in range(world)))
+            if not same_cfg:
+                match = None
+        except Exception:
+            pass
+        out["result_sha"] = all_sha
+        out["matches_single_gpu"] = match
+        out["result_sha_note"] = ("per rank: sha256 of road masks | N,M,K,R | winning trials | plane flags, ':' first 16 hex of the sha256 of "
+                                  "the planes' float64 bits; compared with tests/golden/bench_sha.json (one GPU, tools/make_bench_sha.py)")
+        if parity:
+            out["parity_mode"] = parity
+        if configs:
+            out["extra"] = {"configs": configs}
         if next_rows:
             for row in next_rows.values():
                 for v in row["kernels"].values():
@@ -410,17 +525,179 @@ def run_b200(args):
                           "ms_per_step": e2e_ms_max, "chunk_frames": args.chunk, "matches_resident_run": e2e["match"],
                           "api": "stereo.vision_b200.pipeline.SequenceStreamer.run (pinned host frames -> pinned host masks/planes/counts; "
                                  "of the colour image only the lattice rows are uploaded)",
-                          "gpu_launches_per_step": e2e["launches_per_step"], "clocks": e2e["clocks"]}
+                          "gpu_launches_per_step": e2e["launches_per_step"], "clocks": e2e["clocks"],
+                          "link": dict(e2e["link"], h2d_gbs_min_over_ranks=link_min[0], d2h_gbs_min_over_ranks=link_min[1]),
+                          "h2d_gbs": e2e["h2d"] / (e2e_ms_max * 1e-3) / 1e9, "d2h_gbs": e2e["d2h"] / (e2e_ms_max * 1e-3) / 1e9}
+            lk = out["e2e"]["link"]
+            # the step moves h2d and d2h bytes concurrently over a full-duplex link: its floor is the slower direction alone
+            floor_ms = max(e2e["h2d"] / (link_min[0] * 1e9), e2e["d2h"] / (link_min[1] * 1e9)) * 1e3
+            out["e2e"]["link_floor_ms"] = floor_ms
+            out["e2e"]["frac_of_link"] = floor_ms / e2e_ms_max
         if world == 1 and not args.no_cpu_baseline:
             procs = ncpu
-            fpp = args.cpu_frames or 4
-            v, wall = cpu_oracle_throughput(fpp, procs, T, S, args.step)
-            out["cpu_baseline"] = {"value": v, "unit": "frames/s", "cores": procs, "kind": "port",
-                                   "sample": "%d independent sequences x %d chained frames through oracle/np_oracle.py "
-                                             "(numpy float64 restatement), one process per core, %.1f s wall" % (procs, fpp, wall)}
+            kind = _reference_kind(S, args.step)
+            fpp = args.cpu_frames or (2 if kind == "reference" else 4)
+            v, wall = cpu_throughput(kind, fpp, procs, T, S, args.step)
+            out["cpu_baseline"] = {"value": v, "unit": "frames/s", "cores": procs, "kind": kind,
+                                   "sample": cpu_sample_text(kind, procs, fpp, wall)}
+            if kind == "reference":                    # the numpy port beside it, for the record (it is ~30x faster than the reference)
+                v2, wall2 = cpu_throughput("port", 4, procs, T, S, args.step)
+                out["cpu_baseline"]["port"] = {"value": v2, "sample": cpu_sample_text("port", procs, 4, wall2)}
         print(json.dumps(out))
     shard.finish()
     return out
+
+
+def _timed(torch, fn, reps, warm=2):
+    """mean device milliseconds of fn() over `reps` back-to-back calls"""
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(reps):
+        fn()
+    b.record()
+    torch.cuda.synchronize()
+    return a.elapsed_time(b) / reps
+
+
+def extra_configs(args, torch, dev, N, cm, disp_d, bgr_d, seed):
+    """BASELINE.json configs 1, 3 and 5 on one GPU (config 2 is `value`, config 4 the multi-GPU run)."""
+    import random
+    import stereo.vision_b200.synth as synth
+    from stereo.vision_b200.pipeline import RoadPath
+    T, S = args.trials, args.samples
+    out = {}
+    # ---- config 1: one frame, prev = None (single_frame.py:53): latency of one RoadPath.process call, host-synchronised
+    one = RoadPath((H, W), step=2, trials=T, samples=S, carmask=cm, max_frames=1, device=dev)
+    d1, c1 = disp_d[:1], bgr_d[:1]
+
+    def latency(fn, reps=30):
+        fn()
+        torch.cuda.synchronize()
+        ts = []
+        for _ in range(reps):
+            t0 = time.perf_counter()
+            fn()
+            torch.cuda.synchronize()
+            ts.append((time.perf_counter() - t0) * 1e3)
+        return float(np.median(ts))
+    lat_dev = latency(lambda: one.process(d1, c1, seed=seed))
+    lat_ref = latency(lambda: one.process(d1, c1, py_seeds=[synth.ransac_seed(0, 0)]))
+    # the drop-in helper chain (stereovision.py:58-140 through stereo.vision_b200.functions, numpy in, numpy out)
+    import stereo.vision_b200.functions as f
+    f.carmask, f.ransac_samples = cm, S
+    dn, cn = disp_d[0].cpu().numpy(), bgr_d[0].cpu().numpy()
+
+    def helper_chain():
+        random.seed(synth.ransac_seed(0, 0))
+        disparity = f.disparityCleaning(dn, 'previous', None)
+        masked = f.maskDisparity(disparity)
+        points = f.projectDisparityTo3d(f.capDisparity(disparity), 128, cn)
+        maskpoints = f.projectDisparityTo3d(masked, 128)
+        normal, abc = f.RANSAC(maskpoints, T)
+        diffs = f.calculatePointErrors(abc, points)
+        points = f.computePlanarThreshold(points, diffs, 0.05)
+        hist = f.calculateColourHistogram(points)
+        points = f.filterPointsByHistogram(points, hist, 10)
+        pp = np.array(f.project3DPointsTo2DImagePoints(points), np.int32).reshape((-1, 1, 2))
+        return f.generatePointsAsImage(pp)
+
+    def wall_ms(fn, reps):
+        fn()
+        ts = []
+        for _ in range(reps):
+            t0 = time.perf_counter()
+            fn()
+            ts.append((time.perf_counter() - t0) * 1e3)
+        return float(np.median(ts))
+    f.ransac_replay = "device"
+    chain_dev = wall_ms(helper_chain, 5)
+    f.ransac_replay = "host"
+    chain_host = wall_ms(helper_chain, 2)
+    f.ransac_replay, f.ransac_samples = "device", 600
+    out["config1_single_frame"] = {
+        "row": "single_frame.py:53: one 1024x544 frame, prev = None, step 2, %d x %d; milliseconds per frame, host-synchronised" % (T, S),
+        "fused_device_draws_ms": round(lat_dev, 4), "fused_reference_draws_ms": round(lat_ref, 4),
+        "dropin_helper_chain_ms": round(chain_dev, 3), "dropin_helper_chain_host_replay_ms": round(chain_host, 3),
+        "note": "fused = RoadPath.process(F=1) on resident inputs; drop-in = the twelve helper calls of stereovision.py:58-140 "
+                "(numpy in, numpy out, Python's random stream replayed on the device / by the host loop)"}
+    del one
+    # ---- config 3: full density (step 1), colour attach, masked-cloud RANSAC
+    F3 = min(60, disp_d.shape[0])
+    e3 = RoadPath((H, W), step=1, trials=T, samples=S, carmask=cm, max_frames=F3, device=dev)
+    ms3 = _timed(torch, lambda: e3.process(disp_d[:F3], bgr_d[:F3], seed=seed), 5)
+    cnt3 = e3.counts[:F3].float().mean(dim=0).tolist()
+    out["config3_step1"] = {"row": "step 1 (555 489 lattice sites per frame), %d chained frames resident, %d x %d" % (F3, T, S),
+                            "frames_per_s": round(F3 / (ms3 * 1e-3), 1), "ms_per_frame": round(ms3 / F3, 5),
+                            "mean_points": dict(zip("NMKR", [round(v, 1) for v in cnt3]))}
+    del e3
+    torch.cuda.empty_cache()
+    # ---- config 5: 2048x1088 frames, RANSAC sweep
+    shape5, F5 = (2 * H, 2 * W), 4
+    from stereo.vision_b200.masks import default_carmask
+    cm5 = default_carmask(shape5, prefer_cwd=False)
+    frames5 = [synth.make_frame(900, t, shape5) for t in range(F5)]
+    d5 = torch.from_numpy(np.stack([a for a, _ in frames5])).to(dev)
+    c5 = torch.from_numpy(np.stack([b for _, b in frames5])).to(dev)
+    sweep = []
+    for (T5, S5) in ((600, 400), (2000, 1000), (10000, 4000)):
+        e5 = RoadPath(shape5, step=2, trials=T5, samples=S5, carmask=cm5, max_frames=F5, device=dev)
+        ms5 = _timed(torch, lambda: e5.process(d5, c5, seed=seed), 3, warm=1)
+        N.profile_enable(True)
+        e5.process(d5, c5, seed=seed)
+        torch.cuda.synchronize()
+        pr = N.profile_read()
+        N.profile_enable(False)
+        rs = pr["ransac_score"][0] / pr["ransac_score"][1]
+        sweep.append({"trials": T5, "samples": S5, "ms_per_frame": round(ms5 / F5, 5), "ransac_score_ms_per_frame": round(rs / F5, 5),
+                      "ransac_share": round(rs / sum(v[0] / v[1] for v in pr.values()), 3),
+                      "sample_terms_per_s": round(F5 * T5 * S5 / (rs * 1e-3), 1),
+                      "frames_with_plane": int((e5.planes[:F5, 7] > 0).sum().item())})
+        del e5
+        torch.cuda.empty_cache()
+    out["config5_2048x1088"] = {"row": "2048x1088 frames (masks scaled x2), step 2, %d chained frames resident, device draws" % F5,
+                                "sweep": sweep,
+                                "note": "ransac_score is issue-bound (shared-memory gathers + 2 mad.wide + 3 fp64 per sample term): "
+                                        "sample_terms_per_s is its throughput; profiles/ holds its warp-instruction count"}
+    return out
+
+
+def measure_link(torch, dev, h2d_bytes, d2h_bytes):
+    """Plain pinned cudaMemcpyAsync bandwidth of this rank's link: one H2D copy of the step's upload size and one D2H
+    copy of its download size, alone and both at once (all ranks run this at the same time: the ceiling e2e is held to)."""
+    hb = torch.empty((h2d_bytes,), dtype=torch.uint8).pin_memory()
+    db = torch.empty((h2d_bytes,), dtype=torch.uint8, device=dev)
+    ho = torch.empty((d2h_bytes,), dtype=torch.uint8).pin_memory()
+    do = torch.empty((d2h_bytes,), dtype=torch.uint8, device=dev)
+    s1, s2 = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+
+    def run(up, down, reps=4):
+        best = 1e30
+        for _ in range(reps):
+            torch.cuda.synchronize()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            s1.wait_event(a)
+            s2.wait_event(a)
+            if up:
+                with torch.cuda.stream(s1):
+                    db.copy_(hb, non_blocking=True)
+            if down:
+                with torch.cuda.stream(s2):
+                    ho.copy_(do, non_blocking=True)
+            torch.cuda.current_stream().wait_stream(s1)
+            torch.cuda.current_stream().wait_stream(s2)
+            b.record()
+            torch.cuda.synchronize()
+            best = min(best, a.elapsed_time(b))
+        return best
+    run(True, True, 1)
+    up, down, both = run(True, False), run(False, True), run(True, True)
+    return {"h2d_gbs": h2d_bytes / (up * 1e-3) / 1e9, "d2h_gbs": d2h_bytes / (down * 1e-3) / 1e9,
+            "both_ms": both, "h2d_alone_ms": up, "d2h_alone_ms": down,
+            "how": "one pinned cudaMemcpyAsync per direction of the step's byte counts, best of 4, CUDA events; every rank at the same time"}
 
 
 def run_e2e(args, torch, dev, camera, cm, disp_p, bgr_p, seed, ref_counts, clk=None):
@@ -445,39 +722,43 @@ def run_e2e(args, torch, dev, camera, cm, disp_p, bgr_p, seed, ref_counts, clk=N
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / steps
     match = bool(np.array_equal(out["counts"].numpy().astype(np.float64), ref_counts))
-    return {"ms": ms, "h2d": sr.h2d_bytes, "d2h": sr.d2h_bytes, "match": match,
+    import stereo.vision_b200.shard as shard
+    shard.barrier()
+    link = measure_link(torch, dev, sr.h2d_bytes, sr.d2h_bytes)
+    return {"ms": ms, "h2d": sr.h2d_bytes, "d2h": sr.d2h_bytes, "match": match, "link": link,
             "launches_per_step": len(range(0, F, C)) * (sr.engines[0].road_launches + 5)}
 
 
 # ------------------------------------------------------------------ reference arm (CPU)
 def run_reference(args):
-    """The reference's CPU path for the same workload.  /root/reference (pure Python, no build) does
-    not exist on the GPU box, so this arm times the oracle port (oracle/np_oracle.py), one
-    independent sequence per host core; each step is a bounded sample of the 300-frame workload."""
+    """The reference's CPU path for the same workload on the box's host cores: the reference's own helper chain
+    (byte code under oracle/_ref/, built from /root/reference by oracle/build_ref.py; /root/reference itself does not
+    exist on the GPU box), one independent sequence per host core; when that is not available, the oracle port.
+    Each step is a bounded sample of the 300-frame workload."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     world = int(os.environ.get("WORLD_SIZE", "1"))
     procs = os.cpu_count() or 1
-    fpp = args.cpu_frames or 2
     T, S = args.trials, args.samples
+    kind = _reference_kind(S, args.step)
+    fpp = args.cpu_frames or 2
     for _ in range(min(args.warmup, 1)):
-        cpu_oracle_throughput(1, procs, T, S, args.step)
+        cpu_throughput(kind, 1, procs, T, S, args.step)
     vals, walls = [], []
     for _ in range(args.steps):
-        v, wall = cpu_oracle_throughput(fpp, procs, T, S, args.step)
+        v, wall = cpu_throughput(kind, fpp, procs, T, S, args.step)
         vals.append(v)
         walls.append(wall)
     v = float(np.mean(vals))
-    sample = ("each step = %d independent sequences x %d chained frames (of the %d-frame workload) through "
-              "oracle/np_oracle.py, one process per core" % (procs, fpp, args.frames))
+    sample = "each step = " + cpu_sample_text(kind, procs, fpp, float(np.mean(walls))) + " (of the %d-frame workload)" % args.frames
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": v, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
         "warmup": min(args.warmup, 1), "ms_per_step": 1e3 * float(np.mean(walls)), "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f64 (numpy)", "data": "synthetic",
+        "scaling": "weak", "vs_baseline": None, "dtype": "f64 (python / numpy)", "data": "synthetic",
         "config": {"workload": "config 2: %d-frame sequence, 1024x544, previous-disparity fill, step %d, %d RANSAC "
                                "trials x %d samples (bounded sample per step)" % (args.frames, args.step, T, S)},
-        "cpu_baseline": {"value": v, "unit": "frames/s", "cores": procs, "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": v, "unit": "frames/s", "cores": procs, "kind": kind, "sample": sample},
         "e2e": {"value": v, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }))

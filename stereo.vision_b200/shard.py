@@ -44,6 +44,13 @@ def max_over_ranks(values, device="cpu"):
     return t.tolist()
 
 
+def min_over_ranks(values, device="cpu"):
+    t = torch.tensor(list(values), dtype=torch.float64, device=device)
+    if dist.is_initialized():
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+    return t.tolist()
+
+
 def sum_over_ranks(values, device="cpu"):
     t = torch.tensor(list(values), dtype=torch.float64, device=device)
     if dist.is_initialized():

@@ -177,3 +177,31 @@ def test_device_draws_are_statistically_the_references(cuda):
         assert p > 0.01, (name, report)
     for m in (ref, dev):
         assert np.median(m[:, 3]) < 3.0 and (m[:, 3] < 6.0).mean() > 0.95, report
+
+
+@pytest.mark.parametrize("fixture,S", [("seq0_step2_s600", 600), ("seq6_step2_s400", 400)])
+def test_fused_path_reference_draws_equal_reference_goldens(cuda, fixture, S):
+    """RoadPath.process(py_seeds=...) -- the fast reference-identical mode -- against outputs of the UNMODIFIED reference
+    run under the same seeds (tests/golden, oracle/make_golden.py): filled disparity, N, M, plane, K, histogram, R and the
+    road mask, with no oracle in between."""
+    from test_oracle_golden import frame, load, sha
+    from stereo.vision_b200.pipeline import RoadPath
+    g = load(fixture + ".npz")
+    seq, F, T = int(g["seq"]), int(g["n_frames"]), int(g["trials"])
+    assert int(g["n_samples"]) == S and int(g["step"]) == 2
+    disp, bgr = synth.make_sequence(seq, F)
+    cm = _carmask(disp.shape[1:])
+    eng = RoadPath(trials=T, samples=S, carmask=cm, max_frames=F)
+    r = eng.process(disp, bgr, py_seeds=[synth.ransac_seed(seq, t) for t in range(F)])
+    res = to_host(r)
+    for t in range(F):
+        ref = frame(g, t)
+        assert sha(res["filled"][t]) == str(ref["filled_sha"])
+        N_, M_, K_, R_ = (int(v) for v in res["counts"][t])
+        assert (N_, M_) == (int(ref["N"]), int(ref["M"]))
+        assert bool(ref["has_plane"]) and res["planes"][t][7] == 1.0
+        np.testing.assert_allclose(res["planes"][t][:3], ref["abc"], rtol=1e-9, atol=1e-13 * float(np.linalg.norm(ref["abc"])))
+        np.testing.assert_allclose(res["planes"][t][5], float(ref["best_error"]), rtol=1e-9)
+        assert (K_, R_) == (int(ref["near_n"]), int(ref["road_n"]))
+        assert np.array_equal(res["hist"][t][:no.HUE_BINS].astype(np.int64), ref["hist_bins"])
+        assert np.array_equal(np.packbits(res["road_mask"][t] != 0), ref["road_mask_bits"]), "road mask, frame %d" % t
