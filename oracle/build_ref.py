@@ -4,10 +4,10 @@
 from the sources WHERE THEY LIE into byte code under oracle/_ref/ (git-ignored, shipped to the GPU box like the
 built .so files) and copies the five mask PNGs the module reads at import time (functions.py:29-35):
 
-    oracle/_ref/functions.pyc          /root/reference/functions.py, unmodified
-    oracle/_ref/functions_s400.pyc     the same with ONE literal changed: random.sample(points, 600) -> 400
+    oracle/_ref/functions.code          /root/reference/functions.py, unmodified
+    oracle/_ref/functions_s400.code     the same with ONE literal changed: random.sample(points, 600) -> 400
                                        (functions.py:286; BASELINE.json's configs quote 400 samples)
-    oracle/_ref/stereovision.pyc       /root/reference/stereovision.py, unmodified
+    oracle/_ref/stereovision.code       /root/reference/stereovision.py, unmodified
     oracle/_ref/masks/*.png
 
 No source text of the reference is written anywhere.  Users: bench.py --impl reference / cpu_baseline (the timed
@@ -32,7 +32,7 @@ def build(force: bool = False) -> str:
     os.makedirs(os.path.join(OUT, "masks"), exist_ok=True)
     mode = py_compile.PycInvalidationMode.UNCHECKED_HASH
     for name in ("functions", "stereovision"):
-        py_compile.compile(os.path.join(REF, name + ".py"), cfile=os.path.join(OUT, name + ".pyc"), dfile=name + ".py",
+        py_compile.compile(os.path.join(REF, name + ".py"), cfile=os.path.join(OUT, name + ".code"), dfile=name + ".py",
                            doraise=True, invalidation_mode=mode)
     src = open(os.path.join(REF, "functions.py")).read()
     lit = "random.sample(points, 600)"
@@ -41,7 +41,7 @@ def build(force: bool = False) -> str:
         p = os.path.join(tmp, "functions_s400.py")
         with open(p, "w") as fh:
             fh.write(src.replace(lit, "random.sample(points, 400)"))
-        py_compile.compile(p, cfile=os.path.join(OUT, "functions_s400.pyc"), dfile="functions.py (sample literal 400)",
+        py_compile.compile(p, cfile=os.path.join(OUT, "functions_s400.code"), dfile="functions.py (sample literal 400)",
                            doraise=True, invalidation_mode=mode)
     for fn in os.listdir(os.path.join(REF, "masks")):
         if fn.endswith(".png"):

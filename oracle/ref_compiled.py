@@ -11,7 +11,7 @@ REF_DIR = os.path.join(HERE, "_ref")
 
 
 def available() -> bool:
-    return os.path.isfile(os.path.join(REF_DIR, "functions.pyc")) and os.path.isdir(os.path.join(REF_DIR, "masks"))
+    return os.path.isfile(os.path.join(REF_DIR, "functions.code")) and os.path.isdir(os.path.join(REF_DIR, "masks"))
 
 
 def _load(pyc, modname):
@@ -33,7 +33,7 @@ def load_functions(n_samples: int = 600):
     """the reference's functions module (n_samples = 400: the build with functions.py:286's literal changed)"""
     if n_samples not in (600, 400):
         raise ValueError("compiled for 600 (unmodified) and 400 samples")
-    return _load("functions.pyc" if n_samples == 600 else "functions_s400.pyc", "reference_functions_s%d" % n_samples)
+    return _load("functions.code" if n_samples == 600 else "functions_s400.code", "reference_functions_s%d" % n_samples)
 
 
 def load_orchestrator(f):
@@ -41,7 +41,7 @@ def load_orchestrator(f):
     saved = sys.modules.get("functions")
     sys.modules["functions"] = f
     try:
-        return _load("stereovision.pyc", "reference_stereovision_%d" % id(f))
+        return _load("stereovision.code", "reference_stereovision_%d" % id(f))
     finally:
         if saved is None:
             sys.modules.pop("functions", None)

@@ -39,6 +39,7 @@ static const char *k_names[K_COUNT_] = {
     "prep_gamma_gray", "prep_equalize_lut", "prep_apply_lut", "fill_row_mean", "normal_line", "road_hull", "hull_masks",
     "sgbm_prefilter", "sgbm_hsum", "sgbm_vsum", "sgbm_path_v", "sgbm_path_d1", "sgbm_path_d3", "sgbm_path_h", "sgbm_final",
     "sgbm_median", "speckle", "disparity_scale", "ransac_replay"};
+const char *svb_prof_name(int id) { return (id >= 0 && id < K_COUNT_) ? k_names[id] : "svb"; }
 struct EvPair { int id; cudaEvent_t a, b; };
 static std::vector<EvPair> g_events;
 static cudaEvent_t g_pending[K_COUNT_];

@@ -1,8 +1,11 @@
 // Per-kernel CUDA-event tracing (off by default).  When enabled through svb_profile_enable(1) every
 // kernel launch of the library is bracketed by two events on the launching stream; svb_profile_get
 // sums the elapsed times per kernel name.  bench.py uses it for the live roofline numbers.
+// Every launch site is also an NVTX range named after the kernel ("NVTX ranges per stage"), so a timeline
+// tool shows the path's stages without the event tracing; with no tool attached a push / pop is a few nanoseconds.
 #pragma once
 #include <cuda_runtime.h>
+#include <nvtx3/nvToolsExt.h>
 
 enum SvbKernelId {
     K_FILL = 0, K_MASK, K_PROJ_COUNT, K_PROJ_SCAN, K_PROJ_WRITE, K_EXPORT, K_RANSAC_SCORE, K_RANSAC_DUMP,
@@ -16,10 +19,17 @@ enum SvbKernelId {
 
 void svb_prof_begin(int id, cudaStream_t st);
 void svb_prof_end(int id, cudaStream_t st);
+const char *svb_prof_name(int id);
 extern bool g_svb_prof_on;
 
 struct ProfScope {
     int id; cudaStream_t st; bool on;
-    ProfScope(int id_, cudaStream_t st_) : id(id_), st(st_), on(g_svb_prof_on) { if (on) svb_prof_begin(id, st); }
-    ~ProfScope() { if (on) svb_prof_end(id, st); }
+    ProfScope(int id_, cudaStream_t st_) : id(id_), st(st_), on(g_svb_prof_on) {
+        nvtxRangePushA(svb_prof_name(id));
+        if (on) svb_prof_begin(id, st);
+    }
+    ~ProfScope() {
+        if (on) svb_prof_end(id, st);
+        nvtxRangePop();
+    }
 };

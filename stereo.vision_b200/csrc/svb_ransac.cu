@@ -353,7 +353,12 @@ ransac_score_persistent(const uint32_t *__restrict__ mcloud, int stride, int64_t
             else        score_trial<EXPLICIT, false>(rec, stride, s_rec_addr, (uint32_t)Mi, S, cam, fB_over_S, s_invd_addr, samp, trip, key, lane, err_out);
         }
         w = (int64_t)f * T + te;
-        if (w < w1) __syncthreads();                                  // everyone is done with this frame's records
+        if (w < w1) {
+            __syncthreads();                                          // everyone is done with this frame's records
+            // the next frame's bulk copies write s_rec through the async proxy: order this frame's generic-proxy
+            // reads and tail stores before them
+            if (tid == 0) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        }
     }
 }
 
@@ -381,20 +386,22 @@ extern "C" int svb_ransac_score(const uint32_t *mcloud, int rec_stride_words, in
     int64_t total = (int64_t)F * T;
     int blocks = (int)min((int64_t)sms, (total + 63) / 64);
     if (blocks < 1) blocks = 1;
-    cudaError_t e;
-    if (sample_idx) {
-        e = cudaFuncSetAttribute(ransac_score_persistent<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    // the opt-in to 200 KB of dynamic shared memory is a per-device function attribute: set once per device, not per call
+    static bool attr_done[64] = {false};
+    if (dev < 0 || dev >= 64 || !attr_done[dev]) {
+        cudaError_t e = cudaFuncSetAttribute(ransac_score_persistent<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(ransac_score_persistent<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
         if (e != cudaSuccess) return (int)e;
+        if (dev >= 0 && dev < 64) attr_done[dev] = true;
+    }
+    if (sample_idx)
         ransac_score_persistent<true><<<blocks, RANSAC_SMEM_THREADS, smem, st>>>(
             mcloud, rec_stride_words, slab_stride_records, counts, counts_stride, counts_col, F, T, S, cap, c,
             sample_idx, triple_idx, rng_seed, frame0, errors);
-    } else {
-        e = cudaFuncSetAttribute(ransac_score_persistent<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return (int)e;
+    else
         ransac_score_persistent<false><<<blocks, RANSAC_SMEM_THREADS, smem, st>>>(
             mcloud, rec_stride_words, slab_stride_records, counts, counts_stride, counts_col, F, T, S, cap, c,
             nullptr, nullptr, rng_seed, frame0, errors);
-    }
     SVB_LAUNCH_CHECK();
     return SVB_OK;
 }

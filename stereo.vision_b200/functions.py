@@ -33,7 +33,9 @@ stereo_camera_baseline_m = DEFAULT_CAMERA.baseline_m
 image_centre_h = DEFAULT_CAMERA.centre_h
 image_centre_w = DEFAULT_CAMERA.centre_w
 max_disparity = 128
-# ---- masks, functions.py:29-35 (masks/*.png of the CWD when present, else the packaged arrays)
+# ---- masks, functions.py:29-35.  carmask: masks/car_front_mask.png + masks/view_range.png of the CWD when present
+# (as the reference reads them), else the packaged arrays; road_threshold_mask and blackImg: the packaged arrays
+# (assign to the module attributes to use others)
 carmask = default_carmask((544, 1024))
 blackImg = np.zeros((544, 1024), dtype=np.uint8)
 road_threshold_mask = default_road_threshold_mask((544, 1024))
@@ -61,11 +63,23 @@ def _to_dev_u8(a):
 
 
 def _carmask_dev():
-    key = (id(carmask), carmask.shape)
+    """`carmask` on the current device.  The cache key holds a digest of the uploaded bytes, so an in-place edit of the
+    module's array is seen, and there is one copy per device."""
+    import hashlib
+    dev = _dev()
+    a = np.ascontiguousarray(carmask, dtype=np.uint8)
+    key = (str(dev), a.shape, hashlib.blake2b(a.tobytes(), digest_size=16).digest())
     if _state.get("cm_key") != key:
-        _state["cm"] = torch.from_numpy(np.ascontiguousarray(carmask)).to(_dev())
+        _state["cm"] = torch.from_numpy(a).to(dev)
         _state["cm_key"] = key
     return _state["cm"]
+
+
+def _same_size(what, a_shape, b_shape):
+    """cv2 raises on operands of different sizes (functions.py:142-146,171), and the orchestrator relies on it: stage 2
+    then falls back to the black image (stereovision.py:54-64)."""
+    if tuple(a_shape[:2]) != tuple(b_shape[:2]):
+        raise ValueError("%s: operand sizes differ, %s and %s" % (what, tuple(a_shape[:2]), tuple(b_shape[:2])))
 
 
 def _back(t, was_tensor):
@@ -89,6 +103,9 @@ def fillDisparity(disparity, previousDisparity):
         return disparity
     d, was = _to_dev_u8(disparity)
     p, _ = _to_dev_u8(previousDisparity)
+    if d.dim() != 2:
+        raise ValueError("fillDisparity expects a single-channel disparity")
+    _same_size("fillDisparity", d.shape, p.shape)
     H, W = d.shape
     out = torch.empty_like(d)
     N.check(N.load().svb_fill_sequence(N.ptr(d), N.ptr(p), N.ptr(out), 1, H, W, N.stream_ptr()), "svb_fill_sequence")
@@ -104,6 +121,9 @@ def capDisparity(disparity):
 def maskDisparity(disparity):
     """functions.py:169-172."""
     d, was = _to_dev_u8(disparity)
+    if d.dim() != 2:
+        raise ValueError("maskDisparity expects a single-channel disparity")
+    _same_size("maskDisparity (carmask)", d.shape, np.shape(carmask))
     H, W = d.shape
     out = torch.empty_like(d)
     N.check(N.load().svb_mask_disparity(N.ptr(d), N.ptr(_carmask_dev()), N.ptr(out), 1, H, W, N.stream_ptr()),
@@ -120,6 +140,8 @@ def projectDisparityTo3d(disparity, max_disparity, rgb=[]):
     H, W = d.shape[:2]
     has_rgb = len(rgb) > 0
     c = _to_dev_u8(rgb)[0] if has_rgb else None
+    if has_rgb and (c.dim() != 3 or c.shape[2] != 3 or tuple(c.shape[:2]) != (H, W)):
+        raise IndexError("projectDisparityTo3d: rgb is %s, the disparity %s" % (tuple(c.shape), (H, W)))    # rgb[y,x,2], :195
     step = int(lattice_step)
     L = lib.svb_lattice_rows(H, step) * lib.svb_lattice_cols(W, step)
     dev = d.device
@@ -300,11 +322,13 @@ def generatePointsAsImage(points):
 
 # ---------------------------------------------------------------- f1
 def _threshold_bits(H, W):
-    key = (id(road_threshold_mask), road_threshold_mask.shape)
+    import hashlib
+    if tuple(road_threshold_mask.shape) != (H, W):               # cv2.bitwise_and(.., mask=) raises on a size mismatch, :355
+        raise ValueError("road_threshold_mask is %s, the image %s" % (road_threshold_mask.shape, (H, W)))
+    a = np.ascontiguousarray(road_threshold_mask, dtype=np.uint8)
+    key = (str(_dev()), a.shape, hashlib.blake2b(a.tobytes(), digest_size=16).digest())
     if _state.get("tb_key") != key:
-        if road_threshold_mask.shape != (H, W):
-            raise ValueError("road_threshold_mask is %s, the image %s" % (road_threshold_mask.shape, (H, W)))
-        m = torch.from_numpy(np.ascontiguousarray(road_threshold_mask, dtype=np.uint8)).to(_dev())
+        m = torch.from_numpy(a).to(_dev())
         bits = torch.empty((N.load().svb_bits_words(H, W),), dtype=torch.int32, device=m.device)
         N.check(N.load().svb_pack_mask(N.ptr(m), 1, H, W, N.ptr(bits), 0, N.stream_ptr()), "svb_pack_mask")
         N.count(1)

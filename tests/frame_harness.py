@@ -1,16 +1,13 @@
-"""The reference's frame orchestrator on the B200 helpers: stereovision.py:26-247 without its display layer.
-
-`performStereoVision(imgL, imgR, prev_disp, opt)` runs the reference's stages 1-9 in the reference's order through
-the drop-in helpers of `stereo.vision_b200.functions` (every stage on the GPU) and returns what the reference
-returns -- except that the first element is a dict of the stage images instead of the tiled display image
-(tiling, drawing and the HighGUI window are out of scope: no display on this box).  Exceptions are handled
-stage by stage exactly like the reference (a failing stage leaves a black image / no plane and the frame goes on).
-For throughput use `pipeline.FrontEnd` / `Matcher` / `RoadPath` / `RoadCleaner`, which batch the same kernels
-over many frames; this module is the one-frame drop-in for `loop.py:78` / `single_frame.py:53`.
+"""TEST HARNESS -- the reference's frame orchestrator (stereovision.py:26-247) restated on the drop-in helpers, without its
+display layer.  The product story is INTEGRATION.md section 1: the UNMODIFIED orchestrator with `functions` routed to the
+GPU helpers (stereo.vision_b200.dropin.route), which tests/test_gpu_frame.py::test_unmodified_orchestrator_on_gpu_helpers
+executes.  This restatement exists so that every stage's product can be held to tests/golden/frames.npz (the recorded
+products of the unmodified orchestrator): it returns a dict of the stage images instead of the tiled display image.
+Exceptions are handled stage by stage exactly like the reference (a failing stage leaves a black image / no plane).
 """
 import numpy as np
 
-from . import functions as f
+import stereo.vision_b200.functions as f
 
 # stereovision.py:10-24
 default_opts = {
@@ -66,7 +63,11 @@ def performStereoVision(imgL, imgR, prev_disp=None, opt=default_opts):
         print("There was an error with generating a plane:", e)
         stats["Planar Points Before"] = stats["Planar Points After"] = stats["Planar Pre-Filtering Accuracy"] = "-"
         stats["Computed Planar"] = 0
-    # 6. road image (:139-143)
+    # 6. the overlay (:129-135) and the road image (:139-143)
+    imageRoadMap = np.array(imgL, copy=True)
+    for i in planePoints:
+        imageRoadMap[i[0][1]][i[0][0]] = [0, 255, 0]
+    images["Image Road Map"] = imageRoadMap
     try:
         roadImage = f.generatePointsAsImage(planePoints)
     except Exception as e:

@@ -83,7 +83,7 @@ def test_no_cpu_fallback():
     with pytest.raises(N.SvbError):
         f.projectDisparityTo3d(np.zeros((8, 8), np.uint8), 128)
     from stereo.vision_b200.pipeline import Matcher
-    import stereo.vision_b200.stereovision as sv
+    import frame_harness as sv
     with pytest.raises(N.SvbError):
         Matcher()
     with pytest.raises(N.SvbError):

@@ -1,4 +1,4 @@
-"""GPU: whole frames.  stereo.vision_b200.stereovision.performStereoVision (the reference's stage sequence on the drop-in
+"""GPU: whole frames.  tests/frame_harness.performStereoVision (the reference's stage sequence on the drop-in
 helpers, every stage on the GPU) against tests/golden/frames.npz, which oracle/make_golden_frame.py recorded from the
 UNMODIFIED reference orchestrator (stereovision.py:26-247) on three chained synthetic BGR stereo frames: matcher
 disparity, carried disparity, plane, point counts, road image, cleaned image and points, hull centre, normal line."""
@@ -8,7 +8,7 @@ import random
 import numpy as np
 import pytest
 
-import stereo.vision_b200.stereovision as sv
+import frame_harness as sv
 import stereo.vision_b200.synth as synth
 from test_oracle_golden import sha
 
@@ -91,3 +91,38 @@ def test_batched_pipeline_on_the_golden_frames(cuda):
         want, wpts = no.sanitise_road_image(res.road_mask[t].cpu().numpy(), tm)
         assert np.array_equal(out["cleaned"][t].cpu().numpy(), want)
         assert int(out["counts"][t]) == len(wpts)
+
+
+def test_unmodified_orchestrator_on_gpu_helpers(cuda):
+    """INTEGRATION.md section 1, executed: the reference's own stereovision.performStereoVision (byte code of the unmodified
+    source, oracle/_ref/) with `functions` routed to the GPU helpers (stereo.vision_b200.dropin.route), against the same
+    orchestrator on the reference's own functions module -- two chained frames, `random.seed` before each call: the tiled
+    display image (every stage's picture), the carried disparity and the plane normal must agree."""
+    import ref_compiled as rc
+    import ref_harness as rh
+    import stereo.vision_b200.dropin as dropin
+    if not rc.available():
+        pytest.skip("oracle/_ref was not built (python oracle/build_ref.py where /root/reference exists)")
+    f_ref = rc.load_functions()
+    f_ref.cv2 = rh._Cv2Compat(f_ref.cv2)              # OpenCV 4's findContours in the OpenCV 3 signature functions.py:379 expects
+    f_ref2 = rc.load_functions()
+    f_ref2.cv2 = rh._Cv2Compat(f_ref2.cv2)
+    sv_ref = rc.load_orchestrator(f_ref)
+    sv_gpu = rc.load_orchestrator(dropin.route(f_ref2))
+    opts = {'crop_disparity': False, 'pause_playback': False, 'max_disparity': 128, 'ransac_trials': 600, 'road_color_thresh': 10,
+            'loop': False, 'point_threshold': 0.05, 'image_tiles': True, 'img_size': (544, 1024), 'threshold_option': 'previous',
+            'record_video': False, 'record_stats': False, 'video_filename': 'previous.avi'}
+    o_ref, o_gpu = dict(opts), dict(opts)
+    p_ref = p_gpu = None
+    for t in range(2):
+        imgL, imgR = synth.make_stereo_bgr(2, t)
+        random.seed(synth.ransac_seed(2, t))
+        tile_ref, p_ref, n_ref = sv_ref.performStereoVision(imgL.copy(), imgR.copy(), p_ref, o_ref)
+        state_ref = random.getstate()
+        random.seed(synth.ransac_seed(2, t))
+        tile_gpu, p_gpu, n_gpu = sv_gpu.performStereoVision(imgL.copy(), imgR.copy(), p_gpu, o_gpu)
+        assert random.getstate() == state_ref, "Python's generator after the frame"
+        assert np.array_equal(np.asarray(p_gpu), np.asarray(p_ref)), "carried disparity, frame %d" % t
+        assert n_ref is not None and n_gpu is not None
+        np.testing.assert_allclose(np.asarray(n_gpu), np.asarray(n_ref), rtol=1e-9, atol=1e-13 * float(np.linalg.norm(n_ref)))
+        assert tile_gpu.shape == tile_ref.shape and np.array_equal(tile_gpu, tile_ref), "tiled display image, frame %d" % t
