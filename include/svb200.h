@@ -41,6 +41,7 @@ extern "C" {
 #define SVB_E_SHAPE      -2   /* H,W outside [2,2048], F < 1, step < 1, ... */
 #define SVB_E_ARG        -3   /* other invalid argument */
 #define SVB_E_SCRATCH    -4   /* scratch buffer too small */
+#define SVB_E_LIMIT      -5   /* size beyond the fixed maximum of an entry point that allocates nothing */
 
 #define SVB_HUE_BINS     1001 /* keys '0.0' .. '1.0' of functions.py:76-78 */
 #define SVB_HIST_STRIDE  1024 /* uint32 per frame in histogram arrays */
@@ -190,6 +191,20 @@ int svb_compact_cloud(const uint64_t *cloud, int n, int mode, const double *dist
                       const uint32_t *hist, double threshold,
                       uint64_t *out_cloud, int32_t *out_count,
                       void *scratch, int64_t scratch_bytes, void *stream);
+
+/* ---- svb_compact_cloud without caller scratch.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  Same arguments, outputs and results as svb_compact_cloud, minus the scratch:
+ * the block counts live in a file-scope device array of the library (8 KB, held by every GPU that loads the library
+ * until exit).  Limit: n <= SVB_COMPACT_STATIC_MAX_N records, else SVB_E_LIMIT and nothing is launched.  The call
+ * performs no cudaMalloc / cudaFree and calls no allocating routine; the first call on a device looks the array's
+ * address up (cudaGetSymbolAddress) -- make that call once outside a capture.  Every call on a device shares the
+ * array: calls that overlap on the GPU (two streams, two threads) race; serialise them.  Nothing in it has to start
+ * at zero (each call stores every entry it later reads). */
+#define SVB_COMPACT_STATIC_MAX_N 4194304
+int svb_compact_cloud_static(const uint64_t *cloud, int n, int mode, const double *dist,
+                             const uint32_t *hist, double threshold,
+                             uint64_t *out_cloud, int32_t *out_count, void *stream);
 
 /* ---- a10-a11  BGRtoHSVHue + calculateColourHistogram                 functions.py:73-78, 215-226
  * hist[bin] += 1 for every record (bin = rint(1000*hue), functions.py:76).  hist is zeroed first. */

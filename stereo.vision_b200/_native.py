@@ -17,8 +17,9 @@ LIB_PATH = os.path.join(_PKG, "libsvb200.so")
 HUE_BINS = 1001
 HIST_STRIDE = 1024
 PLANE_STRIDE = 8
-ABI_VERSION = 11
-SVB_OK, SVB_E_NULL, SVB_E_SHAPE, SVB_E_ARG, SVB_E_SCRATCH = 0, -1, -2, -3, -4      # include/svb200.h
+ABI_VERSION = 12
+SVB_OK, SVB_E_NULL, SVB_E_SHAPE, SVB_E_ARG, SVB_E_SCRATCH, SVB_E_LIMIT = 0, -1, -2, -3, -4, -5      # include/svb200.h
+COMPACT_STATIC_MAX_N = 4194304
 SVB_MAX_DIM = 2048                                                                  # csrc/svb_common.cuh
 
 
@@ -66,6 +67,7 @@ SIGNATURES = {
     "svb_point_errors": (I, [P, I, I, CAMP, P, P, P]),
     "svb_compact_scratch_bytes": (L, [I]),
     "svb_compact_cloud": (I, [P, I, I, P, P, D, P, P, P, L, P]),
+    "svb_compact_cloud_static": (I, [P, I, I, P, P, D, P, P, P]),
     "svb_hue_histogram": (I, [P, I, P, P]),
     "svb_hue_bins": (I, [P, L, P, P]),
     "svb_reproject": (I, [P, I, I, CAMP, P, P, P]),

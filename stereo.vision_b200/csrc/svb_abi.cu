@@ -1,7 +1,7 @@
 // ABI bookkeeping: version and error strings.
 #include "svb_common.cuh"
 
-extern "C" int svb_version(void) { return 11; }
+extern "C" int svb_version(void) { return 12; }
 
 extern "C" const char *svb_error_string(int code) {
     switch (code) {
@@ -10,6 +10,7 @@ extern "C" const char *svb_error_string(int code) {
         case SVB_E_SHAPE: return "invalid shape (F >= 1, 2 <= H,W <= 2048, step >= 1, T,S >= 1)";
         case SVB_E_ARG: return "invalid argument";
         case SVB_E_SCRATCH: return "scratch buffer too small";
+        case SVB_E_LIMIT: return "size beyond the fixed maximum of this no-allocation entry point";
         default: break;
     }
     if (code > 0) return cudaGetErrorString((cudaError_t)code);

@@ -160,6 +160,38 @@ extern "C" int svb_compact_cloud(const uint64_t *cloud, int n, int mode, const d
     return SVB_OK;
 }
 
+// ------------------------------------------------------------------ a9 / a12 without caller scratch (no allocation)
+// The block counts of the compaction live in a file-scope device array instead of caller scratch, for callers that
+// cannot allocate (CUDA graph capture, tight serving loops).  Every GPU that loads the library holds these 8 KB until
+// exit.  In host code `g_compact_static` is only a stand-in for the symbol: its device address comes from
+// cudaGetSymbolAddress, fetched once per device with that device current.  All calls share the array; it keeps the last
+// call's contents, which is harmless here: the count kernel stores (never accumulates) every entry a call reads.
+#define COMPACT_STATIC_BLOCKS (SVB_COMPACT_STATIC_MAX_N / COMPACT_PER_BLOCK)
+static_assert(SVB_COMPACT_STATIC_MAX_N % COMPACT_PER_BLOCK == 0, "the maximum is a whole number of blocks");
+static __device__ __align__(256) uint32_t g_compact_static[COMPACT_STATIC_BLOCKS + 1];
+
+extern "C" int svb_compact_cloud_static(const uint64_t *cloud, int n, int mode, const double *dist,
+                                        const uint32_t *hist, double threshold,
+                                        uint64_t *out_cloud, int32_t *out_count, void *stream) {
+    if (!out_count) return SVB_E_NULL;
+    if (n < 0 || (mode != 0 && mode != 1)) return SVB_E_ARG;
+    if (n > SVB_COMPACT_STATIC_MAX_N) return SVB_E_LIMIT;
+    static uint32_t *dev_ptr[64] = {nullptr};                     // the array's address on each device
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return (int)e;
+    if (dev < 0 || dev >= 64) return SVB_E_ARG;
+    if (!dev_ptr[dev]) {                                          // set-up, once per device, that device current
+        void *p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_compact_static);
+        if (e != cudaSuccess) return (int)e;
+        if (!p) return SVB_E_NULL;
+        dev_ptr[dev] = (uint32_t *)p;
+    }
+    return svb_compact_cloud(cloud, n, mode, dist, hist, threshold, out_cloud, out_count, dev_ptr[dev],
+                             (int64_t)sizeof(g_compact_static), stream);
+}
+
 // ------------------------------------------------------------------ a10-a11 hue histogram
 __global__ void __launch_bounds__(256)
 hue_hist_kernel(const uint64_t *__restrict__ cloud, int n, uint32_t *__restrict__ hist) {
