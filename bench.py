@@ -524,7 +524,7 @@ def run_b200(args):
                           "h2d_bytes_per_step": e2e["h2d"], "d2h_bytes_per_step": e2e["d2h"],
                           "ms_per_step": e2e_ms_max, "chunk_frames": args.chunk, "matches_resident_run": e2e["match"],
                           "api": "stereo.vision_b200.pipeline.SequenceStreamer.run (pinned host frames -> pinned host masks/planes/counts; "
-                                 "of the colour image only the lattice rows are uploaded)",
+                                 "only the lattice rows of the disparity and of the colour image are uploaded)",
                           "gpu_launches_per_step": e2e["launches_per_step"], "clocks": e2e["clocks"],
                           "link": dict(e2e["link"], h2d_gbs_min_over_ranks=link_min[0], d2h_gbs_min_over_ranks=link_min[1]),
                           "h2d_gbs": e2e["h2d"] / (e2e_ms_max * 1e-3) / 1e9, "d2h_gbs": e2e["d2h"] / (e2e_ms_max * 1e-3) / 1e9}

@@ -276,29 +276,35 @@ class SequenceStreamer:
     copy of the frames, the path (RoadPath.process, chained through the filled disparity of the previous
     chunk) and the device->host copy of the results; two engines / input buffers alternate.  Of the colour
     image only the lattice rows are sent (svb_upload_rows): the path never reads the others, and at step 2
-    that is a quarter of all input bytes.  `h2d_bytes` / `d2h_bytes` report what one run() moves.
+    that is a quarter of all input bytes.  With upload="lattice" (the default) the same holds for the disparity:
+    what run() returns -- road masks, planes, counts -- depends on the lattice rows of the (filled) disparity
+    only (functions.py:185-186), so the rows in between are not sent either (they hold zeros on the device);
+    upload="full" sends every disparity row, for a caller who also reads the engines' `filled` frames.
+    `h2d_bytes` / `d2h_bytes` report what one run() moves.
     """
 
     def __init__(self, shape=(544, 1024), step=2, trials=600, samples=600, carmask=None,
-                 camera: Camera = DEFAULT_CAMERA, chunk=30, device="cuda:0", **kw):
+                 camera: Camera = DEFAULT_CAMERA, chunk=30, device="cuda:0", upload="lattice", **kw):
+        if upload not in ("lattice", "full"):
+            raise ValueError("upload is 'lattice' or 'full'")
+        self.upload = upload
         self.H, self.W = int(shape[0]), int(shape[1])
         self.step, self.chunk = int(step), int(chunk)
         self.device = torch.device(device)
         self.engines = [RoadPath(shape, step=step, trials=trials, samples=samples, carmask=carmask, camera=camera,
                                  max_frames=self.chunk, device=device, **kw) for _ in range(2)]
         H, W, C_, dev = self.H, self.W, self.chunk, self.device
-        self.din = [torch.empty((C_, H, W), dtype=torch.uint8, device=dev) for _ in range(2)]
+        self.din = [torch.zeros((C_, H, W), dtype=torch.uint8, device=dev) for _ in range(2)]
         self.cin = [torch.zeros((C_, H, W, 3), dtype=torch.uint8, device=dev) for _ in range(2)]
         self.s_in, self.s_cmp, self.s_out = (torch.cuda.Stream(dev) for _ in range(3))
         self.lib = N.load()
         self.h2d_bytes = self.d2h_bytes = 0
         self._last_cmp, self._last_out = [None, None], [None, None]      # last use of buffer / engine k, across run() calls
 
-    def _upload_colour(self, dst, src, n):
-        """Lattice rows of src [n,H,W,3] (host) -> the same rows of dst (device), on the current stream."""
-        H, W, st = self.H, self.W, self.step
+    def _upload_rows(self, dst, src, n, row):
+        """Lattice rows (`row` bytes each) of src [n,H,...] (host) -> the same rows of dst (device), on the current stream."""
+        H, st = self.H, self.step
         LH = self.engines[0].LH
-        row = W * 3
         if st == 1 or not src.is_contiguous():
             dst[:n].copy_(src, non_blocking=True)
             return n * H * row
@@ -344,8 +350,12 @@ class SequenceStreamer:
             with torch.cuda.stream(s_in):
                 if busy_cmp is not None:
                     s_in.wait_event(busy_cmp)                 # input buffer k is free once its last chunk was computed
-                self.din[k][:n].copy_(disp[a:b], non_blocking=True)
-                h2d += n * H * W + self._upload_colour(self.cin[k], bgr[a:b], n)
+                if self.upload == "lattice":
+                    h2d += self._upload_rows(self.din[k], disp[a:b], n, W)
+                else:
+                    self.din[k][:n].copy_(disp[a:b], non_blocking=True)
+                    h2d += n * H * W
+                h2d += self._upload_rows(self.cin[k], bgr[a:b], n, W * 3)
                 ev_in[i] = torch.cuda.Event()
                 ev_in[i].record(s_in)
             with torch.cuda.stream(s_cmp):

@@ -81,12 +81,14 @@ def planes_sha(planes) -> str:
 
 
 def gather_strings(value: str, device="cpu"):
-    """every rank's string on every rank (fixed 64-byte slots; hashes)"""
+    """every rank's string on every rank (fixed 128-byte slots; hashes)"""
     rank, world, _ = rank_world()
     if not dist.is_initialized():
         return [value]
-    buf = torch.zeros((64,), dtype=torch.uint8, device=device)
-    b = value.encode()[:64]
+    buf = torch.zeros((128,), dtype=torch.uint8, device=device)
+    b = value.encode()
+    if len(b) > 128:
+        raise ValueError("gather_strings carries at most 128 bytes per rank")
     buf[:len(b)] = torch.tensor(list(b), dtype=torch.uint8, device=device)
     out = [torch.zeros_like(buf) for _ in range(world)]
     dist.all_gather(out, buf)

@@ -234,12 +234,22 @@ def test_sequence_streamer_matches_resident_path(cuda):
     cm = _carmask(disp.shape[1:])
     eng = RoadPath(trials=T, samples=S, carmask=cm, max_frames=F)
     ref = to_host(eng.process(disp, bgr, seed=21))
-    sr = SequenceStreamer(trials=T, samples=S, carmask=cm, chunk=3)
+    sr = SequenceStreamer(trials=T, samples=S, carmask=cm, chunk=3, upload="full")
     out = sr.run_sync(torch.from_numpy(disp).pin_memory(), torch.from_numpy(bgr).pin_memory(), seed=21)
     assert np.array_equal(out["counts"].numpy(), ref["counts"])
     assert np.array_equal(out["road_mask"].numpy(), ref["road_mask"])
     assert np.array_equal(out["planes"].numpy(), ref["planes"])
     assert sr.h2d_bytes == F * (544 * 1024 + 272 * 1024 * 3) and ref["road_mask"].any()
+    # the default: only the lattice rows of the disparity travel as well.  N (cloud points) is still the full count:
+    # it is a count over lattice sites
+    sl = SequenceStreamer(trials=T, samples=S, carmask=cm, chunk=3)
+    outl = sl.run_sync(torch.from_numpy(disp).pin_memory(), torch.from_numpy(bgr).pin_memory(), seed=21)
+    for k in ("counts", "road_mask", "planes"):
+        assert np.array_equal(outl[k].numpy(), ref[k]), k
+    assert sl.h2d_bytes == F * (272 * 1024 + 272 * 1024 * 3)
+    # the engines' filled frames are right on the lattice rows: engine 1 still holds frames 3-5, engine 0 frame 6
+    for t, k, j in ((3, 1, 0), (4, 1, 1), (5, 1, 2), (6, 0, 0)):
+        assert np.array_equal(sl.engines[k].filled[j, ::2].cpu().numpy(), ref["filled"][t, ::2]), t
     out2 = sr.run_sync(disp, bgr, seed=21, out=out)               # pageable numpy input, buffers reused
     assert np.array_equal(out2["road_mask"].numpy(), ref["road_mask"])
 

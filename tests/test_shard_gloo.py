@@ -22,6 +22,7 @@ WORKER = textwrap.dedent("""
     import numpy as np
     planes = np.zeros((1, 8)); planes[0, 6] = rank; planes[0, 7] = 1.0
     mine = shard.result_sha((d > 40).astype(np.uint8) * 255, planes, np.full((1, 4), seq, np.int32))
+    mine = mine + ":" + mine[:16]                     # the length bench.py sends (81 characters)
     everyone = shard.gather_strings(mine)
     print(json.dumps({"rank": rank, "world": world, "seq": seq, "sha": hashlib.sha256(d.tobytes()).hexdigest(),
                       "max": mx, "frames": frames, "result_sha": mine, "gathered": everyone}), flush=True)
@@ -47,4 +48,4 @@ def test_two_ranks_gloo(tmp_path):
     for o in outs:
         assert o["world"] == 2 and o["max"] == [15.0, 3.0] and o["frames"] == [14.0]
         assert o["gathered"] == [outs[0]["result_sha"], outs[1]["result_sha"]]      # every rank sees every rank's hash
-    assert len(outs[0]["result_sha"]) == 64 and outs[0]["result_sha"] != outs[1]["result_sha"]
+    assert len(outs[0]["result_sha"]) == 81 and outs[0]["result_sha"] != outs[1]["result_sha"]
