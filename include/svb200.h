@@ -125,12 +125,16 @@ int svb_cloud_export(const uint32_t *records, int rec_stride_words, int n, const
  * max_m: an upper bound of every frame's cloud size known to the host (e.g. the number of lattice sites
  *        inside carmask), or 0.  When 4*max_m bytes fit in shared memory each block stages its frame's
  *        cloud there once and the S gathers of a hypothesis become shared-memory reads; frames that
- *        turn out larger than max_m, and max_m = 0, gather from global memory (L2). */
+ *        turn out larger than max_m, and max_m = 0, gather from global memory (L2).
+ * flags: SVB_RANSAC_SHARE_SM = blocks of 512 threads instead of 1024 (half of an SM's registers), so that blocks of a
+ *        kernel launched on another stream can run on the same SM at the same time (pipeline.RoadPath(overlap=True)
+ *        runs two half-batches on two streams).  Same results. */
+#define SVB_RANSAC_SHARE_SM 1
 int svb_ransac_score(const uint32_t *mcloud, int rec_stride_words, int64_t slab_stride_records,
                      const int32_t *counts, int counts_stride, int counts_col,
                      int F, int T, int S, int max_m, const svb_camera *cam,
                      const int32_t *sample_idx, const int32_t *triple_idx,
-                     uint64_t rng_seed, int frame0,
+                     uint64_t rng_seed, int frame0, int flags,
                      double *errors, void *stream);
 int svb_ransac_dump_indices(const uint32_t *mcloud, int rec_stride_words, int64_t slab_stride_records,
                             const int32_t *counts, int counts_stride, int counts_col,

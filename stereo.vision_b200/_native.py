@@ -17,7 +17,8 @@ LIB_PATH = os.path.join(_PKG, "libsvb200.so")
 HUE_BINS = 1001
 HIST_STRIDE = 1024
 PLANE_STRIDE = 8
-ABI_VERSION = 12
+RANSAC_SHARE_SM = 1
+ABI_VERSION = 13
 SVB_OK, SVB_E_NULL, SVB_E_SHAPE, SVB_E_ARG, SVB_E_SCRATCH, SVB_E_LIMIT = 0, -1, -2, -3, -4, -5      # include/svb200.h
 COMPACT_STATIC_MAX_N = 4194304
 SVB_MAX_DIM = 2048                                                                  # csrc/svb_common.cuh
@@ -57,7 +58,7 @@ SIGNATURES = {
     "svb_project_compact": (I, [P, P, P, I, I, I, I, CAMP, P, P, P, P, L, P]),
     "svb_project_compact_counted": (I, [P, P, P, I, I, I, I, CAMP, P, P, P, P, L, P]),
     "svb_cloud_export": (I, [P, I, I, CAMP, P, P, P, P, P, P, P]),
-    "svb_ransac_score": (I, [P, I, L, P, I, I, I, I, I, I, CAMP, P, P, U64, I, P, P]),
+    "svb_ransac_score": (I, [P, I, L, P, I, I, I, I, I, I, CAMP, P, P, U64, I, I, P, P]),
     "svb_ransac_dump_indices": (I, [P, I, L, P, I, I, I, I, I, CAMP, U64, I, P, P, P]),
     "svb_pyrandom_setsize": (L, [I]),
     "svb_ransac_replay_scratch_bytes": (L, [I, I, I]),

@@ -310,7 +310,7 @@ ransac_score_persistent(const uint32_t *__restrict__ mcloud, int stride, int64_t
     extern __shared__ __align__(128) uint32_t s_rec[];
     __shared__ double s_invd[256];
     __shared__ __align__(8) uint64_t s_bar;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = RANSAC_SMEM_THREADS / 32;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = (int)blockDim.x >> 5;
     const int64_t total = (int64_t)F * T;
     const int64_t w0 = total * blockIdx.x / gridDim.x, w1 = total * (blockIdx.x + 1) / gridDim.x;
     if (tid < 256) s_invd[tid] = tid ? __ddiv_rn(1.0, (double)tid) : 0.0;
@@ -336,7 +336,7 @@ ransac_score_persistent(const uint32_t *__restrict__ mcloud, int stride, int64_t
                 for (uint32_t o = 0; o < bytes; o += RANSAC_BULK_BYTES)
                     bulk_g2s((char *)s_rec + o, (const char *)rec + o, min(RANSAC_BULK_BYTES, bytes - o), &s_bar);
             }
-            for (int i = nb + tid; i < Mi; i += RANSAC_SMEM_THREADS) s_rec[i] = __ldg(rec + (int64_t)i * stride);
+            for (int i = nb + tid; i < Mi; i += (int)blockDim.x) s_rec[i] = __ldg(rec + (int64_t)i * stride);
             if (bulk && nb > 0) { mbar_wait(&s_bar, phase); phase ^= 1u; }
             __syncthreads();
         }
@@ -366,8 +366,11 @@ extern "C" int svb_ransac_score(const uint32_t *mcloud, int rec_stride_words, in
                                 const int32_t *counts, int counts_stride, int counts_col,
                                 int F, int T, int S, int max_m, const svb_camera *cam,
                                 const int32_t *sample_idx, const int32_t *triple_idx,
-                                uint64_t rng_seed, int frame0, double *errors, void *stream) {
+                                uint64_t rng_seed, int frame0, int flags, double *errors, void *stream) {
     if (!mcloud || !counts || !cam || !errors) return SVB_E_NULL;
+    if (flags & ~SVB_RANSAC_SHARE_SM) return SVB_E_ARG;
+    // SHARE_SM: 512-thread blocks (half of an SM's registers) so that blocks of a kernel on another stream co-reside
+    const int threads = (flags & SVB_RANSAC_SHARE_SM) ? RANSAC_SMEM_THREADS / 2 : RANSAC_SMEM_THREADS;
     if ((sample_idx == nullptr) != (triple_idx == nullptr)) return SVB_E_NULL;
     if (F < 1 || T < 1 || S < 1) return SVB_E_SHAPE;
     if ((rec_stride_words != 1 && rec_stride_words != 2) || counts_stride < 1 || counts_col < 0 ||
@@ -395,11 +398,11 @@ extern "C" int svb_ransac_score(const uint32_t *mcloud, int rec_stride_words, in
         if (dev >= 0 && dev < 64) attr_done[dev] = true;
     }
     if (sample_idx)
-        ransac_score_persistent<true><<<blocks, RANSAC_SMEM_THREADS, smem, st>>>(
+        ransac_score_persistent<true><<<blocks, threads, smem, st>>>(
             mcloud, rec_stride_words, slab_stride_records, counts, counts_stride, counts_col, F, T, S, cap, c,
             sample_idx, triple_idx, rng_seed, frame0, errors);
     else
-        ransac_score_persistent<false><<<blocks, RANSAC_SMEM_THREADS, smem, st>>>(
+        ransac_score_persistent<false><<<blocks, threads, smem, st>>>(
             mcloud, rec_stride_words, slab_stride_records, counts, counts_stride, counts_col, F, T, S, cap, c,
             nullptr, nullptr, rng_seed, frame0, errors);
     SVB_LAUNCH_CHECK();

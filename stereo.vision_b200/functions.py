@@ -289,7 +289,7 @@ def RANSAC(points, trials):
     planes = torch.zeros((1, N.PLANE_STRIDE), dtype=torch.float64, device=dev)
     cc, st = N.ccam(points.camera), N.stream_ptr()
     N.check(lib.svb_ransac_score(N.ptr(points.records), 2, 0, N.ptr(counts), 1, 0, 1, T, S, M, C.byref(cc), N.ptr(si),
-                                 N.ptr(ti), 0, 0, N.ptr(errors), st), "svb_ransac_score")
+                                 N.ptr(ti), 0, 0, 0, N.ptr(errors), st), "svb_ransac_score")
     N.check(lib.svb_ransac_finalize(N.ptr(points.records), 2, 0, N.ptr(counts), 1, 0, 1, T, S, C.byref(cc), N.ptr(ti),
                                     0, 0, N.ptr(errors), 0.0, N.ptr(planes), st), "svb_ransac_finalize")
     N.count(2)

@@ -73,12 +73,18 @@ class BatchResult:
 class RoadPath:
     def __init__(self, shape=(544, 1024), step=2, trials=600, samples=600, point_threshold=0.05,
                  colour_threshold=10, carmask=None, camera: Camera = DEFAULT_CAMERA, max_frames=1,
-                 device="cuda:0", use_reproj_table=True, road_path="sites"):
+                 device="cuda:0", use_reproj_table=True, road_path="sites", overlap=False):
         if road_path not in ("sites", "records"):
             raise ValueError("road_path is 'sites' or 'records'")
         N.require_cuda()
         self.lib = N.load()
         self.device = torch.device(device)
+        # overlap=True: a batch of >= 32 frames is processed as two half-batches on two streams, the hypothesis scoring of
+        # one half (512-thread blocks) beside the projection / road-point kernels of the other.  Same results (after the
+        # fill, a frame depends on no other frame).  Off by default: measured on B200 it gains nothing (0.585 ms against
+        # 0.574 ms per 300 frames) -- every kernel of the path is limited by instruction issue, not by DRAM bandwidth
+        # (DESIGN.md 8), so there is no idle resource for the other half to use.
+        self.overlap, self._side, self._scratch2 = bool(overlap), None, None
         with torch.cuda.device(self.device):
             self._init(shape, step, trials, samples, point_threshold, colour_threshold, carmask, camera, max_frames,
                        use_reproj_table, road_path)
@@ -173,36 +179,19 @@ class RoadPath:
         F = disp.shape[0]
         if F > self.Fmax or tuple(disp.shape[1:]) != (self.H, self.W) or tuple(bgr.shape) != (F, self.H, self.W, 3):
             raise ValueError("bad batch shape %s / %s" % (tuple(disp.shape), tuple(bgr.shape)))
-        H, W, st = self.H, self.W, N.stream_ptr()
+        H, W = self.H, self.W
         res = BatchResult(self, F)
-        if fill:
-            # a1 + the counting pass of a4 in one kernel; the scratch carries the counts to the projection
-            prev_t = _as_cuda_u8(prev, dev) if prev is not None else None
-            if prev_t is not None and tuple(prev_t.shape) != (H, W):
-                raise ValueError("prev is %s, the frames are %s" % (tuple(prev_t.shape), (H, W)))
-            if prev_t is not None and prev_t.untyped_storage().data_ptr() == self.filled.untyped_storage().data_ptr():
-                prev_t = prev_t.clone()     # result.filled[-1] of the last call: the fill kernel is about to overwrite it
-            N.check(lib.svb_fill_sequence_counted(N.ptr(disp), N.ptr(prev_t), N.ptr(self.filled), N.ptr(self.carmask),
-                                                  F, H, W, self.step, N.ptr(self.scratch), self.scratch.numel(), st),
-                    "svb_fill_sequence_counted")
-            project = lib.svb_project_compact_counted
-        else:
-            self.filled[:F].copy_(disp)
-            project = lib.svb_project_compact
-        src = self.filled
-        N.check(project(N.ptr(src), N.ptr(self.carmask), N.ptr(bgr), F, H, W, self.step,
-                        C.byref(self._cam), N.ptr(self.cloud), N.ptr(self.mcloud), N.ptr(self.counts),
-                        N.ptr(self.scratch), self.scratch.numel(), st), "svb_project_compact")
-        si = ti = None
+        # ---- draws: explicit index tensors, the reference's (replayed on the device per range below), or device draws
+        si = ti = seeds_t = None
+        chain = py_stream is not None
+        replay = py_seeds is not None or chain
         if indices is not None:
             si = indices[0] if torch.is_tensor(indices[0]) else torch.from_numpy(np.ascontiguousarray(indices[0], dtype=np.int32))
             ti = indices[1] if torch.is_tensor(indices[1]) else torch.from_numpy(np.ascontiguousarray(indices[1], dtype=np.int32))
             si = si.to(dev).contiguous().view(F, self.T, self.S)
             ti = ti.to(dev).contiguous().view(F, self.T, 3)
-        elif py_seeds is not None or py_stream is not None:
+        elif replay:
             si, ti = self._replay_buffers(F)
-            chain = py_stream is not None
-            seeds_t = None
             if chain and not isinstance(py_stream, int):
                 self.mt_setstate(py_stream)
             else:
@@ -210,34 +199,87 @@ class RoadPath:
                 if len(vals) != (1 if chain else F) or min(vals) < 0 or max(vals) >= 1 << 64:
                     raise ValueError("py_seeds: one non-negative 64-bit integer per frame")
                 seeds_t = torch.tensor([v - (1 << 64) if v >= 1 << 63 else v for v in vals], dtype=torch.int64).to(dev)
-            N.check(lib.svb_ransac_replay_draws(N.ptr(self.mcloud), 1, self.L, N.ptr(self.counts), 4, 1, F, self.T, self.S,
-                                                max(self.max_m, 1), C.byref(self._cam), N.ptr(seeds_t), N.ptr(self._mt),
-                                                1 if chain else 0, N.ptr(si), N.ptr(ti), N.ptr(self._replay_scratch),
-                                                self._replay_scratch.numel(), st), "svb_ransac_replay_draws")
-            N.count(1)
         res.indices = (si, ti) if si is not None else None
-        N.check(lib.svb_ransac_score(N.ptr(self.mcloud), 1, self.L, N.ptr(self.counts), 4, 1, F, self.T, self.S,
-                                     self.max_m, C.byref(self._cam), N.ptr(si), N.ptr(ti), seed, frame0, N.ptr(self.errors), st),
-                "svb_ransac_score")
-        N.check(lib.svb_ransac_finalize(N.ptr(self.mcloud), 1, self.L, N.ptr(self.counts), 4, 1, F, self.T, self.S,
-                                        C.byref(self._cam), N.ptr(ti), seed, frame0, N.ptr(self.errors),
-                                        self.point_threshold, N.ptr(self.planes), st), "svb_ransac_finalize")
         ov = None
         if overlay is not None:
             ov = _as_cuda_u8(overlay, dev)
             res.overlay = ov
+        # ---- frame ranges: one, or two half-batches on two side streams (self.overlap).  Only the fill chains frames
+        # (functions.py:140-147), so it runs range after range on the caller's stream; everything behind it is per frame.
+        cur = torch.cuda.current_stream(dev)
+        split = self.overlap and F >= 2 * self.OVERLAP_MIN_FRAMES and not chain
+        ranges = [(0, F // 2), (F // 2, F)] if split else [(0, F)]
+        if split and self._side is None:
+            self._side = (torch.cuda.Stream(dev), torch.cuda.Stream(dev))
+            self._scratch2 = torch.empty_like(self.scratch)
+        scratches = [self.scratch, self._scratch2] if split else [self.scratch]
+        ready = []
+        if fill:
+            prev_t = _as_cuda_u8(prev, dev) if prev is not None else None
+            if prev_t is not None and tuple(prev_t.shape) != (H, W):
+                raise ValueError("prev is %s, the frames are %s" % (tuple(prev_t.shape), (H, W)))
+            if prev_t is not None and prev_t.untyped_storage().data_ptr() == self.filled.untyped_storage().data_ptr():
+                prev_t = prev_t.clone()     # result.filled[-1] of the last call: the fill kernel is about to overwrite it
+            for (a, b), sc in zip(ranges, scratches):
+                # a1 + the counting pass of a4 in one kernel; the scratch carries the counts to the projection
+                N.check(lib.svb_fill_sequence_counted(N.ptr(disp[a:b]), N.ptr(prev_t if a == 0 else self.filled[a - 1]),
+                                                      N.ptr(self.filled[a:b]), N.ptr(self.carmask), b - a, H, W, self.step,
+                                                      N.ptr(sc), sc.numel(), C.c_void_p(cur.cuda_stream)), "svb_fill_sequence_counted")
+                if split:
+                    ready.append(torch.cuda.Event())
+                    ready[-1].record(cur)
+        else:
+            self.filled[:F].copy_(disp)
+            if split:
+                ready = [torch.cuda.Event(), torch.cuda.Event()]
+                ready[0].record(cur)
+                ready[1] = ready[0]
+        for k, ((a, b), sc) in enumerate(zip(ranges, scratches)):
+            stream = self._side[k] if split else cur
+            if split:
+                stream.wait_event(ready[k])
+            self._stages(a, b, bgr, ov, si, ti, seeds_t, chain, replay, seed, frame0, fill, sc, C.c_void_p(stream.cuda_stream),
+                         N.RANSAC_SHARE_SM if split else 0)
+        if split:
+            cur.wait_stream(self._side[0])
+            cur.wait_stream(self._side[1])
+        N.count(len(ranges) * (KERNELS_PER_BATCH - 1 + self.road_launches + (1 if replay else 0)) + (0 if fill else 2))
+        return res
+
+    OVERLAP_MIN_FRAMES = 16
+
+    def _stages(self, a, b, bgr, ov, si, ti, seeds_t, chain, replay, seed, frame0, fill, scratch, st, score_flags):
+        """a2-a14 of frames [a, b) of the batch, enqueued on stream `st`: clouds, draws, hypotheses, plane, road points."""
+        lib, H, W, n = self.lib, self.H, self.W, b - a
+        cloud, mcloud, counts, planes = self.cloud[a:b], self.mcloud[a:b], self.counts[a:b], self.planes[a:b]
+        errors, src, bgr = self.errors[a:b], self.filled[a:b], bgr[a:b]
+        project = lib.svb_project_compact_counted if fill else lib.svb_project_compact
+        N.check(project(N.ptr(src), N.ptr(self.carmask), N.ptr(bgr), n, H, W, self.step, C.byref(self._cam), N.ptr(cloud),
+                        N.ptr(mcloud), N.ptr(counts), N.ptr(scratch), scratch.numel(), st), "svb_project_compact")
+        if si is not None:
+            si, ti = si[a:b], ti[a:b]
+        if replay:
+            per = (self._replay_scratch.numel() - 256) // self.Fmax // 4 * 4      # bytes of workspace per frame
+            rs = self._replay_scratch[a * per:]                                   # ranges run concurrently: disjoint slices
+            N.check(lib.svb_ransac_replay_draws(N.ptr(mcloud), 1, self.L, N.ptr(counts), 4, 1, n, self.T, self.S, max(self.max_m, 1),
+                                                C.byref(self._cam), N.ptr(seeds_t[a:b] if (seeds_t is not None and not chain) else seeds_t),
+                                                N.ptr(self._mt[a:b]), 1 if chain else 0, N.ptr(si), N.ptr(ti),
+                                                N.ptr(rs), rs.numel(), st), "svb_ransac_replay_draws")
+        N.check(lib.svb_ransac_score(N.ptr(mcloud), 1, self.L, N.ptr(counts), 4, 1, n, self.T, self.S, self.max_m, C.byref(self._cam),
+                                     N.ptr(si), N.ptr(ti), seed, frame0 + a, score_flags, N.ptr(errors), st), "svb_ransac_score")
+        N.check(lib.svb_ransac_finalize(N.ptr(mcloud), 1, self.L, N.ptr(counts), 4, 1, n, self.T, self.S, C.byref(self._cam),
+                                        N.ptr(ti), seed, frame0 + a, N.ptr(errors), self.point_threshold, N.ptr(planes), st),
+                "svb_ransac_finalize")
+        ovr = ov[a:b] if ov is not None else None
         if self.sites_road:
-            N.check(lib.svb_road_points_sites(N.ptr(src), N.ptr(bgr), N.ptr(self.planes), F, H, W, self.step, C.byref(self._cam),
-                                              self.colour_threshold, N.ptr(self.reproj_bits), N.ptr(self.hist), N.ptr(self.road_mask),
-                                              N.ptr(ov), N.ptr(self.counts), N.ptr(self.scratch), self.scratch.numel(), st),
+            N.check(lib.svb_road_points_sites(N.ptr(src), N.ptr(bgr), N.ptr(planes), n, H, W, self.step, C.byref(self._cam),
+                                              self.colour_threshold, N.ptr(self.reproj_bits), N.ptr(self.hist[a:b]),
+                                              N.ptr(self.road_mask[a:b]), N.ptr(ovr), N.ptr(counts), N.ptr(scratch), scratch.numel(), st),
                     "svb_road_points_sites")
         else:
-            N.check(lib.svb_road_points(N.ptr(self.cloud), N.ptr(self.counts), N.ptr(self.planes), F, H, W, self.step,
-                                        C.byref(self._cam), self.colour_threshold, N.ptr(self.reproj_bits), N.ptr(self.hist), N.ptr(self.road_mask),
-                                        N.ptr(ov), N.ptr(self.counts), N.ptr(self.scratch), self.scratch.numel(), st),
-                    "svb_road_points")
-        N.count(KERNELS_PER_BATCH - 1 + self.road_launches + (0 if fill else 2))   # no fill: copy + count kernels
-        return res
+            N.check(lib.svb_road_points(N.ptr(cloud), N.ptr(counts), N.ptr(planes), n, H, W, self.step, C.byref(self._cam),
+                                        self.colour_threshold, N.ptr(self.reproj_bits), N.ptr(self.hist[a:b]), N.ptr(self.road_mask[a:b]),
+                                        N.ptr(ovr), N.ptr(counts), N.ptr(scratch), scratch.numel(), st), "svb_road_points")
 
     # the generator state of the reference-identical mode, in random.getstate() / setstate() form
     @property

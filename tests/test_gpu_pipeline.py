@@ -83,6 +83,41 @@ def test_small_ragged_shapes(cuda, shape, step):
         assert np.array_equal(res[k], res3[k]), k
 
 
+def test_two_half_batches_on_two_streams_equal_one_batch(cuda):
+    """RoadPath(overlap=True) runs a batch of >= 32 frames as two half-batches on two streams (512-thread scorer blocks
+    beside the other half's kernels): every output equals the one-batch run's, for device draws, the reference's draws
+    (per-frame seeds) and explicit indices; an odd frame count; two calls in a row (buffers of the last call in flight)."""
+    import torch
+    from stereo.vision_b200.pipeline import RoadPath
+    F, T, S = 37, 300, 400
+    disp, bgr = synth.make_sequence(14, F)
+    cm = _carmask(disp.shape[1:])
+    one = RoadPath(trials=T, samples=S, carmask=cm, max_frames=F, overlap=False)
+    two = RoadPath(trials=T, samples=S, carmask=cm, max_frames=F, overlap=True)
+    seeds = [synth.ransac_seed(14, t) for t in range(F)]
+    for kw in (dict(seed=77, frame0=5), dict(py_seeds=seeds), dict(seed=78)):
+        a = one.process(disp, bgr, **kw)
+        b = two.process(disp, bgr, **kw)
+        assert two._side is not None
+        for k in ("filled", "counts", "planes", "errors", "hist", "road_mask", "cloud", "mcloud"):
+            ta, tb = getattr(a, k), getattr(b, k)
+            if k in ("cloud", "mcloud"):                    # slabs: only the first N / M records of a frame are defined
+                n = a.counts[:, 0 if k == "cloud" else 1].cpu().numpy()
+                for t in range(F):
+                    assert torch.equal(ta[t, :n[t]], tb[t, :n[t]]), (k, t)
+            else:
+                assert torch.equal(ta, tb), (k, list(kw))
+        if "py_seeds" in kw:
+            assert torch.equal(a.indices[0], b.indices[0]) and torch.equal(a.indices[1], b.indices[1])
+            assert torch.equal(one.mt_state[:F], two.mt_state[:F])
+    si, ti = one.dump_indices(F, seed=78)
+    c = two.process(disp, bgr, indices=(si, ti))
+    # explicit indices are summed in another order than device draws: the winner's error agrees to rounding, the rest exactly
+    assert torch.equal(c.planes[:, :5], a.planes[:, :5]) and torch.equal(c.planes[:, 6:], a.planes[:, 6:])
+    assert torch.allclose(c.planes[:, 5], a.planes[:, 5], rtol=1e-12, atol=0) and torch.equal(c.road_mask, a.road_mask)
+    assert (a.planes[:, 7] == 1).all() and a.road_mask.any()
+
+
 def test_no_plane_when_masked_cloud_too_small(cuda):
     """M < S: every trial raises in the reference -> RANSAC returns (None, None) -> black mask."""
     from stereo.vision_b200.pipeline import RoadPath
