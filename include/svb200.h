@@ -320,13 +320,16 @@ int svb_road_hull(const uint32_t *bits, int F, int H, int W, int cap, int32_t *h
  *                       block odd in [1,31], W - 128 > block / 2.  The cost volumes travel through `scratch`:
  *                       svb_sgbm_scratch_bytes(f, H, W, 128) is what f frames in flight need (250 MB per 1024x544
  *                       frame); any size from one frame up is accepted and the batch is processed in chunks.
+ *                       *status (device int32, may be NULL; the caller zeroes it) gets bit 0 when a block cost exceeded
+ *                       32767 - P2 (a mean pixel cost above 74 over the whole window): OpenCV's own int16 stores wrap
+ *                       or saturate there depending on its SIMD path, so the output is then not specified.
  * svb_filter_speckles = cv2.filterSpeckles(disp16, new_val, max_size, max_diff) in place      (functions.py:111)
  * svb_disparity_scale = threshold-to-zero, (d / 16.) -> uint8, x (256. / max_disparity) -> uint8 (functions.py:117-127;
  *                       the crop of functions.py:121-123 is a view the host takes). */
 int     svb_sgbm_supported(int H, int W, int num_disparities, int block);
 int64_t svb_sgbm_scratch_bytes(int F, int H, int W, int num_disparities);
 int     svb_sgbm_compute(const uint8_t *grayL, const uint8_t *grayR, int F, int H, int W, int num_disparities, int block,
-                         int16_t *disp16, void *scratch, int64_t scratch_bytes, void *stream);
+                         int16_t *disp16, int32_t *status, void *scratch, int64_t scratch_bytes, void *stream);
 int64_t svb_speckle_scratch_bytes(int F, int H, int W);
 int     svb_filter_speckles(int16_t *img16, int F, int H, int W, int new_val, int max_size, int max_diff, void *scratch,
                             int64_t scratch_bytes, void *stream);

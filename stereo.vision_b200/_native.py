@@ -18,7 +18,7 @@ HUE_BINS = 1001
 HIST_STRIDE = 1024
 PLANE_STRIDE = 8
 RANSAC_SHARE_SM = 1
-ABI_VERSION = 13
+ABI_VERSION = 14
 SVB_OK, SVB_E_NULL, SVB_E_SHAPE, SVB_E_ARG, SVB_E_SCRATCH, SVB_E_LIMIT = 0, -1, -2, -3, -4, -5      # include/svb200.h
 COMPACT_STATIC_MAX_N = 4194304
 SVB_MAX_DIM = 2048                                                                  # csrc/svb_common.cuh
@@ -84,7 +84,7 @@ SIGNATURES = {
     "svb_road_hull_scratch_bytes": (L, [I, I]),
     "svb_sgbm_supported": (I, [I, I, I, I]),
     "svb_sgbm_scratch_bytes": (L, [I, I, I, I]),
-    "svb_sgbm_compute": (I, [P, P, I, I, I, I, I, P, P, L, P]),
+    "svb_sgbm_compute": (I, [P, P, I, I, I, I, I, P, P, P, L, P]),
     "svb_speckle_scratch_bytes": (L, [I, I, I]),
     "svb_filter_speckles": (I, [P, I, I, I, I, I, I, P, L, P]),
     "svb_disparity_scale": (I, [P, L, I, P, P]),

@@ -1,7 +1,7 @@
 // ABI bookkeeping: version and error strings.
 #include "svb_common.cuh"
 
-extern "C" int svb_version(void) { return 13; }
+extern "C" int svb_version(void) { return 14; }
 
 extern "C" const char *svb_error_string(int code) {
     switch (code) {

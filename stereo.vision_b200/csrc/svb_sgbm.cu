@@ -248,8 +248,10 @@ __global__ void __launch_bounds__(256) sgbm_path_kernel(const uint2 *__restrict_
 // written once for the other directions, and feeds the vertical path (DIR 2) on the spot: C is not read back for
 // it.  The row that leaves the window was read 2*SH2+1 rows earlier: it waits in a per-warp ring in shared memory
 // (lane-private slots, no synchronisation), so hsum is read from memory exactly once.
+// *status (may be NULL) gets bit 0 when a block cost exceeds 32767 - P2: the int16 cost stores of OpenCV wrap or
+// saturate there depending on its SIMD path, so beyond that point no output is "the reference's".
 __global__ void __launch_bounds__(256) sgbm_vsum_v_kernel(const uint2 *__restrict__ hsum, int F, int H, int w1, int SH2,
-                                                          uint2 *__restrict__ C, uint16_t *__restrict__ E) {
+                                                          uint2 *__restrict__ C, uint16_t *__restrict__ E, int32_t *__restrict__ status) {
     extern __shared__ uint2 vring[];                               // [warp of the CTA][slot][lane]
     const int RING = 2 * SH2 + 2;
     const int lane = threadIdx.x & 31;
@@ -270,6 +272,8 @@ __global__ void __launch_bounds__(256) sgbm_vsum_v_kernel(const uint2 *__restric
         acc.x = __vadd2(acc.x, hlast.x); acc.y = __vadd2(acc.y, hlast.y);
     }
     PathState s = {0, 0, 0, 0, 0};
+    const uint32_t lim = (uint32_t)(SG_MAXC - SG_P2) * 0x00010001u;      // per 16-bit half
+    uint32_t over = __vcmpgtu2(acc.x, lim) | __vcmpgtu2(acc.y, lim);
     C[base] = acc;
     path_step(s, acc, lane);
     E[base] = (uint16_t)excess4(s, acc);
@@ -281,6 +285,7 @@ __global__ void __launch_bounds__(256) sgbm_vsum_v_kernel(const uint2 *__restric
         uint2 b = h0;
         if (y - SH2 - 1 >= 0) { b = ring[oi * 32]; oi = oi + 1 == RING ? 0 : oi + 1; }
         acc.x = __vsub2(__vadd2(acc.x, hlast.x), b.x); acc.y = __vsub2(__vadd2(acc.y, hlast.y), b.y);
+        over |= __vcmpgtu2(acc.x, lim) | __vcmpgtu2(acc.y, lim);
         C[base + (int64_t)y * rs] = acc;
         path_step(s, acc, lane);
         E[base + (int64_t)y * rs] = (uint16_t)excess4(s, acc);
@@ -303,6 +308,7 @@ __global__ void __launch_bounds__(256) sgbm_vsum_v_kernel(const uint2 *__restric
         for (int k = 0; k < 8; ++k) a[k] = an[k];
     }
     for (; y < H; ++y) advance(y, __ldg(hsum + base + (int64_t)min(y + SH2, H - 1) * rs));
+    if (status && __any_sync(0xffffffffu, over != 0u) && lane == 0) atomicOr(status, 1);
 }
 
 // nibbles of a uint16 (each at most 10 here) to the bytes of a word
@@ -571,7 +577,7 @@ extern "C" int64_t svb_sgbm_scratch_bytes(int F, int H, int W, int num_dispariti
 }
 
 extern "C" int svb_sgbm_compute(const uint8_t *grayL, const uint8_t *grayR, int F, int H, int W, int num_disparities, int block,
-                                int16_t *disp16, void *scratch, int64_t scratch_bytes, void *stream) {
+                                int16_t *disp16, int32_t *status, void *scratch, int64_t scratch_bytes, void *stream) {
     if (!grayL || !grayR || !disp16 || !scratch) return SVB_E_NULL;
     if (F < 1) return SVB_E_SHAPE;
     if (!svb_sgbm_supported(H, W, num_disparities, block)) return SVB_E_ARG;
@@ -605,7 +611,7 @@ extern "C" int svb_sgbm_compute(const uint8_t *grayL, const uint8_t *grayR, int 
               cudaError_t e = cudaFuncSetAttribute(sgbm_vsum_v_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)vs);
               if (e != cudaSuccess) return (int)e;
           }
-          sgbm_vsum_v_kernel<<<(unsigned)(((int64_t)n * w1 + 7) / 8), 256, vs, st>>>((const uint2 *)hs, n, H, w1, SW2, (uint2 *)Cv, E0); }
+          sgbm_vsum_v_kernel<<<(unsigned)(((int64_t)n * w1 + 7) / 8), 256, vs, st>>>((const uint2 *)hs, n, H, w1, SW2, (uint2 *)Cv, E0, status); }
         SVB_LAUNCH_CHECK();
         { ProfScope ps(K_SGBM_PATH_D1, st); sgbm_path_kernel<1><<<diag_blocks, 256, 0, st>>>(C2, E + 0 * plane, n, H, w1); }
         { ProfScope ps(K_SGBM_PATH_D3, st); sgbm_path_kernel<3><<<diag_blocks, 256, 0, st>>>(C2, E + 1 * plane, n, H, w1); }

@@ -488,6 +488,10 @@ def disparity(grayL, grayR, max_disparity, crop_disparity):
                                     device=L.device)
         _state["matcher_key"] = key
     out = _state["matcher"].disparity(L, R)[0]
+    if int(_state["matcher"].status.item()) & 1:
+        import warnings
+        warnings.warn("disparity: a block cost exceeded 32767 - P2; cv2.StereoSGBM's own int16 stores wrap or saturate there "
+                      "depending on its SIMD path, so this output is not specified", RuntimeWarning)
     if crop_disparity:
         out = out[0:390, 135:out.shape[1]]
     return _back(out.clone(), was_tensor)

@@ -57,7 +57,7 @@ class BatchResult:
         self.errors = eng.errors[:F]          # float64 [F,T]
         self.hist = eng.hist[:F]              # uint32-as-int32 [F,1024]
         self.road_mask = eng.road_mask[:F]    # uint8 [F,H,W]
-        self.cloud = eng.cloud[:F]            # int64 [F,L] (uint64 records)
+        self.cloud = eng.cloud[:F] if eng.emit_cloud else None     # int64 [F,L] (uint64 records)
         self.mcloud = eng.mcloud[:F]          # int32 [F,L] (uint32 records)
         self.overlay = None
         self.indices = None                   # (sample_idx, triple_idx) when the draws were explicit or replayed
@@ -73,7 +73,7 @@ class BatchResult:
 class RoadPath:
     def __init__(self, shape=(544, 1024), step=2, trials=600, samples=600, point_threshold=0.05,
                  colour_threshold=10, carmask=None, camera: Camera = DEFAULT_CAMERA, max_frames=1,
-                 device="cuda:0", use_reproj_table=True, road_path="sites", overlap=False):
+                 device="cuda:0", use_reproj_table=True, road_path="sites", overlap=False, emit_cloud=True):
         if road_path not in ("sites", "records"):
             raise ValueError("road_path is 'sites' or 'records'")
         N.require_cuda()
@@ -85,6 +85,10 @@ class RoadPath:
         # 0.574 ms per 300 frames) -- every kernel of the path is limited by instruction issue, not by DRAM bandwidth
         # (DESIGN.md 8), so there is no idle resource for the other half to use.
         self.overlap, self._side, self._scratch2 = bool(overlap), None, None
+        # emit_cloud=False: the 8-byte coloured cloud (a4's first product) is neither written nor is the colour image
+        # read by the projection -- for callers who want masks, planes and counts only (SequenceStreamer).  The masked
+        # cloud (RANSAC's input) and N are produced as always; needs the road path that reads the disparity ("sites").
+        self.emit_cloud = bool(emit_cloud)
         with torch.cuda.device(self.device):
             self._init(shape, step, trials, samples, point_threshold, colour_threshold, carmask, camera, max_frames,
                        use_reproj_table, road_path)
@@ -112,7 +116,7 @@ class RoadPath:
         cm_host = self.carmask.cpu().numpy()
         self.max_m = int((cm_host[0:H - 1:self.step, 0:W - 1:self.step] != 0).sum())
         self.filled = torch.empty((F, H, W), dtype=torch.uint8, device=dev)
-        self.cloud = torch.empty((F, self.L), dtype=torch.int64, device=dev)
+        self.cloud = torch.empty((F if self.emit_cloud else 0, self.L), dtype=torch.int64, device=dev)
         self.mcloud = torch.empty((F, self.L), dtype=torch.int32, device=dev)
         self.counts = torch.zeros((F, 4), dtype=torch.int32, device=dev)
         self.errors = torch.empty((F, self.T), dtype=torch.float64, device=dev)
@@ -140,6 +144,8 @@ class RoadPath:
                            and bool(self.lib.svb_road_sites_supported(H, W, self.step)))
         if self.sites_road:
             self.road_launches = 2
+        if not self.emit_cloud and not self.sites_road:
+            raise ValueError("emit_cloud=False needs road_path='sites' (the records path reads the cloud)")
         self._si = self._ti = self._replay_scratch = None      # reference-identical draws (py_seeds): allocated on first use
 
     # ------------------------------------------------------------------
@@ -251,11 +257,13 @@ class RoadPath:
     def _stages(self, a, b, bgr, ov, si, ti, seeds_t, chain, replay, seed, frame0, fill, scratch, st, score_flags):
         """a2-a14 of frames [a, b) of the batch, enqueued on stream `st`: clouds, draws, hypotheses, plane, road points."""
         lib, H, W, n = self.lib, self.H, self.W, b - a
-        cloud, mcloud, counts, planes = self.cloud[a:b], self.mcloud[a:b], self.counts[a:b], self.planes[a:b]
+        cloud = self.cloud[a:b] if self.emit_cloud else None
+        mcloud, counts, planes = self.mcloud[a:b], self.counts[a:b], self.planes[a:b]
         errors, src, bgr = self.errors[a:b], self.filled[a:b], bgr[a:b]
         project = lib.svb_project_compact_counted if fill else lib.svb_project_compact
-        N.check(project(N.ptr(src), N.ptr(self.carmask), N.ptr(bgr), n, H, W, self.step, C.byref(self._cam), N.ptr(cloud),
-                        N.ptr(mcloud), N.ptr(counts), N.ptr(scratch), scratch.numel(), st), "svb_project_compact")
+        N.check(project(N.ptr(src), N.ptr(self.carmask), N.ptr(bgr) if self.emit_cloud else None, n, H, W, self.step,
+                        C.byref(self._cam), N.ptr(cloud), N.ptr(mcloud), N.ptr(counts), N.ptr(scratch), scratch.numel(), st),
+                "svb_project_compact")
         if si is not None:
             si, ti = si[a:b], ti[a:b]
         if replay:
@@ -326,10 +334,14 @@ class SequenceStreamer:
     """
 
     def __init__(self, shape=(544, 1024), step=2, trials=600, samples=600, carmask=None,
-                 camera: Camera = DEFAULT_CAMERA, chunk=30, device="cuda:0", upload="lattice", **kw):
+                 camera: Camera = DEFAULT_CAMERA, chunk=30, device="cuda:0", upload="lattice", pack_mask=False, **kw):
         if upload not in ("lattice", "full"):
             raise ValueError("upload is 'lattice' or 'full'")
         self.upload = upload
+        # pack_mask=True: the road masks come back as bit rows ("road_bits" int32 [F, H * ceil(W / 32)], bit x & 31 of
+        # word x >> 5 of a row = pixel x; unpack_road_mask() expands them) -- an eighth of the bytes over the link
+        self.pack_mask = bool(pack_mask)
+        kw.setdefault("emit_cloud", False)          # run() returns masks, planes and counts: nothing reads the cloud
         self.H, self.W = int(shape[0]), int(shape[1])
         self.step, self.chunk = int(step), int(chunk)
         self.device = torch.device(device)
@@ -339,6 +351,8 @@ class SequenceStreamer:
         self.din = [torch.zeros((C_, H, W), dtype=torch.uint8, device=dev) for _ in range(2)]
         self.cin = [torch.zeros((C_, H, W, 3), dtype=torch.uint8, device=dev) for _ in range(2)]
         self.s_in, self.s_cmp, self.s_out = (torch.cuda.Stream(dev) for _ in range(3))
+        self.words = int(N.load().svb_bits_words(H, W))
+        self.bits = [torch.empty((C_, self.words), dtype=torch.int32, device=dev) for _ in range(2)] if self.pack_mask else None
         self.lib = N.load()
         self.h2d_bytes = self.d2h_bytes = 0
         self._last_cmp, self._last_out = [None, None], [None, None]      # last use of buffer / engine k, across run() calls
@@ -374,10 +388,14 @@ class SequenceStreamer:
         F, H, W, Cn = disp.shape[0], self.H, self.W, self.chunk
         if tuple(disp.shape) != (F, H, W) or tuple(bgr.shape) != (F, H, W, 3):
             raise ValueError("bad sequence shape %s / %s" % (tuple(disp.shape), tuple(bgr.shape)))
-        if out is None or out["road_mask"].shape[0] != F:
-            out = {"road_mask": torch.empty((F, H, W), dtype=torch.uint8).pin_memory(),
-                   "planes": torch.empty((F, N.PLANE_STRIDE), dtype=torch.float64).pin_memory(),
+        mkey = "road_bits" if self.pack_mask else "road_mask"
+        if out is None or mkey not in out or out[mkey].shape[0] != F:
+            out = {"planes": torch.empty((F, N.PLANE_STRIDE), dtype=torch.float64).pin_memory(),
                    "counts": torch.empty((F, 4), dtype=torch.int32).pin_memory()}
+            if self.pack_mask:
+                out["road_bits"] = torch.empty((F, self.words), dtype=torch.int32).pin_memory()
+            else:
+                out["road_mask"] = torch.empty((F, H, W), dtype=torch.uint8).pin_memory()
         s_in, s_cmp, s_out = self.s_in, self.s_cmp, self.s_out
         chunks = [(a, min(F, a + Cn)) for a in range(0, F, Cn)]
         ev_in, ev_cmp, ev_out = {}, {}, {}
@@ -407,11 +425,18 @@ class SequenceStreamer:
                 prev = self.engines[1 - k].filled[chunks[i - 1][1] - chunks[i - 1][0] - 1] if i else None
                 r = self.engines[k].process(self.din[k][:n], self.cin[k][:n], prev=prev, seed=seed, frame0=a,
                                             py_seeds=None if py_seeds is None else py_seeds[a:b])
+                if self.pack_mask:
+                    N.check(self.lib.svb_pack_mask(N.ptr(r.road_mask), n, H, W, N.ptr(self.bits[k]), None,
+                                                   C.c_void_p(s_cmp.cuda_stream)), "svb_pack_mask")
+                    N.count(1)
                 ev_cmp[i] = torch.cuda.Event()
                 ev_cmp[i].record(s_cmp)
             with torch.cuda.stream(s_out):
                 s_out.wait_event(ev_cmp[i])
-                out["road_mask"][a:b].copy_(r.road_mask, non_blocking=True)
+                if self.pack_mask:
+                    out["road_bits"][a:b].copy_(self.bits[k][:n], non_blocking=True)
+                else:
+                    out["road_mask"][a:b].copy_(r.road_mask, non_blocking=True)
                 out["planes"][a:b].copy_(r.planes, non_blocking=True)
                 out["counts"][a:b].copy_(r.counts, non_blocking=True)
                 ev_out[i] = torch.cuda.Event()
@@ -422,6 +447,14 @@ class SequenceStreamer:
         self.d2h_bytes = int(sum(t.numel() * t.element_size() for t in out.values()))
         self._last = out
         return out
+
+    def unpack_road_mask(self, road_bits):
+        """uint8 [F,H,W] (0 / 255) of the bit rows run() returns with pack_mask=True (host side, numpy)"""
+        b = road_bits.numpy() if torch.is_tensor(road_bits) else np.asarray(road_bits)
+        F = b.shape[0]
+        wpr = (self.W + 31) // 32
+        bits = np.unpackbits(b.reshape(F, self.H, wpr).view(np.uint8), axis=2, bitorder="little")[:, :, :self.W]
+        return bits * np.uint8(255)
 
     def run_sync(self, disp, bgr, seed=0, out=None, py_seeds=None):
         out = self.run(disp, bgr, seed=seed, out=out, py_seeds=py_seeds)
@@ -580,6 +613,8 @@ class Matcher:
         self.scratch = torch.empty((nb,), dtype=torch.uint8, device=self.device)
         self.disp16 = torch.empty((self.F, self.H, self.W), dtype=torch.int16, device=self.device)
         self.disp8 = torch.empty((self.F, self.H, self.W), dtype=torch.uint8, device=self.device)
+        # bit 0 after compute(): a block cost exceeded 32767 - P2, where cv2's own output depends on its SIMD path
+        self.status = torch.zeros((1,), dtype=torch.int32, device=self.device)
 
     @_on_device
     def compute(self, grayL, grayR):
@@ -590,8 +625,10 @@ class Matcher:
         F = L.shape[0]
         if tuple(L.shape[1:]) != (self.H, self.W) or L.shape != R.shape or F > self.F:
             raise ValueError("expected up to %d pairs of %dx%d, got %s / %s" % (self.F, self.H, self.W, tuple(L.shape), tuple(R.shape)))
+        self.status.zero_()
         N.check(self.lib.svb_sgbm_compute(N.ptr(L), N.ptr(R), F, self.H, self.W, 128, self.block, N.ptr(self.disp16),
-                                          N.ptr(self.scratch), self.scratch.numel(), N.stream_ptr()), "svb_sgbm_compute")
+                                          N.ptr(self.status), N.ptr(self.scratch), self.scratch.numel(), N.stream_ptr()),
+                "svb_sgbm_compute")
         per = self.lib.svb_sgbm_scratch_bytes(1, self.H, self.W, 128) - 256           # bytes one frame in flight needs
         in_flight = max(1, min(F, (self.scratch.numel() - 256) // per))
         N.count(8 * ((F + in_flight - 1) // in_flight))      # per chunk: prefilter, hsum, vsum_v, d1, d3, h, final, median

@@ -285,6 +285,21 @@ def test_sequence_streamer_matches_resident_path(cuda):
     # the engines' filled frames are right on the lattice rows: engine 1 still holds frames 3-5, engine 0 frame 6
     for t, k, j in ((3, 1, 0), (4, 1, 1), (5, 1, 2), (6, 0, 0)):
         assert np.array_equal(sl.engines[k].filled[j, ::2].cpu().numpy(), ref["filled"][t, ::2]), t
+    # bit-packed masks over the link, and an engine that emits no cloud (the streamer's default) against one that does
+    assert not sl.engines[0].emit_cloud and sl.engines[0].cloud.numel() == 0 and eng.emit_cloud
+    sp = SequenceStreamer(trials=T, samples=S, carmask=cm, chunk=3, pack_mask=True)
+    outp = sp.run_sync(torch.from_numpy(disp).pin_memory(), torch.from_numpy(bgr).pin_memory(), seed=21)
+    assert "road_mask" not in outp and outp["road_bits"].shape == (F, 544 * 32)
+    assert np.array_equal(sp.unpack_road_mask(outp["road_bits"]), ref["road_mask"])
+    assert np.array_equal(outp["counts"].numpy(), ref["counts"]) and np.array_equal(outp["planes"].numpy(), ref["planes"])
+    assert sp.d2h_bytes == F * (544 * 32 * 4 + 8 * 8 + 4 * 4)
+    nocloud = RoadPath(trials=T, samples=S, carmask=cm, max_frames=F, emit_cloud=False)
+    rn = nocloud.process(disp, bgr, seed=21)
+    assert rn.cloud is None
+    for k in ("counts", "planes", "errors", "hist", "road_mask", "filled"):
+        assert np.array_equal(getattr(rn, k).cpu().numpy(), ref[k]), k
+    with pytest.raises(ValueError):
+        RoadPath(carmask=cm, max_frames=1, emit_cloud=False, road_path="records")
     out2 = sr.run_sync(disp, bgr, seed=21, out=out)               # pageable numpy input, buffers reused
     assert np.array_equal(out2["road_mask"].numpy(), ref["road_mask"])
 

@@ -28,7 +28,7 @@ def gpu_compute(cuda, L, R, block=21, frames_in_flight=None):
     nb = lib.svb_sgbm_scratch_bytes(frames_in_flight or F, H, W, 128)
     scratch = rz.alloc((nb,), torch.uint8)
     dL, dR = torch.from_numpy(L).to(cuda), torch.from_numpy(R).to(cuda)          # named: both must stay alive
-    N.check(lib.svb_sgbm_compute(N.ptr(dL), N.ptr(dR), F, H, W, 128, block, N.ptr(out), N.ptr(scratch), nb, 0), "svb_sgbm_compute")
+    N.check(lib.svb_sgbm_compute(N.ptr(dL), N.ptr(dR), F, H, W, 128, block, N.ptr(out), None, N.ptr(scratch), nb, 0), "svb_sgbm_compute")
     torch.cuda.synchronize()
     rz.check()
     return out.cpu().numpy()
@@ -166,11 +166,38 @@ def test_argument_errors(cuda):
     t = torch.zeros((1, 40, 200), dtype=torch.uint8, device=cuda)
     o = torch.zeros((1, 40, 200), dtype=torch.int16, device=cuda)
     s = torch.zeros((lib.svb_sgbm_scratch_bytes(1, 40, 200, 128),), dtype=torch.uint8, device=cuda)
-    assert lib.svb_sgbm_compute(None, N.ptr(t), 1, 40, 200, 128, 21, N.ptr(o), N.ptr(s), s.numel(), 0) == N.SVB_E_NULL
-    assert lib.svb_sgbm_compute(N.ptr(t), N.ptr(t), 1, 40, 200, 64, 21, N.ptr(o), N.ptr(s), s.numel(), 0) == N.SVB_E_ARG
-    assert lib.svb_sgbm_compute(N.ptr(t), N.ptr(t), 1, 40, 200, 128, 20, N.ptr(o), N.ptr(s), s.numel(), 0) == N.SVB_E_ARG
-    assert lib.svb_sgbm_compute(N.ptr(t), N.ptr(t), 1, 40, 130, 128, 21, N.ptr(o), N.ptr(s), s.numel(), 0) == N.SVB_E_ARG
-    assert lib.svb_sgbm_compute(N.ptr(t), N.ptr(t), 1, 40, 200, 128, 21, N.ptr(o), N.ptr(s), 1000, 0) == N.SVB_E_SCRATCH
+    assert lib.svb_sgbm_compute(None, N.ptr(t), 1, 40, 200, 128, 21, N.ptr(o), None, N.ptr(s), s.numel(), 0) == N.SVB_E_NULL
+    assert lib.svb_sgbm_compute(N.ptr(t), N.ptr(t), 1, 40, 200, 64, 21, N.ptr(o), None, N.ptr(s), s.numel(), 0) == N.SVB_E_ARG
+    assert lib.svb_sgbm_compute(N.ptr(t), N.ptr(t), 1, 40, 200, 128, 20, N.ptr(o), None, N.ptr(s), s.numel(), 0) == N.SVB_E_ARG
+    assert lib.svb_sgbm_compute(N.ptr(t), N.ptr(t), 1, 40, 130, 128, 21, N.ptr(o), None, N.ptr(s), s.numel(), 0) == N.SVB_E_ARG
+    assert lib.svb_sgbm_compute(N.ptr(t), N.ptr(t), 1, 40, 200, 128, 21, N.ptr(o), None, N.ptr(s), 1000, 0) == N.SVB_E_SCRATCH
     assert lib.svb_filter_speckles(N.ptr(o), 1, 40, 200, 0, 10, 1, N.ptr(s), 100, 0) == N.SVB_E_SCRATCH
     with pytest.raises(ValueError):
         sf.disparity(np.zeros((40, 200), np.uint8), np.zeros((41, 200), np.uint8), 128, False)
+
+
+def test_block_cost_overflow_raises_the_status_bit(cuda):
+    """a block cost above 32767 - P2 (where cv2's own int16 stores wrap or saturate depending on its SIMD path) is
+    reported in status bit 0; ordinary pairs leave it clear.  At the reference's block size (21 x 21 = 441 pixels) the bound
+    is a mean pixel cost of 74, which 8-bit images hardly reach (the half-pixel interval of the Birchfield-Tomasi cost
+    absorbs edges; the raw term wants flat areas, the gradient term slopes); at the largest supported block (31 x 31) it is
+    34, and wide stripes against their inverse exceed it (so do ordinary pairs at wrong disparities)."""
+    import warnings
+    import stereo.vision_b200.functions as f
+    from stereo.vision_b200.pipeline import Matcher
+    stripes = np.tile(np.repeat(np.array([0, 255], np.uint8), 8), 19)[:300]
+    hi = np.ascontiguousarray(np.broadcast_to(stripes, (64, 300)))
+    mt = Matcher(shape=(64, 300), block=31, max_frames=1, frames_in_flight=1, device=cuda)
+    mt.disparity(hi, (255 - hi).astype(np.uint8))
+    assert int(mt.status.item()) & 1
+    mt21 = Matcher(shape=(64, 300), block=21, max_frames=1, frames_in_flight=1, device=cuda)
+    mt21.disparity(hi, (255 - hi).astype(np.uint8))
+    assert int(mt21.status.item()) == 0                                   # 441 pixels: the same input stays below the bound
+    gl, gr = synth.make_stereo_pair(3, 1, (120, 400))
+    mt2 = Matcher(shape=(120, 400), block=21, max_frames=1, frames_in_flight=1, device=cuda)      # the reference's block size
+    mt2.disparity(gl, gr)
+    assert int(mt2.status.item()) == 0
+    with warnings.catch_warnings(record=True) as w:
+        warnings.simplefilter("always")
+        f.disparity(gl, gr, 128, False)
+    assert not any(issubclass(x.category, RuntimeWarning) for x in w)
