@@ -269,6 +269,7 @@ def run_b200(args):
     launches = N.launches
     counts = res.counts.cpu().numpy().astype(np.float64)
     ref_counts = counts.copy()
+    ref_mask = res.road_mask.cpu().numpy() if not args.no_e2e else None      # `res` is a view: later legs overwrite it
     planes_valid = float(res.planes[:, 7].sum().item())
 
     # ---- the two-stream variant of the step (RoadPath(overlap=True)): measured beside `value`, not part of it
@@ -477,7 +478,7 @@ def run_b200(args):
     e2e = None
     if not args.no_e2e:
         with ClockSampler(local) as clk2:
-            e2e = run_e2e(args, torch, dev, eng.camera, cm, disp_p, bgr_p, seed, ref_counts)
+            e2e = run_e2e(args, torch, dev, eng.camera, cm, disp_p, bgr_p, seed, ref_counts, ref_mask=ref_mask)
         e2e["clocks"] = clk2.summary()
 
     # ---- max over ranks
@@ -553,7 +554,8 @@ def run_b200(args):
             out["e2e"] = {"value": F * world / (e2e_ms_max * 1e-3), "unit": "frames/s",
                           "h2d_bytes_per_step": e2e["h2d"], "d2h_bytes_per_step": e2e["d2h"],
                           "ms_per_step": e2e_ms_max, "chunk_frames": args.chunk, "matches_resident_run": e2e["match"],
-                          "api": "stereo.vision_b200.pipeline.SequenceStreamer.run (pinned host frames -> pinned host masks/planes/counts; "
+                          "api": "stereo.vision_b200.pipeline.SequenceStreamer(pack_mask=True).run (pinned host frames -> pinned host road masks as "
+                                 "bit rows + planes + counts; the unpacked masks are checked against the resident run outside the timed region; "
                                  "only the lattice rows of the disparity and of the colour image are uploaded)",
                           "gpu_launches_per_step": e2e["launches_per_step"], "clocks": e2e["clocks"],
                           "link": dict(e2e["link"], h2d_gbs_min_over_ranks=link_min[0], d2h_gbs_min_over_ranks=link_min[1]),
@@ -730,14 +732,14 @@ def measure_link(torch, dev, h2d_bytes, d2h_bytes):
             "how": "one pinned cudaMemcpyAsync per direction of the step's byte counts, best of 4, CUDA events; every rank at the same time"}
 
 
-def run_e2e(args, torch, dev, camera, cm, disp_p, bgr_p, seed, ref_counts, clk=None):
+def run_e2e(args, torch, dev, camera, cm, disp_p, bgr_p, seed, ref_counts, clk=None, ref_mask=None):
     """One sequence through the public host-to-host entry point (pipeline.SequenceStreamer.run): pinned
     HOST frames in, road masks + planes + counts in pinned host memory out; per chunk the H2D copy of
     the frames, the path and the D2H copy of the results run on three streams, double buffered."""
     from stereo.vision_b200.pipeline import SequenceStreamer
     F, C = args.frames, min(args.chunk, args.frames)
     sr = SequenceStreamer((H, W), step=args.step, trials=args.trials, samples=args.samples, carmask=cm, camera=camera,
-                          chunk=C, device=dev)
+                          chunk=C, device=dev, pack_mask=True)
     outs = [None, None]                                   # two result sets alternate: a step's results stay readable
     for i in range(2):                                    # while the next step's uploads have already begun
         outs[i] = sr.run(disp_p, bgr_p, seed=seed, out=outs[i])
@@ -752,11 +754,13 @@ def run_e2e(args, torch, dev, camera, cm, disp_p, bgr_p, seed, ref_counts, clk=N
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / steps
     match = bool(np.array_equal(out["counts"].numpy().astype(np.float64), ref_counts))
+    if ref_mask is not None:                              # outside the timed region: the bit rows unpack to the resident run's masks
+        match = match and bool(np.array_equal(sr.unpack_road_mask(out["road_bits"]), ref_mask))
     import stereo.vision_b200.shard as shard
     shard.barrier()
     link = measure_link(torch, dev, sr.h2d_bytes, sr.d2h_bytes)
     return {"ms": ms, "h2d": sr.h2d_bytes, "d2h": sr.d2h_bytes, "match": match, "link": link,
-            "launches_per_step": len(range(0, F, C)) * (sr.engines[0].road_launches + 5)}
+            "launches_per_step": len(range(0, F, C)) * (sr.engines[0].road_launches + 5 + 1)}      # + svb_pack_mask
 
 
 # ------------------------------------------------------------------ reference arm (CPU)

@@ -24,6 +24,9 @@ PATH_KERNELS = {"fill_seq": "fill_seq", "proj_write": "proj_write", "proj_scan":
                 "road_sites_scatter": "road_sites_scatter", "road_sites_fused": "road_sites"}
 
 
+MAX_ID = None          # --max-id N: only the first N + 1 captured launches (one step) enter the metrics table / traffic.json
+
+
 def short(name):
     n = name.split("(")[0]
     n = re.sub(r"^void\s+", "", n)
@@ -53,6 +56,8 @@ def metrics(rep, tag, frames):
     agg = collections.OrderedDict()
     for r in rows[2:]:
         if len(r) < len(hdr):
+            continue
+        if MAX_ID is not None and int(r[col["ID"]]) > MAX_ID:
             continue
         key = (short(r[col["Kernel Name"]]), r[col["Grid Size"]].replace(" ", ""), r[col["launch__block_size"]])
         vals = []
@@ -143,6 +148,8 @@ def sass(tag):
 if __name__ == "__main__":
     tag, rep = sys.argv[1], sys.argv[2]
     frames = int(sys.argv[sys.argv.index("--frames") + 1]) if "--frames" in sys.argv else 300
+    if "--max-id" in sys.argv:
+        MAX_ID = int(sys.argv[sys.argv.index("--max-id") + 1])
     ks = metrics(rep, tag, frames)
     stalls(rep, tag, ks)
     csvs = [a for a in sys.argv[3:] if a.endswith(".csv")]
