@@ -229,7 +229,9 @@ __device__ __forceinline__ void score_trial(const uint32_t *__restrict__ rec, in
         const uint32_t lt = (1u << lane) - 1u;
         uint32_t x = dr.x;
         int have = 0;                                                             // warp-uniform: sample points taken
-        for (;;) {                                                                // four rounds of 32 draws per turn
+        // blocks of four rounds (128 draws, their loads and arithmetic interleaved) while a whole block is sure to be
+        // used, then single rounds: for S = 400 and 98 % of the values below M that is 13 rounds instead of 16
+        while (have + 128 <= S) {
             const uint32_t x0 = x, x1 = (x0 * dr.A32 + dr.C32) & dr.mask, x2 = (x1 * dr.A32 + dr.C32) & dr.mask,
                            x3 = (x2 * dr.A32 + dr.C32) & dr.mask;
             x = (x3 * dr.A32 + dr.C32) & dr.mask;
@@ -240,22 +242,24 @@ __device__ __forceinline__ void score_trial(const uint32_t *__restrict__ rec, in
             const double t1 = sample_term<STAGED>(h, k1 ? x1 : 0u, rec, stride, s_rec_addr, s_invd_addr);
             const double t2 = sample_term<STAGED>(h, k2 ? x2 : 0u, rec, stride, s_rec_addr, s_invd_addr);
             const double t3 = sample_term<STAGED>(h, k3 ? x3 : 0u, rec, stride, s_rec_addr, s_invd_addr);
-            const int n0 = __popc(b0), n1 = __popc(b1), n2 = __popc(b2), n3 = __popc(b3);
-            if (have + n0 + n1 + n2 + n3 < S) {
-                acc0 += (k0 ? t0 : 0.0) + (k2 ? t2 : 0.0);
-                acc1 += (k1 ? t1 : 0.0) + (k3 ? t3 : 0.0);
-                have += n0 + n1 + n2 + n3;
+            acc0 += (k0 ? t0 : 0.0) + (k2 ? t2 : 0.0);
+            acc1 += (k1 ? t1 : 0.0) + (k3 ? t3 : 0.0);
+            have += __popc(b0) + __popc(b1) + __popc(b2) + __popc(b3);
+        }
+        for (;;) {
+            const uint32_t x0 = x;
+            x = (x0 * dr.A32 + dr.C32) & dr.mask;
+            const bool k0 = x0 < M;
+            const uint32_t b0 = __ballot_sync(0xffffffffu, k0);
+            const double t0 = sample_term<STAGED>(h, k0 ? x0 : 0u, rec, stride, s_rec_addr, s_invd_addr);
+            const int n0 = __popc(b0);
+            if (have + n0 < S) {
+                if (k0) acc0 += t0;
+                have += n0;
                 continue;
             }
-            // the sample ends inside these rounds: accepted draws count in sequence order (round, then lane)
-            int room = S - have;
-            if (k0 && __popc(b0 & lt) < room) acc0 += t0;
-            room -= n0;
-            if (k1 && __popc(b1 & lt) < room) acc1 += t1;
-            room -= n1;
-            if (k2 && __popc(b2 & lt) < room) acc0 += t2;
-            room -= n2;
-            if (k3 && __popc(b3 & lt) < room) acc1 += t3;
+            // the sample ends inside this round: accepted draws count in sequence order (lane order)
+            if (k0 && __popc(b0 & lt) < S - have) acc0 += t0;
             break;
         }
     }

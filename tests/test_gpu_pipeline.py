@@ -118,6 +118,35 @@ def test_two_half_batches_on_two_streams_equal_one_batch(cuda):
     assert (a.planes[:, 7] == 1).all() and a.road_mask.any()
 
 
+def test_repeated_runs_are_bit_identical(cuda):
+    """compute-sanitizer (racecheck) is closed on the GPU pool; what a data race in the compaction, the shared-memory
+    histograms, the staged scorer or the scatter would do is change a result from run to run.  Ten runs of one batch on two
+    engines (fresh and reused buffers), both road paths: every output identical, every time."""
+    import torch
+    from stereo.vision_b200.pipeline import RoadPath
+    F, T, S = 12, 600, 400
+    disp, bgr = synth.make_sequence(15, F)
+    cm = _carmask(disp.shape[1:])
+    ov0 = torch.from_numpy(bgr).to(cuda)
+    for road_path in ("sites", "records"):
+        first = None
+        for run in range(10):
+            eng = RoadPath(trials=T, samples=S, carmask=cm, max_frames=F, road_path=road_path) if run % 5 == 0 else eng
+            ov = ov0.clone()
+            r = eng.process(disp, bgr, seed=3, overlay=ov)
+            n = r.counts[:, :2].cpu().numpy()
+            got = {k: getattr(r, k).clone() for k in ("filled", "counts", "planes", "errors", "hist", "road_mask")}
+            got["overlay"] = ov
+            got["cloud"] = torch.cat([r.cloud[t, :n[t, 0]] for t in range(F)])
+            got["mcloud"] = torch.cat([r.mcloud[t, :n[t, 1]] for t in range(F)])
+            if first is None:
+                first = got
+            else:
+                for k, v in got.items():
+                    assert torch.equal(v, first[k]), (road_path, run, k)
+        assert (first["planes"][:, 7] == 1).all() and first["road_mask"].any()
+
+
 def test_no_plane_when_masked_cloud_too_small(cuda):
     """M < S: every trial raises in the reference -> RANSAC returns (None, None) -> black mask."""
     from stereo.vision_b200.pipeline import RoadPath
