@@ -118,6 +118,22 @@ def test_two_half_batches_on_two_streams_equal_one_batch(cuda):
     assert (a.planes[:, 7] == 1).all() and a.road_mask.any()
 
 
+def test_chained_calls_on_one_engine_with_its_own_filled_frame(cuda):
+    """prev = result.filled[-1] of the SAME engine is a view of the buffer the next fill overwrites (process() clones it):
+    two chained calls equal one call over all frames"""
+    from stereo.vision_b200.pipeline import RoadPath
+    F, T, S = 6, 200, 400
+    disp, bgr = synth.make_sequence(16, F)
+    cm = _carmask(disp.shape[1:])
+    whole = to_host(RoadPath(trials=T, samples=S, carmask=cm, max_frames=F).process(disp, bgr, seed=9))
+    eng = RoadPath(trials=T, samples=S, carmask=cm, max_frames=3)
+    a = eng.process(disp[:3], bgr[:3], seed=9)
+    first = to_host(a)
+    b = to_host(eng.process(disp[3:], bgr[3:], prev=a.filled[-1], seed=9, frame0=3))
+    for k in ("filled", "counts", "planes", "hist", "road_mask"):
+        assert np.array_equal(np.concatenate([first[k], b[k]]), whole[k]), k
+
+
 def test_repeated_runs_are_bit_identical(cuda):
     """compute-sanitizer (racecheck) is closed on the GPU pool; what a data race in the compaction, the shared-memory
     histograms, the staged scorer or the scatter would do is change a result from run to run.  Ten runs of one batch on two
