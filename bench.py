@@ -760,7 +760,7 @@ def run_e2e(args, torch, dev, camera, cm, disp_p, bgr_p, seed, ref_counts, clk=N
     shard.barrier()
     link = measure_link(torch, dev, sr.h2d_bytes, sr.d2h_bytes)
     return {"ms": ms, "h2d": sr.h2d_bytes, "d2h": sr.d2h_bytes, "match": match, "link": link,
-            "launches_per_step": len(range(0, F, C)) * (sr.engines[0].road_launches + 5 + 1)}      # + svb_pack_mask
+            "launches_per_step": len(range(0, F, C)) * (sr.engines[0].road_launches + 4 + 1)}      # fill, write, score, finalize + svb_pack_mask
 
 
 # ------------------------------------------------------------------ reference arm (CPU)

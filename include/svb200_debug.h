@@ -12,8 +12,6 @@ extern "C" {
 int svb_debug_force_two_pass(int on);
 /* test hook: row bands per frame of the 1024-wide cleaning kernel (default 4); 0 = use the general kernel */
 int svb_debug_clean_bands(int bands);
-/* tuning hook: pixels per thread on lattice / odd rows of the balanced fill kernel (0 = default) */
-int svb_debug_fill_split(int mode);
 #ifdef __cplusplus
 }
 #endif

@@ -110,7 +110,6 @@ SIGNATURES = {
 DEBUG_SIGNATURES = {
     "svb_debug_force_two_pass": (I, [I]),
     "svb_debug_clean_bands": (I, [I]),
-    "svb_debug_fill_split": (I, [I]),
 }
 
 _lib = None

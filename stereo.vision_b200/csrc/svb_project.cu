@@ -436,9 +436,6 @@ fill_seq_split(const uint8_t *__restrict__ raw, const uint8_t *__restrict__ prev
     }
 }
 
-static int g_fill_split = 0;                            // tuning hook (svb_debug_fill_split): 0 = default
-extern "C" int svb_debug_fill_split(int mode) { g_fill_split = mode; return SVB_OK; }
-
 static int launch_fill(const uint8_t *raw, const uint8_t *prev0, uint8_t *filled, int F, int H, int W,
                        const uint8_t *carmask, const ProjGeom *g, uint32_t *group_counts, cudaStream_t st) {
     int64_t pixels = (int64_t)H * W;
@@ -459,12 +456,9 @@ static int launch_fill(const uint8_t *raw, const uint8_t *prev0, uint8_t *filled
             fill_seq_split<FILL_UNROLL, PE, PO><<<(unsigned)((warps + FS_WARPS - 1) / FS_WARPS), FS_WARPS * 32, 0, st>>>( \
                 raw, prev0, filled, F, H, W, carmask, *g, group_counts);                                                  \
         } while (0)
-        switch (g_fill_split) {                         // 300 frames of 1024 x 544: 87.6 / 94.1 / 88.6 / 92.1 us
-            case 1: LAUNCH_SPLIT(8, 16); break;
-            case 2: LAUNCH_SPLIT(4, 8); break;
-            case 3: LAUNCH_SPLIT(4, 4); break;
-            default: LAUNCH_SPLIT(8, 8); break;
-        }
+        // pixels per thread on lattice / odd rows.  Measured on 300 frames of 1024 x 544: (8, 8) 87.6 us, (8, 16) 94.1,
+        // (4, 8) 88.6, (4, 4) 92.1
+        LAUNCH_SPLIT(8, 8);
 #undef LAUNCH_SPLIT
         return SVB_OK;
     }
@@ -613,15 +607,25 @@ __device__ __forceinline__ void emit_site(const ChunkBits &c, const uint32_t *px
 template <int STEP, bool HAS_MASK, bool HAS_RGB>
 __global__ void __launch_bounds__(PROJ_THREADS)
 proj_write_kernel(const uint8_t *__restrict__ disp, const uint8_t *__restrict__ carmask,
-                  const uint8_t *__restrict__ bgr, ProjGeom g, const uint32_t *__restrict__ group_offsets,
-                  int64_t plane_stride, uint64_t *__restrict__ cloud, uint32_t *__restrict__ mcloud) {
+                  const uint8_t *__restrict__ bgr, ProjGeom g, const uint32_t *__restrict__ group_counts,
+                  int32_t *__restrict__ counts, uint64_t *__restrict__ cloud, uint32_t *__restrict__ mcloud) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ uint32_t warp_tot[PROJ_THREADS / 32];
+    __shared__ uint32_t s_base[2];                               // records of this frame in the row groups before mine
     const int cap = g.cap;                                       // sites a block can hold (multiple of 32)
     uint64_t *s_cloud = (uint64_t *)smem_raw;                    // [cap]
     uint32_t *s_m = (uint32_t *)(smem_raw + (size_t)cap * 8);    // [cap]
 
     int f = blockIdx.y, grp = blockIdx.x;
+    // my offset in the frame's slabs = the (cloud | mcloud << 16) counts of the row groups before mine, summed here
+    // (at most a few hundred words per frame) instead of by a scan kernel of its own between the count and this one
+    if (threadIdx.x < 2) s_base[threadIdx.x] = 0;
+    uint32_t pv = 0, pm = 0;
+    for (int i = threadIdx.x; i < grp; i += PROJ_THREADS) {
+        const uint32_t p = __ldg(group_counts + (int64_t)f * g.groups + i);
+        pv += p & 0xFFFFu;
+        pm += p >> 16;
+    }
     int r = threadIdx.x / g.cpr, ch = threadIdx.x % g.cpr;
     int ly = grp * g.rpb + r;
     ChunkBits c;
@@ -660,6 +664,9 @@ proj_write_kernel(const uint8_t *__restrict__ disp, const uint8_t *__restrict__ 
     uint32_t off = block_excl_scan(cnt, warp_tot, &total);
     int ov = (int)(off & 0xFFFFu), om = (int)(off >> 16);
     int tv = (int)(total & 0xFFFFu), tm = (int)(total >> 16);
+    pv = __reduce_add_sync(0xffffffffu, pv);                     // (the barrier inside the scan orders s_base's zeroing before this)
+    pm = __reduce_add_sync(0xffffffffu, pm);
+    if ((threadIdx.x & 31) == 0 && (pv | pm)) { atomicAdd(&s_base[0], pv); atomicAdd(&s_base[1], pm); }
 
     if (c.vm) {
         const uint32_t base_lo = pack_xyd(x0, y, 0);
@@ -674,15 +681,18 @@ proj_write_kernel(const uint8_t *__restrict__ disp, const uint8_t *__restrict__ 
     }
     __syncthreads();
 
-    const uint32_t *offs_v = group_offsets + (int64_t)f * g.groups;
-    const uint32_t *offs_m = group_offsets + plane_stride + (int64_t)f * g.groups;
+    const uint32_t base_v = s_base[0], base_m = s_base[1];
+    if (grp == (int)gridDim.x - 1 && threadIdx.x == 0) {        // the last row group knows the frame's totals: N, M
+        counts[f * 4 + 0] = (int32_t)(base_v + (uint32_t)tv);
+        counts[f * 4 + 1] = (int32_t)(base_m + (uint32_t)tm);
+    }
     int64_t slab = (int64_t)f * g.LH * g.LW;
     if (cloud) {
-        uint64_t *dst = cloud + slab + offs_v[grp];
+        uint64_t *dst = cloud + slab + base_v;
         for (int i = threadIdx.x; i < tv; i += PROJ_THREADS) __stcs((unsigned long long *)dst + i, (unsigned long long)s_cloud[swz8(i)]);
     }
     if (mcloud) {
-        uint32_t *dst = mcloud + slab + offs_m[grp];
+        uint32_t *dst = mcloud + slab + base_m;
         for (int i = threadIdx.x; i < tm; i += PROJ_THREADS) dst[i] = s_m[swz4(i)];
     }
 }
@@ -751,19 +761,18 @@ static int project_compact_impl(const uint8_t *disp, const uint8_t *carmask, con
         else         proj_count_kernel<false><<<grid, PROJ_THREADS, 0, st>>>(disp, carmask, g, gc);
         SVB_LAUNCH_CHECK();
     }
-    {
+    if (!cloud && !mcloud) {                                     // counts only: N, M by the stand-alone scan
         ProfScope ps(K_PROJ_SCAN, st);
         proj_scan_kernel<<<F, 256, 0, st>>>(gc, g.groups, counts);
+        SVB_LAUNCH_CHECK();
+        return SVB_OK;
     }
-    SVB_LAUNCH_CHECK();
-    if (!cloud && !mcloud) return SVB_OK;
     size_t smem = (size_t)g.cap * 12;
-    int64_t plane = (int64_t)F * g.groups;
 #define LAUNCH_W(S, M, R)                                                                           \
     do {                                                                                            \
         if (smem + 256 > 48 * 1024)                                                                 \
             cudaFuncSetAttribute(proj_write_kernel<S, M, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
-        proj_write_kernel<S, M, R><<<grid, PROJ_THREADS, smem, st>>>(disp, carmask, bgr, g, gc, plane, cloud, mcloud); \
+        proj_write_kernel<S, M, R><<<grid, PROJ_THREADS, smem, st>>>(disp, carmask, bgr, g, gc, counts, cloud, mcloud); \
     } while (0)
 #define LAUNCH_WS(S)                                                                                \
     do {                                                                                            \

@@ -152,7 +152,7 @@ def projectDisparityTo3d(disparity, max_disparity, rgb=[]):
     cc = N.ccam(cam)
     N.check(lib.svb_project_compact(N.ptr(d), None, N.ptr(c), 1, H, W, step, C.byref(cc), N.ptr(cloud), None,
                                     N.ptr(counts), N.ptr(scratch), scratch.numel(), N.stream_ptr()), "svb_project_compact")
-    N.count(3)
+    N.count(2)
     n = int(counts[0, 0].item())
     return PointCloud(cloud, n, cam, has_rgb)
 

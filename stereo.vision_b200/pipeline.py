@@ -6,7 +6,7 @@ synchronisation:
 
     svb_fill_sequence_counted    a1    temporal fill (the only cross-frame dependency, walked in-kernel)
                                        + the site counts of a4 (the bytes are in registers anyway)
-    svb_project_compact_counted  a2-a4 scan / write: cloud (8 B records) + masked cloud (4 B)
+    svb_project_compact_counted  a2-a4 write: cloud (8 B records) + masked cloud (4 B); offsets summed per block
     svb_ransac_score     a5-a7   T hypotheses x S samples per frame, one warp per hypothesis
     svb_ransac_finalize          first-minimum arg-min, winning plane, exact threshold cutoff
     svb_road_points      a8-a14  near-plane test + hue histogram, colour filter + reprojection + mask
@@ -21,7 +21,7 @@ import torch
 from . import _native as N
 from .camera import DEFAULT_CAMERA, Camera
 
-KERNELS_PER_BATCH = 6      # fill+count, scan, write, score, finalize, road cluster kernel
+KERNELS_PER_BATCH = 5      # fill+count, write, score, finalize, road cluster kernel
 
 
 def _on_device(fn):

@@ -28,11 +28,6 @@ def timeit(fn, n=10):
     return a.elapsed_time(b) / n * 1e3
 
 t_plain = timeit(lambda: N.check(lib.svb_fill_sequence(N.ptr(raw), None, N.ptr(out), F, H, W, st), "fill"))
-for mode in (0, 1, 2, 3):
-    lib.svb_debug_fill_split(mode)
-    tm = timeit(lambda: N.check(lib.svb_fill_sequence_counted(N.ptr(raw), None, N.ptr(out), N.ptr(cm), F, H, W, 2, N.ptr(scratch), nb, st), "fillc"))
-    print("fill+count split mode %d: %.1f us" % (mode, tm))
-lib.svb_debug_fill_split(0)
 t_cnt = timeit(lambda: N.check(lib.svb_fill_sequence_counted(N.ptr(raw), None, N.ptr(out), N.ptr(cm), F, H, W, 2, N.ptr(scratch), nb, st), "fillc"))
 t_copy = timeit(lambda: out.copy_(raw))
 print("fill plain %.1f us, fill+count %.1f us, torch copy %.1f us (%.0f GB/s)" % (t_plain, t_cnt, t_copy, 2 * raw.numel() / t_copy / 1e3))
