@@ -740,6 +740,8 @@ def run_e2e(args, torch, dev, camera, cm, disp_p, bgr_p, seed, ref_counts, clk=N
     F, C = args.frames, min(args.chunk, args.frames)
     sr = SequenceStreamer((H, W), step=args.step, trials=args.trials, samples=args.samples, carmask=cm, camera=camera,
                           chunk=C, device=dev, pack_mask=True)
+    import stereo.vision_b200.shard as shard
+    shard.barrier()                                       # every rank streams at the same time (rank 0 ran extra legs before)
     outs = [None, None]                                   # two result sets alternate: a step's results stay readable
     for i in range(2):                                    # while the next step's uploads have already begun
         outs[i] = sr.run(disp_p, bgr_p, seed=seed, out=outs[i])
@@ -756,7 +758,6 @@ def run_e2e(args, torch, dev, camera, cm, disp_p, bgr_p, seed, ref_counts, clk=N
     match = bool(np.array_equal(out["counts"].numpy().astype(np.float64), ref_counts))
     if ref_mask is not None:                              # outside the timed region: the bit rows unpack to the resident run's masks
         match = match and bool(np.array_equal(sr.unpack_road_mask(out["road_bits"]), ref_mask))
-    import stereo.vision_b200.shard as shard
     shard.barrier()
     link = measure_link(torch, dev, sr.h2d_bytes, sr.d2h_bytes)
     return {"ms": ms, "h2d": sr.h2d_bytes, "d2h": sr.d2h_bytes, "match": match, "link": link,
