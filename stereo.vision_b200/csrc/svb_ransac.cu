@@ -40,12 +40,25 @@ __host__ __device__ __forceinline__ uint32_t trial_key(uint64_t seed, int frame,
 // different shared-memory banks.  An earlier version drew a systematic sample (start + j * stride, stride from a
 // table of 256 primes): the winner's mean error over 240 frames was then distributed differently from the
 // reference's draws (two-sample KS p = 8e-17, median 0.231 against 0.271: an arithmetic progression clusters on
-// image columns, and the minimum over 600 trials finds the lucky clusters).  The congruential sample is
-// statistically indistinguishable from random.sample on those observables (tests/test_gpu_replay.py).
-struct Draws { uint32_t x, A32, C32, mask; };
+// image columns, and the minimum over 600 trials finds the lucky clusters).
+// The state x_n is NOT the index: the low j bits of a power-of-two congruential sequence have period 2^j, so every
+// run of 2^j states is exactly balanced modulo 2^j -- used directly, each sample was stratified over image columns,
+// its mean error had less variance than a simple random sample's, and the winner was measurably BETTER than with
+// the reference's draws (K and the angle to the true plane over 3 x 240 frames: every median on one side, KS p down
+// to 0.007).  The index is the state passed through the k-bit bijection scramble() (PCG's output step: fold the
+// high, long-period bits into the low ones), which keeps the S indices distinct.  tests/test_gpu_replay.py holds
+// the result to random.sample's on those observables.
+#define SCRAMBLE_MUL 0x9E3779B1u
+struct Draws { uint32_t x, A32, C32, mask, sh; };
+__device__ __forceinline__ uint32_t scramble(uint32_t x, uint32_t sh, uint32_t mask) {
+    x ^= x >> sh;
+    x = (x * SCRAMBLE_MUL) & mask;
+    return x ^ (x >> sh);
+}
 __device__ __forceinline__ Draws make_draws(uint32_t key, uint32_t M, int lane) {
     Draws d;
-    d.mask = M > 1u ? (0xFFFFFFFFu >> __clz(M - 1u)) : 0u;         // 2^k - 1, 2^k >= M
+    d.mask = M > 2u ? (0xFFFFFFFFu >> __clz(M - 1u)) : 1u;         // 2^k - 1, 2^k >= M, k >= 1
+    d.sh = (33u - (uint32_t)__clz(d.mask)) >> 1;                    // ceil(k / 2)
     uint32_t A = (mix32(key ^ 0x51ED270Bu) & ~7u) | 5u;
     uint32_t C = mix32(key + 0x9E3779B9u) | 1u;
     uint32_t x = mix32(key ^ 0xC2B2AE35u);
@@ -128,36 +141,20 @@ __device__ __forceinline__ bool trial_triple(const uint32_t *__restrict__ rec, i
 // int -> double without the (quarter-rate) conversion instruction: 2^52 + x has x in its low mantissa bits
 __device__ __forceinline__ double u2d(uint32_t x) { return __hiloint2double(0x43300000, (int)x) - 4503599627370496.0; }
 
-// Warp-cooperative draw of the triple of one trial: lanes 0..2 fetch one record each.  Returns false when the
-// trial has no plane (bad explicit index, image-collinear triple, retry budget exhausted).  Same decisions as
-// trial_triple(): an exactly collinear triple (np.cross == 0, functions.py:256-259) is necessarily
-// image-collinear, so the float64 expansion is only needed -- to tell "draw again" from "skip" -- when det == 0.
-template <bool EXPLICIT>
-__device__ __forceinline__ bool warp_triple(const uint32_t *__restrict__ rec, int stride, uint32_t M, const CamD &cam,
-                                            const int32_t *__restrict__ triple, uint32_t key, int lane,
+// Warp-cooperative fetch of the explicit triple of one trial: lanes 0..2 fetch one record each.  Returns false when
+// the trial has no plane (bad index, image-collinear triple): the decisions of trial_triple() for explicit indices.
+__device__ __forceinline__ bool warp_triple(const uint32_t *__restrict__ rec, int stride, uint32_t M,
+                                            const int32_t *__restrict__ triple, int lane,
                                             uint32_t &r1, uint32_t &r2, uint32_t &r3) {
-    const int rounds = EXPLICIT ? 1 : MAX_TRIPLE_ROUNDS;
-    for (int round = 0; round < rounds; ++round) {
-        uint32_t idx;
-        if (EXPLICIT) {
-            int i = lane < 3 ? __ldg(triple + lane) : 0;
-            bool valid = i >= 0 && (uint32_t)i < M;
-            if (__any_sync(0xffffffffu, !valid)) return false;
-            idx = (uint32_t)i;
-        } else {
-            idx = uniform_draw(key, 3u * round + (lane < 3 ? lane : 0), M);
-        }
-        uint32_t r = __ldg(rec + (int64_t)idx * stride);
-        r1 = __shfl_sync(0xffffffffu, r, 0); r2 = __shfl_sync(0xffffffffu, r, 1); r3 = __shfl_sync(0xffffffffu, r, 2);
-        if (img_det(r1, r2, r3) != 0) return true;
-        if (EXPLICIT) return false;
-        P3 p1 = expand_point(cam, r1), p2 = expand_point(cam, r2), p3 = expand_point(cam, r3);   // rare (3.5e-4 of draws)
-        if (!exactly_collinear(p1, p2, p3)) return false;
-    }
-    return false;
+    const int i = lane < 3 ? __ldg(triple + lane) : 0;
+    const bool valid = i >= 0 && (uint32_t)i < M;
+    if (__any_sync(0xffffffffu, !valid)) return false;
+    const uint32_t r = __ldg(rec + (int64_t)i * stride);
+    r1 = __shfl_sync(0xffffffffu, r, 0); r2 = __shfl_sync(0xffffffffu, r, 1); r3 = __shfl_sync(0xffffffffu, r, 2);
+    return img_det(r1, r2, r3) != 0;
 }
 
-// One warp scores one trial.  STAGED: the S sample gathers read the frame's records from shared memory
+// One warp scores one trial with explicit indices (parity mode).  STAGED: the S sample gathers read the frame's records from shared memory
 // (s_rec, stride 1); otherwise from global memory (L2).  Writes the mean error (or +inf) to *err_out.
 // Per sample: one draw (add, subtract, min), one gather, and  |(Na x + Nb y + Ng)/d - det|  as two 32x32+64 integer multiply-adds whose
 // 64-bit result IS the bit pattern of the double 2^52 + 2^40 + (Na x + Nb y + Ng) (the bias and the
@@ -194,13 +191,13 @@ __device__ __forceinline__ double sample_term(const TrialPlane &h, uint32_t idx,
     return fabs(fma(lin, lds_f64(s_invd_addr + ((r >> 19) & 0x7F8u)), -h.det));
 }
 
-template <bool EXPLICIT, bool STAGED>
+template <bool STAGED>
 __device__ __forceinline__ void score_trial(const uint32_t *__restrict__ rec, int stride, uint32_t s_rec_addr,
                                             uint32_t M, int S, const CamD &cam, double fB_over_S, uint32_t s_invd_addr,
                                             const int32_t *__restrict__ samp, const int32_t *__restrict__ trip,
-                                            uint32_t key, int lane, double *err_out) {
+                                            int lane, double *err_out) {
     uint32_t r1, r2, r3;
-    if (!warp_triple<EXPLICIT>(rec, stride, M, cam, trip, key, lane, r1, r2, r3)) {
+    if (!warp_triple(rec, stride, M, trip, lane, r1, r2, r3)) {
         if (lane == 0) *err_out = INFINITY;
         return;
     }
@@ -216,54 +213,14 @@ __device__ __forceinline__ void score_trial(const uint32_t *__restrict__ rec, in
     // |Na x + Nb y + Ng| < 2^35, so 2^40 + it is a positive integer below 2^52: put it in the mantissa of 2^52
     h.base = ng_i + (1ll << 40) + (0x43300000ll << 32);
     h.det = (double)det_i;
-    double acc0 = 0.0, acc1 = 0.0;
+    double acc0 = 0.0;
     bool bad = false;
-    if (EXPLICIT) {
-        for (int j = lane; j < S; j += 32) {
-            int i = __ldg(samp + j);
-            bad |= (i < 0 || (uint32_t)i >= M);
-            acc0 += sample_term<STAGED>(h, bad ? 0u : (uint32_t)i, rec, stride, s_rec_addr, s_invd_addr);
-        }
-    } else {
-        const Draws dr = make_draws(key, M, lane);
-        const uint32_t lt = (1u << lane) - 1u;
-        uint32_t x = dr.x;
-        int have = 0;                                                             // warp-uniform: sample points taken
-        // blocks of four rounds (128 draws, their loads and arithmetic interleaved) while a whole block is sure to be
-        // used, then single rounds: for S = 400 and 98 % of the values below M that is 13 rounds instead of 16
-        while (have + 128 <= S) {
-            const uint32_t x0 = x, x1 = (x0 * dr.A32 + dr.C32) & dr.mask, x2 = (x1 * dr.A32 + dr.C32) & dr.mask,
-                           x3 = (x2 * dr.A32 + dr.C32) & dr.mask;
-            x = (x3 * dr.A32 + dr.C32) & dr.mask;
-            const bool k0 = x0 < M, k1 = x1 < M, k2 = x2 < M, k3 = x3 < M;        // values >= M are skipped
-            const uint32_t b0 = __ballot_sync(0xffffffffu, k0), b1 = __ballot_sync(0xffffffffu, k1),
-                           b2 = __ballot_sync(0xffffffffu, k2), b3 = __ballot_sync(0xffffffffu, k3);
-            const double t0 = sample_term<STAGED>(h, k0 ? x0 : 0u, rec, stride, s_rec_addr, s_invd_addr);
-            const double t1 = sample_term<STAGED>(h, k1 ? x1 : 0u, rec, stride, s_rec_addr, s_invd_addr);
-            const double t2 = sample_term<STAGED>(h, k2 ? x2 : 0u, rec, stride, s_rec_addr, s_invd_addr);
-            const double t3 = sample_term<STAGED>(h, k3 ? x3 : 0u, rec, stride, s_rec_addr, s_invd_addr);
-            acc0 += (k0 ? t0 : 0.0) + (k2 ? t2 : 0.0);
-            acc1 += (k1 ? t1 : 0.0) + (k3 ? t3 : 0.0);
-            have += __popc(b0) + __popc(b1) + __popc(b2) + __popc(b3);
-        }
-        for (;;) {
-            const uint32_t x0 = x;
-            x = (x0 * dr.A32 + dr.C32) & dr.mask;
-            const bool k0 = x0 < M;
-            const uint32_t b0 = __ballot_sync(0xffffffffu, k0);
-            const double t0 = sample_term<STAGED>(h, k0 ? x0 : 0u, rec, stride, s_rec_addr, s_invd_addr);
-            const int n0 = __popc(b0);
-            if (have + n0 < S) {
-                if (k0) acc0 += t0;
-                have += n0;
-                continue;
-            }
-            // the sample ends inside this round: accepted draws count in sequence order (lane order)
-            if (k0 && __popc(b0 & lt) < S - have) acc0 += t0;
-            break;
-        }
+    for (int j = lane; j < S; j += 32) {
+        int i = __ldg(samp + j);
+        bad |= (i < 0 || (uint32_t)i >= M);
+        acc0 += sample_term<STAGED>(h, bad ? 0u : (uint32_t)i, rec, stride, s_rec_addr, s_invd_addr);
     }
-    double acc = warp_sum(acc0 + acc1);
+    double acc = warp_sum(acc0);
     bad = __any_sync(0xffffffffu, bad);
     if (lane == 0) {
         const double Na = (double)h.na, Nb = (double)h.nb, Ng = (double)ng_i;
@@ -271,6 +228,86 @@ __device__ __forceinline__ void score_trial(const uint32_t *__restrict__ rec, in
         const double e = acc * fB_over_S * rsqrt(A * A + B * B + C * C);
         *err_out = (bad || !(e < INFINITY)) ? INFINITY : e;       // NaN never beats bestError, :291
     }
+}
+
+// ------------------------------------------------------------------ score: one THREAD per hypothesis (device draws)
+// With a warp per hypothesis the per-hypothesis work -- trial key, triple, the integer determinants, the draw parameters,
+// the reduction and the final scaling, ~240 instructions -- is executed by all 32 lanes, and the lanes need a vote and a
+// population count per round to agree on which draws count.  With device draws nothing has to be read coalesced, so a thread
+// can own a hypothesis: it walks the trial's congruential sequence x_0, x_1, ... itself and keeps the first S values below
+// M.  That is the sequence, in the order, that the warp version consumes (lane l walks x_l, x_(l+32), ... and accepted draws
+// count round by round, lane by lane), so the SAMPLE SETS ARE THE SAME and svb_ransac_dump_indices describes both; only
+// the order of the floating-point sum differs.  Explicit indices (parity mode) keep the warp version: their loads want
+// to be coalesced.
+template <bool STAGED>
+__device__ __forceinline__ uint32_t fetch_rec(uint32_t idx, const uint32_t *__restrict__ rec, int stride, uint32_t s_rec_addr) {
+    return STAGED ? lds_u32(s_rec_addr + idx * 4u) : __ldg(rec + (int64_t)idx * stride);
+}
+template <bool STAGED>
+__device__ __forceinline__ double score_trial_thread(const uint32_t *__restrict__ rec, int stride, uint32_t s_rec_addr,
+                                                     uint32_t M, int S, const CamD &cam, double fB_over_S, uint32_t s_invd_addr,
+                                                     uint32_t key) {
+    // the triple: the decisions of warp_triple<false>
+    uint32_t r1 = 0, r2 = 0, r3 = 0;
+    bool ok = false;
+    for (int round = 0; round < MAX_TRIPLE_ROUNDS; ++round) {
+        r1 = fetch_rec<STAGED>(uniform_draw(key, 3u * round + 0u, M), rec, stride, s_rec_addr);
+        r2 = fetch_rec<STAGED>(uniform_draw(key, 3u * round + 1u, M), rec, stride, s_rec_addr);
+        r3 = fetch_rec<STAGED>(uniform_draw(key, 3u * round + 2u, M), rec, stride, s_rec_addr);
+        if (img_det(r1, r2, r3) != 0) { ok = true; break; }
+        if (!exactly_collinear(expand_point(cam, r1), expand_point(cam, r2), expand_point(cam, r3))) break;   // rare (3.5e-4 of draws)
+    }
+    if (!ok) return INFINITY;
+    const int x1 = rec_x(r1), y1 = rec_y(r1), d1 = rec_d(r1);
+    const int x2 = rec_x(r2), y2 = rec_y(r2), d2 = rec_d(r2);
+    const int x3 = rec_x(r3), y3 = rec_y(r3), d3 = rec_d(r3);
+    const int det_i = x1 * (y2 - y3) + x2 * (y3 - y1) + x3 * (y1 - y2);
+    const long long ng_i = (long long)(d1 * (x2 * y3 - x3 * y2)) + (long long)(d2 * (x3 * y1 - x1 * y3)) +
+                           (long long)(d3 * (x1 * y2 - x2 * y1));
+    TrialPlane h;
+    h.na = d1 * (y2 - y3) + d2 * (y3 - y1) + d3 * (y1 - y2);
+    h.nb = d1 * (x3 - x2) + d2 * (x1 - x3) + d3 * (x2 - x1);
+    h.base = ng_i + (1ll << 40) + (0x43300000ll << 32);
+    h.det = (double)det_i;
+    // the draws: make_draws' sequence through scramble(), walked by one thread.  The k-bit state lives in the TOP k bits
+    // of a word (X = x << (32 - k)), so the products wrap modulo 2^k by themselves: per draw one multiply-add for the
+    // state and shift, xor-and, multiply, shift, xor, shift for the index -- the same indices, two masks fewer.
+    const uint32_t k = M > 2u ? 32u - (uint32_t)__clz(M - 1u) : 1u, up = 32u - k, sh = (k + 1u) >> 1;
+    const uint32_t top = 0xFFFFFFFFu << up;
+    const uint32_t A = (mix32(key ^ 0x51ED270Bu) & ~7u) | 5u, C = (mix32(key + 0x9E3779B9u) | 1u) << up;
+    uint32_t X = mix32(key ^ 0xC2B2AE35u) << up;
+    double acc0 = 0.0, acc1 = 0.0;
+    int have = 0;
+    while (have + 8 <= S) {                                       // eight draws in flight; at most eight more are taken
+        uint32_t is[8];
+        bool ks[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const uint32_t Z = ((X ^ (X >> sh)) & top) * SCRAMBLE_MUL;
+            is[u] = (Z ^ (Z >> sh)) >> up;
+            ks[u] = is[u] < M;                                    // values >= M are skipped
+            X = X * A + C;
+        }
+        double ts[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) ts[u] = sample_term<STAGED>(h, ks[u] ? is[u] : 0u, rec, stride, s_rec_addr, s_invd_addr);
+#pragma unroll
+        for (int u = 0; u < 8; u += 2) {
+            acc0 += ks[u] ? ts[u] : 0.0;
+            acc1 += ks[u + 1] ? ts[u + 1] : 0.0;
+            have += (int)ks[u] + (int)ks[u + 1];
+        }
+    }
+    while (have < S) {
+        const uint32_t Z = ((X ^ (X >> sh)) & top) * SCRAMBLE_MUL;
+        const uint32_t i0 = (Z ^ (Z >> sh)) >> up;
+        X = X * A + C;
+        if (i0 < M) { acc0 += sample_term<STAGED>(h, i0, rec, stride, s_rec_addr, s_invd_addr); ++have; }
+    }
+    const double Na = (double)h.na, Nb = (double)h.nb, Ng = (double)ng_i;
+    const double Ap = cam.f * Na, Bp = cam.f * Nb, Cp = Ng + cam.cw * Na + cam.ch * Nb;
+    const double e = (acc0 + acc1) * fB_over_S * rsqrt(Ap * Ap + Bp * Bp + Cp * Cp);
+    return e < INFINITY ? e : INFINITY;                           // NaN never beats bestError, :291
 }
 
 // ---- bulk (TMA) staging helpers: one elected thread copies global -> shared and an mbarrier counts the bytes
@@ -304,8 +341,9 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
 // are strided) gather from global memory instead.
 #define RANSAC_SMEM_THREADS 1024
 #define RANSAC_BULK_BYTES 32768u
-template <bool EXPLICIT>
-__global__ void __launch_bounds__(RANSAC_SMEM_THREADS, 1)
+#define RANSAC_PT_THREADS 640                                     // thread-per-hypothesis blocks: one pass for the reference's 600 trials
+template <bool PER_THREAD>                                        // false: explicit indices, a warp per hypothesis
+__global__ void __launch_bounds__(PER_THREAD ? RANSAC_PT_THREADS : RANSAC_SMEM_THREADS, 1)
 ransac_score_persistent(const uint32_t *__restrict__ mcloud, int stride, int64_t slab_records,
                         const int32_t *__restrict__ counts, int cstride, int ccol,
                         int F, int T, int S, int cap, CamD cam,
@@ -344,17 +382,27 @@ ransac_score_persistent(const uint32_t *__restrict__ mcloud, int stride, int64_t
             if (bulk && nb > 0) { mbar_wait(&s_bar, phase); phase ^= 1u; }
             __syncthreads();
         }
+        if (PER_THREAD) {                                             // a thread per hypothesis (device draws)
+            for (int t = tb + tid; t < te; t += (int)blockDim.x) {
+                double e = INFINITY;
+                if (!none) {
+                    const uint32_t key = trial_key(seed, frame0 + f, t);
+                    e = staged ? score_trial_thread<true>(rec, stride, s_rec_addr, (uint32_t)Mi, S, cam, fB_over_S, s_invd_addr, key)
+                               : score_trial_thread<false>(rec, stride, s_rec_addr, (uint32_t)Mi, S, cam, fB_over_S, s_invd_addr, key);
+                }
+                errors[(int64_t)f * T + t] = e;
+            }
+        } else
         for (int t = tb + warp; t < te; t += nwarps) {
             double *err_out = errors + (int64_t)f * T + t;
             if (none) {
                 if (lane == 0) *err_out = INFINITY;
                 continue;
             }
-            const int32_t *samp = EXPLICIT ? sample_idx + ((int64_t)f * T + t) * S : nullptr;
-            const int32_t *trip = EXPLICIT ? triple_idx + ((int64_t)f * T + t) * 3 : nullptr;
-            const uint32_t key = trial_key(seed, frame0 + f, t);
-            if (staged) score_trial<EXPLICIT, true>(rec, stride, s_rec_addr, (uint32_t)Mi, S, cam, fB_over_S, s_invd_addr, samp, trip, key, lane, err_out);
-            else        score_trial<EXPLICIT, false>(rec, stride, s_rec_addr, (uint32_t)Mi, S, cam, fB_over_S, s_invd_addr, samp, trip, key, lane, err_out);
+            const int32_t *samp = sample_idx + ((int64_t)f * T + t) * S;
+            const int32_t *trip = triple_idx + ((int64_t)f * T + t) * 3;
+            if (staged) score_trial<true>(rec, stride, s_rec_addr, (uint32_t)Mi, S, cam, fB_over_S, s_invd_addr, samp, trip, lane, err_out);
+            else        score_trial<false>(rec, stride, s_rec_addr, (uint32_t)Mi, S, cam, fB_over_S, s_invd_addr, samp, trip, lane, err_out);
         }
         w = (int64_t)f * T + te;
         if (w < w1) {
@@ -396,17 +444,17 @@ extern "C" int svb_ransac_score(const uint32_t *mcloud, int rec_stride_words, in
     // the opt-in to 200 KB of dynamic shared memory is a per-device function attribute: set once per device, not per call
     static bool attr_done[64] = {false};
     if (dev < 0 || dev >= 64 || !attr_done[dev]) {
-        cudaError_t e = cudaFuncSetAttribute(ransac_score_persistent<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(ransac_score_persistent<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        cudaError_t e = cudaFuncSetAttribute(ransac_score_persistent<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(ransac_score_persistent<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
         if (e != cudaSuccess) return (int)e;
         if (dev >= 0 && dev < 64) attr_done[dev] = true;
     }
-    if (sample_idx)
-        ransac_score_persistent<true><<<blocks, threads, smem, st>>>(
+    if (sample_idx)                                               // explicit draws: a warp per hypothesis (coalesced index loads)
+        ransac_score_persistent<false><<<blocks, threads, smem, st>>>(
             mcloud, rec_stride_words, slab_stride_records, counts, counts_stride, counts_col, F, T, S, cap, c,
             sample_idx, triple_idx, rng_seed, frame0, errors);
-    else
-        ransac_score_persistent<false><<<blocks, threads, smem, st>>>(
+    else                                                          // device draws: a thread per hypothesis
+        ransac_score_persistent<true><<<blocks, (flags & SVB_RANSAC_SHARE_SM) ? RANSAC_PT_THREADS / 2 : RANSAC_PT_THREADS, smem, st>>>(
             mcloud, rec_stride_words, slab_stride_records, counts, counts_stride, counts_col, F, T, S, cap, c,
             nullptr, nullptr, rng_seed, frame0, errors);
     SVB_LAUNCH_CHECK();
@@ -436,10 +484,11 @@ __global__ void ransac_dump_kernel(const uint32_t *__restrict__ mcloud, int stri
     const Draws dr = make_draws(key, M, lane);
     uint32_t x = dr.x;
     for (int have = 0; have < S;) {                                  // the scorer's draws, in sequence order
-        const bool k = x < M;
+        const uint32_t i = scramble(x, dr.sh, dr.mask);
+        const bool k = i < M;
         const uint32_t b = __ballot_sync(0xffffffffu, k);
         const int at = have + __popc(b & ((1u << lane) - 1u));
-        if (k && at < S) samp[at] = (int32_t)x;
+        if (k && at < S) samp[at] = (int32_t)i;
         have += __popc(b);
         x = (x * dr.A32 + dr.C32) & dr.mask;
     }

@@ -143,39 +143,53 @@ def test_dropin_ransac_device_draws_equal_host_replay(cuda):
 
 
 def test_device_draws_are_statistically_the_references(cuda):
-    """The throughput mode draws a systematic sample per trial instead of random.sample's.  Over 240 frames (8
-    sequences x 30 chained frames) the observables that depend on the draws -- the winner's mean error, K (near
-    points), R (road points), the angle between the fitted and the rendered road plane -- must be distributed as
-    with the reference's own draws (two-sample Kolmogorov-Smirnov, p > 0.01), and both modes must find the road
-    (median angle below 3 degrees; the oracle with Python's draws gives 0.1 - 2.1 degrees on these frames)."""
+    """The throughput mode draws each trial's sample from a scrambled congruential sequence instead of random.sample.
+    Over 240 frames (8 sequences x 30 chained frames) the observables that depend on the draws -- the winner's mean
+    error, K (near points), R (road points), the angle between the fitted and the rendered road plane -- must be
+    distributed as with the reference's own draws: two-sample Kolmogorov-Smirnov p > 0.05 for BOTH of two independent
+    device streams against BOTH of two independent CPython streams (the same test between the two CPython streams is
+    printed as the calibration: tools/ks_spread.py shows p = 0.3 - 0.99 there).  One pairing at p > 0.01 is not enough:
+    the unscrambled sequence passed that with these seeds and still had every median of K, R and the angle on one side
+    of the reference's (svb_ransac.cu, scramble()).  Both modes must find the road (median angle below 3 degrees; the
+    oracle with Python's draws gives 0.1 - 2.1 degrees on these frames)."""
     from scipy.stats import ks_2samp
     from stereo.vision_b200.pipeline import RoadPath
     NSEQ, F, T, S = 8, 30, 600, 400
     cm = _carmask((544, 1024))
     eng = RoadPath(trials=T, samples=S, carmask=cm, max_frames=F)
-    obs = {"ref": [], "dev": []}
+    names = ("ref0", "ref1", "dev0", "dev1")
+    obs = {n: [] for n in names}
     for seq in range(NSEQ):
         disp, bgr = synth.make_sequence(20 + seq, F)
         truth = np.stack([synth.true_plane(20 + seq, t) for t in range(F)])
         truth /= np.linalg.norm(truth, axis=1, keepdims=True)
-        for mode in ("ref", "dev"):
-            if mode == "ref":
-                r = eng.process(disp, bgr, py_seeds=[synth.ransac_seed(20 + seq, t) for t in range(F)])
+        for n in names:
+            k = int(n[3])
+            if n.startswith("ref"):
+                r = eng.process(disp, bgr, py_seeds=[synth.ransac_seed(20 + seq, t) + 7777 * k for t in range(F)])
             else:
-                r = eng.process(disp, bgr, seed=99 + seq)
+                r = eng.process(disp, bgr, seed=99 + seq + 1000 * k)
             pl = r.planes.cpu().numpy()
             cn = r.counts.cpu().numpy()
             assert (pl[:, 7] == 1.0).all()
             ang = np.degrees(np.arccos(np.clip(np.abs(((pl[:, :3] / pl[:, 3:4]) * truth).sum(axis=1)), 0, 1)))
-            obs[mode].append(np.stack([pl[:, 5], cn[:, 2].astype(np.float64), cn[:, 3].astype(np.float64), ang], axis=1))
-    ref, dev = np.concatenate(obs["ref"]), np.concatenate(obs["dev"])
-    report = {}
-    for k, name in enumerate(("best_error", "K", "R", "angle_deg")):
-        report[name] = (float(ks_2samp(ref[:, k], dev[:, k]).pvalue), float(np.median(ref[:, k])), float(np.median(dev[:, k])))
-    print("KS p-value, median with the reference's draws, median with device draws:", report)
-    for name, (p, _, _) in report.items():
-        assert p > 0.01, (name, report)
-    for m in (ref, dev):
+            obs[n].append(np.stack([pl[:, 5], cn[:, 2].astype(np.float64), cn[:, 3].astype(np.float64), ang], axis=1))
+    obs = {n: np.concatenate(v) for n, v in obs.items()}
+    cols = ("best_error", "K", "R", "angle_deg")
+
+    def ks(a, b):
+        return {c: round(float(ks_2samp(obs[a][:, i], obs[b][:, i]).pvalue), 4) for i, c in enumerate(cols)}
+    report = {"medians": {n: [round(float(np.median(obs[n][:, i])), 4) for i in range(4)] for n in names},
+              "ref0 vs ref1 (calibration)": ks("ref0", "ref1")}
+    for a in ("ref0", "ref1"):
+        for b in ("dev0", "dev1"):
+            report["%s vs %s" % (a, b)] = ks(a, b)
+    print("two-sample KS p-values:", report)
+    for a in ("ref0", "ref1"):
+        for b in ("dev0", "dev1"):
+            for c, p in report["%s vs %s" % (a, b)].items():
+                assert p > 0.05, (a, b, c, report)
+    for m in obs.values():
         assert np.median(m[:, 3]) < 3.0 and (m[:, 3] < 6.0).mean() > 0.95, report
 
 
