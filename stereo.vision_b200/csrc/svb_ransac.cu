@@ -240,20 +240,91 @@ __device__ __forceinline__ void score_trial(const uint32_t *__restrict__ rec, in
 // the order of the floating-point sum differs.  Explicit indices (parity mode) keep the warp version: their loads want
 // to be coalesced.
 template <bool STAGED>
-__device__ __forceinline__ uint32_t fetch_rec(uint32_t idx, const uint32_t *__restrict__ rec, int stride, uint32_t s_rec_addr) {
-    return STAGED ? lds_u32(s_rec_addr + idx * 4u) : __ldg(rec + (int64_t)idx * stride);
+__device__ __forceinline__ uint32_t fetch_rec(uint32_t idx, const uint32_t *__restrict__ rec, int stride, const uint32_t *s_rec) {
+    return STAGED ? s_rec[idx] : __ldg(rec + (int64_t)idx * stride);
+}
+// The sample term of the thread version.  The scorer is bound by the alu pipe (shifts, masks, compares, selects: 61 % active
+// against 19 % for the fma pipe that executes IMAD, profiles/r02w), so the work is moved to multiply-adds where it can be:
+//  * NARROW: when |Na| 2047 + |Nb| 2047 + |Ng| < 2^31 (every hypothesis of a 1024 x 544 image) the integer
+//    V = Na x + Nb y + Ng fits 32 bits and, with t = r >> 11 = y + 2^11 d and d = r >> 22,
+//        V = Ng + Na r + (Nb - 2^11 Na) t - 2^11 Nb d      (mod 2^32),
+//    three IMADs on the raw record and its two shifts -- no field is masked out.  2^31 is folded into the constant and
+//    the word is the low half of the double 2^52 + 2^31 + V.  Otherwise the 64-bit form of sample_term().  Both are exact
+//    integers, so the two forms give the same bits.
+//  * the shared-memory reads are plain indexing: the compiler folds scaling and window base into the address operand.
+struct NarrowPlane { uint32_t c0, c1, c2, c3; };
+template <bool STAGED, bool NARROW>
+__device__ __forceinline__ double thread_term(const TrialPlane &h, const NarrowPlane &n, uint32_t idx, const uint32_t *__restrict__ rec,
+                                              int stride, const uint32_t *s_rec, const double *s_invd) {
+    const uint32_t r = STAGED ? s_rec[idx] : __ldg(rec + (int64_t)idx * stride);
+    const uint32_t d = r >> 22;                                                   // bits 30-31 of a record are zero
+    double lin;
+    if (NARROW) {
+        const uint32_t v = n.c1 * r + (n.c2 * (r >> 11) + (n.c3 * d + n.c0));
+        lin = __hiloint2double(0x43300000, (int)v) - 4503601774854144.0;         // 2^52 + 2^31
+    } else {
+        const long long L = mad_wide(h.nb, (int)((r >> 11) & 0x7FFu), mad_wide(h.na, (int)(r & 0x7FFu), h.base));
+        lin = __longlong_as_double(L) - 4504699138998272.0;                      // 2^52 + 2^40
+    }
+    return fma(lin, s_invd[d], -h.det);                                           // its magnitude is the term
+}
+// acc += |t| if the draw i is below M, else one more rejected draw: one compare, a predicated fp64 add and a predicated
+// integer add (written out because the compiler turns the branch into two selects on the alu pipe)
+__device__ __forceinline__ void take_if_below(double &acc, int &rejected, double t, uint32_t i, uint32_t M) {
+    asm("{\n\t.reg .pred p;\n\t.reg .f64 a;\n\tsetp.lt.u32 p, %3, %4;\n\tabs.f64 a, %2;\n\t@p add.f64 %0, %0, a;\n\t@!p add.s32 %1, %1, 1;\n\t}"
+        : "+d"(acc), "+r"(rejected) : "d"(t), "r"(i), "r"(M));
+}
+// the first S values below M of the trial's scrambled congruential sequence, summed
+template <bool STAGED, bool NARROW>
+__device__ __forceinline__ double thread_walk(const TrialPlane &h, const NarrowPlane &n, uint32_t key, uint32_t M, int S,
+                                              const uint32_t *__restrict__ rec, int stride, const uint32_t *s_rec, const double *s_invd) {
+    // The k-bit state lives in the TOP k bits of a word (X = x << (32 - k)), so the products wrap modulo 2^k by themselves:
+    // per draw one multiply-add for the state and shift, xor-and, multiply, shift, xor, multiply-high for the index --
+    // make_draws' sequence through scramble(), two masks fewer.
+    const uint32_t k = M > 2u ? 32u - (uint32_t)__clz(M - 1u) : 1u, up = 32u - k, sh = (k + 1u) >> 1;
+    const uint32_t top = 0xFFFFFFFFu << up, down = 1u << k;       // umulhi(w, 2^k) = w >> (32 - k), on the fma pipe
+    const uint32_t A = (mix32(key ^ 0x51ED270Bu) & ~7u) | 5u, C = (mix32(key + 0x9E3779B9u) | 1u) << up;
+    uint32_t X = mix32(key ^ 0xC2B2AE35u) << up;
+    double acc0 = 0.0, acc1 = 0.0;
+    int drawn = 0, rejected = 0;
+    while (drawn - rejected + 8 <= S) {                           // eight draws in flight; at most eight more are taken
+        uint32_t is[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const uint32_t Z = ((X ^ (X >> sh)) & top) * SCRAMBLE_MUL;
+            is[u] = __umulhi(Z ^ (Z >> sh), down);
+            X = X * A + C;
+        }
+        double ts[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u)                               // values >= M are skipped: their term is computed on record M - 1 and dropped
+            ts[u] = thread_term<STAGED, NARROW>(h, n, min(is[u], M - 1u), rec, stride, s_rec, s_invd);
+#pragma unroll
+        for (int u = 0; u < 8; u += 2) {
+            take_if_below(acc0, rejected, ts[u], is[u], M);
+            take_if_below(acc1, rejected, ts[u + 1], is[u + 1], M);
+        }
+        drawn += 8;
+    }
+    for (int have = drawn - rejected; have < S;) {
+        const uint32_t Z = ((X ^ (X >> sh)) & top) * SCRAMBLE_MUL;
+        const uint32_t i0 = __umulhi(Z ^ (Z >> sh), down);
+        X = X * A + C;
+        if (i0 < M) { acc0 += fabs(thread_term<STAGED, NARROW>(h, n, i0, rec, stride, s_rec, s_invd)); ++have; }
+    }
+    return acc0 + acc1;
 }
 template <bool STAGED>
-__device__ __forceinline__ double score_trial_thread(const uint32_t *__restrict__ rec, int stride, uint32_t s_rec_addr,
-                                                     uint32_t M, int S, const CamD &cam, double fB_over_S, uint32_t s_invd_addr,
+__device__ __forceinline__ double score_trial_thread(const uint32_t *__restrict__ rec, int stride, const uint32_t *s_rec,
+                                                     uint32_t M, int S, const CamD &cam, double fB_over_S, const double *s_invd,
                                                      uint32_t key) {
     // the triple: the decisions of warp_triple<false>
     uint32_t r1 = 0, r2 = 0, r3 = 0;
     bool ok = false;
     for (int round = 0; round < MAX_TRIPLE_ROUNDS; ++round) {
-        r1 = fetch_rec<STAGED>(uniform_draw(key, 3u * round + 0u, M), rec, stride, s_rec_addr);
-        r2 = fetch_rec<STAGED>(uniform_draw(key, 3u * round + 1u, M), rec, stride, s_rec_addr);
-        r3 = fetch_rec<STAGED>(uniform_draw(key, 3u * round + 2u, M), rec, stride, s_rec_addr);
+        r1 = fetch_rec<STAGED>(uniform_draw(key, 3u * round + 0u, M), rec, stride, s_rec);
+        r2 = fetch_rec<STAGED>(uniform_draw(key, 3u * round + 1u, M), rec, stride, s_rec);
+        r3 = fetch_rec<STAGED>(uniform_draw(key, 3u * round + 2u, M), rec, stride, s_rec);
         if (img_det(r1, r2, r3) != 0) { ok = true; break; }
         if (!exactly_collinear(expand_point(cam, r1), expand_point(cam, r2), expand_point(cam, r3))) break;   // rare (3.5e-4 of draws)
     }
@@ -269,44 +340,15 @@ __device__ __forceinline__ double score_trial_thread(const uint32_t *__restrict_
     h.nb = d1 * (x3 - x2) + d2 * (x1 - x3) + d3 * (x2 - x1);
     h.base = ng_i + (1ll << 40) + (0x43300000ll << 32);
     h.det = (double)det_i;
-    // the draws: make_draws' sequence through scramble(), walked by one thread.  The k-bit state lives in the TOP k bits
-    // of a word (X = x << (32 - k)), so the products wrap modulo 2^k by themselves: per draw one multiply-add for the
-    // state and shift, xor-and, multiply, shift, xor, shift for the index -- the same indices, two masks fewer.
-    const uint32_t k = M > 2u ? 32u - (uint32_t)__clz(M - 1u) : 1u, up = 32u - k, sh = (k + 1u) >> 1;
-    const uint32_t top = 0xFFFFFFFFu << up;
-    const uint32_t A = (mix32(key ^ 0x51ED270Bu) & ~7u) | 5u, C = (mix32(key + 0x9E3779B9u) | 1u) << up;
-    uint32_t X = mix32(key ^ 0xC2B2AE35u) << up;
-    double acc0 = 0.0, acc1 = 0.0;
-    int have = 0;
-    while (have + 8 <= S) {                                       // eight draws in flight; at most eight more are taken
-        uint32_t is[8];
-        bool ks[8];
-#pragma unroll
-        for (int u = 0; u < 8; ++u) {
-            const uint32_t Z = ((X ^ (X >> sh)) & top) * SCRAMBLE_MUL;
-            is[u] = (Z ^ (Z >> sh)) >> up;
-            ks[u] = is[u] < M;                                    // values >= M are skipped
-            X = X * A + C;
-        }
-        double ts[8];
-#pragma unroll
-        for (int u = 0; u < 8; ++u) ts[u] = sample_term<STAGED>(h, ks[u] ? is[u] : 0u, rec, stride, s_rec_addr, s_invd_addr);
-#pragma unroll
-        for (int u = 0; u < 8; u += 2) {
-            acc0 += ks[u] ? ts[u] : 0.0;
-            acc1 += ks[u + 1] ? ts[u + 1] : 0.0;
-            have += (int)ks[u] + (int)ks[u + 1];
-        }
-    }
-    while (have < S) {
-        const uint32_t Z = ((X ^ (X >> sh)) & top) * SCRAMBLE_MUL;
-        const uint32_t i0 = (Z ^ (Z >> sh)) >> up;
-        X = X * A + C;
-        if (i0 < M) { acc0 += sample_term<STAGED>(h, i0, rec, stride, s_rec_addr, s_invd_addr); ++have; }
-    }
+    NarrowPlane n;
+    n.c1 = (uint32_t)h.na; n.c2 = (uint32_t)h.nb - ((uint32_t)h.na << 11); n.c3 = 0u - ((uint32_t)h.nb << 11);
+    n.c0 = (uint32_t)ng_i + 0x80000000u;
+    const bool narrow = (long long)abs(h.na) * 2047 + (long long)abs(h.nb) * 2047 + llabs(ng_i) < (1ll << 31);
+    const double acc = narrow ? thread_walk<STAGED, true>(h, n, key, M, S, rec, stride, s_rec, s_invd)
+                              : thread_walk<STAGED, false>(h, n, key, M, S, rec, stride, s_rec, s_invd);
     const double Na = (double)h.na, Nb = (double)h.nb, Ng = (double)ng_i;
     const double Ap = cam.f * Na, Bp = cam.f * Nb, Cp = Ng + cam.cw * Na + cam.ch * Nb;
-    const double e = (acc0 + acc1) * fB_over_S * rsqrt(Ap * Ap + Bp * Bp + Cp * Cp);
+    const double e = acc * fB_over_S * rsqrt(Ap * Ap + Bp * Bp + Cp * Cp);
     return e < INFINITY ? e : INFINITY;                           // NaN never beats bestError, :291
 }
 
@@ -350,12 +392,12 @@ ransac_score_persistent(const uint32_t *__restrict__ mcloud, int stride, int64_t
                         const int32_t *__restrict__ sample_idx, const int32_t *__restrict__ triple_idx,
                         uint64_t seed, int frame0, double *__restrict__ errors) {
     extern __shared__ __align__(128) uint32_t s_rec[];
-    __shared__ double s_invd[256];
+    __shared__ double s_invd[1024];                               // 1 / d; zero for d = 0 and above 255 (bits 30-31 of a record, never set by svb_project)
     __shared__ __align__(8) uint64_t s_bar;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = (int)blockDim.x >> 5;
     const int64_t total = (int64_t)F * T;
     const int64_t w0 = total * blockIdx.x / gridDim.x, w1 = total * (blockIdx.x + 1) / gridDim.x;
-    if (tid < 256) s_invd[tid] = tid ? __ddiv_rn(1.0, (double)tid) : 0.0;
+    for (int i = tid; i < 1024; i += (int)blockDim.x) s_invd[i] = (i > 0 && i < 256) ? __ddiv_rn(1.0, (double)i) : 0.0;
     if (tid == 0) mbar_init(&s_bar, 1);
     __syncthreads();
     const double fB_over_S = cam.fB / (double)S;
@@ -387,8 +429,8 @@ ransac_score_persistent(const uint32_t *__restrict__ mcloud, int stride, int64_t
                 double e = INFINITY;
                 if (!none) {
                     const uint32_t key = trial_key(seed, frame0 + f, t);
-                    e = staged ? score_trial_thread<true>(rec, stride, s_rec_addr, (uint32_t)Mi, S, cam, fB_over_S, s_invd_addr, key)
-                               : score_trial_thread<false>(rec, stride, s_rec_addr, (uint32_t)Mi, S, cam, fB_over_S, s_invd_addr, key);
+                    e = staged ? score_trial_thread<true>(rec, stride, s_rec, (uint32_t)Mi, S, cam, fB_over_S, s_invd, key)
+                               : score_trial_thread<false>(rec, stride, s_rec, (uint32_t)Mi, S, cam, fB_over_S, s_invd, key);
                 }
                 errors[(int64_t)f * T + t] = e;
             }
