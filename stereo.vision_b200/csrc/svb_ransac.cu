@@ -243,40 +243,39 @@ template <bool STAGED>
 __device__ __forceinline__ uint32_t fetch_rec(uint32_t idx, const uint32_t *__restrict__ rec, int stride, const uint32_t *s_rec) {
     return STAGED ? s_rec[idx] : __ldg(rec + (int64_t)idx * stride);
 }
-// The sample term of the thread version.  The scorer is bound by the alu pipe (shifts, masks, compares, selects: 61 % active
-// against 19 % for the fma pipe that executes IMAD, profiles/r02w), so the work is moved to multiply-adds where it can be:
-//  * NARROW: when |Na| 2047 + |Nb| 2047 + |Ng| < 2^31 (every hypothesis of a 1024 x 544 image) the integer
-//    V = Na x + Nb y + Ng fits 32 bits and, with t = r >> 11 = y + 2^11 d and d = r >> 22,
-//        V = Ng + Na r + (Nb - 2^11 Na) t - 2^11 Nb d      (mod 2^32),
-//    three IMADs on the raw record and its two shifts -- no field is masked out.  2^31 is folded into the constant and
-//    the word is the low half of the double 2^52 + 2^31 + V.  Otherwise the 64-bit form of sample_term().  Both are exact
-//    integers, so the two forms give the same bits.
+// The sample term of the thread version.  The scorer is bound by instruction issue, the alu pipe first (shifts, masks, compares,
+// selects: 61 % active against 19 % for the fma pipe that executes IMAD, profiles/r02w), so the term is put in the form that
+// needs the fewest of those:
+//     |(Na x + Nb y + Ng)/d - det| = |W| (1/d),     W = Na x + Nb y + Ng - det d        (an exact integer)
+//  * one product with the table value 1/d instead of an fma that cancels: a single rounding, of a relative 2^-53;
+//  * NARROW: when |Na| 2047 + |Nb| 2047 + |Ng| + 255 |det| < 2^31 (every hypothesis of a 1024 x 544 image) W fits 32 bits
+//    and, with t = r >> 11 = y + 2^11 d and d = r >> 22,
+//        W = Ng + Na r + (Nb - 2^11 Na) t - (2^11 Nb + det) d      (mod 2^32),
+//    three IMADs on the raw record and its two shifts -- no field is masked out.  2^31 is folded into the constant and the
+//    word is the low half of the double 2^52 + 2^31 + W.  Otherwise the same integer from 32 x 32 + 64 multiply-adds;
+//  * STAGED: a draw >= M (skipped) reads the SENTINEL record 2^31 that the block keeps at s_rec[M]: its disparity field is
+//    512, the table is zero there, its term is exactly 0 and its bit 31 counts the rejection -- a min and a shift-add
+//    instead of compare, two selects and a predicated add.  From global memory the term is dropped by a select.
 //  * the shared-memory reads are plain indexing: the compiler folds scaling and window base into the address operand.
+#define RANSAC_SENTINEL 0x80000000u
 struct NarrowPlane { uint32_t c0, c1, c2, c3; };
-template <bool STAGED, bool NARROW>
-__device__ __forceinline__ double thread_term(const TrialPlane &h, const NarrowPlane &n, uint32_t idx, const uint32_t *__restrict__ rec,
-                                              int stride, const uint32_t *s_rec, const double *s_invd) {
-    const uint32_t r = STAGED ? s_rec[idx] : __ldg(rec + (int64_t)idx * stride);
-    const uint32_t d = r >> 22;                                                   // bits 30-31 of a record are zero
-    double lin;
+struct WidePlane { int na, nb, mdet; long long base; };           // base: Ng + 2^40 with the exponent bits of 2^52 on top
+template <bool NARROW>
+__device__ __forceinline__ double record_term(const WidePlane &h, const NarrowPlane &n, uint32_t r, const double *s_invd) {
+    const uint32_t d = r >> 22;                                                   // bits 30-31 of a cloud record are zero
+    double w;
     if (NARROW) {
         const uint32_t v = n.c1 * r + (n.c2 * (r >> 11) + (n.c3 * d + n.c0));
-        lin = __hiloint2double(0x43300000, (int)v) - 4503601774854144.0;         // 2^52 + 2^31
+        w = __hiloint2double(0x43300000, (int)v) - 4503601774854144.0;           // 2^52 + 2^31 (I2F.F64 on the idle xu pipe: no faster)
     } else {
-        const long long L = mad_wide(h.nb, (int)((r >> 11) & 0x7FFu), mad_wide(h.na, (int)(r & 0x7FFu), h.base));
-        lin = __longlong_as_double(L) - 4504699138998272.0;                      // 2^52 + 2^40
+        const long long L = mad_wide(h.mdet, (int)(d & 0xFFu), mad_wide(h.nb, (int)((r >> 11) & 0x7FFu), mad_wide(h.na, (int)(r & 0x7FFu), h.base)));
+        w = __longlong_as_double(L) - 4504699138998272.0;                        // 2^52 + 2^40
     }
-    return fma(lin, s_invd[d], -h.det);                                           // its magnitude is the term
-}
-// acc += |t| if the draw i is below M, else one more rejected draw: one compare, a predicated fp64 add and a predicated
-// integer add (written out because the compiler turns the branch into two selects on the alu pipe)
-__device__ __forceinline__ void take_if_below(double &acc, int &rejected, double t, uint32_t i, uint32_t M) {
-    asm("{\n\t.reg .pred p;\n\t.reg .f64 a;\n\tsetp.lt.u32 p, %3, %4;\n\tabs.f64 a, %2;\n\t@p add.f64 %0, %0, a;\n\t@!p add.s32 %1, %1, 1;\n\t}"
-        : "+d"(acc), "+r"(rejected) : "d"(t), "r"(i), "r"(M));
+    return w * s_invd[d];                                                         // its magnitude is the term
 }
 // the first S values below M of the trial's scrambled congruential sequence, summed
 template <bool STAGED, bool NARROW>
-__device__ __forceinline__ double thread_walk(const TrialPlane &h, const NarrowPlane &n, uint32_t key, uint32_t M, int S,
+__device__ __forceinline__ double thread_walk(const WidePlane &h, const NarrowPlane &n, uint32_t key, uint32_t M, int S,
                                               const uint32_t *__restrict__ rec, int stride, const uint32_t *s_rec, const double *s_invd) {
     // The k-bit state lives in the TOP k bits of a word (X = x << (32 - k)), so the products wrap modulo 2^k by themselves:
     // per draw one multiply-add for the state and shift, xor-and, multiply, shift, xor, multiply-high for the index --
@@ -286,8 +285,11 @@ __device__ __forceinline__ double thread_walk(const TrialPlane &h, const NarrowP
     const uint32_t A = (mix32(key ^ 0x51ED270Bu) & ~7u) | 5u, C = (mix32(key + 0x9E3779B9u) | 1u) << up;
     uint32_t X = mix32(key ^ 0xC2B2AE35u) << up;
     double acc0 = 0.0, acc1 = 0.0;
-    int drawn = 0, rejected = 0;
-    while (drawn - rejected + 8 <= S) {                           // eight draws in flight; at most eight more are taken
+    int drawn = 0;
+    uint32_t rejected = 0;
+    // eight draws in flight; at most eight more are taken.  (drawn <= 2^k: a full period holds M >= S accepted values; the
+    // bound only matters for records that break the format -- bit 31 set -- and then stops the walk instead of hanging)
+    while (drawn - (int)rejected + 8 <= S && drawn < (int)down) {
         uint32_t is[8];
 #pragma unroll
         for (int u = 0; u < 8; ++u) {
@@ -297,20 +299,27 @@ __device__ __forceinline__ double thread_walk(const TrialPlane &h, const NarrowP
         }
         double ts[8];
 #pragma unroll
-        for (int u = 0; u < 8; ++u)                               // values >= M are skipped: their term is computed on record M - 1 and dropped
-            ts[u] = thread_term<STAGED, NARROW>(h, n, min(is[u], M - 1u), rec, stride, s_rec, s_invd);
-#pragma unroll
-        for (int u = 0; u < 8; u += 2) {
-            take_if_below(acc0, rejected, ts[u], is[u], M);
-            take_if_below(acc1, rejected, ts[u + 1], is[u + 1], M);
+        for (int u = 0; u < 8; ++u) {
+            if (STAGED) {
+                const uint32_t r = s_rec[min(is[u], M)];          // values >= M are skipped: the sentinel
+                rejected += r >> 31;
+                ts[u] = record_term<NARROW>(h, n, r, s_invd);
+            } else {
+                const bool keep = is[u] < M;
+                const double t = record_term<NARROW>(h, n, __ldg(rec + (int64_t)min(is[u], M - 1u) * stride), s_invd);
+                rejected += keep ? 0u : 1u;
+                ts[u] = keep ? t : 0.0;
+            }
         }
+#pragma unroll
+        for (int u = 0; u < 8; u += 2) { acc0 += fabs(ts[u]); acc1 += fabs(ts[u + 1]); }
         drawn += 8;
     }
-    for (int have = drawn - rejected; have < S;) {
+    for (int have = drawn - (int)rejected; have < S && drawn < (int)down; ++drawn) {
         const uint32_t Z = ((X ^ (X >> sh)) & top) * SCRAMBLE_MUL;
         const uint32_t i0 = __umulhi(Z ^ (Z >> sh), down);
         X = X * A + C;
-        if (i0 < M) { acc0 += fabs(thread_term<STAGED, NARROW>(h, n, i0, rec, stride, s_rec, s_invd)); ++have; }
+        if (i0 < M) { acc0 += fabs(record_term<NARROW>(h, n, STAGED ? s_rec[i0] : __ldg(rec + (int64_t)i0 * stride), s_invd)); ++have; }
     }
     return acc0 + acc1;
 }
@@ -335,15 +344,15 @@ __device__ __forceinline__ double score_trial_thread(const uint32_t *__restrict_
     const int det_i = x1 * (y2 - y3) + x2 * (y3 - y1) + x3 * (y1 - y2);
     const long long ng_i = (long long)(d1 * (x2 * y3 - x3 * y2)) + (long long)(d2 * (x3 * y1 - x1 * y3)) +
                            (long long)(d3 * (x1 * y2 - x2 * y1));
-    TrialPlane h;
+    WidePlane h;
     h.na = d1 * (y2 - y3) + d2 * (y3 - y1) + d3 * (y1 - y2);
     h.nb = d1 * (x3 - x2) + d2 * (x1 - x3) + d3 * (x2 - x1);
+    h.mdet = -det_i;
     h.base = ng_i + (1ll << 40) + (0x43300000ll << 32);
-    h.det = (double)det_i;
     NarrowPlane n;
-    n.c1 = (uint32_t)h.na; n.c2 = (uint32_t)h.nb - ((uint32_t)h.na << 11); n.c3 = 0u - ((uint32_t)h.nb << 11);
+    n.c1 = (uint32_t)h.na; n.c2 = (uint32_t)h.nb - ((uint32_t)h.na << 11); n.c3 = 0u - ((uint32_t)h.nb << 11) - (uint32_t)det_i;
     n.c0 = (uint32_t)ng_i + 0x80000000u;
-    const bool narrow = (long long)abs(h.na) * 2047 + (long long)abs(h.nb) * 2047 + llabs(ng_i) < (1ll << 31);
+    const bool narrow = (long long)abs(h.na) * 2047 + (long long)abs(h.nb) * 2047 + llabs(ng_i) + (long long)abs(det_i) * 255 < (1ll << 31);
     const double acc = narrow ? thread_walk<STAGED, true>(h, n, key, M, S, rec, stride, s_rec, s_invd)
                               : thread_walk<STAGED, false>(h, n, key, M, S, rec, stride, s_rec, s_invd);
     const double Na = (double)h.na, Nb = (double)h.nb, Ng = (double)ng_i;
@@ -421,6 +430,7 @@ ransac_score_persistent(const uint32_t *__restrict__ mcloud, int stride, int64_t
                     bulk_g2s((char *)s_rec + o, (const char *)rec + o, min(RANSAC_BULK_BYTES, bytes - o), &s_bar);
             }
             for (int i = nb + tid; i < Mi; i += (int)blockDim.x) s_rec[i] = __ldg(rec + (int64_t)i * stride);
+            if (PER_THREAD && tid == 0) s_rec[Mi] = RANSAC_SENTINEL;  // what a skipped draw reads (thread_walk)
             if (bulk && nb > 0) { mbar_wait(&s_bar, phase); phase ^= 1u; }
             __syncthreads();
         }
@@ -473,7 +483,7 @@ extern "C" int svb_ransac_score(const uint32_t *mcloud, int rec_stride_words, in
     CamD c = make_camd(cam);
     ProfScope ps(K_RANSAC_SCORE, st);
     // shared-memory staging when the largest frame fits; otherwise cap = 0 and every gather goes to L2
-    size_t smem = (((size_t)max_m + 3) & ~(size_t)3) * sizeof(uint32_t);
+    size_t smem = (((size_t)max_m + 4) & ~(size_t)3) * sizeof(uint32_t);      // the records and the sentinel behind them
     int cap = max_m;
     if (max_m == 0 || smem > 200 * 1024) { smem = 16; cap = 0; }
     int dev = 0, sms = 148;
