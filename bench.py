@@ -272,8 +272,9 @@ def run_b200(args):
     ref_mask = res.road_mask.cpu().numpy() if not args.no_e2e else None      # `res` is a view: later legs overwrite it
     planes_valid = float(res.planes[:, 7].sum().item())
 
-    # ---- the two-stream variant of the step (RoadPath(overlap=True)): measured beside `value`, not part of it
-    eng.overlap = True
+    # ---- the one-stream variant of the step (RoadPath(overlap=False): whole-batch launches, nothing concurrent): measured
+    # beside `value`, not part of it.  The per-kernel leg below runs this way too, so that a kernel's time is its own.
+    eng.overlap = False
     for _ in range(3):
         step()
     torch.cuda.synchronize()
@@ -283,8 +284,7 @@ def run_b200(args):
         step()
     s1.record()
     torch.cuda.synchronize()
-    overlap_ms = s0.elapsed_time(s1) / 5
-    eng.overlap = False
+    one_stream_ms = s0.elapsed_time(s1) / 5
     # ---- the step without the 8-byte coloured cloud (RoadPath(emit_cloud=False): masks, planes, counts only -- what the
     # end-to-end entry point returns); beside `value`, not part of it
     eng_nc = RoadPath((H, W), step=args.step, trials=T, samples=S, carmask=cm, max_frames=F, device=dev, emit_cloud=False)
@@ -307,6 +307,7 @@ def run_b200(args):
     torch.cuda.synchronize()
     prof = N.profile_read()
     N.profile_enable(False)
+    eng.overlap = True
     Nm, Mm, Km, Rm = counts.mean(axis=0)
     kern = {k: {"ms_per_launch": v[0] / v[1], "launches": v[1]} for k, v in prof.items()}
     tot = sum(v["ms_per_launch"] for v in kern.values())
@@ -513,7 +514,8 @@ def run_b200(args):
             "vs_baseline": None, "dtype": "u8 in / f64 plane + reprojection arithmetic", "data": "synthetic",
             "config": {"workload": "config 2: %d-frame sequence per GPU, 1024x544, previous-disparity fill, step %d, "
                                    "%d RANSAC trials x %d samples, counter-based on-device draws" % (F, args.step, T, S),
-                       "ms_per_step_two_streams": overlap_ms,
+                       "streams": "two half-batches on two streams (RoadPath's default for >= 192 frames; same results)",
+                       "ms_per_step_one_stream": one_stream_ms,
                        "ms_per_step_without_cloud": nocloud_ms, "without_cloud_same_masks_planes_counts": nocloud_same,
                        "frames_per_step_per_gpu": F, "l2": "inputs (%.0f MB/sequence) exceed the 126 MB L2; no flush needed"
                                                           % ((disp_h.nbytes + bgr_h.nbytes) / 1e6),
@@ -524,7 +526,8 @@ def run_b200(args):
             "roofline": {"kernel": dom, "bound": "hbm", "achieved": d["gbs"], "peak": peak, "unit": "GB/s",
                          "frac": d["gbs"] / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                          "alg_bytes_per_launch": d["alg_bytes"], "ms_per_launch": d["ms_per_launch"],
-                         "share_of_step": d["share"], "longest_kernel": top},
+                         "share_of_step": d["share"], "longest_kernel": top,
+                         "timed": "whole-batch launches on one stream (3 steps with event tracing; `share_of_step` is of the one-stream step)"},
             "kernels": {k: {kk: (round(vv, 6) if isinstance(vv, float) else vv) for kk, vv in v.items()} for k, v in kern.items()},
         }
         gold, match = None, None

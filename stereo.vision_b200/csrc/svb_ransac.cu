@@ -258,6 +258,12 @@ __device__ __forceinline__ uint32_t fetch_rec(uint32_t idx, const uint32_t *__re
 //    instead of compare, two selects and a predicated add.  From global memory the term is dropped by a select.
 //  * the shared-memory reads are plain indexing: the compiler folds scaling and window base into the address operand.
 #define RANSAC_SENTINEL 0x80000000u
+// Draws in flight per thread.  From shared memory 4: 109.6 us, 8: 109.6, 12 and 16: 111 (not bound by latency).  A launch
+// that stages nothing (clouds too large for shared memory: step 1, 2048 x 1088) gathers from L2 and wants more loads in
+// flight; it has its own instantiation so that the staged kernel keeps its 80 registers.  The sum does not depend on the
+// depth: even raw draws go to one accumulator, odd ones to the other, in sequence order.
+#define RANSAC_UNROLL 8
+#define RANSAC_UNROLL_GLOBAL 16
 struct NarrowPlane { uint32_t c0, c1, c2, c3; };
 struct WidePlane { int na, nb, mdet; long long base; };           // base: Ng + 2^40 with the exponent bits of 2^52 on top
 template <bool NARROW>
@@ -274,7 +280,7 @@ __device__ __forceinline__ double record_term(const WidePlane &h, const NarrowPl
     return w * s_invd[d];                                                         // its magnitude is the term
 }
 // the first S values below M of the trial's scrambled congruential sequence, summed
-template <bool STAGED, bool NARROW>
+template <bool STAGED, bool NARROW, int U>
 __device__ __forceinline__ double thread_walk(const WidePlane &h, const NarrowPlane &n, uint32_t key, uint32_t M, int S,
                                               const uint32_t *__restrict__ rec, int stride, const uint32_t *s_rec, const double *s_invd) {
     // The k-bit state lives in the TOP k bits of a word (X = x << (32 - k)), so the products wrap modulo 2^k by themselves:
@@ -287,19 +293,19 @@ __device__ __forceinline__ double thread_walk(const WidePlane &h, const NarrowPl
     double acc0 = 0.0, acc1 = 0.0;
     int drawn = 0;
     uint32_t rejected = 0;
-    // eight draws in flight; at most eight more are taken.  (drawn <= 2^k: a full period holds M >= S accepted values; the
+    // U draws in flight; at most as many more are taken.  (drawn <= 2^k: a full period holds M >= S accepted values; the
     // bound only matters for records that break the format -- bit 31 set -- and then stops the walk instead of hanging)
-    while (drawn - (int)rejected + 8 <= S && drawn < (int)down) {
-        uint32_t is[8];
+    while (drawn - (int)rejected + U <= S && drawn < (int)down) {
+        uint32_t is[U];
 #pragma unroll
-        for (int u = 0; u < 8; ++u) {
+        for (int u = 0; u < U; ++u) {
             const uint32_t Z = ((X ^ (X >> sh)) & top) * SCRAMBLE_MUL;
             is[u] = __umulhi(Z ^ (Z >> sh), down);
             X = X * A + C;
         }
-        double ts[8];
+        double ts[U];
 #pragma unroll
-        for (int u = 0; u < 8; ++u) {
+        for (int u = 0; u < U; ++u) {
             if (STAGED) {
                 const uint32_t r = s_rec[min(is[u], M)];          // values >= M are skipped: the sentinel
                 rejected += r >> 31;
@@ -312,18 +318,22 @@ __device__ __forceinline__ double thread_walk(const WidePlane &h, const NarrowPl
             }
         }
 #pragma unroll
-        for (int u = 0; u < 8; u += 2) { acc0 += fabs(ts[u]); acc1 += fabs(ts[u + 1]); }
-        drawn += 8;
+        for (int u = 0; u < U; u += 2) { acc0 += fabs(ts[u]); acc1 += fabs(ts[u + 1]); }
+        drawn += U;
     }
     for (int have = drawn - (int)rejected; have < S && drawn < (int)down; ++drawn) {
         const uint32_t Z = ((X ^ (X >> sh)) & top) * SCRAMBLE_MUL;
         const uint32_t i0 = __umulhi(Z ^ (Z >> sh), down);
         X = X * A + C;
-        if (i0 < M) { acc0 += fabs(record_term<NARROW>(h, n, STAGED ? s_rec[i0] : __ldg(rec + (int64_t)i0 * stride), s_invd)); ++have; }
+        if (i0 < M) {
+            const double t = fabs(record_term<NARROW>(h, n, STAGED ? s_rec[i0] : __ldg(rec + (int64_t)i0 * stride), s_invd));
+            if (drawn & 1) acc1 += t; else acc0 += t;
+            ++have;
+        }
     }
     return acc0 + acc1;
 }
-template <bool STAGED>
+template <bool STAGED, int U>
 __device__ __forceinline__ double score_trial_thread(const uint32_t *__restrict__ rec, int stride, const uint32_t *s_rec,
                                                      uint32_t M, int S, const CamD &cam, double fB_over_S, const double *s_invd,
                                                      uint32_t key) {
@@ -353,8 +363,8 @@ __device__ __forceinline__ double score_trial_thread(const uint32_t *__restrict_
     n.c1 = (uint32_t)h.na; n.c2 = (uint32_t)h.nb - ((uint32_t)h.na << 11); n.c3 = 0u - ((uint32_t)h.nb << 11) - (uint32_t)det_i;
     n.c0 = (uint32_t)ng_i + 0x80000000u;
     const bool narrow = (long long)abs(h.na) * 2047 + (long long)abs(h.nb) * 2047 + llabs(ng_i) + (long long)abs(det_i) * 255 < (1ll << 31);
-    const double acc = narrow ? thread_walk<STAGED, true>(h, n, key, M, S, rec, stride, s_rec, s_invd)
-                              : thread_walk<STAGED, false>(h, n, key, M, S, rec, stride, s_rec, s_invd);
+    const double acc = narrow ? thread_walk<STAGED, true, U>(h, n, key, M, S, rec, stride, s_rec, s_invd)
+                              : thread_walk<STAGED, false, U>(h, n, key, M, S, rec, stride, s_rec, s_invd);
     const double Na = (double)h.na, Nb = (double)h.nb, Ng = (double)ng_i;
     const double Ap = cam.f * Na, Bp = cam.f * Nb, Cp = Ng + cam.cw * Na + cam.ch * Nb;
     const double e = acc * fB_over_S * rsqrt(Ap * Ap + Bp * Bp + Cp * Cp);
@@ -393,7 +403,7 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
 #define RANSAC_SMEM_THREADS 1024
 #define RANSAC_BULK_BYTES 32768u
 #define RANSAC_PT_THREADS 640                                     // thread-per-hypothesis blocks: one pass for the reference's 600 trials
-template <bool PER_THREAD>                                        // false: explicit indices, a warp per hypothesis
+template <bool PER_THREAD, int UG>                                // PER_THREAD false: explicit indices, a warp per hypothesis; UG: unroll of the global-memory walk
 __global__ void __launch_bounds__(PER_THREAD ? RANSAC_PT_THREADS : RANSAC_SMEM_THREADS, 1)
 ransac_score_persistent(const uint32_t *__restrict__ mcloud, int stride, int64_t slab_records,
                         const int32_t *__restrict__ counts, int cstride, int ccol,
@@ -439,8 +449,8 @@ ransac_score_persistent(const uint32_t *__restrict__ mcloud, int stride, int64_t
                 double e = INFINITY;
                 if (!none) {
                     const uint32_t key = trial_key(seed, frame0 + f, t);
-                    e = staged ? score_trial_thread<true>(rec, stride, s_rec, (uint32_t)Mi, S, cam, fB_over_S, s_invd, key)
-                               : score_trial_thread<false>(rec, stride, s_rec, (uint32_t)Mi, S, cam, fB_over_S, s_invd, key);
+                    e = staged ? score_trial_thread<true, RANSAC_UNROLL>(rec, stride, s_rec, (uint32_t)Mi, S, cam, fB_over_S, s_invd, key)
+                               : score_trial_thread<false, UG>(rec, stride, s_rec, (uint32_t)Mi, S, cam, fB_over_S, s_invd, key);
                 }
                 errors[(int64_t)f * T + t] = e;
             }
@@ -496,19 +506,26 @@ extern "C" int svb_ransac_score(const uint32_t *mcloud, int rec_stride_words, in
     // the opt-in to 200 KB of dynamic shared memory is a per-device function attribute: set once per device, not per call
     static bool attr_done[64] = {false};
     if (dev < 0 || dev >= 64 || !attr_done[dev]) {
-        cudaError_t e = cudaFuncSetAttribute(ransac_score_persistent<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(ransac_score_persistent<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        cudaError_t e = cudaFuncSetAttribute(ransac_score_persistent<false, RANSAC_UNROLL>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(ransac_score_persistent<true, RANSAC_UNROLL>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
         if (e != cudaSuccess) return (int)e;
         if (dev >= 0 && dev < 64) attr_done[dev] = true;
     }
     if (sample_idx)                                               // explicit draws: a warp per hypothesis (coalesced index loads)
-        ransac_score_persistent<false><<<blocks, threads, smem, st>>>(
+        ransac_score_persistent<false, RANSAC_UNROLL><<<blocks, threads, smem, st>>>(
             mcloud, rec_stride_words, slab_stride_records, counts, counts_stride, counts_col, F, T, S, cap, c,
             sample_idx, triple_idx, rng_seed, frame0, errors);
-    else                                                          // device draws: a thread per hypothesis
-        ransac_score_persistent<true><<<blocks, (flags & SVB_RANSAC_SHARE_SM) ? RANSAC_PT_THREADS / 2 : RANSAC_PT_THREADS, smem, st>>>(
-            mcloud, rec_stride_words, slab_stride_records, counts, counts_stride, counts_col, F, T, S, cap, c,
-            nullptr, nullptr, rng_seed, frame0, errors);
+    else {                                                        // device draws: a thread per hypothesis
+        const int pt = (flags & SVB_RANSAC_SHARE_SM) ? RANSAC_PT_THREADS / 2 : RANSAC_PT_THREADS;
+        if (cap > 0)
+            ransac_score_persistent<true, RANSAC_UNROLL><<<blocks, pt, smem, st>>>(
+                mcloud, rec_stride_words, slab_stride_records, counts, counts_stride, counts_col, F, T, S, cap, c,
+                nullptr, nullptr, rng_seed, frame0, errors);
+        else                                                      // nothing is staged: the deeper walk (same sums)
+            ransac_score_persistent<true, RANSAC_UNROLL_GLOBAL><<<blocks, pt, smem, st>>>(
+                mcloud, rec_stride_words, slab_stride_records, counts, counts_stride, counts_col, F, T, S, cap, c,
+                nullptr, nullptr, rng_seed, frame0, errors);
+    }
     SVB_LAUNCH_CHECK();
     return SVB_OK;
 }

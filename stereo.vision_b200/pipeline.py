@@ -73,17 +73,18 @@ class BatchResult:
 class RoadPath:
     def __init__(self, shape=(544, 1024), step=2, trials=600, samples=600, point_threshold=0.05,
                  colour_threshold=10, carmask=None, camera: Camera = DEFAULT_CAMERA, max_frames=1,
-                 device="cuda:0", use_reproj_table=True, road_path="sites", overlap=False, emit_cloud=True):
+                 device="cuda:0", use_reproj_table=True, road_path="sites", overlap=True, emit_cloud=True):
         if road_path not in ("sites", "records"):
             raise ValueError("road_path is 'sites' or 'records'")
         N.require_cuda()
         self.lib = N.load()
         self.device = torch.device(device)
-        # overlap=True: a batch of >= 32 frames is processed as two half-batches on two streams, the hypothesis scoring of
-        # one half (512-thread blocks) beside the projection / road-point kernels of the other.  Same results (after the
-        # fill, a frame depends on no other frame).  Off by default: measured on B200 it gains nothing (0.585 ms against
-        # 0.574 ms per 300 frames) -- every kernel of the path is limited by instruction issue, not by DRAM bandwidth
-        # (DESIGN.md 8), so there is no idle resource for the other half to use.
+        # overlap=True: a batch of >= 192 frames is processed as two half-batches on two streams, the hypothesis scoring of
+        # one half beside the projection / road-point kernels of the other.  Same results, bit for bit (after the fill, a
+        # frame depends on no other frame).  With the warp-per-hypothesis scorer (1024 threads, every register of the SM)
+        # this gained nothing (0.585 against 0.574 ms per 300 frames); the thread-per-hypothesis scorer leaves a fifth of
+        # the registers and its shared-memory gathers leave the DRAM idle: 0.466 against 0.493 ms.  Three ranges: 0.484,
+        # four: 0.503, six: 0.58 - 0.68 (the launches get too small).
         self.overlap, self._side, self._scratch2 = bool(overlap), None, None
         # emit_cloud=False: the 8-byte coloured cloud (a4's first product) is neither written nor is the colour image
         # read by the projection -- for callers who want masks, planes and counts only (SequenceStreamer).  The masked
@@ -213,12 +214,13 @@ class RoadPath:
         # ---- frame ranges: one, or two half-batches on two side streams (self.overlap).  Only the fill chains frames
         # (functions.py:140-147), so it runs range after range on the caller's stream; everything behind it is per frame.
         cur = torch.cuda.current_stream(dev)
-        split = self.overlap and F >= 2 * self.OVERLAP_MIN_FRAMES and not chain
-        ranges = [(0, F // 2), (F // 2, F)] if split else [(0, F)]
-        if split and self._side is None:
-            self._side = (torch.cuda.Stream(dev), torch.cuda.Stream(dev))
-            self._scratch2 = torch.empty_like(self.scratch)
-        scratches = [self.scratch, self._scratch2] if split else [self.scratch]
+        parts = self.OVERLAP_PARTS if (self.overlap and F >= self.OVERLAP_PARTS * self.OVERLAP_MIN_FRAMES and not chain) else 1
+        split = parts > 1
+        ranges = [(F * k // parts, F * (k + 1) // parts) for k in range(parts)]
+        if split and (self._side is None or len(self._side) < parts):
+            self._side = tuple(torch.cuda.Stream(dev) for _ in range(parts))
+            self._scratch2 = [torch.empty_like(self.scratch) for _ in range(parts - 1)]
+        scratches = [self.scratch] + (self._scratch2[:parts - 1] if split else [])
         ready = []
         if fill:
             prev_t = _as_cuda_u8(prev, dev) if prev is not None else None
@@ -237,22 +239,23 @@ class RoadPath:
         else:
             self.filled[:F].copy_(disp)
             if split:
-                ready = [torch.cuda.Event(), torch.cuda.Event()]
+                ready = [torch.cuda.Event()] * parts
                 ready[0].record(cur)
-                ready[1] = ready[0]
         for k, ((a, b), sc) in enumerate(zip(ranges, scratches)):
             stream = self._side[k] if split else cur
             if split:
                 stream.wait_event(ready[k])
             self._stages(a, b, bgr, ov, si, ti, seeds_t, chain, replay, seed, frame0, fill, sc, C.c_void_p(stream.cuda_stream),
-                         N.RANSAC_SHARE_SM if split else 0)
+                         0)
         if split:
-            cur.wait_stream(self._side[0])
-            cur.wait_stream(self._side[1])
+            for k in range(parts):
+                cur.wait_stream(self._side[k])
         N.count(len(ranges) * (KERNELS_PER_BATCH - 1 + self.road_launches + (1 if replay else 0)) + (0 if fill else 2))
         return res
 
-    OVERLAP_MIN_FRAMES = 16
+    OVERLAP_MIN_FRAMES = 96                # per range: one stream 0.153 / 0.199 / 0.287 / 0.329 / 0.392 / 0.501 ms at 32 / 64 / 128 / 160 / 200 / 280
+                                           # frames, two streams 0.261 / 0.264 / 0.295 / 0.327 / 0.377 / 0.476 ms
+    OVERLAP_PARTS = 2
 
     def _stages(self, a, b, bgr, ov, si, ti, seeds_t, chain, replay, seed, frame0, fill, scratch, st, score_flags):
         """a2-a14 of frames [a, b) of the batch, enqueued on stream `st`: clouds, draws, hypotheses, plane, road points."""

@@ -84,8 +84,8 @@ def test_small_ragged_shapes(cuda, shape, step):
 
 
 def test_two_half_batches_on_two_streams_equal_one_batch(cuda):
-    """RoadPath(overlap=True) runs a batch of >= 32 frames as two half-batches on two streams (512-thread scorer blocks
-    beside the other half's kernels): every output equals the one-batch run's, for device draws, the reference's draws
+    """RoadPath(overlap=True), the default, runs a batch of >= 192 frames (here: OVERLAP_MIN_FRAMES lowered) as two half-batches on two streams (the scorer
+    of one half beside the other half's kernels): every output equals the one-batch run's, for device draws, the reference's draws
     (per-frame seeds) and explicit indices; an odd frame count; two calls in a row (buffers of the last call in flight)."""
     import torch
     from stereo.vision_b200.pipeline import RoadPath
@@ -94,6 +94,7 @@ def test_two_half_batches_on_two_streams_equal_one_batch(cuda):
     cm = _carmask(disp.shape[1:])
     one = RoadPath(trials=T, samples=S, carmask=cm, max_frames=F, overlap=False)
     two = RoadPath(trials=T, samples=S, carmask=cm, max_frames=F, overlap=True)
+    two.OVERLAP_MIN_FRAMES = 16
     seeds = [synth.ransac_seed(14, t) for t in range(F)]
     for kw in (dict(seed=77, frame0=5), dict(py_seeds=seeds), dict(seed=78)):
         a = one.process(disp, bgr, **kw)
