@@ -111,24 +111,26 @@ int svb_cloud_export(const uint32_t *records, int rec_stride_words, int n, const
                      uint16_t *hue, void *stream);
 
 /* ---- a5-a7  RANSAC / planarFitting / randomNonCollinearPoints       functions.py:240-298
- * One warp scores one hypothesis: plane through the triple (abc = inv([P1;P2;P3]).1, fp64),
- * error = mean |P.abc - 1| / |abc| over the trial's S sample points (functions.py:275,289).
+ * Scores T hypotheses per frame: plane through the triple (abc = inv([P1;P2;P3]).1), error = mean |P.abc - 1| / |abc|
+ * over the trial's S sample points (functions.py:275,289), evaluated in exact-integer form.
  * errors[f*T + t] = +inf for a singular triple or a frame with M_f < S (functions.py:286,294).
+ * Records are x | y << 11 | d << 22 with bits 30-31 ZERO (what svb_project_compact writes).
  *
  * Index source
  *   sample_idx != NULL : explicit draws, sample_idx int32 [F,T,S], triple_idx int32 [F,T,3]
- *                        (the replay of Python's `random` stream) -- parity mode;
- *   sample_idx == NULL : counter-based on-device draws keyed by (rng_seed, frame0+f, t):
- *                        S distinct indices (keyed bijection + cycle walking) and triples redrawn
- *                        while exactly collinear (functions.py:251-259) -- throughput mode.
+ *                        (the replay of Python's `random` stream) -- parity mode; one warp per hypothesis;
+ *   sample_idx == NULL : counter-based on-device draws keyed by (rng_seed, frame0+f, t): S distinct indices (the first
+ *                        S values below M_f of a scrambled full-period congruential sequence) and triples redrawn while
+ *                        exactly collinear (functions.py:251-259) -- throughput mode; one thread per hypothesis.
  *                        svb_ransac_dump_indices writes the same draws out for the oracle.
  * max_m: an upper bound of every frame's cloud size known to the host (e.g. the number of lattice sites
- *        inside carmask), or 0.  When 4*max_m bytes fit in shared memory each block stages its frame's
+ *        inside carmask), or 0.  When 4*(max_m+1) bytes fit in shared memory each block stages its frame's
  *        cloud there once and the S gathers of a hypothesis become shared-memory reads; frames that
- *        turn out larger than max_m, and max_m = 0, gather from global memory (L2).
- * flags: SVB_RANSAC_SHARE_SM = blocks of 512 threads instead of 1024 (half of an SM's registers), so that blocks of a
- *        kernel launched on another stream can run on the same SM at the same time (pipeline.RoadPath(overlap=True)
- *        runs two half-batches on two streams).  Same results. */
+ *        turn out larger than max_m, and max_m = 0, gather from global memory (L2).  The errors do not depend on it,
+ *        nor on F or the flags: a hypothesis' terms are summed in one fixed order (tests/test_gpu_configs.py).
+ * flags: SVB_RANSAC_SHARE_SM = blocks of half the size (half of an SM's registers), so that blocks of a kernel launched
+ *        on another stream find room on the same SM.  Same results.  pipeline.RoadPath no longer sets it: with a thread
+ *        per hypothesis the full-size block leaves that room already. */
 #define SVB_RANSAC_SHARE_SM 1
 int svb_ransac_score(const uint32_t *mcloud, int rec_stride_words, int64_t slab_stride_records,
                      const int32_t *counts, int counts_stride, int counts_col,

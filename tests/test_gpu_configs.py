@@ -168,3 +168,33 @@ def test_result_hash_is_the_single_gpu_hash(cuda):
         disp, bgr = synth.make_sequence(seq, F)
         r = eng.process(disp, bgr, py_seeds=[synth.ransac_seed(seq, t) for t in range(F)])
         assert shard.result_sha(r.road_mask, r.planes, r.counts) == gold["sha"][str(seq)], seq
+
+
+def test_scores_do_not_depend_on_staging_batch_or_flags(cuda):
+    """svb_ransac_score with device draws sums a hypothesis' terms in one fixed order (even raw draws into one accumulator,
+    odd ones into the other): the errors are the same bits whether the cloud is staged in shared memory (max_m >= M) or
+    gathered from L2 (max_m = 0: the instantiation with 16 loads in flight; max_m < M: the global path of the staged kernel),
+    whether a frame is scored alone or in a batch, and with SVB_RANSAC_SHARE_SM -- which is what lets a 30-frame chunk of
+    the streamer and a 300-frame resident batch be compared bit for bit."""
+    import ctypes as C
+    import torch
+    import stereo.vision_b200._native as N
+    from stereo.vision_b200.pipeline import RoadPath
+    F, T, S = 5, 600, 400
+    disp, bgr = synth.make_sequence(9, F)
+    eng = RoadPath(trials=T, samples=S, carmask=_carmask(disp.shape[1:]), max_frames=F)
+    res = eng.process(disp, bgr, seed=41, frame0=3)
+    want = res.errors.cpu().numpy().view(np.uint64).copy()
+    m = res.counts[:, 1].cpu().numpy()
+    assert (m >= S).all() and np.isfinite(res.errors.cpu().numpy()).mean() > 0.99
+
+    def score(f0, n, max_m, flags):
+        err = torch.full((n, T), -1.0, dtype=torch.float64, device=cuda)
+        N.check(eng.lib.svb_ransac_score(N.ptr(eng.mcloud[f0:]), 1, eng.L, N.ptr(eng.counts[f0:]), 4, 1, n, T, S, max_m,
+                                         C.byref(eng._cam), None, None, 41, 3 + f0, flags, N.ptr(err), N.stream_ptr()), "svb_ransac_score")
+        torch.cuda.synchronize()
+        return err.cpu().numpy().view(np.uint64)
+    for max_m, flags in ((eng.max_m, 0), (0, 0), (int(m.min()) - 1, 0), (eng.max_m, N.RANSAC_SHARE_SM), (0, N.RANSAC_SHARE_SM)):
+        assert np.array_equal(score(0, F, max_m, flags), want), (max_m, flags)
+    for f in range(F):                                        # one frame per launch
+        assert np.array_equal(score(f, 1, eng.max_m, 0), want[f:f + 1]), f
