@@ -90,10 +90,17 @@ struct ChunkBits {
 
 __device__ __forceinline__ uint32_t byte_of(const uint32_t *w, int j) { return (w[j >> 2] >> ((j & 3) * 8)) & 0xFFu; }
 
-// nonzero-byte bitmap of 4 packed bytes -> 4 bits
+// nonzero-byte bitmap of 4 packed bytes -> 4 bits.  Bit 7 of every byte of ((w & 0x7f..) + 0x7f..) | w says "byte != 0"
+// (no carry leaves a byte); the product with 2^21 + 2^14 + 2^7 + 1 brings bits 7, 15, 23, 31 to bits 28..31 without
+// two terms meeting in one bit -- five instructions, one of them on the fma pipe (the emulated __vcmpne4 and the three
+// shift-ors it replaced were 14 % of proj_write's instructions, and the kernel is bound by the alu pipe).
 __device__ __forceinline__ uint32_t nz4(uint32_t w) {
-    uint32_t m = __vcmpne4(w, 0u) & 0x01010101u;       // 1 per nonzero byte
-    return (m | (m >> 7) | (m >> 14) | (m >> 21)) & 0xFu;
+    const uint32_t t = (((w & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | w) & 0x80808080u;
+    return (t * 0x00204081u) >> 28;
+}
+// ... of 16 packed bytes -> 16 bits (bit j = byte j)
+__device__ __forceinline__ uint32_t nz16(const uint32_t *w) {
+    return nz4(w[0]) + nz4(w[1]) * 16u + nz4(w[2]) * 256u + nz4(w[3]) * 4096u;
 }
 
 // lattice sites among the 16 pixels starting at x0 (x % step == 0 and x < W-1)
@@ -139,12 +146,11 @@ __device__ __forceinline__ ChunkBits load_chunk(const uint8_t *__restrict__ drow
             m[w] = mv;
         }
     }
-    uint32_t nzd = nz4(c.d[0]) | (nz4(c.d[1]) << 4) | (nz4(c.d[2]) << 8) | (nz4(c.d[3]) << 12);
+    uint32_t nzd = nz16(c.d);
     uint32_t site = site_bits(x0, W, step);
     c.vm = nzd & site;
     if (HAS_MASK) {
-        uint32_t nzm = nz4(m[0]) | (nz4(m[1]) << 4) | (nz4(m[2]) << 8) | (nz4(m[3]) << 12);
-        c.mm = c.vm & nzm;
+        c.mm = c.vm & nz16(m);
     } else {
         c.mm = c.vm;
     }
@@ -300,7 +306,7 @@ __global__ void fill_seq_scalar(const uint8_t *__restrict__ raw, const uint8_t *
     }
 }
 
-#define FILL_UNROLL 16
+#define FILL_UNROLL 16          // frames per batch; 4 / 8 / 12 / 16: 97 / 94 / 90 / 98 us per 300 frames, the step is the same (12 only wins because 300 = 25 x 12)
 // ------------------------------------------------------------------ a1 fill + a4 counts, step 2, balanced
 // fill_seq_v16<.., COUNT> is bound by its slowest warps: a thread walks all F frames of its pixels, so the kernel
 // lasts as long as one warp's serial instruction stream (a warp issues once per ~5.6 cycles on the dependent
@@ -689,7 +695,9 @@ proj_write_kernel(const uint8_t *__restrict__ disp, const uint8_t *__restrict__ 
     int64_t slab = (int64_t)f * g.LH * g.LW;
     if (cloud) {
         uint64_t *dst = cloud + slab + base_v;
-        for (int i = threadIdx.x; i < tv; i += PROJ_THREADS) __stcs((unsigned long long *)dst + i, (unsigned long long)s_cloud[swz8(i)]);
+        // swz8 only touches the low four bits, with bits 4-7 of the index: swz8(t + 256 k) = swz8(t) + 256 k
+        const unsigned long long *src = (const unsigned long long *)s_cloud + swz8((int)threadIdx.x) - (int)threadIdx.x;
+        for (int i = threadIdx.x; i < tv; i += PROJ_THREADS) __stcs((unsigned long long *)dst + i, src[i]);
     }
     if (mcloud) {
         uint32_t *dst = mcloud + slab + base_m;
