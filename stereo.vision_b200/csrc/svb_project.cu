@@ -159,9 +159,17 @@ __device__ __forceinline__ ChunkBits load_chunk(const uint8_t *__restrict__ drow
 
 // ------------------------------------------------------------------ a1 fill
 // d' = sat_add(d, (d <= 2) ? prev : 0) on 4 bytes at once           functions.py:142-146
+// Written out on the word (the video intrinsics __vcmpleu4 / __vaddus4 are emulated on this part: ~20 instructions, all on
+// the alu pipe the kernel is bound by; this is 12, two of them multiplies):
+//   bit 7 of (d | 0x80) - 3 is clear iff (d & 0x7f) < 3, and no byte borrows (each is >= 0x80), so hb = "d <= 2" per byte;
+//   in a hole byte d <= 2, so (prev & 0x7f) + d <= 0x81 does not carry into the next byte (elsewhere the addend is 0);
+//   with prev's bit 7 put back the sum reaches 256 exactly when both bit 7s are set: saturate those bytes (cv2.add).
 __device__ __forceinline__ uint32_t fill4(uint32_t d, uint32_t prev) {
-    uint32_t hole = __vcmpleu4(d, 0x02020202u);        // 0xff where d <= 2
-    return __vaddus4(d, prev & hole);                  // cv2.add saturates
+    const uint32_t hb = ~(((d | 0x80808080u) - 0x03030303u) | d) & 0x80808080u;    // 0x80 where d <= 2
+    const uint32_t m = (hb >> 7) * 0xFFu;                                          // 0xff where d <= 2
+    const uint32_t s7 = (prev & m & 0x7F7F7F7Fu) + d;
+    const uint32_t ph = prev & hb;
+    return s7 | ph | (((s7 & ph) >> 7) * 0xFFu);
 }
 // One thread = 16 pixels for all F frames; the loads of the next U frames are issued back to back
 // (they do not depend on the recurrence) and then consumed in order.  A rolling window of loads does
