@@ -295,7 +295,7 @@ __device__ __forceinline__ double thread_walk(const WidePlane &h, const NarrowPl
     uint32_t rejected = 0;
     // U draws in flight; at most as many more are taken.  (drawn <= 2^k: a full period holds M >= S accepted values; the
     // bound only matters for records that break the format -- bit 31 set -- and then stops the walk instead of hanging)
-    while (drawn - (int)rejected + U <= S && drawn < (int)down) {
+    while (drawn - (int)rejected + U <= S && (uint32_t)drawn < down) {
         uint32_t is[U];
 #pragma unroll
         for (int u = 0; u < U; ++u) {
@@ -321,7 +321,7 @@ __device__ __forceinline__ double thread_walk(const WidePlane &h, const NarrowPl
         for (int u = 0; u < U; u += 2) { acc0 += fabs(ts[u]); acc1 += fabs(ts[u + 1]); }
         drawn += U;
     }
-    for (int have = drawn - (int)rejected; have < S && drawn < (int)down; ++drawn) {
+    for (int have = drawn - (int)rejected; have < S && (uint32_t)drawn < down; ++drawn) {
         const uint32_t Z = ((X ^ (X >> sh)) & top) * SCRAMBLE_MUL;
         const uint32_t i0 = __umulhi(Z ^ (Z >> sh), down);
         X = X * A + C;

@@ -198,3 +198,52 @@ def test_scores_do_not_depend_on_staging_batch_or_flags(cuda):
         assert np.array_equal(score(0, F, max_m, flags), want), (max_m, flags)
     for f in range(F):                                        # one frame per launch
         assert np.array_equal(score(f, 1, eng.max_m, 0), want[f:f + 1]), f
+
+
+@pytest.mark.parametrize("M", [400, 401, 512, 513, 1000, 4096, 4097, 32768, 32769, 60001])
+def test_device_draws_at_edge_cloud_sizes(cuda, M):
+    """svb_ransac_score's own draws on a synthetic masked cloud of exactly M records: M = S (every record is drawn), a power
+    of two (no draw is rejected), one more (every other draw is rejected), a cloud too large for shared memory.  The dumped
+    draws are S distinct indices below M; the scores equal the oracle's (functions.py:262-276, 289) on those draws, and
+    they are the same bits staged and from global memory."""
+    import ctypes as C
+    import torch
+    import stereo.vision_b200._native as N
+    from stereo.vision_b200.pipeline import RoadPath
+    T, S = 96, 400
+    rng = np.random.default_rng(M)
+    cam = no.cam_of(None)
+    eng = RoadPath(shape=(96, 160), step=2, trials=T, samples=S, carmask=np.full((96, 160), 255, np.uint8), max_frames=1)
+    sites = rng.choice(1023 * 543, size=M, replace=False)
+    x, y = (sites % 1023).astype(np.int64), (sites // 1023).astype(np.int64)
+    inv_z = 0.02 * (x - cam.cw) / cam.f - 0.9 * (y - cam.ch) / cam.f + 0.25
+    d = np.clip(np.rint(cam.f * cam.B * np.abs(inv_z)) + rng.integers(-2, 3, M), 1, 254).astype(np.int64)
+    rec = torch.from_numpy((x | (y << 11) | (d << 22)).astype(np.int32)).to(cuda).reshape(1, M)
+    counts = torch.tensor([[M, M, 0, 0]], dtype=torch.int32, device=cuda)
+    si = torch.empty((1, T, S), dtype=torch.int32, device=cuda)
+    ti = torch.empty((1, T, 3), dtype=torch.int32, device=cuda)
+    st = N.stream_ptr()
+    N.check(eng.lib.svb_ransac_dump_indices(N.ptr(rec), 1, M, N.ptr(counts), 4, 1, 1, T, S, C.byref(eng._cam), 77, 5,
+                                            N.ptr(si), N.ptr(ti), st), "dump")
+    errs = {}
+    for name, max_m in (("staged", M), ("global", 0)):
+        e = torch.full((1, T), -1.0, dtype=torch.float64, device=cuda)
+        N.check(eng.lib.svb_ransac_score(N.ptr(rec), 1, M, N.ptr(counts), 4, 1, 1, T, S, max_m, C.byref(eng._cam), None, None,
+                                         77, 5, 0, N.ptr(e), st), "score")
+        errs[name] = e.cpu().numpy()[0]
+    ex = torch.full((1, T), -1.0, dtype=torch.float64, device=cuda)             # the warp-per-hypothesis scorer on the same draws
+    N.check(eng.lib.svb_ransac_score(N.ptr(rec), 1, M, N.ptr(counts), 4, 1, 1, T, S, M, C.byref(eng._cam), N.ptr(si), N.ptr(ti),
+                                     0, 0, 0, N.ptr(ex), st), "score explicit")
+    torch.cuda.synchronize()
+    s, t3 = si.cpu().numpy()[0], ti.cpu().numpy()[0]
+    assert s.min() >= 0 and s.max() < M and (np.diff(np.sort(s, axis=1), axis=1) > 0).all()
+    if M == S:
+        assert (np.sort(s, axis=1) == np.arange(M)).all()
+    assert np.array_equal(errs["staged"].view(np.uint64), errs["global"].view(np.uint64))
+    Z = cam.f * cam.B / d.astype(np.float64)
+    xyz = np.stack([((x - cam.cw) * Z) / cam.f, ((y - cam.ch) * Z) / cam.f, Z], axis=1)
+    _, _, want = no.ransac_from_indices(xyz, s, t3, sites=np.stack([y, x], axis=1))
+    got = errs["staged"]
+    assert np.array_equal(np.isinf(got), np.isinf(want)) and np.isfinite(got).sum() > T // 2
+    fin = np.isfinite(want)
+    assert np.allclose(got[fin], want[fin], rtol=1e-9, atol=0) and np.allclose(ex.cpu().numpy()[0][fin], want[fin], rtol=1e-9, atol=0)
