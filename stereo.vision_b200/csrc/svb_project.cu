@@ -413,12 +413,24 @@ __device__ __forceinline__ void fill_walk(const uint8_t *__restrict__ raw, const
         t += U;
         if (!more2) break;
     }
-    for (; t < F; ++t) {
-        uint32_t c = step(ld_words<P>(src + (int64_t)t * frame, true), t);
-        if (COUNT && lat) {
-            c = __reduce_add_sync(0xffffffffu, c);
-            if (lane == 0 && c) atomicAdd(counts_row + (int64_t)t * groups, c);
+    // the remaining n < U frames as one partial batch: their loads are issued together (a tail of single frames pays a
+    // load-to-use latency per frame)
+    const int n = F - t;
+    if (n > 0) {
+#pragma unroll
+        for (int u = 0; u < U; ++u) if (u < n) d[u] = ld_words<P>(src + (int64_t)(t + u) * frame, true);
+        uint32_t mine = 0;
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            if (u < n) {
+                uint32_t c = step(d[u], t + u);
+                if (COUNT && lat) {
+                    c = __reduce_add_sync(0xffffffffu, c);
+                    if (lane == u) mine = c;
+                }
+            }
         }
+        if (COUNT && lat && lane < n && mine) atomicAdd(counts_row + (int64_t)(t + lane) * groups, mine);
     }
 }
 
