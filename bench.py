@@ -300,9 +300,12 @@ def run_b200(args):
     nocloud_same = bool(torch.equal(rn.road_mask, res.road_mask) and torch.equal(rn.planes, res.planes) and torch.equal(rn.counts, res.counts))
     del eng_nc, rn
     torch.cuda.empty_cache()
-    # ---- per-kernel device times (3 extra steps with event tracing on) -> roofline of the dominant kernel
+    # ---- per-kernel device times (5 extra steps with event tracing on, after 2 untraced ones: the frees above leave the
+    # GPU idle and the first launch after an idle gap is slow) -> roofline of the dominant kernel
+    for _ in range(2):
+        step()
     N.profile_enable(True)
-    for _ in range(3):
+    for _ in range(5):
         step()
     torch.cuda.synchronize()
     prof = N.profile_read()
@@ -527,7 +530,7 @@ def run_b200(args):
                          "frac": d["gbs"] / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                          "alg_bytes_per_launch": d["alg_bytes"], "ms_per_launch": d["ms_per_launch"],
                          "share_of_step": d["share"], "longest_kernel": top,
-                         "timed": "whole-batch launches on one stream (3 steps with event tracing; `share_of_step` is of the one-stream step)"},
+                         "timed": "whole-batch launches on one stream (5 steps with event tracing; `share_of_step` is of the one-stream step)"},
             "kernels": {k: {kk: (round(vv, 6) if isinstance(vv, float) else vv) for kk, vv in v.items()} for k, v in kern.items()},
         }
         gold, match = None, None
