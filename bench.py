@@ -562,7 +562,9 @@ def run_b200(args):
                           "ms_per_step": e2e_ms_max, "chunk_frames": args.chunk, "matches_resident_run": e2e["match"],
                           "api": "stereo.vision_b200.pipeline.SequenceStreamer(pack_mask=True).run (pinned host frames -> pinned host road masks as "
                                  "bit rows + planes + counts; the unpacked masks are checked against the resident run outside the timed region; "
-                                 "only the lattice rows of the disparity and of the colour image are uploaded)",
+                                 "uploaded: the lattice rows of the disparity and, once a chunk's planes are known, the lattice rows of the colour "
+                                 "image that can hold a near-plane point -- nothing else of it is ever read)",
+                          "upload": e2e["upload"], "with_every_lattice_row_of_the_colour_image": e2e["lattice"],
                           "gpu_launches_per_step": e2e["launches_per_step"], "clocks": e2e["clocks"],
                           "link": dict(e2e["link"], h2d_gbs_min_over_ranks=link_min[0], d2h_gbs_min_over_ranks=link_min[1]),
                           "h2d_gbs": e2e["h2d"] / (e2e_ms_max * 1e-3) / 1e9, "d2h_gbs": e2e["d2h"] / (e2e_ms_max * 1e-3) / 1e9}
@@ -766,8 +768,25 @@ def run_e2e(args, torch, dev, camera, cm, disp_p, bgr_p, seed, ref_counts, clk=N
         match = match and bool(np.array_equal(sr.unpack_road_mask(out["road_bits"]), ref_mask))
     shard.barrier()
     link = measure_link(torch, dev, sr.h2d_bytes, sr.d2h_bytes)
-    return {"ms": ms, "h2d": sr.h2d_bytes, "d2h": sr.d2h_bytes, "match": match, "link": link,
-            "launches_per_step": len(range(0, F, C)) * (sr.engines[0].road_launches + 4 + 1)}      # fill, write, score, finalize + svb_pack_mask
+    # beside it: the same with every lattice row of the colour image uploaded (upload="lattice", the r02s streamer)
+    h2d, d2h, mode = sr.h2d_bytes, sr.d2h_bytes, sr.upload
+    road_launches = sr.engines[0].road_launches
+    del sr
+    sl = SequenceStreamer((H, W), step=args.step, trials=args.trials, samples=args.samples, carmask=cm, camera=camera,
+                          chunk=C, device=dev, pack_mask=True, upload="lattice")
+    for i in range(2):
+        outs[i] = sl.run(disp_p, bgr_p, seed=seed, out=outs[i])
+    torch.cuda.synchronize()
+    e0.record()
+    for i in range(3):
+        outs[i % 2] = sl.run(disp_p, bgr_p, seed=seed, out=outs[i % 2])
+    e1.record()
+    torch.cuda.synchronize()
+    lattice = {"frames_per_s": F / (e0.elapsed_time(e1) / 3 * 1e-3), "h2d_bytes_per_step": sl.h2d_bytes,
+               "same_results": bool(torch.equal(outs[0]["road_bits"], out["road_bits"]) and torch.equal(outs[0]["planes"], out["planes"]))}
+    del sl
+    return {"ms": ms, "h2d": h2d, "d2h": d2h, "match": match, "link": link, "upload": mode, "lattice": lattice,
+            "launches_per_step": len(range(0, F, C)) * (road_launches + 4 + 1)}      # fill, write, score, finalize + svb_pack_mask
 
 
 # ------------------------------------------------------------------ reference arm (CPU)

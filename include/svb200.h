@@ -373,6 +373,13 @@ int svb_road_points_sites(const uint8_t *filled, const uint8_t *bgr, const doubl
  * (pinned) host source and the device destination (cudaMemcpy2DAsync), i.e. the rows land where a full-frame
  * copy would have put them and the rows in between are left untouched (never read). */
 int svb_upload_rows(const void *h_src, void *d_dst, int64_t pitch_bytes, int64_t width_bytes, int64_t rows, void *stream);
+/* A block of rows of every frame of a batch in one 3-D copy: both sides hold `frames` frames of `rows_per_frame` rows that
+ * are `pitch_bytes` apart; rows [first, first + nrows) of every frame are copied, `width_bytes` of each.  With pitch =
+ * step x the image row size this addresses lattice rows: the end-to-end streamer sends the colour image only on the lattice
+ * rows that can hold a near-plane point of the chunk's planes (pipeline.SequenceStreamer(upload="needed")); nothing else
+ * of the colour image is ever read (functions.py:195 is only evaluated for cloud points, stereovision.py:103 for near ones). */
+int svb_upload_row_block(const void *h_src, void *d_dst, int64_t pitch_bytes, int64_t width_bytes, int64_t rows_per_frame,
+                         int64_t first, int64_t nrows, int64_t frames, void *stream);
 
 /* ---- tracing: per-kernel CUDA-event timing, off by default.
  * svb_profile_enable(1) clears the records and brackets every later kernel launch of this library

@@ -18,7 +18,7 @@ HUE_BINS = 1001
 HIST_STRIDE = 1024
 PLANE_STRIDE = 8
 RANSAC_SHARE_SM = 1
-ABI_VERSION = 14
+ABI_VERSION = 15
 SVB_OK, SVB_E_NULL, SVB_E_SHAPE, SVB_E_ARG, SVB_E_SCRATCH, SVB_E_LIMIT = 0, -1, -2, -3, -4, -5      # include/svb200.h
 COMPACT_STATIC_MAX_N = 4194304
 SVB_MAX_DIM = 2048                                                                  # csrc/svb_common.cuh
@@ -101,6 +101,7 @@ SIGNATURES = {
     "svb_reproject_bits_words": (L, [I, I]),
     "svb_reproject_bits": (I, [I, I, CAMP, P, P, P]),
     "svb_upload_rows": (I, [P, P, L, L, L, P]),
+    "svb_upload_row_block": (I, [P, P, L, L, L, L, L, L, P]),
     "svb_profile_enable": (I, [I]),
     "svb_profile_kernels": (I, []),
     "svb_profile_get": (I, [I, C.c_char_p, I, C.POINTER(D), C.POINTER(I)]),

@@ -1,7 +1,8 @@
 // ABI bookkeeping: version and error strings.
 #include "svb_common.cuh"
+#include <string.h>
 
-extern "C" int svb_version(void) { return 14; }
+extern "C" int svb_version(void) { return 15; }
 
 extern "C" const char *svb_error_string(int code) {
     switch (code) {
@@ -23,6 +24,25 @@ extern "C" int svb_upload_rows(const void *h_src, void *d_dst, int64_t pitch_byt
     if (pitch_bytes < width_bytes || width_bytes < 1 || rows < 1) return SVB_E_ARG;
     cudaError_t e = cudaMemcpy2DAsync(d_dst, (size_t)pitch_bytes, h_src, (size_t)pitch_bytes, (size_t)width_bytes, (size_t)rows,
                                       cudaMemcpyHostToDevice, (cudaStream_t)stream);
+    return e == cudaSuccess ? SVB_OK : (int)e;
+}
+
+// The same for a block of rows of every frame of a batch: frames of `rows_per_frame` pitched rows each (the same geometry on
+// both sides), rows [first, first + nrows) of each of `frames` frames, width_bytes of every row -- one 3-D copy.
+extern "C" int svb_upload_row_block(const void *h_src, void *d_dst, int64_t pitch_bytes, int64_t width_bytes, int64_t rows_per_frame,
+                                    int64_t first, int64_t nrows, int64_t frames, void *stream) {
+    if (!h_src || !d_dst) return SVB_E_NULL;
+    if (pitch_bytes < width_bytes || width_bytes < 1 || rows_per_frame < 1 || frames < 1 || first < 0 || nrows < 1 ||
+        first + nrows > rows_per_frame) return SVB_E_ARG;
+    cudaMemcpy3DParms p;
+    memset(&p, 0, sizeof(p));
+    p.srcPtr = make_cudaPitchedPtr(const_cast<void *>(h_src), (size_t)pitch_bytes, (size_t)pitch_bytes, (size_t)rows_per_frame);
+    p.dstPtr = make_cudaPitchedPtr(d_dst, (size_t)pitch_bytes, (size_t)pitch_bytes, (size_t)rows_per_frame);
+    p.srcPos = make_cudaPos(0, (size_t)first, 0);
+    p.dstPos = make_cudaPos(0, (size_t)first, 0);
+    p.extent = make_cudaExtent((size_t)width_bytes, (size_t)nrows, (size_t)frames);
+    p.kind = cudaMemcpyHostToDevice;
+    cudaError_t e = cudaMemcpy3DAsync(&p, (cudaStream_t)stream);
     return e == cudaSuccess ? SVB_OK : (int)e;
 }
 

@@ -321,9 +321,9 @@ def test_sequence_streamer_matches_resident_path(cuda):
     assert np.array_equal(out["road_mask"].numpy(), ref["road_mask"])
     assert np.array_equal(out["planes"].numpy(), ref["planes"])
     assert sr.h2d_bytes == F * (544 * 1024 + 272 * 1024 * 3) and ref["road_mask"].any()
-    # the default: only the lattice rows of the disparity travel as well.  N (cloud points) is still the full count:
+    # upload="lattice": only the lattice rows of the disparity travel as well.  N (cloud points) is still the full count:
     # it is a count over lattice sites
-    sl = SequenceStreamer(trials=T, samples=S, carmask=cm, chunk=3)
+    sl = SequenceStreamer(trials=T, samples=S, carmask=cm, chunk=3, upload="lattice")
     outl = sl.run_sync(torch.from_numpy(disp).pin_memory(), torch.from_numpy(bgr).pin_memory(), seed=21)
     for k in ("counts", "road_mask", "planes"):
         assert np.array_equal(outl[k].numpy(), ref[k]), k
@@ -333,7 +333,7 @@ def test_sequence_streamer_matches_resident_path(cuda):
         assert np.array_equal(sl.engines[k].filled[j, ::2].cpu().numpy(), ref["filled"][t, ::2]), t
     # bit-packed masks over the link, and an engine that emits no cloud (the streamer's default) against one that does
     assert not sl.engines[0].emit_cloud and sl.engines[0].cloud.numel() == 0 and eng.emit_cloud
-    sp = SequenceStreamer(trials=T, samples=S, carmask=cm, chunk=3, pack_mask=True)
+    sp = SequenceStreamer(trials=T, samples=S, carmask=cm, chunk=3, pack_mask=True, upload="lattice")
     outp = sp.run_sync(torch.from_numpy(disp).pin_memory(), torch.from_numpy(bgr).pin_memory(), seed=21)
     assert "road_mask" not in outp and outp["road_bits"].shape == (F, 544 * 32)
     assert np.array_equal(sp.unpack_road_mask(outp["road_bits"]), ref["road_mask"])
@@ -387,3 +387,54 @@ def test_road_sites_writes_stay_inside_their_buffers(cuda):
         torch.cuda.synchronize()
         rz.check()
         assert torch.equal(mask, r.road_mask) and torch.equal(hist, r.hist[:F]) and torch.equal(counts[:, 2:], r.counts[:, 2:])
+
+
+def test_streamer_sends_only_the_colour_rows_the_planes_allow(cuda):
+    """SequenceStreamer(upload="needed"), the default: disparity rows up, a1-a7, planes down, near_row_ranges(), only the
+    colour rows that can hold a near-plane point up, a8-a14.  Same masks, planes and counts as upload="lattice" -- with
+    device draws and with the reference's, for chunks that do not divide the sequence, a first frame without a plane
+    (nothing to upload for it), runs back to back, and with the colour buffers full of garbage outside the uploaded rows."""
+    import torch
+    from stereo.vision_b200.pipeline import RoadPath, SequenceStreamer
+    F, T, S = 11, 200, 300
+    disp, bgr = synth.make_sequence(5, F)
+    disp[0] = 0                                                     # prev = None and no disparity: frame 0 has no cloud, no plane
+    cm = _carmask(disp.shape[1:])
+    dp, bp = torch.from_numpy(disp).pin_memory(), torch.from_numpy(bgr).pin_memory()
+    seeds = [synth.ransac_seed(5, t) for t in range(F)]
+    for kw in (dict(seed=3), dict(py_seeds=seeds)):
+        ref = SequenceStreamer(trials=T, samples=S, carmask=cm, chunk=4, upload="lattice").run_sync(dp, bp, **kw)
+        assert ref["planes"][0, 7] == 0 and (ref["planes"][1:, 7] == 1).all() and ref["road_mask"][1:].any()
+        for chunk in (3, 4, 16):
+            sn = SequenceStreamer(trials=T, samples=S, carmask=cm, chunk=chunk)
+            assert sn.upload == "needed"
+            for c in sn.cin:
+                c.random_(0, 256)                                    # whatever is not uploaded must not matter
+            out = None
+            for _ in range(2):
+                out = sn.run_sync(dp, bp, out=out, **kw)
+                for k in ("counts", "road_mask"):
+                    assert torch.equal(out[k], ref[k]), (k, chunk, list(kw))
+                assert torch.equal(out["planes"].view(torch.int64), ref["planes"].view(torch.int64)), (chunk, list(kw))   # bits: frame 0 is NaN
+            lattice = F * (272 * 1024 + 272 * 1024 * 3)
+            assert F * 272 * 1024 < sn.h2d_bytes < 0.8 * lattice, (sn.h2d_bytes, lattice)
+    # bit-packed masks, pageable numpy input
+    sp = SequenceStreamer(trials=T, samples=S, carmask=cm, chunk=5, pack_mask=True)
+    outp = sp.run_sync(disp, bgr, seed=3)
+    ref = SequenceStreamer(trials=T, samples=S, carmask=cm, chunk=5, upload="lattice").run_sync(dp, bp, seed=3)
+    assert np.array_equal(sp.unpack_road_mask(outp["road_bits"]), ref["road_mask"].numpy())
+    # the two halves of RoadPath.process on their own
+    eng = RoadPath(trials=T, samples=S, carmask=cm, max_frames=F, emit_cloud=False)
+    r = eng.process(disp, bgr, seed=3)
+    whole = {k: getattr(r, k).cpu().numpy().copy() for k in ("counts", "planes", "road_mask", "hist")}
+    half = eng.process(disp, None, seed=3, road=False)
+    assert np.array_equal(half.planes.cpu().numpy().view(np.int64), whole["planes"].view(np.int64))
+    eng.process_road(torch.from_numpy(bgr).to(cuda))
+    for k in ("counts", "planes", "road_mask", "hist"):
+        assert np.array_equal(getattr(half, k).cpu().numpy().view(np.uint8), whole[k].view(np.uint8)), k
+    with pytest.raises(RuntimeError):
+        eng.process_road(torch.from_numpy(bgr).to(cuda))
+    with pytest.raises(ValueError):
+        RoadPath(trials=T, samples=S, carmask=cm, max_frames=F).process(disp, None, seed=3, road=False)
+    with pytest.raises(ValueError):
+        SequenceStreamer(trials=T, samples=S, carmask=cm, chunk=4, upload="needed", step=1)
