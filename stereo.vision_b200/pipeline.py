@@ -414,7 +414,7 @@ class SequenceStreamer:
     """
 
     def __init__(self, shape=(544, 1024), step=2, trials=600, samples=600, carmask=None,
-                 camera: Camera = DEFAULT_CAMERA, chunk=30, device="cuda:0", upload="auto", pack_mask=False, **kw):
+                 camera: Camera = DEFAULT_CAMERA, chunk=60, device="cuda:0", upload="auto", pack_mask=False, **kw):
         if upload not in ("auto", "lattice", "full", "needed"):
             raise ValueError("upload is 'auto', 'lattice', 'full' or 'needed'")
         # pack_mask=True: the road masks come back as bit rows ("road_bits" int32 [F, H * ceil(W / 32)], bit x & 31 of
