@@ -45,6 +45,8 @@ extern "C" {
 
 #define SVB_HUE_BINS     1001 /* keys '0.0' .. '1.0' of functions.py:76-78 */
 #define SVB_HIST_STRIDE  1024 /* uint32 per frame in histogram arrays */
+#define SVB_HIST_SPANS   1023 /* slot of a histogram row where svb_road_points_sites leaves the number of 16-pixel colour spans
+                                (48 bytes each) it read for the frame -- what crosses the link when the image is read in place */
 #define SVB_PLANE_STRIDE 8    /* doubles per frame in plane arrays, see svb_ransac_finalize */
 
 /* camera constants, functions.py:15-22 */

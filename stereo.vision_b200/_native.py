@@ -17,6 +17,7 @@ LIB_PATH = os.path.join(_PKG, "libsvb200.so")
 HUE_BINS = 1001
 HIST_STRIDE = 1024
 PLANE_STRIDE = 8
+HIST_SPANS = 1023            # SVB_HIST_SPANS: slot of a histogram row with the colour spans the sites kernel read
 RANSAC_SHARE_SM = 1
 ABI_VERSION = 15
 SVB_OK, SVB_E_NULL, SVB_E_SHAPE, SVB_E_ARG, SVB_E_SCRATCH, SVB_E_LIMIT = 0, -1, -2, -3, -4, -5      # include/svb200.h

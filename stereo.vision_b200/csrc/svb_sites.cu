@@ -130,7 +130,7 @@ road_sites_near_kernel(const uint8_t *__restrict__ filled, const uint8_t *__rest
     }
     uint2 *buf = s_buf[warp];
     uint32_t *seg = list + (((int64_t)f * ST_PARTS + part) * ST_WARPS + warp) * g.seg_cap;
-    int fill = 0, written = 0;                                   // warp-uniform: staged records, list entries written
+    int fill = 0, written = 0, spans = 0;                        // warp-uniform: staged records, list entries written, colour spans read
     const uint32_t *rb_y = rbits + (size_t)g.W * 8;                // the (y, d) rows of the displacement table
     auto dense = [&](uint2 rc, bool on) {                        // rc.x = x | y << 16, rc.y = B | G << 8 | R << 16 | d << 24
         if (on) {
@@ -178,7 +178,9 @@ road_sites_near_kernel(const uint8_t *__restrict__ filled, const uint8_t *__rest
                 if (exact_near_site(cam, x0 + o, y, d, pl[0], pl[1], pl[2], pl[4])) nb |= 1u << j;
             }
         }
-        if (!__any_sync(0xffffffffu, nb != 0)) continue;
+        const uint32_t holders = __ballot_sync(0xffffffffu, nb != 0);
+        if (!holders) continue;
+        spans += __popc(holders);
 
         // colour of my 16 pixels (48 bytes) where I hold a near site
         uint32_t cw[12];
@@ -247,6 +249,7 @@ road_sites_near_kernel(const uint8_t *__restrict__ filled, const uint8_t *__rest
     if (lane == 0) {
         *my_count = written;
         if (written) atomicAdd(&counts_out[f * 4 + 2], written);
+        if (spans) atomicAdd(&s_h[SVB_HIST_SPANS], (uint32_t)spans);
     }
     __syncthreads();
     uint32_t *gh = hist + (int64_t)f * SVB_HIST_STRIDE;
@@ -254,6 +257,7 @@ road_sites_near_kernel(const uint8_t *__restrict__ filled, const uint8_t *__rest
         const uint32_t v = s_h[k];
         if (v) atomicAdd(&gh[k], v);
     }
+    if (tid == 0 && s_h[SVB_HIST_SPANS]) atomicAdd(&gh[SVB_HIST_SPANS], s_h[SVB_HIST_SPANS]);   // bookkeeping, not a hue bin
 }
 
 // colour filter + scatter: warp w of CTA p re-reads segment (p, w) of frame f

@@ -256,8 +256,13 @@ def test_road_paths_agree(cuda):
     sites = RoadPath(carmask=cm, max_frames=F, samples=400)           # the default: a8-a14 from disparity + colour
     assert sites.sites_road
     rs = to_host(sites.process(disp, bgr, seed=5))
-    for k in ("road_mask", "counts", "hist", "planes"):
+    for k in ("road_mask", "counts", "planes"):
         assert np.array_equal(ra[k], rs[k]), ("sites", k)
+    assert np.array_equal(ra["hist"][:, :no.HUE_BINS], rs["hist"][:, :no.HUE_BINS])
+    # slot SVB_HIST_SPANS of a row: the 16-pixel colour spans the sites kernel read (at least one per 8 near points at step 2)
+    spans = rs["hist"][:, 1023]
+    assert (ra["hist"][:, no.HUE_BINS:] == 0).all() and (rs["hist"][:, no.HUE_BINS:1023] == 0).all()
+    assert (spans * 8 >= rs["counts"][:, 2]).all() and (spans <= 272 * 64).all() and (spans > 0).all()
     for mode in (1, 3):
         N.load().svb_debug_force_two_pass(mode)
         try:
@@ -390,7 +395,7 @@ def test_road_sites_writes_stay_inside_their_buffers(cuda):
 
 
 def test_streamer_sends_only_the_colour_rows_the_planes_allow(cuda):
-    """SequenceStreamer(upload="needed"), the default: disparity rows up, a1-a7, planes down, near_row_ranges(), only the
+    """SequenceStreamer(upload="needed") and "pull" (the default): disparity rows up, a1-a7, planes down, near_row_ranges(), only the
     colour rows that can hold a near-plane point up, a8-a14.  Same masks, planes and counts as upload="lattice" -- with
     device draws and with the reference's, for chunks that do not divide the sequence, a first frame without a plane
     (nothing to upload for it), runs back to back, and with the colour buffers full of garbage outside the uploaded rows."""
@@ -405,9 +410,9 @@ def test_streamer_sends_only_the_colour_rows_the_planes_allow(cuda):
     for kw in (dict(seed=3), dict(py_seeds=seeds)):
         ref = SequenceStreamer(trials=T, samples=S, carmask=cm, chunk=4, upload="lattice").run_sync(dp, bp, **kw)
         assert ref["planes"][0, 7] == 0 and (ref["planes"][1:, 7] == 1).all() and ref["road_mask"][1:].any()
-        for chunk in (3, 4, 16):
-            sn = SequenceStreamer(trials=T, samples=S, carmask=cm, chunk=chunk)
-            assert sn.upload == "needed"
+        for chunk, mode in ((3, "needed"), (4, "needed"), (16, "needed"), (3, "pull"), (4, "auto"), (16, "pull")):
+            sn = SequenceStreamer(trials=T, samples=S, carmask=cm, chunk=chunk, upload=mode)
+            assert sn.upload == ("pull" if mode == "auto" else mode)        # "pull": the road kernel reads the pinned frames in place
             for c in sn.cin:
                 c.random_(0, 256)                                    # whatever is not uploaded must not matter
             out = None
@@ -417,10 +422,13 @@ def test_streamer_sends_only_the_colour_rows_the_planes_allow(cuda):
                     assert torch.equal(out[k], ref[k]), (k, chunk, list(kw))
                 assert torch.equal(out["planes"].view(torch.int64), ref["planes"].view(torch.int64)), (chunk, list(kw))   # bits: frame 0 is NaN
             lattice = F * (272 * 1024 + 272 * 1024 * 3)
-            assert F * 272 * 1024 < sn.h2d_bytes < 0.8 * lattice, (sn.h2d_bytes, lattice)
-    # bit-packed masks, pageable numpy input
+            assert F * 272 * 1024 < sn.h2d_bytes < (0.8 if sn.upload == "needed" else 0.7) * lattice, (sn.upload, sn.h2d_bytes, lattice)
+            if sn.upload == "pull":                                  # 48 bytes per span the kernel reports, at least one per 8 near points
+                assert (sn.h2d_bytes - F * 272 * 1024) % 48 == 0 and sn.h2d_bytes - F * 272 * 1024 >= 48 * int(ref["counts"][:, 2].sum()) // 8
+    # bit-packed masks, pageable numpy input (cannot be read in place: the colour rows are copied as with upload="needed")
     sp = SequenceStreamer(trials=T, samples=S, carmask=cm, chunk=5, pack_mask=True)
     outp = sp.run_sync(disp, bgr, seed=3)
+    assert sp.upload == "pull" and sp.h2d_bytes > F * 272 * 1024
     ref = SequenceStreamer(trials=T, samples=S, carmask=cm, chunk=5, upload="lattice").run_sync(dp, bp, seed=3)
     assert np.array_equal(sp.unpack_road_mask(outp["road_bits"]), ref["road_mask"].numpy())
     # the two halves of RoadPath.process on their own
