@@ -471,7 +471,8 @@ class SequenceStreamer:
         py_seeds: F integers -> the reference's own draws per frame (RoadPath.process), else device draws keyed by `seed`.
         Returns dict(road_mask uint8 [F,H,W], planes float64 [F,8], counts int32 [F,4]) of pinned CPU tensors
         (pass the previous result as `out` to reuse them).  Asynchronous: the current stream waits for the
-        result; synchronise (or use run_sync) before reading it on the host."""
+        result; synchronise (or use run_sync) before reading it on the host -- and leave disp / bgr alone until then:
+        the copies are asynchronous, and with upload="pull" the road kernel reads the pinned colour frames in place."""
         if isinstance(disp, np.ndarray):
             disp = torch.from_numpy(disp)
         if isinstance(bgr, np.ndarray):
