@@ -361,7 +361,11 @@ int svb_road_points(const uint64_t *cloud, const int32_t *counts, const double *
  * same pixel).  filled uint8 [F,H,W]; bgr uint8 [F,H,W,3] (lattice rows suffice); reproj_bits is required.
  * counts[f*4+2] = K_f, counts[f*4+3] = R_f; counts[f*4+0..1] are not touched.  Applies when
  * svb_road_sites_supported(H,W,step) = 1 (step 1 or 2); otherwise SVB_E_ARG and the caller uses
- * svb_road_points.  scratch: svb_road_sites_scratch_bytes(F,H,W,step), 4-byte aligned. */
+ * svb_road_points.  scratch: svb_road_sites_scratch_bytes(F,H,W,step), 4-byte aligned.
+ * bgr is read through ordinary loads, 48 bytes (a lane's 16 pixels) at a time and only where a near point sits, so it may
+ * just as well be the caller's PINNED HOST frames (mapped into the device's address space): then only those spans cross
+ * the link and no copy of the colour image is made (pipeline.SequenceStreamer(upload="pull")).  hist[f][SVB_HIST_SPANS]
+ * returns the number of spans read for frame f; hist[f][0 .. SVB_HUE_BINS) are the hue bins. */
 int svb_road_sites_supported(int H, int W, int step);
 int64_t svb_road_sites_scratch_bytes(int F, int H, int W, int step);
 int svb_road_points_sites(const uint8_t *filled, const uint8_t *bgr, const double *planes, int F, int H, int W, int step,
