@@ -34,10 +34,10 @@ __host__ __device__ __forceinline__ uint32_t trial_key(uint64_t seed, int frame,
 // congruential sequence modulo 2^k >= M,
 //   x_{n+1} = (a x_n + c) mod 2^k,   a = 5 (mod 8), c odd, x_0 uniform        (per-trial a, c, x_0 from the key)
 // -- a permutation of [0, 2^k) (Hull-Dobell), so the S indices are distinct (random.sample draws without
-// replacement, functions.py:286).  Lane l walks the sub-sequence x_l, x_{l+32}, ... with the 32-step map
-// x -> A32 x + C32: one multiply-add and one mask per draw; values >= M (fewer than half) are skipped by a vote.
-// The low five bits of x_n repeat every 32 steps and run through all 32 values, so the lanes of a round read 32
-// different shared-memory banks.  An earlier version drew a systematic sample (start + j * stride, stride from a
+// replacement, functions.py:286); values >= M (fewer than half) are skipped.  The scorer walks the sequence with one
+// thread per trial (thread_walk); svb_ransac_dump_indices writes the same draws out with a warp per trial, lane l
+// walking the sub-sequence x_l, x_{l+32}, ... with the 32-step map x -> A32 x + C32 (make_draws) and the accepted draws
+// counted round by round, lane by lane -- the same order.  An earlier version drew a systematic sample (start + j * stride, stride from a
 // table of 256 primes): the winner's mean error over 240 frames was then distributed differently from the
 // reference's draws (two-sample KS p = 8e-17, median 0.231 against 0.271: an arithmetic progression clusters on
 // image columns, and the minimum over 600 trials finds the lucky clusters).
