@@ -124,7 +124,7 @@ __device__ __forceinline__ bool trial_triple(const uint32_t *__restrict__ rec, i
     return false;
 }
 
-// ------------------------------------------------------------------ score: one warp per hypothesis
+// ------------------------------------------------------------------ score: one warp per hypothesis (explicit indices)
 // Arithmetic of the score.  With Z = fB/d, X = (x-cw) Z/f, Y = (y-ch) Z/f the plane a X + b Y + c Z = 1
 // through three points reads, in pixel coordinates,  al x + be y + ga = d/fB  (al = a/f, be = b/f,
 // ga = c - al cw - be ch): a 3x3 system with the INTEGER matrix [x_i y_i 1] and right-hand side d_i/fB.
@@ -156,7 +156,7 @@ __device__ __forceinline__ bool warp_triple(const uint32_t *__restrict__ rec, in
 
 // One warp scores one trial with explicit indices (parity mode).  STAGED: the S sample gathers read the frame's records from shared memory
 // (s_rec, stride 1); otherwise from global memory (L2).  Writes the mean error (or +inf) to *err_out.
-// Per sample: one draw (add, subtract, min), one gather, and  |(Na x + Nb y + Ng)/d - det|  as two 32x32+64 integer multiply-adds whose
+// Per sample: one index load (coalesced), one gather, and  |(Na x + Nb y + Ng)/d - det|  as two 32x32+64 integer multiply-adds whose
 // 64-bit result IS the bit pattern of the double 2^52 + 2^40 + (Na x + Nb y + Ng) (the bias and the
 // exponent are folded into the addend), one subtraction, one fma with the table value 1/d, one add.
 __device__ __forceinline__ long long mad_wide(int a, int b, long long c) {       // a * b + c, signed 32 x 32 + 64
@@ -235,16 +235,15 @@ __device__ __forceinline__ void score_trial(const uint32_t *__restrict__ rec, in
 // the reduction and the final scaling, ~240 instructions -- is executed by all 32 lanes, and the lanes need a vote and a
 // population count per round to agree on which draws count.  With device draws nothing has to be read coalesced, so a thread
 // can own a hypothesis: it walks the trial's congruential sequence x_0, x_1, ... itself and keeps the first S values below
-// M.  That is the sequence, in the order, that the warp version consumes (lane l walks x_l, x_(l+32), ... and accepted draws
-// count round by round, lane by lane), so the SAMPLE SETS ARE THE SAME and svb_ransac_dump_indices describes both; only
-// the order of the floating-point sum differs.  Explicit indices (parity mode) keep the warp version: their loads want
-// to be coalesced.
+// M.  That is the sequence, in the order, that svb_ransac_dump_indices writes out with a warp per trial (lane l walks x_l,
+// x_(l+32), ... and accepted draws count round by round, lane by lane): the dumped indices ARE the scorer's sample.
+// Explicit indices (parity mode) keep the warp version: their loads want to be coalesced.
 template <bool STAGED>
 __device__ __forceinline__ uint32_t fetch_rec(uint32_t idx, const uint32_t *__restrict__ rec, int stride, const uint32_t *s_rec) {
     return STAGED ? s_rec[idx] : __ldg(rec + (int64_t)idx * stride);
 }
 // The sample term of the thread version.  The scorer is bound by instruction issue, the alu pipe first (shifts, masks, compares,
-// selects: 61 % active against 19 % for the fma pipe that executes IMAD, profiles/r02w), so the term is put in the form that
+// selects: 61 % active against 19 % for the fma pipe that executes IMAD in the first thread version), so the term is put in the form that
 // needs the fewest of those:
 //     |(Na x + Nb y + Ng)/d - det| = |W| (1/d),     W = Na x + Nb y + Ng - det d        (an exact integer)
 //  * one product with the table value 1/d instead of an fma that cancels: a single rounding, of a relative 2^-53;
@@ -397,7 +396,7 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
 
 // Persistent kernel: block b owns the contiguous range [b, b+1) * F*T/gridDim.x of the (frame, trial) pairs,
 // i.e. a few consecutive frames.  Entering a frame it stages that frame's masked cloud (<= 4 bytes x max_m)
-// in shared memory with bulk copies (TMA), then its 32 warps share it: the S gathers of a hypothesis are
+// in shared memory with bulk copies (TMA), then its warps share it: the S gathers of a hypothesis are
 // shared-memory reads (no 32-byte-sector over-fetch from L2).  Frames that do not fit (or whose records
 // are strided) gather from global memory instead.
 #define RANSAC_SMEM_THREADS 1024
