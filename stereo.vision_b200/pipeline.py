@@ -417,9 +417,12 @@ class SequenceStreamer:
     """
 
     def __init__(self, shape=(544, 1024), step=2, trials=600, samples=600, carmask=None,
-                 camera: Camera = DEFAULT_CAMERA, chunk=60, device="cuda:0", upload="auto", pack_mask=False, **kw):
+                 camera: Camera = DEFAULT_CAMERA, chunk=60, device="cuda:0", upload="auto", pack_mask=False, buffers=3, **kw):
         if upload not in ("auto", "lattice", "full", "needed", "pull"):
             raise ValueError("upload is 'auto', 'pull', 'needed', 'lattice' or 'full'")
+        # buffers: engines / disparity buffers in rotation.  upload="pull" uses all of them (a chunk's disparity copy then never
+        # waits for the road kernel of the chunk before last, which runs at the pace of the link: 85.8 k frames/s with three,
+        # 81.4 k with two, 83.7 k with four); the other modes alternate the first two.
         # pack_mask=True: the road masks come back as bit rows ("road_bits" int32 [F, H * ceil(W / 32)], bit x & 31 of
         # word x >> 5 of a row = pixel x; unpack_road_mask() expands them) -- an eighth of the bytes over the link
         self.pack_mask = bool(pack_mask)
@@ -428,17 +431,18 @@ class SequenceStreamer:
         self.step, self.chunk = int(step), int(chunk)
         self.device = torch.device(device)
         self.engines = [RoadPath(shape, step=step, trials=trials, samples=samples, carmask=carmask, camera=camera,
-                                 max_frames=self.chunk, device=device, **kw) for _ in range(2)]
+                                 max_frames=self.chunk, device=device, **kw) for _ in range(max(2, int(buffers)))]
         H, W, C_, dev = self.H, self.W, self.chunk, self.device
-        self.din = [torch.zeros((C_, H, W), dtype=torch.uint8, device=dev) for _ in range(2)]
+        nb = len(self.engines)
+        self.din = [torch.zeros((C_, H, W), dtype=torch.uint8, device=dev) for _ in range(nb)]
         self.cin = [torch.zeros((C_, H, W, 3), dtype=torch.uint8, device=dev) for _ in range(2)]
         self.s_in, self.s_cmp, self.s_out = (torch.cuda.Stream(dev) for _ in range(3))
         self.words = int(N.load().svb_bits_words(H, W))
-        self.bits = [torch.empty((C_, self.words), dtype=torch.int32, device=dev) for _ in range(2)] if self.pack_mask else None
+        self.bits = [torch.empty((C_, self.words), dtype=torch.int32, device=dev) for _ in range(nb)] if self.pack_mask else None
         self.lib = N.load()
         self.d2h_bytes = 0
-        self._last_cmp, self._last_out = [None, None], [None, None]      # last use of buffer / engine k, across run() calls
-        self._last_head = [None, None]
+        self._last_cmp, self._last_out = [None] * nb, [None] * nb        # last use of buffer / engine k, across run() calls
+        self._last_head = [None] * nb
         e = self.engines[0]
         can_need = not e.emit_cloud and e.sites_road and self.step >= 2 and H % self.step == 0
         if upload in ("needed", "pull") and not can_need:
@@ -649,11 +653,11 @@ class SequenceStreamer:
         if self._spans_host is None or self._spans_host.shape[0] < F:
             self._spans_host = torch.zeros((F,), dtype=torch.int32).pin_memory()
         ev_cmp, ev_out = {}, {}
-        h2d = 0
+        h2d, nb = 0, len(self.engines)
         for i, (a, b) in enumerate(chunks):
-            k, n = i % 2, b - a
-            busy_cmp = ev_cmp[i - 2] if i >= 2 else self._last_cmp[k]
-            busy_out = ev_out[i - 2] if i >= 2 else self._last_out[k]
+            k, n = i % nb, b - a
+            busy_cmp = ev_cmp[i - nb] if i >= nb else self._last_cmp[k]
+            busy_out = ev_out[i - nb] if i >= nb else self._last_out[k]
             with torch.cuda.stream(s_in):
                 if busy_cmp is not None:
                     s_in.wait_event(busy_cmp)                 # disparity buffer k is free once its last chunk was computed
@@ -664,7 +668,7 @@ class SequenceStreamer:
                 s_cmp.wait_event(ev_in)
                 if busy_out is not None:
                     s_cmp.wait_event(busy_out)                # engine k's outputs were read back
-                prev = self.engines[1 - k].filled[chunks[i - 1][1] - chunks[i - 1][0] - 1] if i else None
+                prev = self.engines[(i - 1) % nb].filled[chunks[i - 1][1] - chunks[i - 1][0] - 1] if i else None
                 r = self.engines[k].process(self.din[k][:n], None, prev=prev, seed=seed, frame0=a,
                                             py_seeds=None if py_seeds is None else py_seeds[a:b], road=False)
                 self.engines[k].process_road(bgr[a:b])        # pinned host frames, read in place
